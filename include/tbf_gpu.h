@@ -1,0 +1,233 @@
+/* tbf_gpu.h -- C-ABI of the B200 batched renderer for tuneBfree's
+ * tonewheel -> scanner-vibrato -> Leslie hot path.
+ *
+ * Plain C, plain pointers and sizes.  Every entry point cites the reference
+ * interface (file:line under the reference tree) it replaces or mirrors.
+ * The reference has no FFI layer of its own: its "operator API" is the set of
+ * C-style engine functions over heap structs (src/tonegen.h:565-597,
+ * src/vibrato.h:70-79, src/whirl.h:223-272, src/global_inst.h:32-40) that
+ * the LV2 / CLAP / JACK hosts call once per 128-sample fragment
+ * (src/clap.cpp:244-270, b_synth/lv2.cpp:212-239, src/main.cpp:243-292).
+ *
+ * All functions return 0 (TBF_OK) or a negative tbf_status; none of them
+ * calls exit() (the reference exits on OOM: src/tonegen.cpp:382-386).
+ */
+#ifndef TBF_GPU_H
+#define TBF_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TBF_FRAGMENT 128     /* BUFFER_SIZE_SAMPLES, src/tonegen.h:53           */
+#define TBF_NOF_WHEELS 256   /* NOF_WHEELS, src/tonegen.h:79 (wheels are 1..256) */
+#define TBF_NOF_BUSES 27     /* NOF_BUSES, src/tonegen.h:49                      */
+#define TBF_NOF_DRAWBARS 9   /* NOF_DRAWBARS, src/tonegen.h:51                   */
+#define TBF_MAX_KEYS 384     /* MAX_KEYS, src/tonegen.h:93                       */
+#define TBF_NOF_FREQS 300    /* NOF_FREQS, src/tonegen.h:85                      */
+#define TBF_MAX_PARTIALS 12  /* MAX_PARTIALS, src/tonegen.h:488                  */
+#define TBF_VIB_TBL 2048     /* INCTBL_SIZE, src/vibrato.h:38                    */
+#define TBF_VIB_BUF 1024     /* BUF_SIZE_BYTES, src/vibrato.h:40                 */
+#define TBF_WHIRL_DISPLC 16384 /* WHIRL_DISPLC_SIZE, src/whirl.h:33              */
+#define TBF_WHIRL_BUF 2048   /* WHIRL_BUF_SIZE_SAMPLES, src/whirl.h:36           */
+
+typedef enum tbf_status {
+    TBF_OK = 0,
+    TBF_ERR_ARG = -1,        /* bad argument                                      */
+    TBF_ERR_CUDA = -2,       /* CUDA runtime failure (tbf_gpu_last_error)         */
+    TBF_ERR_NOMEM = -3,
+    TBF_ERR_HANDLE = -4,     /* unknown table / instance handle                   */
+    TBF_ERR_REFERENCE_UB = -5, /* input drives the reference into undefined
+                                  behaviour (corePgm overflow src/tonegen.h:233,
+                                  keyCompTable over-read src/tonegen.cpp:3233)     */
+    TBF_ERR_GEOMETRY = -6    /* whirl geometry violates the write-ahead window the
+                                kernels rely on (reference asserts: whirl.cpp:607)  */
+} tbf_status;
+
+/* ------------------------------------------------------------------------
+ * Immutable per-configuration tables.  They are what initToneGenerator()
+ * (src/tonegen.cpp:2905-3066) + init_vibrato() (src/vibrato.cpp:312-317)
+ * leave in struct b_tonegen, flattened; many instances share one copy.
+ * ---------------------------------------------------------------------- */
+typedef struct tbf_tonegen_tables {
+    /* wavetables: oscillators[w].wave / lengthSamples, src/tonegen.h:136-146;
+     * wheel w in 1..256, index 0 unused (length 0).                          */
+    uint32_t wave_offset[TBF_NOF_WHEELS + 1]; /* float offset into wave_data  */
+    uint32_t wave_length[TBF_NOF_WHEELS + 1];
+    const float *wave_data;
+    uint64_t wave_total; /* floats in wave_data                               */
+
+    /* keyContrib[key] linked lists (src/tonegen.h:540, built by
+     * compilePlayMatrix src/tonegen.cpp:1122-1213) as CSR, list order kept.  */
+    uint32_t contrib_start[TBF_MAX_KEYS + 1];
+    const uint16_t *contrib_wheel;
+    const uint16_t *contrib_bus;
+    const float *contrib_level;
+
+    float attack_env[TBF_NOF_DRAWBARS][TBF_FRAGMENT];  /* src/tonegen.h:246   */
+    float release_env[TBF_NOF_DRAWBARS][TBF_FRAGMENT]; /* src/tonegen.h:247   */
+    float key_comp_table[128];                         /* src/tonegen.h:227   */
+    float draw_bar_level[TBF_NOF_BUSES][TBF_NOF_DRAWBARS]; /* src/tonegen.h:318 */
+
+    /* percussion constants (src/tonegen.h:351-430) */
+    float perc_env_gain_reset_norm, perc_env_gain_reset_soft, perc_env_scaling;
+    float perc_decay_fast_norm, perc_decay_fast_soft;
+    float perc_decay_slow_norm, perc_decay_slow_soft;
+    float perc_drawbar_normal_gain, perc_drawbar_soft_gain;
+    int32_t perc_send_bus_a, perc_send_bus_b, perc_trigger_bus;
+    float output_level_trim;
+
+    /* scanner vibrato (src/vibrato.h:42-68) */
+    uint32_t vib_offset_table[3][TBF_VIB_TBL];
+    uint32_t vib_stator_increment;
+
+    /* initial run-time scalars, as left by initToneGenerator()               */
+    float init_draw_bar_gain[TBF_NOF_BUSES];
+    float init_swell_pedal_gain;
+    float init_perc_env_gain_reset, init_perc_env_gain_decay, init_perc_drawbar_gain;
+    int32_t init_perc_send_bus, init_perc_trig_restore;
+    int32_t init_perc_is_soft, init_perc_is_fast, init_perc_enabled;
+    uint32_t init_routing;
+    int32_t init_vib_table;  /* 0..2: offset1/2/3Table; reset_vibrato -> 2     */
+    int32_t init_vib_mixed;
+    uint16_t init_draw_bar_change;
+} tbf_tonegen_tables;
+
+/* What initWhirl() (src/whirl.cpp:956-990) leaves in struct b_whirl
+ * (src/whirl.h:65-221), flattened.                                           */
+typedef struct tbf_whirl_tables {
+    double sample_rate;
+    const float *hn_fwd_displ, *hn_bwd_displ, *dr_fwd_displ, *dr_bwd_displ; /* 16384 each */
+    const float *bfw, *bbw; /* 16384 x 5 each, struct _bw src/whirl.h:61      */
+    int32_t horn_phase[6], drum_phase[6];
+    float horn_spacing[6], drum_spacing[6];
+    float hafw[5], hbfw[5], drfL[5], drfR[5]; /* a1 a2 b0 b1 b2               */
+    double mic_angle;
+    float horn_acc, horn_dec, drum_acc, drum_dec;
+    double rev_horn_target[9], rev_drum_target[9]; /* revoptions[]             */
+    int32_t revselects[3];
+    double hn_brake_pos, dr_brake_pos;
+    float horn_level, leakage;
+    float mic_hll, mic_hlr, mic_hrl, mic_hrr, mic_dll, mic_dlr, mic_drl, mic_drr;
+    int32_t bypass;
+    /* initial run-time scalars as left by initWhirl()                        */
+    double init_horn_incr, init_drum_incr, init_horn_target, init_drum_target;
+    double init_horn_angle, init_drum_angle;
+    int32_t init_horn_acdc, init_drum_acdc, init_rev_select;
+} tbf_whirl_tables;
+
+/* ------------------------------------------------------------------------
+ * Control events.  They take effect at a fragment boundary, like every host
+ * of the reference does it (b_synth/lv2.cpp:1130-1136, src/main.cpp:251-266,
+ * src/clap.cpp:251).
+ * ---------------------------------------------------------------------- */
+typedef enum tbf_event_type {
+    TBF_EV_KEY_ON = 1,      /* oscKeyOn  (t, a, a)     src/tonegen.cpp:3134    */
+    TBF_EV_KEY_OFF = 2,     /* oscKeyOff (t, a, a)     src/tonegen.cpp:3096    */
+    TBF_EV_DRAWBAR = 3,     /* setDrawBar(t, a, b)     src/tonegen.cpp:2738    */
+    TBF_EV_PERC_ENABLE = 4, /* setPercussionEnabled(a) src/tonegen.cpp:1678    */
+    TBF_EV_PERC_SOFT = 5,   /* setPercussionVolume(a)  src/tonegen.cpp:1744    */
+    TBF_EV_PERC_FAST = 6,   /* setPercussionFast(a)    src/tonegen.cpp:1733    */
+    TBF_EV_PERC_FIRST = 7,  /* setPercussionFirst(a)   src/tonegen.cpp:1760    */
+    TBF_EV_VIB_UPPER = 8,   /* setVibratoUpper(a)      src/tonegen.cpp:1635    */
+    TBF_EV_VIB_LOWER = 9,   /* setVibratoLower(a)      src/tonegen.cpp:1650    */
+    TBF_EV_VIB_KNOB = 10,   /* setVibratoFromInt(a)    src/vibrato.cpp:118     */
+    TBF_EV_REV_OPTION = 11, /* useRevOption(w, a, 2)   src/whirl.cpp:174       */
+    TBF_EV_SWELL = 12,      /* swellPedalGain = trim*a/127 src/tonegen.cpp:2885 */
+    TBF_EV_REV_SELECT = 13  /* setRevSelect(w, a)      src/whirl.cpp:226       */
+} tbf_event_type;
+
+typedef struct tbf_event {
+    uint32_t instance; /* instance handle                                     */
+    uint32_t fragment; /* fragment index inside the batch the event precedes  */
+    int32_t type;      /* tbf_event_type                                      */
+    int32_t a, b;
+} tbf_event;
+
+/* render flags */
+#define TBF_RENDER_WHIRL_BYPASS 0x1 /* tonegen(+vibrato) only: L = R = mono buf */
+#define TBF_RENDER_WHIRLPROC3 0x2   /* whirlProc3 mic-width mix (whirl.cpp:1653) */
+#define TBF_RENDER_OUT_DEVICE 0x4   /* out_l/out_r are device pointers           */
+#define TBF_RENDER_NO_OUTPUT 0x8    /* keep audio on device, checksums only      */
+
+typedef struct tbf_batch_desc {
+    uint32_t n_instances;
+    const uint32_t *instance_ids; /* NULL = instances 0..n_instances-1         */
+    uint32_t n_fragments;         /* 128-sample fragments to render per instance */
+    const tbf_event *events;      /* sorted by (position in instance_ids, fragment);
+                                     order inside one (instance, fragment) is kept */
+    uint64_t n_events;
+    float *out_l, *out_r; /* [n_instances][out_stride] floats                  */
+    uint64_t out_stride;  /* floats between instances, >= n_fragments*128       */
+    uint32_t flags;
+    uint64_t *checksums;  /* optional, host, [n_instances]: FNV-style hash of the
+                             rendered L/R bit patterns                          */
+} tbf_batch_desc;
+
+typedef struct tbf_ctx tbf_ctx;
+
+/* context = one GPU (one host thread / process per GPU; not re-entrant)      */
+int tbf_gpu_create(tbf_ctx **out, int device);
+void tbf_gpu_destroy(tbf_ctx *ctx);
+const char *tbf_gpu_last_error(const tbf_ctx *ctx);
+
+/* upload table sets; the library copies everything                          */
+int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int *handle);
+int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *handle);
+
+/* replaces allocTonegen+initToneGenerator+allocWhirl+initWhirl as far as the
+ * run-time state goes (src/tonegen.cpp:3780, :2905; src/whirl.cpp:136, :956) */
+int tbf_gpu_instance_create(tbf_ctx *ctx, int tonegen_tables, int whirl_tables, uint32_t count,
+                            uint32_t *first_id);
+int tbf_gpu_instance_count(const tbf_ctx *ctx);
+/* back to the state right after create (what a host gets by re-creating the
+ * engine, b_synth/lv2.cpp:1080-1093)                                         */
+int tbf_gpu_instance_reset(tbf_ctx *ctx, uint32_t first_id, uint32_t count);
+
+/* the batched replacement for the per-fragment chain
+ * oscGenerateFragment -> [vibratoProc] -> whirlProc/whirlProc3
+ * (src/clap.cpp:254-258)                                                     */
+int tbf_gpu_render_batch(tbf_ctx *ctx, const tbf_batch_desc *desc);
+
+/* asynchronous halves used by the benchmark to time the device alone         */
+int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *desc);
+int tbf_gpu_synchronize(tbf_ctx *ctx);
+/* device time of the last launch in ms (CUDA events on the library's stream),
+ * and how many kernels it launched                                           */
+int tbf_gpu_last_launch_ms(tbf_ctx *ctx, float *ms, int *n_kernel_launches);
+
+/* parity debugging: integer + float run-time state of one instance           */
+typedef struct tbf_state_export {
+    int32_t active_osc_l_end;
+    int32_t active_osc_list[TBF_NOF_WHEELS + 1];
+    uint32_t osc_pos[TBF_NOF_WHEELS + 1];
+    int32_t osc_acl_pos[TBF_NOF_WHEELS + 1];
+    int32_t ref_count[TBF_NOF_WHEELS + 1];
+    uint32_t old_routing, new_routing, upper_key_count;
+    int32_t key_down_count;
+    float perc_env_gain, key_comp_level, pz;
+    uint32_t vib_stator, vib_out_pos;
+    float vib_buffer[TBF_VIB_BUF];
+    uint32_t whirl_outpos;
+    double horn_angle, drum_angle, horn_incr, drum_incr;
+    int32_t horn_acdc, drum_acdc;
+    float whirl_buf[4][TBF_WHIRL_BUF]; /* HL HR DL DR                          */
+    float iir_z[4][2];                 /* hafw hbfw drfL drfR: z0 z1           */
+    float filt_z[4];
+    float adx[3][8];
+    int32_t adi[3];
+    uint32_t error_flags;              /* TBF_IFLAG_*                          */
+} tbf_state_export;
+int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *out);
+
+#define TBF_IFLAG_COREPGM_OVERFLOW 0x1 /* > CR_PGMMAX core instrs: reference UB */
+#define TBF_IFLAG_KEYCOMP_OOB 0x2      /* keyDownCount >= 128: reference over-read */
+#define TBF_IFLAG_BAD_EVENT 0x4
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TBF_GPU_H */

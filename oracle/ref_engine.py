@@ -1,0 +1,135 @@
+"""ORACLE (test infrastructure, not product code).
+
+ctypes wrapper around ``oracle/_ref/libtbf_ref.so`` = the UNMODIFIED reference
+engine compiled in place from /root/reference/src (see oracle/Makefile) plus
+the harness ``oracle/ref_harness.cpp``.  Only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline legs import this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from tunebfree_b200 import cabi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libtbf_ref.so")
+_lib = None
+
+
+def build(quiet=True):
+    """Compile the oracle (needs /root/reference; a no-op when already built)."""
+    if not os.path.isdir(os.environ.get("TBF_REFERENCE", "/root/reference")):
+        if os.path.exists(LIB_PATH):
+            return LIB_PATH
+        raise RuntimeError("reference tree absent and oracle/_ref not prebuilt")
+    subprocess.run(["make", "-C", _HERE, "-j8"], check=True,
+                   stdout=subprocess.DEVNULL if quiet else None)
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        L.ref_create.restype = C.c_void_p
+        L.ref_create.argtypes = [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                 C.c_uint, C.c_char_p]
+        L.ref_destroy.argtypes = [C.c_void_p]
+        L.ref_event.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.ref_render.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.POINTER(cabi.Event),
+                                 C.c_ulonglong, C.c_void_p, C.c_void_p]
+        L.ref_active_wheels.argtypes = [C.c_void_p]
+        L.ref_dump_tonegen_tables.argtypes = [C.c_void_p, C.POINTER(cabi.TonegenTables)]
+        L.ref_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
+        L.ref_dump_whirl_tables.argtypes = [C.c_void_p, C.POINTER(cabi.WhirlTables)]
+        L.ref_export_state.argtypes = [C.c_void_p, C.POINTER(cabi.StateExport)]
+        _lib = L
+    return _lib
+
+
+def tet12():
+    """12-TET, A4 = 440 Hz: the table libMTSClient serves without a master."""
+    return np.array([440.0 * 2.0 ** ((n - 69) / 12.0) for n in range(128)], dtype=np.float64)
+
+
+def events_array(events):
+    """[(fragment, type, a, b), ...] -> ctypes array of tbf_event (sorted by fragment)."""
+    ev = sorted(events, key=lambda e: e[0])
+    arr = (cabi.Event * max(1, len(ev)))()
+    for i, e in enumerate(ev):
+        arr[i].instance = 0
+        arr[i].fragment = e[0]
+        arr[i].type = e[1]
+        arr[i].a = e[2]
+        arr[i].b = e[3] if len(e) > 3 else 0
+    return arr, len(ev)
+
+
+class RefInstance:
+    """One reference organ (struct b_instance, src/global_inst.h:32-40)."""
+
+    def __init__(self, freqs=None, rate=48000.0, seed=1, cfg="", target_ratio=None):
+        L = lib()
+        f = None
+        if freqs is not None:
+            f = (C.c_double * 128)(*[float(x) for x in freqs])
+        else:
+            f = (C.c_double * 128)(*tet12())
+        tr = None
+        if target_ratio is not None:
+            tr = (C.c_double * 9)(*[float(x) for x in target_ratio])
+        self._h = L.ref_create(rate, f, tr, seed, cfg.encode())
+        if not self._h:
+            raise MemoryError("ref_create failed")
+        self._tt = None
+
+    def close(self):
+        if self._h:
+            if self._tt is not None:
+                lib().ref_free_tonegen_tables(C.byref(self._tt))
+                self._tt = None
+            lib().ref_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def event(self, type_, a=0, b=0):
+        if lib().ref_event(self._h, type_, a, b) != 0:
+            raise ValueError("bad event type %r" % (type_,))
+
+    def render(self, n_fragments, flags=0, events=()):
+        """-> (L, R) float32 arrays of n_fragments*128 samples."""
+        outl = np.zeros(n_fragments * 128, dtype=np.float32)
+        outr = np.zeros(n_fragments * 128, dtype=np.float32)
+        arr, n = events_array(events)
+        lib().ref_render(self._h, n_fragments, flags, arr, n,
+                         outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
+        return outl, outr
+
+    def active_wheels(self):
+        return lib().ref_active_wheels(self._h)
+
+    def tonegen_tables(self):
+        """struct b_tonegen flattened into the boundary's table format (kept alive by self)."""
+        if self._tt is None:
+            self._tt = cabi.TonegenTables()
+            lib().ref_dump_tonegen_tables(self._h, C.byref(self._tt))
+        return self._tt
+
+    def whirl_tables(self):
+        wt = cabi.WhirlTables()
+        lib().ref_dump_whirl_tables(self._h, C.byref(wt))
+        return wt
+
+    def export_state(self):
+        st = cabi.StateExport()
+        lib().ref_export_state(self._h, C.byref(st))
+        return st
