@@ -1,0 +1,67 @@
+"""CPU-side checks of the C-ABI boundary: the library loads, exports every symbol
+include/tbf_gpu.h declares, and the ctypes mirror matches the C struct sizes.
+No compute calls (no GPU here)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from tunebfree_b200 import cabi, engine
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    syms = set()
+    for name in os.listdir(os.path.join(ROOT, "include")):
+        if not name.endswith(".h"):
+            continue
+        txt = open(os.path.join(ROOT, "include", name)).read()
+        txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+        for m in re.finditer(r"\b(tbf_[a-z0-9_]+)\s*\(", txt):
+            syms.add(m.group(1))
+    return syms
+
+
+def test_library_exports_every_declared_symbol():
+    L = engine.lib()
+    syms = _declared_symbols()
+    assert "tbf_gpu_render_batch" in syms and len(syms) >= 12
+    for s in sorted(syms):
+        assert hasattr(L, s), "libtbf_gpu.so does not export %s" % s
+
+
+def test_struct_sizes_match_header():
+    L = engine.lib()
+    assert L.tbf_sizeof_tonegen_tables() == C.sizeof(cabi.TonegenTables)
+    assert L.tbf_sizeof_whirl_tables() == C.sizeof(cabi.WhirlTables)
+    assert L.tbf_sizeof_state_export() == C.sizeof(cabi.StateExport)
+    assert L.tbf_sizeof_batch_desc() == C.sizeof(cabi.BatchDesc)
+    assert L.tbf_sizeof_event() == C.sizeof(cabi.Event)
+
+
+def test_oracle_struct_sizes_match(ref):
+    L = ref.lib()
+    assert L.ref_sizeof_tonegen_tables() == C.sizeof(cabi.TonegenTables)
+    assert L.ref_sizeof_whirl_tables() == C.sizeof(cabi.WhirlTables)
+    assert L.ref_sizeof_state_export() == C.sizeof(cabi.StateExport)
+
+
+def test_no_gpu_means_loud_failure():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(engine.TbfError):
+        engine.Context(0)
+
+
+def test_product_never_imports_oracle():
+    """The product package must not reference oracle/ (no CPU fallback)."""
+    pkg = os.path.join(ROOT, "tunebfree_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "ref_engine" not in txt and "libtbf_ref" not in txt, f
+                assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f

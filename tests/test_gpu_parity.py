@@ -1,0 +1,195 @@
+"""GPU parity tests: the CUDA path, called through the C-ABI, against the oracle
+(the reference engine compiled in place) on the same seeded inputs.
+
+Bar: BIT-EXACT float32 output (north_star's tolerance is 1e-5 of full scale; the
+Leslie's DF-II biquads amplify 1-ulp differences past that, SURVEY 6.2, so the
+design target is 0 and these tests assert array equality), and bit-exact integer
+state (wave positions, active list, reference counts, delay-line indices).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tunebfree_b200 import cabi, workloads
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(ref, ctx, n=1, seed=1, cfg="", freqs=None):
+    r = ref.RefInstance(freqs=freqs, seed=seed, cfg=cfg)
+    tg = ctx.tonegen_tables(r.tonegen_tables())
+    wh = ctx.whirl_tables(r.whirl_tables())
+    first = ctx.create_instances(tg, wh, n)
+    return r, first
+
+
+def _compare_state(gs, rs, whirl=True):
+    n = rs.active_osc_l_end
+    assert gs.active_osc_l_end == n
+    assert list(gs.active_osc_list)[:n] == list(rs.active_osc_list)[:n]
+    assert list(gs.osc_pos) == list(rs.osc_pos)
+    assert list(gs.osc_acl_pos)[1:] == list(rs.osc_acl_pos)[1:]
+    assert list(gs.ref_count) == list(rs.ref_count)
+    assert (gs.old_routing, gs.new_routing, gs.upper_key_count, gs.key_down_count) == \
+           (rs.old_routing, rs.new_routing, rs.upper_key_count, rs.key_down_count)
+    f32 = lambda x: np.float32(x).view(np.uint32)
+    assert f32(gs.perc_env_gain) == f32(rs.perc_env_gain)
+    assert f32(gs.key_comp_level) == f32(rs.key_comp_level)
+    assert f32(gs.pz) == f32(rs.pz)
+    assert (gs.vib_stator, gs.vib_out_pos) == (rs.vib_stator, rs.vib_out_pos)
+    assert np.array_equal(np.ctypeslib.as_array(gs.vib_buffer).view(np.uint32),
+                          np.ctypeslib.as_array(rs.vib_buffer).view(np.uint32))
+    if whirl:
+        assert gs.whirl_outpos == rs.whirl_outpos
+        assert (gs.horn_angle, gs.drum_angle, gs.horn_incr, gs.drum_incr) == \
+               (rs.horn_angle, rs.drum_angle, rs.horn_incr, rs.drum_incr)
+        assert (gs.horn_acdc, gs.drum_acdc) == (rs.horn_acdc, rs.drum_acdc)
+        for name in ("whirl_buf", "iir_z", "filt_z", "adx"):
+            a = np.ctypeslib.as_array(getattr(gs, name)).view(np.uint32)
+            b = np.ctypeslib.as_array(getattr(rs, name)).view(np.uint32)
+            assert np.array_equal(a, b), name
+        assert list(gs.adi) == list(rs.adi)
+    assert gs.error_flags == 0
+
+
+def _bits(x):
+    return np.ascontiguousarray(x).view(np.uint32)
+
+
+def _check(ref, ctx, events, n_frag, flags, seed=1, cfg="", freqs=None, whirl_state=True):
+    r, first = _make(ref, ctx, 1, seed, cfg, freqs)
+    rl, rr = r.render(n_frag, flags, events)
+    gl, gr, cs = ctx.render(1, n_frag, [events], flags, ids=[first], checksums=True)
+    bad = np.nonzero(_bits(gl[0]) != _bits(rl))[0]
+    assert bad.size == 0, "L differs first at sample %d (fragment %d): gpu %r ref %r, max abs %g" % (
+        bad[0], bad[0] // 128, gl[0][bad[0]], rl[bad[0]], np.abs(gl[0] - rl).max())
+    assert np.array_equal(_bits(gr[0]), _bits(rr))
+    from tunebfree_b200.engine import checksum_host
+    assert int(cs[0]) == checksum_host(gl[0], gr[0])
+    _compare_state(ctx.export_state(first), r.export_state(), whirl_state)
+    peak = float(np.abs(rl).max())
+    r.close()
+    return peak
+
+
+def test_tonegen_only_chord_click_percussion(ref, gpu_ctx):
+    """BASELINE config 2 shape: full drawbars, 10-note chord re-struck, percussion +
+    key click, whirl bypassed."""
+    ev = workloads.instance_events(7, 600, config=2)
+    peak = _check(ref, gpu_ctx, ev, 600, cabi.RENDER_WHIRL_BYPASS, whirl_state=False)
+    assert peak > 0.05
+
+
+def test_full_chain_config3(ref, gpu_ctx):
+    """BASELINE config 3 shape: tonegen + vibrato C3 + Leslie fast through whirlProc3."""
+    ev = workloads.instance_events(3, 800, config=3)
+    peak = _check(ref, gpu_ctx, ev, 800, cabi.RENDER_WHIRLPROC3)
+    assert peak > 0.05
+
+
+def test_whirlproc_plain_and_speed_changes(ref, gpu_ctx):
+    """whirlProc (no mic mix); all nine useRevOption speeds incl. accel/decel ramps."""
+    ev = workloads.setup_events(3)
+    ev += [(0, cabi.EV_KEY_ON, k, 0) for k in (48, 55, 60, 64)]
+    for i, n in enumerate([4, 8, 0, 2, 6, 1, 7, 3, 5, 8]):
+        ev.append((40 + 90 * i, cabi.EV_REV_OPTION, n, 0))
+    ev += [(700, cabi.EV_REV_SELECT, 1, 0), (820, cabi.EV_REV_SELECT, 2, 0)]
+    _check(ref, gpu_ctx, ev, 1000, 0)
+
+
+def test_setters_midstream(ref, gpu_ctx):
+    """Drawbar, percussion, vibrato routing / knob and swell changes between fragments,
+    keys on all three manuals, re-striking a held key, silence with the scanner on."""
+    E = cabi
+    ev = [(0, E.EV_KEY_ON, 60, 0), (0, E.EV_KEY_ON, 128 + 48, 0), (0, E.EV_KEY_ON, 256 + 36, 0),
+          (5, E.EV_DRAWBAR, 3, 8), (5, E.EV_DRAWBAR, 8, 5), (9, E.EV_PERC_ENABLE, 1, 0),
+          (12, E.EV_KEY_ON, 64, 0), (12, E.EV_KEY_ON, 60, 0),  # 60 re-struck while held
+          (20, E.EV_VIB_UPPER, 1, 0), (25, E.EV_VIB_KNOB, 1, 0), (30, E.EV_VIB_LOWER, 1, 0),
+          (33, E.EV_PERC_SOFT, 1, 0), (35, E.EV_PERC_FAST, 0, 0), (37, E.EV_PERC_FIRST, 1, 0),
+          (40, E.EV_DRAWBAR, 8, 8), (44, E.EV_SWELL, 90, 0), (50, E.EV_VIB_KNOB, 4, 0),
+          (55, E.EV_KEY_OFF, 60, 0), (55, E.EV_KEY_OFF, 64, 0), (60, E.EV_KEY_ON, 72, 0),
+          (70, E.EV_PERC_ENABLE, 0, 0), (75, E.EV_VIB_UPPER, 0, 0), (80, E.EV_VIB_KNOB, 3, 0),
+          (90, E.EV_KEY_OFF, 72, 0), (90, E.EV_KEY_OFF, 128 + 48, 0), (90, E.EV_KEY_OFF, 256 + 36, 0),
+          (100, E.EV_DRAWBAR, 9, 8), (100, E.EV_DRAWBAR, 20, 8), (130, E.EV_KEY_ON, 40, 0),
+          (131, E.EV_KEY_OFF, 40, 0), (131, E.EV_KEY_ON, 40, 0), (160, E.EV_KEY_OFF, 40, 0),
+          (0, E.EV_REV_OPTION, 4, 0)]
+    _check(ref, gpu_ctx, ev, 260, cabi.RENDER_WHIRLPROC3)
+
+
+def test_all_61_keys_and_release(ref, gpu_ctx):
+    """Many active wheels (169 wheels / 221 core instructions in the reference: close
+    to its 256-instruction corePgm), then full release down to an empty active list."""
+    ev = workloads.setup_events(3)
+    ev += [(2, cabi.EV_KEY_ON, k, 0) for k in range(36, 97)]
+    ev += [(60, cabi.EV_KEY_OFF, k, 0) for k in range(36, 97)]
+    _check(ref, gpu_ctx, ev, 120, cabi.RENDER_WHIRLPROC3)
+
+
+def test_long_run_wave_wraps(ref, gpu_ctx):
+    """20 s held chord: every wavetable wraps many times (incl. the pos == length case)."""
+    ev = workloads.setup_events(3) + [(0, cabi.EV_KEY_ON, k, 0) for k in (36, 41, 52, 60, 67, 77, 84, 96)]
+    _check(ref, gpu_ctx, ev, 7500, cabi.RENDER_WHIRLPROC3)
+
+
+def test_batch_split_equals_one_shot(ref, gpu_ctx):
+    """Rendering in several tbf_gpu_render_batch calls carries the state exactly."""
+    n_frag = 300
+    ev = workloads.instance_events(11, n_frag, config=3)
+    r, first = _make(ref, gpu_ctx, 1)
+    rl, rr = r.render(n_frag, cabi.RENDER_WHIRLPROC3, ev)
+    outs = []
+    for lo, hi in ((0, 1), (1, 100), (100, 101), (101, 300)):
+        sub = [(f - lo, t, a, b) for (f, t, a, b) in ev if lo <= f < hi]
+        l, rgt = gpu_ctx.render(1, hi - lo, [sub], cabi.RENDER_WHIRLPROC3, ids=[first])
+        outs.append((l[0], rgt[0]))
+    gl = np.concatenate([o[0] for o in outs])
+    gr = np.concatenate([o[1] for o in outs])
+    assert np.array_equal(_bits(gl), _bits(rl)) and np.array_equal(_bits(gr), _bits(rr))
+    _compare_state(gpu_ctx.export_state(first), r.export_state())
+
+
+def test_many_instances_independent(ref, gpu_ctx):
+    """64 instances with different chords in one launch == 64 oracle renders."""
+    n, n_frag = 64, 200
+    r0, first = _make(ref, gpu_ctx, n)
+    evs = [workloads.instance_events(i, n_frag, config=3) for i in range(n)]
+    gl, gr = gpu_ctx.render(n, n_frag, evs, cabi.RENDER_WHIRLPROC3, ids=list(range(first, first + n)))
+    for i in (0, 1, 17, 63):
+        r = ref.RefInstance(seed=1)
+        rl, rr = r.render(n_frag, cabi.RENDER_WHIRLPROC3, evs[i])
+        assert np.array_equal(_bits(gl[i]), _bits(rl)), i
+        assert np.array_equal(_bits(gr[i]), _bits(rr)), i
+        r.close()
+    # reset puts every instance back to the post-init state
+    gpu_ctx.reset(first, n)
+    gl2, gr2 = gpu_ctx.render(n, n_frag, evs, cabi.RENDER_WHIRLPROC3, ids=list(range(first, first + n)))
+    assert np.array_equal(_bits(gl), _bits(gl2)) and np.array_equal(_bits(gr), _bits(gr2))
+
+
+def test_cfg_variants(ref, gpu_ctx):
+    """osc-*/whirl-* style cfg variants resolved by the reference's own parser:
+    sawtooth harmonics, no crosstalk, whirl-sharp's dead horn filter, brake position,
+    mic width + angle, whirl bypass."""
+    cfgs = [
+        "osc.harmonic.1=1.0\nosc.harmonic.2=0.5\nosc.harmonic.3=0.333\nosc.harmonic.4=0.25\n",
+        "osc.compartment-crosstalk=0\nosc.transformer-crosstalk=0\nosc.terminalstrip-crosstalk=0\nosc.wiring-crosstalk=0\n",
+        "whirl.horn.filter.b.gain=-60\nwhirl.horn.filter.a.hz=3000\n",
+        "whirl.horn.brakepos=0.25\nwhirl.drum.brakepos=0.5\n",
+        "whirl.horn.mic.angle=90\nwhirl.drum.width=0.4\nwhirl.horn.width=-0.3\n",
+        "whirl.bypass=1\n",
+        "osc.attack.model=cosine\nosc.release.model=click\nscanner.hz=6.1\nscanner.modulation.v3=11\n",
+    ]
+    for cfg in cfgs:
+        ev = workloads.setup_events(3) + [(1, cabi.EV_KEY_ON, k, 0) for k in (43, 60, 64, 79)]
+        ev += [(150, cabi.EV_REV_OPTION, 0, 0), (320, cabi.EV_KEY_OFF, 60, 0)]
+        _check(ref, gpu_ctx, ev, 700, cabi.RENDER_WHIRLPROC3, seed=5, cfg=cfg)
+        _check(ref, gpu_ctx, ev, 100, 0, seed=5, cfg=cfg)
+
+
+def test_error_paths(gpu_ctx):
+    from tunebfree_b200.engine import TbfError
+    with pytest.raises(TbfError):
+        gpu_ctx.render(1, 4, [[]], 0, ids=[10 ** 6])
+    with pytest.raises(TbfError):
+        gpu_ctx.create_instances(999, 999, 1)

@@ -1,0 +1,651 @@
+/* tbf_api.cu -- host side of the C-ABI declared in include/tbf_gpu.h.
+ *
+ * One context per GPU.  Tables are uploaded once and shared by any number of
+ * instances; per-instance state is a flat blob array in HBM (tbf_device.h).
+ * Nothing here computes audio on the host: if the CUDA device or a kernel
+ * launch is unavailable every entry point fails with TBF_ERR_CUDA.
+ */
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "tbf_device.h"
+
+struct TgSet {
+    tbf_tonegen_tables host; /* scalars only; pointers nulled */
+    float *wave = nullptr;
+    uint16_t *cw = nullptr, *cb = nullptr;
+    float *cl = nullptr;
+};
+struct WhSet {
+    tbf_whirl_tables host;
+    float *tables = nullptr; /* 4 x 16384 displacement + 2 x 16384 x 5 FIR */
+};
+
+struct tbf_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    std::vector<TgSet> tg;
+    std::vector<WhSet> wh;
+    DevTonegenTables *d_tg = nullptr;
+    DevWhirlTables *d_wh = nullptr;
+    size_t d_tg_cap = 0, d_wh_cap = 0;
+    InstState *d_states = nullptr;
+    size_t n_inst = 0, cap_inst = 0;
+    std::vector<int> inst_tg, inst_wh;
+    InstState *d_tmpl = nullptr;
+    /* per-render scratch, grown on demand */
+    tbf_event *d_events = nullptr;
+    size_t cap_events = 0;
+    uint64_t *d_ev_start = nullptr;
+    uint32_t *d_ids = nullptr;
+    unsigned long long *d_csum = nullptr;
+    size_t cap_slots = 0;
+    float *d_out = nullptr;
+    size_t cap_out = 0;
+    /* pending host copies of the launch in flight */
+    tbf_batch_desc pending{};
+    bool in_flight = false;
+    int launches = 0;
+    std::vector<uint64_t> ev_start_host;
+};
+
+#define CK(call)                                                                            \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess) {                                                            \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                  \
+            return TBF_ERR_CUDA;                                                            \
+        }                                                                                   \
+    } while (0)
+
+static int fail(tbf_ctx *ctx, int code, const char *msg)
+{
+    if (ctx)
+        ctx->err = msg;
+    return code;
+}
+
+extern "C" {
+
+int tbf_gpu_create(tbf_ctx **out, int device)
+{
+    if (!out)
+        return TBF_ERR_ARG;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n)
+        return TBF_ERR_CUDA;
+    tbf_ctx *ctx = new tbf_ctx();
+    ctx->device = device;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+        cudaMalloc(&ctx->d_tmpl, sizeof(InstState)) != cudaSuccess) {
+        delete ctx;
+        return TBF_ERR_CUDA;
+    }
+    *out = ctx;
+    return TBF_OK;
+}
+
+void tbf_gpu_destroy(tbf_ctx *ctx)
+{
+    if (!ctx)
+        return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &t : ctx->tg) {
+        cudaFree(t.wave);
+        cudaFree(t.cw);
+        cudaFree(t.cb);
+        cudaFree(t.cl);
+    }
+    for (auto &w : ctx->wh)
+        cudaFree(w.tables);
+    cudaFree(ctx->d_tg);
+    cudaFree(ctx->d_wh);
+    cudaFree(ctx->d_states);
+    cudaFree(ctx->d_tmpl);
+    cudaFree(ctx->d_events);
+    cudaFree(ctx->d_ev_start);
+    cudaFree(ctx->d_ids);
+    cudaFree(ctx->d_csum);
+    cudaFree(ctx->d_out);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *tbf_gpu_last_error(const tbf_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int *handle)
+{
+    if (!ctx || !t || !handle || !t->wave_data)
+        return fail(ctx, TBF_ERR_ARG, "tonegen tables: null argument");
+    const uint32_t nc = t->contrib_start[TBF_MAX_KEYS];
+    for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
+        if ((uint64_t)t->wave_offset[w] + t->wave_length[w] > t->wave_total)
+            return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave slice out of range");
+        if (t->wave_length[w] && t->wave_length[w] < TBF_FRAGMENT)
+            return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave shorter than one fragment");
+    }
+    for (int k = 0; k < TBF_MAX_KEYS; ++k)
+        if (t->contrib_start[k] > t->contrib_start[k + 1])
+            return fail(ctx, TBF_ERR_ARG, "tonegen tables: contrib_start not monotone");
+    for (uint32_t e = 0; e < nc; ++e)
+        if (t->contrib_wheel[e] < 1 || t->contrib_wheel[e] > TBF_NOF_WHEELS ||
+            t->contrib_bus[e] >= TBF_NOF_BUSES || t->wave_length[t->contrib_wheel[e]] == 0)
+            return fail(ctx, TBF_ERR_ARG, "tonegen tables: contribution out of range");
+    CK(cudaSetDevice(ctx->device));
+
+    TgSet s;
+    s.host = *t;
+    CK(cudaMalloc(&s.wave, sizeof(float) * std::max<uint64_t>(1, t->wave_total)));
+    CK(cudaMalloc(&s.cw, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
+    CK(cudaMalloc(&s.cb, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
+    CK(cudaMalloc(&s.cl, sizeof(float) * std::max<uint32_t>(1, nc)));
+    CK(cudaMemcpy(s.wave, t->wave_data, sizeof(float) * t->wave_total, cudaMemcpyHostToDevice));
+    if (nc) {
+        CK(cudaMemcpy(s.cw, t->contrib_wheel, sizeof(uint16_t) * nc, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(s.cb, t->contrib_bus, sizeof(uint16_t) * nc, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(s.cl, t->contrib_level, sizeof(float) * nc, cudaMemcpyHostToDevice));
+    }
+    s.host.wave_data = nullptr;
+    s.host.contrib_wheel = s.host.contrib_bus = nullptr;
+    s.host.contrib_level = nullptr;
+
+    DevTonegenTables *d = new DevTonegenTables();
+    d->wave_data = s.wave;
+    d->contrib_wheel = s.cw;
+    d->contrib_bus = s.cb;
+    d->contrib_level = s.cl;
+    memcpy(d->wave_offset, t->wave_offset, sizeof(d->wave_offset));
+    memcpy(d->wave_length, t->wave_length, sizeof(d->wave_length));
+    memcpy(d->contrib_start, t->contrib_start, sizeof(d->contrib_start));
+    for (int r = 0; r < 8; ++r) {
+        memcpy(d->env[r], t->attack_env[r], sizeof(float) * TBF_FRAGMENT);
+        memcpy(d->env[8 + r], t->release_env[r], sizeof(float) * TBF_FRAGMENT);
+    }
+    memcpy(d->key_comp_table, t->key_comp_table, sizeof(d->key_comp_table));
+    memcpy(d->draw_bar_level, t->draw_bar_level, sizeof(d->draw_bar_level));
+    d->perc_env_gain_reset_norm = t->perc_env_gain_reset_norm;
+    d->perc_env_gain_reset_soft = t->perc_env_gain_reset_soft;
+    d->perc_env_scaling = t->perc_env_scaling;
+    d->perc_decay_fast_norm = t->perc_decay_fast_norm;
+    d->perc_decay_fast_soft = t->perc_decay_fast_soft;
+    d->perc_decay_slow_norm = t->perc_decay_slow_norm;
+    d->perc_decay_slow_soft = t->perc_decay_slow_soft;
+    d->perc_drawbar_normal_gain = t->perc_drawbar_normal_gain;
+    d->perc_drawbar_soft_gain = t->perc_drawbar_soft_gain;
+    d->perc_send_bus_a = t->perc_send_bus_a;
+    d->perc_send_bus_b = t->perc_send_bus_b;
+    d->perc_trigger_bus = t->perc_trigger_bus;
+    d->output_level_trim = t->output_level_trim;
+    memcpy(d->vib_offset_table, t->vib_offset_table, sizeof(d->vib_offset_table));
+    d->vib_stator_increment = t->vib_stator_increment;
+
+    const size_t idx = ctx->tg.size();
+    if (idx + 1 > ctx->d_tg_cap) {
+        const size_t ncap = std::max<size_t>(8, ctx->d_tg_cap * 2);
+        DevTonegenTables *nd = nullptr;
+        cudaError_t e = cudaMalloc(&nd, sizeof(DevTonegenTables) * ncap);
+        if (e != cudaSuccess) {
+            delete d;
+            ctx->err = cudaGetErrorString(e);
+            return TBF_ERR_NOMEM;
+        }
+        if (idx)
+            cudaMemcpy(nd, ctx->d_tg, sizeof(DevTonegenTables) * idx, cudaMemcpyDeviceToDevice);
+        cudaFree(ctx->d_tg);
+        ctx->d_tg = nd;
+        ctx->d_tg_cap = ncap;
+    }
+    cudaError_t e = cudaMemcpy(ctx->d_tg + idx, d, sizeof(DevTonegenTables), cudaMemcpyHostToDevice);
+    delete d;
+    if (e != cudaSuccess) {
+        ctx->err = cudaGetErrorString(e);
+        return TBF_ERR_CUDA;
+    }
+    ctx->tg.push_back(s);
+    *handle = (int)idx;
+    return TBF_OK;
+}
+
+int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *handle)
+{
+    if (!ctx || !w || !handle || !w->hn_fwd_displ || !w->hn_bwd_displ || !w->dr_fwd_displ ||
+        !w->dr_bwd_displ || !w->bfw || !w->bbw)
+        return fail(ctx, TBF_ERR_ARG, "whirl tables: null argument");
+    if (!(w->sample_rate > 0))
+        return fail(ctx, TBF_ERR_ARG, "whirl tables: bad sample rate");
+    CK(cudaSetDevice(ctx->device));
+    WhSet s;
+    s.host = *w;
+    const size_t N = TBF_WHIRL_DISPLC;
+    CK(cudaMalloc(&s.tables, sizeof(float) * N * 14));
+    const float *src[4] = {w->hn_fwd_displ, w->hn_bwd_displ, w->dr_fwd_displ, w->dr_bwd_displ};
+    for (int i = 0; i < 4; ++i)
+        CK(cudaMemcpy(s.tables + N * i, src[i], sizeof(float) * N, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(s.tables + N * 4, w->bfw, sizeof(float) * N * 5, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(s.tables + N * 9, w->bbw, sizeof(float) * N * 5, cudaMemcpyHostToDevice));
+    s.host.hn_fwd_displ = s.host.hn_bwd_displ = s.host.dr_fwd_displ = s.host.dr_bwd_displ = nullptr;
+    s.host.bfw = s.host.bbw = nullptr;
+
+    DevWhirlTables d;
+    memset(&d, 0, sizeof(d));
+    d.hn_fwd_displ = s.tables;
+    d.hn_bwd_displ = s.tables + N;
+    d.dr_fwd_displ = s.tables + 2 * N;
+    d.dr_bwd_displ = s.tables + 3 * N;
+    d.bfw = s.tables + 4 * N;
+    d.bbw = s.tables + 9 * N;
+    d.sample_rate = w->sample_rate;
+    d.fw_ang = w->mic_angle * .25;            /* src/whirl.cpp:1379 */
+    d.bw_ang = 1. + w->mic_angle * -.25;      /* src/whirl.cpp:1380 */
+    const float tau[4] = {w->horn_acc, w->horn_dec, w->drum_acc, w->drum_dec};
+    for (int i = 0; i < 4; ++i) {
+        /* l = exp(-1.0 / (SR / n * tau)), src/whirl.cpp:1255-1257, :1306-1308 */
+        const double l = exp(-1.0 / (w->sample_rate / (double)(size_t)TBF_FRAGMENT * tau[i]));
+        d.one_minus_l[i] = 1 - l;
+    }
+    for (int i = 0; i < 9; ++i) {
+        d.rev_horn_target[i] = w->rev_horn_target[i];
+        d.rev_drum_target[i] = w->rev_drum_target[i];
+    }
+    d.hn_brake_pos = w->hn_brake_pos;
+    d.dr_brake_pos = w->dr_brake_pos;
+    for (int i = 0; i < 6; ++i) {
+        d.horn_phase[i] = w->horn_phase[i];
+        d.drum_phase[i] = w->drum_phase[i];
+        d.horn_spacing[i] = w->horn_spacing[i];
+        d.drum_spacing[i] = w->drum_spacing[i];
+    }
+    memcpy(d.iir[0], w->hafw, sizeof(float) * 5);
+    memcpy(d.iir[1], w->hbfw, sizeof(float) * 5);
+    memcpy(d.iir[2], w->drfL, sizeof(float) * 5);
+    memcpy(d.iir[3], w->drfR, sizeof(float) * 5);
+    for (int i = 0; i < 3; ++i) {
+        if (w->revselects[i] < 0)
+            return fail(ctx, TBF_ERR_ARG, "whirl tables: negative revselect");
+        d.revselects[i] = w->revselects[i];
+    }
+    d.horn_level = w->horn_level;
+    d.leakage = w->leakage;
+    d.mic_hll = w->mic_hll;
+    d.mic_hlr = w->mic_hlr;
+    d.mic_hrl = w->mic_hrl;
+    d.mic_hrr = w->mic_hrr;
+    d.mic_dll = w->mic_dll;
+    d.mic_dlr = w->mic_dlr;
+    d.mic_drl = w->mic_drl;
+    d.mic_drr = w->mic_drr;
+    d.bypass = w->bypass;
+
+    const size_t idx = ctx->wh.size();
+    if (idx + 1 > ctx->d_wh_cap) {
+        const size_t ncap = std::max<size_t>(8, ctx->d_wh_cap * 2);
+        DevWhirlTables *nd = nullptr;
+        CK(cudaMalloc(&nd, sizeof(DevWhirlTables) * ncap));
+        if (idx)
+            cudaMemcpy(nd, ctx->d_wh, sizeof(DevWhirlTables) * idx, cudaMemcpyDeviceToDevice);
+        cudaFree(ctx->d_wh);
+        ctx->d_wh = nd;
+        ctx->d_wh_cap = ncap;
+    }
+    CK(cudaMemcpy(ctx->d_wh + idx, &d, sizeof(d), cudaMemcpyHostToDevice));
+    ctx->wh.push_back(s);
+    *handle = (int)idx;
+    return TBF_OK;
+}
+
+/* the state allocTonegen+initToneGenerator+init_vibrato and allocWhirl+initWhirl
+ * leave behind (src/tonegen.cpp:196-300, :2905-3022; src/vibrato.cpp:288-317;
+ * src/whirl.cpp:40-131, :626-662) */
+static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
+                          const tbf_whirl_tables &w, int whh)
+{
+    memset(s, 0, sizeof(*s));
+    s->newRouting = s->oldRouting = t.init_routing;
+    s->percSendBus = t.init_perc_send_bus;
+    s->swellPedalGain = t.init_swell_pedal_gain;
+    s->drawBarChange = t.init_draw_bar_change;
+    s->percEnabled = t.init_perc_enabled;
+    s->percTrigRestore = t.init_perc_trig_restore;
+    s->percIsSoft = t.init_perc_is_soft;
+    s->percIsFast = t.init_perc_is_fast;
+    s->percEnvGain = 0.0f;
+    s->percEnvGainReset = t.init_perc_env_gain_reset;
+    s->percEnvGainDecay = t.init_perc_env_gain_decay;
+    s->percDrawbarGain = t.init_perc_drawbar_gain;
+    s->outputGain = 1.0f;
+    s->pz = 0.0f;
+    s->keyCompLevel = 1.0f; /* KEYCOMP_ZERO_LEVEL */
+    memcpy(s->drawBarGain, t.init_draw_bar_gain, sizeof(s->drawBarGain));
+    for (int i = 0; i <= TBF_NOF_WHEELS; ++i)
+        s->osc[i].aclPos = -1;
+    s->vibStator = 0;
+    s->vibOutPos = 0x3FF / 2; /* BUF_MASK_SAMPLES / 2, src/vibrato.cpp:294 */
+    s->vibTable = t.init_vib_table;
+    s->vibMixed = t.init_vib_mixed;
+    s->hornAngle = w.init_horn_angle;
+    s->drumAngle = w.init_drum_angle;
+    s->hornIncr = w.init_horn_incr;
+    s->drumIncr = w.init_drum_incr;
+    s->hornTarget = w.init_horn_target;
+    s->drumTarget = w.init_drum_target;
+    s->hornAcDc = w.init_horn_acdc;
+    s->drumAcDc = w.init_drum_acdc;
+    s->revSelect = w.init_rev_select;
+    s->tgTables = tgh;
+    s->whTables = whh;
+}
+
+static int replicate(tbf_ctx *ctx, int tgh, int whh, uint32_t first, uint32_t count)
+{
+    InstState *tmpl = new InstState();
+    fill_template(tmpl, ctx->tg[tgh].host, tgh, ctx->wh[whh].host, whh);
+    cudaError_t e = cudaMemcpyAsync(ctx->d_tmpl, tmpl, sizeof(InstState), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess)
+        e = (cudaError_t)tbf_launch_replicate(ctx->d_states, first, count, ctx->d_tmpl, ctx->stream);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(ctx->stream);
+    delete tmpl;
+    if (e != cudaSuccess) {
+        ctx->err = std::string("instance init: ") + cudaGetErrorString(e);
+        return TBF_ERR_CUDA;
+    }
+    return TBF_OK;
+}
+
+int tbf_gpu_instance_create(tbf_ctx *ctx, int tgh, int whh, uint32_t count, uint32_t *first_id)
+{
+    if (!ctx || !count)
+        return fail(ctx, TBF_ERR_ARG, "instance_create: bad argument");
+    if (tgh < 0 || (size_t)tgh >= ctx->tg.size() || whh < 0 || (size_t)whh >= ctx->wh.size())
+        return fail(ctx, TBF_ERR_HANDLE, "instance_create: unknown table handle");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "instance_create: a launch is in flight");
+    CK(cudaSetDevice(ctx->device));
+    const size_t need = ctx->n_inst + count;
+    if (need > ctx->cap_inst) {
+        size_t ncap = std::max<size_t>(need, ctx->cap_inst * 2);
+        InstState *nd = nullptr;
+        cudaError_t e = cudaMalloc(&nd, sizeof(InstState) * ncap);
+        if (e != cudaSuccess) {
+            ctx->err = std::string("instance_create: ") + cudaGetErrorString(e);
+            cudaGetLastError();
+            return TBF_ERR_NOMEM;
+        }
+        if (ctx->n_inst)
+            CK(cudaMemcpy(nd, ctx->d_states, sizeof(InstState) * ctx->n_inst, cudaMemcpyDeviceToDevice));
+        cudaFree(ctx->d_states);
+        ctx->d_states = nd;
+        ctx->cap_inst = ncap;
+    }
+    const uint32_t first = (uint32_t)ctx->n_inst;
+    int rc = replicate(ctx, tgh, whh, first, count);
+    if (rc != TBF_OK)
+        return rc;
+    ctx->n_inst = need;
+    ctx->inst_tg.resize(need, tgh);
+    ctx->inst_wh.resize(need, whh);
+    if (first_id)
+        *first_id = first;
+    return TBF_OK;
+}
+
+int tbf_gpu_instance_count(const tbf_ctx *ctx) { return ctx ? (int)ctx->n_inst : TBF_ERR_ARG; }
+
+int tbf_gpu_instance_reset(tbf_ctx *ctx, uint32_t first_id, uint32_t count)
+{
+    if (!ctx || (size_t)first_id + count > ctx->n_inst)
+        return fail(ctx, TBF_ERR_HANDLE, "instance_reset: range out of bounds");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "instance_reset: a launch is in flight");
+    CK(cudaSetDevice(ctx->device));
+    uint32_t i = first_id;
+    const uint32_t end = first_id + count;
+    while (i < end) { /* runs of instances sharing both table sets */
+        uint32_t j = i + 1;
+        while (j < end && ctx->inst_tg[j] == ctx->inst_tg[i] && ctx->inst_wh[j] == ctx->inst_wh[i])
+            ++j;
+        int rc = replicate(ctx, ctx->inst_tg[i], ctx->inst_wh[i], i, j - i);
+        if (rc != TBF_OK)
+            return rc;
+        i = j;
+    }
+    return TBF_OK;
+}
+
+} /* extern "C" */
+
+template <typename T> static cudaError_t grow(T **p, size_t *cap, size_t need)
+{
+    if (need <= *cap)
+        return cudaSuccess;
+    cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    cudaError_t e = cudaMalloc(p, sizeof(T) * need);
+    if (e == cudaSuccess)
+        *cap = need;
+    return e;
+}
+
+extern "C" {
+
+int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *d)
+{
+    if (!ctx || !d)
+        return fail(ctx, TBF_ERR_ARG, "render: null argument");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "render: previous launch not synchronized");
+    if (!d->n_instances || !d->n_fragments)
+        return fail(ctx, TBF_ERR_ARG, "render: empty batch");
+    const bool no_out = (d->flags & TBF_RENDER_NO_OUTPUT) != 0;
+    const bool dev_out = (d->flags & TBF_RENDER_OUT_DEVICE) != 0;
+    const uint64_t frames = (uint64_t)d->n_fragments * TBF_FRAGMENT;
+    if (!no_out && (!d->out_l || !d->out_r || d->out_stride < frames))
+        return fail(ctx, TBF_ERR_ARG, "render: output buffers missing or stride too small");
+    if (frames > 0xFFFFFFFFull)
+        return fail(ctx, TBF_ERR_ARG, "render: batch longer than 2^32 samples");
+    if (d->n_events && !d->events)
+        return fail(ctx, TBF_ERR_ARG, "render: events missing");
+    if (d->instance_ids) {
+        /* an instance may appear once per batch: one CTA owns its state */
+        std::vector<uint8_t> seen(ctx->n_inst, 0);
+        for (uint32_t i = 0; i < d->n_instances; ++i) {
+            const uint32_t id = d->instance_ids[i];
+            if (id >= ctx->n_inst)
+                return fail(ctx, TBF_ERR_HANDLE, "render: unknown instance id");
+            if (seen[id])
+                return fail(ctx, TBF_ERR_ARG, "render: instance listed twice");
+            seen[id] = 1;
+        }
+    } else if (d->n_instances > ctx->n_inst) {
+        return fail(ctx, TBF_ERR_HANDLE, "render: more instances than created");
+    }
+    /* events: sorted by (slot, fragment); build the per-slot CSR */
+    std::vector<uint64_t> &evs = ctx->ev_start_host;
+    evs.assign((size_t)d->n_instances + 1, 0);
+    {
+        uint32_t prev_slot = 0, prev_frag = 0;
+        for (uint64_t e = 0; e < d->n_events; ++e) {
+            const tbf_event &ev = d->events[e];
+            if (ev.instance >= d->n_instances || ev.fragment >= d->n_fragments)
+                return fail(ctx, TBF_ERR_ARG, "render: event slot or fragment out of range");
+            if (ev.instance < prev_slot || (ev.instance == prev_slot && ev.fragment < prev_frag))
+                return fail(ctx, TBF_ERR_ARG, "render: events not sorted by (slot, fragment)");
+            prev_slot = ev.instance;
+            prev_frag = ev.fragment;
+            evs[ev.instance + 1]++;
+        }
+        for (uint32_t i = 0; i < d->n_instances; ++i)
+            evs[i + 1] += evs[i];
+    }
+    CK(cudaSetDevice(ctx->device));
+    CK(grow(&ctx->d_events, &ctx->cap_events, std::max<uint64_t>(1, d->n_events)));
+    if (d->n_instances + 1 > ctx->cap_slots) {
+        size_t c0 = 0, c1 = 0, c2 = 0;
+        CK(grow(&ctx->d_ev_start, &c0, (size_t)d->n_instances + 1));
+        CK(grow(&ctx->d_ids, &c1, (size_t)d->n_instances + 1));
+        CK(grow(&ctx->d_csum, &c2, (size_t)d->n_instances + 1));
+        ctx->cap_slots = (size_t)d->n_instances + 1;
+    }
+    float *o_l = nullptr, *o_r = nullptr;
+    uint64_t stride = d->out_stride;
+    if (!no_out) {
+        if (dev_out) {
+            o_l = d->out_l;
+            o_r = d->out_r;
+        } else {
+            stride = frames;
+            cudaError_t e = grow(&ctx->d_out, &ctx->cap_out, (size_t)2 * d->n_instances * frames);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                ctx->err = "render: device output staging buffer does not fit";
+                return TBF_ERR_NOMEM;
+            }
+            o_l = ctx->d_out;
+            o_r = ctx->d_out + (size_t)d->n_instances * frames;
+        }
+    }
+    if (d->n_events)
+        CK(cudaMemcpyAsync(ctx->d_events, d->events, sizeof(tbf_event) * d->n_events,
+                           cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->d_ev_start, evs.data(), sizeof(uint64_t) * evs.size(),
+                       cudaMemcpyHostToDevice, ctx->stream));
+    if (d->instance_ids)
+        CK(cudaMemcpyAsync(ctx->d_ids, d->instance_ids, sizeof(uint32_t) * d->n_instances,
+                           cudaMemcpyHostToDevice, ctx->stream));
+
+    RenderParams p;
+    p.states = ctx->d_states;
+    p.ids = d->instance_ids ? ctx->d_ids : nullptr;
+    p.tg = ctx->d_tg;
+    p.wh = ctx->d_wh;
+    p.events = ctx->d_events;
+    p.ev_start = ctx->d_ev_start;
+    p.out_l = o_l;
+    p.out_r = o_r;
+    p.checksums = d->checksums ? ctx->d_csum : nullptr;
+    p.out_stride = stride;
+    p.n_instances = d->n_instances;
+    p.n_fragments = d->n_fragments;
+    p.flags = d->flags;
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    int rc = tbf_launch_render(p, ctx->stream);
+    if (rc != 0) {
+        ctx->err = std::string("render kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
+        return TBF_ERR_CUDA;
+    }
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->launches = 1;
+    if (!no_out && !dev_out) {
+        CK(cudaMemcpy2DAsync(d->out_l, sizeof(float) * d->out_stride, o_l, sizeof(float) * frames,
+                             sizeof(float) * frames, d->n_instances, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpy2DAsync(d->out_r, sizeof(float) * d->out_stride, o_r, sizeof(float) * frames,
+                             sizeof(float) * frames, d->n_instances, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (d->checksums)
+        CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * d->n_instances,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->in_flight = true;
+    return TBF_OK;
+}
+
+int tbf_gpu_synchronize(tbf_ctx *ctx)
+{
+    if (!ctx)
+        return TBF_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    ctx->in_flight = false;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return TBF_OK;
+}
+
+int tbf_gpu_render_batch(tbf_ctx *ctx, const tbf_batch_desc *d)
+{
+    int rc = tbf_gpu_render_batch_launch(ctx, d);
+    if (rc != TBF_OK)
+        return rc;
+    return tbf_gpu_synchronize(ctx);
+}
+
+int tbf_gpu_last_launch_ms(tbf_ctx *ctx, float *ms, int *n_kernel_launches)
+{
+    if (!ctx || ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "last_launch_ms: synchronize first");
+    if (ms)
+        CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
+    if (n_kernel_launches)
+        *n_kernel_launches = ctx->launches;
+    return TBF_OK;
+}
+
+int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
+{
+    if (!ctx || !o || instance >= ctx->n_inst)
+        return fail(ctx, TBF_ERR_HANDLE, "export_state: unknown instance");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "export_state: synchronize first");
+    CK(cudaSetDevice(ctx->device));
+    InstState *s = new InstState();
+    cudaError_t e = cudaMemcpy(s, ctx->d_states + instance, sizeof(InstState), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+        delete s;
+        ctx->err = cudaGetErrorString(e);
+        return TBF_ERR_CUDA;
+    }
+    memset(o, 0, sizeof(*o));
+    o->active_osc_l_end = s->activeOscLEnd;
+    for (int i = 0; i < s->activeOscLEnd && i <= TBF_NOF_WHEELS; ++i)
+        o->active_osc_list[i] = s->activeOscList[i];
+    for (int i = 0; i <= TBF_NOF_WHEELS; ++i) {
+        o->osc_pos[i] = s->osc[i].pos;
+        o->osc_acl_pos[i] = s->osc[i].aclPos;
+        o->ref_count[i] = s->osc[i].refCount;
+    }
+    o->old_routing = s->oldRouting;
+    o->new_routing = s->newRouting;
+    o->upper_key_count = s->upperKeyCount;
+    o->key_down_count = s->keyDownCount;
+    o->perc_env_gain = s->percEnvGain;
+    o->key_comp_level = s->keyCompLevel;
+    o->pz = s->pz;
+    o->vib_stator = s->vibStator;
+    o->vib_out_pos = s->vibOutPos;
+    memcpy(o->vib_buffer, s->vibBuffer, sizeof(o->vib_buffer));
+    o->whirl_outpos = s->outpos;
+    o->horn_angle = s->hornAngle;
+    o->drum_angle = s->drumAngle;
+    o->horn_incr = s->hornIncr;
+    o->drum_incr = s->drumIncr;
+    o->horn_acdc = s->hornAcDc;
+    o->drum_acdc = s->drumAcDc;
+    memcpy(o->whirl_buf, s->wbuf, sizeof(o->whirl_buf));
+    memcpy(o->iir_z, s->iirz, sizeof(o->iir_z));
+    memcpy(o->filt_z, s->z, sizeof(o->filt_z));
+    memcpy(o->adx, s->adx, sizeof(o->adx));
+    memcpy(o->adi, s->adi, sizeof(o->adi));
+    o->error_flags = s->errorFlags;
+    delete s;
+    return TBF_OK;
+}
+
+unsigned tbf_sizeof_tonegen_tables(void) { return (unsigned)sizeof(tbf_tonegen_tables); }
+unsigned tbf_sizeof_whirl_tables(void) { return (unsigned)sizeof(tbf_whirl_tables); }
+unsigned tbf_sizeof_state_export(void) { return (unsigned)sizeof(tbf_state_export); }
+unsigned tbf_sizeof_batch_desc(void) { return (unsigned)sizeof(tbf_batch_desc); }
+unsigned tbf_sizeof_event(void) { return (unsigned)sizeof(tbf_event); }
+
+} /* extern "C" */

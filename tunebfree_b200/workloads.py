@@ -1,0 +1,75 @@
+"""Synthetic event scripts for BASELINE.json's configurations.
+
+All randomness comes from splitmix64(instance_id xor config_id), so the GPU
+renderer, the oracle and the CPU baseline see identical inputs.
+"""
+import numpy as np
+
+from . import cabi
+
+FRAGMENTS_PER_SECOND = 375  # 48000 / 128
+MASK64 = (1 << 64) - 1
+
+
+def splitmix64(state):
+    """One step of splitmix64 -> (new_state, output)."""
+    state = (state + 0x9E3779B97F4A7C15) & MASK64
+    z = state
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & MASK64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & MASK64
+    return state, z ^ (z >> 31)
+
+
+def chord_keys(instance_id, config_id=0, n_notes=10, lo=36, hi=96):
+    """n_notes distinct upper-manual keys in [lo, hi] for this instance."""
+    s = (instance_id ^ (config_id << 32)) & MASK64
+    keys = []
+    while len(keys) < n_notes:
+        s, r = splitmix64(s)
+        k = lo + r % (hi - lo + 1)
+        if k not in keys:
+            keys.append(k)
+    return keys
+
+
+def setup_events(config):
+    """Fragment-0 control events of a config (before any key)."""
+    ev = [(0, cabi.EV_DRAWBAR, b, 8) for b in range(9)]          # 888888888 upper
+    ev += [(0, cabi.EV_PERC_ENABLE, 1, 0), (0, cabi.EV_PERC_SOFT, 0, 0),
+           (0, cabi.EV_PERC_FAST, 1, 0), (0, cabi.EV_PERC_FIRST, 0, 0)]  # normal / fast / 3rd
+    if config >= 3:
+        ev += [(0, cabi.EV_VIB_UPPER, 1, 0), (0, cabi.EV_VIB_KNOB, 5, 0),  # C3 on the upper manual
+               (0, cabi.EV_REV_OPTION, 8, 0)]                               # horn + drum fast
+    return ev
+
+
+def instance_events(instance_id, n_fragments, config=3, restrike=187, hold=140):
+    """[(fragment, type, a, b)] for one instance: setup at fragment 0, then a 10-note
+    chord struck every `restrike` fragments (~0.5 s) and released after `hold`."""
+    ev = setup_events(config)
+    keys = chord_keys(instance_id, config)
+    f = 0
+    while f < n_fragments:
+        ev += [(f, cabi.EV_KEY_ON, k, 0) for k in keys]
+        off = f + hold
+        if off < n_fragments:
+            ev += [(off, cabi.EV_KEY_OFF, k, 0) for k in keys]
+        f += restrike
+    return ev
+
+
+def batch_events_numpy(first_instance, n_instances, n_fragments, config=3):
+    """int32 [n, 5] rows (slot, fragment, type, a, b) sorted by (slot, fragment)."""
+    rows = []
+    for slot in range(n_instances):
+        evs = sorted(instance_events(first_instance + slot, n_fragments, config), key=lambda t: t[0])
+        a = np.array(evs, dtype=np.int32).reshape(-1, 4)
+        s = np.full((a.shape[0], 1), slot, dtype=np.int32)
+        rows.append(np.concatenate([s, a], axis=1))
+    return np.concatenate(rows, axis=0)
+
+
+def render_flags(config):
+    if config == 2:
+        return cabi.RENDER_WHIRL_BYPASS
+    return cabi.RENDER_WHIRLPROC3
