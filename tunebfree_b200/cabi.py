@@ -205,3 +205,86 @@ class StateExport(C.Structure):
         ("adi", C.c_int32 * 3),
         ("error_flags", C.c_uint32),
     ]
+
+MAX_EXTRA_HARMONICS = 64
+
+
+class TonegenSpec(C.Structure):
+    """tbf_tonegen_spec (include/tbf_tables.h)"""
+    _fields_ = [
+        ("sample_rate", C.c_double),
+        ("freqs", C.c_double * 128),
+        ("target_ratio", C.c_double * 9),
+        ("seed", C.c_uint32),
+        ("precision", C.c_double),
+        ("eq_macro", C.c_int32),
+        ("eq_p1y", C.c_double),
+        ("eq_r1y", C.c_double),
+        ("eq_p4y", C.c_double),
+        ("eq_r4y", C.c_double),
+        ("compartment_crosstalk", C.c_double),
+        ("transformer_crosstalk", C.c_double),
+        ("terminalstrip_crosstalk", C.c_double),
+        ("wiring_crosstalk", C.c_double),
+        ("contribution_floor", C.c_double),
+        ("contribution_min", C.c_double),
+        ("n_extra_harmonics", C.c_int32),
+        ("extra_harmonic_n", C.c_int32 * MAX_EXTRA_HARMONICS),
+        ("extra_harmonic_level", C.c_float * MAX_EXTRA_HARMONICS),
+        ("attack_model", C.c_int32),
+        ("release_model", C.c_int32),
+        ("attack_click_level", C.c_float),
+        ("release_click_level", C.c_float),
+        ("atk_clk_min_length", C.c_int32),
+        ("atk_clk_max_length", C.c_int32),
+        ("perc_gain_norm", C.c_float),
+        ("perc_gain_soft", C.c_float),
+        ("perc_gain_scaling", C.c_float),
+        ("perc_bus_a", C.c_int32),
+        ("perc_bus_b", C.c_int32),
+        ("perc_bus_trig", C.c_int32),
+        ("scanner_hz", C.c_double),
+        ("scanner_amp", C.c_double * 3),
+    ]
+
+
+class WhirlSpec(C.Structure):
+    """tbf_whirl_spec (include/tbf_tables.h)"""
+    _fields_ = [
+        ("sample_rate", C.c_double),
+        ("bypass", C.c_int32),
+        ("hn_brake_pos", C.c_double),
+        ("dr_brake_pos", C.c_double),
+        ("horn_rpm_slow", C.c_float),
+        ("horn_rpm_fast", C.c_float),
+        ("drum_rpm_slow", C.c_float),
+        ("drum_rpm_fast", C.c_float),
+        ("horn_acc", C.c_float),
+        ("horn_dec", C.c_float),
+        ("drum_acc", C.c_float),
+        ("drum_dec", C.c_float),
+        ("mic_angle", C.c_double),
+        ("air_speed", C.c_float),
+        ("mic_dist_cm", C.c_float),
+        ("horn_x_offset_cm", C.c_float),
+        ("horn_z_offset_cm", C.c_float),
+        ("horn_radius_cm", C.c_float),
+        ("drum_radius_cm", C.c_float),
+        ("lp_type", C.c_int32),
+        ("lp_f", C.c_double),
+        ("lp_q", C.c_double),
+        ("lp_g", C.c_double),
+        ("ha_type", C.c_int32),
+        ("ha_f", C.c_float),
+        ("ha_q", C.c_float),
+        ("ha_g", C.c_float),
+        ("hb_type", C.c_int32),
+        ("hb_f", C.c_float),
+        ("hb_q", C.c_float),
+        ("hb_g", C.c_float),
+        ("horn_level", C.c_float),
+        ("leak_level", C.c_float),
+        ("drum_mic_width", C.c_float),
+        ("horn_mic_width", C.c_float),
+        ("rev_select", C.c_int32),
+    ]

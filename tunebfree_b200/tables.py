@@ -1,0 +1,135 @@
+"""Host-side instance specification and table building (include/tbf_tables.h).
+
+`InstanceSpec` is the resolved form of the reference's inputs: the 128 MTS-ESP
+note frequencies, cfg text (osc.*, scanner.*, whirl.*), the rand() seed and the
+sample rate.  `build()` runs the C++ table builder in libtbf_gpu.so -- the
+product's own restatement of initToneGenerator / init_vibrato / initWhirl.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import cabi
+from .engine import lib as _gpu_lib
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = _gpu_lib()
+    if not _bound:
+        L.tbf_tonegen_spec_default.argtypes = [C.POINTER(cabi.TonegenSpec), C.c_double]
+        L.tbf_tonegen_spec_default.restype = None
+        L.tbf_whirl_spec_default.argtypes = [C.POINTER(cabi.WhirlSpec), C.c_double]
+        L.tbf_whirl_spec_default.restype = None
+        L.tbf_freqs_12tet.argtypes = [C.POINTER(C.c_double)]
+        L.tbf_freqs_12tet.restype = None
+        L.tbf_freqs_from_scl.argtypes = [C.c_char_p, C.POINTER(C.c_double)]
+        L.tbf_spec_apply_cfg.argtypes = [C.POINTER(cabi.TonegenSpec), C.POINTER(cabi.WhirlSpec),
+                                         C.c_char_p, C.c_char_p]
+        L.tbf_build_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenSpec),
+                                               C.POINTER(cabi.TonegenTables)]
+        L.tbf_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
+        L.tbf_free_tonegen_tables.restype = None
+        L.tbf_build_whirl_tables.argtypes = [C.POINTER(cabi.WhirlSpec), C.POINTER(cabi.WhirlTables)]
+        L.tbf_free_whirl_tables.argtypes = [C.POINTER(cabi.WhirlTables)]
+        L.tbf_free_whirl_tables.restype = None
+        L.tbf_extend_frequencies.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                             C.POINTER(C.c_int), C.POINTER(C.c_float)]
+        L.tbf_srand.argtypes = [C.c_void_p, C.c_uint32]
+        L.tbf_srand.restype = None
+        L.tbf_rand.argtypes = [C.c_void_p]
+        L.tbf_rand.restype = C.c_int32
+        _bound = True
+    return L
+
+
+def freqs_12tet():
+    f = (C.c_double * 128)()
+    _lib().tbf_freqs_12tet(f)
+    return np.array(f, dtype=np.float64)
+
+
+def freqs_from_scl(text):
+    """Scala .scl text -> 128 note frequencies (degree 0 at MIDI 60 = 261.6255653 Hz)."""
+    f = (C.c_double * 128)()
+    rc = _lib().tbf_freqs_from_scl(text.encode("latin-1", "replace"), f)
+    if rc != cabi.OK:
+        raise ValueError("unparsable .scl (%d)" % rc)
+    return np.array(f, dtype=np.float64)
+
+
+def extend_frequencies(freqs128):
+    f = (C.c_double * 128)(*[float(x) for x in freqs128])
+    out = (C.c_double * cabi.NOF_FREQS)()
+    ss = C.c_int(0)
+    per = C.c_float(0)
+    _lib().tbf_extend_frequencies(f, out, C.byref(ss), C.byref(per))
+    return np.array(out, dtype=np.float64), ss.value, per.value
+
+
+def parse_cfg_lines(text):
+    """cfg text -> [(key, value)] the way the reference tokenises a line
+    (parseConfigurationLine, src/cfgParser.cpp:94-160): '#' comments, key=value,
+    surrounding blanks stripped."""
+    out = []
+    for line in text.splitlines():
+        s = line.strip()
+        if not s or s.startswith("#") or s.startswith("="):
+            continue
+        key, _, val = s.partition("=")
+        val = val.split("#", 1)[0]
+        out.append((key.strip(), val.strip()))
+    return out
+
+
+class InstanceSpec:
+    def __init__(self, freqs=None, rate=48000.0, seed=1, cfg="", target_ratio=None):
+        L = _lib()
+        self.tg = cabi.TonegenSpec()
+        self.wh = cabi.WhirlSpec()
+        L.tbf_tonegen_spec_default(C.byref(self.tg), rate)
+        L.tbf_whirl_spec_default(C.byref(self.wh), rate)
+        if freqs is not None:
+            for i in range(128):
+                self.tg.freqs[i] = float(freqs[i])
+        if target_ratio is not None:
+            for i in range(9):
+                self.tg.target_ratio[i] = float(target_ratio[i])
+        self.tg.seed = seed
+        self.rejected = []   # out-of-range values: ignored, like the reference does
+        self.unclaimed = []  # keys of other modules (midi.*, reverb.*, ...): not this path
+        if cfg:
+            self.apply_cfg(cfg)
+
+    def apply_cfg(self, text):
+        L = _lib()
+        for key, val in parse_cfg_lines(text):
+            rc = L.tbf_spec_apply_cfg(C.byref(self.tg), C.byref(self.wh), key.encode(), val.encode())
+            if rc == 0:
+                self.unclaimed.append((key, val))
+            elif rc < 0:
+                self.rejected.append((key, val))
+
+    def build(self):
+        """-> (TonegenTables, WhirlTables); free with free_tables()."""
+        L = _lib()
+        tt = cabi.TonegenTables()
+        rc = L.tbf_build_tonegen_tables(C.byref(self.tg), C.byref(tt))
+        if rc != cabi.OK:
+            raise ValueError("tbf_build_tonegen_tables failed (%d)" % rc)
+        wt = cabi.WhirlTables()
+        rc = L.tbf_build_whirl_tables(C.byref(self.wh), C.byref(wt))
+        if rc != cabi.OK:
+            L.tbf_free_tonegen_tables(C.byref(tt))
+            raise ValueError("tbf_build_whirl_tables failed (%d)" % rc)
+        return tt, wt
+
+
+def free_tables(tt, wt):
+    L = _lib()
+    if tt is not None:
+        L.tbf_free_tonegen_tables(C.byref(tt))
+    if wt is not None:
+        L.tbf_free_whirl_tables(C.byref(wt))
