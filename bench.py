@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py -- realtime-instances benchmark of the tonewheel -> scanner -> Leslie path.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU engine
+
+A "step" = one pass of the hot path over one batch: `instances` organs x `seconds`
+of 48 kHz stereo audio (default: BASELINE config 3 = 4096 instances, tonegen +
+vibrato C3 + Leslie fast through whirlProc3, 10 s each).  Multi-GPU: one process per
+GPU (torchrun), every rank renders its own `instances` organs (weak scaling, no
+collective on the data path); the timed region is bracketed by barriers and the
+slowest rank's device time is used.
+
+metric  = organ-seconds of 48 kHz stereo audio rendered per wall-second
+value   = device-resident: events uploaded before the timed region, audio kept in HBM
+e2e     = through tbf_gpu_render_batch with HOST buffers: events copied host->device and
+          all audio copied device->host inside the timed region, every step
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+
+METRIC = "realtime-instances: 48 kHz stereo organ-seconds rendered per wall-second"
+UNIT = "organ-seconds/s"
+N_TABLE_SETS = 16  # engine seeds 1 + id mod 16: 16 dither/click realisations
+DEFAULT_INSTANCES = {2: 1024, 3: 4096, 5: 16384}
+WORKLOAD_NAME = {
+    2: "config2: tonegen only, drawbars 888888888, 10-note chords re-struck every 0.5 s, "
+       "percussion + key click, whirl bypassed",
+    3: "config3: tonegen + vibrato C3 + Leslie fast (whirlProc3), drawbars 888888888, 10-note "
+       "chords re-struck every 0.5 s, percussion + key click",
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=3, choices=[2, 3])
+    ap.add_argument("--instances", type=int, default=0, help="instances per GPU")
+    ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per instance per step")
+    ap.add_argument("--cpu-sample-seconds", type=float, default=15.0,
+                    help="target CPU time of the bounded cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------
+# CPU arm: the reference's own engine (oracle/_ref), one instance per host core
+# --------------------------------------------------------------------------
+def _cpu_worker(args):
+    """Runs in a forked worker: init its instances, wait for the common start time, render."""
+    ids, n_frag, config, start_at = args
+    from oracle import ref_engine
+    from tunebfree_b200 import workloads
+    # a few engine instances per worker, cycled: the render cost does not depend on which
+    # organ plays which script, and 3 MB per reference instance adds up on many-core hosts
+    engines = [ref_engine.RefInstance(seed=1 + i % N_TABLE_SETS) for i in ids[:4]]
+    insts = []
+    for j, i in enumerate(ids):
+        ev = workloads.instance_events(i, n_frag, config)
+        insts.append((engines[j % len(engines)], ref_engine.events_array(ev)))
+    flags = workloads.render_flags(config)
+    outl = np.zeros(n_frag * 128, dtype=np.float32)
+    outr = np.zeros(n_frag * 128, dtype=np.float32)
+    L = ref_engine.lib()
+    import ctypes as C
+    while time.time() < start_at:
+        time.sleep(0.001)
+    t0 = time.time()
+    for r, (arr, n) in insts:
+        L.ref_render(r._h, n_frag, flags, arr, n, outl.ctypes.data_as(C.c_void_p),
+                     outr.ctypes.data_as(C.c_void_p))
+    t1 = time.time()
+    return t0, t1, float(np.abs(outl).max())
+
+
+def cpu_reference_pass(config, n_frag, per_core, cores):
+    """One bounded sample: cores x per_core instances of n_frag fragments on `cores` worker
+    processes (the engine is single-threaded and rand() is process-global).  Returns
+    organ-seconds/s over the common render window."""
+    import multiprocessing as mp
+    ctx = mp.get_context("fork")
+    start_at = time.time() + 3.0 + 0.01 * per_core  # every worker finishes its inits first
+    jobs = [(list(range(c * per_core, (c + 1) * per_core)), n_frag, config, start_at)
+            for c in range(cores)]
+    with ctx.Pool(cores) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    t0 = min(r[0] for r in res)
+    t1 = max(r[1] for r in res)
+    organ_seconds = cores * per_core * n_frag / 375.0
+    return organ_seconds / (t1 - t0), t1 - t0
+
+
+def cpu_sample_plan(config, seconds, target_cpu_seconds, cores):
+    """Instances per core so that one sample is about target_cpu_seconds of wall time
+    (the reference runs ~45x realtime per core with the Leslie, ~400x without)."""
+    per_core_rate = 45.0 if config >= 3 else 350.0
+    per_core = max(1, int(round(target_cpu_seconds * per_core_rate / seconds)))
+    return per_core
+
+
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # the CPU engine has no use for more ranks: rank 0 alone measures
+    from oracle import ref_engine
+    ref_engine.lib()
+    cores = os.cpu_count() or 1
+    n_frag = int(round(a.seconds * 375))
+    per_core = cpu_sample_plan(a.config, a.seconds, a.cpu_sample_seconds, cores)
+    vals = []
+    for _ in range(a.warmup and 1):  # one short warm-up pass: page in the library, spin clocks up
+        cpu_reference_pass(a.config, max(8, n_frag // 20), 1, cores)
+    t_all = 0.0
+    for _ in range(a.steps):
+        v, dt = cpu_reference_pass(a.config, n_frag, per_core, cores)
+        vals.append(v)
+        t_all += dt
+    value = float(np.mean(vals))
+    sample = "%d instances x %.1f s (%d per core) per step, oracle/_ref = reference engine, strict IEEE -O2" % (
+        cores * per_core, a.seconds, per_core)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * t_all / max(1, a.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD_NAME[a.config], "instances_per_step": cores * per_core,
+                   "seconds_per_instance": a.seconds, "sample_rate": 48000, "host_cores": cores},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------
+# clocks during the timed region
+# --------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    def __init__(self, device_index):
+        super().__init__(daemon=True)
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_ev = threading.Event()
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._h = None
+
+    def run(self):
+        if self._h is None:
+            return
+        nv = self._nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self._stop_ev.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop_ev.wait(0.1)
+
+    def stop(self):
+        self._stop_ev.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def physical_device_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+# --------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return None
+
+
+def run_gpu_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    # CPU baseline first (forks worker processes: must happen before any CUDA context)
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        n_frag_cpu = int(round(a.seconds * 375))
+        per_core = cpu_sample_plan(a.config, a.seconds, a.cpu_sample_seconds, cores)
+        cpu_reference_pass(a.config, max(8, n_frag_cpu // 20), 1, cores)
+        v, _ = cpu_reference_pass(a.config, n_frag_cpu, per_core, cores)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference",
+                        "sample": "%d instances x %.1f s (%d per core), oracle/_ref = the reference "
+                                  "engine compiled strict IEEE -O2, one process per core"
+                                  % (cores * per_core, a.seconds, per_core)}
+
+    import torch
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from tunebfree_b200 import cabi, engine, tables, workloads
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n_inst = a.instances or DEFAULT_INSTANCES[a.config]
+    n_frag = int(round(a.seconds * 375))
+    frames = n_frag * 128
+    flags = workloads.render_flags(a.config)
+    first_global = rank * n_inst  # every rank plays different organs
+
+    ctx = engine.Context(local_rank)
+    # 16 table sets (seeds 1..16) built by the product's own host-side builder
+    handles = []
+    wh_handle = None
+    for s in range(N_TABLE_SETS):
+        spec = tables.InstanceSpec(seed=1 + s)
+        tt, wt = spec.build()
+        handles.append(ctx.tonegen_tables(tt))
+        if wh_handle is None:
+            wh_handle = ctx.whirl_tables(wt)
+        tables.free_tables(tt, wt)
+    # slot i plays global instance first_global + i with table set (global id) mod 16
+    ids = np.zeros(n_inst, dtype=np.uint32)
+    per_set = [[] for _ in range(N_TABLE_SETS)]
+    for slot in range(n_inst):
+        per_set[(first_global + slot) % N_TABLE_SETS].append(slot)
+    for s in range(N_TABLE_SETS):
+        if per_set[s]:
+            first = ctx.create_instances(handles[s], wh_handle, len(per_set[s]))
+            ids[per_set[s]] = np.arange(first, first + len(per_set[s]), dtype=np.uint32)
+    ev_np = workloads.batch_events_numpy(first_global, n_inst, n_frag, a.config)
+    events = engine.events_from_numpy(ev_np)
+    h2d_bytes = int(ev_np.shape[0] * 20 + n_inst * 4 + (n_inst + 1) * 8)
+
+    # ---- value: device resident ----
+    out = torch.empty((2, n_inst, frames), dtype=torch.float32, device="cuda:%d" % local_rank)
+    ctx.prepare(n_inst, n_frag, events, flags | cabi.RENDER_OUT_DEVICE, out[0].data_ptr(),
+                out[1].data_ptr(), frames, ids=ids)
+    for _ in range(a.warmup):
+        ctx.launch()
+        ctx.synchronize()
+    sampler = ClockSampler(physical_device_index(local_rank))
+    torch.cuda.synchronize()
+    barrier()
+    sampler.start()
+    kernel_ms = 0.0
+    launches = 0
+    ctx.timer_start()
+    for _ in range(a.steps):
+        ctx.launch()
+        ctx.synchronize()
+        ms, nl = ctx.last_launch_ms()
+        kernel_ms += ms
+        launches += nl
+    total_ms = ctx.timer_stop()
+    torch.cuda.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    total_ms = max_over_ranks(total_ms)
+    peak_out = float(out[0, 0].abs().max().item())
+    st = ctx.export_state(int(ids[0]))
+    n_act = st.stat_active_wheels / max(1, st.stat_fragments)
+    del out
+    torch.cuda.empty_cache()
+
+    organ_seconds_step = n_inst * a.seconds
+    value = world * organ_seconds_step * a.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host buffers through tbf_gpu_render_batch ----
+    e2e = None
+    if not a.no_e2e:
+        try:
+            hl, pl = ctx.host_alloc((n_inst, frames))
+            hr, pr = ctx.host_alloc((n_inst, frames))
+            pinned = True
+        except MemoryError:
+            hl = np.empty((n_inst, frames), dtype=np.float32)
+            hr = np.empty((n_inst, frames), dtype=np.float32)
+            pl = pr = None
+            pinned = False
+
+        def e2e_step():
+            ctx.prepare(n_inst, n_frag, events, flags, hl.ctypes.data, hr.ctypes.data, frames, ids=ids)
+            ctx.launch()
+            ctx.synchronize()
+
+        for _ in range(max(1, min(a.warmup, 2))):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            e2e_step()
+        dt = time.perf_counter() - t0
+        barrier()
+        dt = max_over_ranks(dt)
+        e2e = {"value": world * organ_seconds_step * a.steps / dt, "unit": UNIT,
+               "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(2 * n_inst * frames * 4),
+               "host_buffers": "page-locked" if pinned else "pageable",
+               "peak_abs_sample": float(np.abs(hl[0]).max())}
+        if pl:
+            ctx.host_free(pl)
+            ctx.host_free(pr)
+
+    if rank == 0:
+        peaks = measured_peaks()
+        hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
+        secs_per_launch = organ_seconds_step * a.steps / max(1, launches)
+        dur = (kernel_ms * 1e-3) / max(1, launches)
+        whirl = 1 if a.config >= 3 else 0
+        f_clk = (clocks.get("sm_mhz") or (peaks or {}).get("sm_max_mhz") or 1965.0) * 1e6
+        # algorithmic work per organ-second (DESIGN.md "Rooflines")
+        hbm_bytes = 48000 * 2 * 4
+        w32 = 48000 * (6 * n_act + 17 + 253 * whirl)
+        bsm = 48000 * (4 * n_act + 70 + 380 * whirl)
+        ach_hbm = hbm_bytes * secs_per_launch / dur / 1e9
+        roofline = {"bound": "hbm", "achieved": ach_hbm, "peak": hbm_peak, "unit": "GB/s",
+                    "frac": ach_hbm / hbm_peak, "traffic": None,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                    "note": "HBM is not the binding roofline of this path (384 kB of output per "
+                            "organ-second); the FP32-issue and shared-memory rooflines below are",
+                    "kernel": "tbf_render_kernel", "avg_launch_ms": dur * 1e3,
+                    "n_act": n_act,
+                    "fp32_issue": {"achieved": w32 * secs_per_launch / dur / 1e12,
+                                   "peak": 148 * 128 * f_clk / 1e12, "unit": "T lane-ops/s",
+                                   "frac": (w32 * secs_per_launch / dur) / (148 * 128 * f_clk)},
+                    "smem_bw": {"achieved": bsm * secs_per_launch / dur / 1e12,
+                                "peak": 148 * 128 * f_clk / 1e12, "unit": "TB/s",
+                                "frac": (bsm * secs_per_launch / dur) / (148 * 128 * f_clk)}}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": total_ms / a.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_NAME[a.config], "instances_per_gpu": n_inst,
+                       "seconds_per_instance": a.seconds, "sample_rate": 48000,
+                       "table_sets": N_TABLE_SETS, "tuning": "12-TET",
+                       "l2": "inputs larger than L2 (instance state %.0f MB + %.1f GB of output per step)"
+                             % (n_inst * 0.08, 2 * n_inst * frames * 4 / 1e9),
+                       "parallelism": "instances sharded over %d GPU(s), no collective" % world},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches + (a.steps * ((n_frag + 124) // 125) if e2e else 0),
+            "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "checks": {"peak_abs_sample": peak_out, "error_flags": int(st.error_flags)},
+        }
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_gpu_arm(a)
+
+
+if __name__ == "__main__":
+    main()

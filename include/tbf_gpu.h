@@ -192,9 +192,22 @@ int tbf_gpu_instance_reset(tbf_ctx *ctx, uint32_t first_id, uint32_t count);
  * (src/clap.cpp:254-258)                                                     */
 int tbf_gpu_render_batch(tbf_ctx *ctx, const tbf_batch_desc *desc);
 
-/* asynchronous halves used by the benchmark to time the device alone         */
+/* asynchronous pieces: prepare validates the batch and uploads events / ids once;
+ * launch renders the prepared batch on the library's stream and may be repeated
+ * (the instances keep playing the same event script); render_batch_launch =
+ * prepare + launch; render_batch = prepare + launch + synchronize.
+ * Host outputs are streamed back in chunks overlapping the render (page-locked
+ * buffers from tbf_gpu_host_alloc make that copy asynchronous).               */
+int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *desc);
+int tbf_gpu_batch_launch(tbf_ctx *ctx);
 int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *desc);
 int tbf_gpu_synchronize(tbf_ctx *ctx);
+void *tbf_gpu_host_alloc(tbf_ctx *ctx, size_t bytes);
+void tbf_gpu_host_free(tbf_ctx *ctx, void *p);
+int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments);
+/* CUDA-event stopwatch on the library's stream                                 */
+int tbf_gpu_timer_start(tbf_ctx *ctx);
+int tbf_gpu_timer_stop(tbf_ctx *ctx, float *ms);
 /* device time of the last launch in ms (CUDA events on the library's stream),
  * and how many kernels it launched                                           */
 int tbf_gpu_last_launch_ms(tbf_ctx *ctx, float *ms, int *n_kernel_launches);
@@ -220,6 +233,9 @@ typedef struct tbf_state_export {
     float adx[3][8];
     int32_t adi[3];
     uint32_t error_flags;              /* TBF_IFLAG_*                          */
+    uint32_t pad_;
+    uint64_t stat_fragments;           /* fragments rendered since create/reset */
+    uint64_t stat_active_wheels;       /* sum over them of the active-list length */
 } tbf_state_export;
 int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *out);
 

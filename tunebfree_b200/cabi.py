@@ -204,6 +204,9 @@ class StateExport(C.Structure):
         ("adx", (C.c_float * 8) * 3),
         ("adi", C.c_int32 * 3),
         ("error_flags", C.c_uint32),
+        ("pad_", C.c_uint32),
+        ("stat_fragments", C.c_uint64),
+        ("stat_active_wheels", C.c_uint64),
     ]
 
 MAX_EXTRA_HARMONICS = 64

@@ -51,7 +51,14 @@ struct tbf_ctx {
     float *d_out = nullptr;
     size_t cap_out = 0;
     /* pending host copies of the launch in flight */
-    tbf_batch_desc pending{};
+    tbf_batch_desc prepared{};
+    bool has_prepared = false, prepared_has_ids = false;
+    uint32_t prepared_chunk = 0;
+    uint32_t host_chunk_fragments = 125; /* 1/3 s of audio per staging chunk */
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t render_done[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr};
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    uint64_t *d_ev_cursor = nullptr;
     bool in_flight = false;
     int launches = 0;
     std::vector<uint64_t> ev_start_host;
@@ -87,7 +94,13 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     ctx->device = device;
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+        cudaEventCreate(&ctx->t0) != cudaSuccess || cudaEventCreate(&ctx->t1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->render_done[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->render_done[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->copy_done[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->copy_done[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaMalloc(&ctx->d_tmpl, sizeof(InstState)) != cudaSuccess) {
         delete ctx;
         return TBF_ERR_CUDA;
@@ -116,11 +129,19 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     cudaFree(ctx->d_tmpl);
     cudaFree(ctx->d_events);
     cudaFree(ctx->d_ev_start);
+    cudaFree(ctx->d_ev_cursor);
     cudaFree(ctx->d_ids);
     cudaFree(ctx->d_csum);
     cudaFree(ctx->d_out);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
+    for (int i = 0; i < 2; ++i) {
+        cudaEventDestroy(ctx->render_done[i]);
+        cudaEventDestroy(ctx->copy_done[i]);
+    }
+    cudaEventDestroy(ctx->t0);
+    cudaEventDestroy(ctx->t1);
+    cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -443,12 +464,16 @@ template <typename T> static cudaError_t grow(T **p, size_t *cap, size_t need)
 
 extern "C" {
 
-int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *d)
+/* Validate a batch, upload its events / ids and reset the per-slot event cursors.
+ * The prepared batch can then be launched (and re-launched: the instances simply
+ * keep playing) without touching the host data again. */
+int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
 {
     if (!ctx || !d)
         return fail(ctx, TBF_ERR_ARG, "render: null argument");
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "render: previous launch not synchronized");
+    ctx->has_prepared = false;
     if (!d->n_instances || !d->n_fragments)
         return fail(ctx, TBF_ERR_ARG, "render: empty batch");
     const bool no_out = (d->flags & TBF_RENDER_NO_OUTPUT) != 0;
@@ -494,29 +519,26 @@ int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *d)
     }
     CK(cudaSetDevice(ctx->device));
     CK(grow(&ctx->d_events, &ctx->cap_events, std::max<uint64_t>(1, d->n_events)));
-    if (d->n_instances + 1 > ctx->cap_slots) {
-        size_t c0 = 0, c1 = 0, c2 = 0;
+    if ((size_t)d->n_instances + 1 > ctx->cap_slots) {
+        size_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
         CK(grow(&ctx->d_ev_start, &c0, (size_t)d->n_instances + 1));
+        CK(grow(&ctx->d_ev_cursor, &c3, (size_t)d->n_instances + 1));
         CK(grow(&ctx->d_ids, &c1, (size_t)d->n_instances + 1));
         CK(grow(&ctx->d_csum, &c2, (size_t)d->n_instances + 1));
         ctx->cap_slots = (size_t)d->n_instances + 1;
     }
-    float *o_l = nullptr, *o_r = nullptr;
-    uint64_t stride = d->out_stride;
-    if (!no_out) {
-        if (dev_out) {
-            o_l = d->out_l;
-            o_r = d->out_r;
-        } else {
-            stride = frames;
-            cudaError_t e = grow(&ctx->d_out, &ctx->cap_out, (size_t)2 * d->n_instances * frames);
-            if (e != cudaSuccess) {
-                cudaGetLastError();
-                ctx->err = "render: device output staging buffer does not fit";
-                return TBF_ERR_NOMEM;
-            }
-            o_l = ctx->d_out;
-            o_r = ctx->d_out + (size_t)d->n_instances * frames;
+    /* host outputs are streamed back in chunks of fragments through two device
+     * staging buffers, so the device-to-host copy of chunk i overlaps the render
+     * of chunk i+1; device outputs (or none) are one launch */
+    uint32_t chunk = d->n_fragments;
+    if (!no_out && !dev_out) {
+        chunk = std::min<uint32_t>(d->n_fragments, ctx->host_chunk_fragments);
+        const size_t need = (size_t)2 /*buffers*/ * 2 /*L,R*/ * d->n_instances * chunk * TBF_FRAGMENT;
+        cudaError_t e = grow(&ctx->d_out, &ctx->cap_out, need);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            ctx->err = "render: device output staging buffer does not fit";
+            return TBF_ERR_NOMEM;
         }
     }
     if (d->n_events)
@@ -527,40 +549,97 @@ int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *d)
     if (d->instance_ids)
         CK(cudaMemcpyAsync(ctx->d_ids, d->instance_ids, sizeof(uint32_t) * d->n_instances,
                            cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream)); /* the host arrays may be freed after prepare */
+    ctx->prepared = *d;
+    ctx->prepared.events = nullptr;
+    ctx->prepared.instance_ids = nullptr;
+    ctx->prepared_has_ids = d->instance_ids != nullptr;
+    ctx->prepared_chunk = chunk;
+    ctx->has_prepared = true;
+    return TBF_OK;
+}
+
+/* Launch the prepared batch on the library's stream (asynchronous). */
+int tbf_gpu_batch_launch(tbf_ctx *ctx)
+{
+    if (!ctx || !ctx->has_prepared)
+        return fail(ctx, TBF_ERR_ARG, "launch: no prepared batch");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "launch: previous launch not synchronized");
+    const tbf_batch_desc *d = &ctx->prepared;
+    const bool no_out = (d->flags & TBF_RENDER_NO_OUTPUT) != 0;
+    const bool dev_out = (d->flags & TBF_RENDER_OUT_DEVICE) != 0;
+    const bool host_out = !no_out && !dev_out;
+    const uint32_t chunk = ctx->prepared_chunk;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpyAsync(ctx->d_ev_cursor, ctx->d_ev_start, sizeof(uint64_t) * d->n_instances,
+                       cudaMemcpyDeviceToDevice, ctx->stream));
+    if (d->checksums)
+        CK(cudaMemsetAsync(ctx->d_csum, 0, sizeof(uint64_t) * d->n_instances, ctx->stream));
 
     RenderParams p;
     p.states = ctx->d_states;
-    p.ids = d->instance_ids ? ctx->d_ids : nullptr;
+    p.ids = ctx->prepared_has_ids ? ctx->d_ids : nullptr;
     p.tg = ctx->d_tg;
     p.wh = ctx->d_wh;
     p.events = ctx->d_events;
     p.ev_start = ctx->d_ev_start;
-    p.out_l = o_l;
-    p.out_r = o_r;
+    p.ev_cursor = ctx->d_ev_cursor;
     p.checksums = d->checksums ? ctx->d_csum : nullptr;
-    p.out_stride = stride;
     p.n_instances = d->n_instances;
-    p.n_fragments = d->n_fragments;
     p.flags = d->flags;
+    ctx->launches = 0;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    int rc = tbf_launch_render(p, ctx->stream);
-    if (rc != 0) {
-        ctx->err = std::string("render kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
-        return TBF_ERR_CUDA;
+    const size_t half = (size_t)2 * d->n_instances * chunk * TBF_FRAGMENT;
+    int k = 0;
+    for (uint32_t base = 0; base < d->n_fragments; base += chunk, ++k) {
+        const uint32_t nf = std::min<uint32_t>(chunk, d->n_fragments - base);
+        const int buf = k & 1;
+        p.frag_base = base;
+        p.n_fragments = nf;
+        if (host_out) {
+            /* staging buffer `buf` is free once the copy issued two chunks ago is done */
+            if (k >= 2)
+                CK(cudaStreamWaitEvent(ctx->stream, ctx->copy_done[buf], 0));
+            p.out_stride = (uint64_t)nf * TBF_FRAGMENT;
+            p.out_l = ctx->d_out + half * buf;
+            p.out_r = p.out_l + (size_t)d->n_instances * p.out_stride;
+        } else {
+            p.out_stride = d->out_stride;
+            p.out_l = no_out ? nullptr : d->out_l + (size_t)base * TBF_FRAGMENT;
+            p.out_r = no_out ? nullptr : d->out_r + (size_t)base * TBF_FRAGMENT;
+        }
+        int rc = tbf_launch_render(p, ctx->stream);
+        if (rc != 0) {
+            ctx->err = std::string("render kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
+            return TBF_ERR_CUDA;
+        }
+        ctx->launches++;
+        if (host_out) {
+            CK(cudaEventRecord(ctx->render_done[buf], ctx->stream));
+            CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->render_done[buf], 0));
+            const size_t w = sizeof(float) * (size_t)nf * TBF_FRAGMENT;
+            CK(cudaMemcpy2DAsync(d->out_l + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
+                                 p.out_l, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            CK(cudaMemcpy2DAsync(d->out_r + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
+                                 p.out_r, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            CK(cudaEventRecord(ctx->copy_done[buf], ctx->copy_stream));
+        }
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->launches = 1;
-    if (!no_out && !dev_out) {
-        CK(cudaMemcpy2DAsync(d->out_l, sizeof(float) * d->out_stride, o_l, sizeof(float) * frames,
-                             sizeof(float) * frames, d->n_instances, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpy2DAsync(d->out_r, sizeof(float) * d->out_stride, o_r, sizeof(float) * frames,
-                             sizeof(float) * frames, d->n_instances, cudaMemcpyDeviceToHost, ctx->stream));
-    }
     if (d->checksums)
         CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * d->n_instances,
                            cudaMemcpyDeviceToHost, ctx->stream));
     ctx->in_flight = true;
     return TBF_OK;
+}
+
+int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *d)
+{
+    int rc = tbf_gpu_batch_prepare(ctx, d);
+    if (rc != TBF_OK)
+        return rc;
+    return tbf_gpu_batch_launch(ctx);
 }
 
 int tbf_gpu_synchronize(tbf_ctx *ctx)
@@ -570,6 +649,7 @@ int tbf_gpu_synchronize(tbf_ctx *ctx)
     CK(cudaSetDevice(ctx->device));
     ctx->in_flight = false;
     CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaStreamSynchronize(ctx->copy_stream));
     return TBF_OK;
 }
 
@@ -589,6 +669,54 @@ int tbf_gpu_last_launch_ms(tbf_ctx *ctx, float *ms, int *n_kernel_launches)
         CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
     if (n_kernel_launches)
         *n_kernel_launches = ctx->launches;
+    return TBF_OK;
+}
+
+/* CUDA-event stopwatch on the library's stream (bench: time K launches on the device) */
+int tbf_gpu_timer_start(tbf_ctx *ctx)
+{
+    if (!ctx)
+        return TBF_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventRecord(ctx->t0, ctx->stream));
+    return TBF_OK;
+}
+
+int tbf_gpu_timer_stop(tbf_ctx *ctx, float *ms)
+{
+    if (!ctx || !ms)
+        return TBF_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventRecord(ctx->t1, ctx->stream));
+    CK(cudaEventSynchronize(ctx->t1));
+    CK(cudaEventElapsedTime(ms, ctx->t0, ctx->t1));
+    return TBF_OK;
+}
+
+/* page-locked host buffers, so host-output batches stream back asynchronously */
+void *tbf_gpu_host_alloc(tbf_ctx *ctx, size_t bytes)
+{
+    void *p = nullptr;
+    if (!ctx || cudaSetDevice(ctx->device) != cudaSuccess)
+        return nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void tbf_gpu_host_free(tbf_ctx *ctx, void *p)
+{
+    if (ctx && p)
+        cudaFreeHost(p);
+}
+
+int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments)
+{
+    if (!ctx || !fragments)
+        return TBF_ERR_ARG;
+    ctx->host_chunk_fragments = fragments;
     return TBF_OK;
 }
 
@@ -638,6 +766,8 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
     memcpy(o->adx, s->adx, sizeof(o->adx));
     memcpy(o->adi, s->adi, sizeof(o->adi));
     o->error_flags = s->errorFlags;
+    o->stat_fragments = s->statFragments;
+    o->stat_active_wheels = s->statActiveWheels;
     delete s;
     return TBF_OK;
 }

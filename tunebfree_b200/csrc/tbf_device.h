@@ -67,6 +67,7 @@ struct InstState {
     uint32_t errorFlags;
     int32_t tgTables, whTables;
     uint32_t pad_;
+    unsigned long long statFragments, statActiveWheels; /* rendered fragments, sum of active-list lengths */
 };
 
 /* tbf_tonegen_tables with device pointers */
@@ -116,10 +117,12 @@ struct RenderParams {
     const DevWhirlTables *wh;
     const tbf_event *events;
     const uint64_t *ev_start;  /* [n_instances + 1] */
+    uint64_t *ev_cursor;       /* [n_instances]: next unapplied event, carried over chunks */
     float *out_l, *out_r;
     unsigned long long *checksums; /* [n_instances] or NULL */
     uint64_t out_stride;
     uint32_t n_instances, n_fragments, flags;
+    uint32_t frag_base;        /* batch fragment index of this launch's fragment 0 */
 };
 
 size_t tbf_render_smem_bytes();

@@ -369,6 +369,8 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem
 
     if (tid == 0) {
         sm.n_rec = n_act;
+        st->statFragments += 1;
+        st->statActiveWheels += (unsigned long long)n_act;
         st->drawBarChange = 0;
         if (sm.n_ins > 256)
             st->errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
@@ -774,15 +776,15 @@ tbf_render_kernel(const RenderParams p)
     if (tid == 0)
         sm.csum = 0ull;
     uint32_t outpos0 = st->outpos;
-    uint64_t ev_cur = p.ev_start ? p.ev_start[slot] : 0;
-    const uint64_t ev_end = p.ev_start ? p.ev_start[slot + 1] : 0;
+    uint64_t ev_cur = p.ev_cursor[slot];
+    const uint64_t ev_end = p.ev_start[slot + 1];
     unsigned long long csum = 0ull;
     __syncthreads();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
         /* -- S0: control events that precede this fragment, routing, key compression -- */
         if (tid == 0) {
-            while (ev_cur < ev_end && p.events[ev_cur].fragment <= f) {
+            while (ev_cur < ev_end && p.events[ev_cur].fragment <= p.frag_base + f) {
                 apply_event(st, tg, wh, p.events[ev_cur]);
                 ++ev_cur;
             }
@@ -938,11 +940,11 @@ tbf_render_kernel(const RenderParams p)
             outpos0 = (outpos0 + TBF_FRAGMENT) & WBUF_MASK;
         }
 
-        const size_t o = (size_t)f * TBF_FRAGMENT + tid;
         if (store) {
-            out_l[o] = o_l;
-            out_r[o] = o_r;
+            out_l[(size_t)f * TBF_FRAGMENT + tid] = o_l;
+            out_r[(size_t)f * TBF_FRAGMENT + tid] = o_r;
         }
+        const size_t o = (size_t)(p.frag_base + f) * TBF_FRAGMENT + tid; /* position in the batch */
         csum += mix64(((unsigned long long)(uint32_t)o << 32) | __float_as_uint(o_l));
         csum += mix64((((unsigned long long)(uint32_t)o << 32) | __float_as_uint(o_r)) ^ 0x5555555555555555ull);
         __syncthreads();
@@ -959,13 +961,15 @@ tbf_render_kernel(const RenderParams p)
     }
     if (tid < 4)
         st->z[tid] = sm.zs[tid];
-    if (tid == 0)
+    if (tid == 0) {
         st->outpos = outpos0;
+        p.ev_cursor[slot] = ev_cur;
+    }
     if (p.checksums) {
         atomicAdd(&sm.csum, csum);
         __syncthreads();
         if (tid == 0)
-            p.checksums[slot] = sm.csum;
+            p.checksums[slot] += sm.csum; /* zeroed by the host; accumulates over chunks */
     }
 }
 

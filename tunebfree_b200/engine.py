@@ -53,6 +53,15 @@ def lib():
         L.tbf_gpu_render_batch.argtypes = [vp, C.POINTER(cabi.BatchDesc)]
         L.tbf_gpu_render_batch_launch.argtypes = [vp, C.POINTER(cabi.BatchDesc)]
         L.tbf_gpu_synchronize.argtypes = [vp]
+        L.tbf_gpu_batch_prepare.argtypes = [vp, C.POINTER(cabi.BatchDesc)]
+        L.tbf_gpu_batch_launch.argtypes = [vp]
+        L.tbf_gpu_host_alloc.argtypes = [vp, C.c_size_t]
+        L.tbf_gpu_host_alloc.restype = C.c_void_p
+        L.tbf_gpu_host_free.argtypes = [vp, C.c_void_p]
+        L.tbf_gpu_host_free.restype = None
+        L.tbf_gpu_set_host_chunk.argtypes = [vp, C.c_uint32]
+        L.tbf_gpu_timer_start.argtypes = [vp]
+        L.tbf_gpu_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
         L.tbf_gpu_last_launch_ms.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
         L.tbf_gpu_export_state.argtypes = [vp, C.c_uint32, C.POINTER(cabi.StateExport)]
         _lib = L
@@ -198,6 +207,44 @@ class Context:
         fn = lib().tbf_gpu_render_batch_launch if launch_only else lib().tbf_gpu_render_batch
         self._ck(fn(self._h, C.byref(d)))
         self._keep = keep
+
+    def prepare(self, n_instances, n_fragments, events, flags, out_l_ptr=None, out_r_ptr=None,
+                stride=0, ids=None, checksums=None):
+        """tbf_gpu_batch_prepare: upload events once; launch() may then be repeated.
+        Pointers are raw addresses (host, or device with RENDER_OUT_DEVICE)."""
+        if not out_l_ptr:
+            flags |= cabi.RENDER_NO_OUTPUT
+        d, keep = self._desc(n_instances, n_fragments, events, flags, ids, out_l_ptr, out_r_ptr,
+                             stride or n_fragments * cabi.FRAGMENT, checksums)
+        self._ck(lib().tbf_gpu_batch_prepare(self._h, C.byref(d)))
+        self._keep = (keep, checksums)
+
+    def launch(self):
+        self._ck(lib().tbf_gpu_batch_launch(self._h))
+
+    def timer_start(self):
+        self._ck(lib().tbf_gpu_timer_start(self._h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._ck(lib().tbf_gpu_timer_stop(self._h, C.byref(ms)))
+        return ms.value
+
+    def host_alloc(self, shape, dtype=np.float32):
+        """Page-locked host array (freed with host_free)."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = lib().tbf_gpu_host_alloc(self._h, n)
+        if not p:
+            raise MemoryError("tbf_gpu_host_alloc(%d) failed" % n)
+        buf = (C.c_char * n).from_address(p)
+        arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        return arr, p
+
+    def host_free(self, p):
+        lib().tbf_gpu_host_free(self._h, p)
+
+    def set_host_chunk(self, fragments):
+        self._ck(lib().tbf_gpu_set_host_chunk(self._h, fragments))
 
     def synchronize(self):
         self._ck(lib().tbf_gpu_synchronize(self._h))
