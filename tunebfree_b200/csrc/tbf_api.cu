@@ -335,39 +335,39 @@ static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
                           const tbf_whirl_tables &w, int whh)
 {
     memset(s, 0, sizeof(*s));
-    s->newRouting = s->oldRouting = t.init_routing;
-    s->percSendBus = t.init_perc_send_bus;
-    s->swellPedalGain = t.init_swell_pedal_gain;
-    s->drawBarChange = t.init_draw_bar_change;
-    s->percEnabled = t.init_perc_enabled;
-    s->percTrigRestore = t.init_perc_trig_restore;
-    s->percIsSoft = t.init_perc_is_soft;
-    s->percIsFast = t.init_perc_is_fast;
-    s->percEnvGain = 0.0f;
-    s->percEnvGainReset = t.init_perc_env_gain_reset;
-    s->percEnvGainDecay = t.init_perc_env_gain_decay;
-    s->percDrawbarGain = t.init_perc_drawbar_gain;
-    s->outputGain = 1.0f;
-    s->pz = 0.0f;
-    s->keyCompLevel = 1.0f; /* KEYCOMP_ZERO_LEVEL */
-    memcpy(s->drawBarGain, t.init_draw_bar_gain, sizeof(s->drawBarGain));
+    s->sc.newRouting = s->sc.oldRouting = t.init_routing;
+    s->sc.percSendBus = t.init_perc_send_bus;
+    s->sc.swellPedalGain = t.init_swell_pedal_gain;
+    s->sc.drawBarChange = t.init_draw_bar_change;
+    s->sc.percEnabled = t.init_perc_enabled;
+    s->sc.percTrigRestore = t.init_perc_trig_restore;
+    s->sc.percIsSoft = t.init_perc_is_soft;
+    s->sc.percIsFast = t.init_perc_is_fast;
+    s->sc.percEnvGain = 0.0f;
+    s->sc.percEnvGainReset = t.init_perc_env_gain_reset;
+    s->sc.percEnvGainDecay = t.init_perc_env_gain_decay;
+    s->sc.percDrawbarGain = t.init_perc_drawbar_gain;
+    s->sc.outputGain = 1.0f;
+    s->sc.pz = 0.0f;
+    s->sc.keyCompLevel = 1.0f; /* KEYCOMP_ZERO_LEVEL */
+    memcpy(s->sc.drawBarGain, t.init_draw_bar_gain, sizeof(s->sc.drawBarGain));
     for (int i = 0; i <= TBF_NOF_WHEELS; ++i)
         s->osc[i].aclPos = -1;
-    s->vibStator = 0;
-    s->vibOutPos = 0x3FF / 2; /* BUF_MASK_SAMPLES / 2, src/vibrato.cpp:294 */
-    s->vibTable = t.init_vib_table;
-    s->vibMixed = t.init_vib_mixed;
-    s->hornAngle = w.init_horn_angle;
-    s->drumAngle = w.init_drum_angle;
-    s->hornIncr = w.init_horn_incr;
-    s->drumIncr = w.init_drum_incr;
-    s->hornTarget = w.init_horn_target;
-    s->drumTarget = w.init_drum_target;
-    s->hornAcDc = w.init_horn_acdc;
-    s->drumAcDc = w.init_drum_acdc;
-    s->revSelect = w.init_rev_select;
-    s->tgTables = tgh;
-    s->whTables = whh;
+    s->sc.vibStator = 0;
+    s->sc.vibOutPos = 0x3FF / 2; /* BUF_MASK_SAMPLES / 2, src/vibrato.cpp:294 */
+    s->sc.vibTable = t.init_vib_table;
+    s->sc.vibMixed = t.init_vib_mixed;
+    s->sc.hornAngle = w.init_horn_angle;
+    s->sc.drumAngle = w.init_drum_angle;
+    s->sc.hornIncr = w.init_horn_incr;
+    s->sc.drumIncr = w.init_drum_incr;
+    s->sc.hornTarget = w.init_horn_target;
+    s->sc.drumTarget = w.init_drum_target;
+    s->sc.hornAcDc = w.init_horn_acdc;
+    s->sc.drumAcDc = w.init_drum_acdc;
+    s->sc.revSelect = w.init_rev_select;
+    s->sc.tgTables = tgh;
+    s->sc.whTables = whh;
 }
 
 static int replicate(tbf_ctx *ctx, int tgh, int whh, uint32_t first, uint32_t count)
@@ -735,39 +735,39 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
         return TBF_ERR_CUDA;
     }
     memset(o, 0, sizeof(*o));
-    o->active_osc_l_end = s->activeOscLEnd;
-    for (int i = 0; i < s->activeOscLEnd && i <= TBF_NOF_WHEELS; ++i)
+    o->active_osc_l_end = s->sc.activeOscLEnd;
+    for (int i = 0; i < s->sc.activeOscLEnd && i <= TBF_NOF_WHEELS; ++i)
         o->active_osc_list[i] = s->activeOscList[i];
     for (int i = 0; i <= TBF_NOF_WHEELS; ++i) {
         o->osc_pos[i] = s->osc[i].pos;
         o->osc_acl_pos[i] = s->osc[i].aclPos;
         o->ref_count[i] = s->osc[i].refCount;
     }
-    o->old_routing = s->oldRouting;
-    o->new_routing = s->newRouting;
-    o->upper_key_count = s->upperKeyCount;
-    o->key_down_count = s->keyDownCount;
-    o->perc_env_gain = s->percEnvGain;
-    o->key_comp_level = s->keyCompLevel;
-    o->pz = s->pz;
-    o->vib_stator = s->vibStator;
-    o->vib_out_pos = s->vibOutPos;
+    o->old_routing = s->sc.oldRouting;
+    o->new_routing = s->sc.newRouting;
+    o->upper_key_count = s->sc.upperKeyCount;
+    o->key_down_count = s->sc.keyDownCount;
+    o->perc_env_gain = s->sc.percEnvGain;
+    o->key_comp_level = s->sc.keyCompLevel;
+    o->pz = s->sc.pz;
+    o->vib_stator = s->sc.vibStator;
+    o->vib_out_pos = s->sc.vibOutPos;
     memcpy(o->vib_buffer, s->vibBuffer, sizeof(o->vib_buffer));
-    o->whirl_outpos = s->outpos;
-    o->horn_angle = s->hornAngle;
-    o->drum_angle = s->drumAngle;
-    o->horn_incr = s->hornIncr;
-    o->drum_incr = s->drumIncr;
-    o->horn_acdc = s->hornAcDc;
-    o->drum_acdc = s->drumAcDc;
+    o->whirl_outpos = s->sc.outpos;
+    o->horn_angle = s->sc.hornAngle;
+    o->drum_angle = s->sc.drumAngle;
+    o->horn_incr = s->sc.hornIncr;
+    o->drum_incr = s->sc.drumIncr;
+    o->horn_acdc = s->sc.hornAcDc;
+    o->drum_acdc = s->sc.drumAcDc;
     memcpy(o->whirl_buf, s->wbuf, sizeof(o->whirl_buf));
-    memcpy(o->iir_z, s->iirz, sizeof(o->iir_z));
-    memcpy(o->filt_z, s->z, sizeof(o->filt_z));
-    memcpy(o->adx, s->adx, sizeof(o->adx));
-    memcpy(o->adi, s->adi, sizeof(o->adi));
-    o->error_flags = s->errorFlags;
-    o->stat_fragments = s->statFragments;
-    o->stat_active_wheels = s->statActiveWheels;
+    memcpy(o->iir_z, s->sc.iirz, sizeof(o->iir_z));
+    memcpy(o->filt_z, s->sc.z, sizeof(o->filt_z));
+    memcpy(o->adx, s->sc.adx, sizeof(o->adx));
+    memcpy(o->adi, s->sc.adi, sizeof(o->adi));
+    o->error_flags = s->sc.errorFlags;
+    o->stat_fragments = s->sc.statFragments;
+    o->stat_active_wheels = s->sc.statActiveWheels;
     delete s;
     return TBF_OK;
 }

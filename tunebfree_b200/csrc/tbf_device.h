@@ -33,7 +33,9 @@ struct OscState {      /* struct _oscillator + the scalar part of AOTElement */
     float sumUpper, sumLower, sumPedal, sumPercn, sumSwell, sumScanr;
 };
 
-struct InstState {
+/* Every scalar of the run-time state: copied to shared memory when a launch
+ * starts and back when it ends, so the serial control code never waits on HBM. */
+struct InstScalars {
     /* ---- tone generator ---- */
     int32_t activeOscLEnd;
     uint32_t newRouting, oldRouting;
@@ -46,28 +48,32 @@ struct InstState {
     float percEnvGain, percEnvGainReset, percEnvGainDecay, percDrawbarGain;
     float outputGain, pz, keyCompLevel;
     float drawBarGain[TBF_NOF_BUSES];
-    int32_t activeOscList[TBF_NOF_WHEELS + 1];
-    uint8_t activeKeys[TBF_MAX_KEYS];
-    OscState osc[TBF_NOF_WHEELS + 1];
-    float busLevel[(TBF_NOF_WHEELS + 1) * TBF_NOF_BUSES]; /* aot[w].busLevel[b] */
     /* ---- scanner vibrato ---- */
     uint32_t vibStator, vibOutPos;
     int32_t vibTable, vibMixed;
-    float vibBuffer[TBF_VIB_BUF];
     /* ---- whirl ---- */
-    double hornAngle, drumAngle, hornIncr, drumIncr, hornTarget, drumTarget;
     int32_t hornAcDc, drumAcDc, revSelect;
     uint32_t outpos;
+    double hornAngle, drumAngle, hornIncr, drumIncr, hornTarget, drumTarget;
     float z[4];
     float iirz[4][2]; /* hafw hbfw drfL drfR : z0 z1 */
     float adx[3][8];
     int32_t adi[3];
-    float wbuf[4][TBF_WHIRL_BUF]; /* HL HR DL DR */
     /* ---- bookkeeping ---- */
     uint32_t errorFlags;
     int32_t tgTables, whTables;
     uint32_t pad_;
-    unsigned long long statFragments, statActiveWheels; /* rendered fragments, sum of active-list lengths */
+    unsigned long long statFragments, statActiveWheels; /* fragments rendered, sum of active-list lengths */
+};
+
+struct InstState {
+    InstScalars sc;
+    int32_t activeOscList[TBF_NOF_WHEELS + 1];
+    uint8_t activeKeys[TBF_MAX_KEYS];
+    OscState osc[TBF_NOF_WHEELS + 1];
+    float busLevel[(TBF_NOF_WHEELS + 1) * TBF_NOF_BUSES]; /* aot[w].busLevel[b] */
+    float vibBuffer[TBF_VIB_BUF];
+    float wbuf[4][TBF_WHIRL_BUF]; /* HL HR DL DR */
 };
 
 /* tbf_tonegen_tables with device pointers */
@@ -108,6 +114,15 @@ struct DevWhirlTables {
     float horn_level, leakage;
     float mic_hll, mic_hlr, mic_hrl, mic_hrr, mic_dll, mic_dlr, mic_drl, mic_drr;
     int32_t bypass;
+    /* delay-line geometry derived from the tables on the host (tbf_api.cu):
+     * every tap writes `delay` slots ahead of the reader with
+     * tap_dmin <= delay <= tap_dmax (secondary slot included) */
+    int32_t ring_size;      /* 512 or 2048: shared-memory ring per delay line          */
+    int32_t gather_ok;      /* 1: the three taps of every line have disjoint delay ranges,
+                               so the ordered scatter can be evaluated as a parallel gather */
+    int32_t window;         /* slots ahead of the reader that can be non-zero, + 128    */
+    int32_t tap_order[4][3];/* per line HL HR DL DR: tap ids (0..11), farthest delay first */
+    int32_t tap_dmin[12], tap_dmax[12];
 };
 
 struct RenderParams {
@@ -125,8 +140,8 @@ struct RenderParams {
     uint32_t frag_base;        /* batch fragment index of this launch's fragment 0 */
 };
 
-size_t tbf_render_smem_bytes();
-int tbf_launch_render(const RenderParams &p, void *stream);
+size_t tbf_render_smem_bytes(int ring_size);
+int tbf_launch_render(const RenderParams &p, int ring_size, void *stream);
 int tbf_launch_replicate(InstState *states, uint32_t first, uint32_t count, const InstState *dev_tmpl,
                          void *stream);
 
