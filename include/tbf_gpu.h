@@ -177,6 +177,10 @@ const char *tbf_gpu_last_error(const tbf_ctx *ctx);
 /* upload table sets; the library copies everything                          */
 int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int *handle);
 int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *handle);
+/* how the kernels treat a whirl table set: 1 = parallel ordered gather of the delay lines
+ * (the three taps of each line have disjoint delay ranges), 0 = serial path; ring = shared-
+ * memory slots per delay line (512 or 2048); window = live slots ahead of the reader */
+int tbf_gpu_whirl_tables_info(tbf_ctx *ctx, int handle, int *gather_ok, int *ring_size, int *window);
 
 /* replaces allocTonegen+initToneGenerator+allocWhirl+initWhirl as far as the
  * run-time state goes (src/tonegen.cpp:3780, :2905; src/whirl.cpp:136, :956) */
@@ -242,6 +246,8 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *out)
 #define TBF_IFLAG_COREPGM_OVERFLOW 0x1 /* > CR_PGMMAX core instrs: reference UB */
 #define TBF_IFLAG_KEYCOMP_OOB 0x2      /* keyDownCount >= 128: reference over-read */
 #define TBF_IFLAG_BAD_EVENT 0x4
+#define TBF_IFLAG_GATHER_FALLBACK 0x8  /* informational: some fragment used the serial
+                                          delay-line path (rotor faster than the gather covers) */
 
 #ifdef __cplusplus
 }

@@ -187,6 +187,36 @@ def test_cfg_variants(ref, gpu_ctx):
         _check(ref, gpu_ctx, [e for e in ev if e[0] < 100], 100, 0, seed=5, cfg=cfg)
 
 
+def test_default_geometry_uses_the_parallel_gather(ref, gpu_ctx):
+    """The stock Leslie geometry must run the ordered-gather delay lines on a 512-slot
+    shared-memory ring (a silent fall-back to the serial lanes would hide a perf bug)."""
+    r = ref.RefInstance(seed=1)
+    wh = gpu_ctx.whirl_tables(r.whirl_tables())
+    gather_ok, ring, window = gpu_ctx.whirl_tables_info(wh)
+    assert (gather_ok, ring) == (1, 512) and 128 < window <= 640
+    r.close()
+
+
+def test_wide_geometry_and_fast_rotors_fall_back_exactly(ref, gpu_ctx):
+    """Geometries whose tap delay ranges overlap use the serial delay-line path, and a
+    rotor spun far beyond any Leslie exercises the per-fragment monotonicity check:
+    both must still match the reference bit for bit."""
+    ev = workloads.setup_events(3) + [(1, cabi.EV_KEY_ON, k, 0) for k in (43, 60, 64, 79)]
+    cfg = "whirl.horn.radius=45\nwhirl.drum.radius=50\nwhirl.mic.distance=70\n"
+    r = ref.RefInstance(seed=2, cfg=cfg)
+    wh = gpu_ctx.whirl_tables(r.whirl_tables())
+    assert gpu_ctx.whirl_tables_info(wh)[0] == 0
+    r.close()
+    _check(ref, gpu_ctx, ev, 300, cabi.RENDER_WHIRLPROC3, seed=2, cfg=cfg)
+    cfg = "whirl.horn.fastrpm=90000\nwhirl.drum.fastrpm=70000\nwhirl.horn.acceleration=0.01\n"
+    r, first = _make(ref, gpu_ctx, 1, 2, cfg)
+    rl, rr = r.render(300, cabi.RENDER_WHIRLPROC3, ev)
+    gl, gr = gpu_ctx.render(1, 300, [ev], cabi.RENDER_WHIRLPROC3, ids=[first])
+    assert np.array_equal(_bits(gl[0]), _bits(rl)) and np.array_equal(_bits(gr[0]), _bits(rr))
+    assert gpu_ctx.export_state(first).error_flags & cabi.IFLAG_GATHER_FALLBACK
+    r.close()
+
+
 def test_error_paths(gpu_ctx):
     from tunebfree_b200.engine import TbfError
     with pytest.raises(TbfError):

@@ -48,6 +48,7 @@ RENDER_NO_OUTPUT = 0x8
 IFLAG_COREPGM_OVERFLOW = 0x1
 IFLAG_KEYCOMP_OOB = 0x2
 IFLAG_BAD_EVENT = 0x4
+IFLAG_GATHER_FALLBACK = 0x8
 
 _f32p = C.POINTER(C.c_float)
 _u16p = C.POINTER(C.c_uint16)

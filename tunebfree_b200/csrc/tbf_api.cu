@@ -25,6 +25,7 @@ struct TgSet {
 struct WhSet {
     tbf_whirl_tables host;
     float *tables = nullptr; /* 4 x 16384 displacement + 2 x 16384 x 5 FIR */
+    int ring_size = TBF_WHIRL_BUF, gather_ok = 0, window = 0;
 };
 
 struct tbf_ctx {
@@ -311,6 +312,61 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
     d.mic_drr = w->mic_drr;
     d.bypass = w->bypass;
 
+    /* Delay-line geometry: how far ahead of the reader each tap can write
+     * (t = spacing + displacement + outpos, slot = floor(t), src/whirl.cpp:1432-1469).
+     * One slot of margin on each side covers the float rounding of the sum; the
+     * secondary slot (n + 1) is included in dmax. */
+    {
+        const float *disp[12];
+        for (int p = 0; p < 6; ++p) {
+            const bool fwd = (p == 0 || p == 3 || p == 4);
+            disp[p] = fwd ? w->hn_fwd_displ : w->hn_bwd_displ;
+            disp[6 + p] = fwd ? w->dr_fwd_displ : w->dr_bwd_displ;
+        }
+        int wmax = 0;
+        bool ok = true;
+        for (int p = 0; p < 12; ++p) {
+            float mn = disp[p][0], mx = disp[p][0];
+            for (size_t i = 1; i < N; ++i) {
+                mn = std::min(mn, disp[p][i]);
+                mx = std::max(mx, disp[p][i]);
+            }
+            const float sp = p < 6 ? w->horn_spacing[p] : w->drum_spacing[p - 6];
+            if (!(mn == mn) || !(mx == mx) || !(sp == sp))
+                return fail(ctx, TBF_ERR_GEOMETRY, "whirl tables: NaN in displacement tables");
+            /* the float sum spacing + displacement + outpos (< 4096) is within 1e-3 of
+             * the exact value; +1 is the secondary slot */
+            d.tap_dmin[p] = (int)floor((double)sp + (double)mn - 0.01);
+            d.tap_dmax[p] = (int)floor((double)sp + (double)mx + 0.01) + 1;
+            if (d.tap_dmin[p] < 0)
+                ok = false;
+            wmax = std::max(wmax, d.tap_dmax[p]);
+        }
+        d.window = wmax + 1 + TBF_FRAGMENT;
+        if (d.window >= TBF_WHIRL_BUF - TBF_FRAGMENT)
+            return fail(ctx, TBF_ERR_GEOMETRY,
+                        "whirl tables: tap delays do not fit the 2048-sample delay lines");
+        for (int line = 0; line < 4; ++line) {
+            int t[3];
+            const int base = (line < 2) ? (line & 1) : 6 + (line & 1);
+            for (int k = 0; k < 3; ++k)
+                t[k] = base + 2 * k;
+            std::sort(t, t + 3, [&](int a, int b) { return d.tap_dmin[a] > d.tap_dmin[b]; });
+            for (int k = 0; k < 3; ++k)
+                d.tap_order[line][k] = t[k];
+            for (int k = 0; k + 1 < 3; ++k) /* farther tap strictly beyond the nearer one */
+                if (!(d.tap_dmin[t[k]] > d.tap_dmax[t[k + 1]]))
+                    ok = false;
+        }
+        /* a 512-slot shared ring holds the live part of a line as long as no tap reaches
+         * 512 slots ahead; the gather covers windows of up to 5 slots per thread */
+        d.gather_ok = (ok && d.window <= 640) ? 1 : 0;
+        d.ring_size = (wmax + 2 <= 512 && ok && d.window <= 640) ? 512 : TBF_WHIRL_BUF;
+        s.ring_size = d.ring_size;
+        s.gather_ok = d.gather_ok;
+        s.window = d.window;
+    }
+
     const size_t idx = ctx->wh.size();
     if (idx + 1 > ctx->d_wh_cap) {
         const size_t ncap = std::max<size_t>(8, ctx->d_wh_cap * 2);
@@ -589,6 +645,9 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     p.n_instances = d->n_instances;
     p.flags = d->flags;
     ctx->launches = 0;
+    int ring = 512; /* shared-memory delay-line ring: the largest any table set needs */
+    for (auto &w : ctx->wh)
+        ring = std::max(ring, w.ring_size);
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     const size_t half = (size_t)2 * d->n_instances * chunk * TBF_FRAGMENT;
     int k = 0;
@@ -609,7 +668,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             p.out_l = no_out ? nullptr : d->out_l + (size_t)base * TBF_FRAGMENT;
             p.out_r = no_out ? nullptr : d->out_r + (size_t)base * TBF_FRAGMENT;
         }
-        int rc = tbf_launch_render(p, ctx->stream);
+        int rc = tbf_launch_render(p, ring, ctx->stream);
         if (rc != 0) {
             ctx->err = std::string("render kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
             return TBF_ERR_CUDA;
@@ -669,6 +728,21 @@ int tbf_gpu_last_launch_ms(tbf_ctx *ctx, float *ms, int *n_kernel_launches)
         CK(cudaEventElapsedTime(ms, ctx->ev0, ctx->ev1));
     if (n_kernel_launches)
         *n_kernel_launches = ctx->launches;
+    return TBF_OK;
+}
+
+/* how the kernels will treat a whirl table set: parallel ordered gather or the serial
+ * delay-line path, shared-memory ring size per line, live window in slots */
+int tbf_gpu_whirl_tables_info(tbf_ctx *ctx, int handle, int *gather_ok, int *ring_size, int *window)
+{
+    if (!ctx || handle < 0 || (size_t)handle >= ctx->wh.size())
+        return fail(ctx, TBF_ERR_HANDLE, "whirl_tables_info: unknown handle");
+    if (gather_ok)
+        *gather_ok = ctx->wh[handle].gather_ok;
+    if (ring_size)
+        *ring_size = ctx->wh[handle].ring_size;
+    if (window)
+        *window = ctx->wh[handle].window;
     return TBF_OK;
 }
 

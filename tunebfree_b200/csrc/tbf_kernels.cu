@@ -1,12 +1,17 @@
 /* tbf_kernels.cu -- sm_100a kernels for the tonewheel -> scanner -> Leslie path.
  *
  * One CTA of 128 threads owns one organ instance for a whole batch of
- * fragments: thread n is sample n of the 128-sample fragment for every stage
- * that has no recurrence (additive wheel sum, envelopes, percussion high-pass,
- * Leslie tap geometry + 5-tap FIRs, output mixes), and single lanes in
- * different warps run the short serial recurrences concurrently (biquads,
- * rotor angles, percussion / key-compression ramps, ordered delay-line
- * scatter).  Delay lines live in shared memory for the whole batch.
+ * fragments.  Thread n is sample n of the 128-sample fragment for every stage
+ * without a recurrence: the additive wheel sum, envelopes, percussion
+ * high-pass, the Leslie tap geometry + 5-tap FIRs and the output mixes.  The
+ * reference's two scatter-add delay structures (scanner ring, four Leslie delay
+ * lines) are evaluated as ORDERED GATHERS, thread = destination slot, adding
+ * the contributions in exactly the order the reference's sample loop does.
+ * Only the true recurrences stay on single lanes, spread over different warps
+ * so they overlap: four biquads, two rotor angles, the percussion / key
+ * compression ramps and the control-event bookkeeping.
+ * Per-instance scalars and the live window of every delay line sit in shared
+ * memory for the whole launch.
  *
  * Numerics contract: bit-exact float/double arithmetic in the
  * reference's source operation order.  This file is compiled with
@@ -28,7 +33,12 @@
 #include "tbf_device.h"
 
 #define DISPLC_MASK (TBF_WHIRL_DISPLC - 1)
-#define WBUF_MASK (TBF_WHIRL_BUF - 1)
+#define GLOBAL_WBUF_MASK (TBF_WHIRL_BUF - 1)
+#define VRING 256            /* shared-memory scanner ring: writes land <= 27 slots ahead */
+#define VRING_MASK (VRING - 1)
+#define VWINDOW (TBF_FRAGMENT + 100)
+#define FIRST_W 640          /* slots covered by the per-tap inverse map (5 per thread) */
+#define GATHER_K 5
 
 namespace {
 
@@ -45,25 +55,31 @@ struct CoreRec {
 };
 
 struct __align__(16) Smem {
-    float wbuf[4][TBF_WHIRL_BUF];
-    float vibbuf[TBF_VIB_BUF];
+    InstScalars sc;
     CoreRec rec[TBF_NOF_WHEELS + 1];
     uint8_t removed[TBF_NOF_WHEELS + 3];
     uint16_t removed_wheel[TBF_NOF_WHEELS + 1];
-    float vib_in[TBF_FRAGMENT], vib_y[TBF_FRAGMENT], prc[TBF_FRAGMENT];
+    float vib_in[TBF_FRAGMENT], prc[TBF_FRAGMENT];
     float pg[TBF_FRAGMENT], kc[TBF_FRAGMENT], mono[TBF_FRAGMENT];
+    /* scanner: per-sample contributions, inverse slot map, ring */
+    float va[TBF_FRAGMENT], vb[TBF_FRAGMENT], vib_y[TBF_FRAGMENT];
+    uint16_t vh[TBF_FRAGMENT];
+    uint8_t vfirst[VRING];
+    float vring[VRING];
     /* whirl */
     double hang[TBF_FRAGMENT], dang[TBF_FRAGMENT];
     float hx[3][8 + TBF_FRAGMENT]; /* horn stage inputs with 8 samples of history */
     float dx[3][1 + TBF_FRAGMENT]; /* drum stage inputs with 1 sample of history  */
     float leak[TBF_FRAGMENT];
-    uint16_t tapn[12][TBF_FRAGMENT];
+    uint16_t tapn[12][TBF_FRAGMENT]; /* destination slot of the tap's main part (ring index) */
     float tapa[12][TBF_FRAGMENT], tapb[12][TBF_FRAGMENT];
-    float lineout[4][TBF_FRAGMENT]; /* HL HR raw reads, DL DR after the drum biquad */
+    uint8_t first[12][FIRST_W];      /* slot (relative to the reader) -> first sample hitting it */
+    float lineout[4][TBF_FRAGMENT];  /* HL HR raw reads, DL DR after the drum biquad */
     unsigned long long csum;
     int n_rec, n_ins, recompute_routing, draw_bar_change, vib_on, perc_on;
     float key_comp_delta;
     float zs[4]; /* FILTER_C states z[0..3], NaN-scrubbed per fragment */
+    /* followed by float wring[4][ring_size]: the Leslie delay lines */
 };
 
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x)
@@ -83,7 +99,7 @@ __device__ __forceinline__ unsigned f2u_x86(float f) { return (unsigned)(long lo
 /* control events: thread 0 only                                       */
 /* ------------------------------------------------------------------ */
 
-__device__ void key_off(InstState *st, const DevTonegenTables *tg, int key)
+__device__ void key_off(InstScalars &sc, InstState *st, const DevTonegenTables *tg, int key)
 {
     if (key < 0 || key >= TBF_MAX_KEYS)
         return;
@@ -91,8 +107,8 @@ __device__ void key_off(InstState *st, const DevTonegenTables *tg, int key)
         return;
     st->activeKeys[key] = 0;
     if (key < 128)
-        st->upperKeyCount--;
-    st->keyDownCount--;
+        sc.upperKeyCount--;
+    sc.keyDownCount--;
     const uint32_t e0 = tg->contrib_start[key], e1 = tg->contrib_start[key + 1];
     for (uint32_t e = e0; e < e1; ++e) {
         const int w = tg->contrib_wheel[e];
@@ -108,16 +124,16 @@ __device__ void key_off(InstState *st, const DevTonegenTables *tg, int key)
     }
 }
 
-__device__ void key_on(InstState *st, const DevTonegenTables *tg, int key)
+__device__ void key_on(InstScalars &sc, InstState *st, const DevTonegenTables *tg, int key)
 {
     if (key < 0 || key >= TBF_MAX_KEYS)
         return;
     if (st->activeKeys[key])
-        key_off(st, tg, key);
+        key_off(sc, st, tg, key);
     st->activeKeys[key] = 1;
     if (key < 128)
-        st->upperKeyCount++;
-    st->keyDownCount++;
+        sc.upperKeyCount++;
+    sc.keyDownCount++;
     const uint32_t e0 = tg->contrib_start[key], e1 = tg->contrib_start[key + 1];
     for (uint32_t e = e0; e < e1; ++e) {
         const int w = tg->contrib_wheel[e];
@@ -126,8 +142,8 @@ __device__ void key_on(InstState *st, const DevTonegenTables *tg, int key)
         if (o->refCount == 0) {
             o->rflags = OR_ADD;
             if (o->aclPos == -1) {
-                o->aclPos = st->activeOscLEnd;
-                st->activeOscList[st->activeOscLEnd++] = w;
+                o->aclPos = sc.activeOscLEnd;
+                st->activeOscList[sc.activeOscLEnd++] = w;
             }
         } else {
             o->rflags |= ORF_MODIFIED;
@@ -138,127 +154,127 @@ __device__ void key_on(InstState *st, const DevTonegenTables *tg, int key)
     }
 }
 
-__device__ void perc_resets(InstState *st, const DevTonegenTables *tg)
+__device__ void perc_resets(InstScalars &sc, const DevTonegenTables *tg)
 {
-    if (st->percIsFast)
-        st->percEnvGainDecay = st->percIsSoft ? tg->perc_decay_fast_soft : tg->perc_decay_fast_norm;
+    if (sc.percIsFast)
+        sc.percEnvGainDecay = sc.percIsSoft ? tg->perc_decay_fast_soft : tg->perc_decay_fast_norm;
     else
-        st->percEnvGainDecay = st->percIsSoft ? tg->perc_decay_slow_soft : tg->perc_decay_slow_norm;
+        sc.percEnvGainDecay = sc.percIsSoft ? tg->perc_decay_slow_soft : tg->perc_decay_slow_norm;
 }
 
-__device__ void use_rev_option(InstState *st, const DevWhirlTables *wh, int n, int signals)
+__device__ void use_rev_option(InstScalars &sc, const DevWhirlTables *wh, int n, int signals)
 {
     const int i = n % 9;
-    st->hornTarget = wh->rev_horn_target[i];
-    st->drumTarget = wh->rev_drum_target[i];
-    if (st->hornIncr < st->hornTarget)
-        st->hornAcDc = 1;
-    else if (st->hornTarget < st->hornIncr)
-        st->hornAcDc = -1;
-    if (st->drumIncr < st->drumTarget)
-        st->drumAcDc = 1;
-    else if (st->drumTarget < st->drumIncr)
-        st->drumAcDc = -1;
+    sc.hornTarget = wh->rev_horn_target[i];
+    sc.drumTarget = wh->rev_drum_target[i];
+    if (sc.hornIncr < sc.hornTarget)
+        sc.hornAcDc = 1;
+    else if (sc.hornTarget < sc.hornIncr)
+        sc.hornAcDc = -1;
+    if (sc.drumIncr < sc.drumTarget)
+        sc.drumAcDc = 1;
+    else if (sc.drumTarget < sc.drumIncr)
+        sc.drumAcDc = -1;
     if (signals & 2) {
         const int hr = (n / 3) % 3;
-        st->revSelect = (hr == 2) ? 2 : (hr == 1) ? 0 : 1; /* WHIRL_FAST / SLOW / STOP */
+        sc.revSelect = (hr == 2) ? 2 : (hr == 1) ? 0 : 1; /* WHIRL_FAST / SLOW / STOP */
     }
 }
 
-__device__ void apply_event(InstState *st, const DevTonegenTables *tg, const DevWhirlTables *wh,
-                            const tbf_event &ev)
+__device__ void apply_event(InstScalars &sc, InstState *st, const DevTonegenTables *tg,
+                            const DevWhirlTables *wh, const tbf_event &ev)
 {
     const int a = ev.a, b = ev.b;
     switch (ev.type) {
     case TBF_EV_KEY_ON:
-        key_on(st, tg, a);
+        key_on(sc, st, tg, a);
         break;
     case TBF_EV_KEY_OFF:
-        key_off(st, tg, a);
+        key_off(sc, st, tg, a);
         break;
     case TBF_EV_DRAWBAR:
         if (a < 0 || a >= TBF_NOF_BUSES || b < 0 || b >= 9) { /* reference asserts */
-            st->errorFlags |= TBF_IFLAG_BAD_EVENT;
+            sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
             break;
         }
-        st->drawBarChange = 1;
+        sc.drawBarChange = 1;
         if (a == tg->perc_trigger_bus) {
-            st->percTrigRestore = b;
-            if (st->percEnabled)
+            sc.percTrigRestore = b;
+            if (sc.percEnabled)
                 break;
         }
-        st->drawBarGain[a] = tg->draw_bar_level[a][b];
+        sc.drawBarGain[a] = tg->draw_bar_level[a][b];
         break;
     case TBF_EV_PERC_ENABLE:
         if (a) {
-            st->newRouting |= RT_PERC;
+            sc.newRouting |= RT_PERC;
             if (-1 < tg->perc_trigger_bus) {
-                st->drawBarGain[tg->perc_trigger_bus] = 0.0f;
-                st->drawBarChange = 1;
+                sc.drawBarGain[tg->perc_trigger_bus] = 0.0f;
+                sc.drawBarChange = 1;
             }
         } else {
-            st->newRouting &= ~RT_PERC;
+            sc.newRouting &= ~RT_PERC;
             if (-1 < tg->perc_trigger_bus) {
-                st->drawBarGain[tg->perc_trigger_bus] =
-                    tg->draw_bar_level[tg->perc_trigger_bus][st->percTrigRestore];
-                st->drawBarChange = 1;
+                sc.drawBarGain[tg->perc_trigger_bus] =
+                    tg->draw_bar_level[tg->perc_trigger_bus][sc.percTrigRestore];
+                sc.drawBarChange = 1;
             }
         }
-        st->percEnabled = a;
+        sc.percEnabled = a;
         break;
     case TBF_EV_PERC_SOFT:
-        st->percIsSoft = a;
-        st->percEnvGainReset = __fmul_rn(
+        sc.percIsSoft = a;
+        sc.percEnvGainReset = __fmul_rn(
             tg->perc_env_scaling, a ? tg->perc_env_gain_reset_soft : tg->perc_env_gain_reset_norm);
-        st->percDrawbarGain = a ? tg->perc_drawbar_soft_gain : tg->perc_drawbar_normal_gain;
-        perc_resets(st, tg);
+        sc.percDrawbarGain = a ? tg->perc_drawbar_soft_gain : tg->perc_drawbar_normal_gain;
+        perc_resets(sc, tg);
         break;
     case TBF_EV_PERC_FAST:
-        st->percIsFast = a;
-        perc_resets(st, tg);
+        sc.percIsFast = a;
+        perc_resets(sc, tg);
         break;
     case TBF_EV_PERC_FIRST:
-        st->percSendBus = a ? tg->perc_send_bus_a : tg->perc_send_bus_b;
+        sc.percSendBus = a ? tg->perc_send_bus_a : tg->perc_send_bus_b;
         break;
     case TBF_EV_VIB_UPPER:
         if (a)
-            st->newRouting |= RT_UPPRVIB;
+            sc.newRouting |= RT_UPPRVIB;
         else
-            st->newRouting &= ~RT_UPPRVIB;
+            sc.newRouting &= ~RT_UPPRVIB;
         break;
     case TBF_EV_VIB_LOWER:
         if (a)
-            st->newRouting |= RT_LOWRVIB;
+            sc.newRouting |= RT_LOWRVIB;
         else
-            st->newRouting &= ~RT_LOWRVIB;
+            sc.newRouting &= ~RT_LOWRVIB;
         break;
     case TBF_EV_VIB_KNOB:
         if (a >= 0 && a <= 5) { /* V1 C1 V2 C2 V3 C3 */
-            st->vibTable = a >> 1;
-            st->vibMixed = (a & 1) ? 0x80 : 0;
+            sc.vibTable = a >> 1;
+            sc.vibMixed = (a & 1) ? 0x80 : 0;
         }
         break;
     case TBF_EV_REV_OPTION:
         if (a < 0) {
-            st->errorFlags |= TBF_IFLAG_BAD_EVENT;
+            sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
             break;
         }
-        use_rev_option(st, wh, a, 2);
+        use_rev_option(sc, wh, a, 2);
         break;
     case TBF_EV_REV_SELECT:
         if (a < 0) {
-            st->errorFlags |= TBF_IFLAG_BAD_EVENT;
+            sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
             break;
         }
-        st->revSelect = a % 3;
-        use_rev_option(st, wh, wh->revselects[st->revSelect], 1);
+        sc.revSelect = a % 3;
+        use_rev_option(sc, wh, wh->revselects[sc.revSelect], 1);
         break;
     case TBF_EV_SWELL:
-        st->swellPedalGain =
+        sc.swellPedalGain =
             (float)(((double)tg->output_level_trim * (double)(unsigned char)a) / 127.0);
         break;
     default:
-        st->errorFlags |= TBF_IFLAG_BAD_EVENT;
+        sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
         break;
     }
 }
@@ -271,8 +287,9 @@ __device__ void apply_event(InstState *st, const DevTonegenTables *tg, const Dev
  * only its own wheel's state), so thread i handles entries i, i+128, ... */
 __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem &sm, int tid)
 {
-    const int n_act = st->activeOscLEnd;
-    const uint32_t routing = st->oldRouting; /* already updated by thread 0 */
+    InstScalars &sc = sm.sc;
+    const int n_act = sc.activeOscLEnd;
+    const uint32_t routing = sc.oldRouting; /* already updated by thread 0 */
     const bool recompute_routing = sm.recompute_routing != 0;
     const bool draw_bar_change = sm.draw_bar_change != 0;
     int my_ins = 0;
@@ -311,22 +328,22 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem
                 const float *bl = &st->busLevel[w * TBF_NOF_BUSES];
                 float sum = 0.0f;
                 for (int d = 0; d < 9; ++d)
-                    sum = __fadd_rn(sum, __fmul_rn(bl[d], st->drawBarGain[d]));
+                    sum = __fadd_rn(sum, __fmul_rn(bl[d], sc.drawBarGain[d]));
                 o->sumUpper = sum;
                 sum = 0.0f;
                 for (int d = 9; d < 18; ++d)
-                    sum = __fadd_rn(sum, __fmul_rn(bl[d], st->drawBarGain[d]));
+                    sum = __fadd_rn(sum, __fmul_rn(bl[d], sc.drawBarGain[d]));
                 o->sumLower = sum;
                 sum = 0.0f;
                 for (int d = 18; d < 27; ++d)
-                    sum = __fadd_rn(sum, __fmul_rn(bl[d], st->drawBarGain[d]));
+                    sum = __fadd_rn(sum, __fmul_rn(bl[d], sc.drawBarGain[d]));
                 o->sumPedal = sum;
                 reroute = true;
             }
             if (reroute || recompute_routing) {
                 float percn = 0.0f;
                 if (routing & RT_PERC)
-                    percn = st->busLevel[w * TBF_NOF_BUSES + st->percSendBus];
+                    percn = st->busLevel[w * TBF_NOF_BUSES + sc.percSendBus];
                 float scanr = 0.0f;
                 float swell = o->sumPedal;
                 if (routing & RT_UPPRVIB)
@@ -369,11 +386,11 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem
 
     if (tid == 0) {
         sm.n_rec = n_act;
-        st->statFragments += 1;
-        st->statActiveWheels += (unsigned long long)n_act;
-        st->drawBarChange = 0;
+        sc.statFragments += 1;
+        sc.statActiveWheels += (unsigned long long)n_act;
+        sc.drawBarChange = 0;
         if (sm.n_ins > 256)
-            st->errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
+            sc.errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
         if (any_removed) {
             /* removal list in ascending active-list index, swap-with-last
              * (src/tonegen.cpp:3576-3594); changes the list order and with it
@@ -399,7 +416,7 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem
                     }
                 }
             }
-            st->activeOscLEnd = l_end;
+            sc.activeOscLEnd = l_end;
         }
     }
 }
@@ -447,17 +464,72 @@ __device__ __forceinline__ void core_interpreter(const DevTonegenTables *tg, con
 }
 
 /* ------------------------------------------------------------------ */
-/* scanner vibrato, ordered scatter by one lane (src/vibrato.cpp:365-411) */
+/* scanner vibrato (src/vibrato.cpp:365-411)                            */
 /* ------------------------------------------------------------------ */
-__device__ void vibrato_serial(InstState *st, const DevTonegenTables *tg, Smem &sm)
+
+/* Per-sample part, thread = sample m.  Everything integer is closed form in m:
+ * stator(m) = stator0 + m*inc, outPos(m) = outPos0 + m.  Sample m adds (x - g) to
+ * slot h(m) and g to slot h(m)+1.  Returns non-zero when the gather's assumptions
+ * (slots advance monotonically, stay inside the shared ring) do not hold. */
+__device__ __forceinline__ int vibrato_contrib(const InstScalars &sc, const DevTonegenTables *tg,
+                                               Smem &sm, int m, float x)
+{
+    const float fnorm = (float)(1.0 / 65536.0);
+    const uint32_t *tab = tg->vib_offset_table[sc.vibTable];
+    const uint32_t inc = tg->vib_stator_increment;
+    const uint32_t stator = (sc.vibStator + (uint32_t)m * inc) & 0x07FFFFFFu;
+    const uint32_t op = (sc.vibOutPos + (uint32_t)m) & 0x3FFu;
+    const uint32_t j = ((op << 16) + __ldg(&tab[stator >> 16])) & 0x03FFFFFFu;
+    const uint32_t h = j >> 16;
+    const float f = __fmul_rn(fnorm, (float)(j & 0xFFFFu));
+    const float g = __fmul_rn(f, x);
+    sm.va[m] = __fsub_rn(x, g);
+    sm.vb[m] = g;
+    sm.vh[m] = (uint16_t)h;
+    const uint32_t rel = (h - sc.vibOutPos) & 0x3FFu; /* slots ahead of the fragment's first read */
+    int bad = (rel < (uint32_t)m) || (rel + 1 >= (uint32_t)VWINDOW);
+    uint32_t hprev = 0xFFFFFFFFu;
+    if (m > 0) {
+        const uint32_t sp = (sc.vibStator + (uint32_t)(m - 1) * inc) & 0x07FFFFFFu;
+        const uint32_t opp = (sc.vibOutPos + (uint32_t)(m - 1)) & 0x3FFu;
+        hprev = (((opp << 16) + __ldg(&tab[sp >> 16])) & 0x03FFFFFFu) >> 16;
+        bad |= ((h - hprev) & 0x3FFu) >= 512u; /* went backwards */
+    }
+    if (!bad && h != hprev)
+        sm.vfirst[rel] = (uint8_t)m;
+    return bad;
+}
+
+/* Gather, thread = slot s ahead of the fragment's first read position.  The slot
+ * collects, in sample order, the g-parts of the samples that hit slot s-1 and then
+ * the (x-g)-parts of the samples that hit s -- the order the reference's loop adds
+ * them in, because h(m) never decreases.  Slots s < 128 are read (and cleared) by
+ * sample s after all of its contributors (they are >= 1 sample older). */
+__device__ __forceinline__ float vibrato_gather_slot(const InstScalars &sc, Smem &sm, int s)
+{
+    const uint32_t S = (sc.vibOutPos + (uint32_t)s) & 0x3FFu;
+    float v = sm.vring[S & VRING_MASK];
+    if (s > 0) {
+        const uint32_t Sm1 = (S - 1) & 0x3FFu;
+        for (int m = sm.vfirst[s - 1]; m < TBF_FRAGMENT && sm.vh[m] == Sm1; ++m)
+            v = __fadd_rn(v, sm.vb[m]);
+    }
+    for (int m = sm.vfirst[s]; m < TBF_FRAGMENT && sm.vh[m] == S; ++m)
+        v = __fadd_rn(v, sm.va[m]);
+    return v;
+}
+
+/* the reference's loop as written, one lane: fallback when the gather's
+ * assumptions fail (pathological offset tables) */
+__device__ void vibrato_serial(InstScalars &sc, const DevTonegenTables *tg, Smem &sm)
 {
     const float fnorm = (float)(1.0 / 65536.0);
     const float mixnorm = (float)0.7071067811865475;
-    const uint32_t *tab = tg->vib_offset_table[st->vibTable];
+    const uint32_t *tab = tg->vib_offset_table[sc.vibTable];
     const uint32_t inc = tg->vib_stator_increment;
-    const int mixed = st->vibMixed;
-    uint32_t stator = st->vibStator, out_pos = st->vibOutPos;
-    float *buf = sm.vibbuf;
+    const int mixed = sc.vibMixed;
+    uint32_t stator = sc.vibStator, out_pos = sc.vibOutPos;
+    float *buf = sm.vring;
     for (int i = 0; i < TBF_FRAGMENT; ++i) {
         const float x = sm.vib_in[i];
         const uint32_t j = ((out_pos << 16) + __ldg(&tab[stator >> 16])) & 0x03FFFFFFu;
@@ -465,45 +537,45 @@ __device__ void vibrato_serial(InstState *st, const DevTonegenTables *tg, Smem &
         const uint32_t k = (h + 1) & 0x3FFu;
         const float f = __fmul_rn(fnorm, (float)(j & 0xFFFFu));
         const float g = __fmul_rn(f, x);
-        buf[h] = __fadd_rn(buf[h], __fsub_rn(x, g));
-        buf[k] = __fadd_rn(buf[k], g);
+        buf[h & VRING_MASK] = __fadd_rn(buf[h & VRING_MASK], __fsub_rn(x, g));
+        buf[k & VRING_MASK] = __fadd_rn(buf[k & VRING_MASK], g);
         float y;
         if (mixed)
-            y = __fmul_rn(__fadd_rn(x, buf[out_pos]), mixnorm);
+            y = __fmul_rn(__fadd_rn(x, buf[out_pos & VRING_MASK]), mixnorm);
         else
-            y = buf[out_pos];
+            y = buf[out_pos & VRING_MASK];
         sm.vib_y[i] = y;
-        buf[out_pos] = 0.0f;
+        buf[out_pos & VRING_MASK] = 0.0f;
         out_pos = (out_pos + 1) & 0x3FFu;
         stator = (stator + inc) & 0x07FFFFFFu;
     }
-    st->vibStator = stator;
-    st->vibOutPos = out_pos;
 }
 
 /* percussion-gain decay and key-compression chase: two scalar recurrences
  * carried across fragments (src/tonegen.cpp:3733-3771), one lane */
-__device__ void gain_ramps(InstState *st, Smem &sm, bool perc_on)
+__device__ void gain_ramps(InstScalars &sc, Smem &sm, bool perc_on)
 {
-    float kc = st->keyCompLevel;
+    float kc = sc.keyCompLevel;
     const float delta = sm.key_comp_delta;
     if (perc_on) {
-        float pg = st->percEnvGain;
-        const float decay = st->percEnvGainDecay;
+        float pg = sc.percEnvGain;
+        const float decay = sc.percEnvGainDecay;
+#pragma unroll 8
         for (int i = 0; i < TBF_FRAGMENT; ++i) {
             sm.pg[i] = pg;
             sm.kc[i] = kc;
             pg = __fmul_rn(pg, decay);
             kc = __fadd_rn(kc, delta);
         }
-        st->percEnvGain = pg;
+        sc.percEnvGain = pg;
     } else {
+#pragma unroll 8
         for (int i = 0; i < TBF_FRAGMENT; ++i) {
             sm.kc[i] = kc;
             kc = __fadd_rn(kc, delta);
         }
     }
-    st->keyCompLevel = kc;
+    sc.keyCompLevel = kc;
 }
 
 /* ------------------------------------------------------------------ */
@@ -605,17 +677,20 @@ __device__ __forceinline__ float eq_iir(const float *c, float &z0, float &z1, fl
     return y;
 }
 
+
 /* horn input filters A and B in series, one lane (src/whirl.cpp:1513-1525) */
-__device__ void horn_filter_lane(InstState *st, const DevWhirlTables *wh, Smem &sm)
+__device__ void horn_filter_lane(InstScalars &sc, const DevWhirlTables *wh, Smem &sm)
 {
     float c0[5], c1[5];
+#pragma unroll
     for (int k = 0; k < 5; ++k) {
         c0[k] = wh->iir[0][k];
         c1[k] = wh->iir[1][k];
     }
-    float a0 = st->iirz[0][0], a1 = st->iirz[0][1];
-    float b0 = st->iirz[1][0], b1 = st->iirz[1][1];
+    float a0 = sc.iirz[0][0], a1 = sc.iirz[0][1];
+    float b0 = sc.iirz[1][0], b1 = sc.iirz[1][1];
     const float leakage = wh->leakage;
+#pragma unroll 8
     for (int i = 0; i < TBF_FRAGMENT; ++i) {
         const float x = (float)__dadd_rn((double)sm.mono[i], 1e-14); /* DENORMAL_HACK */
         sm.dx[0][1 + i] = x;
@@ -625,10 +700,26 @@ __device__ void horn_filter_lane(InstState *st, const DevWhirlTables *wh, Smem &
         sm.leak[i] = __fmul_rn(y, leakage);
     }
     /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
-    st->iirz[0][0] = isnan(a0) ? 0.0f : a0;
-    st->iirz[0][1] = isnan(a1) ? 0.0f : a1;
-    st->iirz[1][0] = isnan(b0) ? 0.0f : b0;
-    st->iirz[1][1] = isnan(b1) ? 0.0f : b1;
+    sc.iirz[0][0] = isnan(a0) ? 0.0f : a0;
+    sc.iirz[0][1] = isnan(a1) ? 0.0f : a1;
+    sc.iirz[1][0] = isnan(b0) ? 0.0f : b0;
+    sc.iirz[1][1] = isnan(b1) ? 0.0f : b1;
+}
+
+/* drum filter of one channel on the values read from its delay line, one lane */
+__device__ void drum_filter_lane(InstScalars &sc, const DevWhirlTables *wh, Smem &sm, int line)
+{
+    float c[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+        c[k] = wh->iir[line][k];
+    float z0 = sc.iirz[line][0], z1 = sc.iirz[line][1];
+    float *v = sm.lineout[line];
+#pragma unroll 8
+    for (int i = 0; i < TBF_FRAGMENT; ++i)
+        v[i] = eq_iir(c, z0, z1, v[i]);
+    sc.iirz[line][0] = isnan(z0) ? 0.0f : z0;
+    sc.iirz[line][1] = isnan(z1) ? 0.0f : z1;
 }
 
 /* FILTER_C(0.4, 0.4): the literals are double, so the 2-tap FIR is evaluated in
@@ -641,8 +732,7 @@ __device__ __forceinline__ float filter_c(float x, float z)
 /* ------------------------------------------------------------------ */
 /* whirl: tap geometry, thread = sample (HN_MOTION / DR_MOTION,         */
 /* src/whirl.cpp:1432-1469).  Writes the slot and the two contributions */
-/* of every tap to shared memory; the ordered accumulation into the     */
-/* delay lines is done by scatter_lane().                               */
+/* of every tap to shared memory.                                       */
 /* ------------------------------------------------------------------ */
 __device__ __forceinline__ void tap_position(double ang_grd, int phase, const float *__restrict__ dsp,
                                              float spacing, uint32_t outpos, float &frac,
@@ -658,12 +748,12 @@ __device__ __forceinline__ void tap_position(double ang_grd, int phase, const fl
     const float t = __fadd_rn(__fadd_rn(spacing, intp), (float)outpos);
     const float r = floorf(t);
     frac = __fsub_rn(t, r);
-    slot = f2u_x86(r) & WBUF_MASK;
+    slot = f2u_x86(r) & GLOBAL_WBUF_MASK;
 }
 
 __device__ void whirl_taps(const DevWhirlTables *wh, Smem &sm, int i, uint32_t outpos0)
 {
-    const uint32_t outpos = (outpos0 + (uint32_t)i) & WBUF_MASK;
+    const uint32_t outpos = (outpos0 + (uint32_t)i) & GLOBAL_WBUF_MASK;
     const double hang = sm.hang[i], dang = sm.dang[i];
 #pragma unroll
     for (int p = 0; p < 6; ++p) {
@@ -703,41 +793,73 @@ __device__ void whirl_taps(const DevWhirlTables *wh, Smem &sm, int i, uint32_t o
     }
 }
 
-/* One lane per delay line (0 HL, 1 HR, 2 DL, 3 DR): per sample, accumulate the
- * line's three taps in source order, then read and clear the output slot; the
- * drum lines run their biquad on the value read (src/whirl.cpp:1540-1616). */
-__device__ void scatter_lane(InstState *st, const DevWhirlTables *wh, Smem &sm, int line,
+/* After the taps: build the inverse map slot -> first sample that hits it, and
+ * check what the gather relies on: per tap the slots advance monotonically with
+ * the sample index and stay inside [reader, reader + window). */
+__device__ __forceinline__ int whirl_index_taps(const DevWhirlTables *wh, Smem &sm, int i,
+                                                uint32_t outpos0)
+{
+    int bad = 0;
+    const uint32_t window = (uint32_t)wh->window;
+#pragma unroll
+    for (int p = 0; p < 12; ++p) {
+        const uint32_t n = sm.tapn[p][i];
+        const uint32_t rel = (n - outpos0) & GLOBAL_WBUF_MASK;
+        bad |= (rel < (uint32_t)i) | (rel + 1 >= window);
+        uint32_t prev = 0xFFFFFFFFu;
+        if (i > 0) {
+            prev = sm.tapn[p][i - 1];
+            bad |= ((n - prev) & GLOBAL_WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
+        }
+        if (n != prev && rel < FIRST_W)
+            sm.first[p][rel] = (uint8_t)i;
+    }
+    return bad;
+}
+
+/* Ordered gather of one delay-line slot, thread = slot.  The three taps of a line
+ * have disjoint delay ranges (checked on the host), so everything the farthest tap
+ * writes into a slot is written before anything the middle tap writes, and so on:
+ * the reference's accumulation order per slot is "taps by decreasing delay, and per
+ * tap the q-part of the samples hitting slot-1, then the (x-q)-part of the samples
+ * hitting the slot, in sample order". */
+__device__ __forceinline__ float whirl_gather_slot(const DevWhirlTables *wh, const Smem &sm,
+                                                   const float *ring, uint32_t rmask, int line,
+                                                   int s, uint32_t outpos0, bool fresh)
+{
+    const uint32_t S = (outpos0 + (uint32_t)s) & GLOBAL_WBUF_MASK;
+    const uint32_t Sm1 = (S - 1) & GLOBAL_WBUF_MASK;
+    float v = fresh ? 0.0f : ring[S & rmask];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int p = wh->tap_order[line][k];
+        if (s > 0)
+            for (int m = sm.first[p][s - 1]; m < TBF_FRAGMENT && sm.tapn[p][m] == Sm1; ++m)
+                v = __fadd_rn(v, sm.tapb[p][m]);
+        for (int m = sm.first[p][s]; m < TBF_FRAGMENT && sm.tapn[p][m] == S; ++m)
+            v = __fadd_rn(v, sm.tapa[p][m]);
+    }
+    return v;
+}
+
+/* The reference's loop as written, one lane per delay line (0 HL, 1 HR, 2 DL,
+ * 3 DR): fallback for geometries / rotor speeds the gather does not cover. */
+__device__ void scatter_lane(const Smem &sm, float *buf, uint32_t rmask, float *lineout, int line,
                              uint32_t outpos0)
 {
-    float *buf = sm.wbuf[line];
     const int tap0 = (line < 2) ? (line & 1) : 6 + (line & 1);
-    float c[5];
-    float z0 = 0.f, z1 = 0.f;
-    if (line >= 2) {
-        for (int k = 0; k < 5; ++k)
-            c[k] = wh->iir[line][k];
-        z0 = st->iirz[line][0];
-        z1 = st->iirz[line][1];
-    }
     for (int i = 0; i < TBF_FRAGMENT; ++i) {
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
             const int p = tap0 + 2 * s;
             const uint32_t n = sm.tapn[p][i];
-            buf[n] = __fadd_rn(buf[n], sm.tapa[p][i]);
-            const uint32_t n1 = (n + 1) & WBUF_MASK;
-            buf[n1] = __fadd_rn(buf[n1], sm.tapb[p][i]);
+            buf[n & rmask] = __fadd_rn(buf[n & rmask], sm.tapa[p][i]);
+            const uint32_t n1 = (n + 1) & GLOBAL_WBUF_MASK;
+            buf[n1 & rmask] = __fadd_rn(buf[n1 & rmask], sm.tapb[p][i]);
         }
-        const uint32_t op = (outpos0 + (uint32_t)i) & WBUF_MASK;
-        float v = buf[op];
-        buf[op] = 0.0f;
-        if (line >= 2)
-            v = eq_iir(c, z0, z1, v);
-        sm.lineout[line][i] = v;
-    }
-    if (line >= 2) {
-        st->iirz[line][0] = isnan(z0) ? 0.0f : z0;
-        st->iirz[line][1] = isnan(z1) ? 0.0f : z1;
+        const uint32_t op = (outpos0 + (uint32_t)i) & GLOBAL_WBUF_MASK;
+        lineout[i] = buf[op & rmask];
+        buf[op & rmask] = 0.0f;
     }
 }
 
@@ -745,137 +867,180 @@ __device__ void scatter_lane(InstState *st, const DevWhirlTables *wh, Smem &sm, 
 /* the batched render kernel: grid = instances, block = 128 threads     */
 /* ------------------------------------------------------------------ */
 __global__ void __launch_bounds__(TBF_THREADS)
-tbf_render_kernel(const RenderParams p)
+tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
+    float *wring = reinterpret_cast<float *>(smem_raw + sizeof(Smem));
+    const uint32_t rmask = ring_size - 1;
     const int tid = threadIdx.x;
     const uint32_t slot = blockIdx.x;
     const uint32_t id = p.ids ? p.ids[slot] : slot;
     InstState *st = p.states + id;
-    const DevTonegenTables *tg = p.tg + st->tgTables;
-    const DevWhirlTables *wh = p.wh + st->whTables;
+    InstScalars &sc = sm.sc;
+
+    /* ---- stage scalars, delay-line windows and FIR histories in shared memory ---- */
+    for (int i = tid; i < (int)(sizeof(InstScalars) / 4); i += TBF_THREADS)
+        reinterpret_cast<uint32_t *>(&sm.sc)[i] = reinterpret_cast<const uint32_t *>(&st->sc)[i];
+    for (int i = tid; i < VRING; i += TBF_THREADS)
+        sm.vfirst[i] = 0;
+    for (int i = tid; i < 12 * FIRST_W / 4; i += TBF_THREADS)
+        reinterpret_cast<uint32_t *>(&sm.first[0][0])[i] = 0u;
+    if (tid == 0)
+        sm.csum = 0ull;
+    __syncthreads();
+    const DevTonegenTables *tg = p.tg + sc.tgTables;
+    const DevWhirlTables *wh = p.wh + sc.whTables;
+    for (int s = tid; s < VRING; s += TBF_THREADS) {
+        const uint32_t g = (sc.vibOutPos + (uint32_t)s) & 0x3FFu;
+        sm.vring[g & VRING_MASK] = st->vibBuffer[g];
+    }
+    for (int line = 0; line < 4; ++line)
+        for (uint32_t s = tid; s < ring_size; s += TBF_THREADS) {
+            const uint32_t g = (sc.outpos + s) & GLOBAL_WBUF_MASK;
+            wring[line * ring_size + (g & rmask)] = st->wbuf[line][g];
+        }
+    if (tid < 24) {
+        const int s = tid >> 3, k = tid & 7;
+        sm.hx[s][7 - k] = sc.adx[s][(sc.adi[s] + k) & 7];
+    }
+    if (tid < 4)
+        sm.zs[tid] = sc.z[tid];
+
     const bool whirl_off = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
     const bool whirl3 = (p.flags & TBF_RENDER_WHIRLPROC3) != 0;
     const bool whirl_run = !whirl_off && !wh->bypass;
+    const bool gather_ok = wh->gather_ok != 0;
+    const int window = wh->window;
     const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
     float *out_l = p.out_l + (size_t)slot * p.out_stride;
     float *out_r = p.out_r + (size_t)slot * p.out_stride;
-
-    /* ---- stage the delay lines and FIR histories in shared memory ---- */
-    for (int i = tid; i < TBF_VIB_BUF; i += TBF_THREADS)
-        sm.vibbuf[i] = st->vibBuffer[i];
-    for (int i = tid; i < 4 * TBF_WHIRL_BUF; i += TBF_THREADS)
-        (&sm.wbuf[0][0])[i] = (&st->wbuf[0][0])[i];
-    if (tid < 24) {
-        const int s = tid >> 3, k = tid & 7;
-        sm.hx[s][7 - k] = st->adx[s][(st->adi[s] + k) & 7];
-    }
-    if (tid < 4)
-        sm.zs[tid] = st->z[tid];
-    if (tid == 0)
-        sm.csum = 0ull;
-    uint32_t outpos0 = st->outpos;
+    uint32_t outpos0 = sc.outpos;
     uint64_t ev_cur = p.ev_cursor[slot];
     const uint64_t ev_end = p.ev_start[slot + 1];
     unsigned long long csum = 0ull;
     __syncthreads();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
-        /* -- S0: control events that precede this fragment, routing, key compression -- */
+        /* -- P0: control events that precede this fragment, routing, key compression -- */
         if (tid == 0) {
             while (ev_cur < ev_end && p.events[ev_cur].fragment <= p.frag_base + f) {
-                apply_event(st, tg, wh, p.events[ev_cur]);
+                apply_event(sc, st, tg, wh, p.events[ev_cur]);
                 ++ev_cur;
             }
-            int kdc = st->keyDownCount;
+            int kdc = sc.keyDownCount;
             if (kdc > 127 || kdc < 0) { /* reference reads past keyCompTable[128] */
-                st->errorFlags |= TBF_IFLAG_KEYCOMP_OOB;
+                sc.errorFlags |= TBF_IFLAG_KEYCOMP_OOB;
                 kdc = kdc < 0 ? 0 : 127;
             }
             const float key_comp = tg->key_comp_table[kdc];
             /* (keyComp - level) / 128.f: dividing by 2^7 and multiplying by 2^-7 round identically */
-            sm.key_comp_delta = __fmul_rn(__fsub_rn(key_comp, st->keyCompLevel), 0.0078125f);
-            sm.recompute_routing = (st->oldRouting != st->newRouting);
+            sm.key_comp_delta = __fmul_rn(__fsub_rn(key_comp, sc.keyCompLevel), 0.0078125f);
+            sm.recompute_routing = (sc.oldRouting != sc.newRouting);
             if (sm.recompute_routing)
-                st->oldRouting = st->newRouting;
-            sm.draw_bar_change = st->drawBarChange;
-            sm.vib_on = (st->oldRouting & RT_VIB) != 0;
-            sm.perc_on = (st->oldRouting & RT_PERC) != 0;
+                sc.oldRouting = sc.newRouting;
+            sm.draw_bar_change = sc.drawBarChange;
+            sm.vib_on = (sc.oldRouting & RT_VIB) != 0;
+            sm.perc_on = (sc.oldRouting & RT_PERC) != 0;
             sm.n_ins = 0;
         }
         __syncthreads();
-
-        /* -- S1: active list -> core program records -- */
-        active_list_pass(st, tg, sm, tid);
-        __syncthreads();
         const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
 
-        /* -- S2: additive synthesis, thread = sample -- */
+        /* -- P1: data-independent recurrences on single lanes of warps 1..3, while the
+         *        active list is turned into core-program records -- */
+        if (tid == 32) {
+            gain_ramps(sc, sm, perc_on);
+        } else if (tid == 64 && whirl_run) {
+            const RotorConst rc = {10.f, 60.f, 1};
+            int acdc = sc.hornAcDc;
+            double incr = sc.hornIncr, ang = sc.hornAngle;
+            const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, sc.hornTarget, wh->hn_brake_pos,
+                                         wh->one_minus_l[0], wh->one_minus_l[1]);
+            double fin;
+            angle_lane(ang, incr, sm.hang, &fin);
+            sc.hornAcDc = acdc;
+            sc.hornIncr = brake ? 0.0 : incr;
+            sc.hornAngle = fin;
+        } else if (tid == 96 && whirl_run) {
+            const RotorConst rc = {8.f, 100.f, 0};
+            int acdc = sc.drumAcDc;
+            double incr = sc.drumIncr, ang = sc.drumAngle;
+            const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, sc.drumTarget, wh->dr_brake_pos,
+                                         wh->one_minus_l[2], wh->one_minus_l[3]);
+            double fin;
+            angle_lane(ang, incr, sm.dang, &fin);
+            sc.drumAcDc = acdc;
+            sc.drumIncr = brake ? 0.0 : incr;
+            sc.drumAngle = fin;
+        }
+        active_list_pass(st, tg, sm, tid);
+        __syncthreads();
+
+        /* -- P2: additive synthesis, thread = sample; scanner contributions -- */
         float swl, vib, prc;
         core_interpreter(tg, sm, tid, swl, vib, prc);
         sm.vib_in[tid] = vib;
         sm.prc[tid] = prc;
-        __syncthreads();
+        int vbad = 0;
+        if (vib_on)
+            vbad = vibrato_contrib(sc, tg, sm, tid, vib);
+        vbad = __syncthreads_or(vbad);
 
-        /* -- S3: serial lanes in four different warps + percussion high-pass -- */
-        if (tid == 0) {
-            if (vib_on)
-                vibrato_serial(st, tg, sm);
-        } else if (tid == 32) {
-            gain_ramps(st, sm, perc_on);
-        } else if (tid == 64 && whirl_run) {
-            const RotorConst rc = {10.f, 60.f, 1};
-            int acdc = st->hornAcDc;
-            double incr = st->hornIncr, ang = st->hornAngle;
-            const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, st->hornTarget,
-                                         wh->hn_brake_pos, wh->one_minus_l[0], wh->one_minus_l[1]);
-            double fin;
-            angle_lane(ang, incr, sm.hang, &fin);
-            st->hornAcDc = acdc;
-            st->hornIncr = brake ? 0.0 : incr;
-            st->hornAngle = fin;
-        } else if (tid == 96 && whirl_run) {
-            const RotorConst rc = {8.f, 100.f, 0};
-            int acdc = st->drumAcDc;
-            double incr = st->drumIncr, ang = st->drumAngle;
-            const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, st->drumTarget,
-                                         wh->dr_brake_pos, wh->one_minus_l[2], wh->one_minus_l[3]);
-            double fin;
-            angle_lane(ang, incr, sm.dang, &fin);
-            st->drumAcDc = acdc;
-            st->drumIncr = brake ? 0.0 : incr;
-            st->drumAngle = fin;
+        /* -- P3: scanner gather (thread = slot), percussion high-pass, mixdown -- */
+        float vib_y = 0.0f;
+        if (vib_on) {
+            if (!vbad) {
+                const float v = vibrato_gather_slot(sc, sm, tid);
+                float v2 = 0.0f;
+                const bool second = tid + TBF_FRAGMENT < VWINDOW;
+                if (second)
+                    v2 = vibrato_gather_slot(sc, sm, tid + TBF_FRAGMENT);
+                vib_y = sc.vibMixed ? __fmul_rn(__fadd_rn(vib, v), (float)0.7071067811865475) : v;
+                __syncthreads(); /* every slot gathered before any ring slot changes */
+                sm.vring[(sc.vibOutPos + (uint32_t)tid) & VRING_MASK] = 0.0f;
+                if (second)
+                    sm.vring[(sc.vibOutPos + (uint32_t)(tid + TBF_FRAGMENT)) & VRING_MASK] = v2;
+            } else {
+                if (tid == 0)
+                    vibrato_serial(sc, tg, sm);
+                __syncthreads();
+                vib_y = sm.vib_y[tid];
+            }
         }
         float prc_hp = 0.0f;
         if (perc_on) /* in-place differencer, src/tonegen.cpp:3719-3732 */
-            prc_hp = __fsub_rn(tid ? sm.prc[tid - 1] : st->pz, prc);
-        __syncthreads();
-
-        /* -- S4: mixdown (src/tonegen.cpp:3733-3777) -- */
+            prc_hp = __fsub_rn(tid ? sm.prc[tid - 1] : sc.pz, prc);
         float mono;
         {
             const float kc = sm.kc[tid];
             if (perc_on) {
-                const float og = __fmul_rn(st->swellPedalGain, st->percDrawbarGain);
+                const float og = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
                 const float pterm = __fmul_rn(prc_hp, sm.pg[tid]);
-                const float acc = vib_on ? __fadd_rn(__fadd_rn(swl, sm.vib_y[tid]), pterm)
-                                         : __fadd_rn(swl, pterm);
+                const float acc = vib_on ? __fadd_rn(__fadd_rn(swl, vib_y), pterm) : __fadd_rn(swl, pterm);
                 mono = __fmul_rn(__fmul_rn(og, kc), acc);
             } else {
-                const float acc = vib_on ? __fadd_rn(swl, sm.vib_y[tid]) : swl;
-                mono = __fmul_rn(__fmul_rn(st->swellPedalGain, kc), acc);
+                const float acc = vib_on ? __fadd_rn(swl, vib_y) : swl;
+                mono = __fmul_rn(__fmul_rn(sc.swellPedalGain, kc), acc);
             }
         }
         sm.mono[tid] = mono;
         __syncthreads();
+
+        /* -- P4: end-of-fragment tone generator scalars + horn filters A,B (lane 0) -- */
         if (tid == 0) {
-            if (perc_on) {
-                st->outputGain = __fmul_rn(st->swellPedalGain, st->percDrawbarGain);
-                st->pz = sm.prc[TBF_FRAGMENT - 1];
+            if (vib_on) {
+                sc.vibStator = (sc.vibStator + TBF_FRAGMENT * tg->vib_stator_increment) & 0x07FFFFFFu;
+                sc.vibOutPos = (sc.vibOutPos + TBF_FRAGMENT) & 0x3FFu;
             }
-            if (st->upperKeyCount == 0)
-                st->percEnvGain = st->percEnvGainReset;
+            if (perc_on) {
+                sc.outputGain = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
+                sc.pz = sm.prc[TBF_FRAGMENT - 1];
+            }
+            if (sc.upperKeyCount == 0)
+                sc.percEnvGain = sc.percEnvGainReset;
+            if (whirl_run)
+                horn_filter_lane(sc, wh, sm);
         }
 
         float o_l, o_r;
@@ -889,25 +1054,79 @@ tbf_render_kernel(const RenderParams p)
                                           __fmul_rn(0.0f, wh->mic_drl)), __fmul_rn(0.0f, wh->mic_drr));
             }
         } else {
-            /* -- S5: horn filters A,B: serial lane -- */
-            if (tid == 0)
-                horn_filter_lane(st, wh, sm);
             __syncthreads();
-            /* -- S6: reflection filters (2-tap FIRs in double) -- */
-            sm.hx[1][8 + tid] = filter_c(sm.hx[0][8 + tid], tid ? sm.hx[0][7 + tid] : sm.zs[0]);
-            sm.dx[1][1 + tid] = filter_c(sm.dx[0][1 + tid], tid ? sm.dx[0][tid] : sm.zs[2]);
+            /* -- P5: the two reflection filters of each path (2-tap FIRs in double);
+             *        stage 1 of sample i-1 is recomputed locally to save a barrier -- */
+            {
+                const float h0 = sm.hx[0][8 + tid], h0m = tid ? sm.hx[0][7 + tid] : sm.zs[0];
+                const float h1 = filter_c(h0, h0m);
+                const float h1m = tid ? filter_c(h0m, tid > 1 ? sm.hx[0][6 + tid] : sm.zs[0]) : sm.zs[1];
+                sm.hx[1][8 + tid] = h1;
+                sm.hx[2][8 + tid] = filter_c(h1, h1m);
+                const float d0 = sm.dx[0][1 + tid], d0m = tid ? sm.dx[0][tid] : sm.zs[2];
+                const float d1 = filter_c(d0, d0m);
+                const float d1m = tid ? filter_c(d0m, tid > 1 ? sm.dx[0][tid - 1] : sm.zs[2]) : sm.zs[3];
+                sm.dx[1][1 + tid] = d1;
+                sm.dx[2][1 + tid] = filter_c(d1, d1m);
+            }
             __syncthreads();
-            sm.hx[2][8 + tid] = filter_c(sm.hx[1][8 + tid], tid ? sm.hx[1][7 + tid] : sm.zs[1]);
-            sm.dx[2][1 + tid] = filter_c(sm.dx[1][1 + tid], tid ? sm.dx[1][tid] : sm.zs[3]);
-            __syncthreads();
-            /* -- S7: tap geometry + FIRs, thread = sample -- */
+            /* -- P6: tap geometry + FIRs, thread = sample -- */
             whirl_taps(wh, sm, tid, outpos0);
             __syncthreads();
-            /* -- S8: ordered scatter / read / drum biquads: one lane per line -- */
-            if ((tid & 31) == 0)
-                scatter_lane(st, wh, sm, tid >> 5, outpos0);
+            int wbad = 1;
+            if (gather_ok)
+                wbad = whirl_index_taps(wh, sm, tid, outpos0);
+            wbad = __syncthreads_or(wbad);
+            /* -- P7: delay lines: ordered gather (thread = slot) or the serial fallback -- */
+            if (!wbad) {
+                /* slots [0, window) ahead of the reader, window <= 640: slot s >= ring_size
+                 * shares its ring cell with slot s - ring_size, which is one of the 128 slots
+                 * read (and cleared) in this fragment, and nothing older can have reached
+                 * that far ahead: its starting value is 0 */
+                float keepv[4][GATHER_K];
+#pragma unroll
+                for (int line = 0; line < 4; ++line) {
+#pragma unroll
+                    for (int k = 0; k < GATHER_K; ++k) {
+                        const int s = tid + k * TBF_FRAGMENT;
+                        keepv[line][k] = (s < window)
+                            ? whirl_gather_slot(wh, sm, wring + line * ring_size, rmask, line, s, outpos0,
+                                                (uint32_t)s >= ring_size)
+                            : 0.0f;
+                    }
+                }
+                __syncthreads(); /* all slots gathered before the rings change */
+#pragma unroll
+                for (int line = 0; line < 4; ++line) {
+                    sm.lineout[line][tid] = keepv[line][0];
+                    wring[line * ring_size + ((outpos0 + (uint32_t)tid) & rmask)] = 0.0f;
+                }
+                __syncthreads(); /* cells of the slots just read are clear before reuse */
+#pragma unroll
+                for (int line = 0; line < 4; ++line) {
+                    float *ring = wring + line * ring_size;
+#pragma unroll
+                    for (int k = 1; k < GATHER_K; ++k) {
+                        const int s = tid + k * TBF_FRAGMENT;
+                        if (s < window)
+                            ring[(outpos0 + (uint32_t)s) & rmask] = keepv[line][k];
+                    }
+                }
+            } else {
+                if (gather_ok && tid == 0)
+                    sc.errorFlags |= TBF_IFLAG_GATHER_FALLBACK;
+                if ((tid & 31) == 0)
+                    scatter_lane(sm, wring + (tid >> 5) * ring_size, rmask, sm.lineout[tid >> 5],
+                                 tid >> 5, outpos0);
+            }
             __syncthreads();
-            /* -- S9: output mix -- */
+            /* -- P8: drum filters, one lane per channel in two different warps -- */
+            if (tid == 64)
+                drum_filter_lane(sc, wh, sm, 2);
+            else if (tid == 96)
+                drum_filter_lane(sc, wh, sm, 3);
+            __syncthreads();
+            /* -- P9: output mix -- */
             const float hl = sm.lineout[0][tid], hr = sm.lineout[1][tid];
             const float yl = sm.lineout[2][tid], yr = sm.lineout[3][tid];
             const float leak = sm.leak[tid];
@@ -937,7 +1156,7 @@ tbf_render_kernel(const RenderParams p)
                 sm.hx[tid >> 3][tid & 7] = keep;
             if (tid >= 32 && tid < 36)
                 sm.zs[tid - 32] = isnan(zc) ? 0.0f : zc; /* src/whirl.cpp:1627-1630 */
-            outpos0 = (outpos0 + TBF_FRAGMENT) & WBUF_MASK;
+            outpos0 = (outpos0 + TBF_FRAGMENT) & GLOBAL_WBUF_MASK;
         }
 
         if (store) {
@@ -951,20 +1170,29 @@ tbf_render_kernel(const RenderParams p)
     }
 
     /* ---- write the staged state back ---- */
-    for (int i = tid; i < TBF_VIB_BUF; i += TBF_THREADS)
-        st->vibBuffer[i] = sm.vibbuf[i];
-    for (int i = tid; i < 4 * TBF_WHIRL_BUF; i += TBF_THREADS)
-        (&st->wbuf[0][0])[i] = (&sm.wbuf[0][0])[i];
     if (tid < 24) {
         const int s = tid >> 3, k = tid & 7;
-        st->adx[s][(st->adi[s] + k) & 7] = sm.hx[s][7 - k];
+        sc.adx[s][(sc.adi[s] + k) & 7] = sm.hx[s][7 - k];
     }
     if (tid < 4)
-        st->z[tid] = sm.zs[tid];
+        sc.z[tid] = sm.zs[tid];
     if (tid == 0) {
-        st->outpos = outpos0;
+        sc.outpos = outpos0;
         p.ev_cursor[slot] = ev_cur;
     }
+    __syncthreads();
+    for (int i = tid; i < (int)(sizeof(InstScalars) / 4); i += TBF_THREADS)
+        reinterpret_cast<uint32_t *>(&st->sc)[i] = reinterpret_cast<const uint32_t *>(&sm.sc)[i];
+    /* outside the live windows every ring slot is zero (cleared when read) */
+    for (int s = tid; s < TBF_VIB_BUF; s += TBF_THREADS) {
+        const uint32_t g = (sc.vibOutPos + (uint32_t)s) & 0x3FFu;
+        st->vibBuffer[g] = (s < VRING) ? sm.vring[g & VRING_MASK] : 0.0f;
+    }
+    for (int line = 0; line < 4; ++line)
+        for (uint32_t s = tid; s < TBF_WHIRL_BUF; s += TBF_THREADS) {
+            const uint32_t g = (outpos0 + s) & GLOBAL_WBUF_MASK;
+            st->wbuf[line][g] = (s < ring_size) ? wring[line * ring_size + (g & rmask)] : 0.0f;
+        }
     if (p.checksums) {
         atomicAdd(&sm.csum, csum);
         __syncthreads();
@@ -987,19 +1215,20 @@ __global__ void tbf_replicate_kernel(InstState *states, uint32_t first, uint32_t
 
 } /* namespace */
 
-size_t tbf_render_smem_bytes() { return sizeof(Smem); }
+size_t tbf_render_smem_bytes(int ring_size) { return sizeof(Smem) + (size_t)4 * ring_size * sizeof(float); }
 
-int tbf_launch_render(const RenderParams &p, void *stream)
+int tbf_launch_render(const RenderParams &p, int ring_size, void *stream)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static int attr_set_for = 0;
+    const size_t smem = tbf_render_smem_bytes(ring_size);
+    if (attr_set_for < (int)smem) {
         cudaError_t e = cudaFuncSetAttribute(tbf_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)sizeof(Smem));
+                                             (int)smem);
         if (e != cudaSuccess)
             return (int)e;
-        attr_set = true;
+        attr_set_for = (int)smem;
     }
-    tbf_render_kernel<<<p.n_instances, TBF_THREADS, sizeof(Smem), (cudaStream_t)stream>>>(p);
+    tbf_render_kernel<<<p.n_instances, TBF_THREADS, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
     return (int)cudaGetLastError();
 }
 

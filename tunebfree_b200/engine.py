@@ -46,6 +46,8 @@ def lib():
                                                     C.POINTER(C.c_int)]
         L.tbf_gpu_whirl_tables_create.argtypes = [vp, C.POINTER(cabi.WhirlTables),
                                                   C.POINTER(C.c_int)]
+        L.tbf_gpu_whirl_tables_info.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                                C.POINTER(C.c_int)]
         L.tbf_gpu_instance_create.argtypes = [vp, C.c_int, C.c_int, C.c_uint32,
                                               C.POINTER(C.c_uint32)]
         L.tbf_gpu_instance_count.argtypes = [vp]
@@ -147,6 +149,12 @@ class Context:
         h = C.c_int(-1)
         self._ck(lib().tbf_gpu_whirl_tables_create(self._h, C.byref(tables), C.byref(h)))
         return h.value
+
+    def whirl_tables_info(self, handle):
+        """-> (gather_ok, ring_size, window)"""
+        g, r, w = C.c_int(0), C.c_int(0), C.c_int(0)
+        self._ck(lib().tbf_gpu_whirl_tables_info(self._h, handle, C.byref(g), C.byref(r), C.byref(w)))
+        return g.value, r.value, w.value
 
     def create_instances(self, tg_handle, wh_handle, count=1):
         first = C.c_uint32(0)
