@@ -358,10 +358,17 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
                 if (!(d.tap_dmin[t[k]] > d.tap_dmax[t[k + 1]]))
                     ok = false;
         }
-        /* a 512-slot shared ring holds the live part of a line as long as no tap reaches
-         * 512 slots ahead; the gather covers windows of up to 5 slots per thread */
-        d.gather_ok = (ok && d.window <= 640) ? 1 : 0;
-        d.ring_size = (wmax + 2 <= 512 && ok && d.window <= 640) ? 512 : TBF_WHIRL_BUF;
+        /* A 512-slot shared ring holds a line as long as the slots that alias (>= 512 ahead
+         * of the reader) fall on cells the kernel reads and clears before it scatters:
+         * the first min(128, line_dmin) slots of the fragment. */
+        int min_line_dmin = TBF_FRAGMENT;
+        for (int line = 0; line < 4; ++line) {
+            d.line_dmin[line] = std::max(0, std::min(TBF_FRAGMENT, d.tap_dmin[d.tap_order[line][2]]));
+            min_line_dmin = std::min(min_line_dmin, d.line_dmin[line]);
+        }
+        const bool ring512 = ok && (d.window <= 512 || d.window - 512 <= min_line_dmin);
+        d.gather_ok = ring512 ? 1 : 0;
+        d.ring_size = ring512 ? 512 : TBF_WHIRL_BUF;
         s.ring_size = d.ring_size;
         s.gather_ok = d.gather_ok;
         s.window = d.window;

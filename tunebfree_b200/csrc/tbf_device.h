@@ -123,6 +123,7 @@ struct DevWhirlTables {
     int32_t window;         /* slots ahead of the reader that can be non-zero, + 128    */
     int32_t tap_order[4][3];/* per line HL HR DL DR: tap ids (0..11), farthest delay first */
     int32_t tap_dmin[12], tap_dmax[12];
+    int32_t line_dmin[4];   /* per line: slots nearer than this cannot be written in a fragment */
 };
 
 struct RenderParams {

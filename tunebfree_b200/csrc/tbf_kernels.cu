@@ -37,8 +37,6 @@
 #define VRING 256            /* shared-memory scanner ring: writes land <= 27 slots ahead */
 #define VRING_MASK (VRING - 1)
 #define VWINDOW (TBF_FRAGMENT + 100)
-#define FIRST_W 640          /* slots covered by the per-tap inverse map (5 per thread) */
-#define GATHER_K 5
 
 namespace {
 
@@ -73,7 +71,6 @@ struct __align__(16) Smem {
     float leak[TBF_FRAGMENT];
     uint16_t tapn[12][TBF_FRAGMENT]; /* destination slot of the tap's main part (ring index) */
     float tapa[12][TBF_FRAGMENT], tapb[12][TBF_FRAGMENT];
-    uint8_t first[12][FIRST_W];      /* slot (relative to the reader) -> first sample hitting it */
     float lineout[4][TBF_FRAGMENT];  /* HL HR raw reads, DL DR after the drum biquad */
     unsigned long long csum;
     int n_rec, n_ins, recompute_routing, draw_bar_change, vib_on, perc_on;
@@ -660,11 +657,44 @@ __device__ __forceinline__ double angle_step(double a, double incr)
 __device__ void angle_lane(double a0, double incr, double *out, double *final_angle)
 {
     double a = a0;
-    for (int i = 0; i < TBF_FRAGMENT; ++i) {
-        out[i] = a;
-        a = angle_step(a, incr);
+    if (a0 >= 0.0 && a0 < 1.0 && incr >= 0.0 && incr < 1.0) {
+        /* every sum stays in [0, 2): fmod(t, 1.0) is t or t - 1, both exact */
+#pragma unroll 8
+        for (int i = 0; i < TBF_FRAGMENT; ++i) {
+            out[i] = a;
+            const double t = __dadd_rn(a, incr);
+            a = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+        }
+    } else {
+        for (int i = 0; i < TBF_FRAGMENT; ++i) {
+            out[i] = a;
+            a = angle_step(a, incr);
+        }
     }
     *final_angle = a;
+}
+
+/* speed ramp + angle sequence of one rotor; the horn and the drum lane run this in
+ * lockstep on two lanes of one warp */
+__device__ void rotor_lane(InstScalars &sc, const DevWhirlTables *wh, Smem &sm, bool horn)
+{
+    RotorConst rc;
+    rc.hardstop_rpm = horn ? 10.f : 8.f;
+    rc.brake_limit_rpm = horn ? 60.f : 100.f;
+    rc.is_horn = horn ? 1 : 0;
+    int *p_acdc = horn ? &sc.hornAcDc : &sc.drumAcDc;
+    double *p_incr = horn ? &sc.hornIncr : &sc.drumIncr;
+    double *p_ang = horn ? &sc.hornAngle : &sc.drumAngle;
+    int acdc = *p_acdc;
+    double incr = *p_incr, ang = *p_ang;
+    const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, horn ? sc.hornTarget : sc.drumTarget,
+                                 horn ? wh->hn_brake_pos : wh->dr_brake_pos,
+                                 wh->one_minus_l[horn ? 0 : 2], wh->one_minus_l[horn ? 1 : 3]);
+    double fin;
+    angle_lane(ang, incr, horn ? sm.hang : sm.dang, &fin);
+    *p_acdc = acdc;
+    *p_incr = brake ? 0.0 : incr;
+    *p_ang = fin;
 }
 
 /* DF-II biquad, float, source operation order (EQ_IIR, src/whirl.cpp:1479-1485) */
@@ -678,32 +708,39 @@ __device__ __forceinline__ float eq_iir(const float *c, float &z0, float &z1, fl
 }
 
 
-/* horn input filters A and B in series, one lane (src/whirl.cpp:1513-1525) */
-__device__ void horn_filter_lane(InstScalars &sc, const DevWhirlTables *wh, Smem &sm)
+/* horn input filters A and B in series (src/whirl.cpp:1513-1525), software-pipelined
+ * over lanes 0 and 1 of warp 0: in iteration it lane 0 runs filter A on sample it while
+ * lane 1 runs filter B on filter A's output of sample it-1 (handed over by shuffle), so
+ * both recurrences share one instruction stream.  Call with tid 0 and 1 only. */
+__device__ void horn_filter_lanes(InstScalars &sc, const DevWhirlTables *wh, Smem &sm, int lane)
 {
-    float c0[5], c1[5];
+    float c[5];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
-        c0[k] = wh->iir[0][k];
-        c1[k] = wh->iir[1][k];
-    }
-    float a0 = sc.iirz[0][0], a1 = sc.iirz[0][1];
-    float b0 = sc.iirz[1][0], b1 = sc.iirz[1][1];
+    for (int k = 0; k < 5; ++k)
+        c[k] = wh->iir[lane][k];
+    float z0 = sc.iirz[lane][0], z1 = sc.iirz[lane][1];
     const float leakage = wh->leakage;
-#pragma unroll 8
-    for (int i = 0; i < TBF_FRAGMENT; ++i) {
-        const float x = (float)__dadd_rn((double)sm.mono[i], 1e-14); /* DENORMAL_HACK */
-        sm.dx[0][1 + i] = x;
-        float y = eq_iir(c0, a0, a1, x);
-        y = eq_iir(c1, b0, b1, y);
-        sm.hx[0][8 + i] = y;
-        sm.leak[i] = __fmul_rn(y, leakage);
+    float handed = 0.0f; /* lane 1: filter A's output of the previous iteration */
+#pragma unroll 4
+    for (int it = 0; it <= TBF_FRAGMENT; ++it) {
+        float in = handed;
+        if (lane == 0 && it < TBF_FRAGMENT) {
+            in = (float)__dadd_rn((double)sm.mono[it], 1e-14); /* DENORMAL_HACK */
+            sm.dx[0][1 + it] = in;
+        }
+        const bool active = lane == 0 ? (it < TBF_FRAGMENT) : (it > 0);
+        float y = 0.0f;
+        if (active)
+            y = eq_iir(c, z0, z1, in);
+        handed = __shfl_sync(0x3u, y, 0);
+        if (lane == 1 && it > 0) {
+            sm.hx[0][8 + it - 1] = y;
+            sm.leak[it - 1] = __fmul_rn(y, leakage);
+        }
     }
     /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
-    sc.iirz[0][0] = isnan(a0) ? 0.0f : a0;
-    sc.iirz[0][1] = isnan(a1) ? 0.0f : a1;
-    sc.iirz[1][0] = isnan(b0) ? 0.0f : b0;
-    sc.iirz[1][1] = isnan(b1) ? 0.0f : b1;
+    sc.iirz[lane][0] = isnan(z0) ? 0.0f : z0;
+    sc.iirz[lane][1] = isnan(z1) ? 0.0f : z1;
 }
 
 /* drum filter of one channel on the values read from its delay line, one lane */
@@ -793,10 +830,10 @@ __device__ void whirl_taps(const DevWhirlTables *wh, Smem &sm, int i, uint32_t o
     }
 }
 
-/* After the taps: build the inverse map slot -> first sample that hits it, and
- * check what the gather relies on: per tap the slots advance monotonically with
- * the sample index and stay inside [reader, reader + window). */
-__device__ __forceinline__ int whirl_index_taps(const DevWhirlTables *wh, Smem &sm, int i,
+/* What the parallel delay-line update relies on, checked per fragment: per tap the
+ * destination slots advance monotonically with the sample index and stay inside
+ * [reader, reader + window). */
+__device__ __forceinline__ int whirl_check_taps(const DevWhirlTables *wh, const Smem &sm, int i,
                                                 uint32_t outpos0)
 {
     int bad = 0;
@@ -806,40 +843,52 @@ __device__ __forceinline__ int whirl_index_taps(const DevWhirlTables *wh, Smem &
         const uint32_t n = sm.tapn[p][i];
         const uint32_t rel = (n - outpos0) & GLOBAL_WBUF_MASK;
         bad |= (rel < (uint32_t)i) | (rel + 1 >= window);
-        uint32_t prev = 0xFFFFFFFFu;
-        if (i > 0) {
-            prev = sm.tapn[p][i - 1];
-            bad |= ((n - prev) & GLOBAL_WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
-        }
-        if (n != prev && rel < FIRST_W)
-            sm.first[p][rel] = (uint8_t)i;
+        if (i > 0)
+            bad |= ((n - (uint32_t)sm.tapn[p][i - 1]) & GLOBAL_WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
     }
     return bad;
 }
 
-/* Ordered gather of one delay-line slot, thread = slot.  The three taps of a line
- * have disjoint delay ranges (checked on the host), so everything the farthest tap
- * writes into a slot is written before anything the middle tap writes, and so on:
- * the reference's accumulation order per slot is "taps by decreasing delay, and per
- * tap the q-part of the samples hitting slot-1, then the (x-q)-part of the samples
- * hitting the slot, in sample order". */
-__device__ __forceinline__ float whirl_gather_slot(const DevWhirlTables *wh, const Smem &sm,
-                                                   const float *ring, uint32_t rmask, int line,
-                                                   int s, uint32_t outpos0, bool fresh)
+/* Ordered scatter of ONE tap, thread = sample.  Because the tap's slot sequence n[i]
+ * never decreases, the samples hitting a slot form a contiguous run, and the
+ * reference's loop adds to slot S first the q-parts of the run that hit S-1, then the
+ * (x-q)-parts of the run that hits S.  The first sample of each run applies exactly
+ * that sequence to its slot; a slot that only receives q-parts (the run after it
+ * skips it, or the fragment ends) is completed by the last sample of the run before.
+ * Distinct threads touch distinct slots, so one pass needs no atomics; the three taps
+ * of a line are applied in three passes, farthest delay first (see tap_order). */
+__device__ __forceinline__ void whirl_tap_pass(const Smem &sm, float *ring, uint32_t rmask, int p, int i)
 {
-    const uint32_t S = (outpos0 + (uint32_t)s) & GLOBAL_WBUF_MASK;
-    const uint32_t Sm1 = (S - 1) & GLOBAL_WBUF_MASK;
-    float v = fresh ? 0.0f : ring[S & rmask];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int p = wh->tap_order[line][k];
-        if (s > 0)
-            for (int m = sm.first[p][s - 1]; m < TBF_FRAGMENT && sm.tapn[p][m] == Sm1; ++m)
-                v = __fadd_rn(v, sm.tapb[p][m]);
-        for (int m = sm.first[p][s]; m < TBF_FRAGMENT && sm.tapn[p][m] == S; ++m)
-            v = __fadd_rn(v, sm.tapa[p][m]);
+    const uint16_t *n = sm.tapn[p];
+    const float *a = sm.tapa[p];
+    const float *b = sm.tapb[p];
+    const uint32_t ni = n[i];
+    const uint32_t prev = i ? (uint32_t)n[i - 1] : 0xFFFFFFFFu;
+    const uint32_t next = (i < TBF_FRAGMENT - 1) ? (uint32_t)n[i + 1] : 0xFFFFFFFFu;
+    if (ni != prev) { /* first sample of the run hitting slot ni */
+        float v = ring[ni & rmask];
+        const uint32_t sm1 = (ni - 1) & GLOBAL_WBUF_MASK;
+        int j0 = i;
+        while (j0 > 0 && n[j0 - 1] == sm1)
+            --j0;
+        for (int j = j0; j < i; ++j)
+            v = __fadd_rn(v, b[j]);
+        for (int m = i; m < TBF_FRAGMENT && n[m] == ni; ++m)
+            v = __fadd_rn(v, a[m]);
+        ring[ni & rmask] = v;
     }
-    return v;
+    if (ni != next) { /* last sample of its run */
+        const uint32_t sp1 = (ni + 1) & GLOBAL_WBUF_MASK;
+        if (next != sp1) { /* nobody hits ni+1 as a main slot in this fragment */
+            float v = ring[sp1 & rmask];
+            int j0 = i;
+            while (j0 > 0 && n[j0 - 1] == ni)
+                --j0;
+            for (int j = j0; j <= i; ++j)
+                v = __fadd_rn(v, b[j]);
+            ring[sp1 & rmask] = v;
+        }
+    }
 }
 
 /* The reference's loop as written, one lane per delay line (0 HL, 1 HR, 2 DL,
@@ -884,8 +933,6 @@ tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
         reinterpret_cast<uint32_t *>(&sm.sc)[i] = reinterpret_cast<const uint32_t *>(&st->sc)[i];
     for (int i = tid; i < VRING; i += TBF_THREADS)
         sm.vfirst[i] = 0;
-    for (int i = tid; i < 12 * FIRST_W / 4; i += TBF_THREADS)
-        reinterpret_cast<uint32_t *>(&sm.first[0][0])[i] = 0u;
     if (tid == 0)
         sm.csum = 0ull;
     __syncthreads();
@@ -951,28 +998,8 @@ tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
          *        active list is turned into core-program records -- */
         if (tid == 32) {
             gain_ramps(sc, sm, perc_on);
-        } else if (tid == 64 && whirl_run) {
-            const RotorConst rc = {10.f, 60.f, 1};
-            int acdc = sc.hornAcDc;
-            double incr = sc.hornIncr, ang = sc.hornAngle;
-            const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, sc.hornTarget, wh->hn_brake_pos,
-                                         wh->one_minus_l[0], wh->one_minus_l[1]);
-            double fin;
-            angle_lane(ang, incr, sm.hang, &fin);
-            sc.hornAcDc = acdc;
-            sc.hornIncr = brake ? 0.0 : incr;
-            sc.hornAngle = fin;
-        } else if (tid == 96 && whirl_run) {
-            const RotorConst rc = {8.f, 100.f, 0};
-            int acdc = sc.drumAcDc;
-            double incr = sc.drumIncr, ang = sc.drumAngle;
-            const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, sc.drumTarget, wh->dr_brake_pos,
-                                         wh->one_minus_l[2], wh->one_minus_l[3]);
-            double fin;
-            angle_lane(ang, incr, sm.dang, &fin);
-            sc.drumAcDc = acdc;
-            sc.drumIncr = brake ? 0.0 : incr;
-            sc.drumAngle = fin;
+        } else if ((tid == 64 || tid == 65) && whirl_run) {
+            rotor_lane(sc, wh, sm, tid == 64); /* horn and drum rotor: two lanes in lockstep */
         }
         active_list_pass(st, tg, sm, tid);
         __syncthreads();
@@ -1039,9 +1066,9 @@ tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
             }
             if (sc.upperKeyCount == 0)
                 sc.percEnvGain = sc.percEnvGainReset;
-            if (whirl_run)
-                horn_filter_lane(sc, wh, sm);
         }
+        if (tid < 2 && whirl_run)
+            horn_filter_lanes(sc, wh, sm, tid);
 
         float o_l, o_r;
         if (!whirl_run) {
@@ -1075,43 +1102,35 @@ tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
             __syncthreads();
             int wbad = 1;
             if (gather_ok)
-                wbad = whirl_index_taps(wh, sm, tid, outpos0);
+                wbad = whirl_check_taps(wh, sm, tid, outpos0);
             wbad = __syncthreads_or(wbad);
-            /* -- P7: delay lines: ordered gather (thread = slot) or the serial fallback -- */
+            /* -- P7: delay lines: ordered parallel scatter or the serial fallback -- */
             if (!wbad) {
-                /* slots [0, window) ahead of the reader, window <= 640: slot s >= ring_size
-                 * shares its ring cell with slot s - ring_size, which is one of the 128 slots
-                 * read (and cleared) in this fragment, and nothing older can have reached
-                 * that far ahead: its starting value is 0 */
-                float keepv[4][GATHER_K];
+                /* slots nearer than the line's shortest delay cannot be written in this
+                 * fragment: read and clear them first (this also frees the ring cells
+                 * that slots >= ring_size ahead alias with) */
 #pragma unroll
-                for (int line = 0; line < 4; ++line) {
-#pragma unroll
-                    for (int k = 0; k < GATHER_K; ++k) {
-                        const int s = tid + k * TBF_FRAGMENT;
-                        keepv[line][k] = (s < window)
-                            ? whirl_gather_slot(wh, sm, wring + line * ring_size, rmask, line, s, outpos0,
-                                                (uint32_t)s >= ring_size)
-                            : 0.0f;
+                for (int line = 0; line < 4; ++line)
+                    if (tid < wh->line_dmin[line]) {
+                        float *c = wring + line * ring_size + ((outpos0 + (uint32_t)tid) & rmask);
+                        sm.lineout[line][tid] = *c;
+                        *c = 0.0f;
                     }
+                __syncthreads();
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+#pragma unroll
+                    for (int line = 0; line < 4; ++line)
+                        whirl_tap_pass(sm, wring + line * ring_size, rmask, wh->tap_order[line][k], tid);
+                    __syncthreads();
                 }
-                __syncthreads(); /* all slots gathered before the rings change */
 #pragma unroll
-                for (int line = 0; line < 4; ++line) {
-                    sm.lineout[line][tid] = keepv[line][0];
-                    wring[line * ring_size + ((outpos0 + (uint32_t)tid) & rmask)] = 0.0f;
-                }
-                __syncthreads(); /* cells of the slots just read are clear before reuse */
-#pragma unroll
-                for (int line = 0; line < 4; ++line) {
-                    float *ring = wring + line * ring_size;
-#pragma unroll
-                    for (int k = 1; k < GATHER_K; ++k) {
-                        const int s = tid + k * TBF_FRAGMENT;
-                        if (s < window)
-                            ring[(outpos0 + (uint32_t)s) & rmask] = keepv[line][k];
+                for (int line = 0; line < 4; ++line)
+                    if (tid >= wh->line_dmin[line]) {
+                        float *c = wring + line * ring_size + ((outpos0 + (uint32_t)tid) & rmask);
+                        sm.lineout[line][tid] = *c;
+                        *c = 0.0f;
                     }
-                }
             } else {
                 if (gather_ok && tid == 0)
                     sc.errorFlags |= TBF_IFLAG_GATHER_FALLBACK;
@@ -1121,10 +1140,8 @@ tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
             }
             __syncthreads();
             /* -- P8: drum filters, one lane per channel in two different warps -- */
-            if (tid == 64)
-                drum_filter_lane(sc, wh, sm, 2);
-            else if (tid == 96)
-                drum_filter_lane(sc, wh, sm, 3);
+            if (tid == 64 || tid == 65) /* two lanes of one warp in lockstep */
+                drum_filter_lane(sc, wh, sm, 2 + (tid & 1));
             __syncthreads();
             /* -- P9: output mix -- */
             const float hl = sm.lineout[0][tid], hr = sm.lineout[1][tid];
