@@ -21,12 +21,23 @@ struct TgSet {
     float *wave = nullptr;
     uint16_t *cw = nullptr, *cb = nullptr;
     float *cl = nullptr;
+    uint16_t *rw = nullptr, *rn = nullptr; /* per-key wheel runs: wheel, entries */
 };
 struct WhSet {
     tbf_whirl_tables host;
     float *tables = nullptr; /* 4 x 16384 displacement + 2 x 16384 x 5 FIR */
     int ring_size = TBF_WHIRL_BUF, gather_ok = 0, window = 0;
 };
+
+/* Streams between the stage kernels for one chunk of fragments, [slot][chunk samples]. */
+struct StageScratch {
+    FragCtl *ctl = nullptr;
+    float *f32 = nullptr;   /* u, php, dx0, hx0, line[4]: 8 planes */
+    double *f64 = nullptr;  /* hang, dang: 2 planes */
+    size_t cap_ctl = 0, cap_f32 = 0, cap_f64 = 0;
+};
+
+#define TBF_SCAT_BLOCK 32 /* samples the kernels scatter before they read (tbf_kernels.cu BLK) */
 
 struct tbf_ctx {
     int device = 0;
@@ -59,7 +70,10 @@ struct tbf_ctx {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t render_done[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr};
     cudaEvent_t t0 = nullptr, t1 = nullptr;
-    uint64_t *d_ev_cursor = nullptr;
+    uint64_t *d_ev_cursor = nullptr; /* [2][cap_slots]: stage T, stage R */
+    StageScratch scratch;
+    size_t scratch_budget = (size_t)4 << 30; /* bytes of HBM the stage streams may take */
+    uint32_t max_stage_chunk = 64;           /* fragments per stage-kernel launch       */
     bool in_flight = false;
     int launches = 0;
     std::vector<uint64_t> ev_start_host;
@@ -121,6 +135,8 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
         cudaFree(t.cw);
         cudaFree(t.cb);
         cudaFree(t.cl);
+        cudaFree(t.rw);
+        cudaFree(t.rn);
     }
     for (auto &w : ctx->wh)
         cudaFree(w.tables);
@@ -134,6 +150,9 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     cudaFree(ctx->d_ids);
     cudaFree(ctx->d_csum);
     cudaFree(ctx->d_out);
+    cudaFree(ctx->scratch.ctl);
+    cudaFree(ctx->scratch.f32);
+    cudaFree(ctx->scratch.f64);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     for (int i = 0; i < 2; ++i) {
@@ -167,10 +186,52 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
         if (t->contrib_wheel[e] < 1 || t->contrib_wheel[e] > TBF_NOF_WHEELS ||
             t->contrib_bus[e] >= TBF_NOF_BUSES || t->wave_length[t->contrib_wheel[e]] == 0)
             return fail(ctx, TBF_ERR_ARG, "tonegen tables: contribution out of range");
+    /* the kernels keep a 256-slot window of the scanner's delay line in shared memory:
+     * every write must land inside it (offsets are (1 + A + A sin) * 65536 with A <= 9
+     * for the reference's tables, src/vibrato.cpp:249-255) */
+    for (int k = 0; k < 3; ++k)
+        for (int i = 0; i < TBF_VIB_TBL; ++i)
+            if ((t->vib_offset_table[k][i] >> 16) + TBF_SCAT_BLOCK + 2 >= TBF_VRING)
+                return fail(ctx, TBF_ERR_GEOMETRY, "tonegen tables: scanner offset beyond the 256-slot window");
+    /* wheel runs of every key's contribution list; a warp applies a key event with
+     * lane = contribution when the list is wheel-sorted with unique (wheel, bus) pairs
+     * (compilePlayMatrix builds it that way, src/tonegen.cpp:1183-1201) */
+    std::vector<uint16_t> run_wheel, run_count;
+    std::vector<uint32_t> run_start(TBF_MAX_KEYS + 1, 0);
+    bool coop = true;
+    for (int k = 0; k < TBF_MAX_KEYS; ++k) {
+        run_start[k] = (uint32_t)run_wheel.size();
+        std::vector<uint8_t> wheel_seen(TBF_NOF_WHEELS + 1, 0);
+        for (uint32_t e = t->contrib_start[k]; e < t->contrib_start[k + 1];) {
+            const uint16_t w = t->contrib_wheel[e];
+            if (wheel_seen[w])
+                coop = false; /* the wheel comes back after another one */
+            wheel_seen[w] = 1;
+            uint32_t e2 = e;
+            uint32_t bus_seen = 0;
+            while (e2 < t->contrib_start[k + 1] && t->contrib_wheel[e2] == w) {
+                if (bus_seen & (1u << t->contrib_bus[e2]))
+                    coop = false;
+                bus_seen |= 1u << t->contrib_bus[e2];
+                ++e2;
+            }
+            run_wheel.push_back(w);
+            run_count.push_back((uint16_t)(e2 - e));
+            e = e2;
+        }
+    }
+    run_start[TBF_MAX_KEYS] = (uint32_t)run_wheel.size();
+    const size_t nr = run_wheel.size();
     CK(cudaSetDevice(ctx->device));
 
     TgSet s;
     s.host = *t;
+    CK(cudaMalloc(&s.rw, sizeof(uint16_t) * std::max<size_t>(1, nr)));
+    CK(cudaMalloc(&s.rn, sizeof(uint16_t) * std::max<size_t>(1, nr)));
+    if (nr) {
+        CK(cudaMemcpy(s.rw, run_wheel.data(), sizeof(uint16_t) * nr, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(s.rn, run_count.data(), sizeof(uint16_t) * nr, cudaMemcpyHostToDevice));
+    }
     CK(cudaMalloc(&s.wave, sizeof(float) * std::max<uint64_t>(1, t->wave_total)));
     CK(cudaMalloc(&s.cw, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
     CK(cudaMalloc(&s.cb, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
@@ -190,6 +251,10 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     d->contrib_wheel = s.cw;
     d->contrib_bus = s.cb;
     d->contrib_level = s.cl;
+    d->run_wheel = s.rw;
+    d->run_count = s.rn;
+    memcpy(d->run_start, run_start.data(), sizeof(d->run_start));
+    d->coop_events = coop ? 1 : 0;
     memcpy(d->wave_offset, t->wave_offset, sizeof(d->wave_offset));
     memcpy(d->wave_length, t->wave_length, sizeof(d->wave_length));
     memcpy(d->contrib_start, t->contrib_start, sizeof(d->contrib_start));
@@ -342,8 +407,10 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
                 ok = false;
             wmax = std::max(wmax, d.tap_dmax[p]);
         }
-        d.window = wmax + 1 + TBF_FRAGMENT;
-        if (d.window >= TBF_WHIRL_BUF - TBF_FRAGMENT)
+        /* the kernels scatter 32 samples, then read them: after a block's scatter the
+         * live slots reach wmax + 32 ahead of the block's first read */
+        d.window = wmax + 1 + TBF_SCAT_BLOCK;
+        if (d.window >= TBF_WHIRL_BUF - TBF_SCAT_BLOCK)
             return fail(ctx, TBF_ERR_GEOMETRY,
                         "whirl tables: tap delays do not fit the 2048-sample delay lines");
         for (int line = 0; line < 4; ++line) {
@@ -358,17 +425,16 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
                 if (!(d.tap_dmin[t[k]] > d.tap_dmax[t[k + 1]]))
                     ok = false;
         }
-        /* A 512-slot shared ring holds a line as long as the slots that alias (>= 512 ahead
-         * of the reader) fall on cells the kernel reads and clears before it scatters:
-         * the first min(128, line_dmin) slots of the fragment. */
-        int min_line_dmin = TBF_FRAGMENT;
-        for (int line = 0; line < 4; ++line) {
-            d.line_dmin[line] = std::max(0, std::min(TBF_FRAGMENT, d.tap_dmin[d.tap_order[line][2]]));
-            min_line_dmin = std::min(min_line_dmin, d.line_dmin[line]);
-        }
-        const bool ring512 = ok && (d.window <= 512 || d.window - 512 <= min_line_dmin);
-        d.gather_ok = ring512 ? 1 : 0;
-        d.ring_size = ring512 ? 512 : TBF_WHIRL_BUF;
+        /* shared-memory ring per delay line: the smallest power of two that holds the
+         * live window; the serial path keeps the whole 2048-slot line */
+        d.gather_ok = ok ? 1 : 0;
+        d.ring_size = TBF_WHIRL_BUF;
+        if (ok)
+            for (int r = 512; r <= TBF_WHIRL_BUF; r *= 2)
+                if (d.window <= r) {
+                    d.ring_size = r;
+                    break;
+                }
         s.ring_size = d.ring_size;
         s.gather_ok = d.gather_ok;
         s.window = d.window;
@@ -398,39 +464,39 @@ static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
                           const tbf_whirl_tables &w, int whh)
 {
     memset(s, 0, sizeof(*s));
-    s->sc.newRouting = s->sc.oldRouting = t.init_routing;
-    s->sc.percSendBus = t.init_perc_send_bus;
-    s->sc.swellPedalGain = t.init_swell_pedal_gain;
-    s->sc.drawBarChange = t.init_draw_bar_change;
-    s->sc.percEnabled = t.init_perc_enabled;
-    s->sc.percTrigRestore = t.init_perc_trig_restore;
-    s->sc.percIsSoft = t.init_perc_is_soft;
-    s->sc.percIsFast = t.init_perc_is_fast;
-    s->sc.percEnvGain = 0.0f;
-    s->sc.percEnvGainReset = t.init_perc_env_gain_reset;
-    s->sc.percEnvGainDecay = t.init_perc_env_gain_decay;
-    s->sc.percDrawbarGain = t.init_perc_drawbar_gain;
-    s->sc.outputGain = 1.0f;
-    s->sc.pz = 0.0f;
-    s->sc.keyCompLevel = 1.0f; /* KEYCOMP_ZERO_LEVEL */
-    memcpy(s->sc.drawBarGain, t.init_draw_bar_gain, sizeof(s->sc.drawBarGain));
+    s->tg.newRouting = s->tg.oldRouting = t.init_routing;
+    s->tg.percSendBus = t.init_perc_send_bus;
+    s->tg.swellPedalGain = t.init_swell_pedal_gain;
+    s->tg.drawBarChange = t.init_draw_bar_change;
+    s->tg.percEnabled = t.init_perc_enabled;
+    s->tg.percTrigRestore = t.init_perc_trig_restore;
+    s->tg.percIsSoft = t.init_perc_is_soft;
+    s->tg.percIsFast = t.init_perc_is_fast;
+    s->rp.percEnvGain = 0.0f;
+    s->tg.percEnvGainReset = t.init_perc_env_gain_reset;
+    s->tg.percEnvGainDecay = t.init_perc_env_gain_decay;
+    s->tg.percDrawbarGain = t.init_perc_drawbar_gain;
+    s->tg.outputGain = 1.0f;
+    s->tg.pz = 0.0f;
+    s->rp.keyCompLevel = 1.0f; /* KEYCOMP_ZERO_LEVEL */
+    memcpy(s->tg.drawBarGain, t.init_draw_bar_gain, sizeof(s->tg.drawBarGain));
     for (int i = 0; i <= TBF_NOF_WHEELS; ++i)
         s->osc[i].aclPos = -1;
-    s->sc.vibStator = 0;
-    s->sc.vibOutPos = 0x3FF / 2; /* BUF_MASK_SAMPLES / 2, src/vibrato.cpp:294 */
-    s->sc.vibTable = t.init_vib_table;
-    s->sc.vibMixed = t.init_vib_mixed;
-    s->sc.hornAngle = w.init_horn_angle;
-    s->sc.drumAngle = w.init_drum_angle;
-    s->sc.hornIncr = w.init_horn_incr;
-    s->sc.drumIncr = w.init_drum_incr;
-    s->sc.hornTarget = w.init_horn_target;
-    s->sc.drumTarget = w.init_drum_target;
-    s->sc.hornAcDc = w.init_horn_acdc;
-    s->sc.drumAcDc = w.init_drum_acdc;
-    s->sc.revSelect = w.init_rev_select;
-    s->sc.tgTables = tgh;
-    s->sc.whTables = whh;
+    s->tg.vibStator = 0;
+    s->tg.vibOutPos = 0x3FF / 2; /* BUF_MASK_SAMPLES / 2, src/vibrato.cpp:294 */
+    s->tg.vibTable = t.init_vib_table;
+    s->tg.vibMixed = t.init_vib_mixed;
+    s->rp.hornAngle = w.init_horn_angle;
+    s->rp.drumAngle = w.init_drum_angle;
+    s->rp.hornIncr = w.init_horn_incr;
+    s->rp.drumIncr = w.init_drum_incr;
+    s->rp.hornTarget = w.init_horn_target;
+    s->rp.drumTarget = w.init_drum_target;
+    s->rp.hornAcDc = w.init_horn_acdc;
+    s->rp.drumAcDc = w.init_drum_acdc;
+    s->rp.revSelect = w.init_rev_select;
+    s->tg.tgTables = tgh;
+    s->tg.whTables = whh;
 }
 
 static int replicate(tbf_ctx *ctx, int tgh, int whh, uint32_t first, uint32_t count)
@@ -585,7 +651,7 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     if ((size_t)d->n_instances + 1 > ctx->cap_slots) {
         size_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
         CK(grow(&ctx->d_ev_start, &c0, (size_t)d->n_instances + 1));
-        CK(grow(&ctx->d_ev_cursor, &c3, (size_t)d->n_instances + 1));
+        CK(grow(&ctx->d_ev_cursor, &c3, 2 * ((size_t)d->n_instances + 1)));
         CK(grow(&ctx->d_ids, &c1, (size_t)d->n_instances + 1));
         CK(grow(&ctx->d_csum, &c2, (size_t)d->n_instances + 1));
         ctx->cap_slots = (size_t)d->n_instances + 1;
@@ -622,7 +688,16 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     return TBF_OK;
 }
 
-/* Launch the prepared batch on the library's stream (asynchronous). */
+/* bytes of stage streams per (slot, fragment): FragCtl + 8 float planes + 2 double planes */
+static size_t stream_bytes_per_fragment(bool whirl)
+{
+    const size_t planes32 = whirl ? 8 : 2, planes64 = whirl ? 2 : 0;
+    return sizeof(FragCtl) + (size_t)TBF_FRAGMENT * (4 * planes32 + 8 * planes64);
+}
+
+/* Launch the prepared batch on the library's stream (asynchronous).  Every chunk of
+ * fragments runs the four stage kernels T -> R -> W -> D (T -> R when the Leslie is
+ * bypassed for the whole batch). */
 int tbf_gpu_batch_launch(tbf_ctx *ctx)
 {
     if (!ctx || !ctx->has_prepared)
@@ -633,68 +708,115 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     const bool no_out = (d->flags & TBF_RENDER_NO_OUTPUT) != 0;
     const bool dev_out = (d->flags & TBF_RENDER_OUT_DEVICE) != 0;
     const bool host_out = !no_out && !dev_out;
+    const bool whirl = (d->flags & TBF_RENDER_WHIRL_BYPASS) == 0;
     const uint32_t chunk = ctx->prepared_chunk;
+    const size_t n = d->n_instances;
     CK(cudaSetDevice(ctx->device));
-    CK(cudaMemcpyAsync(ctx->d_ev_cursor, ctx->d_ev_start, sizeof(uint64_t) * d->n_instances,
-                       cudaMemcpyDeviceToDevice, ctx->stream));
+    uint64_t *cur_t = ctx->d_ev_cursor, *cur_r = ctx->d_ev_cursor + ctx->cap_slots;
+    CK(cudaMemcpyAsync(cur_t, ctx->d_ev_start, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(cur_r, ctx->d_ev_start, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, ctx->stream));
     if (d->checksums)
-        CK(cudaMemsetAsync(ctx->d_csum, 0, sizeof(uint64_t) * d->n_instances, ctx->stream));
+        CK(cudaMemsetAsync(ctx->d_csum, 0, sizeof(uint64_t) * n, ctx->stream));
+
+    /* stage streams: as many fragments per stage launch as the scratch budget allows */
+    uint32_t sc_frag = (uint32_t)std::min<size_t>(
+        ctx->max_stage_chunk, std::max<size_t>(1, ctx->scratch_budget / (n * stream_bytes_per_fragment(whirl))));
+    sc_frag = std::min(sc_frag, chunk);
+    const size_t pitch = (size_t)sc_frag * TBF_FRAGMENT;
+    StageScratch &ss = ctx->scratch;
+    {
+        cudaError_t e = grow(&ss.ctl, &ss.cap_ctl, n * sc_frag);
+        if (e == cudaSuccess)
+            e = grow(&ss.f32, &ss.cap_f32, n * pitch * (whirl ? 8 : 2));
+        if (e == cudaSuccess && whirl)
+            e = grow(&ss.f64, &ss.cap_f64, n * pitch * 2);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            ctx->err = "render: stage stream buffers do not fit";
+            return TBF_ERR_NOMEM;
+        }
+    }
 
     RenderParams p;
+    memset(&p, 0, sizeof(p));
     p.states = ctx->d_states;
     p.ids = ctx->prepared_has_ids ? ctx->d_ids : nullptr;
     p.tg = ctx->d_tg;
     p.wh = ctx->d_wh;
     p.events = ctx->d_events;
     p.ev_start = ctx->d_ev_start;
-    p.ev_cursor = ctx->d_ev_cursor;
+    p.ev_cursor_t = cur_t;
+    p.ev_cursor_r = cur_r;
     p.checksums = d->checksums ? ctx->d_csum : nullptr;
     p.n_instances = d->n_instances;
     p.flags = d->flags;
+    p.ctl = ss.ctl;
+    p.pitch = pitch;
+    p.u = ss.f32;
+    p.php = ss.f32 + n * pitch;
+    if (whirl) {
+        p.dx0 = ss.f32 + 2 * n * pitch;
+        p.hx0 = ss.f32 + 3 * n * pitch;
+        for (int l = 0; l < 4; ++l)
+            p.line[l] = ss.f32 + (4 + l) * n * pitch;
+        p.hang = ss.f64;
+        p.dang = ss.f64 + n * pitch;
+    }
     ctx->launches = 0;
     int ring = 512; /* shared-memory delay-line ring: the largest any table set needs */
     for (auto &w : ctx->wh)
         ring = std::max(ring, w.ring_size);
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
-    const size_t half = (size_t)2 * d->n_instances * chunk * TBF_FRAGMENT;
+    const size_t half = (size_t)2 * n * chunk * TBF_FRAGMENT;
     int k = 0;
     for (uint32_t base = 0; base < d->n_fragments; base += chunk, ++k) {
         const uint32_t nf = std::min<uint32_t>(chunk, d->n_fragments - base);
         const int buf = k & 1;
-        p.frag_base = base;
-        p.n_fragments = nf;
+        float *out_l, *out_r;
         if (host_out) {
             /* staging buffer `buf` is free once the copy issued two chunks ago is done */
             if (k >= 2)
                 CK(cudaStreamWaitEvent(ctx->stream, ctx->copy_done[buf], 0));
             p.out_stride = (uint64_t)nf * TBF_FRAGMENT;
-            p.out_l = ctx->d_out + half * buf;
-            p.out_r = p.out_l + (size_t)d->n_instances * p.out_stride;
+            out_l = ctx->d_out + half * buf;
+            out_r = out_l + n * p.out_stride;
         } else {
             p.out_stride = d->out_stride;
-            p.out_l = no_out ? nullptr : d->out_l + (size_t)base * TBF_FRAGMENT;
-            p.out_r = no_out ? nullptr : d->out_r + (size_t)base * TBF_FRAGMENT;
+            out_l = no_out ? nullptr : d->out_l + (size_t)base * TBF_FRAGMENT;
+            out_r = no_out ? nullptr : d->out_r + (size_t)base * TBF_FRAGMENT;
         }
-        int rc = tbf_launch_render(p, ring, ctx->stream);
-        if (rc != 0) {
-            ctx->err = std::string("render kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
-            return TBF_ERR_CUDA;
+        for (uint32_t ib = 0; ib < nf; ib += sc_frag) {
+            p.frag_base = base + ib;
+            p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
+            p.out_l = out_l ? out_l + (size_t)ib * TBF_FRAGMENT : nullptr;
+            p.out_r = out_r ? out_r + (size_t)ib * TBF_FRAGMENT : nullptr;
+            int rc = tbf_launch_stage_t(p, ctx->stream);
+            if (rc == 0)
+                rc = tbf_launch_stage_r(p, ctx->stream);
+            if (rc == 0 && whirl)
+                rc = tbf_launch_stage_w(p, ring, ctx->stream);
+            if (rc == 0 && whirl)
+                rc = tbf_launch_stage_d(p, ctx->stream);
+            if (rc != 0) {
+                ctx->err = std::string("stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
+                return TBF_ERR_CUDA;
+            }
+            ctx->launches += whirl ? 4 : 2;
         }
-        ctx->launches++;
         if (host_out) {
             CK(cudaEventRecord(ctx->render_done[buf], ctx->stream));
             CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->render_done[buf], 0));
             const size_t w = sizeof(float) * (size_t)nf * TBF_FRAGMENT;
             CK(cudaMemcpy2DAsync(d->out_l + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
-                                 p.out_l, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
+                                 out_l, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
             CK(cudaMemcpy2DAsync(d->out_r + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
-                                 p.out_r, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
+                                 out_r, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
             CK(cudaEventRecord(ctx->copy_done[buf], ctx->copy_stream));
         }
     }
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     if (d->checksums)
-        CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * d->n_instances,
+        CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * n,
                            cudaMemcpyDeviceToHost, ctx->stream));
     ctx->in_flight = true;
     return TBF_OK;
@@ -816,39 +938,40 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
         return TBF_ERR_CUDA;
     }
     memset(o, 0, sizeof(*o));
-    o->active_osc_l_end = s->sc.activeOscLEnd;
-    for (int i = 0; i < s->sc.activeOscLEnd && i <= TBF_NOF_WHEELS; ++i)
+    o->active_osc_l_end = s->tg.activeOscLEnd;
+    for (int i = 0; i < s->tg.activeOscLEnd && i <= TBF_NOF_WHEELS; ++i)
         o->active_osc_list[i] = s->activeOscList[i];
     for (int i = 0; i <= TBF_NOF_WHEELS; ++i) {
         o->osc_pos[i] = s->osc[i].pos;
         o->osc_acl_pos[i] = s->osc[i].aclPos;
         o->ref_count[i] = s->osc[i].refCount;
     }
-    o->old_routing = s->sc.oldRouting;
-    o->new_routing = s->sc.newRouting;
-    o->upper_key_count = s->sc.upperKeyCount;
-    o->key_down_count = s->sc.keyDownCount;
-    o->perc_env_gain = s->sc.percEnvGain;
-    o->key_comp_level = s->sc.keyCompLevel;
-    o->pz = s->sc.pz;
-    o->vib_stator = s->sc.vibStator;
-    o->vib_out_pos = s->sc.vibOutPos;
+    o->old_routing = s->tg.oldRouting;
+    o->new_routing = s->tg.newRouting;
+    o->upper_key_count = s->tg.upperKeyCount;
+    o->key_down_count = s->tg.keyDownCount;
+    o->perc_env_gain = s->rp.percEnvGain;
+    o->key_comp_level = s->rp.keyCompLevel;
+    o->pz = s->tg.pz;
+    o->vib_stator = s->tg.vibStator;
+    o->vib_out_pos = s->tg.vibOutPos;
     memcpy(o->vib_buffer, s->vibBuffer, sizeof(o->vib_buffer));
-    o->whirl_outpos = s->sc.outpos;
-    o->horn_angle = s->sc.hornAngle;
-    o->drum_angle = s->sc.drumAngle;
-    o->horn_incr = s->sc.hornIncr;
-    o->drum_incr = s->sc.drumIncr;
-    o->horn_acdc = s->sc.hornAcDc;
-    o->drum_acdc = s->sc.drumAcDc;
+    o->whirl_outpos = s->wl.outpos;
+    o->horn_angle = s->rp.hornAngle;
+    o->drum_angle = s->rp.drumAngle;
+    o->horn_incr = s->rp.hornIncr;
+    o->drum_incr = s->rp.drumIncr;
+    o->horn_acdc = s->rp.hornAcDc;
+    o->drum_acdc = s->rp.drumAcDc;
     memcpy(o->whirl_buf, s->wbuf, sizeof(o->whirl_buf));
-    memcpy(o->iir_z, s->sc.iirz, sizeof(o->iir_z));
-    memcpy(o->filt_z, s->sc.z, sizeof(o->filt_z));
-    memcpy(o->adx, s->sc.adx, sizeof(o->adx));
-    memcpy(o->adi, s->sc.adi, sizeof(o->adi));
-    o->error_flags = s->sc.errorFlags;
-    o->stat_fragments = s->sc.statFragments;
-    o->stat_active_wheels = s->sc.statActiveWheels;
+    memcpy(o->iir_z[0], s->rp.iirz, sizeof(s->rp.iirz));
+    memcpy(o->iir_z[2], s->dr.iirz, sizeof(s->dr.iirz));
+    memcpy(o->filt_z, s->wl.z, sizeof(o->filt_z));
+    memcpy(o->adx, s->wl.adx, sizeof(o->adx));
+    memcpy(o->adi, s->wl.adi, sizeof(o->adi));
+    o->error_flags = s->tg.errorFlags | s->rp.errorFlags | s->wl.errorFlags;
+    o->stat_fragments = s->tg.statFragments;
+    o->stat_active_wheels = s->tg.statActiveWheels;
     delete s;
     return TBF_OK;
 }

@@ -1,17 +1,23 @@
 /* Device-side data layout shared by the kernels and the C-ABI host code.
  *
- * Per-instance run-time state is one flat POD blob in HBM (array of structs:
- * one CTA owns one instance, so its threads read consecutive words of one
- * blob).  Field meanings follow struct b_tonegen (reference src/tonegen.h:176-563),
- * struct b_vibrato (src/vibrato.h:42-68) and struct b_whirl (src/whirl.h:65-221).
+ * Per-instance run-time state is one flat POD blob in HBM.  Field meanings follow
+ * struct b_tonegen (reference src/tonegen.h:176-563), struct b_vibrato
+ * (src/vibrato.h:42-68) and struct b_whirl (src/whirl.h:65-221).
+ *
+ * The path runs as four stage kernels per chunk of fragments (tbf_kernels.cu):
+ *   T  tone generator + scanner      warp = instance, lane = 4 samples of a fragment
+ *   R  gain ramps, horn biquads,     lane = instance (the recurrences of 32 organs
+ *      rotor speed ramp + angles     advance in lockstep in one warp)
+ *   W  Leslie taps + delay lines     warp = instance, lane = sample of a 32-sample block
+ *   D  drum biquads + output mix     lane = instance, then lane = sample for the mix
+ * Every scalar of the state is owned by exactly one stage (the sub-structs below), so
+ * stages of different chunks may overlap on different streams.
  */
 #ifndef TBF_DEVICE_H
 #define TBF_DEVICE_H
 
 #include <stdint.h>
 #include "tbf_gpu.h"
-
-#define TBF_THREADS 128
 
 /* rendering flag bits, src/tonegen.cpp:124-130 */
 #define ORF_MODIFIED 0x4u
@@ -25,6 +31,9 @@
 #define RT_LOWRVIB 0x01u
 #define RT_VIB 0x03u
 
+#define TBF_VRING 256 /* shared-memory scanner ring: host checks that every offset-table
+                         entry keeps the writes inside it (tbf_api.cu)               */
+
 struct OscState {      /* struct _oscillator + the scalar part of AOTElement */
     uint32_t pos;      /* wave read position                                 */
     int32_t aclPos;    /* position in active list, -1 = not listed           */
@@ -33,10 +42,8 @@ struct OscState {      /* struct _oscillator + the scalar part of AOTElement */
     float sumUpper, sumLower, sumPedal, sumPercn, sumSwell, sumScanr;
 };
 
-/* Every scalar of the run-time state: copied to shared memory when a launch
- * starts and back when it ends, so the serial control code never waits on HBM. */
-struct InstScalars {
-    /* ---- tone generator ---- */
+/* ---- stage T: tone generator and scanner ---- */
+struct TgScalars {
     int32_t activeOscLEnd;
     uint32_t newRouting, oldRouting;
     int32_t percSendBus;
@@ -45,29 +52,46 @@ struct InstScalars {
     float swellPedalGain;
     uint32_t drawBarChange;
     int32_t percEnabled, percTrigRestore, percIsSoft, percIsFast;
-    float percEnvGain, percEnvGainReset, percEnvGainDecay, percDrawbarGain;
-    float outputGain, pz, keyCompLevel;
+    float percEnvGainReset, percEnvGainDecay, percDrawbarGain;
+    float outputGain, pz;
     float drawBarGain[TBF_NOF_BUSES];
-    /* ---- scanner vibrato ---- */
     uint32_t vibStator, vibOutPos;
     int32_t vibTable, vibMixed;
-    /* ---- whirl ---- */
+    uint32_t errorFlags;
+    int32_t tgTables, whTables; /* read-only after create; every stage reads them */
+    uint32_t pad_;
+    unsigned long long statFragments, statActiveWheels;
+};
+
+/* ---- stage R: percussion / key-compression ramps, horn filters, rotors ---- */
+struct RampScalars {
+    float percEnvGain, keyCompLevel;
+    float iirz[2][2]; /* hafw hbfw : z0 z1 */
     int32_t hornAcDc, drumAcDc, revSelect;
-    uint32_t outpos;
+    uint32_t errorFlags;
     double hornAngle, drumAngle, hornIncr, drumIncr, hornTarget, drumTarget;
+};
+
+/* ---- stage W: Leslie reflections, taps, delay lines ---- */
+struct WhirlScalars {
+    uint32_t outpos;
+    uint32_t errorFlags;
     float z[4];
-    float iirz[4][2]; /* hafw hbfw drfL drfR : z0 z1 */
     float adx[3][8];
     int32_t adi[3];
-    /* ---- bookkeeping ---- */
-    uint32_t errorFlags;
-    int32_t tgTables, whTables;
     uint32_t pad_;
-    unsigned long long statFragments, statActiveWheels; /* fragments rendered, sum of active-list lengths */
+};
+
+/* ---- stage D: drum filters ---- */
+struct DrumScalars {
+    float iirz[2][2]; /* drfL drfR : z0 z1 */
 };
 
 struct InstState {
-    InstScalars sc;
+    TgScalars tg;
+    RampScalars rp;
+    WhirlScalars wl;
+    DrumScalars dr;
     int32_t activeOscList[TBF_NOF_WHEELS + 1];
     uint8_t activeKeys[TBF_MAX_KEYS];
     OscState osc[TBF_NOF_WHEELS + 1];
@@ -82,6 +106,12 @@ struct DevTonegenTables {
     const uint16_t *contrib_wheel;
     const uint16_t *contrib_bus;
     const float *contrib_level;
+    /* per key: runs of contributions to one wheel, (wheel, entries) in list order; lets a
+     * warp apply a key event with lane = contribution / lane = wheel */
+    const uint16_t *run_wheel;
+    const uint16_t *run_count;
+    uint32_t run_start[TBF_MAX_KEYS + 1];
+    int32_t coop_events; /* 1: every key's list is wheel-sorted with unique (wheel, bus) pairs */
     uint32_t wave_offset[TBF_NOF_WHEELS + 1];
     uint32_t wave_length[TBF_NOF_WHEELS + 1];
     uint32_t contrib_start[TBF_MAX_KEYS + 1];
@@ -117,14 +147,26 @@ struct DevWhirlTables {
     /* delay-line geometry derived from the tables on the host (tbf_api.cu):
      * every tap writes `delay` slots ahead of the reader with
      * tap_dmin <= delay <= tap_dmax (secondary slot included) */
-    int32_t ring_size;      /* 512 or 2048: shared-memory ring per delay line          */
+    int32_t ring_size;      /* 512, 1024 or 2048: shared-memory ring per delay line       */
     int32_t gather_ok;      /* 1: the three taps of every line have disjoint delay ranges,
-                               so the ordered scatter can be evaluated as a parallel gather */
-    int32_t window;         /* slots ahead of the reader that can be non-zero, + 128    */
+                               so the ordered scatter can be evaluated in parallel passes  */
+    int32_t window;         /* slots ahead of the reader that can be non-zero after a
+                               32-sample block has been scattered                         */
     int32_t tap_order[4][3];/* per line HL HR DL DR: tap ids (0..11), farthest delay first */
     int32_t tap_dmin[12], tap_dmax[12];
-    int32_t line_dmin[4];   /* per line: slots nearer than this cannot be written in a fragment */
 };
+
+/* what stage T hands to stage R for every (slot, fragment) */
+struct __align__(16) FragCtl {
+    float key_comp;  /* keyCompTable[keyDownCount]                           */
+    float gain;      /* swellPedalGain * percDrawbarGain, or swellPedalGain   */
+    float decay;     /* percEnvGainDecay                                     */
+    float reset;     /* percEnvGainReset                                     */
+    uint32_t flags;  /* FC_*                                                 */
+    uint32_t pad_[3];
+};
+#define FC_PERC_ON 0x1u     /* RT_PERC routed: percussion term + decay         */
+#define FC_PERC_RESET 0x2u  /* no upper key down at the end of the fragment    */
 
 struct RenderParams {
     InstState *states;
@@ -133,16 +175,28 @@ struct RenderParams {
     const DevWhirlTables *wh;
     const tbf_event *events;
     const uint64_t *ev_start;  /* [n_instances + 1] */
-    uint64_t *ev_cursor;       /* [n_instances]: next unapplied event, carried over chunks */
+    uint64_t *ev_cursor_t;     /* [n_instances]: next unapplied event of stage T, over chunks */
+    uint64_t *ev_cursor_r;     /* same for stage R (it applies the rotor-speed events)        */
     float *out_l, *out_r;
     unsigned long long *checksums; /* [n_instances] or NULL */
     uint64_t out_stride;
     uint32_t n_instances, n_fragments, flags;
     uint32_t frag_base;        /* batch fragment index of this launch's fragment 0 */
+    /* stage-to-stage streams of this chunk, [slot][pitch] floats (doubles for angles) */
+    FragCtl *ctl;              /* [slot][n_fragments]                                   */
+    float *u, *php;            /* T -> R: swell (+ scanner) sum, percussion high-pass   */
+    float *dx0, *hx0;          /* R -> W: whirl input, horn-filter output                */
+    double *hang, *dang;       /* R -> W: rotor angles                                  */
+    float *line[4];            /* W -> D: delay-line reads HL HR DL DR                  */
+    uint64_t pitch;            /* elements per slot row of every stream                 */
 };
 
-size_t tbf_render_smem_bytes(int ring_size);
-int tbf_launch_render(const RenderParams &p, int ring_size, void *stream);
+size_t tbf_stage_t_smem(void);
+size_t tbf_stage_w_smem(int ring_size);
+int tbf_launch_stage_t(const RenderParams &p, void *stream);
+int tbf_launch_stage_r(const RenderParams &p, void *stream);
+int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream);
+int tbf_launch_stage_d(const RenderParams &p, void *stream);
 int tbf_launch_replicate(InstState *states, uint32_t first, uint32_t count, const InstState *dev_tmpl,
                          void *stream);
 

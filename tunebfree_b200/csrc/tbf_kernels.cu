@@ -1,22 +1,27 @@
 /* tbf_kernels.cu -- sm_100a kernels for the tonewheel -> scanner -> Leslie path.
  *
- * One CTA of 128 threads owns one organ instance for a whole batch of
- * fragments.  Thread n is sample n of the 128-sample fragment for every stage
- * without a recurrence: the additive wheel sum, envelopes, percussion
- * high-pass, the Leslie tap geometry + 5-tap FIRs and the output mixes.  The
- * reference's two scatter-add delay structures (scanner ring, four Leslie delay
- * lines) are evaluated as ORDERED GATHERS, thread = destination slot, adding
- * the contributions in exactly the order the reference's sample loop does.
- * Only the true recurrences stay on single lanes, spread over different warps
- * so they overlap: four biquads, two rotor angles, the percussion / key
- * compression ramps and the control-event bookkeeping.
- * Per-instance scalars and the live window of every delay line sit in shared
- * memory for the whole launch.
+ * The per-fragment chain oscGenerateFragment -> vibratoProc -> whirlProc2/3 is a feed-
+ * forward pipeline whose recurrences all stay inside one stage, so it runs as four
+ * kernels per chunk of fragments, each with the thread layout its stage wants:
  *
- * Numerics contract: bit-exact float/double arithmetic in the
- * reference's source operation order.  This file is compiled with
- * -fmad=false -ftz=false -prec-div=true -prec-sqrt=true; no FMA contraction,
- * no re-association, denormals kept.
+ *   stage T (warp = instance, lane = samples lane, lane+32, lane+64, lane+96 of a fragment)
+ *       control events, active-list pass, additive wheel sum, scanner vibrato (ordered
+ *       two-point scatter), percussion high-pass           -> u, php, per-fragment FragCtl
+ *   stage R (lane = instance: 32 organs advance in lockstep in one warp)
+ *       percussion decay / key-compression chase, mixdown, horn biquads A and B, rotor
+ *       speed ramp + angle recurrence in double            -> dx0, hx0, hang, dang
+ *   stage W (warp = instance, lane = sample of a 32-sample block)
+ *       reflection filters (double islands), tap geometry, 5-tap FIRs, ordered scatter
+ *       into the four delay lines held in shared memory    -> raw reads of HL HR DL DR
+ *   stage D (lane = instance for the drum biquads, lane = sample for the mix)
+ *       drum biquads, horn level + leak, whirlProc / whirlProc3 mix -> out_l, out_r
+ *
+ * The streams between stages live in HBM as [slot][sample]; lane = instance stages
+ * transpose 32 x 32 tiles through shared memory so every global access is coalesced.
+ *
+ * Numerics contract: bit-exact float/double arithmetic in the reference's
+ * source operation order.  This file is compiled with -fmad=false -ftz=false
+ * -prec-div=true -prec-sqrt=true; no FMA contraction, no re-association, denormals kept.
  *
  * Reference functions restated here (never copied):
  *   oscKeyOn/oscKeyOff          src/tonegen.cpp:3096-3166
@@ -33,51 +38,17 @@
 #include "tbf_device.h"
 
 #define DISPLC_MASK (TBF_WHIRL_DISPLC - 1)
-#define GLOBAL_WBUF_MASK (TBF_WHIRL_BUF - 1)
-#define VRING 256            /* shared-memory scanner ring: writes land <= 27 slots ahead */
-#define VRING_MASK (VRING - 1)
-#define VWINDOW (TBF_FRAGMENT + 100)
+#define WBUF_MASK (TBF_WHIRL_BUF - 1)
+#define VBUF_MASK (TBF_VIB_BUF - 1)
+#define VRING_MASK (TBF_VRING - 1)
+#define FULL 0xFFFFFFFFu
+#define BLK 32 /* samples per scatter block = one per lane */
+#define TILE_PITCH 33
+
+#define T_WARPS 4
+#define W_WARPS 4
 
 namespace {
-
-/* One entry of the per-fragment "core program": the reference emits 1-2 CoreIns
- * per active wheel (src/tonegen.h:114-129); since every thread is one sample, the
- * wrap split collapses into a modular index and one record per wheel suffices. */
-struct CoreRec {
-    uint32_t wave_off;
-    uint32_t len;
-    uint32_t pos;
-    int32_t env; /* -1: plain gain; 0..7 attack row; 8..15 release row */
-    float gs, gv, gp;
-    float ds, dv, dp;
-};
-
-struct __align__(16) Smem {
-    InstScalars sc;
-    CoreRec rec[TBF_NOF_WHEELS + 1];
-    uint8_t removed[TBF_NOF_WHEELS + 3];
-    uint16_t removed_wheel[TBF_NOF_WHEELS + 1];
-    float vib_in[TBF_FRAGMENT], prc[TBF_FRAGMENT];
-    float pg[TBF_FRAGMENT], kc[TBF_FRAGMENT], mono[TBF_FRAGMENT];
-    /* scanner: per-sample contributions, inverse slot map, ring */
-    float va[TBF_FRAGMENT], vb[TBF_FRAGMENT], vib_y[TBF_FRAGMENT];
-    uint16_t vh[TBF_FRAGMENT];
-    uint8_t vfirst[VRING];
-    float vring[VRING];
-    /* whirl */
-    double hang[TBF_FRAGMENT], dang[TBF_FRAGMENT];
-    float hx[3][8 + TBF_FRAGMENT]; /* horn stage inputs with 8 samples of history */
-    float dx[3][1 + TBF_FRAGMENT]; /* drum stage inputs with 1 sample of history  */
-    float leak[TBF_FRAGMENT];
-    uint16_t tapn[12][TBF_FRAGMENT]; /* destination slot of the tap's main part (ring index) */
-    float tapa[12][TBF_FRAGMENT], tapb[12][TBF_FRAGMENT];
-    float lineout[4][TBF_FRAGMENT];  /* HL HR raw reads, DL DR after the drum biquad */
-    unsigned long long csum;
-    int n_rec, n_ins, recompute_routing, draw_bar_change, vib_on, perc_on;
-    float key_comp_delta;
-    float zs[4]; /* FILTER_C states z[0..3], NaN-scrubbed per fragment */
-    /* followed by float wring[4][ring_size]: the Leslie delay lines */
-};
 
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x)
 {
@@ -87,32 +58,93 @@ __device__ __forceinline__ unsigned long long mix64(unsigned long long x)
     return x ^ (x >> 31);
 }
 
+/* position-keyed additive hash of one stereo sample (order independent) */
+__device__ __forceinline__ unsigned long long sample_hash(uint32_t pos, float l, float r)
+{
+    return mix64(((unsigned long long)pos << 32) | __float_as_uint(l)) +
+           mix64((((unsigned long long)pos << 32) | __float_as_uint(r)) ^ 0x5555555555555555ull);
+}
+
 /* x86 semantics of `(unsigned int)f` for the float->unsigned casts of
  * src/whirl.cpp:56-58: gcc converts through a 64-bit signed integer and keeps
  * the low 32 bits (CUDA's direct cast would saturate negatives to 0). */
 __device__ __forceinline__ unsigned f2u_x86(float f) { return (unsigned)(long long)f; }
 
 /* ------------------------------------------------------------------ */
-/* control events: thread 0 only                                       */
+/* Ordered two-point scatter of one 32-sample block, lane = sample.     */
+/* Sample i adds a[i] to slot n[i] and b[i] to slot n[i]+1 (scanner:    */
+/* src/vibrato.cpp:389-390; Leslie taps: src/whirl.cpp:1448-1451).      */
+/* Because n[] never decreases inside the block, the samples hitting a  */
+/* slot form a contiguous run and the reference's sample loop adds to   */
+/* slot S first the b-parts of the run that hit S-1, then the a-parts   */
+/* of the run that hits S.  The first sample of each run applies        */
+/* exactly that sequence; a slot that only receives b-parts (the next   */
+/* run skips it, or the block ends) is completed by the last sample of  */
+/* the run before.  Distinct lanes own distinct slots: no atomics.      */
 /* ------------------------------------------------------------------ */
-
-__device__ void key_off(InstScalars &sc, InstState *st, const DevTonegenTables *tg, int key)
+__device__ __forceinline__ void ordered_pass(const uint16_t *n, const float *a, const float *b,
+                                             float *ring, uint32_t rmask, uint32_t smask, int i)
 {
-    if (key < 0 || key >= TBF_MAX_KEYS)
-        return;
-    if (!st->activeKeys[key])
-        return;
-    st->activeKeys[key] = 0;
-    if (key < 128)
-        sc.upperKeyCount--;
-    sc.keyDownCount--;
+    const uint32_t ni = n[i];
+    const uint32_t prev = i ? (uint32_t)n[i - 1] : 0xFFFFFFFFu;
+    const uint32_t next = (i < BLK - 1) ? (uint32_t)n[i + 1] : 0xFFFFFFFFu;
+    if (ni != prev) { /* first sample of the run hitting slot ni */
+        float v = ring[ni & rmask];
+        const uint32_t sm1 = (ni - 1) & smask;
+        int j0 = i;
+        while (j0 > 0 && n[j0 - 1] == sm1)
+            --j0;
+        for (int j = j0; j < i; ++j)
+            v = __fadd_rn(v, b[j]);
+        for (int m = i; m < BLK && n[m] == ni; ++m)
+            v = __fadd_rn(v, a[m]);
+        ring[ni & rmask] = v;
+    }
+    if (ni != next) { /* last sample of its run */
+        const uint32_t sp1 = (ni + 1) & smask;
+        if (next != sp1) { /* nobody hits ni+1 as a main slot in this block */
+            float v = ring[sp1 & rmask];
+            int j0 = i;
+            while (j0 > 0 && n[j0 - 1] == ni)
+                --j0;
+            for (int j = j0; j <= i; ++j)
+                v = __fadd_rn(v, b[j]);
+            ring[sp1 & rmask] = v;
+        }
+    }
+}
+
+/* ================================================================== */
+/* stage T: tone generator + scanner                                   */
+/* ================================================================== */
+
+/* One entry of the per-fragment "core program": the reference emits 1-2 CoreIns per
+ * active wheel (src/tonegen.h:114-129); with a modular index the wrap split collapses
+ * and one record per wheel suffices. */
+struct TWarp {
+    TgScalars sc;
+    int4 recA[TBF_NOF_WHEELS + 1];   /* wave_off, len, pos, env (-1 plain, 0..7 attack, 8..15 release) */
+    float4 recB[TBF_NOF_WHEELS + 1]; /* gs gv gp ds */
+    float2 recC[TBF_NOF_WHEELS + 1]; /* dv dp */
+    float vring[TBF_VRING];
+    float va[BLK], vb[BLK], vy[BLK];
+    uint16_t vn[BLK];
+    uint16_t removed_wheel[TBF_NOF_WHEELS + 1];
+    uint8_t removed[TBF_NOF_WHEELS + 3];
+    int n_rec, n_ins, recompute_routing, draw_bar_change, vib_on, perc_on;
+};
+
+/* -- key events, one lane (src/tonegen.cpp:3096-3166 + the queue drain :3257-3327): the
+ *    fallback when a key's contribution list is not wheel-sorted with unique pairs -- */
+__device__ void key_off_serial(TgScalars &sc, InstState *st, const DevTonegenTables *tg, int key)
+{
     const uint32_t e0 = tg->contrib_start[key], e1 = tg->contrib_start[key + 1];
     for (uint32_t e = e0; e < e1; ++e) {
         const int w = tg->contrib_wheel[e];
         const int b = tg->contrib_bus[e];
         OscState *o = &st->osc[w];
         float *bl = &st->busLevel[w * TBF_NOF_BUSES + b];
-        *bl = *bl - tg->contrib_level[e];
+        *bl = __fsub_rn(*bl, tg->contrib_level[e]);
         o->refCount -= 1;
         if (o->refCount == 0)
             o->rflags = OR_REM;
@@ -121,16 +153,8 @@ __device__ void key_off(InstScalars &sc, InstState *st, const DevTonegenTables *
     }
 }
 
-__device__ void key_on(InstScalars &sc, InstState *st, const DevTonegenTables *tg, int key)
+__device__ void key_on_serial(TgScalars &sc, InstState *st, const DevTonegenTables *tg, int key)
 {
-    if (key < 0 || key >= TBF_MAX_KEYS)
-        return;
-    if (st->activeKeys[key])
-        key_off(sc, st, tg, key);
-    st->activeKeys[key] = 1;
-    if (key < 128)
-        sc.upperKeyCount++;
-    sc.keyDownCount++;
     const uint32_t e0 = tg->contrib_start[key], e1 = tg->contrib_start[key + 1];
     for (uint32_t e = e0; e < e1; ++e) {
         const int w = tg->contrib_wheel[e];
@@ -146,12 +170,105 @@ __device__ void key_on(InstScalars &sc, InstState *st, const DevTonegenTables *t
             o->rflags |= ORF_MODIFIED;
         }
         float *bl = &st->busLevel[w * TBF_NOF_BUSES + b];
-        *bl = *bl + tg->contrib_level[e];
+        *bl = __fadd_rn(*bl, tg->contrib_level[e]);
         o->refCount += 1;
     }
 }
 
-__device__ void perc_resets(InstScalars &sc, const DevTonegenTables *tg)
+/* -- key events, whole warp: lane = contribution for the bus levels (every (wheel, bus)
+ *    cell of one key is distinct), lane = wheel run for the reference counts, flags and
+ *    the order-preserving append to the active list -- */
+__device__ void key_off_warp(TWarp &sm, InstState *st, const DevTonegenTables *tg, int key, int lane)
+{
+    TgScalars &sc = sm.sc;
+    if (lane == 0) {
+        st->activeKeys[key] = 0;
+        if (key < 128)
+            sc.upperKeyCount--;
+        sc.keyDownCount--;
+    }
+    if (!tg->coop_events) {
+        if (lane == 0)
+            key_off_serial(sc, st, tg, key);
+        __syncwarp();
+        return;
+    }
+    const uint32_t e0 = tg->contrib_start[key], e1 = tg->contrib_start[key + 1];
+    for (uint32_t e = e0 + lane; e < e1; e += 32) {
+        float *bl = &st->busLevel[(int)tg->contrib_wheel[e] * TBF_NOF_BUSES + (int)tg->contrib_bus[e]];
+        *bl = __fsub_rn(*bl, tg->contrib_level[e]);
+    }
+    const uint32_t r0 = tg->run_start[key], r1 = tg->run_start[key + 1];
+    for (uint32_t r = r0 + lane; r < r1; r += 32) {
+        OscState *o = &st->osc[tg->run_wheel[r]];
+        const int rc = o->refCount - (int)tg->run_count[r];
+        o->refCount = rc;
+        if (rc == 0)
+            o->rflags = OR_REM;
+        else
+            o->rflags |= ORF_MODIFIED;
+    }
+    __syncwarp();
+}
+
+__device__ void key_on_warp(TWarp &sm, InstState *st, const DevTonegenTables *tg, int key, int lane)
+{
+    TgScalars &sc = sm.sc;
+    if (st->activeKeys[key]) /* re-striking a held key: off, then on (src/tonegen.cpp:3139-3142) */
+        key_off_warp(sm, st, tg, key, lane);
+    if (lane == 0) {
+        st->activeKeys[key] = 1;
+        if (key < 128)
+            sc.upperKeyCount++;
+        sc.keyDownCount++;
+    }
+    if (!tg->coop_events) {
+        if (lane == 0)
+            key_on_serial(sc, st, tg, key);
+        __syncwarp();
+        return;
+    }
+    const uint32_t e0 = tg->contrib_start[key], e1 = tg->contrib_start[key + 1];
+    for (uint32_t e = e0 + lane; e < e1; e += 32) {
+        float *bl = &st->busLevel[(int)tg->contrib_wheel[e] * TBF_NOF_BUSES + (int)tg->contrib_bus[e]];
+        *bl = __fadd_rn(*bl, tg->contrib_level[e]);
+    }
+    const uint32_t r0 = tg->run_start[key], r1 = tg->run_start[key + 1];
+    int l_end = sc.activeOscLEnd; /* uniform */
+    for (uint32_t base = r0; base < r1; base += 32) {
+        const uint32_t r = base + lane;
+        const bool valid = r < r1;
+        int w = 0, rc = 1;
+        bool append = false;
+        if (valid) {
+            w = tg->run_wheel[r];
+            rc = st->osc[w].refCount;
+            append = (rc == 0) && (st->osc[w].aclPos == -1);
+        }
+        const unsigned am = __ballot_sync(FULL, append);
+        if (valid) {
+            OscState *o = &st->osc[w];
+            if (rc == 0) {
+                o->rflags = OR_ADD;
+                if (append) {
+                    const int pos = l_end + __popc(am & ((1u << lane) - 1u));
+                    o->aclPos = pos;
+                    st->activeOscList[pos] = w;
+                }
+            } else {
+                o->rflags |= ORF_MODIFIED;
+            }
+            o->refCount = rc + (int)tg->run_count[r];
+        }
+        l_end += __popc(am);
+    }
+    __syncwarp();
+    if (lane == 0)
+        sc.activeOscLEnd = l_end;
+    __syncwarp();
+}
+
+__device__ void perc_resets(TgScalars &sc, const DevTonegenTables *tg)
 {
     if (sc.percIsFast)
         sc.percEnvGainDecay = sc.percIsSoft ? tg->perc_decay_fast_soft : tg->perc_decay_fast_norm;
@@ -159,36 +276,11 @@ __device__ void perc_resets(InstScalars &sc, const DevTonegenTables *tg)
         sc.percEnvGainDecay = sc.percIsSoft ? tg->perc_decay_slow_soft : tg->perc_decay_slow_norm;
 }
 
-__device__ void use_rev_option(InstScalars &sc, const DevWhirlTables *wh, int n, int signals)
+/* setters of the tone generator and the scanner, one lane */
+__device__ void apply_scalar_event(TgScalars &sc, const DevTonegenTables *tg, const int type,
+                                   const int a, const int b)
 {
-    const int i = n % 9;
-    sc.hornTarget = wh->rev_horn_target[i];
-    sc.drumTarget = wh->rev_drum_target[i];
-    if (sc.hornIncr < sc.hornTarget)
-        sc.hornAcDc = 1;
-    else if (sc.hornTarget < sc.hornIncr)
-        sc.hornAcDc = -1;
-    if (sc.drumIncr < sc.drumTarget)
-        sc.drumAcDc = 1;
-    else if (sc.drumTarget < sc.drumIncr)
-        sc.drumAcDc = -1;
-    if (signals & 2) {
-        const int hr = (n / 3) % 3;
-        sc.revSelect = (hr == 2) ? 2 : (hr == 1) ? 0 : 1; /* WHIRL_FAST / SLOW / STOP */
-    }
-}
-
-__device__ void apply_event(InstScalars &sc, InstState *st, const DevTonegenTables *tg,
-                            const DevWhirlTables *wh, const tbf_event &ev)
-{
-    const int a = ev.a, b = ev.b;
-    switch (ev.type) {
-    case TBF_EV_KEY_ON:
-        key_on(sc, st, tg, a);
-        break;
-    case TBF_EV_KEY_OFF:
-        key_off(sc, st, tg, a);
-        break;
+    switch (type) {
     case TBF_EV_DRAWBAR:
         if (a < 0 || a >= TBF_NOF_BUSES || b < 0 || b >= 9) { /* reference asserts */
             sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
@@ -251,75 +343,59 @@ __device__ void apply_event(InstScalars &sc, InstState *st, const DevTonegenTabl
             sc.vibMixed = (a & 1) ? 0x80 : 0;
         }
         break;
-    case TBF_EV_REV_OPTION:
-        if (a < 0) {
-            sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
-            break;
-        }
-        use_rev_option(sc, wh, a, 2);
-        break;
-    case TBF_EV_REV_SELECT:
-        if (a < 0) {
-            sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
-            break;
-        }
-        sc.revSelect = a % 3;
-        use_rev_option(sc, wh, wh->revselects[sc.revSelect], 1);
-        break;
     case TBF_EV_SWELL:
         sc.swellPedalGain =
             (float)(((double)tg->output_level_trim * (double)(unsigned char)a) / 127.0);
         break;
+    case TBF_EV_REV_OPTION:
+    case TBF_EV_REV_SELECT:
+        break; /* rotor speed events belong to stage R */
     default:
         sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
         break;
     }
 }
 
-/* ------------------------------------------------------------------ */
-/* tone generator: active-list pass (src/tonegen.cpp:3333-3594)        */
-/* ------------------------------------------------------------------ */
-
-/* Entry i of the active list is independent of every other entry (it touches
- * only its own wheel's state), so thread i handles entries i, i+128, ... */
-__device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem &sm, int tid)
+/* active-list pass (src/tonegen.cpp:3333-3594).  Entry i of the active list touches only
+ * its own wheel's state, so lane l handles entries l, l+32, ... */
+__device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, TWarp &sm, int lane)
 {
-    InstScalars &sc = sm.sc;
+    TgScalars &sc = sm.sc;
     const int n_act = sc.activeOscLEnd;
-    const uint32_t routing = sc.oldRouting; /* already updated by thread 0 */
+    const uint32_t routing = sc.oldRouting; /* already updated by lane 0 */
     const bool recompute_routing = sm.recompute_routing != 0;
     const bool draw_bar_change = sm.draw_bar_change != 0;
     int my_ins = 0;
     int any_removed = 0;
 
-    for (int i = tid; i < n_act; i += TBF_THREADS) {
+    for (int i = lane; i < n_act; i += 32) {
         const int w = st->activeOscList[i];
         OscState *o = &st->osc[w];
         const uint32_t rflags = o->rflags;
-        CoreRec r;
-        r.wave_off = tg->wave_offset[w];
-        r.len = tg->wave_length[w];
-        r.pos = o->pos;
+        const uint32_t len = tg->wave_length[w];
+        const uint32_t pos = o->pos;
+        int env;
+        float gs, gv, gp, ds, dv, dp;
 
         if (rflags & ORF_REMOVED) {
             sm.removed[i] = 1;
             any_removed = 1;
-            r.env = 8 + (i & 7);
-            r.gs = o->sumSwell;
-            r.gp = o->sumPercn;
-            r.gv = o->sumScanr;
-            r.ds = __fsub_rn(0.0f, r.gs);
-            r.dp = __fsub_rn(0.0f, r.gp);
-            r.dv = __fsub_rn(0.0f, r.gv);
+            env = 8 + (i & 7);
+            gs = o->sumSwell;
+            gp = o->sumPercn;
+            gv = o->sumScanr;
+            ds = __fsub_rn(0.0f, gs);
+            dp = __fsub_rn(0.0f, gp);
+            dv = __fsub_rn(0.0f, gv);
         } else {
             sm.removed[i] = 0;
             bool reroute = false;
             if (rflags & ORF_ADDED) {
-                r.gs = r.gp = r.gv = 0.0f;
+                gs = gp = gv = 0.0f;
             } else {
-                r.gs = o->sumSwell;
-                r.gp = o->sumPercn;
-                r.gv = o->sumScanr;
+                gs = o->sumSwell;
+                gp = o->sumPercn;
+                gv = o->sumScanr;
             }
             if ((rflags & ORF_MODIFIED) || draw_bar_change) {
                 const float *bl = &st->busLevel[w * TBF_NOF_BUSES];
@@ -356,45 +432,47 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem
                 o->sumSwell = swell;
             }
             if (rflags & OR_ADD) {
-                r.env = i & 7;
-                r.ds = __fsub_rn(o->sumSwell, r.gs);
-                r.dp = __fsub_rn(o->sumPercn, r.gp);
-                r.dv = __fsub_rn(o->sumScanr, r.gv);
+                env = i & 7;
+                ds = __fsub_rn(o->sumSwell, gs);
+                dp = __fsub_rn(o->sumPercn, gp);
+                dv = __fsub_rn(o->sumScanr, gv);
             } else {
-                r.env = -1;
-                r.ds = r.dp = r.dv = 0.0f;
+                env = -1;
+                ds = dp = dv = 0.0f;
             }
         }
         /* advance the read position; wrap test is `length < pos + 128`
          * (src/tonegen.cpp:3376, :3524), so pos may rest at == length */
-        if (r.len < r.pos + TBF_FRAGMENT) {
-            o->pos = TBF_FRAGMENT - (r.len - r.pos);
+        if (len < pos + TBF_FRAGMENT) {
+            o->pos = TBF_FRAGMENT - (len - pos);
             my_ins += 2;
         } else {
-            o->pos = r.pos + TBF_FRAGMENT;
+            o->pos = pos + TBF_FRAGMENT;
             my_ins += 1;
         }
         o->rflags = 0;
-        sm.rec[i] = r;
+        sm.recA[i] = make_int4((int)tg->wave_offset[w], (int)len, (int)pos, env);
+        sm.recB[i] = make_float4(gs, gv, gp, ds);
+        sm.recC[i] = make_float2(dv, dp);
     }
-    if (my_ins)
-        atomicAdd(&sm.n_ins, my_ins);
-    any_removed = __syncthreads_or(any_removed);
+    const int n_ins = __reduce_add_sync(FULL, my_ins);
+    any_removed = __any_sync(FULL, any_removed);
+    __syncwarp(); /* removed[] and the wheel state are visible to lane 0 */
 
-    if (tid == 0) {
+    if (lane == 0) {
         sm.n_rec = n_act;
         sc.statFragments += 1;
         sc.statActiveWheels += (unsigned long long)n_act;
         sc.drawBarChange = 0;
-        if (sm.n_ins > 256)
+        if (n_ins > 256)
             sc.errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
         if (any_removed) {
             /* removal list in ascending active-list index, swap-with-last
-             * (src/tonegen.cpp:3576-3594); changes the list order and with it
-             * next fragment's summation order and envelope rows */
+             * (src/tonegen.cpp:3576-3594); changes the list order and with it next
+             * fragment's summation order and envelope rows.  Victims are identified by
+             * wheel number BEFORE any swap moves entries around: the reference collects
+             * removedList[] first */
             int l_end = n_act;
-            /* victims must be identified by wheel number BEFORE any swap moves
-             * entries around: the reference collects removedList[] first */
             for (int i = 0; i < n_act; ++i)
                 if (sm.removed[i])
                     sm.removed_wheel[i] = (uint16_t)st->activeOscList[i];
@@ -416,190 +494,291 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, Smem
             sc.activeOscLEnd = l_end;
         }
     }
+    __syncwarp();
 }
 
-/* ------------------------------------------------------------------ */
-/* tone generator: core interpreter, thread = sample                   */
-/* (src/tonegen.cpp:3607-3687)                                         */
-/* ------------------------------------------------------------------ */
-__device__ __forceinline__ void core_interpreter(const DevTonegenTables *tg, const Smem &sm, int n,
-                                                 float &swl, float &vib, float &prc)
+/* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples lane + 32k */
+__device__ __forceinline__ void core_interpreter(const DevTonegenTables *tg, const TWarp &sm, int lane,
+                                                 float (&s)[4], float (&v)[4], float (&p)[4])
 {
     const int n_rec = sm.n_rec;
     const float *__restrict__ wave = tg->wave_data;
-    float s = 0.0f, v = 0.0f, p = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        s[k] = v[k] = p[k] = 0.0f;
     for (int i = 0; i < n_rec; ++i) {
-        const CoreRec &r = sm.rec[i];
-        uint32_t idx = r.pos + (uint32_t)n;
-        if (idx >= r.len)
-            idx -= r.len;
-        const float x = __ldg(wave + r.wave_off + idx);
-        float cs, cv, cp;
-        if (r.env >= 0) {
-            const float e = __ldg(&tg->env[r.env][n]);
-            cs = __fmul_rn(x, __fadd_rn(r.gs, __fmul_rn(e, r.ds)));
-            cv = __fmul_rn(x, __fadd_rn(r.gv, __fmul_rn(e, r.dv)));
-            cp = __fmul_rn(x, __fadd_rn(r.gp, __fmul_rn(e, r.dp)));
+        const int4 ra = sm.recA[i];
+        const float4 rb = sm.recB[i];
+        const uint32_t len = (uint32_t)ra.y;
+        const float *wp = wave + (uint32_t)ra.x;
+        uint32_t idx = (uint32_t)ra.z + (uint32_t)lane;
+        float x[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t j = idx + 32u * k;
+            if (j >= len)
+                j -= len;
+            x[k] = __ldg(wp + j);
+        }
+        float cs[4], cv[4], cp[4];
+        if (ra.w >= 0) {
+            const float2 rc = sm.recC[i];
+            const float *ev = tg->env[ra.w];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float e = __ldg(ev + lane + 32 * k);
+                cs[k] = __fmul_rn(x[k], __fadd_rn(rb.x, __fmul_rn(e, rb.w)));
+                cv[k] = __fmul_rn(x[k], __fadd_rn(rb.y, __fmul_rn(e, rc.x)));
+                cp[k] = __fmul_rn(x[k], __fadd_rn(rb.z, __fmul_rn(e, rc.y)));
+            }
         } else {
-            cs = __fmul_rn(x, r.gs);
-            cv = __fmul_rn(x, r.gv);
-            cp = __fmul_rn(x, r.gp);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                cs[k] = __fmul_rn(x[k], rb.x);
+                cv[k] = __fmul_rn(x[k], rb.y);
+                cp[k] = __fmul_rn(x[k], rb.z);
+            }
         }
         if (i == 0) { /* first instruction of a fragment copies, the rest add */
-            s = cs;
-            v = cv;
-            p = cp;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                s[k] = cs[k];
+                v[k] = cv[k];
+                p[k] = cp[k];
+            }
         } else {
-            s = __fadd_rn(s, cs);
-            v = __fadd_rn(v, cv);
-            p = __fadd_rn(p, cp);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                s[k] = __fadd_rn(s[k], cs[k]);
+                v[k] = __fadd_rn(v[k], cv[k]);
+                p[k] = __fadd_rn(p[k], cp[k]);
+            }
         }
     }
-    swl = s;
-    vib = v;
-    prc = p;
 }
 
-/* ------------------------------------------------------------------ */
-/* scanner vibrato (src/vibrato.cpp:365-411)                            */
-/* ------------------------------------------------------------------ */
-
-/* Per-sample part, thread = sample m.  Everything integer is closed form in m:
- * stator(m) = stator0 + m*inc, outPos(m) = outPos0 + m.  Sample m adds (x - g) to
- * slot h(m) and g to slot h(m)+1.  Returns non-zero when the gather's assumptions
- * (slots advance monotonically, stay inside the shared ring) do not hold. */
-__device__ __forceinline__ int vibrato_contrib(const InstScalars &sc, const DevTonegenTables *tg,
-                                               Smem &sm, int m, float x)
+/* scanner vibrato of one 32-sample block (src/vibrato.cpp:365-411), lane = sample.
+ * Everything integer is closed form in the sample index m: stator(m) = stator0 + m*inc,
+ * outPos(m) = outPos0 + m.  Returns y (the value read at outPos(m)). */
+__device__ __forceinline__ float vibrato_block(const DevTonegenTables *tg, TWarp &sm, int k, int lane,
+                                               float x)
 {
+    const TgScalars &sc = sm.sc;
     const float fnorm = (float)(1.0 / 65536.0);
     const uint32_t *tab = tg->vib_offset_table[sc.vibTable];
     const uint32_t inc = tg->vib_stator_increment;
-    const uint32_t stator = (sc.vibStator + (uint32_t)m * inc) & 0x07FFFFFFu;
-    const uint32_t op = (sc.vibOutPos + (uint32_t)m) & 0x3FFu;
+    const uint32_t m = (uint32_t)(BLK * k + lane);
+    const uint32_t stator = (sc.vibStator + m * inc) & 0x07FFFFFFu;
+    const uint32_t op = (sc.vibOutPos + m) & VBUF_MASK;
     const uint32_t j = ((op << 16) + __ldg(&tab[stator >> 16])) & 0x03FFFFFFu;
     const uint32_t h = j >> 16;
     const float f = __fmul_rn(fnorm, (float)(j & 0xFFFFu));
     const float g = __fmul_rn(f, x);
-    sm.va[m] = __fsub_rn(x, g);
-    sm.vb[m] = g;
-    sm.vh[m] = (uint16_t)h;
-    const uint32_t rel = (h - sc.vibOutPos) & 0x3FFu; /* slots ahead of the fragment's first read */
-    int bad = (rel < (uint32_t)m) || (rel + 1 >= (uint32_t)VWINDOW);
-    uint32_t hprev = 0xFFFFFFFFu;
-    if (m > 0) {
-        const uint32_t sp = (sc.vibStator + (uint32_t)(m - 1) * inc) & 0x07FFFFFFu;
-        const uint32_t opp = (sc.vibOutPos + (uint32_t)(m - 1)) & 0x3FFu;
-        hprev = (((opp << 16) + __ldg(&tab[sp >> 16])) & 0x03FFFFFFu) >> 16;
-        bad |= ((h - hprev) & 0x3FFu) >= 512u; /* went backwards */
-    }
-    if (!bad && h != hprev)
-        sm.vfirst[rel] = (uint8_t)m;
-    return bad;
-}
-
-/* Gather, thread = slot s ahead of the fragment's first read position.  The slot
- * collects, in sample order, the g-parts of the samples that hit slot s-1 and then
- * the (x-g)-parts of the samples that hit s -- the order the reference's loop adds
- * them in, because h(m) never decreases.  Slots s < 128 are read (and cleared) by
- * sample s after all of its contributors (they are >= 1 sample older). */
-__device__ __forceinline__ float vibrato_gather_slot(const InstScalars &sc, Smem &sm, int s)
-{
-    const uint32_t S = (sc.vibOutPos + (uint32_t)s) & 0x3FFu;
-    float v = sm.vring[S & VRING_MASK];
-    if (s > 0) {
-        const uint32_t Sm1 = (S - 1) & 0x3FFu;
-        for (int m = sm.vfirst[s - 1]; m < TBF_FRAGMENT && sm.vh[m] == Sm1; ++m)
-            v = __fadd_rn(v, sm.vb[m]);
-    }
-    for (int m = sm.vfirst[s]; m < TBF_FRAGMENT && sm.vh[m] == S; ++m)
-        v = __fadd_rn(v, sm.va[m]);
-    return v;
-}
-
-/* the reference's loop as written, one lane: fallback when the gather's
- * assumptions fail (pathological offset tables) */
-__device__ void vibrato_serial(InstScalars &sc, const DevTonegenTables *tg, Smem &sm)
-{
-    const float fnorm = (float)(1.0 / 65536.0);
-    const float mixnorm = (float)0.7071067811865475;
-    const uint32_t *tab = tg->vib_offset_table[sc.vibTable];
-    const uint32_t inc = tg->vib_stator_increment;
-    const int mixed = sc.vibMixed;
-    uint32_t stator = sc.vibStator, out_pos = sc.vibOutPos;
-    float *buf = sm.vring;
-    for (int i = 0; i < TBF_FRAGMENT; ++i) {
-        const float x = sm.vib_in[i];
-        const uint32_t j = ((out_pos << 16) + __ldg(&tab[stator >> 16])) & 0x03FFFFFFu;
-        const uint32_t h = j >> 16;
-        const uint32_t k = (h + 1) & 0x3FFu;
-        const float f = __fmul_rn(fnorm, (float)(j & 0xFFFFu));
-        const float g = __fmul_rn(f, x);
-        buf[h & VRING_MASK] = __fadd_rn(buf[h & VRING_MASK], __fsub_rn(x, g));
-        buf[k & VRING_MASK] = __fadd_rn(buf[k & VRING_MASK], g);
-        float y;
-        if (mixed)
-            y = __fmul_rn(__fadd_rn(x, buf[out_pos & VRING_MASK]), mixnorm);
-        else
-            y = buf[out_pos & VRING_MASK];
-        sm.vib_y[i] = y;
-        buf[out_pos & VRING_MASK] = 0.0f;
-        out_pos = (out_pos + 1) & 0x3FFu;
-        stator = (stator + inc) & 0x07FFFFFFu;
-    }
-}
-
-/* percussion-gain decay and key-compression chase: two scalar recurrences
- * carried across fragments (src/tonegen.cpp:3733-3771), one lane */
-__device__ void gain_ramps(InstScalars &sc, Smem &sm, bool perc_on)
-{
-    float kc = sc.keyCompLevel;
-    const float delta = sm.key_comp_delta;
-    if (perc_on) {
-        float pg = sc.percEnvGain;
-        const float decay = sc.percEnvGainDecay;
-#pragma unroll 8
-        for (int i = 0; i < TBF_FRAGMENT; ++i) {
-            sm.pg[i] = pg;
-            sm.kc[i] = kc;
-            pg = __fmul_rn(pg, decay);
-            kc = __fadd_rn(kc, delta);
-        }
-        sc.percEnvGain = pg;
+    sm.va[lane] = __fsub_rn(x, g);
+    sm.vb[lane] = g;
+    sm.vn[lane] = (uint16_t)h;
+    /* slots ahead of the block's first read; the parallel pass needs slots that never go
+     * backwards and stay ahead of (or at) their own sample's read position */
+    const uint32_t rel = (h - op + (uint32_t)lane) & VBUF_MASK;
+    int bad = (rel < (uint32_t)lane) || (rel + 1 >= (uint32_t)TBF_VRING);
+    const uint32_t hprev = __shfl_up_sync(FULL, h, 1);
+    if (lane > 0)
+        bad |= ((h - hprev) & VBUF_MASK) >= (TBF_VIB_BUF / 2);
+    bad = __any_sync(FULL, bad);
+    __syncwarp();
+    float y;
+    if (!bad) {
+        ordered_pass(sm.vn, sm.va, sm.vb, sm.vring, VRING_MASK, VBUF_MASK, lane);
+        __syncwarp();
+        y = sm.vring[op & VRING_MASK];
+        sm.vring[op & VRING_MASK] = 0.0f;
     } else {
-#pragma unroll 8
-        for (int i = 0; i < TBF_FRAGMENT; ++i) {
-            sm.kc[i] = kc;
-            kc = __fadd_rn(kc, delta);
+        /* the reference's loop as written, one lane (offset tables with backward steps) */
+        if (lane == 0) {
+            for (int i = 0; i < BLK; ++i) {
+                const uint32_t hh = sm.vn[i];
+                const uint32_t kk = (hh + 1) & VBUF_MASK;
+                const uint32_t oo = (sc.vibOutPos + (uint32_t)(BLK * k + i)) & VBUF_MASK;
+                sm.vring[hh & VRING_MASK] = __fadd_rn(sm.vring[hh & VRING_MASK], sm.va[i]);
+                sm.vring[kk & VRING_MASK] = __fadd_rn(sm.vring[kk & VRING_MASK], sm.vb[i]);
+                sm.vy[i] = sm.vring[oo & VRING_MASK];
+                sm.vring[oo & VRING_MASK] = 0.0f;
+            }
         }
+        __syncwarp();
+        y = sm.vy[lane];
     }
-    sc.keyCompLevel = kc;
+    __syncwarp();
+    return y;
 }
 
-/* ------------------------------------------------------------------ */
-/* whirl: per-call speed ramp and brake logic of ONE rotor, double      */
-/* precision, one lane (src/whirl.cpp:1219-1374; the horn and drum      */
-/* halves there differ only in the constants passed here).              */
-/* Returns non-zero when the brake is engaged (incr is zeroed after the */
-/* sample loop, src/whirl.cpp:1635-1636).                               */
-/* ------------------------------------------------------------------ */
-struct RotorConst {
-    float hardstop_rpm;  /* 10 horn, 8 drum      */
-    float brake_limit_rpm; /* 60 horn, 100 drum  */
-    int is_horn;
-};
-
-__device__ int rotor_ramp(const DevWhirlTables *wh, const RotorConst rc, int *acdc, double *incr,
-                          double *angle, const double target, const double brake_pos,
-                          const double oml_acc, const double oml_dec)
+__global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p)
 {
-    const double SR = wh->sample_rate;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t slot = blockIdx.x * T_WARPS + warp;
+    if (slot >= p.n_instances)
+        return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
+    TWarp &sm = reinterpret_cast<TWarp *>(smem_raw)[warp];
+    const uint32_t id = p.ids ? p.ids[slot] : slot;
+    InstState *st = p.states + id;
+    TgScalars &sc = sm.sc;
+
+    for (int i = lane; i < (int)(sizeof(TgScalars) / 4); i += 32)
+        reinterpret_cast<uint32_t *>(&sm.sc)[i] = reinterpret_cast<const uint32_t *>(&st->tg)[i];
+    __syncwarp();
+    const DevTonegenTables *tg = p.tg + sc.tgTables;
+    for (int s = lane; s < TBF_VRING; s += 32) {
+        const uint32_t g = (sc.vibOutPos + (uint32_t)s) & VBUF_MASK;
+        sm.vring[g & VRING_MASK] = st->vibBuffer[g];
+    }
+    uint64_t ev_cur = p.ev_cursor_t[slot];
+    const uint64_t ev_end = p.ev_start[slot + 1];
+    float *u_row = p.u + (size_t)slot * p.pitch;
+    float *php_row = p.php + (size_t)slot * p.pitch;
+    FragCtl *ctl_row = p.ctl + (size_t)slot * p.n_fragments;
+    __syncwarp();
+
+    for (uint32_t f = 0; f < p.n_fragments; ++f) {
+        /* -- control events that precede this fragment -- */
+        while (ev_cur < ev_end) {
+            const tbf_event *evp = p.events + ev_cur;
+            if (evp->fragment > p.frag_base + f)
+                break;
+            const int type = evp->type, a = evp->a, b = evp->b;
+            if (type == TBF_EV_KEY_ON || type == TBF_EV_KEY_OFF) {
+                if (a >= 0 && a < TBF_MAX_KEYS) {
+                    if (type == TBF_EV_KEY_ON)
+                        key_on_warp(sm, st, tg, a, lane);
+                    else if (st->activeKeys[a])
+                        key_off_warp(sm, st, tg, a, lane);
+                }
+            } else if (lane == 0) {
+                apply_scalar_event(sc, tg, type, a, b);
+            }
+            __syncwarp();
+            ++ev_cur;
+        }
+        /* -- routing, key compression target, what stage R needs -- */
+        if (lane == 0) {
+            int kdc = sc.keyDownCount;
+            if (kdc > 127 || kdc < 0) { /* reference reads past keyCompTable[128] */
+                sc.errorFlags |= TBF_IFLAG_KEYCOMP_OOB;
+                kdc = kdc < 0 ? 0 : 127;
+            }
+            sm.recompute_routing = (sc.oldRouting != sc.newRouting);
+            if (sm.recompute_routing)
+                sc.oldRouting = sc.newRouting;
+            sm.draw_bar_change = sc.drawBarChange;
+            sm.vib_on = (sc.oldRouting & RT_VIB) != 0;
+            sm.perc_on = (sc.oldRouting & RT_PERC) != 0;
+            FragCtl c;
+            c.key_comp = tg->key_comp_table[kdc];
+            c.gain = sm.perc_on ? __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain) : sc.swellPedalGain;
+            c.decay = sc.percEnvGainDecay;
+            c.reset = sc.percEnvGainReset;
+            c.flags = (sm.perc_on ? FC_PERC_ON : 0u) | (sc.upperKeyCount == 0 ? FC_PERC_RESET : 0u);
+            c.pad_[0] = c.pad_[1] = c.pad_[2] = 0u;
+            ctl_row[f] = c;
+        }
+        __syncwarp();
+        const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
+
+        active_list_pass(st, tg, sm, lane);
+
+        /* -- additive synthesis -- */
+        float swl[4], vib[4], prc[4];
+        core_interpreter(tg, sm, lane, swl, vib, prc);
+
+        /* -- scanner, percussion high-pass, hand-over to stage R -- */
+        const float pz = sc.pz;
+        float *u_out = u_row + (size_t)f * TBF_FRAGMENT;
+        float *php_out = php_row + (size_t)f * TBF_FRAGMENT;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float uu = swl[k];
+            if (vib_on) {
+                const float y = vibrato_block(tg, sm, k, lane, vib[k]);
+                const float vy = sc.vibMixed ? __fmul_rn(__fadd_rn(vib[k], y), (float)0.7071067811865475) : y;
+                uu = __fadd_rn(uu, vy);
+            }
+            u_out[BLK * k + lane] = uu;
+            if (perc_on) { /* in-place differencer, src/tonegen.cpp:3719-3732 */
+                float prev = __shfl_up_sync(FULL, prc[k], 1);
+                float carry = pz; /* sample -1 of the fragment */
+                if (k > 0)
+                    carry = __shfl_sync(FULL, prc[k > 0 ? k - 1 : 0], 31);
+                if (lane == 0)
+                    prev = carry;
+                php_out[BLK * k + lane] = __fsub_rn(prev, prc[k]);
+            }
+        }
+        const float prc_last = __shfl_sync(FULL, prc[3], 31);
+        if (lane == 0) {
+            if (vib_on) {
+                sc.vibStator = (sc.vibStator + TBF_FRAGMENT * tg->vib_stator_increment) & 0x07FFFFFFu;
+                sc.vibOutPos = (sc.vibOutPos + TBF_FRAGMENT) & VBUF_MASK;
+            }
+            if (perc_on) {
+                sc.outputGain = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
+                sc.pz = prc_last;
+            }
+        }
+        __syncwarp();
+    }
+
+    /* ---- write the staged state back ---- */
+    if (lane == 0)
+        p.ev_cursor_t[slot] = ev_cur;
+    for (int i = lane; i < (int)(sizeof(TgScalars) / 4); i += 32)
+        reinterpret_cast<uint32_t *>(&st->tg)[i] = reinterpret_cast<const uint32_t *>(&sm.sc)[i];
+    /* outside the live window every ring slot is zero (cleared when read) */
+    for (int s = lane; s < TBF_VIB_BUF; s += 32) {
+        const uint32_t g = (sc.vibOutPos + (uint32_t)s) & VBUF_MASK;
+        st->vibBuffer[g] = (s < TBF_VRING) ? sm.vring[g & VRING_MASK] : 0.0f;
+    }
+}
+
+/* ================================================================== */
+/* stage R: lane = instance                                            */
+/* ================================================================== */
+
+__device__ void use_rev_option(RampScalars &rp, const DevWhirlTables *wh, int n, int signals)
+{
+    const int i = n % 9;
+    rp.hornTarget = wh->rev_horn_target[i];
+    rp.drumTarget = wh->rev_drum_target[i];
+    if (rp.hornIncr < rp.hornTarget)
+        rp.hornAcDc = 1;
+    else if (rp.hornTarget < rp.hornIncr)
+        rp.hornAcDc = -1;
+    if (rp.drumIncr < rp.drumTarget)
+        rp.drumAcDc = 1;
+    else if (rp.drumTarget < rp.drumIncr)
+        rp.drumAcDc = -1;
+    if (signals & 2) {
+        const int hr = (n / 3) % 3;
+        rp.revSelect = (hr == 2) ? 2 : (hr == 1) ? 0 : 1; /* WHIRL_FAST / SLOW / STOP */
+    }
+}
+
+/* per-call speed ramp and brake logic of ONE rotor, double precision
+ * (src/whirl.cpp:1219-1374; the horn and drum halves there differ only in the constants
+ * passed here).  Returns non-zero when the brake is engaged (incr is zeroed after the
+ * sample loop, src/whirl.cpp:1635-1636). */
+__device__ int rotor_ramp(const double SR, const bool is_horn, int *acdc, double *incr, double *angle,
+                          const double target, const double brake_pos, const double oml_acc,
+                          const double oml_dec)
+{
+    const float hardstop_rpm = is_horn ? 10.f : 8.f;
+    const float brake_limit_rpm = is_horn ? 60.f : 100.f;
     const float nsmp = (float)TBF_FRAGMENT;
     const double target_pos =
-        rc.is_horn ? fmod(__dsub_rn(1.25, brake_pos), 1.0) : fmod(__dadd_rn(brake_pos, .75), 1.0);
+        is_horn ? fmod(__dsub_rn(1.25, brake_pos), 1.0) : fmod(__dadd_rn(brake_pos, .75), 1.0);
 
     if (*acdc) {
         int flywheel = 0;
-        const float hardstop = (float)((double)rc.hardstop_rpm / ((double)60.f * SR));
+        const float hardstop = (float)((double)hardstop_rpm / ((double)60.f * SR));
         if (brake_pos > 0 && target == 0 && *incr > 0 && *incr < (double)hardstop) {
             if (fabs(__dsub_rn(*angle, target_pos)) < (2.0 / TBF_WHIRL_DISPLC)) {
                 *angle = target_pos;
@@ -632,7 +811,7 @@ __device__ int rotor_ramp(const DevWhirlTables *wh, const RotorConst rc, int *ac
             if (fabs(__dsub_rn(*angle, target_pos)) < (2.0 / TBF_WHIRL_DISPLC)) {
                 *angle = target_pos;
             } else {
-                const float limit = (float)((double)rc.brake_limit_rpm / (60. * SR));
+                const float limit = (float)((double)brake_limit_rpm / (60. * SR));
                 *incr = fmod(__dsub_rn(__dadd_rn(1., target_pos), *angle), 1.0) / (double)nsmp;
                 if (*incr > (double)limit)
                     *incr = limit;
@@ -654,51 +833,8 @@ __device__ __forceinline__ double angle_step(double a, double incr)
     return fmod(t, 1.0);
 }
 
-__device__ void angle_lane(double a0, double incr, double *out, double *final_angle)
-{
-    double a = a0;
-    if (a0 >= 0.0 && a0 < 1.0 && incr >= 0.0 && incr < 1.0) {
-        /* every sum stays in [0, 2): fmod(t, 1.0) is t or t - 1, both exact */
-#pragma unroll 8
-        for (int i = 0; i < TBF_FRAGMENT; ++i) {
-            out[i] = a;
-            const double t = __dadd_rn(a, incr);
-            a = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
-        }
-    } else {
-        for (int i = 0; i < TBF_FRAGMENT; ++i) {
-            out[i] = a;
-            a = angle_step(a, incr);
-        }
-    }
-    *final_angle = a;
-}
-
-/* speed ramp + angle sequence of one rotor; the horn and the drum lane run this in
- * lockstep on two lanes of one warp */
-__device__ void rotor_lane(InstScalars &sc, const DevWhirlTables *wh, Smem &sm, bool horn)
-{
-    RotorConst rc;
-    rc.hardstop_rpm = horn ? 10.f : 8.f;
-    rc.brake_limit_rpm = horn ? 60.f : 100.f;
-    rc.is_horn = horn ? 1 : 0;
-    int *p_acdc = horn ? &sc.hornAcDc : &sc.drumAcDc;
-    double *p_incr = horn ? &sc.hornIncr : &sc.drumIncr;
-    double *p_ang = horn ? &sc.hornAngle : &sc.drumAngle;
-    int acdc = *p_acdc;
-    double incr = *p_incr, ang = *p_ang;
-    const int brake = rotor_ramp(wh, rc, &acdc, &incr, &ang, horn ? sc.hornTarget : sc.drumTarget,
-                                 horn ? wh->hn_brake_pos : wh->dr_brake_pos,
-                                 wh->one_minus_l[horn ? 0 : 2], wh->one_minus_l[horn ? 1 : 3]);
-    double fin;
-    angle_lane(ang, incr, horn ? sm.hang : sm.dang, &fin);
-    *p_acdc = acdc;
-    *p_incr = brake ? 0.0 : incr;
-    *p_ang = fin;
-}
-
 /* DF-II biquad, float, source operation order (EQ_IIR, src/whirl.cpp:1479-1485) */
-__device__ __forceinline__ float eq_iir(const float *c, float &z0, float &z1, float x)
+__device__ __forceinline__ float eq_iir(const float (&c)[5], float &z0, float &z1, float x)
 {
     const float t = __fsub_rn(__fsub_rn(x, __fmul_rn(c[0], z0)), __fmul_rn(c[1], z1));
     const float y = __fadd_rn(__fadd_rn(__fmul_rn(t, c[2]), __fmul_rn(c[3], z0)), __fmul_rn(c[4], z1));
@@ -707,57 +843,214 @@ __device__ __forceinline__ float eq_iir(const float *c, float &z0, float &z1, fl
     return y;
 }
 
+struct RSmem {
+    float tin[2][BLK * TILE_PITCH];   /* u, php            (row = instance, col = sample) */
+    float tout[2][BLK * TILE_PITCH];  /* dx0 | mono, hx0                                 */
+    double tang[2][BLK * TILE_PITCH]; /* horn, drum angle                                */
+    unsigned long long csum[BLK];
+};
 
-/* horn input filters A and B in series (src/whirl.cpp:1513-1525), software-pipelined
- * over lanes 0 and 1 of warp 0: in iteration it lane 0 runs filter A on sample it while
- * lane 1 runs filter B on filter A's output of sample it-1 (handed over by shuffle), so
- * both recurrences share one instruction stream.  Call with tid 0 and 1 only. */
-__device__ void horn_filter_lanes(InstScalars &sc, const DevWhirlTables *wh, Smem &sm, int lane)
+__global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
 {
-    float c[5];
-#pragma unroll
-    for (int k = 0; k < 5; ++k)
-        c[k] = wh->iir[lane][k];
-    float z0 = sc.iirz[lane][0], z1 = sc.iirz[lane][1];
-    const float leakage = wh->leakage;
-    float handed = 0.0f; /* lane 1: filter A's output of the previous iteration */
-#pragma unroll 4
-    for (int it = 0; it <= TBF_FRAGMENT; ++it) {
-        float in = handed;
-        if (lane == 0 && it < TBF_FRAGMENT) {
-            in = (float)__dadd_rn((double)sm.mono[it], 1e-14); /* DENORMAL_HACK */
-            sm.dx[0][1 + it] = in;
-        }
-        const bool active = lane == 0 ? (it < TBF_FRAGMENT) : (it > 0);
-        float y = 0.0f;
-        if (active)
-            y = eq_iir(c, z0, z1, in);
-        handed = __shfl_sync(0x3u, y, 0);
-        if (lane == 1 && it > 0) {
-            sm.hx[0][8 + it - 1] = y;
-            sm.leak[it - 1] = __fmul_rn(y, leakage);
-        }
+    __shared__ RSmem sm;
+    const int lane = threadIdx.x;
+    const uint32_t slot0 = blockIdx.x * 32;
+    const uint32_t slot = slot0 + lane;
+    const bool valid = slot < p.n_instances;
+    const uint32_t rows = min(32u, p.n_instances - slot0);
+    const bool whirl_off = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
+    const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
+
+    InstState *st = nullptr;
+    const DevWhirlTables *wh = p.wh;
+    RampScalars rp;
+    if (valid) {
+        const uint32_t id = p.ids ? p.ids[slot] : slot;
+        st = p.states + id;
+        rp = st->rp;
+        wh = p.wh + st->tg.whTables;
+    } else {
+        rp = RampScalars();
     }
-    /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
-    sc.iirz[lane][0] = isnan(z0) ? 0.0f : z0;
-    sc.iirz[lane][1] = isnan(z1) ? 0.0f : z1;
+    const bool whirl_run = valid && !whirl_off && !wh->bypass;
+    float cA[5], cB[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        cA[k] = wh->iir[0][k];
+        cB[k] = wh->iir[1][k];
+    }
+    float zA0 = rp.iirz[0][0], zA1 = rp.iirz[0][1], zB0 = rp.iirz[1][0], zB1 = rp.iirz[1][1];
+    float pg = rp.percEnvGain, kc = rp.keyCompLevel;
+    double hang = rp.hornAngle, dang = rp.drumAngle;
+    const double SR = wh->sample_rate;
+    uint64_t ev_cur = 0, ev_end = 0;
+    if (valid) {
+        ev_cur = p.ev_cursor_r[slot];
+        ev_end = p.ev_start[slot + 1];
+    }
+    sm.csum[lane] = 0ull;
+    __syncwarp();
+
+    for (uint32_t f = 0; f < p.n_fragments; ++f) {
+        /* -- rotor speed events that precede this fragment -- */
+        while (ev_cur < ev_end) {
+            const tbf_event *evp = p.events + ev_cur;
+            if (evp->fragment > p.frag_base + f)
+                break;
+            const int type = evp->type, a = evp->a;
+            if (type == TBF_EV_REV_OPTION) {
+                if (a < 0)
+                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
+                else
+                    use_rev_option(rp, wh, a, 2);
+            } else if (type == TBF_EV_REV_SELECT) {
+                if (a < 0) {
+                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
+                } else {
+                    rp.revSelect = a % 3;
+                    use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
+                }
+            }
+            ++ev_cur;
+        }
+        FragCtl c;
+        c.key_comp = c.gain = c.decay = c.reset = 0.0f;
+        c.flags = 0;
+        if (valid)
+            c = p.ctl[(size_t)slot * p.n_fragments + f];
+        const bool perc_on = (c.flags & FC_PERC_ON) != 0;
+        /* (keyComp - level) / 128.f: dividing by 2^7 and multiplying by 2^-7 round identically */
+        const float delta = __fmul_rn(__fsub_rn(c.key_comp, kc), 0.0078125f);
+
+        /* -- per-call speed ramps (src/whirl.cpp:1219-1374) -- */
+        int hbrake = 0, dbrake = 0;
+        double hincr = rp.hornIncr, dincr = rp.drumIncr;
+        if (whirl_run) {
+            hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, wh->hn_brake_pos,
+                                wh->one_minus_l[0], wh->one_minus_l[1]);
+            dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, wh->dr_brake_pos,
+                                wh->one_minus_l[2], wh->one_minus_l[3]);
+        }
+        /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
+        const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
+        const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
+
+        for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
+            const size_t col0 = (size_t)f * TBF_FRAGMENT + (size_t)blk * BLK;
+            /* tile in: row r = instance slot0 + r, this lane = sample col0 + lane */
+            for (uint32_t r = 0; r < rows; ++r) {
+                const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+                sm.tin[0][r * TILE_PITCH + lane] = p.u[g];
+                sm.tin[1][r * TILE_PITCH + lane] = p.php[g];
+            }
+            __syncwarp();
+#pragma unroll 4
+            for (int s = 0; s < BLK; ++s) {
+                const float uu = sm.tin[0][lane * TILE_PITCH + s];
+                float mono;
+                if (perc_on) {
+                    const float pterm = __fmul_rn(sm.tin[1][lane * TILE_PITCH + s], pg);
+                    mono = __fmul_rn(__fmul_rn(c.gain, kc), __fadd_rn(uu, pterm));
+                    pg = __fmul_rn(pg, c.decay);
+                } else {
+                    mono = __fmul_rn(__fmul_rn(c.gain, kc), uu);
+                }
+                kc = __fadd_rn(kc, delta);
+                if (whirl_run) {
+                    const float x = (float)__dadd_rn((double)mono, 1e-14); /* DENORMAL_HACK */
+                    const float ya = eq_iir(cA, zA0, zA1, x);
+                    const float yb = eq_iir(cB, zB0, zB1, ya);
+                    sm.tout[0][lane * TILE_PITCH + s] = x;
+                    sm.tout[1][lane * TILE_PITCH + s] = yb;
+                    sm.tang[0][lane * TILE_PITCH + s] = hang;
+                    sm.tang[1][lane * TILE_PITCH + s] = dang;
+                    if (hfast) {
+                        const double t = __dadd_rn(hang, hincr);
+                        hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                    } else {
+                        hang = angle_step(hang, hincr);
+                    }
+                    if (dfast) {
+                        const double t = __dadd_rn(dang, dincr);
+                        dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                    } else {
+                        dang = angle_step(dang, dincr);
+                    }
+                } else {
+                    sm.tout[0][lane * TILE_PITCH + s] = mono;
+                    sm.tout[1][lane * TILE_PITCH + s] = mono; /* bypassed Leslie: stage D mixes it */
+                }
+            }
+            __syncwarp();
+            /* tile out */
+            if (whirl_off) {
+                for (uint32_t r = 0; r < rows; ++r) {
+                    const float m = sm.tout[0][r * TILE_PITCH + lane];
+                    if (store) {
+                        const size_t g = (size_t)(slot0 + r) * p.out_stride + col0 + lane;
+                        p.out_l[g] = m;
+                        p.out_r[g] = m;
+                    }
+                    if (p.checksums) {
+                        const uint32_t pos = (uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + col0 + lane);
+                        atomicAdd(&sm.csum[r], sample_hash(pos, m, m));
+                    }
+                }
+            } else {
+                for (uint32_t r = 0; r < rows; ++r) {
+                    const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+                    p.dx0[g] = sm.tout[0][r * TILE_PITCH + lane];
+                    p.hx0[g] = sm.tout[1][r * TILE_PITCH + lane];
+                    p.hang[g] = sm.tang[0][r * TILE_PITCH + lane];
+                    p.dang[g] = sm.tang[1][r * TILE_PITCH + lane];
+                }
+            }
+            __syncwarp();
+        }
+
+        /* -- end of the fragment -- */
+        if (whirl_run) {
+            /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
+            zA0 = isnan(zA0) ? 0.0f : zA0;
+            zA1 = isnan(zA1) ? 0.0f : zA1;
+            zB0 = isnan(zB0) ? 0.0f : zB0;
+            zB1 = isnan(zB1) ? 0.0f : zB1;
+            rp.hornIncr = hbrake ? 0.0 : hincr;
+            rp.drumIncr = dbrake ? 0.0 : dincr;
+        }
+        if (c.flags & FC_PERC_RESET)
+            pg = c.reset;
+    }
+
+    if (valid) {
+        rp.iirz[0][0] = zA0;
+        rp.iirz[0][1] = zA1;
+        rp.iirz[1][0] = zB0;
+        rp.iirz[1][1] = zB1;
+        rp.percEnvGain = pg;
+        rp.keyCompLevel = kc;
+        rp.hornAngle = hang;
+        rp.drumAngle = dang;
+        st->rp = rp;
+        p.ev_cursor_r[slot] = ev_cur;
+        if (p.checksums && whirl_off)
+            p.checksums[slot] += sm.csum[lane]; /* zeroed by the host; accumulates over chunks */
+    }
 }
 
-/* drum filter of one channel on the values read from its delay line, one lane */
-__device__ void drum_filter_lane(InstScalars &sc, const DevWhirlTables *wh, Smem &sm, int line)
-{
-    float c[5];
-#pragma unroll
-    for (int k = 0; k < 5; ++k)
-        c[k] = wh->iir[line][k];
-    float z0 = sc.iirz[line][0], z1 = sc.iirz[line][1];
-    float *v = sm.lineout[line];
-#pragma unroll 8
-    for (int i = 0; i < TBF_FRAGMENT; ++i)
-        v[i] = eq_iir(c, z0, z1, v[i]);
-    sc.iirz[line][0] = isnan(z0) ? 0.0f : z0;
-    sc.iirz[line][1] = isnan(z1) ? 0.0f : z1;
-}
+/* ================================================================== */
+/* stage W: Leslie reflections, taps, delay lines; warp = instance     */
+/* ================================================================== */
+
+struct WWarp {
+    float hx[3][8 + TBF_FRAGMENT]; /* horn stage inputs with 8 samples of history */
+    float dx[3][4 + TBF_FRAGMENT]; /* drum stage inputs, history at index 3       */
+    float ta[6][BLK], tb[6][BLK];  /* the two contributions of every tap of a group */
+    float lo[2][BLK];              /* serial fallback: the two line reads of a group */
+    uint16_t tn[6][BLK];           /* destination slot of the tap's main part     */
+    float zs[4];                   /* FILTER_C states z[0..3], NaN-scrubbed per fragment */
+    /* followed by float ring[4][ring_size]: the delay lines HL HR DL DR */
+};
 
 /* FILTER_C(0.4, 0.4): the literals are double, so the 2-tap FIR is evaluated in
  * double and rounded to float once (src/whirl.cpp:1472-1477) */
@@ -766,11 +1059,7 @@ __device__ __forceinline__ float filter_c(float x, float z)
     return (float)__dadd_rn(__dmul_rn(0.4, (double)x), __dmul_rn(0.4, (double)z));
 }
 
-/* ------------------------------------------------------------------ */
-/* whirl: tap geometry, thread = sample (HN_MOTION / DR_MOTION,         */
-/* src/whirl.cpp:1432-1469).  Writes the slot and the two contributions */
-/* of every tap to shared memory.                                       */
-/* ------------------------------------------------------------------ */
+/* tap geometry (HN_MOTION / DR_MOTION, src/whirl.cpp:1432-1469) */
 __device__ __forceinline__ void tap_position(double ang_grd, int phase, const float *__restrict__ dsp,
                                              float spacing, uint32_t outpos, float &frac,
                                              uint32_t &slot, uint32_t &kround)
@@ -785,437 +1074,381 @@ __device__ __forceinline__ void tap_position(double ang_grd, int phase, const fl
     const float t = __fadd_rn(__fadd_rn(spacing, intp), (float)outpos);
     const float r = floorf(t);
     frac = __fsub_rn(t, r);
-    slot = f2u_x86(r) & GLOBAL_WBUF_MASK;
+    slot = f2u_x86(r) & WBUF_MASK;
 }
 
-__device__ void whirl_taps(const DevWhirlTables *wh, Smem &sm, int i, uint32_t outpos0)
-{
-    const uint32_t outpos = (outpos0 + (uint32_t)i) & GLOBAL_WBUF_MASK;
-    const double hang = sm.hang[i], dang = sm.dang[i];
-#pragma unroll
-    for (int p = 0; p < 6; ++p) {
-        /* taps 0,3,4 read the forward displacement table with the backward FIR
-         * bank, taps 1,2,5 the other way round (src/whirl.cpp:1540-1563) */
-        const bool fwd = (p == 0 || p == 3 || p == 4);
-        const float *dsp = fwd ? wh->hn_fwd_displ : wh->hn_bwd_displ;
-        const float *bw = fwd ? wh->bbw : wh->bfw;
-        const double ang = __dadd_rn(hang, (p & 1) ? wh->bw_ang : wh->fw_ang);
-        float frac;
-        uint32_t slot, k;
-        tap_position(ang, wh->horn_phase[p], dsp, wh->horn_spacing[p], outpos, frac, slot, k);
-        const float *hx = &sm.hx[p >> 1][8 + i];
-        const float *b = bw + 5 * k;
-        float xa = __fmul_rn(__ldg(b + 0), hx[0]);
-        xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 1), hx[-1]));
-        xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 2), hx[-2]));
-        xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 3), hx[-3]));
-        xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 4), hx[-4]));
-        const float q = __fmul_rn(xa, frac);
-        sm.tapn[p][i] = (uint16_t)slot;
-        sm.tapa[p][i] = __fsub_rn(xa, q);
-        sm.tapb[p][i] = q;
-    }
-#pragma unroll
-    for (int p = 0; p < 6; ++p) {
-        const bool fwd = (p == 0 || p == 3 || p == 4);
-        const float *dsp = fwd ? wh->dr_fwd_displ : wh->dr_bwd_displ;
-        float frac;
-        uint32_t slot, k;
-        tap_position(dang, wh->drum_phase[p], dsp, wh->drum_spacing[p], outpos, frac, slot, k);
-        const float x = sm.dx[p >> 1][1 + i];
-        const float q = __fmul_rn(x, frac);
-        sm.tapn[6 + p][i] = (uint16_t)slot;
-        sm.tapa[6 + p][i] = __fsub_rn(x, q);
-        sm.tapb[6 + p][i] = q;
-    }
-}
-
-/* What the parallel delay-line update relies on, checked per fragment: per tap the
+/* What the parallel delay-line update relies on, checked per block: per tap the
  * destination slots advance monotonically with the sample index and stay inside
  * [reader, reader + window). */
-__device__ __forceinline__ int whirl_check_taps(const DevWhirlTables *wh, const Smem &sm, int i,
-                                                uint32_t outpos0)
+__device__ __forceinline__ int taps_bad(const DevWhirlTables *wh, const WWarp &sm, int lane,
+                                        uint32_t outpos_blk)
 {
     int bad = 0;
     const uint32_t window = (uint32_t)wh->window;
 #pragma unroll
-    for (int p = 0; p < 12; ++p) {
-        const uint32_t n = sm.tapn[p][i];
-        const uint32_t rel = (n - outpos0) & GLOBAL_WBUF_MASK;
-        bad |= (rel < (uint32_t)i) | (rel + 1 >= window);
-        if (i > 0)
-            bad |= ((n - (uint32_t)sm.tapn[p][i - 1]) & GLOBAL_WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
+    for (int q = 0; q < 6; ++q) {
+        const uint32_t n = sm.tn[q][lane];
+        const uint32_t rel = (n - outpos_blk) & WBUF_MASK;
+        bad |= (rel < (uint32_t)lane) | (rel + 1 >= window);
+        if (lane > 0)
+            bad |= ((n - (uint32_t)sm.tn[q][lane - 1]) & WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
     }
     return bad;
 }
 
-/* Ordered scatter of ONE tap, thread = sample.  Because the tap's slot sequence n[i]
- * never decreases, the samples hitting a slot form a contiguous run, and the
- * reference's loop adds to slot S first the q-parts of the run that hit S-1, then the
- * (x-q)-parts of the run that hits S.  The first sample of each run applies exactly
- * that sequence to its slot; a slot that only receives q-parts (the run after it
- * skips it, or the fragment ends) is completed by the last sample of the run before.
- * Distinct threads touch distinct slots, so one pass needs no atomics; the three taps
- * of a line are applied in three passes, farthest delay first (see tap_order). */
-__device__ __forceinline__ void whirl_tap_pass(const Smem &sm, float *ring, uint32_t rmask, int p, int i)
+/* Scatter the six taps of one group (horn: taps 0..5 -> HL, HR; drum: 6..11 -> DL, DR)
+ * of one 32-sample block into the group's two delay lines and read the block's 32
+ * outputs.  Even taps feed the left line, odd taps the right one. */
+__device__ __forceinline__ void group_scatter_read(const DevWhirlTables *wh, WWarp &sm, float *ring_l,
+                                                   float *ring_r, uint32_t rmask, int line0, int lane,
+                                                   uint32_t outpos_blk, bool gather_ok, int &fell_back,
+                                                   float &out_l, float &out_r)
 {
-    const uint16_t *n = sm.tapn[p];
-    const float *a = sm.tapa[p];
-    const float *b = sm.tapb[p];
-    const uint32_t ni = n[i];
-    const uint32_t prev = i ? (uint32_t)n[i - 1] : 0xFFFFFFFFu;
-    const uint32_t next = (i < TBF_FRAGMENT - 1) ? (uint32_t)n[i + 1] : 0xFFFFFFFFu;
-    if (ni != prev) { /* first sample of the run hitting slot ni */
-        float v = ring[ni & rmask];
-        const uint32_t sm1 = (ni - 1) & GLOBAL_WBUF_MASK;
-        int j0 = i;
-        while (j0 > 0 && n[j0 - 1] == sm1)
-            --j0;
-        for (int j = j0; j < i; ++j)
-            v = __fadd_rn(v, b[j]);
-        for (int m = i; m < TBF_FRAGMENT && n[m] == ni; ++m)
-            v = __fadd_rn(v, a[m]);
-        ring[ni & rmask] = v;
-    }
-    if (ni != next) { /* last sample of its run */
-        const uint32_t sp1 = (ni + 1) & GLOBAL_WBUF_MASK;
-        if (next != sp1) { /* nobody hits ni+1 as a main slot in this fragment */
-            float v = ring[sp1 & rmask];
-            int j0 = i;
-            while (j0 > 0 && n[j0 - 1] == ni)
-                --j0;
-            for (int j = j0; j <= i; ++j)
-                v = __fadd_rn(v, b[j]);
-            ring[sp1 & rmask] = v;
-        }
-    }
-}
-
-/* The reference's loop as written, one lane per delay line (0 HL, 1 HR, 2 DL,
- * 3 DR): fallback for geometries / rotor speeds the gather does not cover. */
-__device__ void scatter_lane(const Smem &sm, float *buf, uint32_t rmask, float *lineout, int line,
-                             uint32_t outpos0)
-{
-    const int tap0 = (line < 2) ? (line & 1) : 6 + (line & 1);
-    for (int i = 0; i < TBF_FRAGMENT; ++i) {
+    int bad = 1;
+    if (gather_ok)
+        bad = taps_bad(wh, sm, lane, outpos_blk);
+    bad = __any_sync(FULL, bad);
+    const uint32_t op = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
+    if (!bad) {
+        const int tap0 = line0 * 3; /* first tap id of the group: 0 (horn) or 6 (drum) */
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
-            const int p = tap0 + 2 * s;
-            const uint32_t n = sm.tapn[p][i];
-            buf[n & rmask] = __fadd_rn(buf[n & rmask], sm.tapa[p][i]);
-            const uint32_t n1 = (n + 1) & GLOBAL_WBUF_MASK;
-            buf[n1 & rmask] = __fadd_rn(buf[n1 & rmask], sm.tapb[p][i]);
+        for (int j = 0; j < 3; ++j) { /* the three taps of a line: farthest delay first */
+            const int ql = wh->tap_order[line0][j] - tap0, qr = wh->tap_order[line0 + 1][j] - tap0;
+            ordered_pass(sm.tn[ql], sm.ta[ql], sm.tb[ql], ring_l, rmask, WBUF_MASK, lane);
+            ordered_pass(sm.tn[qr], sm.ta[qr], sm.tb[qr], ring_r, rmask, WBUF_MASK, lane);
+            __syncwarp();
         }
-        const uint32_t op = (outpos0 + (uint32_t)i) & GLOBAL_WBUF_MASK;
-        lineout[i] = buf[op & rmask];
-        buf[op & rmask] = 0.0f;
+        out_l = ring_l[op & rmask];
+        ring_l[op & rmask] = 0.0f;
+        out_r = ring_r[op & rmask];
+        ring_r[op & rmask] = 0.0f;
+    } else {
+        /* the reference's loop as written, one lane per delay line: geometries / rotor
+         * speeds the parallel passes do not cover */
+        fell_back |= gather_ok ? 1 : 0;
+        if (lane < 2) {
+            float *buf = lane ? ring_r : ring_l;
+            for (int i = 0; i < BLK; ++i) {
+#pragma unroll
+                for (int s = 0; s < 3; ++s) {
+                    const int q = lane + 2 * s;
+                    const uint32_t n = sm.tn[q][i];
+                    buf[n & rmask] = __fadd_rn(buf[n & rmask], sm.ta[q][i]);
+                    const uint32_t n1 = (n + 1) & WBUF_MASK;
+                    buf[n1 & rmask] = __fadd_rn(buf[n1 & rmask], sm.tb[q][i]);
+                }
+                const uint32_t o = (outpos_blk + (uint32_t)i) & WBUF_MASK;
+                sm.lo[lane][i] = buf[o & rmask];
+                buf[o & rmask] = 0.0f;
+            }
+        }
+        __syncwarp();
+        out_l = sm.lo[0][lane];
+        out_r = sm.lo[1][lane];
     }
+    __syncwarp();
 }
 
-/* ------------------------------------------------------------------ */
-/* the batched render kernel: grid = instances, block = 128 threads     */
-/* ------------------------------------------------------------------ */
-__global__ void __launch_bounds__(TBF_THREADS)
-tbf_render_kernel(const RenderParams p, const uint32_t ring_size)
+__global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p, const uint32_t ring_size)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    Smem &sm = *reinterpret_cast<Smem *>(smem_raw);
-    float *wring = reinterpret_cast<float *>(smem_raw + sizeof(Smem));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t slot = blockIdx.x * W_WARPS + warp;
+    if (slot >= p.n_instances)
+        return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
+    const size_t per_warp = sizeof(WWarp) + (size_t)4 * ring_size * sizeof(float);
+    WWarp &sm = *reinterpret_cast<WWarp *>(smem_raw + per_warp * warp);
+    float *ring = reinterpret_cast<float *>(smem_raw + per_warp * warp + sizeof(WWarp));
     const uint32_t rmask = ring_size - 1;
-    const int tid = threadIdx.x;
-    const uint32_t slot = blockIdx.x;
     const uint32_t id = p.ids ? p.ids[slot] : slot;
     InstState *st = p.states + id;
-    InstScalars &sc = sm.sc;
+    const DevWhirlTables *wh = p.wh + st->tg.whTables;
+    if (wh->bypass)
+        return; /* whirlProc2 leaves a bypassed Leslie untouched (src/whirl.cpp:1197-1215) */
 
-    /* ---- stage scalars, delay-line windows and FIR histories in shared memory ---- */
-    for (int i = tid; i < (int)(sizeof(InstScalars) / 4); i += TBF_THREADS)
-        reinterpret_cast<uint32_t *>(&sm.sc)[i] = reinterpret_cast<const uint32_t *>(&st->sc)[i];
-    for (int i = tid; i < VRING; i += TBF_THREADS)
-        sm.vfirst[i] = 0;
-    if (tid == 0)
-        sm.csum = 0ull;
-    __syncthreads();
-    const DevTonegenTables *tg = p.tg + sc.tgTables;
-    const DevWhirlTables *wh = p.wh + sc.whTables;
-    for (int s = tid; s < VRING; s += TBF_THREADS) {
-        const uint32_t g = (sc.vibOutPos + (uint32_t)s) & 0x3FFu;
-        sm.vring[g & VRING_MASK] = st->vibBuffer[g];
-    }
+    WhirlScalars ws = st->wl; /* every lane holds a copy; lane 0 writes it back */
+    uint32_t outpos0 = ws.outpos;
     for (int line = 0; line < 4; ++line)
-        for (uint32_t s = tid; s < ring_size; s += TBF_THREADS) {
-            const uint32_t g = (sc.outpos + s) & GLOBAL_WBUF_MASK;
-            wring[line * ring_size + (g & rmask)] = st->wbuf[line][g];
+        for (uint32_t s = lane; s < ring_size; s += 32) {
+            const uint32_t g = (outpos0 + s) & WBUF_MASK;
+            ring[line * ring_size + (g & rmask)] = st->wbuf[line][g];
         }
-    if (tid < 24) {
-        const int s = tid >> 3, k = tid & 7;
-        sm.hx[s][7 - k] = sc.adx[s][(sc.adi[s] + k) & 7];
+    if (lane < 24) {
+        const int s = lane >> 3, k = lane & 7;
+        sm.hx[s][7 - k] = ws.adx[s][(ws.adi[s] + k) & 7];
     }
-    if (tid < 4)
-        sm.zs[tid] = sc.z[tid];
-
-    const bool whirl_off = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
-    const bool whirl3 = (p.flags & TBF_RENDER_WHIRLPROC3) != 0;
-    const bool whirl_run = !whirl_off && !wh->bypass;
+    if (lane < 4)
+        sm.zs[lane] = ws.z[lane];
     const bool gather_ok = wh->gather_ok != 0;
-    const int window = wh->window;
-    const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
-    float *out_l = p.out_l + (size_t)slot * p.out_stride;
-    float *out_r = p.out_r + (size_t)slot * p.out_stride;
-    uint32_t outpos0 = sc.outpos;
-    uint64_t ev_cur = p.ev_cursor[slot];
-    const uint64_t ev_end = p.ev_start[slot + 1];
-    unsigned long long csum = 0ull;
-    __syncthreads();
+    int fell_back = 0;
+    const size_t row = (size_t)slot * p.pitch;
+    __syncwarp();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
-        /* -- P0: control events that precede this fragment, routing, key compression -- */
-        if (tid == 0) {
-            while (ev_cur < ev_end && p.events[ev_cur].fragment <= p.frag_base + f) {
-                apply_event(sc, st, tg, wh, p.events[ev_cur]);
-                ++ev_cur;
-            }
-            int kdc = sc.keyDownCount;
-            if (kdc > 127 || kdc < 0) { /* reference reads past keyCompTable[128] */
-                sc.errorFlags |= TBF_IFLAG_KEYCOMP_OOB;
-                kdc = kdc < 0 ? 0 : 127;
-            }
-            const float key_comp = tg->key_comp_table[kdc];
-            /* (keyComp - level) / 128.f: dividing by 2^7 and multiplying by 2^-7 round identically */
-            sm.key_comp_delta = __fmul_rn(__fsub_rn(key_comp, sc.keyCompLevel), 0.0078125f);
-            sm.recompute_routing = (sc.oldRouting != sc.newRouting);
-            if (sm.recompute_routing)
-                sc.oldRouting = sc.newRouting;
-            sm.draw_bar_change = sc.drawBarChange;
-            sm.vib_on = (sc.oldRouting & RT_VIB) != 0;
-            sm.perc_on = (sc.oldRouting & RT_PERC) != 0;
-            sm.n_ins = 0;
-        }
-        __syncthreads();
-        const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
-
-        /* -- P1: data-independent recurrences on single lanes of warps 1..3, while the
-         *        active list is turned into core-program records -- */
-        if (tid == 32) {
-            gain_ramps(sc, sm, perc_on);
-        } else if ((tid == 64 || tid == 65) && whirl_run) {
-            rotor_lane(sc, wh, sm, tid == 64); /* horn and drum rotor: two lanes in lockstep */
-        }
-        active_list_pass(st, tg, sm, tid);
-        __syncthreads();
-
-        /* -- P2: additive synthesis, thread = sample; scanner contributions -- */
-        float swl, vib, prc;
-        core_interpreter(tg, sm, tid, swl, vib, prc);
-        sm.vib_in[tid] = vib;
-        sm.prc[tid] = prc;
-        int vbad = 0;
-        if (vib_on)
-            vbad = vibrato_contrib(sc, tg, sm, tid, vib);
-        vbad = __syncthreads_or(vbad);
-
-        /* -- P3: scanner gather (thread = slot), percussion high-pass, mixdown -- */
-        float vib_y = 0.0f;
-        if (vib_on) {
-            if (!vbad) {
-                const float v = vibrato_gather_slot(sc, sm, tid);
-                float v2 = 0.0f;
-                const bool second = tid + TBF_FRAGMENT < VWINDOW;
-                if (second)
-                    v2 = vibrato_gather_slot(sc, sm, tid + TBF_FRAGMENT);
-                vib_y = sc.vibMixed ? __fmul_rn(__fadd_rn(vib, v), (float)0.7071067811865475) : v;
-                __syncthreads(); /* every slot gathered before any ring slot changes */
-                sm.vring[(sc.vibOutPos + (uint32_t)tid) & VRING_MASK] = 0.0f;
-                if (second)
-                    sm.vring[(sc.vibOutPos + (uint32_t)(tid + TBF_FRAGMENT)) & VRING_MASK] = v2;
-            } else {
-                if (tid == 0)
-                    vibrato_serial(sc, tg, sm);
-                __syncthreads();
-                vib_y = sm.vib_y[tid];
-            }
-        }
-        float prc_hp = 0.0f;
-        if (perc_on) /* in-place differencer, src/tonegen.cpp:3719-3732 */
-            prc_hp = __fsub_rn(tid ? sm.prc[tid - 1] : sc.pz, prc);
-        float mono;
-        {
-            const float kc = sm.kc[tid];
-            if (perc_on) {
-                const float og = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
-                const float pterm = __fmul_rn(prc_hp, sm.pg[tid]);
-                const float acc = vib_on ? __fadd_rn(__fadd_rn(swl, vib_y), pterm) : __fadd_rn(swl, pterm);
-                mono = __fmul_rn(__fmul_rn(og, kc), acc);
-            } else {
-                const float acc = vib_on ? __fadd_rn(swl, vib_y) : swl;
-                mono = __fmul_rn(__fmul_rn(sc.swellPedalGain, kc), acc);
-            }
-        }
-        sm.mono[tid] = mono;
-        __syncthreads();
-
-        /* -- P4: end-of-fragment tone generator scalars + horn filters A,B (lane 0) -- */
-        if (tid == 0) {
-            if (vib_on) {
-                sc.vibStator = (sc.vibStator + TBF_FRAGMENT * tg->vib_stator_increment) & 0x07FFFFFFu;
-                sc.vibOutPos = (sc.vibOutPos + TBF_FRAGMENT) & 0x3FFu;
-            }
-            if (perc_on) {
-                sc.outputGain = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
-                sc.pz = sm.prc[TBF_FRAGMENT - 1];
-            }
-            if (sc.upperKeyCount == 0)
-                sc.percEnvGain = sc.percEnvGainReset;
-        }
-        if (tid < 2 && whirl_run)
-            horn_filter_lanes(sc, wh, sm, tid);
-
-        float o_l, o_r;
-        if (!whirl_run) {
-            if (whirl_off || !whirl3) {
-                o_l = o_r = mono;
-            } else { /* whirl.bypass=1 seen through whirlProc3's mic mix */
-                o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(mono, wh->mic_hll), __fmul_rn(mono, wh->mic_hlr)),
-                                          __fmul_rn(0.0f, wh->mic_dll)), __fmul_rn(0.0f, wh->mic_dlr));
-                o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(mono, wh->mic_hrl), __fmul_rn(mono, wh->mic_hrr)),
-                                          __fmul_rn(0.0f, wh->mic_drl)), __fmul_rn(0.0f, wh->mic_drr));
-            }
-        } else {
-            __syncthreads();
-            /* -- P5: the two reflection filters of each path (2-tap FIRs in double);
-             *        stage 1 of sample i-1 is recomputed locally to save a barrier -- */
-            {
-                const float h0 = sm.hx[0][8 + tid], h0m = tid ? sm.hx[0][7 + tid] : sm.zs[0];
-                const float h1 = filter_c(h0, h0m);
-                const float h1m = tid ? filter_c(h0m, tid > 1 ? sm.hx[0][6 + tid] : sm.zs[0]) : sm.zs[1];
-                sm.hx[1][8 + tid] = h1;
-                sm.hx[2][8 + tid] = filter_c(h1, h1m);
-                const float d0 = sm.dx[0][1 + tid], d0m = tid ? sm.dx[0][tid] : sm.zs[2];
-                const float d1 = filter_c(d0, d0m);
-                const float d1m = tid ? filter_c(d0m, tid > 1 ? sm.dx[0][tid - 1] : sm.zs[2]) : sm.zs[3];
-                sm.dx[1][1 + tid] = d1;
-                sm.dx[2][1 + tid] = filter_c(d1, d1m);
-            }
-            __syncthreads();
-            /* -- P6: tap geometry + FIRs, thread = sample -- */
-            whirl_taps(wh, sm, tid, outpos0);
-            __syncthreads();
-            int wbad = 1;
-            if (gather_ok)
-                wbad = whirl_check_taps(wh, sm, tid, outpos0);
-            wbad = __syncthreads_or(wbad);
-            /* -- P7: delay lines: ordered parallel scatter or the serial fallback -- */
-            if (!wbad) {
-                /* slots nearer than the line's shortest delay cannot be written in this
-                 * fragment: read and clear them first (this also frees the ring cells
-                 * that slots >= ring_size ahead alias with) */
+        const size_t col = row + (size_t)f * TBF_FRAGMENT;
 #pragma unroll
-                for (int line = 0; line < 4; ++line)
-                    if (tid < wh->line_dmin[line]) {
-                        float *c = wring + line * ring_size + ((outpos0 + (uint32_t)tid) & rmask);
-                        sm.lineout[line][tid] = *c;
-                        *c = 0.0f;
-                    }
-                __syncthreads();
+        for (int k = 0; k < 4; ++k) {
+            const int i = BLK * k + lane;
+            sm.hx[0][8 + i] = p.hx0[col + i];
+            sm.dx[0][4 + i] = p.dx0[col + i];
+        }
+        if (lane == 0) {
+            sm.dx[0][3] = sm.zs[2];
+            sm.dx[1][3] = sm.zs[3];
+        }
+        __syncwarp();
+        /* -- the two reflection filters of each path (2-tap FIRs in double); stage 1 of
+         *    sample i-1 is recomputed locally instead of exchanged -- */
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
+        for (int k = 0; k < 4; ++k) {
+            const int i = BLK * k + lane;
+            const float h0 = sm.hx[0][8 + i], h0m = i ? sm.hx[0][7 + i] : sm.zs[0];
+            const float h1 = filter_c(h0, h0m);
+            const float h1m = i ? filter_c(h0m, i > 1 ? sm.hx[0][6 + i] : sm.zs[0]) : sm.zs[1];
+            sm.hx[1][8 + i] = h1;
+            sm.hx[2][8 + i] = filter_c(h1, h1m);
+            const float d0 = sm.dx[0][4 + i], d0m = sm.dx[0][3 + i];
+            const float d1 = filter_c(d0, d0m);
+            const float d1m = i ? filter_c(d0m, i > 1 ? sm.dx[0][2 + i] : sm.zs[2]) : sm.zs[3];
+            sm.dx[1][4 + i] = d1;
+            sm.dx[2][4 + i] = filter_c(d1, d1m);
+        }
+        __syncwarp();
+
+#pragma unroll 1
+        for (int k = 0; k < 4; ++k) {
+            const int i = BLK * k + lane;
+            const uint32_t outpos_blk = (outpos0 + (uint32_t)(BLK * k)) & WBUF_MASK;
+            const uint32_t outpos = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
+            const double hang = p.hang[col + i], dang = p.dang[col + i];
+            /* -- horn taps: geometry + 5-tap FIR (src/whirl.cpp:1432-1453, :1540-1563) -- */
 #pragma unroll
-                    for (int line = 0; line < 4; ++line)
-                        whirl_tap_pass(sm, wring + line * ring_size, rmask, wh->tap_order[line][k], tid);
-                    __syncthreads();
-                }
+            for (int q = 0; q < 6; ++q) {
+                /* taps 0,3,4 read the forward displacement table with the backward FIR
+                 * bank, taps 1,2,5 the other way round */
+                const bool fwd = (q == 0 || q == 3 || q == 4);
+                const float *dsp = fwd ? wh->hn_fwd_displ : wh->hn_bwd_displ;
+                const float *bw = fwd ? wh->bbw : wh->bfw;
+                const double ang = __dadd_rn(hang, (q & 1) ? wh->bw_ang : wh->fw_ang);
+                float frac;
+                uint32_t slot_n, kr;
+                tap_position(ang, wh->horn_phase[q], dsp, wh->horn_spacing[q], outpos, frac, slot_n, kr);
+                const float *hx = &sm.hx[q >> 1][8 + i];
+                const float *b = bw + 5 * kr;
+                float xa = __fmul_rn(__ldg(b + 0), hx[0]);
+                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 1), hx[-1]));
+                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 2), hx[-2]));
+                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 3), hx[-3]));
+                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 4), hx[-4]));
+                const float qq = __fmul_rn(xa, frac);
+                sm.tn[q][lane] = (uint16_t)slot_n;
+                sm.ta[q][lane] = __fsub_rn(xa, qq);
+                sm.tb[q][lane] = qq;
+            }
+            __syncwarp();
+            float hl, hr, dl, dr;
+            group_scatter_read(wh, sm, ring, ring + ring_size, rmask, 0, lane, outpos_blk, gather_ok,
+                               fell_back, hl, hr);
+            /* -- drum taps (src/whirl.cpp:1455-1469, :1566-1588) -- */
 #pragma unroll
-                for (int line = 0; line < 4; ++line)
-                    if (tid >= wh->line_dmin[line]) {
-                        float *c = wring + line * ring_size + ((outpos0 + (uint32_t)tid) & rmask);
-                        sm.lineout[line][tid] = *c;
-                        *c = 0.0f;
-                    }
-            } else {
-                if (gather_ok && tid == 0)
-                    sc.errorFlags |= TBF_IFLAG_GATHER_FALLBACK;
-                if ((tid & 31) == 0)
-                    scatter_lane(sm, wring + (tid >> 5) * ring_size, rmask, sm.lineout[tid >> 5],
-                                 tid >> 5, outpos0);
+            for (int q = 0; q < 6; ++q) {
+                const bool fwd = (q == 0 || q == 3 || q == 4);
+                const float *dsp = fwd ? wh->dr_fwd_displ : wh->dr_bwd_displ;
+                float frac;
+                uint32_t slot_n, kr;
+                tap_position(dang, wh->drum_phase[q], dsp, wh->drum_spacing[q], outpos, frac, slot_n, kr);
+                const float x = sm.dx[q >> 1][4 + i];
+                const float qq = __fmul_rn(x, frac);
+                sm.tn[q][lane] = (uint16_t)slot_n;
+                sm.ta[q][lane] = __fsub_rn(x, qq);
+                sm.tb[q][lane] = qq;
             }
-            __syncthreads();
-            /* -- P8: drum filters, one lane per channel in two different warps -- */
-            if (tid == 64 || tid == 65) /* two lanes of one warp in lockstep */
-                drum_filter_lane(sc, wh, sm, 2 + (tid & 1));
-            __syncthreads();
-            /* -- P9: output mix -- */
-            const float hl = sm.lineout[0][tid], hr = sm.lineout[1][tid];
-            const float yl = sm.lineout[2][tid], yr = sm.lineout[3][tid];
-            const float leak = sm.leak[tid];
-            const float hpl = __fmul_rn(wh->horn_level, hl), hpr = __fmul_rn(wh->horn_level, hr);
-            if (!whirl3) {
-                o_l = __fadd_rn(__fadd_rn(yl, hpl), leak);
-                o_r = __fadd_rn(__fadd_rn(yr, hpr), leak);
-            } else {
-                const float ohl = __fadd_rn(hpl, leak), ohr = __fadd_rn(hpr, leak);
-                o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, wh->mic_hll), __fmul_rn(ohr, wh->mic_hlr)),
-                                          __fmul_rn(yl, wh->mic_dll)), __fmul_rn(yr, wh->mic_dlr));
-                o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, wh->mic_hrl), __fmul_rn(ohr, wh->mic_hrr)),
-                                          __fmul_rn(yl, wh->mic_drl)), __fmul_rn(yr, wh->mic_drr));
-            }
-            /* carry FIR histories / filter states into the next fragment */
-            float keep = 0.f;
-            if (tid < 24)
-                keep = sm.hx[tid >> 3][TBF_FRAGMENT + (tid & 7)];
-            float zc = 0.f;
-            if (tid >= 32 && tid < 36) {
-                const int k = tid - 32;
-                zc = (k == 0) ? sm.hx[0][8 + 127] : (k == 1) ? sm.hx[1][8 + 127]
-                     : (k == 2) ? sm.dx[0][128] : sm.dx[1][128];
-            }
-            __syncthreads();
-            if (tid < 24)
-                sm.hx[tid >> 3][tid & 7] = keep;
-            if (tid >= 32 && tid < 36)
-                sm.zs[tid - 32] = isnan(zc) ? 0.0f : zc; /* src/whirl.cpp:1627-1630 */
-            outpos0 = (outpos0 + TBF_FRAGMENT) & GLOBAL_WBUF_MASK;
+            __syncwarp();
+            group_scatter_read(wh, sm, ring + 2 * ring_size, ring + 3 * ring_size, rmask, 2, lane,
+                               outpos_blk, gather_ok, fell_back, dl, dr);
+            p.line[0][col + i] = hl;
+            p.line[1][col + i] = hr;
+            p.line[2][col + i] = dl;
+            p.line[3][col + i] = dr;
         }
 
-        if (store) {
-            out_l[(size_t)f * TBF_FRAGMENT + tid] = o_l;
-            out_r[(size_t)f * TBF_FRAGMENT + tid] = o_r;
-        }
-        const size_t o = (size_t)(p.frag_base + f) * TBF_FRAGMENT + tid; /* position in the batch */
-        csum += mix64(((unsigned long long)(uint32_t)o << 32) | __float_as_uint(o_l));
-        csum += mix64((((unsigned long long)(uint32_t)o << 32) | __float_as_uint(o_r)) ^ 0x5555555555555555ull);
-        __syncthreads();
+        /* carry FIR histories / filter states into the next fragment */
+        float keep = 0.f;
+        if (lane < 24)
+            keep = sm.hx[lane >> 3][TBF_FRAGMENT + (lane & 7)];
+        float zc = 0.f;
+        if (lane < 4)
+            zc = (lane == 0) ? sm.hx[0][8 + 127] : (lane == 1) ? sm.hx[1][8 + 127]
+                 : (lane == 2) ? sm.dx[0][4 + 127] : sm.dx[1][4 + 127];
+        __syncwarp();
+        if (lane < 24)
+            sm.hx[lane >> 3][lane & 7] = keep;
+        if (lane < 4)
+            sm.zs[lane] = isnan(zc) ? 0.0f : zc; /* src/whirl.cpp:1627-1630 */
+        outpos0 = (outpos0 + TBF_FRAGMENT) & WBUF_MASK;
+        __syncwarp();
     }
 
     /* ---- write the staged state back ---- */
-    if (tid < 24) {
-        const int s = tid >> 3, k = tid & 7;
-        sc.adx[s][(sc.adi[s] + k) & 7] = sm.hx[s][7 - k];
+    if (lane < 24) {
+        const int s = lane >> 3, k = lane & 7;
+        st->wl.adx[s][(ws.adi[s] + k) & 7] = sm.hx[s][7 - k];
     }
-    if (tid < 4)
-        sc.z[tid] = sm.zs[tid];
-    if (tid == 0) {
-        sc.outpos = outpos0;
-        p.ev_cursor[slot] = ev_cur;
+    if (lane < 4)
+        st->wl.z[lane] = sm.zs[lane];
+    if (lane == 0) {
+        st->wl.outpos = outpos0;
+        if (fell_back)
+            st->wl.errorFlags = ws.errorFlags | TBF_IFLAG_GATHER_FALLBACK;
     }
-    __syncthreads();
-    for (int i = tid; i < (int)(sizeof(InstScalars) / 4); i += TBF_THREADS)
-        reinterpret_cast<uint32_t *>(&st->sc)[i] = reinterpret_cast<const uint32_t *>(&sm.sc)[i];
     /* outside the live windows every ring slot is zero (cleared when read) */
-    for (int s = tid; s < TBF_VIB_BUF; s += TBF_THREADS) {
-        const uint32_t g = (sc.vibOutPos + (uint32_t)s) & 0x3FFu;
-        st->vibBuffer[g] = (s < VRING) ? sm.vring[g & VRING_MASK] : 0.0f;
-    }
     for (int line = 0; line < 4; ++line)
-        for (uint32_t s = tid; s < TBF_WHIRL_BUF; s += TBF_THREADS) {
-            const uint32_t g = (outpos0 + s) & GLOBAL_WBUF_MASK;
-            st->wbuf[line][g] = (s < ring_size) ? wring[line * ring_size + (g & rmask)] : 0.0f;
+        for (uint32_t s = lane; s < TBF_WHIRL_BUF; s += 32) {
+            const uint32_t g = (outpos0 + s) & WBUF_MASK;
+            st->wbuf[line][g] = (s < ring_size) ? ring[line * ring_size + (g & rmask)] : 0.0f;
         }
-    if (p.checksums) {
-        atomicAdd(&sm.csum, csum);
-        __syncthreads();
-        if (tid == 0)
-            p.checksums[slot] += sm.csum; /* zeroed by the host; accumulates over chunks */
+}
+
+/* ================================================================== */
+/* stage D: drum biquads (lane = instance) + output mix (lane = sample) */
+/* ================================================================== */
+
+struct DRow { /* what the mix needs of an instance's whirl table set */
+    float horn_level, leakage;
+    float hll, hlr, hrl, hrr, dll, dlr, drl, drr;
+    int bypass;
+};
+
+struct DSmem {
+    float tl[BLK * TILE_PITCH], tr[BLK * TILE_PITCH];
+    DRow row[BLK];
+    unsigned long long csum[BLK];
+};
+
+__global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
+{
+    __shared__ DSmem sm;
+    const int lane = threadIdx.x;
+    const uint32_t slot0 = blockIdx.x * 32;
+    const uint32_t slot = slot0 + lane;
+    const bool valid = slot < p.n_instances;
+    const uint32_t rows = min(32u, p.n_instances - slot0);
+    const bool whirl3 = (p.flags & TBF_RENDER_WHIRLPROC3) != 0;
+    const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
+
+    InstState *st = nullptr;
+    const DevWhirlTables *wh = p.wh;
+    float zl0 = 0.f, zl1 = 0.f, zr0 = 0.f, zr1 = 0.f;
+    if (valid) {
+        const uint32_t id = p.ids ? p.ids[slot] : slot;
+        st = p.states + id;
+        wh = p.wh + st->tg.whTables;
+        zl0 = st->dr.iirz[0][0];
+        zl1 = st->dr.iirz[0][1];
+        zr0 = st->dr.iirz[1][0];
+        zr1 = st->dr.iirz[1][1];
     }
+    const bool run = valid && !wh->bypass;
+    float cL[5], cR[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        cL[k] = wh->iir[2][k];
+        cR[k] = wh->iir[3][k];
+    }
+    {
+        DRow r;
+        r.horn_level = wh->horn_level;
+        r.leakage = wh->leakage;
+        r.hll = wh->mic_hll;
+        r.hlr = wh->mic_hlr;
+        r.hrl = wh->mic_hrl;
+        r.hrr = wh->mic_hrr;
+        r.dll = wh->mic_dll;
+        r.dlr = wh->mic_dlr;
+        r.drl = wh->mic_drl;
+        r.drr = wh->mic_drr;
+        r.bypass = wh->bypass;
+        sm.row[lane] = r;
+    }
+    sm.csum[lane] = 0ull;
+    __syncwarp();
+
+    const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+    for (uint32_t blk = 0; blk < n_blocks; ++blk) {
+        const size_t col0 = (size_t)blk * BLK;
+        for (uint32_t r = 0; r < rows; ++r) {
+            const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+            sm.tl[r * TILE_PITCH + lane] = p.line[2][g];
+            sm.tr[r * TILE_PITCH + lane] = p.line[3][g];
+        }
+        __syncwarp();
+        if (run) {
+#pragma unroll 4
+            for (int s = 0; s < BLK; ++s) {
+                sm.tl[lane * TILE_PITCH + s] = eq_iir(cL, zl0, zl1, sm.tl[lane * TILE_PITCH + s]);
+                sm.tr[lane * TILE_PITCH + s] = eq_iir(cR, zr0, zr1, sm.tr[lane * TILE_PITCH + s]);
+            }
+            if ((blk & 3u) == 3u) { /* end of a fragment: NaN scrub (src/whirl.cpp:1624-1625) */
+                zl0 = isnan(zl0) ? 0.0f : zl0;
+                zl1 = isnan(zl1) ? 0.0f : zl1;
+                zr0 = isnan(zr0) ? 0.0f : zr0;
+                zr1 = isnan(zr1) ? 0.0f : zr1;
+            }
+        }
+        __syncwarp();
+        for (uint32_t r = 0; r < rows; ++r) {
+            const DRow w = sm.row[r];
+            const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+            const float h0 = p.hx0[g];
+            float o_l, o_r;
+            if (w.bypass) {
+                /* bypassed Leslie: input copied to both horn outputs, drum silent
+                 * (src/whirl.cpp:1197-1215), then whirlProc3's mic mix (:1676-1680) */
+                if (!whirl3) {
+                    o_l = o_r = h0;
+                } else {
+                    o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, w.hll), __fmul_rn(h0, w.hlr)),
+                                              __fmul_rn(0.0f, w.dll)), __fmul_rn(0.0f, w.dlr));
+                    o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, w.hrl), __fmul_rn(h0, w.hrr)),
+                                              __fmul_rn(0.0f, w.drl)), __fmul_rn(0.0f, w.drr));
+                }
+            } else {
+                const float hl = p.line[0][g], hr = p.line[1][g];
+                const float yl = sm.tl[r * TILE_PITCH + lane], yr = sm.tr[r * TILE_PITCH + lane];
+                const float leak = __fmul_rn(h0, w.leakage);
+                const float hpl = __fmul_rn(w.horn_level, hl), hpr = __fmul_rn(w.horn_level, hr);
+                if (!whirl3) {
+                    o_l = __fadd_rn(__fadd_rn(yl, hpl), leak);
+                    o_r = __fadd_rn(__fadd_rn(yr, hpr), leak);
+                } else {
+                    const float ohl = __fadd_rn(hpl, leak), ohr = __fadd_rn(hpr, leak);
+                    o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, w.hll), __fmul_rn(ohr, w.hlr)),
+                                              __fmul_rn(yl, w.dll)), __fmul_rn(yr, w.dlr));
+                    o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, w.hrl), __fmul_rn(ohr, w.hrr)),
+                                              __fmul_rn(yl, w.drl)), __fmul_rn(yr, w.drr));
+                }
+            }
+            if (store) {
+                const size_t o = (size_t)(slot0 + r) * p.out_stride + col0 + lane;
+                p.out_l[o] = o_l;
+                p.out_r[o] = o_r;
+            }
+            if (p.checksums) {
+                const uint32_t pos = (uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + col0 + lane);
+                atomicAdd(&sm.csum[r], sample_hash(pos, o_l, o_r));
+            }
+        }
+        __syncwarp();
+    }
+
+    if (run) {
+        st->dr.iirz[0][0] = zl0;
+        st->dr.iirz[0][1] = zl1;
+        st->dr.iirz[1][0] = zr0;
+        st->dr.iirz[1][1] = zr1;
+    }
+    if (valid && p.checksums)
+        p.checksums[slot] += sm.csum[lane]; /* zeroed by the host; accumulates over chunks */
 }
 
 __global__ void tbf_replicate_kernel(InstState *states, uint32_t first, uint32_t count,
@@ -1230,22 +1463,58 @@ __global__ void tbf_replicate_kernel(InstState *states, uint32_t first, uint32_t
     }
 }
 
-} /* namespace */
-
-size_t tbf_render_smem_bytes(int ring_size) { return sizeof(Smem) + (size_t)4 * ring_size * sizeof(float); }
-
-int tbf_launch_render(const RenderParams &p, int ring_size, void *stream)
+template <typename K> int set_smem(K kernel, size_t smem, int *have)
 {
-    static int attr_set_for = 0;
-    const size_t smem = tbf_render_smem_bytes(ring_size);
-    if (attr_set_for < (int)smem) {
-        cudaError_t e = cudaFuncSetAttribute(tbf_render_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem);
+    if (*have < (int)smem) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess)
             return (int)e;
-        attr_set_for = (int)smem;
+        *have = (int)smem;
     }
-    tbf_render_kernel<<<p.n_instances, TBF_THREADS, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
+    return 0;
+}
+
+} /* namespace */
+
+size_t tbf_stage_t_smem(void) { return sizeof(TWarp) * T_WARPS; }
+size_t tbf_stage_w_smem(int ring_size)
+{
+    return (sizeof(WWarp) + (size_t)4 * ring_size * sizeof(float)) * W_WARPS;
+}
+
+int tbf_launch_stage_t(const RenderParams &p, void *stream)
+{
+    static int have = 0;
+    const size_t smem = tbf_stage_t_smem();
+    if (int rc = set_smem(tbf_stage_t, smem, &have))
+        return rc;
+    const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
+    tbf_stage_t<<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+int tbf_launch_stage_r(const RenderParams &p, void *stream)
+{
+    const uint32_t grid = (p.n_instances + 31) / 32;
+    tbf_stage_r<<<grid, 32, 0, (cudaStream_t)stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
+{
+    static int have = 0;
+    const size_t smem = tbf_stage_w_smem(ring_size);
+    if (int rc = set_smem(tbf_stage_w, smem, &have))
+        return rc;
+    const uint32_t grid = (p.n_instances + W_WARPS - 1) / W_WARPS;
+    tbf_stage_w<<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
+    return (int)cudaGetLastError();
+}
+
+int tbf_launch_stage_d(const RenderParams &p, void *stream)
+{
+    const uint32_t grid = (p.n_instances + 31) / 32;
+    tbf_stage_d<<<grid, 32, 0, (cudaStream_t)stream>>>(p);
     return (int)cudaGetLastError();
 }
 
