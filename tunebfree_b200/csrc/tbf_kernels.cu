@@ -31,6 +31,7 @@
  *   setters                     src/tonegen.cpp:1635-1765, :2738-2750; src/vibrato.cpp:95-142;
  *                               src/whirl.cpp:174-236
  */
+#include <cuda_pipeline.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -497,7 +498,65 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, TWar
     __syncwarp();
 }
 
-/* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples lane + 32k */
+/* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples lane + 32k.
+ * The wheel's four wave samples of this lane: one base address and immediate offsets
+ * when the 128-sample read does not wrap (uniform per wheel), a modular index else. */
+__device__ __forceinline__ void wave_fetch(const float *__restrict__ wave, const int4 ra, int lane,
+                                           float (&x)[4])
+{
+    const uint32_t len = (uint32_t)ra.y, pos = (uint32_t)ra.z;
+    const float *wp = wave + (uint32_t)ra.x;
+    if (pos + TBF_FRAGMENT <= len) {
+        const float *q = wp + (pos + (uint32_t)lane);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            x[k] = __ldg(q + 32 * k);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t j = pos + (uint32_t)lane + 32u * k;
+            if (j >= len)
+                j -= len;
+            x[k] = __ldg(wp + j);
+        }
+    }
+}
+
+/* one core-program record applied to the lane's four samples; FIRST: the first
+ * instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680) */
+template <bool FIRST>
+__device__ __forceinline__ void wheel_apply(const DevTonegenTables *tg, const TWarp &sm, int i, int lane,
+                                            const int env, const float (&x)[4], float (&s)[4],
+                                            float (&v)[4], float (&p)[4])
+{
+    const float4 rb = sm.recB[i];
+    float cs[4], cv[4], cp[4];
+    if (env >= 0) {
+        const float2 rc = sm.recC[i];
+        const float *ev = tg->env[env] + lane;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float e = __ldg(ev + 32 * k);
+            cs[k] = __fmul_rn(x[k], __fadd_rn(rb.x, __fmul_rn(e, rb.w)));
+            cv[k] = __fmul_rn(x[k], __fadd_rn(rb.y, __fmul_rn(e, rc.x)));
+            cp[k] = __fmul_rn(x[k], __fadd_rn(rb.z, __fmul_rn(e, rc.y)));
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            cs[k] = __fmul_rn(x[k], rb.x);
+            cv[k] = __fmul_rn(x[k], rb.y);
+            cp[k] = __fmul_rn(x[k], rb.z);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        s[k] = FIRST ? cs[k] : __fadd_rn(s[k], cs[k]);
+        v[k] = FIRST ? cv[k] : __fadd_rn(v[k], cv[k]);
+        p[k] = FIRST ? cp[k] : __fadd_rn(p[k], cp[k]);
+    }
+}
+
 __device__ __forceinline__ void core_interpreter(const DevTonegenTables *tg, const TWarp &sm, int lane,
                                                  float (&s)[4], float (&v)[4], float (&p)[4])
 {
@@ -506,54 +565,29 @@ __device__ __forceinline__ void core_interpreter(const DevTonegenTables *tg, con
 #pragma unroll
     for (int k = 0; k < 4; ++k)
         s[k] = v[k] = p[k] = 0.0f;
-    for (int i = 0; i < n_rec; ++i) {
-        const int4 ra = sm.recA[i];
-        const float4 rb = sm.recB[i];
-        const uint32_t len = (uint32_t)ra.y;
-        const float *wp = wave + (uint32_t)ra.x;
-        uint32_t idx = (uint32_t)ra.z + (uint32_t)lane;
-        float x[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            uint32_t j = idx + 32u * k;
-            if (j >= len)
-                j -= len;
-            x[k] = __ldg(wp + j);
+    if (n_rec == 0)
+        return;
+    /* the next wheel's samples are requested before the current wheel's arithmetic */
+    int4 ra = sm.recA[0];
+    float x[4];
+    wave_fetch(wave, ra, lane, x);
+    {
+        int env = ra.w;
+        float xc[4] = {x[0], x[1], x[2], x[3]};
+        if (n_rec > 1) {
+            ra = sm.recA[1];
+            wave_fetch(wave, ra, lane, x);
         }
-        float cs[4], cv[4], cp[4];
-        if (ra.w >= 0) {
-            const float2 rc = sm.recC[i];
-            const float *ev = tg->env[ra.w];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float e = __ldg(ev + lane + 32 * k);
-                cs[k] = __fmul_rn(x[k], __fadd_rn(rb.x, __fmul_rn(e, rb.w)));
-                cv[k] = __fmul_rn(x[k], __fadd_rn(rb.y, __fmul_rn(e, rc.x)));
-                cp[k] = __fmul_rn(x[k], __fadd_rn(rb.z, __fmul_rn(e, rc.y)));
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                cs[k] = __fmul_rn(x[k], rb.x);
-                cv[k] = __fmul_rn(x[k], rb.y);
-                cp[k] = __fmul_rn(x[k], rb.z);
-            }
+        wheel_apply<true>(tg, sm, 0, lane, env, xc, s, v, p);
+    }
+    for (int i = 1; i < n_rec; ++i) {
+        const int env = ra.w;
+        const float xc[4] = {x[0], x[1], x[2], x[3]};
+        if (i + 1 < n_rec) {
+            ra = sm.recA[i + 1];
+            wave_fetch(wave, ra, lane, x);
         }
-        if (i == 0) { /* first instruction of a fragment copies, the rest add */
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                s[k] = cs[k];
-                v[k] = cv[k];
-                p[k] = cp[k];
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                s[k] = __fadd_rn(s[k], cs[k]);
-                v[k] = __fadd_rn(v[k], cv[k]);
-                p[k] = __fadd_rn(p[k], cp[k]);
-            }
-        }
+        wheel_apply<false>(tg, sm, i, lane, env, xc, s, v, p);
     }
 }
 
@@ -844,15 +878,28 @@ __device__ __forceinline__ float eq_iir(const float (&c)[5], float &z0, float &z
 }
 
 struct RSmem {
-    float tin[2][BLK * TILE_PITCH];   /* u, php            (row = instance, col = sample) */
+    float tin[2][2][BLK * TILE_PITCH]; /* [buffer][u, php] (row = instance, col = sample);
+                                          filled by cp.async one block ahead of its use   */
     float tout[2][BLK * TILE_PITCH];  /* dx0 | mono, hx0                                 */
     double tang[2][BLK * TILE_PITCH]; /* horn, drum angle                                */
-    unsigned long long csum[BLK];
+    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums  */
 };
+
+/* request one 32 x 32 block of u and php: element (row r, sample lane) by cp.async */
+__device__ __forceinline__ void r_tile_fetch(const RenderParams &p, float (*tile)[BLK * TILE_PITCH],
+                                             uint32_t slot0, uint32_t rows, size_t col0, int lane)
+{
+    for (uint32_t r = 0; r < rows; ++r) {
+        const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+        __pipeline_memcpy_async(&tile[0][r * TILE_PITCH + lane], p.u + g, 4);
+        __pipeline_memcpy_async(&tile[1][r * TILE_PITCH + lane], p.php + g, 4);
+    }
+}
 
 __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
 {
-    __shared__ RSmem sm;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    RSmem &sm = *reinterpret_cast<RSmem *>(smem_raw);
     const int lane = threadIdx.x;
     const uint32_t slot0 = blockIdx.x * 32;
     const uint32_t slot = slot0 + lane;
@@ -888,7 +935,11 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         ev_cur = p.ev_cursor_r[slot];
         ev_end = p.ev_start[slot + 1];
     }
-    sm.csum[lane] = 0ull;
+    for (int r = 0; r < BLK; ++r)
+        sm.csum[r][lane] = 0ull;
+    const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+    r_tile_fetch(p, sm.tin[0], slot0, rows, 0, lane);
+    __pipeline_commit();
     __syncwarp();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
@@ -936,20 +987,23 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
 
         for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
-            const size_t col0 = (size_t)f * TBF_FRAGMENT + (size_t)blk * BLK;
-            /* tile in: row r = instance slot0 + r, this lane = sample col0 + lane */
-            for (uint32_t r = 0; r < rows; ++r) {
-                const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
-                sm.tin[0][r * TILE_PITCH + lane] = p.u[g];
-                sm.tin[1][r * TILE_PITCH + lane] = p.php[g];
-            }
+            const uint32_t gb = f * (TBF_FRAGMENT / BLK) + (uint32_t)blk;
+            const size_t col0 = (size_t)gb * BLK;
+            const int cur = (int)(gb & 1u);
+            /* tile in: row r = instance slot0 + r, this lane = sample col0 + lane; the
+             * next block's tiles are requested before this block's serial loop */
+            if (gb + 1 < n_blocks)
+                r_tile_fetch(p, sm.tin[cur ^ 1], slot0, rows, (size_t)(gb + 1) * BLK, lane);
+            __pipeline_commit();
+            __pipeline_wait_prior(1);
             __syncwarp();
+            const float *t_u = sm.tin[cur][0], *t_p = sm.tin[cur][1];
 #pragma unroll 4
             for (int s = 0; s < BLK; ++s) {
-                const float uu = sm.tin[0][lane * TILE_PITCH + s];
+                const float uu = t_u[lane * TILE_PITCH + s];
                 float mono;
                 if (perc_on) {
-                    const float pterm = __fmul_rn(sm.tin[1][lane * TILE_PITCH + s], pg);
+                    const float pterm = __fmul_rn(t_p[lane * TILE_PITCH + s], pg);
                     mono = __fmul_rn(__fmul_rn(c.gain, kc), __fadd_rn(uu, pterm));
                     pg = __fmul_rn(pg, c.decay);
                 } else {
@@ -993,7 +1047,7 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
                     }
                     if (p.checksums) {
                         const uint32_t pos = (uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + col0 + lane);
-                        atomicAdd(&sm.csum[r], sample_hash(pos, m, m));
+                        sm.csum[r][lane] += sample_hash(pos, m, m);
                     }
                 }
             } else {
@@ -1033,8 +1087,12 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         rp.drumAngle = dang;
         st->rp = rp;
         p.ev_cursor_r[slot] = ev_cur;
-        if (p.checksums && whirl_off)
-            p.checksums[slot] += sm.csum[lane]; /* zeroed by the host; accumulates over chunks */
+        if (p.checksums && whirl_off) {
+            unsigned long long c = 0ull;
+            for (int j = 0; j < BLK; ++j)
+                c += sm.csum[lane][(j + lane) & (BLK - 1)];
+            p.checksums[slot] += c; /* zeroed by the host; accumulates over chunks */
+        }
     }
 }
 
@@ -1077,23 +1135,64 @@ __device__ __forceinline__ void tap_position(double ang_grd, int phase, const fl
     slot = f2u_x86(r) & WBUF_MASK;
 }
 
-/* What the parallel delay-line update relies on, checked per block: per tap the
- * destination slots advance monotonically with the sample index and stay inside
- * [reader, reader + window). */
-__device__ __forceinline__ int taps_bad(const DevWhirlTables *wh, const WWarp &sm, int lane,
-                                        uint32_t outpos_blk)
+/* ordered_pass() for one tap held in registers (lane = sample), neighbours by shuffle.
+ * Requires what tap_bad() checks: slots never decrease and at most two consecutive
+ * samples share a slot. */
+__device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const float a, const float b,
+                                                 float *ring, const uint32_t rmask, const int lane)
 {
-    int bad = 0;
-    const uint32_t window = (uint32_t)wh->window;
-#pragma unroll
-    for (int q = 0; q < 6; ++q) {
-        const uint32_t n = sm.tn[q][lane];
-        const uint32_t rel = (n - outpos_blk) & WBUF_MASK;
-        bad |= (rel < (uint32_t)lane) | (rel + 1 >= window);
-        if (lane > 0)
-            bad |= ((n - (uint32_t)sm.tn[q][lane - 1]) & WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
+    const uint32_t n1 = __shfl_up_sync(FULL, n, 1), n2 = __shfl_up_sync(FULL, n, 2);
+    const uint32_t nx = __shfl_down_sync(FULL, n, 1);
+    const float b1 = __shfl_up_sync(FULL, b, 1), b2 = __shfl_up_sync(FULL, b, 2);
+    const float ax = __shfl_down_sync(FULL, a, 1);
+    const bool has1 = lane >= 1, has2 = lane >= 2, hasx = lane < BLK - 1;
+    if (!has1 || n1 != n) { /* first sample of the run hitting slot n */
+        float v = ring[n & rmask];
+        const uint32_t sm1 = (n - 1) & WBUF_MASK;
+        if (has2 && n2 == sm1)
+            v = __fadd_rn(v, b2);
+        if (has1 && n1 == sm1)
+            v = __fadd_rn(v, b1);
+        v = __fadd_rn(v, a);
+        if (hasx && nx == n)
+            v = __fadd_rn(v, ax);
+        ring[n & rmask] = v;
     }
+    if (!hasx || nx != n) { /* last sample of its run */
+        const uint32_t sp1 = (n + 1) & WBUF_MASK;
+        if (!hasx || nx != sp1) { /* nobody hits n+1 as a main slot in this block */
+            float v = ring[sp1 & rmask];
+            if (has1 && n1 == n)
+                v = __fadd_rn(v, b1);
+            v = __fadd_rn(v, b);
+            ring[sp1 & rmask] = v;
+        }
+    }
+}
+
+/* What the parallel delay-line update relies on, checked per block and tap: the
+ * destination slots advance monotonically with the sample index, at most two samples
+ * share a slot, and all stay inside [reader, reader + window). */
+__device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t window, const int lane,
+                                       const uint32_t outpos_blk)
+{
+    const uint32_t rel = (n - outpos_blk) & WBUF_MASK;
+    int bad = (rel < (uint32_t)lane) | (rel + 1 >= window);
+    const uint32_t n1 = __shfl_up_sync(FULL, n, 1), n2 = __shfl_up_sync(FULL, n, 2);
+    if (lane >= 1)
+        bad |= ((n - n1) & WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
+    if (lane >= 2)
+        bad |= (n2 == n);
     return bad;
+}
+
+__device__ __forceinline__ uint32_t sel3(int q, uint32_t v0, uint32_t v1, uint32_t v2)
+{
+    return q == 0 ? v0 : (q == 1 ? v1 : v2);
+}
+__device__ __forceinline__ float sel3(int q, float v0, float v1, float v2)
+{
+    return q == 0 ? v0 : (q == 1 ? v1 : v2);
 }
 
 /* Scatter the six taps of one group (horn: taps 0..5 -> HL, HR; drum: 6..11 -> DL, DR)
@@ -1101,21 +1200,22 @@ __device__ __forceinline__ int taps_bad(const DevWhirlTables *wh, const WWarp &s
  * outputs.  Even taps feed the left line, odd taps the right one. */
 __device__ __forceinline__ void group_scatter_read(const DevWhirlTables *wh, WWarp &sm, float *ring_l,
                                                    float *ring_r, uint32_t rmask, int line0, int lane,
-                                                   uint32_t outpos_blk, bool gather_ok, int &fell_back,
-                                                   float &out_l, float &out_r)
+                                                   uint32_t outpos_blk, int bad, int &fell_back,
+                                                   const uint32_t (&tn)[6], const float (&ta)[6],
+                                                   const float (&tb)[6], float &out_l, float &out_r)
 {
-    int bad = 1;
-    if (gather_ok)
-        bad = taps_bad(wh, sm, lane, outpos_blk);
     bad = __any_sync(FULL, bad);
     const uint32_t op = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
     if (!bad) {
         const int tap0 = line0 * 3; /* first tap id of the group: 0 (horn) or 6 (drum) */
 #pragma unroll
         for (int j = 0; j < 3; ++j) { /* the three taps of a line: farthest delay first */
-            const int ql = wh->tap_order[line0][j] - tap0, qr = wh->tap_order[line0 + 1][j] - tap0;
-            ordered_pass(sm.tn[ql], sm.ta[ql], sm.tb[ql], ring_l, rmask, WBUF_MASK, lane);
-            ordered_pass(sm.tn[qr], sm.ta[qr], sm.tb[qr], ring_r, rmask, WBUF_MASK, lane);
+            const int ql = (wh->tap_order[line0][j] - tap0) >> 1;
+            const int qr = (wh->tap_order[line0 + 1][j] - tap0) >> 1;
+            ordered_pass_reg(sel3(ql, tn[0], tn[2], tn[4]), sel3(ql, ta[0], ta[2], ta[4]),
+                             sel3(ql, tb[0], tb[2], tb[4]), ring_l, rmask, lane);
+            ordered_pass_reg(sel3(qr, tn[1], tn[3], tn[5]), sel3(qr, ta[1], ta[3], ta[5]),
+                             sel3(qr, tb[1], tb[3], tb[5]), ring_r, rmask, lane);
             __syncwarp();
         }
         out_l = ring_l[op & rmask];
@@ -1125,7 +1225,14 @@ __device__ __forceinline__ void group_scatter_read(const DevWhirlTables *wh, WWa
     } else {
         /* the reference's loop as written, one lane per delay line: geometries / rotor
          * speeds the parallel passes do not cover */
-        fell_back |= gather_ok ? 1 : 0;
+        fell_back |= wh->gather_ok ? 1 : 0;
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            sm.tn[q][lane] = (uint16_t)tn[q];
+            sm.ta[q][lane] = ta[q];
+            sm.tb[q][lane] = tb[q];
+        }
+        __syncwarp();
         if (lane < 2) {
             float *buf = lane ? ring_r : ring_l;
             for (int i = 0; i < BLK; ++i) {
@@ -1180,6 +1287,7 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
     if (lane < 4)
         sm.zs[lane] = ws.z[lane];
     const bool gather_ok = wh->gather_ok != 0;
+    const uint32_t window = (uint32_t)wh->window;
     int fell_back = 0;
     const size_t row = (size_t)slot * p.pitch;
     __syncwarp();
@@ -1222,6 +1330,9 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
             const uint32_t outpos = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
             const double hang = p.hang[col + i], dang = p.dang[col + i];
             /* -- horn taps: geometry + 5-tap FIR (src/whirl.cpp:1432-1453, :1540-1563) -- */
+            uint32_t tn[6];
+            float ta[6], tb[6];
+            int bad = gather_ok ? 0 : 1;
 #pragma unroll
             for (int q = 0; q < 6; ++q) {
                 /* taps 0,3,4 read the forward displacement table with the backward FIR
@@ -1231,8 +1342,8 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
                 const float *bw = fwd ? wh->bbw : wh->bfw;
                 const double ang = __dadd_rn(hang, (q & 1) ? wh->bw_ang : wh->fw_ang);
                 float frac;
-                uint32_t slot_n, kr;
-                tap_position(ang, wh->horn_phase[q], dsp, wh->horn_spacing[q], outpos, frac, slot_n, kr);
+                uint32_t kr;
+                tap_position(ang, wh->horn_phase[q], dsp, wh->horn_spacing[q], outpos, frac, tn[q], kr);
                 const float *hx = &sm.hx[q >> 1][8 + i];
                 const float *b = bw + 5 * kr;
                 float xa = __fmul_rn(__ldg(b + 0), hx[0]);
@@ -1241,31 +1352,30 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
                 xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 3), hx[-3]));
                 xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 4), hx[-4]));
                 const float qq = __fmul_rn(xa, frac);
-                sm.tn[q][lane] = (uint16_t)slot_n;
-                sm.ta[q][lane] = __fsub_rn(xa, qq);
-                sm.tb[q][lane] = qq;
+                ta[q] = __fsub_rn(xa, qq);
+                tb[q] = qq;
+                bad |= tap_bad(tn[q], window, lane, outpos_blk);
             }
-            __syncwarp();
             float hl, hr, dl, dr;
-            group_scatter_read(wh, sm, ring, ring + ring_size, rmask, 0, lane, outpos_blk, gather_ok,
-                               fell_back, hl, hr);
+            group_scatter_read(wh, sm, ring, ring + ring_size, rmask, 0, lane, outpos_blk, bad,
+                               fell_back, tn, ta, tb, hl, hr);
             /* -- drum taps (src/whirl.cpp:1455-1469, :1566-1588) -- */
+            bad = gather_ok ? 0 : 1;
 #pragma unroll
             for (int q = 0; q < 6; ++q) {
                 const bool fwd = (q == 0 || q == 3 || q == 4);
                 const float *dsp = fwd ? wh->dr_fwd_displ : wh->dr_bwd_displ;
                 float frac;
-                uint32_t slot_n, kr;
-                tap_position(dang, wh->drum_phase[q], dsp, wh->drum_spacing[q], outpos, frac, slot_n, kr);
+                uint32_t kr;
+                tap_position(dang, wh->drum_phase[q], dsp, wh->drum_spacing[q], outpos, frac, tn[q], kr);
                 const float x = sm.dx[q >> 1][4 + i];
                 const float qq = __fmul_rn(x, frac);
-                sm.tn[q][lane] = (uint16_t)slot_n;
-                sm.ta[q][lane] = __fsub_rn(x, qq);
-                sm.tb[q][lane] = qq;
+                ta[q] = __fsub_rn(x, qq);
+                tb[q] = qq;
+                bad |= tap_bad(tn[q], window, lane, outpos_blk);
             }
-            __syncwarp();
             group_scatter_read(wh, sm, ring + 2 * ring_size, ring + 3 * ring_size, rmask, 2, lane,
-                               outpos_blk, gather_ok, fell_back, dl, dr);
+                               outpos_blk, bad, fell_back, tn, ta, tb, dl, dr);
             p.line[0][col + i] = hl;
             p.line[1][col + i] = hr;
             p.line[2][col + i] = dl;
@@ -1320,14 +1430,31 @@ struct DRow { /* what the mix needs of an instance's whirl table set */
 };
 
 struct DSmem {
-    float tl[BLK * TILE_PITCH], tr[BLK * TILE_PITCH];
+    float t[2][5][BLK * TILE_PITCH]; /* [buffer][DL DR HL HR hx0], filled by cp.async one
+                                        block ahead of its use                             */
     DRow row[BLK];
-    unsigned long long csum[BLK];
+    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums */
 };
+
+/* request one 32 x 32 block of the five streams stage D reads */
+__device__ __forceinline__ void d_tile_fetch(const RenderParams &p, float (*tile)[BLK * TILE_PITCH],
+                                             uint32_t slot0, uint32_t rows, size_t col0, int lane)
+{
+    for (uint32_t r = 0; r < rows; ++r) {
+        const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+        const int o = r * TILE_PITCH + lane;
+        __pipeline_memcpy_async(&tile[0][o], p.line[2] + g, 4);
+        __pipeline_memcpy_async(&tile[1][o], p.line[3] + g, 4);
+        __pipeline_memcpy_async(&tile[2][o], p.line[0] + g, 4);
+        __pipeline_memcpy_async(&tile[3][o], p.line[1] + g, 4);
+        __pipeline_memcpy_async(&tile[4][o], p.hx0 + g, 4);
+    }
+}
 
 __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
 {
-    __shared__ DSmem sm;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    DSmem &sm = *reinterpret_cast<DSmem *>(smem_raw);
     const int lane = threadIdx.x;
     const uint32_t slot0 = blockIdx.x * 32;
     const uint32_t slot = slot0 + lane;
@@ -1370,23 +1497,28 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         r.bypass = wh->bypass;
         sm.row[lane] = r;
     }
-    sm.csum[lane] = 0ull;
+    for (int r = 0; r < BLK; ++r)
+        sm.csum[r][lane] = 0ull;
     __syncwarp();
 
     const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+    d_tile_fetch(p, sm.t[0], slot0, rows, 0, lane);
+    __pipeline_commit();
     for (uint32_t blk = 0; blk < n_blocks; ++blk) {
         const size_t col0 = (size_t)blk * BLK;
-        for (uint32_t r = 0; r < rows; ++r) {
-            const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
-            sm.tl[r * TILE_PITCH + lane] = p.line[2][g];
-            sm.tr[r * TILE_PITCH + lane] = p.line[3][g];
-        }
+        const int cur = (int)(blk & 1u);
+        if (blk + 1 < n_blocks)
+            d_tile_fetch(p, sm.t[cur ^ 1], slot0, rows, (size_t)(blk + 1) * BLK, lane);
+        __pipeline_commit();
+        __pipeline_wait_prior(1);
         __syncwarp();
+        float *tl = sm.t[cur][0], *tr = sm.t[cur][1];
+        const float *thl = sm.t[cur][2], *thr = sm.t[cur][3], *th0 = sm.t[cur][4];
         if (run) {
 #pragma unroll 4
             for (int s = 0; s < BLK; ++s) {
-                sm.tl[lane * TILE_PITCH + s] = eq_iir(cL, zl0, zl1, sm.tl[lane * TILE_PITCH + s]);
-                sm.tr[lane * TILE_PITCH + s] = eq_iir(cR, zr0, zr1, sm.tr[lane * TILE_PITCH + s]);
+                tl[lane * TILE_PITCH + s] = eq_iir(cL, zl0, zl1, tl[lane * TILE_PITCH + s]);
+                tr[lane * TILE_PITCH + s] = eq_iir(cR, zr0, zr1, tr[lane * TILE_PITCH + s]);
             }
             if ((blk & 3u) == 3u) { /* end of a fragment: NaN scrub (src/whirl.cpp:1624-1625) */
                 zl0 = isnan(zl0) ? 0.0f : zl0;
@@ -1398,8 +1530,7 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         __syncwarp();
         for (uint32_t r = 0; r < rows; ++r) {
             const DRow w = sm.row[r];
-            const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
-            const float h0 = p.hx0[g];
+            const float h0 = th0[r * TILE_PITCH + lane];
             float o_l, o_r;
             if (w.bypass) {
                 /* bypassed Leslie: input copied to both horn outputs, drum silent
@@ -1413,8 +1544,8 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
                                               __fmul_rn(0.0f, w.drl)), __fmul_rn(0.0f, w.drr));
                 }
             } else {
-                const float hl = p.line[0][g], hr = p.line[1][g];
-                const float yl = sm.tl[r * TILE_PITCH + lane], yr = sm.tr[r * TILE_PITCH + lane];
+                const float hl = thl[r * TILE_PITCH + lane], hr = thr[r * TILE_PITCH + lane];
+                const float yl = tl[r * TILE_PITCH + lane], yr = tr[r * TILE_PITCH + lane];
                 const float leak = __fmul_rn(h0, w.leakage);
                 const float hpl = __fmul_rn(w.horn_level, hl), hpr = __fmul_rn(w.horn_level, hr);
                 if (!whirl3) {
@@ -1435,7 +1566,7 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
             }
             if (p.checksums) {
                 const uint32_t pos = (uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + col0 + lane);
-                atomicAdd(&sm.csum[r], sample_hash(pos, o_l, o_r));
+                sm.csum[r][lane] += sample_hash(pos, o_l, o_r);
             }
         }
         __syncwarp();
@@ -1447,8 +1578,12 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         st->dr.iirz[1][0] = zr0;
         st->dr.iirz[1][1] = zr1;
     }
-    if (valid && p.checksums)
-        p.checksums[slot] += sm.csum[lane]; /* zeroed by the host; accumulates over chunks */
+    if (valid && p.checksums) {
+        unsigned long long c = 0ull;
+        for (int j = 0; j < BLK; ++j)
+            c += sm.csum[lane][(j + lane) & (BLK - 1)];
+        p.checksums[slot] += c; /* zeroed by the host; accumulates over chunks */
+    }
 }
 
 __global__ void tbf_replicate_kernel(InstState *states, uint32_t first, uint32_t count,
@@ -1495,8 +1630,11 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
 
 int tbf_launch_stage_r(const RenderParams &p, void *stream)
 {
+    static int have = 0;
+    if (int rc = set_smem(tbf_stage_r, sizeof(RSmem), &have))
+        return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    tbf_stage_r<<<grid, 32, 0, (cudaStream_t)stream>>>(p);
+    tbf_stage_r<<<grid, 32, sizeof(RSmem), (cudaStream_t)stream>>>(p);
     return (int)cudaGetLastError();
 }
 
@@ -1513,8 +1651,11 @@ int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
 
 int tbf_launch_stage_d(const RenderParams &p, void *stream)
 {
+    static int have = 0;
+    if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), &have))
+        return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    tbf_stage_d<<<grid, 32, 0, (cudaStream_t)stream>>>(p);
+    tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
     return (int)cudaGetLastError();
 }
 
