@@ -37,6 +37,7 @@ struct StageScratch {
     size_t cap_ctl = 0, cap_f32 = 0, cap_f64 = 0;
 };
 
+#define TBF_MAX_GROUPS 4
 #define TBF_SCAT_BLOCK 32 /* samples the kernels scatter before they read (tbf_kernels.cu BLK) */
 
 struct tbf_ctx {
@@ -72,6 +73,11 @@ struct tbf_ctx {
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     uint64_t *d_ev_cursor = nullptr; /* [2][cap_slots]: stage T, stage R */
     StageScratch scratch;
+    /* instance groups: each renders its share of a batch on its own stream, so the
+     * latency-bound lane = instance stages of one group overlap the others' stages */
+    cudaStream_t gstream[TBF_MAX_GROUPS] = {};
+    cudaEvent_t gdone[TBF_MAX_GROUPS] = {};
+    cudaEvent_t fork = nullptr;
     size_t scratch_budget = (size_t)4 << 30; /* bytes of HBM the stage streams may take */
     uint32_t max_stage_chunk = 64;           /* fragments per stage-kernel launch       */
     bool in_flight = false;
@@ -120,6 +126,14 @@ int tbf_gpu_create(tbf_ctx **out, int device)
         delete ctx;
         return TBF_ERR_CUDA;
     }
+    bool ok = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g)
+        ok = cudaStreamCreateWithFlags(&ctx->gstream[g], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ctx->gdone[g], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+        delete ctx;
+        return TBF_ERR_CUDA;
+    }
     *out = ctx;
     return TBF_OK;
 }
@@ -161,6 +175,14 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     }
     cudaEventDestroy(ctx->t0);
     cudaEventDestroy(ctx->t1);
+    for (int g = 0; g < TBF_MAX_GROUPS; ++g) {
+        if (ctx->gstream[g])
+            cudaStreamDestroy(ctx->gstream[g]);
+        if (ctx->gdone[g])
+            cudaEventDestroy(ctx->gdone[g]);
+    }
+    if (ctx->fork)
+        cudaEventDestroy(ctx->fork);
     cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -737,75 +759,99 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
         }
     }
 
-    RenderParams p;
-    memset(&p, 0, sizeof(p));
-    p.states = ctx->d_states;
-    p.ids = ctx->prepared_has_ids ? ctx->d_ids : nullptr;
-    p.tg = ctx->d_tg;
-    p.wh = ctx->d_wh;
-    p.events = ctx->d_events;
-    p.ev_start = ctx->d_ev_start;
-    p.ev_cursor_t = cur_t;
-    p.ev_cursor_r = cur_r;
-    p.checksums = d->checksums ? ctx->d_csum : nullptr;
-    p.n_instances = d->n_instances;
-    p.flags = d->flags;
-    p.ctl = ss.ctl;
-    p.pitch = pitch;
-    p.u = ss.f32;
-    p.php = ss.f32 + n * pitch;
-    if (whirl) {
-        p.dx0 = ss.f32 + 2 * n * pitch;
-        p.hx0 = ss.f32 + 3 * n * pitch;
-        for (int l = 0; l < 4; ++l)
-            p.line[l] = ss.f32 + (4 + l) * n * pitch;
-        p.hang = ss.f64;
-        p.dang = ss.f64 + n * pitch;
+    /* instance groups (multiples of 32 slots, so the lane = instance warps stay full) */
+    int n_groups = n >= 2048 ? 4 : (n >= 512 ? 2 : 1);
+    uint32_t gfirst[TBF_MAX_GROUPS + 1];
+    {
+        const uint32_t per = (uint32_t)(((n + n_groups - 1) / n_groups + 31) / 32 * 32);
+        for (int g = 0; g <= n_groups; ++g)
+            gfirst[g] = (uint32_t)std::min<size_t>(n, (size_t)per * g);
     }
+
+    RenderParams base_p;
+    memset(&base_p, 0, sizeof(base_p));
+    base_p.states = ctx->d_states;
+    base_p.tg = ctx->d_tg;
+    base_p.wh = ctx->d_wh;
+    base_p.events = ctx->d_events;
+    base_p.flags = d->flags;
+    base_p.pitch = pitch;
     ctx->launches = 0;
     int ring = 512; /* shared-memory delay-line ring: the largest any table set needs */
     for (auto &w : ctx->wh)
         ring = std::max(ring, w.ring_size);
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    CK(cudaEventRecord(ctx->fork, ctx->stream));
+    for (int g = 0; g < n_groups; ++g)
+        CK(cudaStreamWaitEvent(ctx->gstream[g], ctx->fork, 0));
     const size_t half = (size_t)2 * n * chunk * TBF_FRAGMENT;
     int k = 0;
     for (uint32_t base = 0; base < d->n_fragments; base += chunk, ++k) {
         const uint32_t nf = std::min<uint32_t>(chunk, d->n_fragments - base);
         const int buf = k & 1;
         float *out_l, *out_r;
+        uint64_t out_stride;
         if (host_out) {
-            /* staging buffer `buf` is free once the copy issued two chunks ago is done */
-            if (k >= 2)
-                CK(cudaStreamWaitEvent(ctx->stream, ctx->copy_done[buf], 0));
-            p.out_stride = (uint64_t)nf * TBF_FRAGMENT;
+            out_stride = (uint64_t)nf * TBF_FRAGMENT;
             out_l = ctx->d_out + half * buf;
-            out_r = out_l + n * p.out_stride;
+            out_r = out_l + n * out_stride;
         } else {
-            p.out_stride = d->out_stride;
+            out_stride = d->out_stride;
             out_l = no_out ? nullptr : d->out_l + (size_t)base * TBF_FRAGMENT;
             out_r = no_out ? nullptr : d->out_r + (size_t)base * TBF_FRAGMENT;
         }
-        for (uint32_t ib = 0; ib < nf; ib += sc_frag) {
-            p.frag_base = base + ib;
-            p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
-            p.out_l = out_l ? out_l + (size_t)ib * TBF_FRAGMENT : nullptr;
-            p.out_r = out_r ? out_r + (size_t)ib * TBF_FRAGMENT : nullptr;
-            int rc = tbf_launch_stage_t(p, ctx->stream);
-            if (rc == 0)
-                rc = tbf_launch_stage_r(p, ctx->stream);
-            if (rc == 0 && whirl)
-                rc = tbf_launch_stage_w(p, ring, ctx->stream);
-            if (rc == 0 && whirl)
-                rc = tbf_launch_stage_d(p, ctx->stream);
-            if (rc != 0) {
-                ctx->err = std::string("stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
-                return TBF_ERR_CUDA;
+        for (int g = 0; g < n_groups; ++g) {
+            const size_t s0 = gfirst[g];
+            const uint32_t ng = gfirst[g + 1] - gfirst[g];
+            if (!ng)
+                continue;
+            cudaStream_t st = ctx->gstream[g];
+            /* staging buffer `buf` is free once the copy issued two chunks ago is done */
+            if (host_out && k >= 2)
+                CK(cudaStreamWaitEvent(st, ctx->copy_done[buf], 0));
+            RenderParams p = base_p;
+            p.n_instances = ng;
+            p.ids = ctx->prepared_has_ids ? ctx->d_ids + s0 : nullptr;
+            p.id_base = (uint32_t)s0;
+            p.ev_start = ctx->d_ev_start + s0;
+            p.ev_cursor_t = cur_t + s0;
+            p.ev_cursor_r = cur_r + s0;
+            p.checksums = d->checksums ? ctx->d_csum + s0 : nullptr;
+            p.out_stride = out_stride;
+            p.ctl = ss.ctl + s0 * sc_frag;
+            p.u = ss.f32 + s0 * pitch;
+            p.php = ss.f32 + (n + s0) * pitch;
+            if (whirl) {
+                p.dx0 = ss.f32 + (2 * n + s0) * pitch;
+                p.hx0 = ss.f32 + (3 * n + s0) * pitch;
+                for (int l = 0; l < 4; ++l)
+                    p.line[l] = ss.f32 + ((4 + l) * n + s0) * pitch;
+                p.hang = ss.f64 + s0 * pitch;
+                p.dang = ss.f64 + (n + s0) * pitch;
             }
-            ctx->launches += whirl ? 4 : 2;
+            for (uint32_t ib = 0; ib < nf; ib += sc_frag) {
+                p.frag_base = base + ib;
+                p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
+                p.out_l = out_l ? out_l + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
+                p.out_r = out_r ? out_r + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
+                int rc = tbf_launch_stage_t(p, st);
+                if (rc == 0)
+                    rc = tbf_launch_stage_r(p, st);
+                if (rc == 0 && whirl)
+                    rc = tbf_launch_stage_w(p, ring, st);
+                if (rc == 0 && whirl)
+                    rc = tbf_launch_stage_d(p, st);
+                if (rc != 0) {
+                    ctx->err = std::string("stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
+                    return TBF_ERR_CUDA;
+                }
+                ctx->launches += whirl ? 4 : 2;
+            }
+            CK(cudaEventRecord(ctx->gdone[g], st));
+            if (host_out)
+                CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->gdone[g], 0));
         }
         if (host_out) {
-            CK(cudaEventRecord(ctx->render_done[buf], ctx->stream));
-            CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->render_done[buf], 0));
             const size_t w = sizeof(float) * (size_t)nf * TBF_FRAGMENT;
             CK(cudaMemcpy2DAsync(d->out_l + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
                                  out_l, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
@@ -814,6 +860,8 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             CK(cudaEventRecord(ctx->copy_done[buf], ctx->copy_stream));
         }
     }
+    for (int g = 0; g < n_groups; ++g)
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->gdone[g], 0));
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     if (d->checksums)
         CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * n,

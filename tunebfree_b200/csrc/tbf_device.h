@@ -170,7 +170,8 @@ struct __align__(16) FragCtl {
 
 struct RenderParams {
     InstState *states;
-    const uint32_t *ids;       /* NULL = identity */
+    const uint32_t *ids;       /* NULL = identity: instance = id_base + slot */
+    uint32_t id_base;
     const DevTonegenTables *tg;
     const DevWhirlTables *wh;
     const tbf_event *events;

@@ -654,7 +654,7 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
     if (slot >= p.n_instances)
         return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
     TWarp &sm = reinterpret_cast<TWarp *>(smem_raw)[warp];
-    const uint32_t id = p.ids ? p.ids[slot] : slot;
+    const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
     InstState *st = p.states + id;
     TgScalars &sc = sm.sc;
 
@@ -912,7 +912,7 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
     const DevWhirlTables *wh = p.wh;
     RampScalars rp;
     if (valid) {
-        const uint32_t id = p.ids ? p.ids[slot] : slot;
+        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
         st = p.states + id;
         rp = st->rp;
         wh = p.wh + st->tg.whTables;
@@ -1267,7 +1267,7 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
     WWarp &sm = *reinterpret_cast<WWarp *>(smem_raw + per_warp * warp);
     float *ring = reinterpret_cast<float *>(smem_raw + per_warp * warp + sizeof(WWarp));
     const uint32_t rmask = ring_size - 1;
-    const uint32_t id = p.ids ? p.ids[slot] : slot;
+    const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
     InstState *st = p.states + id;
     const DevWhirlTables *wh = p.wh + st->tg.whTables;
     if (wh->bypass)
@@ -1467,7 +1467,7 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
     const DevWhirlTables *wh = p.wh;
     float zl0 = 0.f, zl1 = 0.f, zr0 = 0.f, zr1 = 0.f;
     if (valid) {
-        const uint32_t id = p.ids ? p.ids[slot] : slot;
+        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
         st = p.states + id;
         wh = p.wh + st->tg.whTables;
         zl0 = st->dr.iirz[0][0];
