@@ -122,17 +122,20 @@ __device__ __forceinline__ void ordered_pass(const uint16_t *n, const float *a, 
 /* One entry of the per-fragment "core program": the reference emits 1-2 CoreIns per
  * active wheel (src/tonegen.h:114-129); with a modular index the wrap split collapses
  * and one record per wheel suffices. */
+#define REC_TILE 64    /* active-list entries turned into records and summed at a time */
+#define WAVE_STAGES 8  /* wheels whose wave samples are in flight (cp.async) per warp   */
 struct TWarp {
     TgScalars sc;
-    int4 recA[TBF_NOF_WHEELS + 1];   /* wave_off, len, pos, env (-1 plain, 0..7 attack, 8..15 release) */
-    float4 recB[TBF_NOF_WHEELS + 1]; /* gs gv gp ds */
-    float2 recC[TBF_NOF_WHEELS + 1]; /* dv dp */
+    int4 recA[REC_TILE];   /* wave_off, len, pos, env (-1 plain, 0..7 attack, 8..15 release) */
+    float4 recB[REC_TILE]; /* gs gv gp ds */
+    float2 recC[REC_TILE]; /* dv dp */
+    float wstage[WAVE_STAGES][4][32]; /* [stage][k][lane]: sample lane + 32k of a wheel */
     float vring[TBF_VRING];
     float va[BLK], vb[BLK], vy[BLK];
     uint16_t vn[BLK];
     uint16_t removed_wheel[TBF_NOF_WHEELS + 1];
     uint8_t removed[TBF_NOF_WHEELS + 3];
-    int n_rec, n_ins, recompute_routing, draw_bar_change, vib_on, perc_on;
+    int recompute_routing, draw_bar_change, vib_on, perc_on;
 };
 
 /* -- key events, one lane (src/tonegen.cpp:3096-3166 + the queue drain :3257-3327): the
@@ -357,19 +360,18 @@ __device__ void apply_scalar_event(TgScalars &sc, const DevTonegenTables *tg, co
     }
 }
 
-/* active-list pass (src/tonegen.cpp:3333-3594).  Entry i of the active list touches only
- * its own wheel's state, so lane l handles entries l, l+32, ... */
-__device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, TWarp &sm, int lane)
+/* active-list pass (src/tonegen.cpp:3333-3594), entries [base, base + cnt) -> records
+ * 0..cnt-1.  Entry i of the active list touches only its own wheel's state, so lane l
+ * handles entries base + l, base + l + 32. */
+__device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegenTables *tg, TWarp &sm,
+                                                 int lane, int base, int cnt, int &my_ins, int &any_removed)
 {
     TgScalars &sc = sm.sc;
-    const int n_act = sc.activeOscLEnd;
     const uint32_t routing = sc.oldRouting; /* already updated by lane 0 */
     const bool recompute_routing = sm.recompute_routing != 0;
     const bool draw_bar_change = sm.draw_bar_change != 0;
-    int my_ins = 0;
-    int any_removed = 0;
 
-    for (int i = lane; i < n_act; i += 32) {
+    for (int i = base + lane; i < base + cnt; i += 32) {
         const int w = st->activeOscList[i];
         OscState *o = &st->osc[w];
         const uint32_t rflags = o->rflags;
@@ -452,16 +454,22 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, TWar
             my_ins += 1;
         }
         o->rflags = 0;
-        sm.recA[i] = make_int4((int)tg->wave_offset[w], (int)len, (int)pos, env);
-        sm.recB[i] = make_float4(gs, gv, gp, ds);
-        sm.recC[i] = make_float2(dv, dp);
+        sm.recA[i - base] = make_int4((int)tg->wave_offset[w], (int)len, (int)pos, env);
+        sm.recB[i - base] = make_float4(gs, gv, gp, ds);
+        sm.recC[i - base] = make_float2(dv, dp);
     }
+}
+
+/* end of the active-list pass: statistics, reference-UB flag, removal list */
+__device__ __forceinline__ void active_list_finish(InstState *st, TWarp &sm, int lane, int n_act,
+                                                   int my_ins, int any_removed)
+{
+    TgScalars &sc = sm.sc;
     const int n_ins = __reduce_add_sync(FULL, my_ins);
     any_removed = __any_sync(FULL, any_removed);
     __syncwarp(); /* removed[] and the wheel state are visible to lane 0 */
 
     if (lane == 0) {
-        sm.n_rec = n_act;
         sc.statFragments += 1;
         sc.statActiveWheels += (unsigned long long)n_act;
         sc.drawBarChange = 0;
@@ -499,25 +507,27 @@ __device__ void active_list_pass(InstState *st, const DevTonegenTables *tg, TWar
 }
 
 /* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples lane + 32k.
- * The wheel's four wave samples of this lane: one base address and immediate offsets
- * when the 128-sample read does not wrap (uniform per wheel), a modular index else. */
-__device__ __forceinline__ void wave_fetch(const float *__restrict__ wave, const int4 ra, int lane,
-                                           float (&x)[4])
+ * Request the four wave samples of this lane for record j into its stage: one base
+ * address when the 128-sample read does not wrap (uniform per wheel), a modular index
+ * else.  Every lane later reads back only what it requested itself. */
+__device__ __forceinline__ void wave_request(const float *__restrict__ wave, TWarp &sm, int j, int lane)
 {
+    const int4 ra = sm.recA[j];
     const uint32_t len = (uint32_t)ra.y, pos = (uint32_t)ra.z;
     const float *wp = wave + (uint32_t)ra.x;
+    float *dst = &sm.wstage[j & (WAVE_STAGES - 1)][0][lane];
     if (pos + TBF_FRAGMENT <= len) {
         const float *q = wp + (pos + (uint32_t)lane);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            x[k] = __ldg(q + 32 * k);
+            __pipeline_memcpy_async(dst + 32 * k, q + 32 * k, 4);
     } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            uint32_t j = pos + (uint32_t)lane + 32u * k;
-            if (j >= len)
-                j -= len;
-            x[k] = __ldg(wp + j);
+            uint32_t idx = pos + (uint32_t)lane + 32u * k;
+            if (idx >= len)
+                idx -= len;
+            __pipeline_memcpy_async(dst + 32 * k, wp + idx, 4);
         }
     }
 }
@@ -526,10 +536,11 @@ __device__ __forceinline__ void wave_fetch(const float *__restrict__ wave, const
  * instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680) */
 template <bool FIRST>
 __device__ __forceinline__ void wheel_apply(const DevTonegenTables *tg, const TWarp &sm, int i, int lane,
-                                            const int env, const float (&x)[4], float (&s)[4],
-                                            float (&v)[4], float (&p)[4])
+                                            const float (&x)[4], float (&s)[4], float (&v)[4],
+                                            float (&p)[4])
 {
     const float4 rb = sm.recB[i];
+    const int env = sm.recA[i].w;
     float cs[4], cv[4], cp[4];
     if (env >= 0) {
         const float2 rc = sm.recC[i];
@@ -557,37 +568,31 @@ __device__ __forceinline__ void wheel_apply(const DevTonegenTables *tg, const TW
     }
 }
 
-__device__ __forceinline__ void core_interpreter(const DevTonegenTables *tg, const TWarp &sm, int lane,
-                                                 float (&s)[4], float (&v)[4], float (&p)[4])
+/* records 0..cnt-1 of the current tile, in order; WAVE_STAGES wheels stay in flight */
+__device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int cnt,
+                                          bool first_tile, float (&s)[4], float (&v)[4], float (&p)[4])
 {
-    const int n_rec = sm.n_rec;
     const float *__restrict__ wave = tg->wave_data;
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-        s[k] = v[k] = p[k] = 0.0f;
-    if (n_rec == 0)
-        return;
-    /* the next wheel's samples are requested before the current wheel's arithmetic */
-    int4 ra = sm.recA[0];
-    float x[4];
-    wave_fetch(wave, ra, lane, x);
-    {
-        int env = ra.w;
-        float xc[4] = {x[0], x[1], x[2], x[3]};
-        if (n_rec > 1) {
-            ra = sm.recA[1];
-            wave_fetch(wave, ra, lane, x);
-        }
-        wheel_apply<true>(tg, sm, 0, lane, env, xc, s, v, p);
+    for (int j = 0; j < WAVE_STAGES; ++j) {
+        if (j < cnt)
+            wave_request(wave, sm, j, lane);
+        __pipeline_commit();
     }
-    for (int i = 1; i < n_rec; ++i) {
-        const int env = ra.w;
-        const float xc[4] = {x[0], x[1], x[2], x[3]};
-        if (i + 1 < n_rec) {
-            ra = sm.recA[i + 1];
-            wave_fetch(wave, ra, lane, x);
-        }
-        wheel_apply<false>(tg, sm, i, lane, env, xc, s, v, p);
+    for (int i = 0; i < cnt; ++i) {
+        __pipeline_wait_prior(WAVE_STAGES - 1); /* this lane's requests for record i landed */
+        const float *src = &sm.wstage[i & (WAVE_STAGES - 1)][0][lane];
+        float x[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            x[k] = src[32 * k];
+        if (i + WAVE_STAGES < cnt)
+            wave_request(wave, sm, i + WAVE_STAGES, lane);
+        __pipeline_commit();
+        if (first_tile && i == 0)
+            wheel_apply<true>(tg, sm, i, lane, x, s, v, p);
+        else
+            wheel_apply<false>(tg, sm, i, lane, x, s, v, p);
     }
 }
 
@@ -718,11 +723,23 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
         __syncwarp();
         const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
 
-        active_list_pass(st, tg, sm, lane);
-
-        /* -- additive synthesis -- */
+        /* -- active-list pass and additive synthesis, REC_TILE wheels at a time -- */
         float swl[4], vib[4], prc[4];
-        core_interpreter(tg, sm, lane, swl, vib, prc);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            swl[k] = vib[k] = prc[k] = 0.0f;
+        {
+            const int n_act = sc.activeOscLEnd;
+            int my_ins = 0, any_removed = 0;
+            for (int base = 0; base < n_act; base += REC_TILE) {
+                const int cnt = min(REC_TILE, n_act - base);
+                active_list_tile(st, tg, sm, lane, base, cnt, my_ins, any_removed);
+                __syncwarp();
+                core_tile(tg, sm, lane, cnt, base == 0, swl, vib, prc);
+                __syncwarp();
+            }
+            active_list_finish(st, sm, lane, n_act, my_ins, any_removed);
+        }
 
         /* -- scanner, percussion high-pass, hand-over to stage R -- */
         const float pz = sc.pz;
