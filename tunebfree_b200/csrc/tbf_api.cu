@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -75,11 +76,14 @@ struct tbf_ctx {
     StageScratch scratch;
     /* instance groups: each renders its share of a batch on its own stream, so the
      * latency-bound lane = instance stages of one group overlap the others' stages */
-    cudaStream_t gstream[TBF_MAX_GROUPS] = {};
-    cudaEvent_t gdone[TBF_MAX_GROUPS] = {};
+    /* ... and every stage of a group has its own stream: stage s of chunk c overlaps stage
+     * s-1 of chunk c+1 (the stage streams between them are double-buffered by chunk parity) */
+    cudaStream_t sstream[TBF_MAX_GROUPS][4] = {};
+    cudaEvent_t sdone[TBF_MAX_GROUPS][4][2] = {}; /* [group][stage][chunk parity] */
     cudaEvent_t fork = nullptr;
     size_t scratch_budget = (size_t)4 << 30; /* bytes of HBM the stage streams may take */
-    uint32_t max_stage_chunk = 64;           /* fragments per stage-kernel launch       */
+    uint32_t max_stage_chunk = 32;           /* fragments per stage-kernel launch       */
+    int n_groups_max = TBF_MAX_GROUPS;
     bool in_flight = false;
     int launches = 0;
     std::vector<uint64_t> ev_start_host;
@@ -128,12 +132,19 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     }
     bool ok = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming) == cudaSuccess;
     for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g)
-        ok = cudaStreamCreateWithFlags(&ctx->gstream[g], cudaStreamNonBlocking) == cudaSuccess &&
-             cudaEventCreateWithFlags(&ctx->gdone[g], cudaEventDisableTiming) == cudaSuccess;
+        for (int st = 0; st < 4 && ok; ++st)
+            ok = cudaStreamCreateWithFlags(&ctx->sstream[g][st], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&ctx->sdone[g][st][0], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&ctx->sdone[g][st][1], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) {
         delete ctx;
         return TBF_ERR_CUDA;
     }
+    /* tuning knobs (bench sweeps): instance groups and fragments per stage launch */
+    if (const char *e = getenv("TBF_GROUPS"))
+        ctx->n_groups_max = std::max(1, std::min(TBF_MAX_GROUPS, atoi(e)));
+    if (const char *e = getenv("TBF_STAGE_CHUNK"))
+        ctx->max_stage_chunk = (uint32_t)std::max(1, std::min(256, atoi(e)));
     *out = ctx;
     return TBF_OK;
 }
@@ -175,12 +186,14 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     }
     cudaEventDestroy(ctx->t0);
     cudaEventDestroy(ctx->t1);
-    for (int g = 0; g < TBF_MAX_GROUPS; ++g) {
-        if (ctx->gstream[g])
-            cudaStreamDestroy(ctx->gstream[g]);
-        if (ctx->gdone[g])
-            cudaEventDestroy(ctx->gdone[g]);
-    }
+    for (int g = 0; g < TBF_MAX_GROUPS; ++g)
+        for (int st = 0; st < 4; ++st) {
+            if (ctx->sstream[g][st])
+                cudaStreamDestroy(ctx->sstream[g][st]);
+            for (int par = 0; par < 2; ++par)
+                if (ctx->sdone[g][st][par])
+                    cudaEventDestroy(ctx->sdone[g][st][par]);
+        }
     if (ctx->fork)
         cudaEventDestroy(ctx->fork);
     cudaStreamDestroy(ctx->copy_stream);
@@ -740,18 +753,21 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     if (d->checksums)
         CK(cudaMemsetAsync(ctx->d_csum, 0, sizeof(uint64_t) * n, ctx->stream));
 
-    /* stage streams: as many fragments per stage launch as the scratch budget allows */
+    /* stage streams, double-buffered by chunk parity: as many fragments per stage launch
+     * as the scratch budget allows */
     uint32_t sc_frag = (uint32_t)std::min<size_t>(
-        ctx->max_stage_chunk, std::max<size_t>(1, ctx->scratch_budget / (n * stream_bytes_per_fragment(whirl))));
+        ctx->max_stage_chunk,
+        std::max<size_t>(1, ctx->scratch_budget / (2 * n * stream_bytes_per_fragment(whirl))));
     sc_frag = std::min(sc_frag, chunk);
     const size_t pitch = (size_t)sc_frag * TBF_FRAGMENT;
+    const size_t planes32 = whirl ? 8 : 2;
     StageScratch &ss = ctx->scratch;
     {
-        cudaError_t e = grow(&ss.ctl, &ss.cap_ctl, n * sc_frag);
+        cudaError_t e = grow(&ss.ctl, &ss.cap_ctl, 2 * n * sc_frag);
         if (e == cudaSuccess)
-            e = grow(&ss.f32, &ss.cap_f32, n * pitch * (whirl ? 8 : 2));
+            e = grow(&ss.f32, &ss.cap_f32, 2 * n * pitch * planes32);
         if (e == cudaSuccess && whirl)
-            e = grow(&ss.f64, &ss.cap_f64, n * pitch * 2);
+            e = grow(&ss.f64, &ss.cap_f64, 2 * n * pitch * 2);
         if (e != cudaSuccess) {
             cudaGetLastError();
             ctx->err = "render: stage stream buffers do not fit";
@@ -760,13 +776,14 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     }
 
     /* instance groups (multiples of 32 slots, so the lane = instance warps stay full) */
-    int n_groups = n >= 2048 ? 4 : (n >= 512 ? 2 : 1);
+    int n_groups = std::min<int>(ctx->n_groups_max, n >= 2048 ? 4 : (n >= 512 ? 2 : 1));
     uint32_t gfirst[TBF_MAX_GROUPS + 1];
     {
         const uint32_t per = (uint32_t)(((n + n_groups - 1) / n_groups + 31) / 32 * 32);
         for (int g = 0; g <= n_groups; ++g)
             gfirst[g] = (uint32_t)std::min<size_t>(n, (size_t)per * g);
     }
+    const int n_stages = whirl ? 4 : 2, last = n_stages - 1;
 
     RenderParams base_p;
     memset(&base_p, 0, sizeof(base_p));
@@ -783,8 +800,10 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     CK(cudaEventRecord(ctx->fork, ctx->stream));
     for (int g = 0; g < n_groups; ++g)
-        CK(cudaStreamWaitEvent(ctx->gstream[g], ctx->fork, 0));
+        for (int st = 0; st < n_stages; ++st)
+            CK(cudaStreamWaitEvent(ctx->sstream[g][st], ctx->fork, 0));
     const size_t half = (size_t)2 * n * chunk * TBF_FRAGMENT;
+    uint32_t cidx[TBF_MAX_GROUPS] = {0, 0, 0, 0}; /* stage chunks launched per group */
     int k = 0;
     for (uint32_t base = 0; base < d->n_fragments; base += chunk, ++k) {
         const uint32_t nf = std::min<uint32_t>(chunk, d->n_fragments - base);
@@ -805,10 +824,10 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             const uint32_t ng = gfirst[g + 1] - gfirst[g];
             if (!ng)
                 continue;
-            cudaStream_t st = ctx->gstream[g];
+            cudaStream_t *st = ctx->sstream[g];
             /* staging buffer `buf` is free once the copy issued two chunks ago is done */
             if (host_out && k >= 2)
-                CK(cudaStreamWaitEvent(st, ctx->copy_done[buf], 0));
+                CK(cudaStreamWaitEvent(st[last], ctx->copy_done[buf], 0));
             RenderParams p = base_p;
             p.n_instances = ng;
             p.ids = ctx->prepared_has_ids ? ctx->d_ids + s0 : nullptr;
@@ -818,38 +837,64 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             p.ev_cursor_r = cur_r + s0;
             p.checksums = d->checksums ? ctx->d_csum + s0 : nullptr;
             p.out_stride = out_stride;
-            p.ctl = ss.ctl + s0 * sc_frag;
-            p.u = ss.f32 + s0 * pitch;
-            p.php = ss.f32 + (n + s0) * pitch;
-            if (whirl) {
-                p.dx0 = ss.f32 + (2 * n + s0) * pitch;
-                p.hx0 = ss.f32 + (3 * n + s0) * pitch;
-                for (int l = 0; l < 4; ++l)
-                    p.line[l] = ss.f32 + ((4 + l) * n + s0) * pitch;
-                p.hang = ss.f64 + s0 * pitch;
-                p.dang = ss.f64 + (n + s0) * pitch;
-            }
+            int par = 0;
             for (uint32_t ib = 0; ib < nf; ib += sc_frag) {
+                const uint32_t c = cidx[g]++;
+                par = (int)(c & 1u);
+                float *f32 = ss.f32 + (size_t)par * n * pitch * planes32;
+                p.ctl = ss.ctl + ((size_t)par * n + s0) * sc_frag;
+                p.u = f32 + s0 * pitch;
+                p.php = f32 + (n + s0) * pitch;
+                if (whirl) {
+                    p.dx0 = f32 + (2 * n + s0) * pitch;
+                    p.hx0 = f32 + (3 * n + s0) * pitch;
+                    for (int l = 0; l < 4; ++l)
+                        p.line[l] = f32 + ((4 + l) * n + s0) * pitch;
+                    double *f64 = ss.f64 + (size_t)par * n * pitch * 2;
+                    p.hang = f64 + s0 * pitch;
+                    p.dang = f64 + (n + s0) * pitch;
+                }
                 p.frag_base = base + ib;
                 p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
                 p.out_l = out_l ? out_l + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
                 p.out_r = out_r ? out_r + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
-                int rc = tbf_launch_stage_t(p, st);
-                if (rc == 0)
-                    rc = tbf_launch_stage_r(p, st);
-                if (rc == 0 && whirl)
-                    rc = tbf_launch_stage_w(p, ring, st);
-                if (rc == 0 && whirl)
-                    rc = tbf_launch_stage_d(p, st);
+                cudaEvent_t(*ev)[2] = ctx->sdone[g];
+                /* a stage waits for its producer of this chunk and, before it overwrites
+                 * the streams of parity `par`, for their consumers of chunk c - 2 */
+                int rc = 0;
+                if (c >= 2)
+                    CK(cudaStreamWaitEvent(st[0], ev[1][par], 0));
+                rc = tbf_launch_stage_t(p, st[0]);
+                CK(cudaEventRecord(ev[0][par], st[0]));
+                if (rc == 0) {
+                    CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
+                    if (whirl && c >= 2) {
+                        CK(cudaStreamWaitEvent(st[1], ev[2][par], 0));
+                        CK(cudaStreamWaitEvent(st[1], ev[3][par], 0));
+                    }
+                    rc = tbf_launch_stage_r(p, st[1]);
+                    CK(cudaEventRecord(ev[1][par], st[1]));
+                }
+                if (rc == 0 && whirl) {
+                    CK(cudaStreamWaitEvent(st[2], ev[1][par], 0));
+                    if (c >= 2)
+                        CK(cudaStreamWaitEvent(st[2], ev[3][par], 0));
+                    rc = tbf_launch_stage_w(p, ring, st[2]);
+                    CK(cudaEventRecord(ev[2][par], st[2]));
+                }
+                if (rc == 0 && whirl) {
+                    CK(cudaStreamWaitEvent(st[3], ev[2][par], 0));
+                    rc = tbf_launch_stage_d(p, st[3]);
+                    CK(cudaEventRecord(ev[3][par], st[3]));
+                }
                 if (rc != 0) {
                     ctx->err = std::string("stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
                     return TBF_ERR_CUDA;
                 }
-                ctx->launches += whirl ? 4 : 2;
+                ctx->launches += n_stages;
             }
-            CK(cudaEventRecord(ctx->gdone[g], st));
             if (host_out)
-                CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->gdone[g], 0));
+                CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->sdone[g][last][par], 0));
         }
         if (host_out) {
             const size_t w = sizeof(float) * (size_t)nf * TBF_FRAGMENT;
@@ -861,7 +906,8 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
         }
     }
     for (int g = 0; g < n_groups; ++g)
-        CK(cudaStreamWaitEvent(ctx->stream, ctx->gdone[g], 0));
+        if (cidx[g])
+            CK(cudaStreamWaitEvent(ctx->stream, ctx->sdone[g][last][(cidx[g] - 1) & 1u], 0));
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     if (d->checksums)
         CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * n,
