@@ -112,6 +112,9 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     if (!out)
         return TBF_ERR_ARG;
     *out = nullptr;
+    /* 2 groups x 4 stage streams + copy + control: keep them on separate hardware queues
+     * (only effective if set before the process creates its CUDA context) */
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n)
         return TBF_ERR_CUDA;
@@ -131,9 +134,14 @@ int tbf_gpu_create(tbf_ctx **out, int device)
         return TBF_ERR_CUDA;
     }
     bool ok = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming) == cudaSuccess;
+    /* the lane = instance stages (R, D) are latency-bound and small: their CTAs go first
+     * whenever an SM has room, so they run beside the throughput stages instead of after */
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g)
         for (int st = 0; st < 4 && ok; ++st)
-            ok = cudaStreamCreateWithFlags(&ctx->sstream[g][st], cudaStreamNonBlocking) == cudaSuccess &&
+            ok = cudaStreamCreateWithPriority(&ctx->sstream[g][st], cudaStreamNonBlocking,
+                                              (st & 1) ? prio_hi : prio_lo) == cudaSuccess &&
                  cudaEventCreateWithFlags(&ctx->sdone[g][st][0], cudaEventDisableTiming) == cudaSuccess &&
                  cudaEventCreateWithFlags(&ctx->sdone[g][st][1], cudaEventDisableTiming) == cudaSuccess;
     if (!ok) {

@@ -127,9 +127,10 @@ __device__ __forceinline__ void ordered_pass(const uint16_t *n, const float *a, 
 struct TWarp {
     TgScalars sc;
     int4 recA[REC_TILE];   /* wave_off, len, pos, env (-1 plain, 0..7 attack, 8..15 release) */
-    float4 recB[REC_TILE]; /* gs gv gp ds */
-    float2 recC[REC_TILE]; /* dv dp */
-    float wstage[WAVE_STAGES][4][32]; /* [stage][k][lane]: sample lane + 32k of a wheel */
+    float4 recB[REC_TILE]; /* gs gs gv gv: gains duplicated for the packed f32x2 multiply */
+    float2 recC[REC_TILE]; /* gp gp */
+    float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas, read for env >= 0 only */
+    float4 wstage[WAVE_STAGES][32]; /* [stage][lane]: samples lane, +32, +64, +96 of a wheel */
     float vring[TBF_VRING];
     float va[BLK], vb[BLK], vy[BLK];
     uint16_t vn[BLK];
@@ -455,8 +456,10 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
         }
         o->rflags = 0;
         sm.recA[i - base] = make_int4((int)tg->wave_offset[w], (int)len, (int)pos, env);
-        sm.recB[i - base] = make_float4(gs, gv, gp, ds);
-        sm.recC[i - base] = make_float2(dv, dp);
+        sm.recB[i - base] = make_float4(gs, gs, gv, gv);
+        sm.recC[i - base] = make_float2(gp, gp);
+        if (env >= 0)
+            sm.recD[i - base] = make_float4(ds, dv, dp, 0.0f);
     }
 }
 
@@ -515,62 +518,71 @@ __device__ __forceinline__ void wave_request(const float *__restrict__ wave, TWa
     const int4 ra = sm.recA[j];
     const uint32_t len = (uint32_t)ra.y, pos = (uint32_t)ra.z;
     const float *wp = wave + (uint32_t)ra.x;
-    float *dst = &sm.wstage[j & (WAVE_STAGES - 1)][0][lane];
+    float *dst = reinterpret_cast<float *>(&sm.wstage[j & (WAVE_STAGES - 1)][lane]);
     if (pos + TBF_FRAGMENT <= len) {
         const float *q = wp + (pos + (uint32_t)lane);
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            __pipeline_memcpy_async(dst + 32 * k, q + 32 * k, 4);
+            __pipeline_memcpy_async(dst + k, q + 32 * k, 4);
     } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             uint32_t idx = pos + (uint32_t)lane + 32u * k;
             if (idx >= len)
                 idx -= len;
-            __pipeline_memcpy_async(dst + 32 * k, wp + idx, 4);
+            __pipeline_memcpy_async(dst + k, wp + idx, 4);
         }
     }
 }
 
-/* one core-program record applied to the lane's four samples; FIRST: the first
- * instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680) */
-template <bool FIRST>
-__device__ __forceinline__ void wheel_apply(const DevTonegenTables *tg, const TWarp &sm, int i, int lane,
-                                            const float (&x)[4], float (&s)[4], float (&v)[4],
-                                            float (&p)[4])
+/* Packed pairs of floats for Blackwell's two-wide FP32 instructions (FMUL2 / FADD2): each
+ * half is an IEEE round-to-nearest operation, bit-identical to the scalar one.
+ * ptxas contracts a mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which
+ * would break the reference's rounding; core_tile() therefore adds a wheel's products one
+ * loop iteration after they were formed (the loop is kept rolled), and tests/test_cabi.py
+ * checks that the built kernels contain no fused multiply-add at all. */
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
 {
-    const float4 rb = sm.recB[i];
-    const int env = sm.recA[i].w;
-    float cs[4], cv[4], cp[4];
-    if (env >= 0) {
-        const float2 rc = sm.recC[i];
-        const float *ev = tg->env[env] + lane;
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
+{
+    return ((f32x2)__float_as_uint(hi) << 32) | (f32x2)__float_as_uint(lo);
+}
+__device__ __forceinline__ float lo2(f32x2 v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ float hi2(f32x2 v) { return __uint_as_float((uint32_t)(v >> 32)); }
+
+/* accumulators and pending products of the three buffers (swell, scanner, percussion):
+ * [0] = samples lane, lane+32; [1] = samples lane+64, lane+96 */
+struct CoreAcc {
+    f32x2 s[2], v[2], p[2];    /* running sums                                    */
+    f32x2 ps[2], pv[2], pp[2]; /* products of the previous wheel, not yet added   */
+};
+
+/* The first instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680):
+ * with the sums started at -0.0f an add IS a copy, bit for bit ((-0) + x = x for every x,
+ * (-0) + (-0) = -0), and the same holds for the pending products. */
+__device__ __forceinline__ void core_begin(CoreAcc &a)
+{
+    const f32x2 nz = 0x8000000080000000ull;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float e = __ldg(ev + 32 * k);
-            cs[k] = __fmul_rn(x[k], __fadd_rn(rb.x, __fmul_rn(e, rb.w)));
-            cv[k] = __fmul_rn(x[k], __fadd_rn(rb.y, __fmul_rn(e, rc.x)));
-            cp[k] = __fmul_rn(x[k], __fadd_rn(rb.z, __fmul_rn(e, rc.y)));
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            cs[k] = __fmul_rn(x[k], rb.x);
-            cv[k] = __fmul_rn(x[k], rb.y);
-            cp[k] = __fmul_rn(x[k], rb.z);
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        s[k] = FIRST ? cs[k] : __fadd_rn(s[k], cs[k]);
-        v[k] = FIRST ? cv[k] : __fadd_rn(v[k], cv[k]);
-        p[k] = FIRST ? cp[k] : __fadd_rn(p[k], cp[k]);
-    }
+    for (int h = 0; h < 2; ++h)
+        a.s[h] = a.v[h] = a.p[h] = a.ps[h] = a.pv[h] = a.pp[h] = nz;
 }
 
-/* records 0..cnt-1 of the current tile, in order; WAVE_STAGES wheels stay in flight */
+/* records 0..cnt-1 of the current tile, in order (src/tonegen.cpp:3607-3687);
+ * WAVE_STAGES wheels stay in flight */
 __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int cnt,
-                                          bool first_tile, float (&s)[4], float (&v)[4], float (&p)[4])
+                                          CoreAcc &a)
 {
     const float *__restrict__ wave = tg->wave_data;
 #pragma unroll
@@ -579,20 +591,71 @@ __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm,
             wave_request(wave, sm, j, lane);
         __pipeline_commit();
     }
+#pragma unroll 1
     for (int i = 0; i < cnt; ++i) {
         __pipeline_wait_prior(WAVE_STAGES - 1); /* this lane's requests for record i landed */
-        const float *src = &sm.wstage[i & (WAVE_STAGES - 1)][0][lane];
-        float x[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            x[k] = src[32 * k];
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[i & (WAVE_STAGES - 1)][lane]);
         if (i + WAVE_STAGES < cnt)
             wave_request(wave, sm, i + WAVE_STAGES, lane);
         __pipeline_commit();
-        if (first_tile && i == 0)
-            wheel_apply<true>(tg, sm, i, lane, x, s, v, p);
-        else
-            wheel_apply<false>(tg, sm, i, lane, x, s, v, p);
+        /* add the previous wheel's products ... */
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            a.s[h] = add2(a.s[h], a.ps[h]);
+            a.v[h] = add2(a.v[h], a.pv[h]);
+            a.p[h] = add2(a.p[h], a.pp[h]);
+        }
+        /* ... and form this wheel's */
+        const ulonglong2 g = *reinterpret_cast<const ulonglong2 *>(&sm.recB[i]);
+        const f32x2 gp = *reinterpret_cast<const f32x2 *>(&sm.recC[i]);
+        const int env = sm.recA[i].w;
+        if (env < 0) {
+            a.ps[0] = mul2(x.x, g.x);
+            a.ps[1] = mul2(x.y, g.x);
+            a.pv[0] = mul2(x.x, g.y);
+            a.pv[1] = mul2(x.y, g.y);
+            a.pp[0] = mul2(x.x, gp);
+            a.pp[1] = mul2(x.y, gp);
+        } else { /* key click: gain = g + env[n] * (next - g), per sample */
+            const float4 d = sm.recD[i];
+            const float *ev = tg->env[env] + lane;
+            const float gs = lo2(g.x), gv = lo2(g.y), gpp = lo2(gp);
+            float e[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                e[k] = __ldg(ev + 32 * k);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const f32x2 xx = h ? x.y : x.x;
+                const float e0 = e[2 * h], e1 = e[2 * h + 1];
+                a.ps[h] = mul2(xx, pack2(__fadd_rn(gs, __fmul_rn(e0, d.x)), __fadd_rn(gs, __fmul_rn(e1, d.x))));
+                a.pv[h] = mul2(xx, pack2(__fadd_rn(gv, __fmul_rn(e0, d.y)), __fadd_rn(gv, __fmul_rn(e1, d.y))));
+                a.pp[h] = mul2(xx, pack2(__fadd_rn(gpp, __fmul_rn(e0, d.z)), __fadd_rn(gpp, __fmul_rn(e1, d.z))));
+            }
+        }
+    }
+}
+
+/* the last wheel's products; an empty active list leaves the buffers zeroed
+ * (src/tonegen.cpp:3607-3612) */
+__device__ __forceinline__ void core_end(CoreAcc &a, int n_act, float (&s)[4], float (&v)[4], float (&p)[4])
+{
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        a.s[h] = add2(a.s[h], a.ps[h]);
+        a.v[h] = add2(a.v[h], a.pv[h]);
+        a.p[h] = add2(a.p[h], a.pp[h]);
+        s[2 * h] = lo2(a.s[h]);
+        s[2 * h + 1] = hi2(a.s[h]);
+        v[2 * h] = lo2(a.v[h]);
+        v[2 * h + 1] = hi2(a.v[h]);
+        p[2 * h] = lo2(a.p[h]);
+        p[2 * h + 1] = hi2(a.p[h]);
+    }
+    if (n_act == 0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            s[k] = v[k] = p[k] = 0.0f;
     }
 }
 
@@ -725,19 +788,19 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
 
         /* -- active-list pass and additive synthesis, REC_TILE wheels at a time -- */
         float swl[4], vib[4], prc[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            swl[k] = vib[k] = prc[k] = 0.0f;
         {
             const int n_act = sc.activeOscLEnd;
             int my_ins = 0, any_removed = 0;
+            CoreAcc acc;
+            core_begin(acc);
             for (int base = 0; base < n_act; base += REC_TILE) {
                 const int cnt = min(REC_TILE, n_act - base);
                 active_list_tile(st, tg, sm, lane, base, cnt, my_ins, any_removed);
                 __syncwarp();
-                core_tile(tg, sm, lane, cnt, base == 0, swl, vib, prc);
+                core_tile(tg, sm, lane, cnt, acc);
                 __syncwarp();
             }
+            core_end(acc, n_act, swl, vib, prc);
             active_list_finish(st, sm, lane, n_act, my_ins, any_removed);
         }
 
