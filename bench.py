@@ -23,6 +23,9 @@ import sys
 import threading
 import time
 
+# 2 instance groups x 4 stage streams + copy + control stream: one hardware queue each
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -308,6 +311,13 @@ def run_gpu_arm(a):
     peak_out = float(out[0, 0].abs().max().item())
     st = ctx.export_state(int(ids[0]))
     n_act = st.stat_active_wheels / max(1, st.stat_fragments)
+    # per-stage device times: one extra pass with every stage kernel alone between two CUDA
+    # events on its launch stream (outside the timed region: it removes the overlap)
+    ctx.set_stage_profiling(True)
+    ctx.launch()
+    ctx.synchronize()
+    stage = ctx.stage_times()
+    ctx.set_stage_profiling(False)
     del out
     torch.cuda.empty_cache()
 
@@ -339,6 +349,7 @@ def run_gpu_arm(a):
         for _ in range(a.steps):
             e2e_step()
         dt = time.perf_counter() - t0
+        e2e_launches = a.steps * ctx.last_launch_ms()[1]
         barrier()
         dt = max_over_ranks(dt)
         e2e = {"value": world * organ_seconds_step * a.steps / dt, "unit": UNIT,
@@ -352,28 +363,39 @@ def run_gpu_arm(a):
     if rank == 0:
         peaks = measured_peaks()
         hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
-        secs_per_launch = organ_seconds_step * a.steps / max(1, launches)
-        dur = (kernel_ms * 1e-3) / max(1, launches)
         whirl = 1 if a.config >= 3 else 0
         f_clk = (clocks.get("sm_mhz") or (peaks or {}).get("sm_max_mhz") or 1965.0) * 1e6
-        # algorithmic work per organ-second (DESIGN.md "Rooflines")
-        hbm_bytes = 48000 * 2 * 4
+        rate = value / world  # organ-seconds per second per GPU
+        # dominant kernel = the stage with the largest summed device time in the profiled pass
+        names = {"T": "tbf_stage_t", "R": "tbf_stage_r", "W": "tbf_stage_w", "D": "tbf_stage_d"}
+        dom = max(stage, key=lambda k: stage[k][0])
+        dom_ms, dom_n = stage[dom]
+        dur = dom_ms * 1e-3 / max(1, dom_n)                      # average launch duration
+        secs_per_dom_launch = organ_seconds_step / max(1, dom_n)  # organ-seconds one launch renders
+        # algorithmic HBM-side bytes per organ-second of each stage (DESIGN.md "Work model"):
+        # T reads 4 B per active wheel and sample, writes u + php; R reads them, writes dx0, hx0
+        # and two double angles; W reads those, writes four line reads; D reads them + hx0, writes L, R
+        stage_bytes = {"T": 48000 * (4 * n_act + 8), "R": 48000 * (8 + 24), "W": 48000 * (24 + 16),
+                       "D": 48000 * (20 + 8)}
+        ach_hbm = stage_bytes[dom] * secs_per_dom_launch / dur / 1e9
+        # algorithmic work of the whole path per organ-second
         w32 = 48000 * (6 * n_act + 17 + 253 * whirl)
         bsm = 48000 * (4 * n_act + 70 + 380 * whirl)
-        ach_hbm = hbm_bytes * secs_per_launch / dur / 1e9
         roofline = {"bound": "hbm", "achieved": ach_hbm, "peak": hbm_peak, "unit": "GB/s",
                     "frac": ach_hbm / hbm_peak, "traffic": None,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                    "note": "HBM is not the binding roofline of this path (384 kB of output per "
-                            "organ-second); the FP32-issue and shared-memory rooflines below are",
-                    "kernel": "tbf_render_kernel", "avg_launch_ms": dur * 1e3,
+                    "note": "bytes = the dominant stage kernel's algorithmic reads + writes; the path is "
+                            "bound by instruction issue, not HBM: see fp32_issue / smem_bw (whole path, "
+                            "against the timed region) and profiles/",
+                    "kernel": names[dom], "avg_launch_ms": dur * 1e3, "launches_profiled": dom_n,
                     "n_act": n_act,
-                    "fp32_issue": {"achieved": w32 * secs_per_launch / dur / 1e12,
+                    "stage_ms_per_step": {names[k]: stage[k][0] for k in "TRWD"},
+                    "fp32_issue": {"achieved": w32 * rate / 1e12,
                                    "peak": 148 * 128 * f_clk / 1e12, "unit": "T lane-ops/s",
-                                   "frac": (w32 * secs_per_launch / dur) / (148 * 128 * f_clk)},
-                    "smem_bw": {"achieved": bsm * secs_per_launch / dur / 1e12,
+                                   "frac": (w32 * rate) / (148 * 128 * f_clk)},
+                    "smem_bw": {"achieved": bsm * rate / 1e12,
                                 "peak": 148 * 128 * f_clk / 1e12, "unit": "TB/s",
-                                "frac": (bsm * secs_per_launch / dur) / (148 * 128 * f_clk)}}
+                                "frac": (bsm * rate) / (148 * 128 * f_clk)}}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": total_ms / a.steps, "higher_is_better": True,
@@ -384,7 +406,7 @@ def run_gpu_arm(a):
                        "l2": "inputs larger than L2 (instance state %.0f MB + %.1f GB of output per step)"
                              % (n_inst * 0.08, 2 * n_inst * frames * 4 / 1e9),
                        "parallelism": "instances sharded over %d GPU(s), no collective" % world},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches + (a.steps * ((n_frag + 124) // 125) if e2e else 0),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches + (e2e_launches if e2e else 0),
             "roofline": roofline, "cpu_baseline": cpu_baseline,
             "checks": {"peak_abs_sample": peak_out, "error_flags": int(st.error_flags)},
         }

@@ -216,6 +216,12 @@ int tbf_gpu_timer_stop(tbf_ctx *ctx, float *ms);
  * and how many kernels it launched                                           */
 int tbf_gpu_last_launch_ms(tbf_ctx *ctx, float *ms, int *n_kernel_launches);
 
+/* per-stage device times: while profiling is on every stage kernel (T tone generator +
+ * scanner, R ramps + horn filters + rotors, W Leslie taps + delay lines, D drum filters +
+ * mix) runs alone between two CUDA events; times accumulate until profiling is reset  */
+int tbf_gpu_set_stage_profiling(tbf_ctx *ctx, int on);
+int tbf_gpu_stage_times(tbf_ctx *ctx, float ms[4], int launches[4]);
+
 /* parity debugging: integer + float run-time state of one instance           */
 typedef struct tbf_state_export {
     int32_t active_osc_l_end;

@@ -65,3 +65,21 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "ref_engine" not in txt and "libtbf_ref" not in txt, f
                 assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f
+
+
+def test_no_contracted_packed_fma_in_kernels():
+    """The tone generator's sum runs on packed FP32 pairs (FMUL2 / FADD2).  ptxas contracts a
+    mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which would change the
+    reference's rounding; the kernels are written so that it cannot (tbf_kernels.cu, core_tile)
+    and this test pins it: no FFMA2 anywhere in the library's SASS, and the packed multiply /
+    add are there."""
+    import shutil
+    import subprocess
+    from tunebfree_b200 import engine
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump) or not os.path.exists(engine.LIB_PATH):
+        pytest.skip("cuobjdump or the built library is not available")
+    sass = subprocess.run([cuobjdump, "-sass", engine.LIB_PATH], capture_output=True, text=True,
+                          check=True).stdout
+    assert "FFMA2" not in sass
+    assert "FMUL2" in sass and "FADD2" in sass

@@ -86,6 +86,12 @@ struct tbf_ctx {
     int n_groups_max = TBF_MAX_GROUPS;
     bool in_flight = false;
     int launches = 0;
+    /* stage profiling: every stage kernel serialised on the main stream between two events */
+    bool profile_stages = false;
+    std::vector<cudaEvent_t> prof_events;        /* pool, pairs */
+    std::vector<int> prof_stage;                  /* stage of pair i of the last launch */
+    float stage_ms[4] = {0, 0, 0, 0};
+    int stage_launches[4] = {0, 0, 0, 0};
     std::vector<uint64_t> ev_start_host;
 };
 
@@ -204,6 +210,8 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
         }
     if (ctx->fork)
         cudaEventDestroy(ctx->fork);
+    for (cudaEvent_t e : ctx->prof_events)
+        cudaEventDestroy(e);
     cudaStreamDestroy(ctx->copy_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -812,6 +820,23 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             CK(cudaStreamWaitEvent(ctx->sstream[g][st], ctx->fork, 0));
     const size_t half = (size_t)2 * n * chunk * TBF_FRAGMENT;
     uint32_t cidx[TBF_MAX_GROUPS] = {0, 0, 0, 0}; /* stage chunks launched per group */
+    ctx->prof_stage.clear();
+    auto prof_mark = [&](int stage, bool begin) -> cudaError_t {
+        if (!ctx->profile_stages)
+            return cudaSuccess;
+        const size_t idx = 2 * ctx->prof_stage.size() + (begin ? 0 : 1);
+        while (ctx->prof_events.size() <= idx) {
+            cudaEvent_t e;
+            cudaError_t rc = cudaEventCreate(&e);
+            if (rc != cudaSuccess)
+                return rc;
+            ctx->prof_events.push_back(e);
+        }
+        cudaError_t rc = cudaEventRecord(ctx->prof_events[idx], ctx->stream);
+        if (!begin)
+            ctx->prof_stage.push_back(stage);
+        return rc;
+    };
     int k = 0;
     for (uint32_t base = 0; base < d->n_fragments; base += chunk, ++k) {
         const uint32_t nf = std::min<uint32_t>(chunk, d->n_fragments - base);
@@ -832,7 +857,8 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             const uint32_t ng = gfirst[g + 1] - gfirst[g];
             if (!ng)
                 continue;
-            cudaStream_t *st = ctx->sstream[g];
+            cudaStream_t prof_st[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
+            cudaStream_t *st = ctx->profile_stages ? prof_st : ctx->sstream[g];
             /* staging buffer `buf` is free once the copy issued two chunks ago is done */
             if (host_out && k >= 2)
                 CK(cudaStreamWaitEvent(st[last], ctx->copy_done[buf], 0));
@@ -872,7 +898,9 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                 int rc = 0;
                 if (c >= 2)
                     CK(cudaStreamWaitEvent(st[0], ev[1][par], 0));
-                rc = tbf_launch_stage_t(p, st[0]);
+                CK(prof_mark(0, true));
+                    rc = tbf_launch_stage_t(p, st[0]);
+                    CK(prof_mark(0, false));
                 CK(cudaEventRecord(ev[0][par], st[0]));
                 if (rc == 0) {
                     CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
@@ -880,19 +908,25 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                         CK(cudaStreamWaitEvent(st[1], ev[2][par], 0));
                         CK(cudaStreamWaitEvent(st[1], ev[3][par], 0));
                     }
+                    CK(prof_mark(1, true));
                     rc = tbf_launch_stage_r(p, st[1]);
+                    CK(prof_mark(1, false));
                     CK(cudaEventRecord(ev[1][par], st[1]));
                 }
                 if (rc == 0 && whirl) {
                     CK(cudaStreamWaitEvent(st[2], ev[1][par], 0));
                     if (c >= 2)
                         CK(cudaStreamWaitEvent(st[2], ev[3][par], 0));
+                    CK(prof_mark(2, true));
                     rc = tbf_launch_stage_w(p, ring, st[2]);
+                    CK(prof_mark(2, false));
                     CK(cudaEventRecord(ev[2][par], st[2]));
                 }
                 if (rc == 0 && whirl) {
                     CK(cudaStreamWaitEvent(st[3], ev[2][par], 0));
+                    CK(prof_mark(3, true));
                     rc = tbf_launch_stage_d(p, st[3]);
+                    CK(prof_mark(3, false));
                     CK(cudaEventRecord(ev[3][par], st[3]));
                 }
                 if (rc != 0) {
@@ -940,6 +974,13 @@ int tbf_gpu_synchronize(tbf_ctx *ctx)
     ctx->in_flight = false;
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaStreamSynchronize(ctx->copy_stream));
+    for (size_t i = 0; i < ctx->prof_stage.size(); ++i) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, ctx->prof_events[2 * i], ctx->prof_events[2 * i + 1]));
+        ctx->stage_ms[ctx->prof_stage[i]] += ms;
+        ctx->stage_launches[ctx->prof_stage[i]] += 1;
+    }
+    ctx->prof_stage.clear();
     return TBF_OK;
 }
 
@@ -1015,6 +1056,34 @@ void tbf_gpu_host_free(tbf_ctx *ctx, void *p)
 {
     if (ctx && p)
         cudaFreeHost(p);
+}
+
+/* Stage profiling: while on, every stage kernel of a launch runs alone on the library's
+ * stream between two CUDA events (no overlap); tbf_gpu_stage_times returns the device time
+ * and launch count per stage (T, R, W, D) accumulated since profiling was switched on. */
+int tbf_gpu_set_stage_profiling(tbf_ctx *ctx, int on)
+{
+    if (!ctx || ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "set_stage_profiling: synchronize first");
+    ctx->profile_stages = on != 0;
+    for (int i = 0; i < 4; ++i) {
+        ctx->stage_ms[i] = 0.f;
+        ctx->stage_launches[i] = 0;
+    }
+    return TBF_OK;
+}
+
+int tbf_gpu_stage_times(tbf_ctx *ctx, float ms[4], int launches[4])
+{
+    if (!ctx || ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "stage_times: synchronize first");
+    for (int i = 0; i < 4; ++i) {
+        if (ms)
+            ms[i] = ctx->stage_ms[i];
+        if (launches)
+            launches[i] = ctx->stage_launches[i];
+    }
+    return TBF_OK;
 }
 
 int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments)

@@ -66,6 +66,8 @@ def lib():
         L.tbf_gpu_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
         L.tbf_gpu_last_launch_ms.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
         L.tbf_gpu_export_state.argtypes = [vp, C.c_uint32, C.POINTER(cabi.StateExport)]
+        L.tbf_gpu_set_stage_profiling.argtypes = [vp, C.c_int]
+        L.tbf_gpu_stage_times.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
         _lib = L
     return _lib
 
@@ -262,6 +264,17 @@ class Context:
         n = C.c_int(0)
         self._ck(lib().tbf_gpu_last_launch_ms(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def set_stage_profiling(self, on):
+        """While on, every stage kernel runs alone between two CUDA events (no overlap)."""
+        self._ck(lib().tbf_gpu_set_stage_profiling(self._h, 1 if on else 0))
+
+    def stage_times(self):
+        """-> {stage: (device ms, launches)} for stages T, R, W, D since profiling was set."""
+        ms = (C.c_float * 4)()
+        n = (C.c_int * 4)()
+        self._ck(lib().tbf_gpu_stage_times(self._h, ms, n))
+        return {k: (ms[i], n[i]) for i, k in enumerate("TRWD")}
 
     def export_state(self, instance):
         st = cabi.StateExport()
