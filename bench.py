@@ -257,7 +257,10 @@ def run_gpu_arm(a):
     n_frag = int(round(a.seconds * 375))
     frames = n_frag * 128
     flags = workloads.render_flags(a.config)
-    first_global = rank * n_inst  # every rank plays different organs
+    from tunebfree_b200 import sharding
+    # every rank plays different organs; slot i plays global organ first_global + i with
+    # table set (global id) mod 16
+    first_global, per_set = sharding.shard_plan(rank, world, n_inst, N_TABLE_SETS)
 
     ctx = engine.Context(local_rank)
     # 16 table sets (seeds 1..16) built by the product's own host-side builder
@@ -270,15 +273,7 @@ def run_gpu_arm(a):
         if wh_handle is None:
             wh_handle = ctx.whirl_tables(wt)
         tables.free_tables(tt, wt)
-    # slot i plays global instance first_global + i with table set (global id) mod 16
-    ids = np.zeros(n_inst, dtype=np.uint32)
-    per_set = [[] for _ in range(N_TABLE_SETS)]
-    for slot in range(n_inst):
-        per_set[(first_global + slot) % N_TABLE_SETS].append(slot)
-    for s in range(N_TABLE_SETS):
-        if per_set[s]:
-            first = ctx.create_instances(handles[s], wh_handle, len(per_set[s]))
-            ids[per_set[s]] = np.arange(first, first + len(per_set[s]), dtype=np.uint32)
+    ids = sharding.slot_instance_ids(per_set, lambda s, count: ctx.create_instances(handles[s], wh_handle, count))
     ev_np = workloads.batch_events_numpy(first_global, n_inst, n_frag, a.config)
     events = engine.events_from_numpy(ev_np)
     h2d_bytes = int(ev_np.shape[0] * 20 + n_inst * 4 + (n_inst + 1) * 8)

@@ -1,0 +1,43 @@
+"""Multi-GPU sharding of a batch of organs: one process per GPU, no data-path collective.
+
+Organs are independent: rank r renders global organs
+[r * per_gpu, (r + 1) * per_gpu), each with the table set `global id mod n_table_sets`.
+torch.distributed is used only around the timed region (barrier, max of the device times)."""
+import numpy as np
+
+
+def shard_plan(rank, world, per_gpu, n_table_sets):
+    """-> (first_global_id, per_set) where per_set[s] lists the batch slots of this rank that
+    play with table set s (slot i plays global organ first_global_id + i)."""
+    if not (0 <= rank < world) or per_gpu <= 0 or n_table_sets <= 0:
+        raise ValueError("bad shard arguments")
+    first = rank * per_gpu
+    per_set = [[] for _ in range(n_table_sets)]
+    for slot in range(per_gpu):
+        per_set[(first + slot) % n_table_sets].append(slot)
+    return first, per_set
+
+
+def slot_instance_ids(per_set, create):
+    """create(set_index, count) -> first instance handle of `count` new instances.
+    Returns the uint32 handle of every batch slot."""
+    n = sum(len(s) for s in per_set)
+    ids = np.zeros(n, dtype=np.uint32)
+    for s, slots in enumerate(per_set):
+        if slots:
+            first = create(s, len(slots))
+            ids[slots] = np.arange(first, first + len(slots), dtype=np.uint32)
+    return ids
+
+
+def whole_job_rate(organ_seconds_per_rank, local_ms, dist=None, device="cpu"):
+    """Whole-job organ-seconds per second: units all ranks rendered / slowest rank's time."""
+    world = 1
+    ms = float(local_ms)
+    if dist is not None:
+        import torch
+        world = dist.get_world_size()
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return world * organ_seconds_per_rank / (ms * 1e-3), ms
