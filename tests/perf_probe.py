@@ -29,3 +29,9 @@ for it in range(3):
     secs = n * nf / 375.0
     print("iter %d: kernel %.2f ms (wall %.2f ms) -> %.0f organ-s/s  [%d inst x %d frag, config %d]" % (
         it, ms, wall * 1e3, secs / (ms * 1e-3), n, nf, cfg))
+if os.environ.get("PROBE_STAGES"):
+    ctx.set_stage_profiling(True)
+    ctx.render_device(n, nf, ev, flags, None, None, nf * 128)
+    st = ctx.stage_times()
+    ctx.set_stage_profiling(False)
+    print("stages: " + "  ".join("%s %.2f ms/%d" % (k, v[0], v[1]) for k, v in st.items()))

@@ -807,7 +807,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     base_p.tg = ctx->d_tg;
     base_p.wh = ctx->d_wh;
     base_p.events = ctx->d_events;
-    base_p.flags = d->flags;
+    base_p.flags = d->flags | (getenv("TBF_NO_FAST_PASS") ? 0x100u : 0u);
     base_p.pitch = pitch;
     ctx->launches = 0;
     int ring = 512; /* shared-memory delay-line ring: the largest any table set needs */

@@ -35,6 +35,8 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 #include "tbf_device.h"
 
@@ -123,13 +125,19 @@ __device__ __forceinline__ void ordered_pass(const uint16_t *n, const float *a, 
  * active wheel (src/tonegen.h:114-129); with a modular index the wrap split collapses
  * and one record per wheel suffices. */
 #define REC_TILE 64    /* active-list entries turned into records and summed at a time */
+#define REC_CAP 128   /* longest active list whose records persist across fragments   */
 #define WAVE_STAGES 8  /* wheels whose wave samples are in flight (cp.async) per warp   */
 struct TWarp {
     TgScalars sc;
-    int4 recA[REC_TILE];   /* wave_off, len, pos, env (-1 plain, 0..7 attack, 8..15 release) */
-    float4 recB[REC_TILE]; /* gs gs gv gv: gains duplicated for the packed f32x2 multiply */
-    float2 recC[REC_TILE]; /* gp gp */
-    float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas, read for env >= 0 only */
+    /* core-program records.  Lists of up to REC_CAP wheels keep their records here from one
+     * fragment to the next: a fragment without events only advances the read positions
+     * (fast_pass) and never touches the per-wheel state in HBM */
+    int4 recA[REC_CAP];    /* address of wave[pos] (lo, hi), samples before the wrap | len << 16,
+                              env (-1 plain, 0..7 attack, 8..15 release) */
+    float4 recB[REC_CAP];  /* gs gs gv gv: gains duplicated for the packed f32x2 multiply */
+    float2 recC[REC_CAP];  /* gp gp */
+    float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas of the current tile, env >= 0 only */
+    uint16_t wl[REC_CAP];  /* wheel of every record (to write the positions back) */
     float4 wstage[WAVE_STAGES][32]; /* [stage][lane]: samples lane, +32, +64, +96 of a wheel */
     float vring[TBF_VRING];
     float va[BLK], vb[BLK], vy[BLK];
@@ -137,6 +145,10 @@ struct TWarp {
     uint16_t removed_wheel[TBF_NOF_WHEELS + 1];
     uint8_t removed[TBF_NOF_WHEELS + 3];
     int recompute_routing, draw_bar_change, vib_on, perc_on;
+    /* raised by any lane during the active-list pass of a fragment.  Shared-memory flags read
+     * after a __syncwarp(), not warp votes: ptxas assumed the warp converged behind the tile
+     * loop, dropped the WARPSYNC before VOTE.ANY, and lanes got different answers */
+    int any_removed, any_env;
 };
 
 /* -- key events, one lane (src/tonegen.cpp:3096-3166 + the queue drain :3257-3327): the
@@ -365,7 +377,7 @@ __device__ void apply_scalar_event(TgScalars &sc, const DevTonegenTables *tg, co
  * 0..cnt-1.  Entry i of the active list touches only its own wheel's state, so lane l
  * handles entries base + l, base + l + 32. */
 __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegenTables *tg, TWarp &sm,
-                                                 int lane, int base, int cnt, int &my_ins, int &any_removed)
+                                                 int lane, int base, int cnt, int rec0, int &my_ins)
 {
     TgScalars &sc = sm.sc;
     const uint32_t routing = sc.oldRouting; /* already updated by lane 0 */
@@ -374,6 +386,12 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
 
     for (int i = base + lane; i < base + cnt; i += 32) {
         const int w = st->activeOscList[i];
+#ifdef TBF_DEBUG_CHECKS
+        if (w < 1 || w > TBF_NOF_WHEELS) {
+            printf("active list bad: slot %d i %d w %d base %d cnt %d rec0 %d lend %d lane %d keys %d\n", (int)(blockIdx.x * T_WARPS + threadIdx.x / 32), i, w, base, cnt, rec0, sc.activeOscLEnd, lane, sc.keyDownCount);
+            __trap();
+        }
+#endif
         OscState *o = &st->osc[w];
         const uint32_t rflags = o->rflags;
         const uint32_t len = tg->wave_length[w];
@@ -383,7 +401,7 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
 
         if (rflags & ORF_REMOVED) {
             sm.removed[i] = 1;
-            any_removed = 1;
+            sm.any_removed = 1;
             env = 8 + (i & 7);
             gs = o->sumSwell;
             gp = o->sumPercn;
@@ -455,22 +473,66 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
             my_ins += 1;
         }
         o->rflags = 0;
-        sm.recA[i - base] = make_int4((int)tg->wave_offset[w], (int)len, (int)pos, env);
-        sm.recB[i - base] = make_float4(gs, gs, gv, gv);
-        sm.recC[i - base] = make_float2(gp, gp);
-        if (env >= 0)
+        {
+            const unsigned long long addr =
+                (unsigned long long)(tg->wave_data + tg->wave_offset[w] + pos);
+            sm.recA[rec0 + i - base] = make_int4((int)(uint32_t)addr, (int)(uint32_t)(addr >> 32),
+                                                 (int)((len - pos) | (len << 16)), env);
+        }
+        sm.recB[rec0 + i - base] = make_float4(gs, gs, gv, gv);
+        sm.recC[rec0 + i - base] = make_float2(gp, gp);
+        sm.wl[rec0 + i - base] = (uint16_t)w;
+        if (env >= 0) {
             sm.recD[i - base] = make_float4(ds, dv, dp, 0.0f);
+            sm.any_env = 1;
+        }
+    }
+}
+
+/* A fragment without events, routing or drawbar change over a list whose records persist:
+ * every wheel plays on with unchanged gains, only its read position advances
+ * (src/tonegen.cpp:3521-3555: wrap test `length < pos + 128`, pos may rest at == length). */
+__device__ __forceinline__ void fast_pass(TWarp &sm, int lane, int n_act, int &my_ins)
+{
+    for (int i = lane; i < n_act; i += 32) {
+        int4 ra = sm.recA[i];
+        uint32_t rem = (uint32_t)ra.z & 0xFFFFu;
+        const uint32_t len = (uint32_t)ra.z >> 16;
+        unsigned long long addr = ((unsigned long long)(uint32_t)ra.y << 32) | (unsigned long long)(uint32_t)ra.x;
+        /* the position this record was rendered from moves on by one fragment */
+        if (rem < TBF_FRAGMENT) {
+            addr -= 4ull * (len - TBF_FRAGMENT);
+            rem = len - TBF_FRAGMENT + rem;
+        } else {
+            addr += 4ull * TBF_FRAGMENT;
+            rem -= TBF_FRAGMENT;
+        }
+        my_ins += (rem < TBF_FRAGMENT) ? 2 : 1;
+        ra.x = (int)(uint32_t)addr;
+        ra.y = (int)(uint32_t)(addr >> 32);
+        ra.z = (int)(rem | (len << 16));
+        sm.recA[i] = ra;
+    }
+}
+
+/* persistent records -> HBM: the position after the fragment last rendered from them */
+__device__ __forceinline__ void flush_positions(InstState *st, const TWarp &sm, int lane, int n_act)
+{
+    for (int i = lane; i < n_act; i += 32) {
+        const uint32_t z = (uint32_t)sm.recA[i].z;
+        const uint32_t rem = z & 0xFFFFu, len = z >> 16;
+        st->osc[sm.wl[i]].pos = (rem < TBF_FRAGMENT) ? TBF_FRAGMENT - rem : len - rem + TBF_FRAGMENT;
     }
 }
 
 /* end of the active-list pass: statistics, reference-UB flag, removal list */
 __device__ __forceinline__ void active_list_finish(InstState *st, TWarp &sm, int lane, int n_act,
-                                                   int my_ins, int any_removed)
+                                                   int my_ins)
 {
     TgScalars &sc = sm.sc;
+    __syncwarp(); /* removed[], the flags and the wheel state are visible to lane 0 */
     const int n_ins = __reduce_add_sync(FULL, my_ins);
-    any_removed = __any_sync(FULL, any_removed);
-    __syncwarp(); /* removed[] and the wheel state are visible to lane 0 */
+    const int any_removed = sm.any_removed;
 
     if (lane == 0) {
         sc.statFragments += 1;
@@ -510,27 +572,37 @@ __device__ __forceinline__ void active_list_finish(InstState *st, TWarp &sm, int
 }
 
 /* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples lane + 32k.
- * Request the four wave samples of this lane for record j into its stage: one base
- * address when the 128-sample read does not wrap (uniform per wheel), a modular index
- * else.  Every lane later reads back only what it requested itself. */
-__device__ __forceinline__ void wave_request(const float *__restrict__ wave, TWarp &sm, int j, int lane)
+ * Request the four wave samples of this lane for record j into its stage: one address and
+ * immediate offsets when the 128-sample read does not wrap (uniform per wheel), a step back
+ * by the loop length else.  Sample k of lane l goes to float (k + l/8) & 3 of the lane's
+ * float4: with that rotation the 4-byte writes of a warp fall into 32 different banks, and
+ * the lane reads its float4 back in one instruction.  The accumulators simply live in the
+ * rotated order for the whole fragment (core_end() undoes it).  Every lane reads back only
+ * what it requested itself. */
+__device__ __forceinline__ void wave_request(TWarp &sm, int rec, int j, int lane, const int (&rot)[4])
 {
-    const int4 ra = sm.recA[j];
-    const uint32_t len = (uint32_t)ra.y, pos = (uint32_t)ra.z;
-    const float *wp = wave + (uint32_t)ra.x;
+    const int4 ra = sm.recA[rec];
+    const uint32_t rem = (uint32_t)ra.z & 0xFFFFu, len = (uint32_t)ra.z >> 16;
+#ifdef TBF_DEBUG_CHECKS
+    if (rec < 0 || rec >= REC_CAP || j < 0 || len < 128 || len > 40000 || rem > len || (ra.x & 3) || ra.y == 0) {
+        printf("wave_request bad: rec %d j %d rem %u len %u addr %08x%08x env %d lane %d\n", rec, j, rem, len, ra.y, ra.x, ra.w, lane);
+        __trap();
+    }
+#endif
+    const float *q = reinterpret_cast<const float *>(
+                         ((unsigned long long)(uint32_t)ra.y << 32) | (unsigned long long)(uint32_t)ra.x) + lane;
     float *dst = reinterpret_cast<float *>(&sm.wstage[j & (WAVE_STAGES - 1)][lane]);
-    if (pos + TBF_FRAGMENT <= len) {
-        const float *q = wp + (pos + (uint32_t)lane);
+    if (rem >= TBF_FRAGMENT) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
-            __pipeline_memcpy_async(dst + k, q + 32 * k, 4);
+            __pipeline_memcpy_async(dst + rot[k], q + 32 * k, 4);
     } else {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            uint32_t idx = pos + (uint32_t)lane + 32u * k;
-            if (idx >= len)
-                idx -= len;
-            __pipeline_memcpy_async(dst + k, wp + idx, 4);
+            const float *src = q + 32 * k;
+            if ((uint32_t)(lane + 32 * k) >= rem)
+                src -= len;
+            __pipeline_memcpy_async(dst + rot[k], src, 4);
         }
     }
 }
@@ -562,95 +634,137 @@ __device__ __forceinline__ float lo2(f32x2 v) { return __uint_as_float((uint32_t
 __device__ __forceinline__ float hi2(f32x2 v) { return __uint_as_float((uint32_t)(v >> 32)); }
 
 /* accumulators and pending products of the three buffers (swell, scanner, percussion):
- * [0] = samples lane, lane+32; [1] = samples lane+64, lane+96 */
+ * [0] = float4 positions 0, 1; [1] = positions 2, 3 of the lane's staged samples.  Two wheels
+ * are pending at a time (A = even record of the last iteration, B = odd). */
+struct WheelProd {
+    f32x2 s[2], v[2], p[2];
+};
 struct CoreAcc {
-    f32x2 s[2], v[2], p[2];    /* running sums                                    */
-    f32x2 ps[2], pv[2], pp[2]; /* products of the previous wheel, not yet added   */
+    WheelProd sum;   /* running sums                                            */
+    WheelProd pa, pb; /* products of the previous two wheels, not yet added      */
 };
 
 /* The first instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680):
  * with the sums started at -0.0f an add IS a copy, bit for bit ((-0) + x = x for every x,
- * (-0) + (-0) = -0), and the same holds for the pending products. */
-__device__ __forceinline__ void core_begin(CoreAcc &a)
+ * (-0) + (-0) = -0); pending products of -0.0f are likewise an exact no-op. */
+__device__ __forceinline__ void prod_none(WheelProd &w)
 {
     const f32x2 nz = 0x8000000080000000ull;
 #pragma unroll
     for (int h = 0; h < 2; ++h)
-        a.s[h] = a.v[h] = a.p[h] = a.ps[h] = a.pv[h] = a.pp[h] = nz;
+        w.s[h] = w.v[h] = w.p[h] = nz;
+}
+__device__ __forceinline__ void core_begin(CoreAcc &a)
+{
+    prod_none(a.sum);
+    prod_none(a.pa);
+    prod_none(a.pb);
+}
+__device__ __forceinline__ void prod_add(WheelProd &sum, const WheelProd &w)
+{
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        sum.s[h] = add2(sum.s[h], w.s[h]);
+        sum.v[h] = add2(sum.v[h], w.v[h]);
+        sum.p[h] = add2(sum.p[h], w.p[h]);
+    }
 }
 
-/* records 0..cnt-1 of the current tile, in order (src/tonegen.cpp:3607-3687);
- * WAVE_STAGES wheels stay in flight */
-__device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int cnt,
-                                          CoreAcc &a)
+/* products of record i with the lane's staged samples x */
+__device__ __forceinline__ void wheel_products(const DevTonegenTables *tg, const TWarp &sm, int i,
+                                               int i_tile, int lane, const ulonglong2 x, WheelProd &w)
 {
-    const float *__restrict__ wave = tg->wave_data;
+    const ulonglong2 g = *reinterpret_cast<const ulonglong2 *>(&sm.recB[i]);
+    const f32x2 gp = *reinterpret_cast<const f32x2 *>(&sm.recC[i]);
+    const int env = sm.recA[i].w;
+    if (env < 0) {
+        w.s[0] = mul2(x.x, g.x);
+        w.s[1] = mul2(x.y, g.x);
+        w.v[0] = mul2(x.x, g.y);
+        w.v[1] = mul2(x.y, g.y);
+        w.p[0] = mul2(x.x, gp);
+        w.p[1] = mul2(x.y, gp);
+    } else { /* key click: gain = g + env[n] * (next - g), per sample */
+        const float4 d = sm.recD[i_tile]; /* only the pass's tiles (<= REC_TILE records) carry envelopes */
+        const float *ev = tg->env[env] + lane;
+        const float gs = lo2(g.x), gv = lo2(g.y), gpp = lo2(gp);
+        const int r = lane >> 3;
+        float e[4]; /* envelope sample of the wave sample held at position j */
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            e[j] = __ldg(ev + 32 * ((j - r) & 3));
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const f32x2 xx = h ? x.y : x.x;
+            const float e0 = e[2 * h], e1 = e[2 * h + 1];
+            w.s[h] = mul2(xx, pack2(__fadd_rn(gs, __fmul_rn(e0, d.x)), __fadd_rn(gs, __fmul_rn(e1, d.x))));
+            w.v[h] = mul2(xx, pack2(__fadd_rn(gv, __fmul_rn(e0, d.y)), __fadd_rn(gv, __fmul_rn(e1, d.y))));
+            w.p[h] = mul2(xx, pack2(__fadd_rn(gpp, __fmul_rn(e0, d.z)), __fadd_rn(gpp, __fmul_rn(e1, d.z))));
+        }
+    }
+}
+
+/* records 0..cnt-1 of the current tile, in order (src/tonegen.cpp:3607-3687), two per
+ * iteration; WAVE_STAGES wheels stay in flight.  The loop must stay rolled: the products
+ * formed in one iteration are added in the next (see the note at mul2/add2). */
+__device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
+                                          int cnt, CoreAcc &a)
+{
+    const int r = lane >> 3;
+    const int rot[4] = {r & 3, (r + 1) & 3, (r + 2) & 3, (r + 3) & 3};
 #pragma unroll
     for (int j = 0; j < WAVE_STAGES; ++j) {
         if (j < cnt)
-            wave_request(wave, sm, j, lane);
+            wave_request(sm, rec0 + j, j, lane, rot);
         __pipeline_commit();
     }
 #pragma unroll 1
-    for (int i = 0; i < cnt; ++i) {
-        __pipeline_wait_prior(WAVE_STAGES - 1); /* this lane's requests for record i landed */
-        const ulonglong2 x = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[i & (WAVE_STAGES - 1)][lane]);
+    for (int i = 0; i < cnt; i += 2) {
+        __pipeline_wait_prior(WAVE_STAGES - 2); /* this lane's requests for records i, i+1 landed */
+        const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[i & (WAVE_STAGES - 1)][lane]);
+        const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[(i + 1) & (WAVE_STAGES - 1)][lane]);
         if (i + WAVE_STAGES < cnt)
-            wave_request(wave, sm, i + WAVE_STAGES, lane);
+            wave_request(sm, rec0 + i + WAVE_STAGES, i + WAVE_STAGES, lane, rot);
         __pipeline_commit();
-        /* add the previous wheel's products ... */
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            a.s[h] = add2(a.s[h], a.ps[h]);
-            a.v[h] = add2(a.v[h], a.pv[h]);
-            a.p[h] = add2(a.p[h], a.pp[h]);
-        }
-        /* ... and form this wheel's */
-        const ulonglong2 g = *reinterpret_cast<const ulonglong2 *>(&sm.recB[i]);
-        const f32x2 gp = *reinterpret_cast<const f32x2 *>(&sm.recC[i]);
-        const int env = sm.recA[i].w;
-        if (env < 0) {
-            a.ps[0] = mul2(x.x, g.x);
-            a.ps[1] = mul2(x.y, g.x);
-            a.pv[0] = mul2(x.x, g.y);
-            a.pv[1] = mul2(x.y, g.y);
-            a.pp[0] = mul2(x.x, gp);
-            a.pp[1] = mul2(x.y, gp);
-        } else { /* key click: gain = g + env[n] * (next - g), per sample */
-            const float4 d = sm.recD[i];
-            const float *ev = tg->env[env] + lane;
-            const float gs = lo2(g.x), gv = lo2(g.y), gpp = lo2(gp);
-            float e[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                e[k] = __ldg(ev + 32 * k);
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const f32x2 xx = h ? x.y : x.x;
-                const float e0 = e[2 * h], e1 = e[2 * h + 1];
-                a.ps[h] = mul2(xx, pack2(__fadd_rn(gs, __fmul_rn(e0, d.x)), __fadd_rn(gs, __fmul_rn(e1, d.x))));
-                a.pv[h] = mul2(xx, pack2(__fadd_rn(gv, __fmul_rn(e0, d.y)), __fadd_rn(gv, __fmul_rn(e1, d.y))));
-                a.pp[h] = mul2(xx, pack2(__fadd_rn(gpp, __fmul_rn(e0, d.z)), __fadd_rn(gpp, __fmul_rn(e1, d.z))));
-            }
-        }
+        if (i + WAVE_STAGES + 1 < cnt)
+            wave_request(sm, rec0 + i + WAVE_STAGES + 1, i + WAVE_STAGES + 1, lane, rot);
+        __pipeline_commit();
+        /* add the previous two wheels' products, in list order ... */
+        prod_add(a.sum, a.pa);
+        prod_add(a.sum, a.pb);
+        /* ... and form this pair's */
+        wheel_products(tg, sm, rec0 + i, i, lane, xa, a.pa);
+        if (i + 1 < cnt)
+            wheel_products(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
+        else
+            prod_none(a.pb);
     }
 }
 
 /* the last wheel's products; an empty active list leaves the buffers zeroed
  * (src/tonegen.cpp:3607-3612) */
-__device__ __forceinline__ void core_end(CoreAcc &a, int n_act, float (&s)[4], float (&v)[4], float (&p)[4])
+__device__ __forceinline__ void core_end(CoreAcc &a, int n_act, int lane, float (&s)[4], float (&v)[4],
+                                         float (&p)[4])
 {
+    float rs[4], rv[4], rp[4]; /* rotated order: position j holds sample (j - lane/8) & 3 */
+    prod_add(a.sum, a.pa);
+    prod_add(a.sum, a.pb);
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-        a.s[h] = add2(a.s[h], a.ps[h]);
-        a.v[h] = add2(a.v[h], a.pv[h]);
-        a.p[h] = add2(a.p[h], a.pp[h]);
-        s[2 * h] = lo2(a.s[h]);
-        s[2 * h + 1] = hi2(a.s[h]);
-        v[2 * h] = lo2(a.v[h]);
-        v[2 * h + 1] = hi2(a.v[h]);
-        p[2 * h] = lo2(a.p[h]);
-        p[2 * h + 1] = hi2(a.p[h]);
+        rs[2 * h] = lo2(a.sum.s[h]);
+        rs[2 * h + 1] = hi2(a.sum.s[h]);
+        rv[2 * h] = lo2(a.sum.v[h]);
+        rv[2 * h + 1] = hi2(a.sum.v[h]);
+        rp[2 * h] = lo2(a.sum.p[h]);
+        rp[2 * h + 1] = hi2(a.sum.p[h]);
+    }
+    const int r = lane >> 3;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { /* sample k sits at position (k + r) & 3 */
+        const int j = (k + r) & 3;
+        s[k] = j == 0 ? rs[0] : j == 1 ? rs[1] : j == 2 ? rs[2] : rs[3];
+        v[k] = j == 0 ? rv[0] : j == 1 ? rv[1] : j == 2 ? rv[2] : rv[3];
+        p[k] = j == 0 ? rp[0] : j == 1 ? rp[1] : j == 2 ? rp[2] : rp[3];
     }
     if (n_act == 0) {
 #pragma unroll
@@ -714,6 +828,36 @@ __device__ __forceinline__ float vibrato_block(const DevTonegenTables *tg, TWarp
     return y;
 }
 
+#ifdef TBF_DEBUG_CHECKS
+__device__ void check_list(InstState *st, TWarp &sm, int lane, int where, int f, int a)
+{
+    __syncwarp();
+    const int n = sm.sc.activeOscLEnd;
+    int bad = 0;
+    for (int i = lane; i < n; i += 32) {
+        const int w = st->activeOscList[i];
+        if (w < 1 || w > TBF_NOF_WHEELS || st->osc[w].aclPos != i) {
+            bad = 1;
+            if (blockIdx.x == 0 && threadIdx.x < 32)
+                printf("  list[%d] = %d aclPos %d rflags %x ref %d\n", i, w, (w >= 0 && w <= TBF_NOF_WHEELS) ? st->osc[w].aclPos : -99,
+                       (w >= 0 && w <= TBF_NOF_WHEELS) ? st->osc[w].rflags : 0u, (w >= 0 && w <= TBF_NOF_WHEELS) ? st->osc[w].refCount : 0);
+        }
+    }
+    if (n < 0 || n > TBF_NOF_WHEELS)
+        bad = 1;
+    const int bad_local = bad;
+    bad = __any_sync(FULL, bad);
+    if (bad) {
+        if (blockIdx.x == 0 && threadIdx.x < 32)
+            printf("  lane %d bad_local %d n %d active %08x\n", lane, bad_local, n, __activemask());
+        if (lane == 0)
+            printf("check_list: slot %d where %d frag %d a %d lend %d\n",
+                   (int)(blockIdx.x * T_WARPS + threadIdx.x / 32), where, f, a, n);
+        __syncwarp();
+        __trap();
+    }
+}
+#endif
 __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -741,13 +885,20 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
     FragCtl *ctl_row = p.ctl + (size_t)slot * p.n_fragments;
     __syncwarp();
 
+    bool cache_valid = false; /* the records in shared memory describe the last fragment */
+#ifdef TBF_DEBUG_CHECKS
+    int dbg_fast = 0;
+#endif
+    int n_act_cached = 0;
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
         /* -- control events that precede this fragment -- */
+        bool ev_applied = false;
         while (ev_cur < ev_end) {
             const tbf_event *evp = p.events + ev_cur;
             if (evp->fragment > p.frag_base + f)
                 break;
             const int type = evp->type, a = evp->a, b = evp->b;
+            ev_applied = true;
             if (type == TBF_EV_KEY_ON || type == TBF_EV_KEY_OFF) {
                 if (a >= 0 && a < TBF_MAX_KEYS) {
                     if (type == TBF_EV_KEY_ON)
@@ -759,6 +910,9 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
                 apply_scalar_event(sc, tg, type, a, b);
             }
             __syncwarp();
+#ifdef TBF_DEBUG_CHECKS
+            check_list(st, sm, lane, type, (int)f, a);
+#endif
             ++ev_cur;
         }
         /* -- routing, key compression target, what stage R needs -- */
@@ -772,6 +926,7 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
             if (sm.recompute_routing)
                 sc.oldRouting = sc.newRouting;
             sm.draw_bar_change = sc.drawBarChange;
+            sm.any_removed = sm.any_env = 0;
             sm.vib_on = (sc.oldRouting & RT_VIB) != 0;
             sm.perc_on = (sc.oldRouting & RT_PERC) != 0;
             FragCtl c;
@@ -790,19 +945,52 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
         float swl[4], vib[4], prc[4];
         {
             const int n_act = sc.activeOscLEnd;
-            int my_ins = 0, any_removed = 0;
+            int my_ins = 0;
             CoreAcc acc;
             core_begin(acc);
-            for (int base = 0; base < n_act; base += REC_TILE) {
-                const int cnt = min(REC_TILE, n_act - base);
-                active_list_tile(st, tg, sm, lane, base, cnt, my_ins, any_removed);
+            if (cache_valid && !ev_applied && !sm.recompute_routing && !sm.draw_bar_change) {
+                /* quiet fragment: the records of the last fragment, one fragment further */
+#ifdef TBF_DEBUG_CHECKS
+                ++dbg_fast;
+#endif
+                fast_pass(sm, lane, n_act, my_ins);
                 __syncwarp();
-                core_tile(tg, sm, lane, cnt, acc);
+                core_tile(tg, sm, lane, 0, n_act, acc);
                 __syncwarp();
+                const int n_ins = __reduce_add_sync(FULL, my_ins);
+                if (lane == 0) {
+                    sc.statFragments += 1;
+                    sc.statActiveWheels += (unsigned long long)n_act;
+                    if (n_ins > 256)
+                        sc.errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
+                }
+            } else {
+                if (cache_valid) /* the pass below reads the positions from HBM */
+                    flush_positions(st, sm, lane, n_act_cached);
+                __syncwarp();
+                const bool persist = n_act <= REC_CAP;
+                for (int base = 0; base < n_act; base += REC_TILE) {
+                    const int cnt = min(REC_TILE, n_act - base);
+                    const int rec0 = persist ? base : 0;
+                    active_list_tile(st, tg, sm, lane, base, cnt, rec0, my_ins);
+                    __syncwarp();
+                    core_tile(tg, sm, lane, rec0, cnt, acc);
+                    __syncwarp();
+                }
+                active_list_finish(st, sm, lane, n_act, my_ins);
+#ifdef TBF_DEBUG_CHECKS
+                check_list(st, sm, lane, 1000, (int)f, n_act);
+#endif
+                /* the records can be reused if they are all plain and the list kept its order */
+                cache_valid = persist && !sm.any_env && !sm.any_removed && !sm.recompute_routing &&
+                              !sm.draw_bar_change; /* (their records still carry the old gains) */
+                n_act_cached = n_act;
+                if (p.flags & 0x100u) /* debugging: always take the full pass */
+                    cache_valid = false;
             }
-            core_end(acc, n_act, swl, vib, prc);
-            active_list_finish(st, sm, lane, n_act, my_ins, any_removed);
+            core_end(acc, n_act, lane, swl, vib, prc);
         }
+        __syncwarp();
 
         /* -- scanner, percussion high-pass, hand-over to stage R -- */
         const float pz = sc.pz;
@@ -842,6 +1030,12 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
     }
 
     /* ---- write the staged state back ---- */
+#ifdef TBF_DEBUG_CHECKS
+    if (slot == 5 && lane == 0)
+        printf("slot 5: %d of %u fragments on the fast path, lend %d\n", dbg_fast, p.n_fragments, sc.activeOscLEnd);
+#endif
+    if (cache_valid)
+        flush_positions(st, sm, lane, n_act_cached);
     if (lane == 0)
         p.ev_cursor_t[slot] = ev_cur;
     for (int i = lane; i < (int)(sizeof(TgScalars) / 4); i += 32)
@@ -1691,6 +1885,18 @@ template <typename K> int set_smem(K kernel, size_t smem, int *have)
 
 } /* namespace */
 
+/* TBF_DEBUG_SYNC=1: wait for every stage kernel and name the one that faulted (the pool has no
+ * compute-sanitizer; -DTBF_DEBUG_CHECKS adds device-side invariant checks to stage T) */
+static void debug_sync(void *stream, const char *stage)
+{
+    static const int on = getenv("TBF_DEBUG_SYNC") != nullptr;
+    if (!on)
+        return;
+    const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+    if (e != cudaSuccess)
+        fprintf(stderr, "tbf: stage %s: %s\n", stage, cudaGetErrorString(e));
+}
+
 size_t tbf_stage_t_smem(void) { return sizeof(TWarp) * T_WARPS; }
 size_t tbf_stage_w_smem(int ring_size)
 {
@@ -1705,6 +1911,7 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
         return rc;
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
     tbf_stage_t<<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
+    debug_sync(stream, "T");
     return (int)cudaGetLastError();
 }
 
@@ -1715,6 +1922,7 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
     tbf_stage_r<<<grid, 32, sizeof(RSmem), (cudaStream_t)stream>>>(p);
+    debug_sync(stream, "R");
     return (int)cudaGetLastError();
 }
 
@@ -1726,6 +1934,7 @@ int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
         return rc;
     const uint32_t grid = (p.n_instances + W_WARPS - 1) / W_WARPS;
     tbf_stage_w<<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
+    debug_sync(stream, "W");
     return (int)cudaGetLastError();
 }
 
@@ -1736,6 +1945,7 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream)
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
     tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
+    debug_sync(stream, "D");
     return (int)cudaGetLastError();
 }
 
