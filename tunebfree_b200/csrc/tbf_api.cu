@@ -229,6 +229,8 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
             return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave slice out of range");
         if (t->wave_length[w] && t->wave_length[w] < TBF_FRAGMENT)
             return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave shorter than one fragment");
+        if (t->wave_length[w] > 0xFFFFu)
+            return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave longer than 65535 samples");
     }
     for (int k = 0; k < TBF_MAX_KEYS; ++k)
         if (t->contrib_start[k] > t->contrib_start[k + 1])
@@ -283,11 +285,31 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
         CK(cudaMemcpy(s.rw, run_wheel.data(), sizeof(uint16_t) * nr, cudaMemcpyHostToDevice));
         CK(cudaMemcpy(s.rn, run_count.data(), sizeof(uint16_t) * nr, cudaMemcpyHostToDevice));
     }
-    CK(cudaMalloc(&s.wave, sizeof(float) * std::max<uint64_t>(1, t->wave_total)));
+    /* The device keeps four copies of every wave, copy s rotated left by s samples and extended
+     * by one fragment of wrap-around: a 128-sample read from any position then starts 16-byte
+     * aligned in copy (pos & 3) and never wraps, so a lane fetches its four consecutive samples
+     * with one 16-byte cp.async (tbf_kernels.cu, wave_request). */
+    std::vector<float> wave4;
+    uint32_t wave4_offset[TBF_NOF_WHEELS + 1] = {0};
+    for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
+        const uint32_t len = t->wave_length[w];
+        if (!len)
+            continue;
+        const uint32_t cl = tbf_wave_copy_len(len);
+        if (wave4.size() + (size_t)4 * cl > 0xFFFFFFFFull)
+            return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave store too large");
+        wave4_offset[w] = (uint32_t)wave4.size();
+        const float *src = t->wave_data + t->wave_offset[w];
+        for (uint32_t c = 0; c < 4; ++c)
+            for (uint32_t i = 0; i < cl; ++i)
+                wave4.push_back(src[(i + c) % len]);
+    }
+    CK(cudaMalloc(&s.wave, sizeof(float) * std::max<size_t>(4, wave4.size())));
     CK(cudaMalloc(&s.cw, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
     CK(cudaMalloc(&s.cb, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
     CK(cudaMalloc(&s.cl, sizeof(float) * std::max<uint32_t>(1, nc)));
-    CK(cudaMemcpy(s.wave, t->wave_data, sizeof(float) * t->wave_total, cudaMemcpyHostToDevice));
+    if (!wave4.empty())
+        CK(cudaMemcpy(s.wave, wave4.data(), sizeof(float) * wave4.size(), cudaMemcpyHostToDevice));
     if (nc) {
         CK(cudaMemcpy(s.cw, t->contrib_wheel, sizeof(uint16_t) * nc, cudaMemcpyHostToDevice));
         CK(cudaMemcpy(s.cb, t->contrib_bus, sizeof(uint16_t) * nc, cudaMemcpyHostToDevice));
@@ -298,7 +320,7 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     s.host.contrib_level = nullptr;
 
     DevTonegenTables *d = new DevTonegenTables();
-    d->wave_data = s.wave;
+    d->wave4 = s.wave;
     d->contrib_wheel = s.cw;
     d->contrib_bus = s.cb;
     d->contrib_level = s.cl;
@@ -306,7 +328,7 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     d->run_count = s.rn;
     memcpy(d->run_start, run_start.data(), sizeof(d->run_start));
     d->coop_events = coop ? 1 : 0;
-    memcpy(d->wave_offset, t->wave_offset, sizeof(d->wave_offset));
+    memcpy(d->wave4_offset, wave4_offset, sizeof(d->wave4_offset));
     memcpy(d->wave_length, t->wave_length, sizeof(d->wave_length));
     memcpy(d->contrib_start, t->contrib_start, sizeof(d->contrib_start));
     for (int r = 0; r < 8; ++r) {

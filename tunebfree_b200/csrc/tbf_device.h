@@ -100,9 +100,16 @@ struct InstState {
     float wbuf[4][TBF_WHIRL_BUF]; /* HL HR DL DR */
 };
 
+/* Floats per rotated copy of a wave of `len` samples: copy c holds wave[(i + c) % len] for
+ * i < len + 128, padded to whole float4s.  Copies 0..3 of a wheel lie back to back. */
+static inline __host__ __device__ uint32_t tbf_wave_copy_len(uint32_t len)
+{
+    return (len + TBF_FRAGMENT + 3u) & ~3u;
+}
+
 /* tbf_tonegen_tables with device pointers */
 struct DevTonegenTables {
-    const float *wave_data;
+    const float *wave4; /* four rotated, wrap-extended copies per wave, see tbf_wave_copy_len() */
     const uint16_t *contrib_wheel;
     const uint16_t *contrib_bus;
     const float *contrib_level;
@@ -112,7 +119,7 @@ struct DevTonegenTables {
     const uint16_t *run_count;
     uint32_t run_start[TBF_MAX_KEYS + 1];
     int32_t coop_events; /* 1: every key's list is wheel-sorted with unique (wheel, bus) pairs */
-    uint32_t wave_offset[TBF_NOF_WHEELS + 1];
+    uint32_t wave4_offset[TBF_NOF_WHEELS + 1]; /* floats, multiple of 4: copy 0 of the wheel */
     uint32_t wave_length[TBF_NOF_WHEELS + 1];
     uint32_t contrib_start[TBF_MAX_KEYS + 1];
     float env[2 * 8][TBF_FRAGMENT]; /* rows 0..7 attack, 8..15 release (row 8 of the

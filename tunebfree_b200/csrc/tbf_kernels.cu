@@ -132,13 +132,13 @@ struct TWarp {
     /* core-program records.  Lists of up to REC_CAP wheels keep their records here from one
      * fragment to the next: a fragment without events only advances the read positions
      * (fast_pass) and never touches the per-wheel state in HBM */
-    int4 recA[REC_CAP];    /* address of wave[pos] (lo, hi), samples before the wrap | len << 16,
-                              env (-1 plain, 0..7 attack, 8..15 release) */
+    int4 recA[REC_CAP];    /* address of the lane-0 float4 of the 128 samples (lo, hi), read
+                              position, env (-1 plain, 0..7 attack, 8..15 release) */
     float4 recB[REC_CAP];  /* gs gs gv gv: gains duplicated for the packed f32x2 multiply */
     float2 recC[REC_CAP];  /* gp gp */
     float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas of the current tile, env >= 0 only */
-    uint16_t wl[REC_CAP];  /* wheel of every record (to write the positions back) */
-    float4 wstage[WAVE_STAGES][32]; /* [stage][lane]: samples lane, +32, +64, +96 of a wheel */
+    uint2 recP[REC_CAP];   /* wave length | wheel << 16, wave4_offset of the wheel */
+    float4 wstage[WAVE_STAGES][32]; /* [stage][lane]: samples 4*lane .. 4*lane+3 of a wheel */
     float vring[TBF_VRING];
     float va[BLK], vb[BLK], vy[BLK];
     uint16_t vn[BLK];
@@ -373,6 +373,19 @@ __device__ void apply_scalar_event(TgScalars &sc, const DevTonegenTables *tg, co
     }
 }
 
+/* read position one fragment later (src/tonegen.cpp:3376, :3524) */
+__device__ __forceinline__ uint32_t next_position(uint32_t pos, uint32_t len)
+{
+    return (len < pos + TBF_FRAGMENT) ? TBF_FRAGMENT - (len - pos) : pos + TBF_FRAGMENT;
+}
+
+/* where the 128 samples from `pos` start in the wave store: copy (pos & 3), float4-aligned */
+__device__ __forceinline__ unsigned long long wave_addr(const float *wave4, uint32_t off4, uint32_t len,
+                                                        uint32_t pos)
+{
+    return (unsigned long long)(wave4 + off4 + (pos & 3u) * tbf_wave_copy_len(len) + (pos & ~3u));
+}
+
 /* active-list pass (src/tonegen.cpp:3333-3594), entries [base, base + cnt) -> records
  * 0..cnt-1.  Entry i of the active list touches only its own wheel's state, so lane l
  * handles entries base + l, base + l + 32. */
@@ -474,14 +487,14 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
         }
         o->rflags = 0;
         {
-            const unsigned long long addr =
-                (unsigned long long)(tg->wave_data + tg->wave_offset[w] + pos);
-            sm.recA[rec0 + i - base] = make_int4((int)(uint32_t)addr, (int)(uint32_t)(addr >> 32),
-                                                 (int)((len - pos) | (len << 16)), env);
+            const uint32_t off4 = tg->wave4_offset[w];
+            const unsigned long long addr = wave_addr(tg->wave4, off4, len, pos);
+            sm.recA[rec0 + i - base] =
+                make_int4((int)(uint32_t)addr, (int)(uint32_t)(addr >> 32), (int)pos, env);
+            sm.recP[rec0 + i - base] = make_uint2(len | ((uint32_t)w << 16), off4);
         }
         sm.recB[rec0 + i - base] = make_float4(gs, gs, gv, gv);
         sm.recC[rec0 + i - base] = make_float2(gp, gp);
-        sm.wl[rec0 + i - base] = (uint16_t)w;
         if (env >= 0) {
             sm.recD[i - base] = make_float4(ds, dv, dp, 0.0f);
             sm.any_env = 1;
@@ -492,25 +505,21 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
 /* A fragment without events, routing or drawbar change over a list whose records persist:
  * every wheel plays on with unchanged gains, only its read position advances
  * (src/tonegen.cpp:3521-3555: wrap test `length < pos + 128`, pos may rest at == length). */
-__device__ __forceinline__ void fast_pass(TWarp &sm, int lane, int n_act, int &my_ins)
+__device__ __forceinline__ void fast_pass(const DevTonegenTables *tg, TWarp &sm, int lane, int n_act,
+                                          int &my_ins)
 {
+    const float *wave4 = tg->wave4;
     for (int i = lane; i < n_act; i += 32) {
         int4 ra = sm.recA[i];
-        uint32_t rem = (uint32_t)ra.z & 0xFFFFu;
-        const uint32_t len = (uint32_t)ra.z >> 16;
-        unsigned long long addr = ((unsigned long long)(uint32_t)ra.y << 32) | (unsigned long long)(uint32_t)ra.x;
+        const uint2 rp = sm.recP[i];
+        const uint32_t len = rp.x & 0xFFFFu;
         /* the position this record was rendered from moves on by one fragment */
-        if (rem < TBF_FRAGMENT) {
-            addr -= 4ull * (len - TBF_FRAGMENT);
-            rem = len - TBF_FRAGMENT + rem;
-        } else {
-            addr += 4ull * TBF_FRAGMENT;
-            rem -= TBF_FRAGMENT;
-        }
-        my_ins += (rem < TBF_FRAGMENT) ? 2 : 1;
+        const uint32_t pos = next_position((uint32_t)ra.z, len);
+        my_ins += (len < pos + TBF_FRAGMENT) ? 2 : 1;
+        const unsigned long long addr = wave_addr(wave4, rp.y, len, pos);
         ra.x = (int)(uint32_t)addr;
         ra.y = (int)(uint32_t)(addr >> 32);
-        ra.z = (int)(rem | (len << 16));
+        ra.z = (int)pos;
         sm.recA[i] = ra;
     }
 }
@@ -519,9 +528,8 @@ __device__ __forceinline__ void fast_pass(TWarp &sm, int lane, int n_act, int &m
 __device__ __forceinline__ void flush_positions(InstState *st, const TWarp &sm, int lane, int n_act)
 {
     for (int i = lane; i < n_act; i += 32) {
-        const uint32_t z = (uint32_t)sm.recA[i].z;
-        const uint32_t rem = z & 0xFFFFu, len = z >> 16;
-        st->osc[sm.wl[i]].pos = (rem < TBF_FRAGMENT) ? TBF_FRAGMENT - rem : len - rem + TBF_FRAGMENT;
+        const uint32_t x = sm.recP[i].x;
+        st->osc[x >> 16].pos = next_position((uint32_t)sm.recA[i].z, x & 0xFFFFu);
     }
 }
 
@@ -571,40 +579,23 @@ __device__ __forceinline__ void active_list_finish(InstState *st, TWarp &sm, int
     __syncwarp();
 }
 
-/* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples lane + 32k.
- * Request the four wave samples of this lane for record j into its stage: one address and
- * immediate offsets when the 128-sample read does not wrap (uniform per wheel), a step back
- * by the loop length else.  Sample k of lane l goes to float (k + l/8) & 3 of the lane's
- * float4: with that rotation the 4-byte writes of a warp fall into 32 different banks, and
- * the lane reads its float4 back in one instruction.  The accumulators simply live in the
- * rotated order for the whole fragment (core_end() undoes it).  Every lane reads back only
- * what it requested itself. */
-__device__ __forceinline__ void wave_request(TWarp &sm, int rec, int j, int lane, const int (&rot)[4])
+/* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples 4*lane .. 4*lane+3 of the
+ * fragment while the wheels are summed.  The device's wave store (tbf_api.cu) has an aligned,
+ * never-wrapping image of every 128-sample read, so a lane requests its four samples of record
+ * `rec` with ONE 16-byte cp.async into its own float4 of stage `slot` and reads them back with
+ * one LDS.128.  Every lane reads back only what it requested itself. */
+__device__ __forceinline__ void wave_request(TWarp &sm, int rec, int slot, int lane)
 {
-    const int4 ra = sm.recA[rec];
-    const uint32_t rem = (uint32_t)ra.z & 0xFFFFu, len = (uint32_t)ra.z >> 16;
+    const uint2 a = *reinterpret_cast<const uint2 *>(&sm.recA[rec]);
+    const float4 *q =
+        reinterpret_cast<const float4 *>(((unsigned long long)a.y << 32) | (unsigned long long)a.x) + lane;
 #ifdef TBF_DEBUG_CHECKS
-    if (rec < 0 || rec >= REC_CAP || j < 0 || len < 128 || len > 40000 || rem > len || (ra.x & 3) || ra.y == 0) {
-        printf("wave_request bad: rec %d j %d rem %u len %u addr %08x%08x env %d lane %d\n", rec, j, rem, len, ra.y, ra.x, ra.w, lane);
+    if (rec < 0 || rec >= REC_CAP || slot < 0 || slot >= WAVE_STAGES || (a.x & 15u) || a.y == 0) {
+        printf("wave_request bad: rec %d slot %d addr %08x%08x lane %d\n", rec, slot, a.y, a.x, lane);
         __trap();
     }
 #endif
-    const float *q = reinterpret_cast<const float *>(
-                         ((unsigned long long)(uint32_t)ra.y << 32) | (unsigned long long)(uint32_t)ra.x) + lane;
-    float *dst = reinterpret_cast<float *>(&sm.wstage[j & (WAVE_STAGES - 1)][lane]);
-    if (rem >= TBF_FRAGMENT) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            __pipeline_memcpy_async(dst + rot[k], q + 32 * k, 4);
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float *src = q + 32 * k;
-            if ((uint32_t)(lane + 32 * k) >= rem)
-                src -= len;
-            __pipeline_memcpy_async(dst + rot[k], src, 4);
-        }
-    }
+    __pipeline_memcpy_async(&sm.wstage[slot][lane], q, 16);
 }
 
 /* Packed pairs of floats for Blackwell's two-wide FP32 instructions (FMUL2 / FADD2): each
@@ -631,16 +622,15 @@ __device__ __forceinline__ f32x2 pack2(float lo, float hi)
     return ((f32x2)__float_as_uint(hi) << 32) | (f32x2)__float_as_uint(lo);
 }
 __device__ __forceinline__ float lo2(f32x2 v) { return __uint_as_float((uint32_t)v); }
-__device__ __forceinline__ float hi2(f32x2 v) { return __uint_as_float((uint32_t)(v >> 32)); }
 
 /* accumulators and pending products of the three buffers (swell, scanner, percussion):
- * [0] = float4 positions 0, 1; [1] = positions 2, 3 of the lane's staged samples.  Two wheels
- * are pending at a time (A = even record of the last iteration, B = odd). */
+ * [0] = samples 4*lane, 4*lane+1; [1] = samples 4*lane+2, 4*lane+3.  Two wheels are pending at
+ * a time (A = even record of the last iteration, B = odd). */
 struct WheelProd {
     f32x2 s[2], v[2], p[2];
 };
 struct CoreAcc {
-    WheelProd sum;   /* running sums                                            */
+    WheelProd sum;    /* running sums                                            */
     WheelProd pa, pb; /* products of the previous two wheels, not yet added      */
 };
 
@@ -670,14 +660,16 @@ __device__ __forceinline__ void prod_add(WheelProd &sum, const WheelProd &w)
     }
 }
 
-/* products of record i with the lane's staged samples x */
+/* products of record i with the lane's staged samples x.  ENV = false: the caller knows that
+ * every record of the tile plays with constant gains (no key click in flight). */
+template <bool ENV>
 __device__ __forceinline__ void wheel_products(const DevTonegenTables *tg, const TWarp &sm, int i,
                                                int i_tile, int lane, const ulonglong2 x, WheelProd &w)
 {
     const ulonglong2 g = *reinterpret_cast<const ulonglong2 *>(&sm.recB[i]);
     const f32x2 gp = *reinterpret_cast<const f32x2 *>(&sm.recC[i]);
-    const int env = sm.recA[i].w;
-    if (env < 0) {
+    const int env = ENV ? sm.recA[i].w : -1;
+    if (!ENV || env < 0) {
         w.s[0] = mul2(x.x, g.x);
         w.s[1] = mul2(x.y, g.x);
         w.v[0] = mul2(x.x, g.y);
@@ -686,13 +678,12 @@ __device__ __forceinline__ void wheel_products(const DevTonegenTables *tg, const
         w.p[1] = mul2(x.y, gp);
     } else { /* key click: gain = g + env[n] * (next - g), per sample */
         const float4 d = sm.recD[i_tile]; /* only the pass's tiles (<= REC_TILE records) carry envelopes */
-        const float *ev = tg->env[env] + lane;
+        const float *ev = tg->env[env] + 4 * lane;
         const float gs = lo2(g.x), gv = lo2(g.y), gpp = lo2(gp);
-        const int r = lane >> 3;
-        float e[4]; /* envelope sample of the wave sample held at position j */
+        float e[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            e[j] = __ldg(ev + 32 * ((j - r) & 3));
+            e[j] = __ldg(ev + j);
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const f32x2 xx = h ? x.y : x.x;
@@ -704,68 +695,85 @@ __device__ __forceinline__ void wheel_products(const DevTonegenTables *tg, const
     }
 }
 
-/* records 0..cnt-1 of the current tile, in order (src/tonegen.cpp:3607-3687), two per
- * iteration; WAVE_STAGES wheels stay in flight.  The loop must stay rolled: the products
- * formed in one iteration are added in the next (see the note at mul2/add2). */
+/* records 0..cnt-1 of the current tile, in order (src/tonegen.cpp:3607-3687), two per trip;
+ * WAVE_STAGES wheels stay in flight, committed in pairs.  The loops must stay rolled: the
+ * products formed in one trip are added in the next (see the note at mul2/add2).  Without
+ * envelopes the bulk of the tile runs in a trip without any conditional. */
+template <bool ENV>
 __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
                                           int cnt, CoreAcc &a)
 {
-    const int r = lane >> 3;
-    const int rot[4] = {r & 3, (r + 1) & 3, (r + 2) & 3, (r + 3) & 3};
 #pragma unroll
-    for (int j = 0; j < WAVE_STAGES; ++j) {
+    for (int j = 0; j < WAVE_STAGES; j += 2) {
         if (j < cnt)
-            wave_request(sm, rec0 + j, j, lane, rot);
+            wave_request(sm, rec0 + j, j, lane);
+        if (j + 1 < cnt)
+            wave_request(sm, rec0 + j + 1, j + 1, lane);
         __pipeline_commit();
     }
+    int i = 0;
+    if (!ENV) {
 #pragma unroll 1
-    for (int i = 0; i < cnt; i += 2) {
-        __pipeline_wait_prior(WAVE_STAGES - 2); /* this lane's requests for records i, i+1 landed */
-        const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[i & (WAVE_STAGES - 1)][lane]);
-        const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[(i + 1) & (WAVE_STAGES - 1)][lane]);
+        for (; i + WAVE_STAGES + 1 < cnt; i += 2) {
+            __pipeline_wait_prior(WAVE_STAGES / 2 - 1); /* this lane's records i, i+1 landed */
+            const int s = i & (WAVE_STAGES - 1);
+            const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
+            const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
+            wave_request(sm, rec0 + i + WAVE_STAGES, s, lane);
+            wave_request(sm, rec0 + i + WAVE_STAGES + 1, s + 1, lane);
+            __pipeline_commit();
+            prod_add(a.sum, a.pa);
+            prod_add(a.sum, a.pb);
+            wheel_products<false>(tg, sm, rec0 + i, i, lane, xa, a.pa);
+            wheel_products<false>(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
+        }
+    }
+#pragma unroll 1
+    for (; i < cnt; i += 2) {
+        __pipeline_wait_prior(WAVE_STAGES / 2 - 1);
+        const int s = i & (WAVE_STAGES - 1);
+        const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
+        const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
         if (i + WAVE_STAGES < cnt)
-            wave_request(sm, rec0 + i + WAVE_STAGES, i + WAVE_STAGES, lane, rot);
-        __pipeline_commit();
+            wave_request(sm, rec0 + i + WAVE_STAGES, s, lane);
         if (i + WAVE_STAGES + 1 < cnt)
-            wave_request(sm, rec0 + i + WAVE_STAGES + 1, i + WAVE_STAGES + 1, lane, rot);
+            wave_request(sm, rec0 + i + WAVE_STAGES + 1, s + 1, lane);
         __pipeline_commit();
         /* add the previous two wheels' products, in list order ... */
         prod_add(a.sum, a.pa);
         prod_add(a.sum, a.pb);
         /* ... and form this pair's */
-        wheel_products(tg, sm, rec0 + i, i, lane, xa, a.pa);
+        wheel_products<ENV>(tg, sm, rec0 + i, i, lane, xa, a.pa);
         if (i + 1 < cnt)
-            wheel_products(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
+            wheel_products<ENV>(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
         else
             prod_none(a.pb);
     }
 }
 
-/* the last wheel's products; an empty active list leaves the buffers zeroed
- * (src/tonegen.cpp:3607-3612) */
-__device__ __forceinline__ void core_end(CoreAcc &a, int n_act, int lane, float (&s)[4], float (&v)[4],
-                                         float (&p)[4])
+/* the last wheels' products, then from lane = 4 consecutive samples to lane = sample of a
+ * 32-sample block (s[k] = sample 32k + lane) through the idle wave stages; an empty active
+ * list leaves the buffers zeroed (src/tonegen.cpp:3607-3612) */
+__device__ __forceinline__ void core_end(CoreAcc &a, TWarp &sm, int n_act, int lane, float (&s)[4],
+                                         float (&v)[4], float (&p)[4])
 {
-    float rs[4], rv[4], rp[4]; /* rotated order: position j holds sample (j - lane/8) & 3 */
     prod_add(a.sum, a.pa);
     prod_add(a.sum, a.pb);
+    __pipeline_wait_prior(0);
+    *reinterpret_cast<ulonglong2 *>(&sm.wstage[0][lane]) = make_ulonglong2(a.sum.s[0], a.sum.s[1]);
+    *reinterpret_cast<ulonglong2 *>(&sm.wstage[1][lane]) = make_ulonglong2(a.sum.v[0], a.sum.v[1]);
+    *reinterpret_cast<ulonglong2 *>(&sm.wstage[2][lane]) = make_ulonglong2(a.sum.p[0], a.sum.p[1]);
+    __syncwarp();
+    const float *fs = reinterpret_cast<const float *>(sm.wstage[0]);
+    const float *fv = reinterpret_cast<const float *>(sm.wstage[1]);
+    const float *fp = reinterpret_cast<const float *>(sm.wstage[2]);
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        rs[2 * h] = lo2(a.sum.s[h]);
-        rs[2 * h + 1] = hi2(a.sum.s[h]);
-        rv[2 * h] = lo2(a.sum.v[h]);
-        rv[2 * h + 1] = hi2(a.sum.v[h]);
-        rp[2 * h] = lo2(a.sum.p[h]);
-        rp[2 * h + 1] = hi2(a.sum.p[h]);
+    for (int k = 0; k < 4; ++k) {
+        s[k] = fs[BLK * k + lane];
+        v[k] = fv[BLK * k + lane];
+        p[k] = fp[BLK * k + lane];
     }
-    const int r = lane >> 3;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { /* sample k sits at position (k + r) & 3 */
-        const int j = (k + r) & 3;
-        s[k] = j == 0 ? rs[0] : j == 1 ? rs[1] : j == 2 ? rs[2] : rs[3];
-        v[k] = j == 0 ? rv[0] : j == 1 ? rv[1] : j == 2 ? rv[2] : rv[3];
-        p[k] = j == 0 ? rp[0] : j == 1 ? rp[1] : j == 2 ? rp[2] : rp[3];
-    }
+    __syncwarp(); /* the stages are requested into again by the next fragment */
     if (n_act == 0) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
@@ -953,9 +961,9 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
 #ifdef TBF_DEBUG_CHECKS
                 ++dbg_fast;
 #endif
-                fast_pass(sm, lane, n_act, my_ins);
+                fast_pass(tg, sm, lane, n_act, my_ins);
                 __syncwarp();
-                core_tile(tg, sm, lane, 0, n_act, acc);
+                core_tile<false>(tg, sm, lane, 0, n_act, acc);
                 __syncwarp();
                 const int n_ins = __reduce_add_sync(FULL, my_ins);
                 if (lane == 0) {
@@ -974,7 +982,7 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
                     const int rec0 = persist ? base : 0;
                     active_list_tile(st, tg, sm, lane, base, cnt, rec0, my_ins);
                     __syncwarp();
-                    core_tile(tg, sm, lane, rec0, cnt, acc);
+                    core_tile<true>(tg, sm, lane, rec0, cnt, acc);
                     __syncwarp();
                 }
                 active_list_finish(st, sm, lane, n_act, my_ins);
@@ -988,7 +996,7 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
                 if (p.flags & 0x100u) /* debugging: always take the full pass */
                     cache_valid = false;
             }
-            core_end(acc, n_act, lane, swl, vib, prc);
+            core_end(acc, sm, n_act, lane, swl, vib, prc);
         }
         __syncwarp();
 
