@@ -391,23 +391,35 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
     WhSet s;
     s.host = *w;
     const size_t N = TBF_WHIRL_DISPLC;
-    CK(cudaMalloc(&s.tables, sizeof(float) * N * 14));
-    const float *src[4] = {w->hn_fwd_displ, w->hn_bwd_displ, w->dr_fwd_displ, w->dr_bwd_displ};
-    for (int i = 0; i < 4; ++i)
-        CK(cudaMemcpy(s.tables + N * i, src[i], sizeof(float) * N, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(s.tables + N * 4, w->bfw, sizeof(float) * N * 5, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(s.tables + N * 9, w->bbw, sizeof(float) * N * 5, cudaMemcpyHostToDevice));
+    /* device layout: 4 displacement tables as pairs (2N floats each), then the two FIR banks
+     * padded to 8 floats per position */
+    {
+        std::vector<float> t(N * 24, 0.0f);
+        const float *src[4] = {w->hn_fwd_displ, w->hn_bwd_displ, w->dr_fwd_displ, w->dr_bwd_displ};
+        for (int i = 0; i < 4; ++i)
+            for (size_t k = 0; k < N; ++k) {
+                t[2 * N * i + 2 * k] = src[i][k];
+                t[2 * N * i + 2 * k + 1] = src[i][(k + 1) & (N - 1)];
+            }
+        const float *fir[2] = {w->bfw, w->bbw};
+        for (int i = 0; i < 2; ++i)
+            for (size_t k = 0; k < N; ++k)
+                for (int c = 0; c < 5; ++c)
+                    t[8 * N + 8 * N * i + 8 * k + c] = fir[i][5 * k + c];
+        CK(cudaMalloc(&s.tables, sizeof(float) * t.size()));
+        CK(cudaMemcpy(s.tables, t.data(), sizeof(float) * t.size(), cudaMemcpyHostToDevice));
+    }
     s.host.hn_fwd_displ = s.host.hn_bwd_displ = s.host.dr_fwd_displ = s.host.dr_bwd_displ = nullptr;
     s.host.bfw = s.host.bbw = nullptr;
 
     DevWhirlTables d;
     memset(&d, 0, sizeof(d));
-    d.hn_fwd_displ = s.tables;
-    d.hn_bwd_displ = s.tables + N;
-    d.dr_fwd_displ = s.tables + 2 * N;
-    d.dr_bwd_displ = s.tables + 3 * N;
-    d.bfw = s.tables + 4 * N;
-    d.bbw = s.tables + 9 * N;
+    d.hn_fwd_displ = reinterpret_cast<const float2 *>(s.tables);
+    d.hn_bwd_displ = reinterpret_cast<const float2 *>(s.tables + 2 * N);
+    d.dr_fwd_displ = reinterpret_cast<const float2 *>(s.tables + 4 * N);
+    d.dr_bwd_displ = reinterpret_cast<const float2 *>(s.tables + 6 * N);
+    d.bfw = s.tables + 8 * N;
+    d.bbw = s.tables + 16 * N;
     d.sample_rate = w->sample_rate;
     d.fw_ang = w->mic_angle * .25;            /* src/whirl.cpp:1379 */
     d.bw_ang = 1. + w->mic_angle * -.25;      /* src/whirl.cpp:1380 */

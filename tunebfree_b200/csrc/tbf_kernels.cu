@@ -1382,6 +1382,20 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
 /* stage W: Leslie reflections, taps, delay lines; warp = instance     */
 /* ================================================================== */
 
+/* One tap as the block loop needs it, in processing order: the three taps of the group's left
+ * line, farthest delay first, then the three of the right line (tap_order, tbf_api.cu).
+ * Filled once per launch so the loop reads parameters with warp-uniform LDS and indexes its
+ * per-tap registers statically. */
+struct WTap {
+    const float2 *dsp; /* displacement table as pairs {d[k], d[k+1]}                    */
+    const float *bw;   /* horn: FIR bank, 8 floats per table position; drum: unused       */
+    double ang_off;    /* horn: microphone angle offset added to the rotor angle         */
+    float spacing;
+    int phase;
+    int stage;         /* reflection stage feeding the tap (tap id >> 1)                  */
+    int q;             /* tap id inside its group, 0..5 (serial fallback order)           */
+};
+
 struct WWarp {
     float hx[3][8 + TBF_FRAGMENT]; /* horn stage inputs with 8 samples of history */
     float dx[3][4 + TBF_FRAGMENT]; /* drum stage inputs, history at index 3       */
@@ -1389,6 +1403,7 @@ struct WWarp {
     float lo[2][BLK];              /* serial fallback: the two line reads of a group */
     uint16_t tn[6][BLK];           /* destination slot of the tap's main part     */
     float zs[4];                   /* FILTER_C states z[0..3], NaN-scrubbed per fragment */
+    WTap tap[12];                  /* horn taps 0..5, drum taps 6..11 in processing order  */
     /* followed by float ring[4][ring_size]: the delay lines HL HR DL DR */
 };
 
@@ -1400,16 +1415,15 @@ __device__ __forceinline__ float filter_c(float x, float z)
 }
 
 /* tap geometry (HN_MOTION / DR_MOTION, src/whirl.cpp:1432-1469) */
-__device__ __forceinline__ void tap_position(double ang_grd, int phase, const float *__restrict__ dsp,
+__device__ __forceinline__ void tap_position(double ang_grd, int phase, const float2 *__restrict__ dsp,
                                              float spacing, uint32_t outpos, float &frac,
                                              uint32_t &slot, uint32_t &kround)
 {
     const float h1 = (float)__dadd_rn(__dmul_rn(ang_grd, (double)TBF_WHIRL_DISPLC), (double)phase);
     const float hd = __fsub_rn(h1, truncf(h1)); /* fmodf(h1, 1.f), exact */
     const uint32_t hl = f2u_x86(floorf(h1)) & DISPLC_MASK;
-    const uint32_t hh = (hl + 1) & DISPLC_MASK;
-    const float intp =
-        __fadd_rn(__fmul_rn(__ldg(dsp + hl), __fsub_rn(1.f, hd)), __fmul_rn(hd, __ldg(dsp + hh)));
+    const float2 d = __ldg(dsp + hl); /* d[hl], d[(hl + 1) & mask] */
+    const float intp = __fadd_rn(__fmul_rn(d.x, __fsub_rn(1.f, hd)), __fmul_rn(hd, d.y));
     kround = f2u_x86(roundf(h1)) & DISPLC_MASK;
     const float t = __fadd_rn(__fadd_rn(spacing, intp), (float)outpos);
     const float r = floorf(t);
@@ -1417,13 +1431,14 @@ __device__ __forceinline__ void tap_position(double ang_grd, int phase, const fl
     slot = f2u_x86(r) & WBUF_MASK;
 }
 
-/* ordered_pass() for one tap held in registers (lane = sample), neighbours by shuffle.
+/* ordered_pass() for one tap held in registers (lane = sample), neighbours by shuffle
+ * (n1, n2: the slots of samples lane-1, lane-2, already fetched for tap_bad()).
  * Requires what tap_bad() checks: slots never decrease and at most two consecutive
  * samples share a slot. */
-__device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const float a, const float b,
-                                                 float *ring, const uint32_t rmask, const int lane)
+__device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_t n1, const uint32_t n2,
+                                                 const float a, const float b, float *ring,
+                                                 const uint32_t rmask, const int lane)
 {
-    const uint32_t n1 = __shfl_up_sync(FULL, n, 1), n2 = __shfl_up_sync(FULL, n, 2);
     const uint32_t nx = __shfl_down_sync(FULL, n, 1);
     const float b1 = __shfl_up_sync(FULL, b, 1), b2 = __shfl_up_sync(FULL, b, 2);
     const float ax = __shfl_down_sync(FULL, a, 1);
@@ -1455,12 +1470,11 @@ __device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const float a
 /* What the parallel delay-line update relies on, checked per block and tap: the
  * destination slots advance monotonically with the sample index, at most two samples
  * share a slot, and all stay inside [reader, reader + window). */
-__device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t window, const int lane,
-                                       const uint32_t outpos_blk)
+__device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t n1, const uint32_t n2,
+                                       const uint32_t window, const int lane, const uint32_t outpos_blk)
 {
     const uint32_t rel = (n - outpos_blk) & WBUF_MASK;
     int bad = (rel < (uint32_t)lane) | (rel + 1 >= window);
-    const uint32_t n1 = __shfl_up_sync(FULL, n, 1), n2 = __shfl_up_sync(FULL, n, 2);
     if (lane >= 1)
         bad |= ((n - n1) & WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
     if (lane >= 2)
@@ -1468,36 +1482,24 @@ __device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t window, 
     return bad;
 }
 
-__device__ __forceinline__ uint32_t sel3(int q, uint32_t v0, uint32_t v1, uint32_t v2)
-{
-    return q == 0 ? v0 : (q == 1 ? v1 : v2);
-}
-__device__ __forceinline__ float sel3(int q, float v0, float v1, float v2)
-{
-    return q == 0 ? v0 : (q == 1 ? v1 : v2);
-}
-
-/* Scatter the six taps of one group (horn: taps 0..5 -> HL, HR; drum: 6..11 -> DL, DR)
- * of one 32-sample block into the group's two delay lines and read the block's 32
- * outputs.  Even taps feed the left line, odd taps the right one. */
-__device__ __forceinline__ void group_scatter_read(const DevWhirlTables *wh, WWarp &sm, float *ring_l,
-                                                   float *ring_r, uint32_t rmask, int line0, int lane,
-                                                   uint32_t outpos_blk, int bad, int &fell_back,
-                                                   const uint32_t (&tn)[6], const float (&ta)[6],
-                                                   const float (&tb)[6], float &out_l, float &out_r)
+/* Scatter the six taps of one group (horn: HL, HR; drum: DL, DR) of one 32-sample block
+ * into the group's two delay lines and read the block's 32 outputs.  tn/ta/tb are in
+ * processing order (WTap): 0..2 feed the left line, 3..5 the right one, farthest delay first. */
+__device__ __forceinline__ void group_scatter_read(const WTap *tap, WWarp &sm, float *ring_l,
+                                                   float *ring_r, uint32_t rmask, int lane,
+                                                   uint32_t outpos_blk, int bad, int gather_ok,
+                                                   int &fell_back, const uint32_t (&tn)[6],
+                                                   const uint32_t (&tn1)[6], const uint32_t (&tn2)[6],
+                                                   const float (&ta)[6], const float (&tb)[6],
+                                                   float &out_l, float &out_r)
 {
     bad = __any_sync(FULL, bad);
     const uint32_t op = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
     if (!bad) {
-        const int tap0 = line0 * 3; /* first tap id of the group: 0 (horn) or 6 (drum) */
 #pragma unroll
-        for (int j = 0; j < 3; ++j) { /* the three taps of a line: farthest delay first */
-            const int ql = (wh->tap_order[line0][j] - tap0) >> 1;
-            const int qr = (wh->tap_order[line0 + 1][j] - tap0) >> 1;
-            ordered_pass_reg(sel3(ql, tn[0], tn[2], tn[4]), sel3(ql, ta[0], ta[2], ta[4]),
-                             sel3(ql, tb[0], tb[2], tb[4]), ring_l, rmask, lane);
-            ordered_pass_reg(sel3(qr, tn[1], tn[3], tn[5]), sel3(qr, ta[1], ta[3], ta[5]),
-                             sel3(qr, tb[1], tb[3], tb[5]), ring_r, rmask, lane);
+        for (int j = 0; j < 3; ++j) {
+            ordered_pass_reg(tn[j], tn1[j], tn2[j], ta[j], tb[j], ring_l, rmask, lane);
+            ordered_pass_reg(tn[3 + j], tn1[3 + j], tn2[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, lane);
             __syncwarp();
         }
         out_l = ring_l[op & rmask];
@@ -1507,12 +1509,13 @@ __device__ __forceinline__ void group_scatter_read(const DevWhirlTables *wh, WWa
     } else {
         /* the reference's loop as written, one lane per delay line: geometries / rotor
          * speeds the parallel passes do not cover */
-        fell_back |= wh->gather_ok ? 1 : 0;
+        fell_back |= gather_ok;
 #pragma unroll
-        for (int q = 0; q < 6; ++q) {
-            sm.tn[q][lane] = (uint16_t)tn[q];
-            sm.ta[q][lane] = ta[q];
-            sm.tb[q][lane] = tb[q];
+        for (int j = 0; j < 6; ++j) {
+            const int q = tap[j].q;
+            sm.tn[q][lane] = (uint16_t)tn[j];
+            sm.ta[q][lane] = ta[j];
+            sm.tb[q][lane] = tb[j];
         }
         __syncwarp();
         if (lane < 2) {
@@ -1568,10 +1571,35 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
     }
     if (lane < 4)
         sm.zs[lane] = ws.z[lane];
+    if (lane < 12) {
+        const int g = lane / 6, jj = lane % 6; /* group, processing index */
+        const int q = wh->tap_order[2 * g + jj / 3][jj % 3] - 6 * g;
+        /* taps 0,3,4 read the forward displacement table with the backward FIR bank,
+         * taps 1,2,5 the other way round */
+        const bool fwd = (q == 0 || q == 3 || q == 4);
+        WTap t;
+        if (g == 0) {
+            t.dsp = fwd ? wh->hn_fwd_displ : wh->hn_bwd_displ;
+            t.bw = fwd ? wh->bbw : wh->bfw;
+            t.ang_off = (q & 1) ? wh->bw_ang : wh->fw_ang;
+            t.spacing = wh->horn_spacing[q];
+            t.phase = wh->horn_phase[q];
+        } else {
+            t.dsp = fwd ? wh->dr_fwd_displ : wh->dr_bwd_displ;
+            t.bw = nullptr;
+            t.ang_off = 0.0;
+            t.spacing = wh->drum_spacing[q];
+            t.phase = wh->drum_phase[q];
+        }
+        t.stage = q >> 1;
+        t.q = q;
+        sm.tap[lane] = t;
+    }
     const bool gather_ok = wh->gather_ok != 0;
     const uint32_t window = (uint32_t)wh->window;
     int fell_back = 0;
     const size_t row = (size_t)slot * p.pitch;
+    double hang_next = p.hang[row + lane], dang_next = p.dang[row + lane];
     __syncwarp();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
@@ -1610,54 +1638,61 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
             const int i = BLK * k + lane;
             const uint32_t outpos_blk = (outpos0 + (uint32_t)(BLK * k)) & WBUF_MASK;
             const uint32_t outpos = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
-            const double hang = p.hang[col + i], dang = p.dang[col + i];
+            const double hang = hang_next, dang = dang_next;
+            { /* the next block's rotor angles, one block ahead of their use */
+                const size_t nx = col + i + BLK;
+                if (k < 3 || f + 1 < p.n_fragments) {
+                    hang_next = p.hang[nx];
+                    dang_next = p.dang[nx];
+                }
+            }
             /* -- horn taps: geometry + 5-tap FIR (src/whirl.cpp:1432-1453, :1540-1563) -- */
-            uint32_t tn[6];
+            uint32_t tn[6], tn1[6], tn2[6];
             float ta[6], tb[6];
             int bad = gather_ok ? 0 : 1;
 #pragma unroll
-            for (int q = 0; q < 6; ++q) {
-                /* taps 0,3,4 read the forward displacement table with the backward FIR
-                 * bank, taps 1,2,5 the other way round */
-                const bool fwd = (q == 0 || q == 3 || q == 4);
-                const float *dsp = fwd ? wh->hn_fwd_displ : wh->hn_bwd_displ;
-                const float *bw = fwd ? wh->bbw : wh->bfw;
-                const double ang = __dadd_rn(hang, (q & 1) ? wh->bw_ang : wh->fw_ang);
+            for (int j = 0; j < 6; ++j) {
+                const WTap &t = sm.tap[j];
                 float frac;
                 uint32_t kr;
-                tap_position(ang, wh->horn_phase[q], dsp, wh->horn_spacing[q], outpos, frac, tn[q], kr);
-                const float *hx = &sm.hx[q >> 1][8 + i];
-                const float *b = bw + 5 * kr;
-                float xa = __fmul_rn(__ldg(b + 0), hx[0]);
-                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 1), hx[-1]));
-                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 2), hx[-2]));
-                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 3), hx[-3]));
-                xa = __fadd_rn(xa, __fmul_rn(__ldg(b + 4), hx[-4]));
+                tap_position(__dadd_rn(hang, t.ang_off), t.phase, t.dsp, t.spacing, outpos, frac, tn[j], kr);
+                const float *hx = &sm.hx[t.stage][8 + i];
+                const float *b = t.bw + 8 * kr;
+                const float4 b03 = __ldg(reinterpret_cast<const float4 *>(b));
+                const float b4 = __ldg(b + 4);
+                float xa = __fmul_rn(b03.x, hx[0]);
+                xa = __fadd_rn(xa, __fmul_rn(b03.y, hx[-1]));
+                xa = __fadd_rn(xa, __fmul_rn(b03.z, hx[-2]));
+                xa = __fadd_rn(xa, __fmul_rn(b03.w, hx[-3]));
+                xa = __fadd_rn(xa, __fmul_rn(b4, hx[-4]));
                 const float qq = __fmul_rn(xa, frac);
-                ta[q] = __fsub_rn(xa, qq);
-                tb[q] = qq;
-                bad |= tap_bad(tn[q], window, lane, outpos_blk);
+                ta[j] = __fsub_rn(xa, qq);
+                tb[j] = qq;
+                tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
+                tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
+                bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
             }
             float hl, hr, dl, dr;
-            group_scatter_read(wh, sm, ring, ring + ring_size, rmask, 0, lane, outpos_blk, bad,
-                               fell_back, tn, ta, tb, hl, hr);
+            group_scatter_read(&sm.tap[0], sm, ring, ring + ring_size, rmask, lane, outpos_blk, bad,
+                               gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, hl, hr);
             /* -- drum taps (src/whirl.cpp:1455-1469, :1566-1588) -- */
             bad = gather_ok ? 0 : 1;
 #pragma unroll
-            for (int q = 0; q < 6; ++q) {
-                const bool fwd = (q == 0 || q == 3 || q == 4);
-                const float *dsp = fwd ? wh->dr_fwd_displ : wh->dr_bwd_displ;
+            for (int j = 0; j < 6; ++j) {
+                const WTap &t = sm.tap[6 + j];
                 float frac;
                 uint32_t kr;
-                tap_position(dang, wh->drum_phase[q], dsp, wh->drum_spacing[q], outpos, frac, tn[q], kr);
-                const float x = sm.dx[q >> 1][4 + i];
+                tap_position(dang, t.phase, t.dsp, t.spacing, outpos, frac, tn[j], kr);
+                const float x = sm.dx[t.stage][4 + i];
                 const float qq = __fmul_rn(x, frac);
-                ta[q] = __fsub_rn(x, qq);
-                tb[q] = qq;
-                bad |= tap_bad(tn[q], window, lane, outpos_blk);
+                ta[j] = __fsub_rn(x, qq);
+                tb[j] = qq;
+                tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
+                tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
+                bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
             }
-            group_scatter_read(wh, sm, ring + 2 * ring_size, ring + 3 * ring_size, rmask, 2, lane,
-                               outpos_blk, bad, fell_back, tn, ta, tb, dl, dr);
+            group_scatter_read(&sm.tap[6], sm, ring + 2 * ring_size, ring + 3 * ring_size, rmask, lane,
+                               outpos_blk, bad, gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, dl, dr);
             p.line[0][col + i] = hl;
             p.line[1][col + i] = hr;
             p.line[2][col + i] = dl;
