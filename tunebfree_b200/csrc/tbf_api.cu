@@ -83,7 +83,8 @@ struct tbf_ctx {
     cudaEvent_t fork = nullptr;
     size_t scratch_budget = (size_t)4 << 30; /* bytes of HBM the stage streams may take */
     uint32_t max_stage_chunk = 32;           /* fragments per stage-kernel launch       */
-    int n_groups_max = TBF_MAX_GROUPS;
+    int n_groups_max = 1; /* measured best from 512 to 8192 organs once stage T and W of
+                             consecutive chunks overlap on the stage streams; TBF_GROUPS raises it */
     bool in_flight = false;
     int launches = 0;
     /* stage profiling: every stage kernel serialised on the main stream between two events */
