@@ -85,37 +85,39 @@ __device__ __forceinline__ unsigned f2u_x86(float f) { return (unsigned)(long lo
 /* run skips it, or the block ends) is completed by the last sample of  */
 /* the run before.  Distinct lanes own distinct slots: no atomics.      */
 /* ------------------------------------------------------------------ */
-__device__ __forceinline__ void ordered_pass(const uint16_t *n, const float *a, const float *b,
-                                             float *ring, uint32_t rmask, uint32_t smask, int i)
+__device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_t n1, const uint32_t n2,
+                                                 const float a, const float b, float *ring,
+                                                 const uint32_t rmask, const uint32_t smask,
+                                                 const int lane)
 {
-    const uint32_t ni = n[i];
-    const uint32_t prev = i ? (uint32_t)n[i - 1] : 0xFFFFFFFFu;
-    const uint32_t next = (i < BLK - 1) ? (uint32_t)n[i + 1] : 0xFFFFFFFFu;
-    if (ni != prev) { /* first sample of the run hitting slot ni */
-        float v = ring[ni & rmask];
-        const uint32_t sm1 = (ni - 1) & smask;
-        int j0 = i;
-        while (j0 > 0 && n[j0 - 1] == sm1)
-            --j0;
-        for (int j = j0; j < i; ++j)
-            v = __fadd_rn(v, b[j]);
-        for (int m = i; m < BLK && n[m] == ni; ++m)
-            v = __fadd_rn(v, a[m]);
-        ring[ni & rmask] = v;
+    const uint32_t nx = __shfl_down_sync(FULL, n, 1);
+    const float b1 = __shfl_up_sync(FULL, b, 1), b2 = __shfl_up_sync(FULL, b, 2);
+    const float ax = __shfl_down_sync(FULL, a, 1);
+    const bool has1 = lane >= 1, has2 = lane >= 2, hasx = lane < BLK - 1;
+    if (!has1 || n1 != n) { /* first sample of the run hitting slot n */
+        float v = ring[n & rmask];
+        const uint32_t sm1 = (n - 1) & smask;
+        if (has2 && n2 == sm1)
+            v = __fadd_rn(v, b2);
+        if (has1 && n1 == sm1)
+            v = __fadd_rn(v, b1);
+        v = __fadd_rn(v, a);
+        if (hasx && nx == n)
+            v = __fadd_rn(v, ax);
+        ring[n & rmask] = v;
     }
-    if (ni != next) { /* last sample of its run */
-        const uint32_t sp1 = (ni + 1) & smask;
-        if (next != sp1) { /* nobody hits ni+1 as a main slot in this block */
+    if (!hasx || nx != n) { /* last sample of its run */
+        const uint32_t sp1 = (n + 1) & smask;
+        if (!hasx || nx != sp1) { /* nobody hits n+1 as a main slot in this block */
             float v = ring[sp1 & rmask];
-            int j0 = i;
-            while (j0 > 0 && n[j0 - 1] == ni)
-                --j0;
-            for (int j = j0; j <= i; ++j)
-                v = __fadd_rn(v, b[j]);
+            if (has1 && n1 == n)
+                v = __fadd_rn(v, b1);
+            v = __fadd_rn(v, b);
             ring[sp1 & rmask] = v;
         }
     }
 }
+
 
 /* ================================================================== */
 /* stage T: tone generator + scanner                                   */
@@ -124,9 +126,9 @@ __device__ __forceinline__ void ordered_pass(const uint16_t *n, const float *a, 
 /* One entry of the per-fragment "core program": the reference emits 1-2 CoreIns per
  * active wheel (src/tonegen.h:114-129); with a modular index the wrap split collapses
  * and one record per wheel suffices. */
-#define REC_TILE 64    /* active-list entries turned into records and summed at a time */
+#define REC_TILE 32    /* active-list entries turned into records and summed at a time */
 #define REC_CAP 128   /* longest active list whose records persist across fragments   */
-#define WAVE_STAGES 8  /* wheels whose wave samples are in flight (cp.async) per warp   */
+#define WAVE_STAGES 6  /* wheels whose wave samples are in flight (cp.async) per warp   */
 struct TWarp {
     TgScalars sc;
     /* core-program records.  Lists of up to REC_CAP wheels keep their records here from one
@@ -136,13 +138,13 @@ struct TWarp {
                               position, env (-1 plain, 0..7 attack, 8..15 release) */
     float4 recB[REC_CAP];  /* gs gs gv gv: gains duplicated for the packed f32x2 multiply */
     float2 recC[REC_CAP];  /* gp gp */
-    float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas of the current tile, env >= 0 only */
+    union {                /* the removal list is built after the last tile has been summed */
+        float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas of the current tile, env >= 0 only */
+        uint16_t removed_wheel[TBF_NOF_WHEELS];
+    };
     uint2 recP[REC_CAP];   /* wave length | wheel << 16, wave4_offset of the wheel */
     float4 wstage[WAVE_STAGES][32]; /* [stage][lane]: samples 4*lane .. 4*lane+3 of a wheel */
     float vring[TBF_VRING];
-    float va[BLK], vb[BLK], vy[BLK];
-    uint16_t vn[BLK];
-    uint16_t removed_wheel[TBF_NOF_WHEELS + 1];
     uint8_t removed[TBF_NOF_WHEELS + 3];
     int recompute_routing, draw_bar_change, vib_on, perc_on;
     /* raised by any lane during the active-list pass of a fragment.  Shared-memory flags read
@@ -711,12 +713,11 @@ __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm,
             wave_request(sm, rec0 + j + 1, j + 1, lane);
         __pipeline_commit();
     }
-    int i = 0;
+    int i = 0, s = 0; /* s = i % WAVE_STAGES: the stage pair of records i, i+1 */
     if (!ENV) {
 #pragma unroll 1
         for (; i + WAVE_STAGES + 1 < cnt; i += 2) {
             __pipeline_wait_prior(WAVE_STAGES / 2 - 1); /* this lane's records i, i+1 landed */
-            const int s = i & (WAVE_STAGES - 1);
             const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
             const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
             wave_request(sm, rec0 + i + WAVE_STAGES, s, lane);
@@ -726,12 +727,12 @@ __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm,
             prod_add(a.sum, a.pb);
             wheel_products<false>(tg, sm, rec0 + i, i, lane, xa, a.pa);
             wheel_products<false>(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
+            s = (s == WAVE_STAGES - 2) ? 0 : s + 2;
         }
     }
 #pragma unroll 1
     for (; i < cnt; i += 2) {
         __pipeline_wait_prior(WAVE_STAGES / 2 - 1);
-        const int s = i & (WAVE_STAGES - 1);
         const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
         const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
         if (i + WAVE_STAGES < cnt)
@@ -748,6 +749,7 @@ __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm,
             wheel_products<ENV>(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
         else
             prod_none(a.pb);
+        s = (s == WAVE_STAGES - 2) ? 0 : s + 2;
     }
 }
 
@@ -798,39 +800,44 @@ __device__ __forceinline__ float vibrato_block(const DevTonegenTables *tg, TWarp
     const uint32_t h = j >> 16;
     const float f = __fmul_rn(fnorm, (float)(j & 0xFFFFu));
     const float g = __fmul_rn(f, x);
-    sm.va[lane] = __fsub_rn(x, g);
-    sm.vb[lane] = g;
-    sm.vn[lane] = (uint16_t)h;
+    const float va = __fsub_rn(x, g), vb = g;
     /* slots ahead of the block's first read; the parallel pass needs slots that never go
-     * backwards and stay ahead of (or at) their own sample's read position */
+     * backwards, at most two samples per slot, and slots that stay ahead of (or at) their
+     * own sample's read position */
     const uint32_t rel = (h - op + (uint32_t)lane) & VBUF_MASK;
     int bad = (rel < (uint32_t)lane) || (rel + 1 >= (uint32_t)TBF_VRING);
-    const uint32_t hprev = __shfl_up_sync(FULL, h, 1);
-    if (lane > 0)
-        bad |= ((h - hprev) & VBUF_MASK) >= (TBF_VIB_BUF / 2);
+    const uint32_t h1 = __shfl_up_sync(FULL, h, 1), h2 = __shfl_up_sync(FULL, h, 2);
+    if (lane >= 1)
+        bad |= ((h - h1) & VBUF_MASK) >= (TBF_VIB_BUF / 2);
+    if (lane >= 2)
+        bad |= (h2 == h);
     bad = __any_sync(FULL, bad);
-    __syncwarp();
     float y;
     if (!bad) {
-        ordered_pass(sm.vn, sm.va, sm.vb, sm.vring, VRING_MASK, VBUF_MASK, lane);
+        ordered_pass_reg(h, h1, h2, va, vb, sm.vring, VRING_MASK, VBUF_MASK, lane);
         __syncwarp();
         y = sm.vring[op & VRING_MASK];
         sm.vring[op & VRING_MASK] = 0.0f;
     } else {
-        /* the reference's loop as written, one lane (offset tables with backward steps) */
-        if (lane == 0) {
-            for (int i = 0; i < BLK; ++i) {
-                const uint32_t hh = sm.vn[i];
+        /* the reference's loop as written, one lane (offset tables with backward steps);
+         * the other lanes hand their sample over by shuffle */
+        y = 0.0f;
+        for (int i = 0; i < BLK; ++i) {
+            const uint32_t hh = __shfl_sync(FULL, h, i);
+            const float ai = __shfl_sync(FULL, va, i), bi = __shfl_sync(FULL, vb, i);
+            float yi = 0.0f;
+            if (lane == 0) {
                 const uint32_t kk = (hh + 1) & VBUF_MASK;
                 const uint32_t oo = (sc.vibOutPos + (uint32_t)(BLK * k + i)) & VBUF_MASK;
-                sm.vring[hh & VRING_MASK] = __fadd_rn(sm.vring[hh & VRING_MASK], sm.va[i]);
-                sm.vring[kk & VRING_MASK] = __fadd_rn(sm.vring[kk & VRING_MASK], sm.vb[i]);
-                sm.vy[i] = sm.vring[oo & VRING_MASK];
+                sm.vring[hh & VRING_MASK] = __fadd_rn(sm.vring[hh & VRING_MASK], ai);
+                sm.vring[kk & VRING_MASK] = __fadd_rn(sm.vring[kk & VRING_MASK], bi);
+                yi = sm.vring[oo & VRING_MASK];
                 sm.vring[oo & VRING_MASK] = 0.0f;
             }
+            yi = __shfl_sync(FULL, yi, 0);
+            if (lane == i)
+                y = yi;
         }
-        __syncwarp();
-        y = sm.vy[lane];
     }
     __syncwarp();
     return y;
@@ -1431,42 +1438,6 @@ __device__ __forceinline__ void tap_position(double ang_grd, int phase, const fl
     slot = f2u_x86(r) & WBUF_MASK;
 }
 
-/* ordered_pass() for one tap held in registers (lane = sample), neighbours by shuffle
- * (n1, n2: the slots of samples lane-1, lane-2, already fetched for tap_bad()).
- * Requires what tap_bad() checks: slots never decrease and at most two consecutive
- * samples share a slot. */
-__device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_t n1, const uint32_t n2,
-                                                 const float a, const float b, float *ring,
-                                                 const uint32_t rmask, const int lane)
-{
-    const uint32_t nx = __shfl_down_sync(FULL, n, 1);
-    const float b1 = __shfl_up_sync(FULL, b, 1), b2 = __shfl_up_sync(FULL, b, 2);
-    const float ax = __shfl_down_sync(FULL, a, 1);
-    const bool has1 = lane >= 1, has2 = lane >= 2, hasx = lane < BLK - 1;
-    if (!has1 || n1 != n) { /* first sample of the run hitting slot n */
-        float v = ring[n & rmask];
-        const uint32_t sm1 = (n - 1) & WBUF_MASK;
-        if (has2 && n2 == sm1)
-            v = __fadd_rn(v, b2);
-        if (has1 && n1 == sm1)
-            v = __fadd_rn(v, b1);
-        v = __fadd_rn(v, a);
-        if (hasx && nx == n)
-            v = __fadd_rn(v, ax);
-        ring[n & rmask] = v;
-    }
-    if (!hasx || nx != n) { /* last sample of its run */
-        const uint32_t sp1 = (n + 1) & WBUF_MASK;
-        if (!hasx || nx != sp1) { /* nobody hits n+1 as a main slot in this block */
-            float v = ring[sp1 & rmask];
-            if (has1 && n1 == n)
-                v = __fadd_rn(v, b1);
-            v = __fadd_rn(v, b);
-            ring[sp1 & rmask] = v;
-        }
-    }
-}
-
 /* What the parallel delay-line update relies on, checked per block and tap: the
  * destination slots advance monotonically with the sample index, at most two samples
  * share a slot, and all stay inside [reader, reader + window). */
@@ -1498,8 +1469,9 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, WWarp &sm, f
     if (!bad) {
 #pragma unroll
         for (int j = 0; j < 3; ++j) {
-            ordered_pass_reg(tn[j], tn1[j], tn2[j], ta[j], tb[j], ring_l, rmask, lane);
-            ordered_pass_reg(tn[3 + j], tn1[3 + j], tn2[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, lane);
+            ordered_pass_reg(tn[j], tn1[j], tn2[j], ta[j], tb[j], ring_l, rmask, WBUF_MASK, lane);
+            ordered_pass_reg(tn[3 + j], tn1[3 + j], tn2[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, WBUF_MASK,
+                             lane);
             __syncwarp();
         }
         out_l = ring_l[op & rmask];
