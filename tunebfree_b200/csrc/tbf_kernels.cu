@@ -1405,10 +1405,8 @@ struct WTap {
 
 struct WWarp {
     float hx[3][8 + TBF_FRAGMENT]; /* horn stage inputs with 8 samples of history */
-    float dx[3][4 + TBF_FRAGMENT]; /* drum stage inputs, history at index 3       */
-    float ta[6][BLK], tb[6][BLK];  /* the two contributions of every tap of a group */
-    float lo[2][BLK];              /* serial fallback: the two line reads of a group */
-    uint16_t tn[6][BLK];           /* destination slot of the tap's main part     */
+    float dx[4 + TBF_FRAGMENT];    /* drum path input, history at index 3 (the two reflection
+                                      stages of a sample are formed in registers)            */
     float zs[4];                   /* FILTER_C states z[0..3], NaN-scrubbed per fragment */
     WTap tap[12];                  /* horn taps 0..5, drum taps 6..11 in processing order  */
     /* followed by float ring[4][ring_size]: the delay lines HL HR DL DR */
@@ -1456,7 +1454,7 @@ __device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t n1, cons
 /* Scatter the six taps of one group (horn: HL, HR; drum: DL, DR) of one 32-sample block
  * into the group's two delay lines and read the block's 32 outputs.  tn/ta/tb are in
  * processing order (WTap): 0..2 feed the left line, 3..5 the right one, farthest delay first. */
-__device__ __forceinline__ void group_scatter_read(const WTap *tap, WWarp &sm, float *ring_l,
+__device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_l,
                                                    float *ring_r, uint32_t rmask, int lane,
                                                    uint32_t outpos_blk, int bad, int gather_ok,
                                                    int &fell_back, const uint32_t (&tn)[6],
@@ -1479,36 +1477,53 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, WWarp &sm, f
         out_r = ring_r[op & rmask];
         ring_r[op & rmask] = 0.0f;
     } else {
-        /* the reference's loop as written, one lane per delay line: geometries / rotor
-         * speeds the parallel passes do not cover */
+        /* the reference's loop as written, one lane per delay line (lane 0 left, lane 1
+         * right): geometries / rotor speeds the parallel passes do not cover.  The lanes
+         * hand sample i of every tap over by shuffle; a line applies its three taps in
+         * tap-id order (src/whirl.cpp:1540-1588). */
         fell_back |= gather_ok;
+        const int j0 = (lane & 1) * 3; /* my line's first processing index */
+        int ord[3];                    /* processing index (0..2 in my line) of tap id lane + 2s */
 #pragma unroll
-        for (int j = 0; j < 6; ++j) {
-            const int q = tap[j].q;
-            sm.tn[q][lane] = (uint16_t)tn[j];
-            sm.ta[q][lane] = ta[j];
-            sm.tb[q][lane] = tb[j];
+        for (int s = 0; s < 3; ++s) {
+            const int q = (lane & 1) + 2 * s;
+            ord[s] = tap[j0].q == q ? 0 : (tap[j0 + 1].q == q ? 1 : 2);
         }
-        __syncwarp();
-        if (lane < 2) {
-            float *buf = lane ? ring_r : ring_l;
-            for (int i = 0; i < BLK; ++i) {
+        out_l = out_r = 0.0f;
+        for (int i = 0; i < BLK; ++i) {
+            uint32_t n3[3];
+            float a3[3], b3[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { /* my line's taps in processing order */
+                const uint32_t nl = __shfl_sync(FULL, tn[c], i), nr = __shfl_sync(FULL, tn[3 + c], i);
+                const float al = __shfl_sync(FULL, ta[c], i), ar = __shfl_sync(FULL, ta[3 + c], i);
+                const float bl = __shfl_sync(FULL, tb[c], i), br = __shfl_sync(FULL, tb[3 + c], i);
+                n3[c] = (lane & 1) ? nr : nl;
+                a3[c] = (lane & 1) ? ar : al;
+                b3[c] = (lane & 1) ? br : bl;
+            }
+            float o_val = 0.0f;
+            if (lane < 2) {
+                float *buf = lane ? ring_r : ring_l;
 #pragma unroll
                 for (int s = 0; s < 3; ++s) {
-                    const int q = lane + 2 * s;
-                    const uint32_t n = sm.tn[q][i];
-                    buf[n & rmask] = __fadd_rn(buf[n & rmask], sm.ta[q][i]);
+                    const uint32_t n = ord[s] == 0 ? n3[0] : (ord[s] == 1 ? n3[1] : n3[2]);
+                    const float a = ord[s] == 0 ? a3[0] : (ord[s] == 1 ? a3[1] : a3[2]);
+                    const float b = ord[s] == 0 ? b3[0] : (ord[s] == 1 ? b3[1] : b3[2]);
+                    buf[n & rmask] = __fadd_rn(buf[n & rmask], a);
                     const uint32_t n1 = (n + 1) & WBUF_MASK;
-                    buf[n1 & rmask] = __fadd_rn(buf[n1 & rmask], sm.tb[q][i]);
+                    buf[n1 & rmask] = __fadd_rn(buf[n1 & rmask], b);
                 }
                 const uint32_t o = (outpos_blk + (uint32_t)i) & WBUF_MASK;
-                sm.lo[lane][i] = buf[o & rmask];
+                o_val = buf[o & rmask];
                 buf[o & rmask] = 0.0f;
             }
+            const float vl = __shfl_sync(FULL, o_val, 0), vr = __shfl_sync(FULL, o_val, 1);
+            if (lane == i) {
+                out_l = vl;
+                out_r = vr;
+            }
         }
-        __syncwarp();
-        out_l = sm.lo[0][lane];
-        out_r = sm.lo[1][lane];
     }
     __syncwarp();
 }
@@ -1580,12 +1595,10 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
         for (int k = 0; k < 4; ++k) {
             const int i = BLK * k + lane;
             sm.hx[0][8 + i] = p.hx0[col + i];
-            sm.dx[0][4 + i] = p.dx0[col + i];
+            sm.dx[4 + i] = p.dx0[col + i];
         }
-        if (lane == 0) {
-            sm.dx[0][3] = sm.zs[2];
-            sm.dx[1][3] = sm.zs[3];
-        }
+        if (lane == 0)
+            sm.dx[3] = sm.zs[2];
         __syncwarp();
         /* -- the two reflection filters of each path (2-tap FIRs in double); stage 1 of
          *    sample i-1 is recomputed locally instead of exchanged -- */
@@ -1597,11 +1610,6 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
             const float h1m = i ? filter_c(h0m, i > 1 ? sm.hx[0][6 + i] : sm.zs[0]) : sm.zs[1];
             sm.hx[1][8 + i] = h1;
             sm.hx[2][8 + i] = filter_c(h1, h1m);
-            const float d0 = sm.dx[0][4 + i], d0m = sm.dx[0][3 + i];
-            const float d1 = filter_c(d0, d0m);
-            const float d1m = i ? filter_c(d0m, i > 1 ? sm.dx[0][2 + i] : sm.zs[2]) : sm.zs[3];
-            sm.dx[1][4 + i] = d1;
-            sm.dx[2][4 + i] = filter_c(d1, d1m);
         }
         __syncwarp();
 
@@ -1645,17 +1653,23 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
                 bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
             }
             float hl, hr, dl, dr;
-            group_scatter_read(&sm.tap[0], sm, ring, ring + ring_size, rmask, lane, outpos_blk, bad,
+            group_scatter_read(&sm.tap[0], ring, ring + ring_size, rmask, lane, outpos_blk, bad,
                                gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, hl, hr);
             /* -- drum taps (src/whirl.cpp:1455-1469, :1566-1588) -- */
             bad = gather_ok ? 0 : 1;
+            /* the drum path's reflection stages of this sample; stage 1 of sample i-1 is
+             * recomputed locally instead of exchanged */
+            const float d0 = sm.dx[4 + i], d0m = sm.dx[3 + i];
+            const float d1 = filter_c(d0, d0m);
+            const float d1m = i ? filter_c(d0m, i > 1 ? sm.dx[2 + i] : sm.zs[2]) : sm.zs[3];
+            const float d2 = filter_c(d1, d1m);
 #pragma unroll
             for (int j = 0; j < 6; ++j) {
                 const WTap &t = sm.tap[6 + j];
                 float frac;
                 uint32_t kr;
                 tap_position(dang, t.phase, t.dsp, t.spacing, outpos, frac, tn[j], kr);
-                const float x = sm.dx[t.stage][4 + i];
+                const float x = t.stage == 0 ? d0 : (t.stage == 1 ? d1 : d2);
                 const float qq = __fmul_rn(x, frac);
                 ta[j] = __fsub_rn(x, qq);
                 tb[j] = qq;
@@ -1663,7 +1677,7 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
                 tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
                 bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
             }
-            group_scatter_read(&sm.tap[6], sm, ring + 2 * ring_size, ring + 3 * ring_size, rmask, lane,
+            group_scatter_read(&sm.tap[6], ring + 2 * ring_size, ring + 3 * ring_size, rmask, lane,
                                outpos_blk, bad, gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, dl, dr);
             p.line[0][col + i] = hl;
             p.line[1][col + i] = hr;
@@ -1678,7 +1692,7 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
         float zc = 0.f;
         if (lane < 4)
             zc = (lane == 0) ? sm.hx[0][8 + 127] : (lane == 1) ? sm.hx[1][8 + 127]
-                 : (lane == 2) ? sm.dx[0][4 + 127] : sm.dx[1][4 + 127];
+                 : (lane == 2) ? sm.dx[4 + 127] : filter_c(sm.dx[4 + 127], sm.dx[4 + 126]);
         __syncwarp();
         if (lane < 24)
             sm.hx[lane >> 3][lane & 7] = keep;
