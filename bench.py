@@ -376,8 +376,18 @@ def run_gpu_arm(a):
         # algorithmic work of the whole path per organ-second
         w32 = 48000 * (6 * n_act + 17 + 253 * whirl)
         bsm = 48000 * (4 * n_act + 70 + 380 * whirl)
+        # DRAM bytes of one launch of that kernel: dram__bytes_read.sum + dram__bytes_write.sum of
+        # the committed `ncu --set full` capture, scaled by organ-fragments per launch
+        traffic = None
+        try:
+            cap = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[names[dom]]
+            if cap["config"] == a.config:
+                frag_now = organ_seconds_step * 375.0 / max(1, dom_n)
+                traffic = cap["dram_bytes"] * frag_now / (cap["instances"] * cap["fragments"])
+        except (OSError, KeyError, ValueError):
+            pass
         roofline = {"bound": "hbm", "achieved": ach_hbm, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": ach_hbm / hbm_peak, "traffic": None,
+                    "frac": ach_hbm / hbm_peak, "traffic": traffic,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
                     "note": "bytes = the dominant stage kernel's algorithmic reads + writes; the path is "
                             "bound by instruction issue, not HBM: see fp32_issue / smem_bw (whole path, "
