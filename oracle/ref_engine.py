@@ -43,6 +43,9 @@ def lib():
         L.ref_render.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.POINTER(cabi.Event),
                                  C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.ref_active_wheels.argtypes = [C.c_void_p]
+        L.ref_render_midi.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.POINTER(C.c_uint),
+                                      C.c_ulonglong, C.c_void_p, C.c_void_p]
+        L.ref_midi_key.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.ref_dump_tonegen_tables.argtypes = [C.c_void_p, C.POINTER(cabi.TonegenTables)]
         L.ref_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
         L.ref_dump_whirl_tables.argtypes = [C.c_void_p, C.POINTER(cabi.WhirlTables)]
@@ -113,6 +116,25 @@ class RefInstance:
         lib().ref_render(self._h, n_fragments, flags, arr, n,
                          outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
         return outl, outr
+
+    def render_midi(self, n_fragments, flags=0, messages=()):
+        """Render with raw MIDI: messages = [(fragment, bytes)] sorted by fragment, each fed
+        to the reference's parse_raw_midi_data() before its fragment.  -> (L, R)."""
+        outl = np.zeros(n_fragments * 128, dtype=np.float32)
+        outr = np.zeros(n_fragments * 128, dtype=np.float32)
+        flat = []
+        for fragment, raw in messages:
+            raw = bytes(raw)
+            flat += [fragment, len(raw)] + list(raw[:3]) + [0] * (3 - min(3, len(raw)))
+        arr = (C.c_uint * max(1, len(flat)))(*flat)
+        lib().ref_render_midi(self._h, n_fragments, flags, arr, len(flat) // 5,
+                              outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
+        return outl, outr
+
+    def midi_key(self, channel, note):
+        """Engine key the reference maps (channel, note) to, -1 if none (observed through
+        activeKeys[], the key tables being private to midi.cpp)."""
+        return lib().ref_midi_key(self._h, channel, note)
 
     def active_wheels(self):
         return lib().ref_active_wheels(self._h)

@@ -196,6 +196,55 @@ int ref_render(void *h, unsigned n_fragments, unsigned flags, const tbf_event *e
     return 0;
 }
 
+/* Render with RAW MIDI input, the way the hosts do it: every message goes through the
+ * reference's own parse_raw_midi_data() (src/midi.cpp:1261) right before the fragment it is
+ * stamped with (b_synth/lv2.cpp:1130-1136).  msgs = n_msgs x {fragment, size, b0, b1, b2} as
+ * uint32, sorted by fragment.  Oracle for the MIDI -> event compiler (include/tbf_midi.h). */
+int ref_render_midi(void *h, unsigned n_fragments, unsigned flags, const unsigned *msgs,
+                    unsigned long long n_msgs, float *outL, float *outR)
+{
+    ref_inst *r = (ref_inst *)h;
+    unsigned long long e = 0;
+    for (unsigned f = 0; f < n_fragments; ++f) {
+        while (e < n_msgs && msgs[5 * e] == f) {
+            uint8_t b[3] = {(uint8_t)msgs[5 * e + 2], (uint8_t)msgs[5 * e + 3], (uint8_t)msgs[5 * e + 4]};
+            parse_raw_midi_data(&r->inst, b, msgs[5 * e + 1]);
+            ++e;
+        }
+        float *L = outL + (size_t)f * 128;
+        float *R = outR + (size_t)f * 128;
+        oscGenerateFragment(r->inst.synth, r->bufA, 128);
+        if (flags & TBF_RENDER_WHIRL_BYPASS) {
+            memcpy(L, r->bufA, sizeof(float) * 128);
+            memcpy(R, r->bufA, sizeof(float) * 128);
+        } else if (flags & TBF_RENDER_WHIRLPROC3) {
+            whirlProc3(r->inst.whirl, r->bufA, L, R, r->tmpL, r->tmpR, 128);
+        } else {
+            whirlProc(r->inst.whirl, r->bufA, L, R, 128);
+        }
+    }
+    return 0;
+}
+
+/* the reference's note -> key table of a channel (-1: none), for the key-mapping tests */
+int ref_midi_key(void *h, int channel, int note)
+{
+    ref_inst *r = (ref_inst *)h;
+    /* b_midicfg is private to midi.cpp: observe the mapping through the engine instead */
+    struct b_tonegen *t = r->inst.synth;
+    uint8_t on[3] = {(uint8_t)(0x90 | (channel & 15)), (uint8_t)(note & 127), 100};
+    uint8_t off[3] = {(uint8_t)(0x80 | (channel & 15)), (uint8_t)(note & 127), 0};
+    int key = -1;
+    parse_raw_midi_data(&r->inst, on, 3);
+    for (int k = 0; k < MAX_KEYS; ++k)
+        if (t->activeKeys[k]) {
+            key = k;
+            break;
+        }
+    parse_raw_midi_data(&r->inst, off, 3);
+    return key;
+}
+
 int ref_active_wheels(void *h) { return ((ref_inst *)h)->inst.synth->activeOscLEnd; }
 
 /* ---- flatten the reference structs into the boundary's table format ---- */

@@ -39,6 +39,9 @@ def test_struct_sizes_match_header():
     assert L.tbf_sizeof_state_export() == C.sizeof(cabi.StateExport)
     assert L.tbf_sizeof_batch_desc() == C.sizeof(cabi.BatchDesc)
     assert L.tbf_sizeof_event() == C.sizeof(cabi.Event)
+    from tunebfree_b200 import midi
+    assert L.tbf_sizeof_midi_map() == C.sizeof(midi._Map)
+    assert L.tbf_sizeof_midi_state() == C.sizeof(midi.MidiState)
 
 
 def test_oracle_struct_sizes_match(ref):
