@@ -46,6 +46,7 @@ def lib():
         L.ref_render_midi.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.POINTER(C.c_uint),
                                       C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.ref_midi_key.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.ref_load_programmes.argtypes = [C.c_void_p, C.c_char_p]
         L.ref_dump_tonegen_tables.argtypes = [C.c_void_p, C.POINTER(cabi.TonegenTables)]
         L.ref_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
         L.ref_dump_whirl_tables.argtypes = [C.c_void_p, C.POINTER(cabi.WhirlTables)]
@@ -130,6 +131,11 @@ class RefInstance:
         lib().ref_render_midi(self._h, n_fragments, flags, arr, len(flat) // 5,
                               outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
         return outl, outr
+
+    def load_programmes(self, text):
+        """Programme definitions (.pgm syntax) through the reference's own parser."""
+        if lib().ref_load_programmes(self._h, text.encode()) != 0:
+            raise ValueError("the reference rejected the programme text")
 
     def midi_key(self, channel, note):
         """Engine key the reference maps (channel, note) to, -1 if none (observed through

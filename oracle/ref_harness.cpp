@@ -20,6 +20,7 @@
 #include "global_inst.h"
 #include "midi.h"
 #include "overdrive.h"
+#include "pgmParser.h"
 #include "program.h"
 #include "reverb.h"
 #include "state.h"
@@ -224,6 +225,24 @@ int ref_render_midi(void *h, unsigned n_fragments, unsigned flags, const unsigne
         }
     }
     return 0;
+}
+
+/* Load programme definitions (.pgm syntax) into the instance's programme table with the
+ * reference's own parser (loadProgrammeFile, src/pgmParser.cpp:376; the string variant is
+ * LV2-only).  0 = parsed. */
+int ref_load_programmes(void *h, const char *text)
+{
+    ref_inst *r = (ref_inst *)h;
+    char path[] = "/tmp/tbf_oracle_pgm_XXXXXX";
+    const int fd = mkstemp(path);
+    if (fd < 0)
+        return -1;
+    FILE *fp = fdopen(fd, "w");
+    fputs(text, fp);
+    fclose(fp);
+    const int rc = loadProgrammeFile(r->inst.progs, path);
+    remove(path);
+    return rc;
 }
 
 /* the reference's note -> key table of a channel (-1: none), for the key-mapping tests */

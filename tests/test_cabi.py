@@ -42,6 +42,7 @@ def test_struct_sizes_match_header():
     from tunebfree_b200 import midi
     assert L.tbf_sizeof_midi_map() == C.sizeof(midi._Map)
     assert L.tbf_sizeof_midi_state() == C.sizeof(midi.MidiState)
+    assert L.tbf_sizeof_programme_table() == C.sizeof(midi.ProgrammeTable)
 
 
 def test_oracle_struct_sizes_match(ref):

@@ -254,3 +254,148 @@ def test_gpu_render_of_compiled_midi_matches_the_reference_fed_raw_midi(ref, gpu
         rl, rr = r.render_midi(n_frag, cabi.RENDER_WHIRLPROC3, scripts[i])
         r.close()
         assert np.array_equal(_bits(gl[i]), _bits(rl)) and np.array_equal(_bits(gr[i]), _bits(rr)), i
+
+
+# ---------------------------------------------------------------- programmes
+
+PGM_TEXT = """
+# programmes of the test (syntax: src/pgmParser.cpp:65-75)
+1 { name="Full organ", drawbars="88 8888 888", drawbarslower = 00-8400-000
+    drawbarspedals=80_0000_000 vibrato=c3 vibratoupper=on vibratolower=off
+    perc=on percvol=soft percspeed=fast percharm=second rotaryspeed=tremolo reverbmix=0.2 }
+2 { name=Jazz drawbars=888000000, perc=yes, percvol=hi, percspeed=slow, percharm=3rd,
+    vibratoknob=v1, vibratoupper=no, overdrive=off, rotaryspeed=chorale }
+3 {name="Split \\"A\\"" keysplitlower=60 keysplitpedals=40 trssplitpedals=-12 trssplitlower=12
+   trssplitupper=-5 vibratolower=yes rotaryspeed=stop}
+7 { transpose=2 transposeupper=-3 transposelower=4 transposepedals=1 perc=off drawbars=008800000 }
+9 { name=random drawbars=random }
+"""
+
+
+def test_programme_text_parser():
+    m = midi.MidiMap(programmes=PGM_TEXT)
+    t = m.programmes
+    g = t.prog[1]
+    assert g.name == b"Full organ" and list(g.drawbars[0]) == [8] * 9
+    assert list(g.drawbars[1]) == [0, 0, 8, 4, 0, 0, 0, 0, 0] and list(g.drawbars[2]) == [8] + [0] * 8
+    assert g.scanner == (0x83 | 0x200) and (g.perc_enabled, g.perc_soft, g.perc_fast, g.perc_second) == (1, 1, 1, 1)
+    assert g.rotary_speed == 2 and abs(g.reverb_mix - 0.2) < 1e-7
+    inuse, drawbr, lowdrw, pdldrw, scannr = 0x1, 0x2, 0x80000, 0x100000, 0x100
+    assert g.flags & (inuse | drawbr | lowdrw | pdldrw | scannr) == (inuse | drawbr | lowdrw | pdldrw | scannr)
+    assert t.prog[2].name == b"Jazz" and t.prog[2].scanner & 0xFF == 1 and t.prog[2].rotary_speed == 0
+    assert t.prog[3].name == b'Split "A"' and (t.prog[3].split_lower, t.prog[3].split_pedals) == (60, 40)
+    assert list(t.prog[7].transpose)[:4] == [2, -3, 4, 1] and t.prog[7].perc_enabled == 0
+    assert t.prog[9].flags & 0x20000 and t.prog[4].flags == 0
+    for bad, line in (("1 { drawbars=123 }", 1), ("1 {\n perc=maybe }", 2), ("\n\n5 { nosuch=1 }", 3),
+                      ("1 { vibrato=v9 }", 1), ("x { }", 1), ("1 { transpose=200 }", 1), ("1 { name= }", 1)):
+        with pytest.raises(ValueError, match="line %d" % line):
+            midi.MidiMap(programmes=bad)
+
+
+def test_programme_change_events():
+    m = midi.MidiMap(programmes=PGM_TEXT)
+    ev, st = m.compile([(5, b"\xc0\x00")])          # programme 0 + offset 1
+    want = [(cabi.EV_DRAWBAR, i, 8) for i in range(9)]
+    want += [(cabi.EV_DRAWBAR, 9 + i, v) for i, v in enumerate([0, 0, 8, 4, 0, 0, 0, 0, 0])]
+    want += [(cabi.EV_DRAWBAR, 18 + i, v) for i, v in enumerate([8] + [0] * 8)]
+    want += [(cabi.EV_VIB_KNOB, 5, 0), (cabi.EV_VIB_UPPER, 1, 0), (cabi.EV_VIB_LOWER, 0, 0),
+             (cabi.EV_VIB_UPPER, 1, 0), (cabi.EV_VIB_LOWER, 0, 0),
+             (cabi.EV_PERC_ENABLE, 1, 0), (cabi.EV_PERC_ENABLE, 1, 0), (cabi.EV_PERC_SOFT, 1, 0),
+             (cabi.EV_PERC_FAST, 1, 0), (cabi.EV_PERC_FIRST, 1, 0), (cabi.EV_REV_SELECT, 2, 0)]
+    assert [e[1:] for e in ev] == want and all(e[0] == 5 for e in ev)
+    assert (st.vib_routing, st.rev_select, st.n_unsupported) == (2, 2, 0)
+    # splits and transposes move the instance's keys, not the shared map
+    st = m.new_state()
+    ev, st = m.compile([(0, b"\xc0\x02"), (1, b"\x90\x1e\x40"), (1, b"\x90\x32\x40"), (1, b"\x90\x46\x40")],
+                       state=st)
+    assert [e[1:3] for e in ev[-3:]] == [(cabi.EV_KEY_ON, 256 + 30 - 12), (cabi.EV_KEY_ON, 128 + 50 + 12),
+                                         (cabi.EV_KEY_ON, 70 - 5)]
+    assert m.key(0, 30) == 30 and m.key_now(st, 0, 30) == 256 + 18
+    ev, st = m.compile([(0, b"\xc0\x06"), (1, b"\x90\x3c\x40"), (1, b"\x91\x3c\x40"), (1, b"\x92\x18\x40")])
+    assert [e[2] for e in ev if e[1] == cabi.EV_KEY_ON] == [60 + 2 - 3, 128 + 60 + 2 + 4, 256 + 24 + 2 + 1]
+    # unused numbers, the table end and random drawbars
+    ev, st = m.compile([(0, b"\xc0\x03"), (0, b"\xc0\x7f"), (0, b"\xc0\x08")])
+    assert ev == [] and (st.n_ignored, st.n_unsupported) == (2, 1)
+    m0 = midi.MidiMap(programmes=PGM_TEXT, cfg="pgm.controller.offset=0\n")
+    assert [e[3] for e in m0.compile([(0, b"\xc0\x02")])[0][:3]] == [8, 8, 8]
+
+
+def _programme_script(seed, n_fragments):
+    rng = np.random.RandomState(seed)
+    msgs = midi_script(seed, n_fragments)
+    for f in sorted(rng.randint(2, n_fragments - 30, size=14)):
+        msgs.append((int(f), bytes([0xC0 | int(rng.randint(0, 3)), int(rng.choice([0, 1, 2, 6, 6, 1, 2]))])))
+    return sorted(msgs, key=lambda t: t[0])
+
+
+def test_programme_changes_render_like_the_reference(ref):
+    """CPU: the reference with the same programme text (its own parser) and raw MIDI, programme
+    changes included, against the reference fed our events."""
+    msgs = _programme_script(21, 300)
+    a = ref.RefInstance(seed=2)
+    a.load_programmes(PGM_TEXT)
+    wt = a.whirl_tables()
+    m = midi.MidiMap(revselects=list(wt.revselects), programmes=PGM_TEXT)
+    events, st = m.compile(msgs, init_rev_select=wt.init_rev_select)
+    assert st.n_unsupported == 0 and sum(1 for e in events if e[1] == cabi.EV_REV_SELECT) >= 3
+    al, ar = a.render_midi(300, cabi.RENDER_WHIRLPROC3, msgs)
+    a.close()
+    b = ref.RefInstance(seed=2)
+    bl, br = b.render(300, cabi.RENDER_WHIRLPROC3, events)
+    b.close()
+    assert np.abs(al).max() > 0.01
+    assert np.array_equal(_bits(al), _bits(bl)) and np.array_equal(_bits(ar), _bits(br))
+
+
+def test_reference_default_programme_file(ref):
+    """pgm/default.pgm of the reference tree, when it is there (not on the GPU box): parsed by
+    both sides, every programme installed once, same audio."""
+    import os
+    path = "/root/reference/pgm/default.pgm"
+    if not os.path.exists(path):
+        pytest.skip("reference tree not present")
+    text = open(path).read()
+    m = midi.MidiMap(programmes=text)
+    used = [p for p in range(1, 129) if m.programmes.prog[p].flags & 1]
+    assert len(used) > 100
+    # programmes with drawbars=random draw from the process-global rand(): not reproducible
+    used = [p for p in used if not m.programmes.prog[p].flags & 0x20000]
+    msgs = [(0, b"\x90\x3c\x64"), (0, b"\x91\x30\x64"), (0, b"\x92\x1c\x64")]
+    msgs += [(2 + 3 * i, bytes([0xC0, p - 1])) for i, p in enumerate(used)]
+    n_frag = 2 + 3 * len(used) + 4
+    a = ref.RefInstance(seed=1)
+    a.load_programmes(text)
+    wt = a.whirl_tables()
+    m = midi.MidiMap(revselects=list(wt.revselects), programmes=text)
+    events, st = m.compile(msgs, init_rev_select=wt.init_rev_select)
+    al, ar = a.render_midi(n_frag, cabi.RENDER_WHIRLPROC3, msgs)
+    a.close()
+    b = ref.RefInstance(seed=1)
+    bl, br = b.render(n_frag, cabi.RENDER_WHIRLPROC3, events)
+    b.close()
+    assert st.n_unsupported == 0
+    assert np.array_equal(_bits(al), _bits(bl)) and np.array_equal(_bits(ar), _bits(br))
+
+
+@pytest.mark.gpu
+def test_gpu_render_of_programme_changes_matches_the_reference(ref, gpu_ctx):
+    """GPU: 4 organs playing through programme changes (drawbars, percussion, vibrato, rotary,
+    splits and transposes) against the reference with the same programme text and raw MIDI."""
+    n_frag, n = 300, 4
+    r0 = ref.RefInstance(seed=6)
+    wt = r0.whirl_tables()
+    tg = gpu_ctx.tonegen_tables(r0.tonegen_tables())
+    wh = gpu_ctx.whirl_tables(wt)
+    r0.close()
+    first = gpu_ctx.create_instances(tg, wh, n)
+    m = midi.MidiMap(revselects=list(wt.revselects), programmes=PGM_TEXT)
+    scripts = [_programme_script(40 + i, n_frag) for i in range(n)]
+    events = [m.compile(s, init_rev_select=wt.init_rev_select)[0] for s in scripts]
+    gl, gr = gpu_ctx.render(n, n_frag, events, cabi.RENDER_WHIRLPROC3,
+                            ids=list(range(first, first + n)))
+    for i in range(n):
+        r = ref.RefInstance(seed=6)
+        r.load_programmes(PGM_TEXT)
+        rl, rr = r.render_midi(n_frag, cabi.RENDER_WHIRLPROC3, scripts[i])
+        r.close()
+        assert np.array_equal(_bits(gl[i]), _bits(rl)) and np.array_equal(_bits(gr[i]), _bits(rr)), i

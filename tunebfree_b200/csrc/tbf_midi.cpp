@@ -185,11 +185,172 @@ inline tbf_event make_event(uint32_t instance, uint32_t fragment, int type, int 
     return e;
 }
 
+/* loadKeyTableA / B / C (midi.cpp:676-726) for one note of channel set `set` */
+struct KeyInts {
+    int transpose, nsh_a, nsh_a_u, nsh_a_pl, nsh_a_ul, nsh_b, nsh_c, split_a_pl, split_a_ul;
+};
+inline int key_of(const KeyInts &k, int set, int i)
+{
+    if (set == 1)
+        return 128 + i + k.transpose + k.nsh_b;
+    if (set == 2)
+        return 2 * 128 + i + k.transpose + k.nsh_c;
+    int off;
+    if (i < k.split_a_pl)
+        off = k.transpose + k.nsh_a_pl + 2 * 128;
+    else if (i < k.split_a_ul)
+        off = k.transpose + k.nsh_a_ul + 128;
+    else if (k.split_a_ul)
+        off = k.transpose + k.nsh_a_u;
+    else
+        off = k.transpose + k.nsh_a;
+    return i + off;
+}
+
 /* revSelect after useRevOption(w, n, 2) (whirl.cpp:205-218) */
 inline int rev_select_of_option(int n)
 {
     const int hr = (n / 3) % 3;
     return hr == 2 ? 2 /* WHIRL_FAST */ : (hr == 1 ? 0 /* WHIRL_SLOW */ : 1 /* WHIRL_STOP */);
+}
+
+/* installProgram (src/program.cpp:735-921): the engine calls a programme change stands for,
+ * in the reference's order.  The setters it reaches through callMIDIControlFunction are the
+ * registered MIDI functions, so their value quantisation applies (knob * 23 -> knob, ...). */
+int install_program(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance, uint32_t fragment,
+                    int number, tbf_event *out, size_t cap)
+{
+    const tbf_programme_table *t = m->programmes;
+    if (!t) {
+        s->n_unsupported++;
+        return 0;
+    }
+    const int p = number + t->controller_offset;
+    if (!(0 < p && p < TBF_MAXPROGS)) {
+        s->n_ignored++;
+        return 0;
+    }
+    const tbf_programme &g = t->prog[p];
+    const uint32_t f = g.flags;
+    if (!(f & TBF_PGM_INUSE)) {
+        s->n_ignored++;
+        return 0;
+    }
+    size_t n = 0;
+#define PUT(type, a, b)                                                                               \
+    do {                                                                                              \
+        if (n >= cap)                                                                                 \
+            return TBF_ERR_ARG;                                                                       \
+        out[n++] = make_event(instance, fragment, (type), (a), (b));                                  \
+        if ((type) == TBF_EV_VIB_UPPER)                                                               \
+            s->vib_routing = (s->vib_routing & ~2) | ((a) ? 2 : 0);                                   \
+        if ((type) == TBF_EV_VIB_LOWER)                                                               \
+            s->vib_routing = (s->vib_routing & ~1) | ((a) ? 1 : 0);                                   \
+    } while (0)
+
+    if (f & TBF_PGM_DRWRND) /* randomizeDrawbars() draws from the process-global rand() */
+        s->n_unsupported++;
+    static const uint32_t manual_flag[3] = {TBF_PGM_DRAWBR, TBF_PGM_LOWDRW, TBF_PGM_PDLDRW};
+    for (int man = 0; man < 3; ++man) /* setDrawBars, tonegen.cpp:2769-2796 */
+        if ((f & manual_flag[man]) && !(f & TBF_PGM_DRWRND))
+            for (int i = 0; i < 9; ++i)
+                PUT(TBF_EV_DRAWBAR, 9 * man + i, g.drawbars[man][i]);
+    if (f & TBF_PGM_SCANNR) {
+        const int knob = ((g.scanner & 0xf) << 1) - ((g.scanner & 0x80) ? 1 : 2);
+        if (knob >= 0 && knob <= 5)
+            PUT(TBF_EV_VIB_KNOB, knob, 0);
+    }
+    if (f & TBF_PGM_VCRUPR) { /* vibrato.routing(rt << 5): both manuals are written */
+        const int rt = (s->vib_routing & ~2) | ((g.scanner & 0x200) ? 2 : 0);
+        PUT(TBF_EV_VIB_UPPER, rt >> 1, 0);
+        PUT(TBF_EV_VIB_LOWER, rt & 1, 0);
+    }
+    if (f & TBF_PGM_VCRLWR) {
+        const int rt = (s->vib_routing & ~1) | ((g.scanner & 0x100) ? 1 : 0);
+        PUT(TBF_EV_VIB_UPPER, rt >> 1, 0);
+        PUT(TBF_EV_VIB_LOWER, rt & 1, 0);
+    }
+    if (f & TBF_PGM_PRCENA) { /* the setter, then the registered function: two calls */
+        PUT(TBF_EV_PERC_ENABLE, g.perc_enabled ? 1 : 0, 0);
+        PUT(TBF_EV_PERC_ENABLE, g.perc_enabled ? 1 : 0, 0);
+    }
+    if (f & TBF_PGM_PRCVOL)
+        PUT(TBF_EV_PERC_SOFT, g.perc_soft ? 1 : 0, 0);
+    if (f & TBF_PGM_PRCSPD)
+        PUT(TBF_EV_PERC_FAST, g.perc_fast ? 1 : 0, 0);
+    if (f & TBF_PGM_PRCHRM)
+        PUT(TBF_EV_PERC_FIRST, g.perc_second ? 1 : 0, 0);
+    if (f & TBF_PGM_ROTSPS) { /* rotary.speed-preset(ceilf(sel * 63.5f)) -> setRevSelect(u / 43) */
+        const int u = (int)ceilf(g.rotary_speed * 63.5f);
+        PUT(TBF_EV_REV_SELECT, u / 43, 0);
+        s->rev_select = (u / 43) % 3;
+    }
+    /* keyboard splits and transposes change the instance's note -> key mapping */
+    if (f & TBF_PGM_KSPLTP)
+        s->split_a_pl = g.split_pedals;
+    if (f & TBF_PGM_KSPLTL)
+        s->split_a_ul = g.split_lower;
+    if (f & TBF_PGM_TRA_PD)
+        s->nsh_a_pl = g.transpose[5];
+    if (f & TBF_PGM_TRA_LM)
+        s->nsh_a_ul = g.transpose[6];
+    if (f & TBF_PGM_TRA_UM)
+        s->nsh_a_u = g.transpose[4];
+    if (f & TBF_PGM_TRANSP)
+        s->transpose = g.transpose[0];
+    if (f & TBF_PGM_TRCH_A)
+        s->nsh_a = g.transpose[1];
+    if (f & TBF_PGM_TRCH_B)
+        s->nsh_b = g.transpose[2];
+    if (f & TBF_PGM_TRCH_C)
+        s->nsh_c = g.transpose[3];
+#undef PUT
+    return (int)n;
+}
+
+bool affirmative(const char *v) /* isAffirmative, program.cpp:242-259 */
+{
+    int n;
+    if (!strcasecmp(v, "on") || !strcasecmp(v, "yes") || !strcasecmp(v, "true") ||
+        !strcasecmp(v, "enabled"))
+        return true;
+    return sscanf(v, "%d", &n) == 1 && n != 0;
+}
+
+bool negatory(const char *v) /* isNegatory, program.cpp:264-283 */
+{
+    int n;
+    if (!strcasecmp(v, "off") || !strcasecmp(v, "no") || !strcasecmp(v, "none") ||
+        !strcasecmp(v, "false") || !strcasecmp(v, "disabled"))
+        return true;
+    return sscanf(v, "%d", &n) == 1 && n == 0;
+}
+
+bool any_of(const char *v, const char *a, const char *b = NULL, const char *c = NULL,
+            const char *d = NULL)
+{
+    const char *opts[4] = {a, b, c, d};
+    for (int i = 0; i < 4; ++i)
+        if (opts[i] && !strcasecmp(v, opts[i]))
+            return true;
+    return false;
+}
+
+/* parseDrawbarRegistration, program.cpp:203-237: nine digits 0..8, blanks, '-' and '_' skipped */
+bool parse_registration(const char *v, uint8_t bar[9])
+{
+    int bus = 0;
+    for (const char *t = v; bus < 9; ++t) {
+        if (*t == '\0')
+            return false;
+        if (*t == ' ' || *t == '\t' || *t == '\n' || *t == '\r' || *t == '\f' || *t == '\v' ||
+            *t == '-' || *t == '_')
+            continue;
+        if (*t < '0' || *t > '8')
+            return false;
+        bar[bus++] = (uint8_t)(*t - '0');
+    }
+    return true;
 }
 
 } // namespace
@@ -362,21 +523,12 @@ int tbf_midi_map_finish(tbf_midi_map *m, const int32_t revselects[3])
     if (revselects)
         memcpy(m->revselects, revselects, sizeof(m->revselects));
     /* key tables A, B, C (midi.cpp:676-726) */
+    const KeyInts ki = {m->transpose, m->nsh_a, m->nsh_a_u, m->nsh_a_pl, m->nsh_a_ul,
+                        m->nsh_b,     m->nsh_c, m->split_a_pl, m->split_a_ul};
     int16_t kt[3][128];
-    for (int i = 0; i < 128; ++i) {
-        int off;
-        if (i < m->split_a_pl)
-            off = m->transpose + m->nsh_a_pl + 2 * 128;
-        else if (i < m->split_a_ul)
-            off = m->transpose + m->nsh_a_ul + 128;
-        else if (m->split_a_ul)
-            off = m->transpose + m->nsh_a_u;
-        else
-            off = m->transpose + m->nsh_a;
-        kt[0][i] = (int16_t)(i + off);
-        kt[1][i] = (int16_t)(128 + i + m->transpose + m->nsh_b);
-        kt[2][i] = (int16_t)(2 * 128 + i + m->transpose + m->nsh_c);
-    }
+    for (int set = 0; set < 3; ++set)
+        for (int i = 0; i < 128; ++i)
+            kt[set][i] = (int16_t)key_of(ki, set, i);
     /* controller vectors A, B, C: the engine modules register their functions one by one,
      * each taking the controller its id is mapped to (midi.cpp:416-446) */
     int16_t vec[3][128];
@@ -395,20 +547,47 @@ int tbf_midi_map_finish(tbf_midi_map *m, const int32_t revselects[3])
     /* status table (midi.cpp:782-800): a channel shared by two manuals goes to the later */
     memset(m->key_table, 0xFF, sizeof(m->key_table));
     memset(m->cc_fn, 0xFF, sizeof(m->cc_fn));
+    memset(m->ch_set, 0xFF, sizeof(m->ch_set));
     for (int s = 0; s < 3; ++s) {
         const int ch = m->rcv_ch[s] & 15;
         memcpy(m->key_table[ch], kt[s], sizeof(kt[s]));
         memcpy(m->cc_fn[ch], vec[s], sizeof(vec[s]));
+        m->ch_set[ch] = (int8_t)s;
     }
     return TBF_OK;
 }
 
-void tbf_midi_state_init(tbf_midi_state *s, int32_t init_rev_select)
+void tbf_midi_state_init(tbf_midi_state *s, const tbf_midi_map *m, int32_t init_rev_select)
 {
     if (!s)
         return;
     memset(s, 0, sizeof(*s));
     s->rev_select = init_rev_select % 3;
+    if (m) {
+        s->transpose = m->transpose;
+        s->nsh_a = m->nsh_a;
+        s->nsh_a_u = m->nsh_a_u;
+        s->nsh_a_pl = m->nsh_a_pl;
+        s->nsh_a_ul = m->nsh_a_ul;
+        s->nsh_b = m->nsh_b;
+        s->nsh_c = m->nsh_c;
+        s->split_a_pl = m->split_a_pl;
+        s->split_a_ul = m->split_a_ul;
+    }
+}
+
+int tbf_midi_key(const tbf_midi_map *m, const tbf_midi_state *s, int channel, int note)
+{
+    if (!m || !s || channel < 0 || channel > 15 || note < 0 || note > 127)
+        return -1;
+    const int set = m->ch_set[channel];
+    if (set < 0)
+        return -1;
+    const KeyInts ki = {s->transpose, s->nsh_a, s->nsh_a_u, s->nsh_a_pl, s->nsh_a_ul,
+                        s->nsh_b,     s->nsh_c, s->split_a_pl, s->split_a_ul};
+    const int key = key_of(ki, set, note);
+    /* the reference keeps keys in a `short` table and plays only non-negative ones */
+    return key < 0 ? -1 : key;
 }
 
 int tbf_midi_compile(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance, uint32_t fragment,
@@ -430,11 +609,15 @@ int tbf_midi_compile(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance
         if (n >= cap)                                                                                 \
             return TBF_ERR_ARG;                                                                       \
         out[n++] = make_event(instance, fragment, (type), (a), (b));                                  \
+        if ((type) == TBF_EV_VIB_UPPER)                                                               \
+            s->vib_routing = (s->vib_routing & ~2) | ((a) ? 2 : 0);                                   \
+        if ((type) == TBF_EV_VIB_LOWER)                                                               \
+            s->vib_routing = (s->vib_routing & ~1) | ((a) ? 1 : 0);                                   \
     } while (0)
 
     if (status == 0x80 || status == 0x90) {
         const int note = msg[1] & 0x7F, vel = msg[2] & 0x7F;
-        const int key = m->key_table[ch][note];
+        const int key = tbf_midi_key(m, s, ch, note);
         if (key < 0) { /* no table on this channel, or transposed below key 0 */
             s->n_ignored++;
             return 0;
@@ -446,9 +629,9 @@ int tbf_midi_compile(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance
         EMIT((status == 0x90 && vel > 0) ? TBF_EV_KEY_ON : TBF_EV_KEY_OFF, key, 0);
         return (int)n;
     }
-    if (status == 0xC0) { /* installProgram(): programme tables are outside this module */
-        s->n_unsupported++;
-        return 0;
+    if (status == 0xC0) {
+        const int rc = install_program(m, s, instance, fragment, msg[1] & 0x7F, out, cap);
+        return rc;
     }
     if (status != 0xB0) { /* pitch bend and everything else */
         s->n_ignored++;
@@ -536,7 +719,244 @@ int tbf_midi_compile(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance
     return (int)n;
 }
 
+void tbf_programmes_init(tbf_programme_table *t)
+{
+    if (!t)
+        return;
+    memset(t, 0, sizeof(*t));
+    t->controller_offset = 1;
+    t->previous = -1;
+}
+
+int tbf_programme_bind(tbf_programme_table *t, int pgmnr, const char *sym, const char *val)
+{
+    if (!t || !sym || !val || pgmnr < 0 || pgmnr >= TBF_MAXPROGS)
+        return TBF_ERR_ARG;
+    tbf_programme &g = t->prog[pgmnr];
+    if (pgmnr != t->previous) { /* a new programme number starts from no properties */
+        g.flags = 0;
+        t->previous = pgmnr;
+    }
+    const uint32_t U = TBF_PGM_INUSE;
+    int iv;
+    float fv;
+    /* keywords: propertySymbols[], program.cpp:132-163 */
+    if (!strcasecmp(sym, "name")) {
+        snprintf(g.name, sizeof(g.name), "%s", val);
+        g.flags |= U;
+    } else if (!strcasecmp(sym, "drawbars") || !strcasecmp(sym, "drawbarsupper") ||
+               !strcasecmp(sym, "drawbarslower") || !strcasecmp(sym, "drawbarspedals")) {
+        const int man = !strcasecmp(sym, "drawbarslower") ? 1 : (!strcasecmp(sym, "drawbarspedals") ? 2 : 0);
+        const uint32_t fl = man == 0 ? TBF_PGM_DRAWBR : (man == 1 ? TBF_PGM_LOWDRW : TBF_PGM_PDLDRW);
+        if (!strcasecmp(val, "random"))
+            g.flags |= U | fl | TBF_PGM_DRWRND;
+        else if (parse_registration(val, g.drawbars[man]))
+            g.flags |= U | fl;
+        else
+            return TBF_ERR_ARG;
+    } else if (!strcasecmp(sym, "attackenv") || !strcasecmp(sym, "attacklvl") ||
+               !strcasecmp(sym, "attackdur")) {
+        /* accepted and unused, as in the reference */
+    } else if (!strcasecmp(sym, "vibrato") || !strcasecmp(sym, "vibratoknob")) {
+        static const char *names[6] = {"v1", "v2", "v3", "c1", "c2", "c3"};
+        static const int codes[6] = {0x01, 0x02, 0x03, 0x81, 0x82, 0x83};
+        int k = -1;
+        for (int i = 0; i < 6; ++i)
+            if (!strcasecmp(val, names[i]))
+                k = i;
+        if (k < 0)
+            return TBF_ERR_ARG;
+        g.scanner = (int16_t)((g.scanner & 0xFF00) | codes[k]);
+        g.flags |= U | TBF_PGM_SCANNR;
+    } else if (!strcasecmp(sym, "vibratoupper") || !strcasecmp(sym, "vibratolower")) {
+        const int bit = !strcasecmp(sym, "vibratoupper") ? 0x200 : 0x100;
+        const uint32_t fl = bit == 0x200 ? TBF_PGM_VCRUPR : TBF_PGM_VCRLWR;
+        if (negatory(val))
+            g.scanner = (int16_t)(g.scanner & ~bit);
+        else if (affirmative(val))
+            g.scanner = (int16_t)(g.scanner | bit);
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | fl;
+    } else if (!strcasecmp(sym, "perc")) {
+        if (affirmative(val))
+            g.perc_enabled = 1;
+        else if (negatory(val))
+            g.perc_enabled = 0;
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | TBF_PGM_PRCENA;
+    } else if (!strcasecmp(sym, "percvol")) {
+        if (any_of(val, "normal", "high", "hi"))
+            g.perc_soft = 0;
+        else if (any_of(val, "soft", "low", "lo"))
+            g.perc_soft = 1;
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | TBF_PGM_PRCVOL;
+    } else if (!strcasecmp(sym, "percspeed")) {
+        if (any_of(val, "fast", "high", "hi"))
+            g.perc_fast = 1;
+        else if (any_of(val, "slow", "low", "lo"))
+            g.perc_fast = 0;
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | TBF_PGM_PRCSPD;
+    } else if (!strcasecmp(sym, "percharm")) {
+        if (any_of(val, "second", "2nd", "low", "lo"))
+            g.perc_second = 1;
+        else if (any_of(val, "third", "3rd", "high", "hi"))
+            g.perc_second = 0;
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | TBF_PGM_PRCHRM;
+    } else if (!strcasecmp(sym, "overdrive")) {
+        if (negatory(val))
+            g.overdrive = 0;
+        else if (affirmative(val))
+            g.overdrive = 1;
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | TBF_PGM_OVRSEL;
+    } else if (!strcasecmp(sym, "rotary")) {
+        /* pr_RotaryEnabled has no case in bindToProgram: accepted, no effect */
+    } else if (!strcasecmp(sym, "rotaryspeed")) {
+        if (any_of(val, "tremolo", "fast", "high", "hi"))
+            g.rotary_speed = 2;
+        else if (any_of(val, "chorale", "slow", "low", "lo"))
+            g.rotary_speed = 0;
+        else if (any_of(val, "stop", "zero", "break", "stopped"))
+            g.rotary_speed = 1;
+        else
+            return TBF_ERR_ARG;
+        g.flags |= U | TBF_PGM_ROTSPS;
+    } else if (!strcasecmp(sym, "reverbmix")) {
+        g.flags |= U | TBF_PGM_RVBMIX;
+        if (sscanf(val, "%f", &fv) != 1 || fv < 0.0f || fv > 1.0f)
+            return TBF_ERR_ARG;
+        g.reverb_mix = fv;
+    } else if (!strcasecmp(sym, "keysplitlower") || !strcasecmp(sym, "keysplitpedals")) {
+        const bool lower = !strcasecmp(sym, "keysplitlower");
+        g.flags |= U | (lower ? TBF_PGM_KSPLTL : TBF_PGM_KSPLTP);
+        if (sscanf(val, "%d", &iv) != 1 || iv < 0 || iv > 127)
+            return TBF_ERR_ARG;
+        (lower ? g.split_lower : g.split_pedals) = (int16_t)iv;
+    } else {
+        static const struct {
+            const char *name;
+            uint32_t flag;
+            int slot;
+        } tr[7] = {{"transpose", TBF_PGM_TRANSP, 0},        {"transposeupper", TBF_PGM_TRCH_A, 1},
+                   {"transposelower", TBF_PGM_TRCH_B, 2},   {"transposepedals", TBF_PGM_TRCH_C, 3},
+                   {"trssplitupper", TBF_PGM_TRA_UM, 4},    {"trssplitpedals", TBF_PGM_TRA_PD, 5},
+                   {"trssplitlower", TBF_PGM_TRA_LM, 6}};
+        int k = -1;
+        for (int i = 0; i < 7; ++i)
+            if (!strcasecmp(sym, tr[i].name))
+                k = i;
+        if (k < 0)
+            return TBF_ERR_ARG; /* unrecognised property */
+        g.flags |= U | tr[k].flag;
+        if (sscanf(val, "%d", &iv) != 1 || iv < -127 || iv > 127)
+            return TBF_ERR_ARG;
+        g.transpose[tr[k].slot] = (int16_t)iv;
+    }
+    return TBF_OK;
+}
+
+int tbf_programmes_load(tbf_programme_table *t, const char *text, int *err_line)
+{
+    if (!t || !text)
+        return TBF_ERR_ARG;
+    /* tokens (getToken, pgmParser.cpp:80-196): '{' '}' '=' ',' and strings -- quoted with
+     * backslash escapes, or bare runs of [A-Za-z0-9-._+]; '#' starts a comment */
+    const char *p = text;
+    int line = 1;
+    enum { T_EOF = 0, T_STR = 1, T_ERR = 2 };
+    char tok[256];
+    auto next = [&]() -> int {
+        for (;;) {
+            while (*p == ' ' || *p == '\t' || *p == '\r' || *p == '\n' || *p == '\f' || *p == '\v') {
+                if (*p == '\n')
+                    ++line;
+                ++p;
+            }
+            if (*p != '#')
+                break;
+            while (*p && *p != '\n')
+                ++p;
+        }
+        if (!*p)
+            return T_EOF;
+        size_t n = 0;
+        tok[0] = 0;
+        if (*p == '{' || *p == '}' || *p == '=' || *p == ',')
+            return *p++;
+        if (*p == '"') {
+            ++p;
+            for (;;) {
+                if (!*p)
+                    return T_ERR;
+                if (*p == '"') {
+                    ++p;
+                    break;
+                }
+                if (*p == '\\' && p[1])
+                    ++p;
+                if (*p == '\n')
+                    ++line;
+                if (n + 1 < sizeof(tok))
+                    tok[n++] = *p;
+                ++p;
+            }
+        } else {
+            while ((*p >= '0' && *p <= '9') || (*p >= 'a' && *p <= 'z') || (*p >= 'A' && *p <= 'Z') ||
+                   *p == '-' || *p == '.' || *p == '_' || *p == '+') {
+                if (n + 1 < sizeof(tok))
+                    tok[n++] = *p;
+                ++p;
+            }
+            if (n == 0)
+                return T_ERR; /* a character no token starts with */
+        }
+        tok[n] = 0;
+        return T_STR;
+    };
+    auto fail = [&]() {
+        if (err_line)
+            *err_line = line;
+        return (int)TBF_ERR_ARG;
+    };
+    int tk = next();
+    while (tk != T_EOF) {
+        int pgmnr;
+        if (tk != T_STR || sscanf(tok, "%d", &pgmnr) != 1)
+            return fail();
+        if ((tk = next()) != '{')
+            return fail();
+        tk = next();
+        while (tk != '}') {
+            char sym[64];
+            if (tk != T_STR)
+                return fail();
+            snprintf(sym, sizeof(sym), "%s", tok);
+            if ((tk = next()) != '=')
+                return fail();
+            if ((tk = next()) != T_STR)
+                return fail();
+            if (tbf_programme_bind(t, pgmnr, sym, tok) != TBF_OK)
+                return fail();
+            tk = next();
+            if (tk == ',')
+                tk = next();
+        }
+        tk = next();
+    }
+    return TBF_OK;
+}
+
 unsigned tbf_sizeof_midi_map(void) { return (unsigned)sizeof(tbf_midi_map); }
 unsigned tbf_sizeof_midi_state(void) { return (unsigned)sizeof(tbf_midi_state); }
+unsigned tbf_sizeof_programme_table(void) { return (unsigned)sizeof(tbf_programme_table); }
 
 } /* extern "C" */
