@@ -600,6 +600,14 @@ __device__ __forceinline__ void wave_request(TWarp &sm, int rec, int slot, int l
     __pipeline_memcpy_async(&sm.wstage[slot][lane], q, 16);
 }
 
+/* the same request with the record's address already in registers */
+__device__ __forceinline__ void wave_request_at(TWarp &sm, const uint2 a, int slot, int lane)
+{
+    const float4 *q =
+        reinterpret_cast<const float4 *>(((unsigned long long)a.y << 32) | (unsigned long long)a.x) + lane;
+    __pipeline_memcpy_async(&sm.wstage[slot][lane], q, 16);
+}
+
 /* Packed pairs of floats for Blackwell's two-wide FP32 instructions (FMUL2 / FADD2): each
  * half is an IEEE round-to-nearest operation, bit-identical to the scalar one.
  * ptxas contracts a mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which
@@ -715,14 +723,20 @@ __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm,
     }
     int i = 0, s = 0; /* s = i % WAVE_STAGES: the stage pair of records i, i+1 */
     if (!ENV) {
+        /* request addresses are read one trip before they are used (an LDS feeding the
+         * LDGSTS directly was the largest stall of the trip) */
+        uint2 qa = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + WAVE_STAGES, REC_CAP - 1)]);
+        uint2 qb = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + WAVE_STAGES + 1, REC_CAP - 1)]);
 #pragma unroll 1
         for (; i + WAVE_STAGES + 1 < cnt; i += 2) {
             __pipeline_wait_prior(WAVE_STAGES / 2 - 1); /* this lane's records i, i+1 landed */
             const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
             const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
-            wave_request(sm, rec0 + i + WAVE_STAGES, s, lane);
-            wave_request(sm, rec0 + i + WAVE_STAGES + 1, s + 1, lane);
+            wave_request_at(sm, qa, s, lane);
+            wave_request_at(sm, qb, s + 1, lane);
             __pipeline_commit();
+            qa = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + i + WAVE_STAGES + 2, REC_CAP - 1)]);
+            qb = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + i + WAVE_STAGES + 3, REC_CAP - 1)]);
             prod_add(a.sum, a.pa);
             prod_add(a.sum, a.pb);
             wheel_products<false>(tg, sm, rec0 + i, i, lane, xa, a.pa);
