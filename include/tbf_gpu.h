@@ -152,6 +152,12 @@ typedef struct tbf_event {
 #define TBF_RENDER_WHIRLPROC3 0x2   /* whirlProc3 mic-width mix (whirl.cpp:1653) */
 #define TBF_RENDER_OUT_DEVICE 0x4   /* out_l/out_r are device pointers           */
 #define TBF_RENDER_NO_OUTPUT 0x8    /* keep audio on device, checksums only      */
+#define TBF_RENDER_WHIRL_INPUT 0x10 /* Leslie only: whirlProc / whirlProc3 on the caller's mono
+                                       buffers `in` (src/whirl.h:232-249) -- the second half of
+                                       the hosts' chain oscGenerateFragment -> preamp -> reverb
+                                       -> whirlProc3 (src/clap.cpp:254-258) when the reverb or
+                                       the overdrive stays on the CPU.  The tone generator's
+                                       state is not touched; only rotor events are applied      */
 
 typedef struct tbf_batch_desc {
     uint32_t n_instances;
@@ -165,6 +171,9 @@ typedef struct tbf_batch_desc {
     uint32_t flags;
     uint64_t *checksums;  /* optional, host, [n_instances]: FNV-style hash of the
                              rendered L/R bit patterns                          */
+    const float *in;      /* TBF_RENDER_WHIRL_INPUT: [n_instances][in_stride] mono input,
+                             host memory, or device memory with TBF_RENDER_OUT_DEVICE   */
+    uint64_t in_stride;   /* floats between instances, >= n_fragments*128       */
 } tbf_batch_desc;
 
 typedef struct tbf_ctx tbf_ctx;

@@ -47,6 +47,8 @@ def lib():
                                       C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.ref_midi_key.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.ref_load_programmes.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_whirl_only.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p, C.POINTER(cabi.Event),
+                                     C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.ref_dump_tonegen_tables.argtypes = [C.c_void_p, C.POINTER(cabi.TonegenTables)]
         L.ref_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
         L.ref_dump_whirl_tables.argtypes = [C.c_void_p, C.POINTER(cabi.WhirlTables)]
@@ -130,6 +132,16 @@ class RefInstance:
         arr = (C.c_uint * max(1, len(flat)))(*flat)
         lib().ref_render_midi(self._h, n_fragments, flags, arr, len(flat) // 5,
                               outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
+        return outl, outr
+
+    def whirl_only(self, n_fragments, flags, mono, events=()):
+        """whirlProc / whirlProc3 on the caller's mono buffer; only rotor events apply."""
+        mono = np.ascontiguousarray(mono, dtype=np.float32)
+        outl = np.zeros(n_fragments * 128, dtype=np.float32)
+        outr = np.zeros(n_fragments * 128, dtype=np.float32)
+        arr, n = events_array(events)
+        lib().ref_whirl_only(self._h, n_fragments, flags, mono.ctypes.data_as(C.c_void_p), arr, n,
+                             outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
         return outl, outr
 
     def load_programmes(self, text):

@@ -197,6 +197,30 @@ int ref_render(void *h, unsigned n_fragments, unsigned flags, const tbf_event *e
     return 0;
 }
 
+/* The Leslie alone on the caller's mono input (whirlProc / whirlProc3, src/whirl.cpp:1640,
+ * :1653): only rotor events are applied.  Oracle for TBF_RENDER_WHIRL_INPUT. */
+int ref_whirl_only(void *h, unsigned n_fragments, unsigned flags, const float *in,
+                   const tbf_event *events, unsigned long long n_events, float *outL, float *outR)
+{
+    ref_inst *r = (ref_inst *)h;
+    unsigned long long e = 0;
+    for (unsigned f = 0; f < n_fragments; ++f) {
+        while (e < n_events && events[e].fragment == f) {
+            if (events[e].type == TBF_EV_REV_OPTION || events[e].type == TBF_EV_REV_SELECT)
+                ref_event(h, events[e].type, events[e].a, events[e].b);
+            ++e;
+        }
+        const float *x = in + (size_t)f * 128;
+        float *L = outL + (size_t)f * 128;
+        float *R = outR + (size_t)f * 128;
+        if (flags & TBF_RENDER_WHIRLPROC3)
+            whirlProc3(r->inst.whirl, x, L, R, r->tmpL, r->tmpR, 128);
+        else
+            whirlProc(r->inst.whirl, x, L, R, 128);
+    }
+    return 0;
+}
+
 /* Render with RAW MIDI input, the way the hosts do it: every message goes through the
  * reference's own parse_raw_midi_data() (src/midi.cpp:1261) right before the fragment it is
  * stamped with (b_synth/lv2.cpp:1130-1136).  msgs = n_msgs x {fragment, size, b0, b1, b2} as

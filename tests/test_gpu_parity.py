@@ -223,3 +223,53 @@ def test_error_paths(gpu_ctx):
         gpu_ctx.render(1, 4, [[]], 0, ids=[10 ** 6])
     with pytest.raises(TbfError):
         gpu_ctx.create_instances(999, 999, 1)
+    with pytest.raises(TbfError):   # Leslie-only and Leslie-bypass exclude each other
+        gpu_ctx.render(1, 4, [[]], cabi.RENDER_WHIRL_BYPASS, ids=[0], inputs=np.zeros((1, 512), np.float32))
+
+
+def test_leslie_only_on_caller_input(ref, gpu_ctx):
+    """TBF_RENDER_WHIRL_INPUT: whirlProc / whirlProc3 on the caller's mono buffers, the second
+    half of the hosts' chain (src/clap.cpp:254-258).  Noise with awkward values, rotor events,
+    two batches back to back, against the reference's whirlProc3 / whirlProc."""
+    rng = np.random.RandomState(7)
+    n_frag = 220
+    for flags in (cabi.RENDER_WHIRLPROC3, 0):
+        r, first = _make(ref, gpu_ctx, 3, seed=2)
+        x = (rng.standard_normal((3, n_frag * 128)) * 0.3).astype(np.float32)
+        x[0, 1000:1400] = 0.0
+        x[1, 5000] = np.float32(1e-38)          # denormal region, DENORMAL_HACK path
+        x[1, 5001] = np.float32(-3.5)
+        x[2, :128] = 0.0
+        ev = [(0, cabi.EV_REV_OPTION, 8, 0), (60, cabi.EV_REV_SELECT, 1, 0), (130, cabi.EV_REV_OPTION, 4, 0),
+              (131, cabi.EV_KEY_ON, 60, 0)]     # key events are not the Leslie's business here
+        cut = 97
+        ev_a = [e for e in ev if e[0] < cut]
+        ev_b = [(f - cut, t, a, b) for (f, t, a, b) in ev if f >= cut]
+        ids = list(range(first, first + 3))
+        la, ra = gpu_ctx.render(3, cut, [ev_a] * 3, flags, ids=ids, inputs=x[:, :cut * 128])
+        lb, rb = gpu_ctx.render(3, n_frag - cut, [ev_b] * 3, flags, ids=ids, inputs=x[:, cut * 128:])
+        gl, gr = np.concatenate([la, lb], axis=1), np.concatenate([ra, rb], axis=1)
+        for i in range(3):
+            ri = ref.RefInstance(seed=2)
+            rl, rr = ri.whirl_only(n_frag, flags, x[i], ev)
+            ri.close()
+            assert np.array_equal(_bits(gl[i]), _bits(rl)) and np.array_equal(_bits(gr[i]), _bits(rr)), (flags, i)
+        # the tone generator was left alone: no key is down, nothing is listed
+        assert gpu_ctx.export_state(first).active_osc_l_end == 0
+        r.close()
+
+
+def test_two_halves_with_host_audio_in_between(ref, gpu_ctx):
+    """tonegen on the GPU (WHIRL_BYPASS) -> audio on the host (where a host would run its
+    preamp / reverb) -> Leslie on the GPU (WHIRL_INPUT) == the contiguous chain, bit for bit."""
+    n_frag = 260
+    ev = workloads.instance_events(5, n_frag, config=3)
+    r, first = _make(ref, gpu_ctx, 1)
+    rl, rr = r.render(n_frag, cabi.RENDER_WHIRLPROC3, ev)
+    r.close()
+    rotor = (cabi.EV_REV_OPTION, cabi.EV_REV_SELECT)
+    mono, _ = gpu_ctx.render(1, n_frag, [[e for e in ev if e[1] not in rotor]],
+                             cabi.RENDER_WHIRL_BYPASS, ids=[first])
+    gl, gr = gpu_ctx.render(1, n_frag, [[e for e in ev if e[1] in rotor]], cabi.RENDER_WHIRLPROC3,
+                            ids=[first], inputs=mono)
+    assert np.array_equal(_bits(gl[0]), _bits(rl)) and np.array_equal(_bits(gr[0]), _bits(rr))

@@ -44,6 +44,7 @@ RENDER_WHIRL_BYPASS = 0x1
 RENDER_WHIRLPROC3 = 0x2
 RENDER_OUT_DEVICE = 0x4
 RENDER_NO_OUTPUT = 0x8
+RENDER_WHIRL_INPUT = 0x10
 
 IFLAG_COREPGM_OVERFLOW = 0x1
 IFLAG_KEYCOMP_OOB = 0x2
@@ -172,6 +173,8 @@ class BatchDesc(C.Structure):
         ("out_stride", C.c_uint64),
         ("flags", C.c_uint32),
         ("checksums", C.POINTER(C.c_uint64)),
+        ("in_", C.c_void_p),
+        ("in_stride", C.c_uint64),
     ]
 
 

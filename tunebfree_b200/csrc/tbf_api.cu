@@ -698,6 +698,12 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
         return fail(ctx, TBF_ERR_ARG, "render: output buffers missing or stride too small");
     if (frames > 0xFFFFFFFFull)
         return fail(ctx, TBF_ERR_ARG, "render: batch longer than 2^32 samples");
+    if (d->flags & TBF_RENDER_WHIRL_INPUT) {
+        if (d->flags & TBF_RENDER_WHIRL_BYPASS)
+            return fail(ctx, TBF_ERR_ARG, "render: WHIRL_INPUT and WHIRL_BYPASS exclude each other");
+        if (!d->in || d->in_stride < frames)
+            return fail(ctx, TBF_ERR_ARG, "render: input buffer missing or stride too small");
+    }
     if (d->n_events && !d->events)
         return fail(ctx, TBF_ERR_ARG, "render: events missing");
     if (d->instance_ids) {
@@ -795,6 +801,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     const bool dev_out = (d->flags & TBF_RENDER_OUT_DEVICE) != 0;
     const bool host_out = !no_out && !dev_out;
     const bool whirl = (d->flags & TBF_RENDER_WHIRL_BYPASS) == 0;
+    const bool whirl_input = (d->flags & TBF_RENDER_WHIRL_INPUT) != 0;
     const uint32_t chunk = ctx->prepared_chunk;
     const size_t n = d->n_instances;
     CK(cudaSetDevice(ctx->device));
@@ -931,14 +938,24 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                 /* a stage waits for its producer of this chunk and, before it overwrites
                  * the streams of parity `par`, for their consumers of chunk c - 2 */
                 int rc = 0;
-                if (c >= 2)
-                    CK(cudaStreamWaitEvent(st[0], ev[1][par], 0));
-                CK(prof_mark(0, true));
+                if (whirl_input) {
+                    /* the caller's mono input takes the place of stage T's output plane (stage R
+                     * of chunk c - 2, the plane's last reader, precedes on the same stream) */
+                    const float *src = d->in + s0 * d->in_stride + (size_t)(base + ib) * TBF_FRAGMENT;
+                    CK(cudaMemcpy2DAsync(p.u, sizeof(float) * pitch, src, sizeof(float) * d->in_stride,
+                                         sizeof(float) * p.n_fragments * TBF_FRAGMENT, ng,
+                                         cudaMemcpyDefault, st[1]));
+                } else {
+                    if (c >= 2)
+                        CK(cudaStreamWaitEvent(st[0], ev[1][par], 0));
+                    CK(prof_mark(0, true));
                     rc = tbf_launch_stage_t(p, st[0]);
                     CK(prof_mark(0, false));
-                CK(cudaEventRecord(ev[0][par], st[0]));
+                    CK(cudaEventRecord(ev[0][par], st[0]));
+                }
                 if (rc == 0) {
-                    CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
+                    if (!whirl_input)
+                        CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
                     if (whirl && c >= 2) {
                         CK(cudaStreamWaitEvent(st[1], ev[2][par], 0));
                         CK(cudaStreamWaitEvent(st[1], ev[3][par], 0));

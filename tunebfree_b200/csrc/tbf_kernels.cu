@@ -1210,6 +1210,9 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
     const uint32_t rows = min(32u, p.n_instances - slot0);
     const bool whirl_off = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
     const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
+    /* Leslie only: plane u holds the caller's mono input (whirlProc's inbuffer) and the
+     * tone generator's mixdown state (percussion gain, key compression) stays as it is */
+    const bool ext_in = (p.flags & TBF_RENDER_WHIRL_INPUT) != 0;
 
     InstState *st = nullptr;
     const DevWhirlTables *wh = p.wh;
@@ -1270,7 +1273,7 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         FragCtl c;
         c.key_comp = c.gain = c.decay = c.reset = 0.0f;
         c.flags = 0;
-        if (valid)
+        if (valid && !ext_in)
             c = p.ctl[(size_t)slot * p.n_fragments + f];
         const bool perc_on = (c.flags & FC_PERC_ON) != 0;
         /* (keyComp - level) / 128.f: dividing by 2^7 and multiplying by 2^-7 round identically */
@@ -1305,14 +1308,18 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
             for (int s = 0; s < BLK; ++s) {
                 const float uu = t_u[lane * TILE_PITCH + s];
                 float mono;
-                if (perc_on) {
-                    const float pterm = __fmul_rn(t_p[lane * TILE_PITCH + s], pg);
-                    mono = __fmul_rn(__fmul_rn(c.gain, kc), __fadd_rn(uu, pterm));
-                    pg = __fmul_rn(pg, c.decay);
+                if (ext_in) {
+                    mono = uu;
                 } else {
-                    mono = __fmul_rn(__fmul_rn(c.gain, kc), uu);
+                    if (perc_on) {
+                        const float pterm = __fmul_rn(t_p[lane * TILE_PITCH + s], pg);
+                        mono = __fmul_rn(__fmul_rn(c.gain, kc), __fadd_rn(uu, pterm));
+                        pg = __fmul_rn(pg, c.decay);
+                    } else {
+                        mono = __fmul_rn(__fmul_rn(c.gain, kc), uu);
+                    }
+                    kc = __fadd_rn(kc, delta);
                 }
-                kc = __fadd_rn(kc, delta);
                 if (whirl_run) {
                     const float x = (float)__dadd_rn((double)mono, 1e-14); /* DENORMAL_HACK */
                     const float ya = eq_iir(cA, zA0, zA1, x);

@@ -194,16 +194,25 @@ class Context:
             d.checksums = checksums.ctypes.data_as(C.POINTER(C.c_uint64))
         return d, keep
 
-    def render(self, n_instances, n_fragments, events=None, flags=0, ids=None, checksums=False):
+    def render(self, n_instances, n_fragments, events=None, flags=0, ids=None, checksums=False,
+               inputs=None):
         """Host-buffer render through tbf_gpu_render_batch.
         events: per-slot lists [(fragment, type, a, b)] or a prebuilt (array, n).
+        inputs: float32 [n_instances, n_fragments*128] mono buffers -> Leslie only
+        (TBF_RENDER_WHIRL_INPUT, whirlProc / whirlProc3 on the caller's audio).
         Returns (L, R[, checksums]) with L, R of shape [n_instances, n_fragments*128]."""
         frames = n_fragments * cabi.FRAGMENT
         out_l = np.empty((n_instances, frames), dtype=np.float32)
         out_r = np.empty((n_instances, frames), dtype=np.float32)
         cs = np.zeros(n_instances, dtype=np.uint64) if checksums else None
+        if inputs is not None:
+            inputs = np.ascontiguousarray(inputs, dtype=np.float32).reshape(n_instances, frames)
+            flags |= cabi.RENDER_WHIRL_INPUT
         d, keep = self._desc(n_instances, n_fragments, events, flags, ids,
                              out_l.ctypes.data, out_r.ctypes.data, frames, cs)
+        if inputs is not None:
+            d.in_ = inputs.ctypes.data
+            d.in_stride = frames
         self._ck(lib().tbf_gpu_render_batch(self._h, C.byref(d)))
         del keep
         return (out_l, out_r, cs) if checksums else (out_l, out_r)
