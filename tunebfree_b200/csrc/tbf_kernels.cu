@@ -4,9 +4,12 @@
  * forward pipeline whose recurrences all stay inside one stage, so it runs as four
  * kernels per chunk of fragments, each with the thread layout its stage wants:
  *
- *   stage T (warp = instance, lane = samples lane, lane+32, lane+64, lane+96 of a fragment)
- *       control events, active-list pass, additive wheel sum, scanner vibrato (ordered
- *       two-point scatter), percussion high-pass           -> u, php, per-fragment FragCtl
+ *   stage T (warp = instance; lane = 4 consecutive samples during the wheel sum, then
+ *            lane = sample of a 32-sample block)
+ *       control events, active-list pass into per-wheel records kept in shared memory across
+ *       quiet fragments, additive wheel sum (16-byte cp.async per lane and wheel from the
+ *       aligned wave store, packed FP32), scanner vibrato (ordered two-point scatter),
+ *       percussion high-pass                              -> u, php, per-fragment FragCtl
  *   stage R (lane = instance: 32 organs advance in lockstep in one warp)
  *       percussion decay / key-compression chase, mixdown, horn biquads A and B, rotor
  *       speed ramp + angle recurrence in double            -> dx0, hx0, hang, dang
