@@ -105,6 +105,9 @@ typedef struct tbf_whirl_tables {
     int32_t horn_phase[6], drum_phase[6];
     float horn_spacing[6], drum_spacing[6];
     float hafw[5], hbfw[5], drfL[5], drfR[5]; /* a1 a2 b0 b1 b2               */
+    /* the horn filters' type, Hz, Q, dB (haT haF haQ haG, hbT ..., src/whirl.h:173-180:
+     * floats there too): what the whirl.horn.filter.* controllers start from          */
+    float ha_param[4], hb_param[4];
     double mic_angle;
     float horn_acc, horn_dec, drum_acc, drum_dec;
     double rev_horn_target[9], rev_drum_target[9]; /* revoptions[]             */
@@ -137,7 +140,20 @@ typedef enum tbf_event_type {
     TBF_EV_VIB_KNOB = 10,   /* setVibratoFromInt(a)    src/vibrato.cpp:118     */
     TBF_EV_REV_OPTION = 11, /* useRevOption(w, a, 2)   src/whirl.cpp:174       */
     TBF_EV_SWELL = 12,      /* swellPedalGain = trim*a/127 src/tonegen.cpp:2885 */
-    TBF_EV_REV_SELECT = 13  /* setRevSelect(w, a)      src/whirl.cpp:226       */
+    TBF_EV_REV_SELECT = 13, /* setRevSelect(w, a)      src/whirl.cpp:226       */
+    /* the run-time Leslie controllers of src/whirl.cpp:975-981; a selects the rotor
+     * parameter, b is the 7-bit controller value the reference's setter receives      */
+    TBF_EV_WHIRL_BRAKE = 14, /* a: 0 setHornBrakePosition, 1 setDrumBrakePosition
+                                (brake position = b / 127.0) src/whirl.cpp:883-893      */
+    TBF_EV_WHIRL_RAMP = 15,  /* a: 0 setHornAcceleration, 1 setHornDeceleration (time
+                                constant .01 + b / 80.0), 2 setDrumAcceleration,
+                                3 setDrumDeceleration (.01 + b / 14.0) whirl.cpp:895-917 */
+    /* one coefficient of a horn IIR as setIIRFilter() (src/whirl.cpp:147-172) leaves it:
+     * a = 8 * filter (0 hafw, 1 hbfw) + index (0..4 = a1 a2 b0 b1 b2), b = the bit pattern
+     * of the float.  The coefficients come out of eqCompute()'s double-precision libm
+     * calls, so the host computes them (tbf_midi_compile() does, for the eight
+     * whirl.horn.filter.* controllers) and the device only stores them                  */
+    TBF_EV_HORN_FILTER = 16
 } tbf_event_type;
 
 typedef struct tbf_event {
@@ -248,6 +264,11 @@ typedef struct tbf_state_export {
     int32_t horn_acdc, drum_acdc;
     float whirl_buf[4][TBF_WHIRL_BUF]; /* HL HR DL DR                          */
     float iir_z[4][2];                 /* hafw hbfw drfL drfR: z0 z1           */
+    float horn_iir[2][5];              /* hafw hbfw: a1 a2 b0 b1 b2 (per instance:
+                                          TBF_EV_HORN_FILTER)                   */
+    double brake_pos[2];               /* hnBrakePos drBrakePos                */
+    double ramp_one_minus_l[4];        /* 1 - exp(-1 / (SR / 128 * tau)), tau = hornAcc
+                                          hornDec drumAcc drumDec               */
     float filt_z[4];
     float adx[3][8];
     int32_t adi[3];

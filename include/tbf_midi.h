@@ -13,8 +13,10 @@
  *                   struct b_midicfg (src/midi.cpp:203-268): receive channels, transposes and
  *                   splits, function -> controller tables, invert flags; and, derived by
  *                   tbf_midi_map_finish(), note -> key and (channel, controller) -> function
- *   tbf_midi_state  the one piece of engine state a controller reads back: b_whirl::revSelect
- *                   (rotary.speed-toggle, src/whirl.cpp:252-261)
+ *   tbf_midi_state  the engine state a controller reads back: b_whirl::revSelect
+ *                   (rotary.speed-toggle, src/whirl.cpp:252-261), the vibrato routing, the key
+ *                   mapping a programme may move, and the horn filters' type / Hz / Q / gain
+ *                   (each whirl.horn.filter.* controller changes one and recomputes the biquad)
  *
  * Plain C ABI, no allocation, no globals; one map may serve any number of instances.
  */
@@ -119,11 +121,14 @@ typedef struct tbf_midi_state {
     /* the instance's key mapping: starts as the map's, programmes may change it
      * (setKeyboardSplitMulti / setKeyboardTranspose*, src/midi.cpp:728-780) */
     int32_t transpose, nsh_a, nsh_a_u, nsh_a_pl, nsh_a_ul, nsh_b, nsh_c, split_a_pl, split_a_ul;
+    /* haT haF haQ haG / hbT hbF hbQ hbG (src/whirl.h:173-180, floats there) and the rate
+     * setIIRFilter() is called with (src/whirl.cpp:674-684) */
+    float horn_filter[2][4];
+    double sample_rate;
     uint32_t n_ignored;     /* messages with no effect on the path (reverb.mix, overdrive.*,
                                unassigned controllers, pitch bend, bank select ...)        */
     uint32_t n_unsupported; /* messages that DO change the reference's hot path but have no
-                               tbf_event: whirl.horn.filter.*, brake and acceleration
-                               controllers, programmes with random drawbars (process-global
+                               tbf_event: programmes with random drawbars (process-global
                                rand()), programme changes without a table.  Parity with the
                                reference holds only while this stays 0                     */
     uint32_t n_unmapped;    /* notes whose key is TBF_MAX_KEYS or above after transposition:
@@ -154,15 +159,18 @@ void tbf_midi_map_split(tbf_midi_map *m, int flags, int split_a_pl, int split_a_
  * revselects = tbf_whirl_tables::revselects, NULL = the defaults {4, 0, 8}. */
 int tbf_midi_map_finish(tbf_midi_map *m, const int32_t revselects[3]);
 
-/* init_rev_select = tbf_whirl_tables::init_rev_select; the vibrato routing starts at 0 */
-void tbf_midi_state_init(tbf_midi_state *s, const tbf_midi_map *m, int32_t init_rev_select);
+/* What a fresh instance of table set `w` starts from: init_rev_select, the horn filter
+ * parameters and the sample rate (w = NULL: whirl.cpp's compiled-in defaults at 48 kHz);
+ * the vibrato routing starts at 0, the key mapping at the map's */
+void tbf_midi_state_init(tbf_midi_state *s, const tbf_midi_map *m, const tbf_whirl_tables *w);
 /* engine key of (channel, note) under the instance's current mapping, -1 = none */
 int tbf_midi_key(const tbf_midi_map *m, const tbf_midi_state *s, int channel, int note);
 
 /* parse_raw_midi_data() + process_midi_event(): one raw message (2 or 3 bytes, status byte
  * first) that arrives before `fragment` of `instance`.  Appends the engine calls it stands for
  * to out[0..cap) and returns their number (0 for messages without effect; CC 120 / 123, the
- * panic, needs TBF_MAX_KEYS; a programme change up to 40), or TBF_ERR_ARG when cap is too
+ * panic, needs TBF_MAX_KEYS; a programme change up to 40; a horn filter controller 5: the
+ * biquad's coefficients, computed here by tbf_iir_coefficients()), or TBF_ERR_ARG when cap is too
  * small or an argument is NULL. */
 int tbf_midi_compile(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance, uint32_t fragment,
                      const uint8_t *msg, size_t size, tbf_event *out, size_t cap);

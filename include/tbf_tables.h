@@ -104,6 +104,13 @@ int tbf_spec_apply_cfg(tbf_tonegen_spec *tg, tbf_whirl_spec *wh, const char *key
 int tbf_build_tonegen_tables(const tbf_tonegen_spec *spec, tbf_tonegen_tables *out);
 void tbf_free_tonegen_tables(tbf_tonegen_tables *t);
 int tbf_build_whirl_tables(const tbf_whirl_spec *spec, tbf_whirl_tables *out);
+
+/* setIIRFilter() (src/whirl.cpp:147-172) over eqCompute() (src/eqcomp.cpp:109-203): the
+ * five float coefficients a1 a2 b0 b1 b2 of one Leslie biquad.  Returns 1 when c5 was
+ * written, 0 when a parameter is outside the range the reference accepts (it then keeps
+ * its previous coefficients, and so does c5), TBF_ERR_ARG for a NULL pointer. */
+int tbf_iir_coefficients(float c5[5], int type, double hz, double q, double gain_db,
+                         double sample_rate);
 void tbf_free_whirl_tables(tbf_whirl_tables *t);
 
 /* the extended 300-entry frequency table (src/tuning.cpp:115-147), for tests  */

@@ -164,6 +164,32 @@ int ref_event(void *h, int type, int a, int b)
          * this is its one assignment. */
         t->swellPedalGain = (t->outputLevelTrim * ((double)(unsigned char)a)) / 127.0;
         break;
+    /* the controller callbacks below are static in the reference (src/whirl.cpp:883-917);
+     * each case is that callback's one assignment */
+    case TBF_EV_WHIRL_BRAKE:
+        if (a == 0)
+            w->hnBrakePos = (double)(unsigned char)b / 127.0;
+        else
+            w->drBrakePos = (double)(unsigned char)b / 127.0;
+        break;
+    case TBF_EV_WHIRL_RAMP:
+        if (a == 0)
+            w->hornAcc = .01 + (double)(unsigned char)b / 80.0;
+        else if (a == 1)
+            w->hornDec = .01 + (double)(unsigned char)b / 80.0;
+        else if (a == 2)
+            w->drumAcc = .01 + (double)(unsigned char)b / 14.0;
+        else
+            w->drumDec = .01 + (double)(unsigned char)b / 14.0;
+        break;
+    case TBF_EV_HORN_FILTER: {
+        /* what setIIRFilter() stores (src/whirl.cpp:167-171), one coefficient at a time */
+        static const int idx[5] = {a1, a2, b0, b1, b2};
+        float v;
+        memcpy(&v, &b, sizeof v);
+        ((a >> 3) ? w->hbfw : w->hafw)[idx[a & 7]] = v;
+        break;
+    }
     default:
         return -1;
     }
@@ -206,7 +232,9 @@ int ref_whirl_only(void *h, unsigned n_fragments, unsigned flags, const float *i
     unsigned long long e = 0;
     for (unsigned f = 0; f < n_fragments; ++f) {
         while (e < n_events && events[e].fragment == f) {
-            if (events[e].type == TBF_EV_REV_OPTION || events[e].type == TBF_EV_REV_SELECT)
+            if (events[e].type == TBF_EV_REV_OPTION || events[e].type == TBF_EV_REV_SELECT ||
+                events[e].type == TBF_EV_WHIRL_BRAKE || events[e].type == TBF_EV_WHIRL_RAMP ||
+                events[e].type == TBF_EV_HORN_FILTER)
                 ref_event(h, events[e].type, events[e].a, events[e].b);
             ++e;
         }
@@ -416,6 +444,10 @@ int ref_dump_whirl_tables(void *h, tbf_whirl_tables *o)
         dst[k][3] = src[k][b1];
         dst[k][4] = src[k][b2];
     }
+    const float hap[4] = {w->haT, w->haF, w->haQ, w->haG};
+    const float hbp[4] = {w->hbT, w->hbF, w->hbQ, w->hbG};
+    memcpy(o->ha_param, hap, sizeof hap);
+    memcpy(o->hb_param, hbp, sizeof hbp);
     o->mic_angle = w->micAngle;
     o->horn_acc = w->hornAcc;
     o->horn_dec = w->hornDec;
@@ -491,6 +523,20 @@ int ref_export_state(void *h, tbf_state_export *o)
     for (int k = 0; k < 4; ++k) {
         o->iir_z[k][0] = f[k][z0];
         o->iir_z[k][1] = f[k][z1];
+    }
+    for (int k = 0; k < 2; ++k) {
+        o->horn_iir[k][0] = f[k][a1];
+        o->horn_iir[k][1] = f[k][a2];
+        o->horn_iir[k][2] = f[k][b0];
+        o->horn_iir[k][3] = f[k][b1];
+        o->horn_iir[k][4] = f[k][b2];
+    }
+    o->brake_pos[0] = w->hnBrakePos;
+    o->brake_pos[1] = w->drBrakePos;
+    {
+        const float tau[4] = {w->hornAcc, w->hornDec, w->drumAcc, w->drumDec};
+        for (int k = 0; k < 4; ++k) /* as src/whirl.cpp:1255-1257 computes it per call */
+            o->ramp_one_minus_l[k] = 1 - exp(-1.0 / (w->SampleRateD / (double)(size_t)128 * tau[k]));
     }
     memcpy(o->filt_z, w->z, sizeof(o->filt_z));
     memcpy(o->adx[0], w->adx0, sizeof(w->adx0));

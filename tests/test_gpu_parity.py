@@ -45,7 +45,9 @@ def _compare_state(gs, rs, whirl=True):
         assert (gs.horn_angle, gs.drum_angle, gs.horn_incr, gs.drum_incr) == \
                (rs.horn_angle, rs.drum_angle, rs.horn_incr, rs.drum_incr)
         assert (gs.horn_acdc, gs.drum_acdc) == (rs.horn_acdc, rs.drum_acdc)
-        for name in ("whirl_buf", "iir_z", "filt_z", "adx"):
+        assert tuple(gs.brake_pos) == tuple(rs.brake_pos)
+        assert tuple(gs.ramp_one_minus_l) == tuple(rs.ramp_one_minus_l)
+        for name in ("whirl_buf", "iir_z", "horn_iir", "filt_z", "adx"):
             a = np.ctypeslib.as_array(getattr(gs, name)).view(np.uint32)
             b = np.ctypeslib.as_array(getattr(rs, name)).view(np.uint32)
             assert np.array_equal(a, b), name
@@ -96,6 +98,39 @@ def test_whirlproc_plain_and_speed_changes(ref, gpu_ctx):
         ev.append((40 + 90 * i, cabi.EV_REV_OPTION, n, 0))
     ev += [(700, cabi.EV_REV_SELECT, 1, 0), (820, cabi.EV_REV_SELECT, 2, 0)]
     _check(ref, gpu_ctx, ev, 1000, 0)
+
+
+def test_leslie_controllers_brakes_ramps_horn_filters(ref, gpu_ctx):
+    """TBF_EV_WHIRL_BRAKE / _RAMP / TBF_EV_HORN_FILTER (src/whirl.cpp:703-917): brake positions
+    while the rotors run down to a stop, every ramp constant at both ends of its range, horn
+    biquads swapped mid-note; per-instance, so a second organ of the same table set keeps the
+    table's values."""
+    from tunebfree_b200 import tables
+    ev = workloads.setup_events(3)
+    ev += [(0, cabi.EV_KEY_ON, k, 0) for k in (40, 52, 60, 67, 76)]
+    ev += [(2, cabi.EV_WHIRL_BRAKE, 0, 64), (2, cabi.EV_WHIRL_BRAKE, 1, 127), (3, cabi.EV_WHIRL_RAMP, 1, 0),
+           (3, cabi.EV_WHIRL_RAMP, 3, 5), (10, cabi.EV_REV_OPTION, 0, 0),       # both rotors to a stop
+           (330, cabi.EV_WHIRL_RAMP, 0, 127), (330, cabi.EV_WHIRL_RAMP, 2, 0), (331, cabi.EV_REV_OPTION, 8, 0),
+           (480, cabi.EV_WHIRL_BRAKE, 0, 1), (480, cabi.EV_WHIRL_BRAKE, 1, 0), (481, cabi.EV_REV_SELECT, 1, 0),
+           (600, cabi.EV_WHIRL_RAMP, 1, 127), (600, cabi.EV_WHIRL_RAMP, 3, 127), (601, cabi.EV_REV_SELECT, 0, 0)]
+    for frag, filt, (typ, hz, q, g) in [(100, 0, (1, 1200.0, 0.8, 0.0)), (200, 1, (2, 700.0, 3.0, 0.0)),
+                                        (400, 0, (8, 5000.0, 1.0, -20.0)), (640, 1, (3, 2500.0, 5.5, 12.0))]:
+        c5 = tables.iir_coefficients(typ, hz, q, g, 48000.0)
+        ev += [(frag, cabi.EV_HORN_FILTER, 8 * filt + k, int(np.float32(c5[k]).view(np.int32))) for k in range(5)]
+    ev.sort(key=lambda e: e[0])
+    _check(ref, gpu_ctx, ev, 760, cabi.RENDER_WHIRLPROC3)
+    # two organs of one table set: only the first gets the controllers
+    r, first = _make(ref, gpu_ctx, 2)
+    plain = workloads.setup_events(3) + [(0, cabi.EV_KEY_ON, 60, 0), (5, cabi.EV_REV_OPTION, 0, 0)]
+    gl, gr = gpu_ctx.render(2, 200, [[e for e in ev if e[0] < 200], plain], cabi.RENDER_WHIRLPROC3,
+                            ids=[first, first + 1])
+    rl, rr = r.render(200, cabi.RENDER_WHIRLPROC3, plain)
+    r.close()
+    assert np.array_equal(_bits(gl[1]), _bits(rl)) and np.array_equal(_bits(gr[1]), _bits(rr))
+    assert not np.array_equal(_bits(gl[0]), _bits(gl[1]))
+    gpu_ctx.render(1, 4, [[(0, cabi.EV_WHIRL_RAMP, 4, 10)]], 0, ids=[first + 1])
+    assert gpu_ctx.export_state(first + 1).error_flags & cabi.IFLAG_BAD_EVENT
+    assert not gpu_ctx.export_state(first).error_flags & cabi.IFLAG_BAD_EVENT
 
 
 def test_setters_midstream(ref, gpu_ctx):

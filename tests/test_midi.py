@@ -6,6 +6,7 @@ Pins, in the order the reference's own tests give them (src/midi.cpp:1460-1873):
   * equivalence of the whole translation: the oracle fed RAW MIDI renders the same bits as the
     oracle fed our compiled events (CPU), and as the CUDA path fed them (gpu).
 """
+import math
 import numpy as np
 import pytest
 
@@ -150,7 +151,8 @@ def test_messages_without_an_event_are_counted():
     assert ev == [] and st.n_ignored == 9 and st.n_unsupported == 1  # pedal release: no action
     m = midi.MidiMap(cfg="midi.controller.upper.20=whirl.horn.filter.a.hz\nmidi.transpose=100\n")
     ev, st = m.compile([(0, b"\xb0\x14\x40"), (0, b"\x92\x7f\x64"), (0, b"\x90\x00\x64")])
-    assert ev == [(0, cabi.EV_KEY_ON, 100, 0)] and st.n_unsupported == 1 and st.n_unmapped == 1
+    assert [e[1] for e in ev] == [cabi.EV_HORN_FILTER] * 5 + [cabi.EV_KEY_ON]
+    assert ev[-1] == (0, cabi.EV_KEY_ON, 100, 0) and st.n_unsupported == 0 and st.n_unmapped == 1
     ev, _ = midi.MidiMap().compile([(3, b"\xb0\x7b\x00")])
     assert [e[2] for e in ev] == list(range(384)) and all(e[1] == cabi.EV_KEY_OFF for e in ev)
 
@@ -158,10 +160,12 @@ def test_messages_without_an_event_are_counted():
 # ---------------------------------------------------------------- whole translation
 
 
-def midi_script(seed, n_fragments, channels=(0, 1, 2), extra_cc=()):
+def midi_script(seed, n_fragments, channels=(0, 1, 2), extra_cc=(), dense_cc=()):
     """A seeded performance: chords on the three manuals, drawbar / percussion / vibrato /
-    rotary / swell controllers, the sustain pedal, one panic."""
+    rotary / swell controllers, the sustain pedal, one panic.  dense_cc: (status, controller)
+    pairs that get a random value every few fragments."""
     rng = np.random.RandomState(seed)
+    rng2 = np.random.RandomState(seed + 7919)
     up, lo, pd = channels
     msgs = [(0, bytes([0xB0 | up, 70 + i, 0])) for i in range(9)]            # 888888888
     msgs += [(0, bytes([0xB0 | lo, 70 + i, 40])) for i in range(4)]
@@ -194,10 +198,23 @@ def midi_script(seed, n_fragments, channels=(0, 1, 2), extra_cc=()):
             pool = [(0xB0 | up, 91, 64), (0xE0 | up, 0, 64), (0xB0 | lo, 66, 127), (0xB0 | 9, 70, 0)]
             pool += list(extra_cc)
             msgs.append((f, bytes(pool[rng.randint(0, len(pool))])))
+        if dense_cc and rng2.randint(0, 2):
+            st, cc = dense_cc[rng2.randint(0, len(dense_cc))]
+            # the ends of the range are where setIIRFilter() rejects Q and gain
+            v = int(rng2.randint(0, 128)) if rng2.randint(0, 4) else (0, 1, 2, 126, 127)[rng2.randint(0, 5)]
+            msgs.append((f, bytes([st, cc, v])))
         f += int(rng.randint(1, 12))
     msgs.append((n_fragments - 20, bytes([0xB0 | up, 123, 0])))
     return sorted(msgs, key=lambda t: t[0])
 
+
+WHIRL_CC = ["whirl.horn.filter.a.type", "whirl.horn.filter.a.hz", "whirl.horn.filter.a.q",
+            "whirl.horn.filter.a.gain", "whirl.horn.filter.b.type", "whirl.horn.filter.b.hz",
+            "whirl.horn.filter.b.q", "whirl.horn.filter.b.gain", "whirl.horn.brakepos",
+            "whirl.drum.brakepos", "whirl.horn.acceleration", "whirl.horn.deceleration",
+            "whirl.drum.acceleration", "whirl.drum.deceleration"]
+
+WHIRL_CC_NUM = list(range(20, 32)) + [34, 35]   # 32 is bank select LSB: never dispatched
 
 SCRIPT_CFGS = [
     ("", (0, 1, 2), ()),
@@ -210,18 +227,21 @@ SCRIPT_CFGS = [
     ("whirl.speed-preset=2\nmidi.controller.reset=1\nmidi.controller.upper.64=rotary.speed-toggle\n"
      "midi.controller.upper.70=vibrato.knob\nmidi.controller.pedals.7=swellpedal1\n",
      (0, 1, 2), ((0xB0, 64, 127), (0xB2, 7, 99), (0xB0, 70, 77))),
+    # the Leslie's run-time controllers (src/whirl.cpp:966-981): horn filters, brakes, ramps
+    ("".join("midi.controller.upper.%d=%s\n" % (c, n) for c, n in zip(WHIRL_CC_NUM, WHIRL_CC)),
+     (0, 1, 2), ((0xB0, 1, 0), (0xB0, 1, 50), (0xB0, 1, 100)), tuple((0xB0, c) for c in WHIRL_CC_NUM)),
 ]
 
 
 @pytest.mark.parametrize("case", range(len(SCRIPT_CFGS)))
 def test_compiled_events_render_like_raw_midi_on_the_reference(ref, case):
     """CPU: the reference engine fed raw MIDI == the reference engine fed our event list."""
-    cfg, channels, extra = SCRIPT_CFGS[case]
-    msgs = midi_script(10 + case, 260, channels, extra)
+    cfg, channels, extra = SCRIPT_CFGS[case][:3]
+    msgs = midi_script(10 + case, 260, channels, extra, *SCRIPT_CFGS[case][3:])
     a = ref.RefInstance(seed=3, cfg=cfg)
     wt = a.whirl_tables()
     m = midi.MidiMap(cfg=cfg, revselects=list(wt.revselects))
-    events, st = m.compile(msgs, init_rev_select=wt.init_rev_select)
+    events, st = m.compile(msgs, whirl_tables=wt)
     assert st.n_unsupported == 0 and len(events) > 100
     al, ar = a.render_midi(260, cabi.RENDER_WHIRLPROC3, msgs)
     a.close()
@@ -232,10 +252,51 @@ def test_compiled_events_render_like_raw_midi_on_the_reference(ref, case):
     assert np.array_equal(_bits(al), _bits(bl)) and np.array_equal(_bits(ar), _bits(br))
 
 
+def test_leslie_controllers_leave_the_reference_in_the_compiled_state(ref):
+    """Every value of every whirl.* controller, one after the other, through the reference's
+    parse_raw_midi_data(); the coefficients / brake positions / ramp factors its struct b_whirl
+    ends up with == what the compiled events carry (filters: tbf_iir_coefficients on the host,
+    incl. the values setIIRFilter() rejects)."""
+    cfg = SCRIPT_CFGS[3][0]
+    r = ref.RefInstance(seed=1, cfg=cfg)
+    wt = r.whirl_tables()
+    m = midi.MidiMap(cfg=cfg, revselects=list(wt.revselects))
+    st = m.new_state(wt)
+    rng = np.random.RandomState(5)
+    order = [(i, v) for i in range(len(WHIRL_CC)) for v in range(128)]
+    rng.shuffle(order)
+    iir = [list(wt.hafw), list(wt.hbfw)]
+    brake = [wt.hn_brake_pos, wt.dr_brake_pos]
+    ramp_v = [None] * 4
+    f32 = lambda x: np.asarray(x, np.float32).view(np.uint32)
+    for start in range(0, len(order), 64):
+        msgs = [(0, bytes([0xB0, WHIRL_CC_NUM[i], v])) for i, v in order[start:start + 64]]
+        ev, st = m.compile(msgs, state=st)
+        for _, t, a, b in ev:
+            if t == cabi.EV_HORN_FILTER:
+                iir[a >> 3][a & 7] = np.int32(b).view(np.float32)
+            elif t == cabi.EV_WHIRL_BRAKE:
+                brake[a] = b / 127.0
+            else:
+                assert t == cabi.EV_WHIRL_RAMP
+                ramp_v[a] = b
+        r.render_midi(1, 0, msgs)
+        rs = r.export_state()
+        assert np.array_equal(f32(iir), f32(np.ctypeslib.as_array(rs.horn_iir))), start
+        assert tuple(rs.brake_pos) == tuple(brake)
+        for k in range(4):
+            if ramp_v[k] is not None:
+                tau = np.float32(.01 + ramp_v[k] / (80.0 if k < 2 else 14.0))
+                assert rs.ramp_one_minus_l[k] == 1 - math.exp(-1.0 / (48000.0 / 128.0 * float(tau)))
+    assert st.n_unsupported == 0 and st.n_ignored == 0
+    r.close()
+
+
 @pytest.mark.gpu
-def test_gpu_render_of_compiled_midi_matches_the_reference_fed_raw_midi(ref, gpu_ctx):
+@pytest.mark.parametrize("case", [1, 3])
+def test_gpu_render_of_compiled_midi_matches_the_reference_fed_raw_midi(ref, gpu_ctx, case):
     """GPU: 6 organs, each with its own MIDI performance, against parse_raw_midi_data()."""
-    cfg, channels, extra = SCRIPT_CFGS[1]
+    cfg, channels, extra = SCRIPT_CFGS[case][:3]
     n_frag = 300
     r0 = ref.RefInstance(seed=4, cfg=cfg)
     wt = r0.whirl_tables()
@@ -245,8 +306,8 @@ def test_gpu_render_of_compiled_midi_matches_the_reference_fed_raw_midi(ref, gpu
     n = 6
     first = gpu_ctx.create_instances(tg, wh, n)
     m = midi.MidiMap(cfg=cfg, revselects=list(wt.revselects))
-    scripts = [midi_script(100 + i, n_frag, channels, extra) for i in range(n)]
-    events = [m.compile(s, init_rev_select=wt.init_rev_select)[0] for s in scripts]
+    scripts = [midi_script(100 + i, n_frag, channels, extra, *SCRIPT_CFGS[case][3:]) for i in range(n)]
+    events = [m.compile(s, whirl_tables=wt)[0] for s in scripts]
     gl, gr = gpu_ctx.render(n, n_frag, events, cabi.RENDER_WHIRLPROC3,
                             ids=list(range(first, first + n)))
     for i in range(n):
@@ -336,7 +397,7 @@ def test_programme_changes_render_like_the_reference(ref):
     a.load_programmes(PGM_TEXT)
     wt = a.whirl_tables()
     m = midi.MidiMap(revselects=list(wt.revselects), programmes=PGM_TEXT)
-    events, st = m.compile(msgs, init_rev_select=wt.init_rev_select)
+    events, st = m.compile(msgs, whirl_tables=wt)
     assert st.n_unsupported == 0 and sum(1 for e in events if e[1] == cabi.EV_REV_SELECT) >= 3
     al, ar = a.render_midi(300, cabi.RENDER_WHIRLPROC3, msgs)
     a.close()
@@ -367,7 +428,7 @@ def test_reference_default_programme_file(ref):
     a.load_programmes(text)
     wt = a.whirl_tables()
     m = midi.MidiMap(revselects=list(wt.revselects), programmes=text)
-    events, st = m.compile(msgs, init_rev_select=wt.init_rev_select)
+    events, st = m.compile(msgs, whirl_tables=wt)
     al, ar = a.render_midi(n_frag, cabi.RENDER_WHIRLPROC3, msgs)
     a.close()
     b = ref.RefInstance(seed=1)
@@ -390,7 +451,7 @@ def test_gpu_render_of_programme_changes_matches_the_reference(ref, gpu_ctx):
     first = gpu_ctx.create_instances(tg, wh, n)
     m = midi.MidiMap(revselects=list(wt.revselects), programmes=PGM_TEXT)
     scripts = [_programme_script(40 + i, n_frag) for i in range(n)]
-    events = [m.compile(s, init_rev_select=wt.init_rev_select)[0] for s in scripts]
+    events = [m.compile(s, whirl_tables=wt)[0] for s in scripts]
     gl, gr = gpu_ctx.render(n, n_frag, events, cabi.RENDER_WHIRLPROC3,
                             ids=list(range(first, first + n)))
     for i in range(n):

@@ -39,6 +39,9 @@ EV_VIB_KNOB = 10
 EV_REV_OPTION = 11
 EV_SWELL = 12
 EV_REV_SELECT = 13
+EV_WHIRL_BRAKE = 14
+EV_WHIRL_RAMP = 15
+EV_HORN_FILTER = 16
 
 RENDER_WHIRL_BYPASS = 0x1
 RENDER_WHIRLPROC3 = 0x2
@@ -118,6 +121,8 @@ class WhirlTables(C.Structure):
         ("hbfw", C.c_float * 5),
         ("drfL", C.c_float * 5),
         ("drfR", C.c_float * 5),
+        ("ha_param", C.c_float * 4),
+        ("hb_param", C.c_float * 4),
         ("mic_angle", C.c_double),
         ("horn_acc", C.c_float),
         ("horn_dec", C.c_float),
@@ -204,6 +209,9 @@ class StateExport(C.Structure):
         ("drum_acdc", C.c_int32),
         ("whirl_buf", (C.c_float * WHIRL_BUF) * 4),
         ("iir_z", (C.c_float * 2) * 4),
+        ("horn_iir", (C.c_float * 5) * 2),
+        ("brake_pos", C.c_double * 2),
+        ("ramp_one_minus_l", C.c_double * 4),
         ("filt_z", C.c_float * 4),
         ("adx", (C.c_float * 8) * 3),
         ("adi", C.c_int32 * 3),

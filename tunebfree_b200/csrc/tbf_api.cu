@@ -105,6 +105,14 @@ struct tbf_ctx {
         }                                                                                   \
     } while (0)
 
+/* 1 - l with l = exp(-1.0 / (SR / n * tau)), the per-call smoothing factor of a rotor ramp
+ * (src/whirl.cpp:1255-1257, :1306-1308); glibc's exp, as the reference's host computes it */
+static double ramp_one_minus_l(double sample_rate, float tau)
+{
+    const double l = exp(-1.0 / (sample_rate / (double)(size_t)TBF_FRAGMENT * tau));
+    return 1 - l;
+}
+
 static int fail(tbf_ctx *ctx, int code, const char *msg)
 {
     if (ctx)
@@ -426,9 +434,13 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
     d.bw_ang = 1. + w->mic_angle * -.25;      /* src/whirl.cpp:1380 */
     const float tau[4] = {w->horn_acc, w->horn_dec, w->drum_acc, w->drum_dec};
     for (int i = 0; i < 4; ++i) {
-        /* l = exp(-1.0 / (SR / n * tau)), src/whirl.cpp:1255-1257, :1306-1308 */
-        const double l = exp(-1.0 / (w->sample_rate / (double)(size_t)TBF_FRAGMENT * tau[i]));
-        d.one_minus_l[i] = 1 - l;
+        d.one_minus_l[i] = ramp_one_minus_l(w->sample_rate, tau[i]);
+        for (int v = 0; v < 128; ++v) {
+            /* setHornAcceleration ... setDrumDeceleration, src/whirl.cpp:895-917: the
+             * sum is a double, the field a float */
+            const float t = (float)(.01 + (double)v / (i < 2 ? 80.0 : 14.0));
+            d.ramp_one_minus_l[i][v] = ramp_one_minus_l(w->sample_rate, t);
+        }
     }
     for (int i = 0; i < 9; ++i) {
         d.rev_horn_target[i] = w->rev_horn_target[i];
@@ -581,6 +593,13 @@ static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
     s->rp.hornAcDc = w.init_horn_acdc;
     s->rp.drumAcDc = w.init_drum_acdc;
     s->rp.revSelect = w.init_rev_select;
+    memcpy(s->rp.iir[0], w.hafw, sizeof(float) * 5);
+    memcpy(s->rp.iir[1], w.hbfw, sizeof(float) * 5);
+    s->rp.brakePos[0] = w.hn_brake_pos;
+    s->rp.brakePos[1] = w.dr_brake_pos;
+    const float tau[4] = {w.horn_acc, w.horn_dec, w.drum_acc, w.drum_dec};
+    for (int i = 0; i < 4; ++i)
+        s->rp.oml[i] = ramp_one_minus_l(w.sample_rate, tau[i]);
     s->tg.tgTables = tgh;
     s->tg.whTables = whh;
 }
@@ -1188,6 +1207,9 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
     o->drum_acdc = s->rp.drumAcDc;
     memcpy(o->whirl_buf, s->wbuf, sizeof(o->whirl_buf));
     memcpy(o->iir_z[0], s->rp.iirz, sizeof(s->rp.iirz));
+    memcpy(o->horn_iir, s->rp.iir, sizeof(s->rp.iir));
+    memcpy(o->brake_pos, s->rp.brakePos, sizeof(s->rp.brakePos));
+    memcpy(o->ramp_one_minus_l, s->rp.oml, sizeof(s->rp.oml));
     memcpy(o->iir_z[2], s->dr.iirz, sizeof(s->dr.iirz));
     memcpy(o->filt_z, s->wl.z, sizeof(o->filt_z));
     memcpy(o->adx, s->wl.adx, sizeof(o->adx));

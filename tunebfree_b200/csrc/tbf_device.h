@@ -67,9 +67,12 @@ struct TgScalars {
 struct RampScalars {
     float percEnvGain, keyCompLevel;
     float iirz[2][2]; /* hafw hbfw : z0 z1 */
+    float iir[2][5];  /* hafw hbfw : a1 a2 b0 b1 b2; the table set's until TBF_EV_HORN_FILTER */
     int32_t hornAcDc, drumAcDc, revSelect;
     uint32_t errorFlags;
     double hornAngle, drumAngle, hornIncr, drumIncr, hornTarget, drumTarget;
+    double brakePos[2]; /* hnBrakePos drBrakePos; TBF_EV_WHIRL_BRAKE                     */
+    double oml[4];      /* DevWhirlTables::one_minus_l until TBF_EV_WHIRL_RAMP           */
 };
 
 /* ---- stage W: Leslie reflections, taps, delay lines ---- */
@@ -143,6 +146,9 @@ struct DevWhirlTables {
     double fw_ang, bw_ang;          /* micAngle*.25, 1 + micAngle*-.25  (whirl.cpp:1379-1380) */
     double one_minus_l[4];          /* 1 - exp(-1/(SR/128*tau)), tau = hornAcc hornDec drumAcc
                                        drumDec (whirl.cpp:1255, :1306), glibc exp on the host */
+    /* the same for every value a ramp controller can send: tau = (float)(.01 + v / 80.0)
+     * for the horn's two, (float)(.01 + v / 14.0) for the drum's (whirl.cpp:895-917)     */
+    double ramp_one_minus_l[4][128];
     double rev_horn_target[9], rev_drum_target[9];
     double hn_brake_pos, dr_brake_pos;
     int32_t horn_phase[6], drum_phase[6];

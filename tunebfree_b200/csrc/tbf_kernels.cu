@@ -371,7 +371,10 @@ __device__ void apply_scalar_event(TgScalars &sc, const DevTonegenTables *tg, co
         break;
     case TBF_EV_REV_OPTION:
     case TBF_EV_REV_SELECT:
-        break; /* rotor speed events belong to stage R */
+    case TBF_EV_WHIRL_BRAKE:
+    case TBF_EV_WHIRL_RAMP:
+    case TBF_EV_HORN_FILTER:
+        break; /* rotor and horn filter events belong to stage R */
     default:
         sc.errorFlags |= TBF_IFLAG_BAD_EVENT;
         break;
@@ -1232,8 +1235,8 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
     float cA[5], cB[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-        cA[k] = wh->iir[0][k];
-        cB[k] = wh->iir[1][k];
+        cA[k] = rp.iir[0][k];
+        cB[k] = rp.iir[1][k];
     }
     float zA0 = rp.iirz[0][0], zA1 = rp.iirz[0][1], zB0 = rp.iirz[1][0], zB1 = rp.iirz[1][1];
     float pg = rp.percEnvGain, kc = rp.keyCompLevel;
@@ -1270,6 +1273,31 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
                     rp.revSelect = a % 3;
                     use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
                 }
+            } else if (type == TBF_EV_WHIRL_BRAKE || type == TBF_EV_WHIRL_RAMP) {
+                const int b = evp->b;
+                if (a < 0 || a > (type == TBF_EV_WHIRL_BRAKE ? 1 : 3) || b < 0 || b > 127) {
+                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
+                } else if (type == TBF_EV_WHIRL_BRAKE) {
+                    /* w->hnBrakePos = (double)uc / 127.0, src/whirl.cpp:883-893 */
+                    rp.brakePos[a] = __ddiv_rn((double)b, 127.0);
+                } else {
+                    rp.oml[a] = wh->ramp_one_minus_l[a][b];
+                }
+            } else if (type == TBF_EV_HORN_FILTER) {
+                const int k = a & 7;
+                if (a < 0 || a > 15 || k > 4) {
+                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
+                } else {
+                    const float v = __int_as_float(evp->b);
+                    rp.iir[a >> 3][k] = v;
+#pragma unroll
+                    for (int j = 0; j < 5; ++j) {
+                        if (a == j)
+                            cA[j] = v;
+                        if (a == 8 + j)
+                            cB[j] = v;
+                    }
+                }
             }
             ++ev_cur;
         }
@@ -1286,10 +1314,10 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         int hbrake = 0, dbrake = 0;
         double hincr = rp.hornIncr, dincr = rp.drumIncr;
         if (whirl_run) {
-            hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, wh->hn_brake_pos,
-                                wh->one_minus_l[0], wh->one_minus_l[1]);
-            dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, wh->dr_brake_pos,
-                                wh->one_minus_l[2], wh->one_minus_l[3]);
+            hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
+                                rp.oml[0], rp.oml[1]);
+            dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
+                                rp.oml[2], rp.oml[3]);
         }
         /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
         const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;

@@ -11,6 +11,7 @@
  * descriptor that says which tbf_event(s) a controller value turns into.
  */
 #include "tbf_midi.h"
+#include "tbf_tables.h"
 
 #include <math.h>
 #include <stdio.h>
@@ -34,7 +35,10 @@ enum Kind {
     K_ROT_PRESET,   /*                           revControl, whirl.cpp:244               */
     K_ROT_TOGGLE,   /*                           setWhirlSustainPedal, whirl.cpp:252     */
     K_ROT_SELECT,   /*                           revControlAll, whirl.cpp:237            */
-    K_UNSUPPORTED,  /* registered, changes the path, no tbf_event                        */
+    K_HORN_FILTER,  /* arg = 4 * filter + {type, hz, q, gain}  setHornFilterAType ..., whirl.cpp:703-840 */
+    K_WHIRL_BRAKE,  /* arg = 0 horn, 1 drum      set{Horn,Drum}BrakePosition, whirl.cpp:883 */
+    K_WHIRL_RAMP,   /* arg = TBF_EV_WHIRL_RAMP's a  set{Horn,Drum}{Ac,De}celeration, :895   */
+    K_UNSUPPORTED,  /* named in ccFuncNames, never registered                             */
     K_OFF_PATH      /* registered, acts on preamp / reverb only                          */
 };
 
@@ -92,7 +96,7 @@ void build_fn_table()
     for (int i = 0; i < 8; ++i) {
         char n[32];
         snprintf(n, sizeof(n), "whirl.horn.filter.%s", hf[i]);
-        add_fn(n, K_UNSUPPORTED, 0, r_whirl + 3 + i);
+        add_fn(n, K_HORN_FILTER, i, r_whirl + 3 + i);
     }
     static const char *df[4] = {"type", "hz", "q", "gain"};
     for (int i = 0; i < 4; ++i) {
@@ -100,12 +104,12 @@ void build_fn_table()
         snprintf(n, sizeof(n), "whirl.drum.filter.%s", df[i]);
         add_fn(n, K_UNSUPPORTED, 0, 0); /* named, but no module registers them */
     }
-    add_fn("whirl.horn.brakepos", K_UNSUPPORTED, 0, r_whirl + 11);
-    add_fn("whirl.drum.brakepos", K_UNSUPPORTED, 0, r_whirl + 12);
-    add_fn("whirl.horn.acceleration", K_UNSUPPORTED, 0, r_whirl + 13);
-    add_fn("whirl.horn.deceleration", K_UNSUPPORTED, 0, r_whirl + 14);
-    add_fn("whirl.drum.acceleration", K_UNSUPPORTED, 0, r_whirl + 15);
-    add_fn("whirl.drum.deceleration", K_UNSUPPORTED, 0, r_whirl + 16);
+    add_fn("whirl.horn.brakepos", K_WHIRL_BRAKE, 0, r_whirl + 11);
+    add_fn("whirl.drum.brakepos", K_WHIRL_BRAKE, 1, r_whirl + 12);
+    add_fn("whirl.horn.acceleration", K_WHIRL_RAMP, 0, r_whirl + 13);
+    add_fn("whirl.horn.deceleration", K_WHIRL_RAMP, 1, r_whirl + 14);
+    add_fn("whirl.drum.acceleration", K_WHIRL_RAMP, 2, r_whirl + 15);
+    add_fn("whirl.drum.deceleration", K_WHIRL_RAMP, 3, r_whirl + 16);
     /* preamp registers xov.ctl_biased, _fb, _fb2, _gfb, sagtobias, character, enable,
      * inputgain, outputgain in that order (src/overdrive.cpp:588-598) */
     add_fn("overdrive.enable", K_OFF_PATH, 0, r + 6);
@@ -557,12 +561,25 @@ int tbf_midi_map_finish(tbf_midi_map *m, const int32_t revselects[3])
     return TBF_OK;
 }
 
-void tbf_midi_state_init(tbf_midi_state *s, const tbf_midi_map *m, int32_t init_rev_select)
+void tbf_midi_state_init(tbf_midi_state *s, const tbf_midi_map *m, const tbf_whirl_tables *w)
 {
     if (!s)
         return;
     memset(s, 0, sizeof(*s));
-    s->rev_select = init_rev_select % 3;
+    if (w) {
+        s->rev_select = w->init_rev_select % 3;
+        memcpy(s->horn_filter[0], w->ha_param, sizeof(w->ha_param));
+        memcpy(s->horn_filter[1], w->hb_param, sizeof(w->hb_param));
+        s->sample_rate = w->sample_rate;
+    } else {
+        tbf_whirl_spec d;
+        tbf_whirl_spec_default(&d, 48000.0);
+        const float a[4] = {(float)d.ha_type, d.ha_f, d.ha_q, d.ha_g};
+        const float b[4] = {(float)d.hb_type, d.hb_f, d.hb_q, d.hb_g};
+        memcpy(s->horn_filter[0], a, sizeof a);
+        memcpy(s->horn_filter[1], b, sizeof b);
+        s->sample_rate = 48000.0;
+    }
     if (m) {
         s->transpose = m->transpose;
         s->nsh_a = m->nsh_a;
@@ -707,6 +724,41 @@ int tbf_midi_compile(const tbf_midi_map *m, tbf_midi_state *s, uint32_t instance
             EMIT(TBF_EV_REV_OPTION, opt, 0);
             s->rev_select = rev_select_of_option(opt);
         }
+        break;
+    case K_HORN_FILTER: {
+        /* setHornFilterAType ... setHornFilterBGain (src/whirl.cpp:703-840): the value in
+         * double, the field a float, then UPDATE_x_FILTER = setIIRFilter on all four */
+        float *q = s->horn_filter[fn.arg >> 2];
+        const double u = (double)val;
+        switch (fn.arg & 3) {
+        case 0:
+            q[0] = (float)(int)(val / 15);
+            break;
+        case 1:
+            q[1] = (float)(250.0 + ((8000.0 - 250.0) * ((u * u) / 16129.0)));
+            break;
+        case 2:
+            q[2] = (float)(0.01 + ((6.00 - 0.01) * (u / 127.0)));
+            break;
+        default:
+            q[3] = (float)(-48.0 + ((48.0 - -48.0) * (u / 127.0)));
+            break;
+        }
+        float c5[5];
+        if (tbf_iir_coefficients(c5, (int)q[0], q[1], q[2], q[3], s->sample_rate) == 1) {
+            for (int k = 0; k < 5; ++k) {
+                int32_t bits;
+                memcpy(&bits, &c5[k], sizeof bits);
+                EMIT(TBF_EV_HORN_FILTER, 8 * (fn.arg >> 2) + k, bits);
+            }
+        } /* else: out of setIIRFilter's range, the old coefficients stay */
+        break;
+    }
+    case K_WHIRL_BRAKE:
+        EMIT(TBF_EV_WHIRL_BRAKE, fn.arg, val);
+        break;
+    case K_WHIRL_RAMP:
+        EMIT(TBF_EV_WHIRL_RAMP, fn.arg, val);
         break;
     case K_UNSUPPORTED:
         s->n_unsupported++;

@@ -1056,16 +1056,16 @@ void eq_compute(int type, double hz, double Q, double dbG, double rate, double *
 
 /* setIIRFilter, src/whirl.cpp:147-172: out-of-range parameters leave the
  * (zeroed) coefficients untouched -- whirl-sharp.cfg relies on it */
-void set_iir(float *c5, int type, double F, double Q, double G, double rate)
+bool set_iir(float *c5, int type, double F, double Q, double G, double rate)
 {
     if (Q <= 0.1 || Q >= 6.00)
-        return;
+        return false;
     if (F / rate <= 0.0002 || F / rate >= 0.4998)
-        return;
+        return false;
     if (G <= -48.0 || G >= 48.0)
-        return;
+        return false;
     if (type < 0 || type > 8)
-        return;
+        return false;
     double a1, a2, b0, b1, b2;
     eq_compute(type, F, Q, G, rate, &a1, &a2, &b0, &b1, &b2);
     c5[0] = (float)a1;
@@ -1073,6 +1073,7 @@ void set_iir(float *c5, int type, double F, double Q, double G, double rate)
     c5[2] = (float)b0;
     c5[3] = (float)b1;
     c5[4] = (float)b2;
+    return true;
 }
 
 /* Angle-dependent horn impulse response: five coefficient curves over
@@ -1135,6 +1136,14 @@ void draw_curve(float *bfw, int partial, const Pt *pts, int n)
 
 } // namespace
 
+extern "C" int tbf_iir_coefficients(float c5[5], int type, double hz, double q, double gain_db,
+                                    double sample_rate)
+{
+    if (!c5)
+        return TBF_ERR_ARG;
+    return set_iir(c5, type, hz, q, gain_db, sample_rate) ? 1 : 0;
+}
+
 extern "C" int tbf_build_whirl_tables(const tbf_whirl_spec *s, tbf_whirl_tables *o)
 {
     if (!s || !o || !(s->sample_rate > 0))
@@ -1161,6 +1170,10 @@ extern "C" int tbf_build_whirl_tables(const tbf_whirl_spec *s, tbf_whirl_tables 
     set_iir(o->drfR, s->lp_type, s->lp_f, s->lp_q, s->lp_g, rate);
     set_iir(o->hafw, s->ha_type, s->ha_f, s->ha_q, s->ha_g, rate);
     set_iir(o->hbfw, s->hb_type, s->hb_f, s->hb_q, s->hb_g, rate);
+    const float hap[4] = {(float)s->ha_type, s->ha_f, s->ha_q, s->ha_g};
+    const float hbp[4] = {(float)s->hb_type, s->hb_f, s->hb_q, s->hb_g};
+    memcpy(o->ha_param, hap, sizeof hap);
+    memcpy(o->hb_param, hbp, sizeof hbp);
 
     /* computeOffsets(), src/whirl.cpp:534-624 */
     const float hs0[6] = {12.0, 18.0, 53.0, 50.0, 106.0, 116.0};

@@ -64,6 +64,8 @@ class MidiState(C.Structure):
         ("transpose", C.c_int32), ("nsh_a", C.c_int32), ("nsh_a_u", C.c_int32),
         ("nsh_a_pl", C.c_int32), ("nsh_a_ul", C.c_int32), ("nsh_b", C.c_int32),
         ("nsh_c", C.c_int32), ("split_a_pl", C.c_int32), ("split_a_ul", C.c_int32),
+        ("horn_filter", (C.c_float * 4) * 2),
+        ("sample_rate", C.c_double),
         ("n_ignored", C.c_uint32),
         ("n_unsupported", C.c_uint32),
         ("n_unmapped", C.c_uint32),
@@ -83,7 +85,8 @@ def _lib():
         L.tbf_midi_map_split.argtypes = [C.POINTER(_Map)] + [C.c_int] * 6
         L.tbf_midi_map_split.restype = None
         L.tbf_midi_map_finish.argtypes = [C.POINTER(_Map), C.POINTER(C.c_int32)]
-        L.tbf_midi_state_init.argtypes = [C.POINTER(MidiState), C.POINTER(_Map), C.c_int32]
+        L.tbf_midi_state_init.argtypes = [C.POINTER(MidiState), C.POINTER(_Map),
+                                          C.POINTER(cabi.WhirlTables)]
         L.tbf_midi_state_init.restype = None
         L.tbf_midi_key.argtypes = [C.POINTER(_Map), C.POINTER(MidiState), C.c_int, C.c_int]
         L.tbf_programmes_init.argtypes = [C.POINTER(ProgrammeTable)]
@@ -146,19 +149,21 @@ class MidiMap:
         f = int(self.c.cc_fn[channel][controller])
         return None if f < 0 else _lib().tbf_midi_function_name(f).decode()
 
-    def new_state(self, init_rev_select=0):
+    def new_state(self, whirl_tables=None):
+        """State of a fresh instance of `whirl_tables` (cabi.WhirlTables; None = the defaults)."""
         st = MidiState()
-        _lib().tbf_midi_state_init(C.byref(st), C.byref(self.c), init_rev_select)
+        wt = C.byref(whirl_tables) if whirl_tables is not None else None
+        _lib().tbf_midi_state_init(C.byref(st), C.byref(self.c), wt)
         return st
 
     def key_now(self, state, channel, note):
         """Engine key under the instance's CURRENT mapping (programmes may have moved it)."""
         return _lib().tbf_midi_key(C.byref(self.c), C.byref(state), channel, note)
 
-    def compile(self, messages, instance=0, init_rev_select=0, state=None):
+    def compile(self, messages, instance=0, whirl_tables=None, state=None):
         """messages: iterable of (fragment, bytes) sorted by fragment -> (events, MidiState)."""
         L = _lib()
-        st = state if state is not None else self.new_state(init_rev_select)
+        st = state if state is not None else self.new_state(whirl_tables)
         buf = (cabi.Event * MAX_KEYS)()
         out = []
         for fragment, raw in messages:

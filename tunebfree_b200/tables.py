@@ -37,6 +37,7 @@ def _lib():
         L.tbf_free_whirl_tables.restype = None
         L.tbf_extend_frequencies.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double),
                                              C.POINTER(C.c_int), C.POINTER(C.c_float)]
+        L.tbf_iir_coefficients.argtypes = [C.POINTER(C.c_float), C.c_int] + [C.c_double] * 4
         L.tbf_srand.argtypes = [C.c_void_p, C.c_uint32]
         L.tbf_srand.restype = None
         L.tbf_rand.argtypes = [C.c_void_p]
@@ -67,6 +68,16 @@ def extend_frequencies(freqs128):
     per = C.c_float(0)
     _lib().tbf_extend_frequencies(f, out, C.byref(ss), C.byref(per))
     return np.array(out, dtype=np.float64), ss.value, per.value
+
+
+def iir_coefficients(type_, hz, q, gain_db, rate=48000.0):
+    """setIIRFilter / eqCompute (src/whirl.cpp:147-172): [a1, a2, b0, b1, b2] as float32, or
+    None when the reference would keep its previous coefficients (parameter out of range)."""
+    c5 = (C.c_float * 5)()
+    rc = _lib().tbf_iir_coefficients(c5, int(type_), hz, q, gain_db, rate)
+    if rc < 0:
+        raise ValueError("tbf_iir_coefficients failed (%d)" % rc)
+    return list(c5) if rc == 1 else None
 
 
 def parse_cfg_lines(text):
