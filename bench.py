@@ -43,6 +43,9 @@ WORKLOAD_NAME = {
        "percussion + key click, whirl bypassed",
     3: "config3: tonegen + vibrato C3 + Leslie fast (whirlProc3), drawbars 888888888, 10-note "
        "chords re-struck every 0.5 s, percussion + key click",
+    5: "config5: config 3's chain and chords over the Cartesian mix of the reference's 10 osc "
+       "cfg variants x 3 whirl cfg variants x 16 engine seeds (80 wave-table sets), organs "
+       "grouped by table set",
 }
 
 
@@ -52,11 +55,14 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", type=int, default=3, choices=[2, 3])
+    ap.add_argument("--config", type=int, default=3, choices=[2, 3, 5])
     ap.add_argument("--instances", type=int, default=0, help="instances per GPU")
     ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per instance per step")
     ap.add_argument("--cpu-sample-seconds", type=float, default=15.0,
                     help="target CPU time of the bounded cpu_baseline sample")
+    ap.add_argument("--ref-build", default="strict", choices=["strict", "stock"],
+                    help="--impl reference: the engine built strict IEEE (the parity oracle) or with "
+                         "the project's stock -O3 -ffast-math flags (timing only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -72,7 +78,10 @@ def _cpu_worker(args):
     from tunebfree_b200 import workloads
     # a few engine instances per worker, cycled: the render cost does not depend on which
     # organ plays which script, and 3 MB per reference instance adds up on many-core hosts
-    engines = [ref_engine.RefInstance(seed=1 + i % N_TABLE_SETS) for i in ids[:4]]
+    engines = []
+    for i in ids[:4]:
+        osc, whirl, seed = workloads.organ_variant(i, config)
+        engines.append(ref_engine.RefInstance(seed=seed, cfg=workloads.variant_cfg(osc, whirl)))
     insts = []
     for j, i in enumerate(ids):
         ev = workloads.instance_events(i, n_frag, config)
@@ -121,6 +130,8 @@ def run_reference_arm(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # the CPU engine has no use for more ranks: rank 0 alone measures
+    if a.ref_build == "stock":
+        os.environ["TBF_REF_BUILD"] = "stock"
     from oracle import ref_engine
     ref_engine.lib()
     cores = os.cpu_count() or 1
@@ -135,8 +146,10 @@ def run_reference_arm(a):
         vals.append(v)
         t_all += dt
     value = float(np.mean(vals))
-    sample = "%d instances x %.1f s (%d per core) per step, oracle/_ref = reference engine, strict IEEE -O2" % (
-        cores * per_core, a.seconds, per_core)
+    sample = "%d instances x %.1f s (%d per core) per step, oracle/_ref = reference engine, %s" % (
+        cores * per_core, a.seconds, per_core,
+        "stock flags -O3 -ffast-math (not bit-exact with the oracle)" if a.ref_build == "stock"
+        else "strict IEEE -O2")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * t_all / max(1, a.steps),
@@ -272,21 +285,30 @@ def run_gpu_arm(a):
     from tunebfree_b200 import sharding
     # every rank plays different organs; slot i plays global organ first_global + i with
     # table set (global id) mod 16
-    first_global, per_set = sharding.shard_plan(rank, world, n_inst, N_TABLE_SETS)
+    variant = lambda g: workloads.organ_variant(g, a.config)
+    if a.config == 5:
+        global_ids, groups = sharding.shard_plan_grouped(rank, world, n_inst, variant)
+    else:
+        first_global, per_set = sharding.shard_plan(rank, world, n_inst, N_TABLE_SETS)
+        global_ids = first_global + np.arange(n_inst, dtype=np.int64)
+        groups = {variant(first_global + slots[0]): slots for slots in per_set if slots}
 
     ctx = engine.Context(local_rank)
-    # 16 table sets (seeds 1..16) built by the product's own host-side builder
-    handles = []
-    wh_handle = None
-    for s in range(N_TABLE_SETS):
-        spec = tables.InstanceSpec(seed=1 + s)
-        tt, wt = spec.build()
-        handles.append(ctx.tonegen_tables(tt))
-        if wh_handle is None:
-            wh_handle = ctx.whirl_tables(wt)
-        tables.free_tables(tt, wt)
-    ids = sharding.slot_instance_ids(per_set, lambda s, count: ctx.create_instances(handles[s], wh_handle, count))
-    ev_np = workloads.batch_events_numpy(first_global, n_inst, n_frag, a.config)
+    # table sets built by the product's own host-side builder: wave tables per (osc variant,
+    # engine seed), Leslie tables per whirl variant
+    tg_handles, wh_handles = {}, {}
+    for osc, whirl, seed in groups:
+        if (osc, seed) not in tg_handles or whirl not in wh_handles:
+            spec = tables.InstanceSpec(seed=seed, cfg=workloads.variant_cfg(osc, whirl))
+            tt, wt = spec.build()
+            if (osc, seed) not in tg_handles:
+                tg_handles[(osc, seed)] = ctx.tonegen_tables(tt)
+            if whirl not in wh_handles:
+                wh_handles[whirl] = ctx.whirl_tables(wt)
+            tables.free_tables(tt, wt)
+    ids = sharding.slot_instance_ids(
+        groups, lambda k, count: ctx.create_instances(tg_handles[(k[0], k[2])], wh_handles[k[1]], count))
+    ev_np = workloads.batch_events_numpy(0, n_inst, n_frag, a.config, global_ids=global_ids)
     events = engine.events_from_numpy(ev_np)
     h2d_bytes = int(ev_np.shape[0] * 20 + n_inst * 4 + (n_inst + 1) * 8)
 
@@ -447,7 +469,8 @@ def run_gpu_arm(a):
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_NAME[a.config], "instances_per_gpu": n_inst,
                        "seconds_per_instance": a.seconds, "sample_rate": 48000,
-                       "table_sets": N_TABLE_SETS, "tuning": "12-TET",
+                       "table_sets": len(tg_handles), "whirl_table_sets": len(wh_handles),
+                       "tuning": "12-TET",
                        "l2": "inputs larger than L2 (instance state %.0f MB + %.1f GB of output per step)"
                              % (n_inst * 0.08, 2 * n_inst * frames * 4 / 1e9),
                        "parallelism": "instances sharded over %d GPU(s), no collective" % world},

@@ -14,7 +14,10 @@ import numpy as np
 from tunebfree_b200 import cabi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_ref", "libtbf_ref.so")
+# TBF_REF_BUILD=stock: the engine compiled with the project's own -O3 -ffast-math flags, for
+# bench.py's second timed CPU row only -- its output is NOT the parity oracle's
+LIB_PATH = os.path.join(_HERE, "_ref", "libtbf_ref_stock.so" if os.environ.get("TBF_REF_BUILD") == "stock"
+                        else "libtbf_ref.so")
 _lib = None
 
 

@@ -46,3 +46,44 @@ def test_config3_4096_organs(ref, gpu_ctx):
 def test_config2_1024_organs(ref, gpu_ctx):
     """1024 organs x 2 s, tone generator only."""
     _run(ref, gpu_ctx, 1024, 750, 2, sampled=(0, 5, 511, 1023))
+
+
+def test_config5_cfg_mix_16384_organs(ref, gpu_ctx):
+    """BASELINE config 5 at its full instance count, 0.25 s: every pair of the reference's 10 osc x
+    3 whirl cfg variants with 16 engine seeds (80 wave-table sets, 3 Leslie table sets, tables from
+    the product's own builder), organs grouped by table set.  One organ of each of the 30 pairs
+    and a few others are rendered by the oracle -- its own cfg parser fed the same text -- and
+    compared through the device checksum."""
+    from tunebfree_b200 import sharding, tables
+    n, n_frag = 16384, 94
+    variant = lambda g: workloads.organ_variant(g, 5)
+    gids, groups = sharding.shard_plan_grouped(0, 1, n, variant)
+    assert len(groups) == 240 and sorted(gids.tolist()) == list(range(n))
+    tgh, whh = {}, {}
+    for osc, whirl, seed in groups:
+        if (osc, seed) not in tgh or whirl not in whh:
+            spec = tables.InstanceSpec(seed=seed, cfg=workloads.variant_cfg(osc, whirl))
+            tt, wt = spec.build()
+            assert spec.rejected == []
+            if (osc, seed) not in tgh:
+                tgh[(osc, seed)] = gpu_ctx.tonegen_tables(tt)
+            if whirl not in whh:
+                whh[whirl] = gpu_ctx.whirl_tables(wt)
+            tables.free_tables(tt, wt)
+    assert len(tgh) == 80 and len(whh) == 3
+    ids = sharding.slot_instance_ids(
+        groups, lambda k, count: gpu_ctx.create_instances(tgh[(k[0], k[2])], whh[k[1]], count))
+    ev = engine.events_from_numpy(workloads.batch_events_numpy(0, n, n_frag, 5, global_ids=gids))
+    flags = workloads.render_flags(5)
+    cs = np.zeros(n, dtype=np.uint64)
+    gpu_ctx.render_device(n, n_frag, ev, flags, None, None, n_frag * 128, ids=ids, checksums=cs)
+    slot_of = {int(g): s for s, g in enumerate(gids)}
+    for g in list(range(30)) + [77, 4099, 9001, 16383]:
+        osc, whirl, seed = variant(g)
+        r = ref.RefInstance(seed=seed, cfg=workloads.variant_cfg(osc, whirl))
+        l, rr = r.render(n_frag, flags, workloads.instance_events(g, n_frag, 5))
+        r.close()
+        assert np.abs(l).max() > 0.01
+        assert engine.checksum_host(l, rr) == int(cs[slot_of[g]]), (g, osc, whirl, seed)
+    for s in (0, n // 3, n - 1):
+        assert gpu_ctx.export_state(int(ids[s])).error_flags == 0

@@ -77,3 +77,28 @@ def test_shard_plan_matches_single_process_generation():
         assert all((first + s) % 16 == k for k, slots in enumerate(per_set) for s in slots)
     with pytest.raises(ValueError):
         sharding.shard_plan(2, 2, 4, 16)
+
+
+def test_grouped_plan_sorts_by_table_key_and_partitions_every_organ():
+    """shard_plan_grouped: organs sharing a table key are neighbours, each GPU gets one block of
+    the sorted list, every organ is played exactly once."""
+    from tunebfree_b200 import sharding, workloads
+    key = lambda g: workloads.organ_variant(g, 5)
+    seen = []
+    for rank in range(2):
+        gids, groups = sharding.shard_plan_grouped(rank, 2, 480, key)
+        assert len(gids) == 480 and sum(len(v) for v in groups.values()) == 480
+        keys = [key(int(g)) for g in gids]
+        assert keys == sorted(keys)
+        for k, slots in groups.items():
+            assert slots == list(range(slots[0], slots[0] + len(slots)))
+            assert all(key(int(gids[s])) == k for s in slots)
+        ids = sharding.slot_instance_ids(groups, lambda k, count: 1000 * len(seen) + 0)
+        assert len(ids) == 480
+        seen += gids.tolist()
+    assert sorted(seen) == list(range(960))
+    # all 240 (osc, whirl, seed) triples occur, 30 cfg pairs x 16 seeds reached through lcm(30, 16)
+    assert len({key(g) for g in range(960)}) == 240
+    assert workloads.organ_variant(7, 3) == ("default", "default", 8)
+    with pytest.raises(ValueError):
+        sharding.shard_plan_grouped(3, 2, 4, key)

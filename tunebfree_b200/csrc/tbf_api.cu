@@ -39,6 +39,7 @@ struct StageScratch {
 };
 
 #define TBF_MAX_GROUPS 4
+#define TBF_MAX_STAGE_BUFS 4
 #define TBF_SCAT_BLOCK 32 /* samples the kernels scatter before they read (tbf_kernels.cu BLK) */
 
 struct tbf_ctx {
@@ -79,9 +80,10 @@ struct tbf_ctx {
     /* ... and every stage of a group has its own stream: stage s of chunk c overlaps stage
      * s-1 of chunk c+1 (the stage streams between them are double-buffered by chunk parity) */
     cudaStream_t sstream[TBF_MAX_GROUPS][4] = {};
-    cudaEvent_t sdone[TBF_MAX_GROUPS][4][2] = {}; /* [group][stage][chunk parity] */
+    cudaEvent_t sdone[TBF_MAX_GROUPS][4][TBF_MAX_STAGE_BUFS] = {}; /* [group][stage][chunk % n_bufs] */
+    int n_bufs = 3; /* copies of the stage streams in flight, 2..TBF_MAX_STAGE_BUFS (TBF_STAGE_BUFS) */
     cudaEvent_t fork = nullptr;
-    size_t scratch_budget = (size_t)4 << 30; /* bytes of HBM the stage streams may take */
+    size_t scratch_budget = (size_t)8 << 30; /* bytes of HBM the stage streams may take */
     uint32_t max_stage_chunk = 32;           /* fragments per stage-kernel launch       */
     int n_groups_max = 1; /* measured best from 512 to 8192 organs once stage T and W of
                              consecutive chunks overlap on the stage streams; TBF_GROUPS raises it */
@@ -89,6 +91,7 @@ struct tbf_ctx {
     int launches = 0;
     /* stage profiling: every stage kernel serialised on the main stream between two events */
     bool profile_stages = false;
+    bool timeline = false;                        /* TBF_TIMELINE=1: see tbf_gpu_synchronize() */
     std::vector<cudaEvent_t> prof_events;        /* pool, pairs */
     std::vector<int> prof_stage;                  /* stage of pair i of the last launch */
     float stage_ms[4] = {0, 0, 0, 0};
@@ -154,11 +157,12 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g)
-        for (int st = 0; st < 4 && ok; ++st)
+        for (int st = 0; st < 4 && ok; ++st) {
             ok = cudaStreamCreateWithPriority(&ctx->sstream[g][st], cudaStreamNonBlocking,
-                                              (st & 1) ? prio_hi : prio_lo) == cudaSuccess &&
-                 cudaEventCreateWithFlags(&ctx->sdone[g][st][0], cudaEventDisableTiming) == cudaSuccess &&
-                 cudaEventCreateWithFlags(&ctx->sdone[g][st][1], cudaEventDisableTiming) == cudaSuccess;
+                                              (st & 1) ? prio_hi : prio_lo) == cudaSuccess;
+            for (int b = 0; ok && b < TBF_MAX_STAGE_BUFS; ++b)
+                ok = cudaEventCreateWithFlags(&ctx->sdone[g][st][b], cudaEventDisableTiming) == cudaSuccess;
+        }
     if (!ok) {
         delete ctx;
         return TBF_ERR_CUDA;
@@ -166,6 +170,8 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     /* tuning knobs (bench sweeps): instance groups and fragments per stage launch */
     if (const char *e = getenv("TBF_GROUPS"))
         ctx->n_groups_max = std::max(1, std::min(TBF_MAX_GROUPS, atoi(e)));
+    if (const char *e = getenv("TBF_STAGE_BUFS"))
+        ctx->n_bufs = std::max(2, std::min(TBF_MAX_STAGE_BUFS, atoi(e)));
     if (const char *e = getenv("TBF_STAGE_CHUNK"))
         ctx->max_stage_chunk = (uint32_t)std::max(1, std::min(256, atoi(e)));
     *out = ctx;
@@ -213,7 +219,7 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
         for (int st = 0; st < 4; ++st) {
             if (ctx->sstream[g][st])
                 cudaStreamDestroy(ctx->sstream[g][st]);
-            for (int par = 0; par < 2; ++par)
+            for (int par = 0; par < TBF_MAX_STAGE_BUFS; ++par)
                 if (ctx->sdone[g][st][par])
                     cudaEventDestroy(ctx->sdone[g][st][par]);
         }
@@ -830,21 +836,24 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     if (d->checksums)
         CK(cudaMemsetAsync(ctx->d_csum, 0, sizeof(uint64_t) * n, ctx->stream));
 
-    /* stage streams, double-buffered by chunk parity: as many fragments per stage launch
-     * as the scratch budget allows */
+    /* stage streams, n_bufs copies in rotation (chunk c uses copy c % n_bufs): as many
+     * fragments per stage launch as the scratch budget allows.  With two copies the buffer
+     * hand-backs close a cycle R(c) -> W(c) -> D(c) -> R(c + 2) that bounds the period of a
+     * chunk by (R + W + D) / 2; the third copy breaks it */
+    const size_t nb = (size_t)ctx->n_bufs;
     uint32_t sc_frag = (uint32_t)std::min<size_t>(
         ctx->max_stage_chunk,
-        std::max<size_t>(1, ctx->scratch_budget / (2 * n * stream_bytes_per_fragment(whirl))));
+        std::max<size_t>(1, ctx->scratch_budget / (nb * n * stream_bytes_per_fragment(whirl))));
     sc_frag = std::min(sc_frag, chunk);
     const size_t pitch = (size_t)sc_frag * TBF_FRAGMENT;
     const size_t planes32 = whirl ? 8 : 2;
     StageScratch &ss = ctx->scratch;
     {
-        cudaError_t e = grow(&ss.ctl, &ss.cap_ctl, 2 * n * sc_frag);
+        cudaError_t e = grow(&ss.ctl, &ss.cap_ctl, nb * n * sc_frag);
         if (e == cudaSuccess)
-            e = grow(&ss.f32, &ss.cap_f32, 2 * n * pitch * planes32);
+            e = grow(&ss.f32, &ss.cap_f32, nb * n * pitch * planes32);
         if (e == cudaSuccess && whirl)
-            e = grow(&ss.f64, &ss.cap_f64, 2 * n * pitch * 2);
+            e = grow(&ss.f64, &ss.cap_f64, nb * n * pitch * 2);
         if (e != cudaSuccess) {
             cudaGetLastError();
             ctx->err = "render: stage stream buffers do not fit";
@@ -882,8 +891,9 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     const size_t half = (size_t)2 * n * chunk * TBF_FRAGMENT;
     uint32_t cidx[TBF_MAX_GROUPS] = {0, 0, 0, 0}; /* stage chunks launched per group */
     ctx->prof_stage.clear();
-    auto prof_mark = [&](int stage, bool begin) -> cudaError_t {
-        if (!ctx->profile_stages)
+    ctx->timeline = !ctx->profile_stages && getenv("TBF_TIMELINE") != nullptr;
+    auto prof_mark = [&](int stage, bool begin, cudaStream_t on) -> cudaError_t {
+        if (!ctx->profile_stages && !ctx->timeline)
             return cudaSuccess;
         const size_t idx = 2 * ctx->prof_stage.size() + (begin ? 0 : 1);
         while (ctx->prof_events.size() <= idx) {
@@ -893,7 +903,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                 return rc;
             ctx->prof_events.push_back(e);
         }
-        cudaError_t rc = cudaEventRecord(ctx->prof_events[idx], ctx->stream);
+        cudaError_t rc = cudaEventRecord(ctx->prof_events[idx], on);
         if (!begin)
             ctx->prof_stage.push_back(stage);
         return rc;
@@ -935,7 +945,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             int par = 0;
             for (uint32_t ib = 0; ib < nf; ib += sc_frag) {
                 const uint32_t c = cidx[g]++;
-                par = (int)(c & 1u);
+                par = (int)(c % (uint32_t)nb);
                 float *f32 = ss.f32 + (size_t)par * n * pitch * planes32;
                 p.ctl = ss.ctl + ((size_t)par * n + s0) * sc_frag;
                 p.u = f32 + s0 * pitch;
@@ -953,9 +963,9 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                 p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
                 p.out_l = out_l ? out_l + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
                 p.out_r = out_r ? out_r + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
-                cudaEvent_t(*ev)[2] = ctx->sdone[g];
+                cudaEvent_t(*ev)[TBF_MAX_STAGE_BUFS] = ctx->sdone[g];
                 /* a stage waits for its producer of this chunk and, before it overwrites
-                 * the streams of parity `par`, for their consumers of chunk c - 2 */
+                 * copy `par` of the streams, for their consumers of chunk c - n_bufs */
                 int rc = 0;
                 if (whirl_input) {
                     /* the caller's mono input takes the place of stage T's output plane (stage R
@@ -965,39 +975,39 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                                          sizeof(float) * p.n_fragments * TBF_FRAGMENT, ng,
                                          cudaMemcpyDefault, st[1]));
                 } else {
-                    if (c >= 2)
+                    if (c >= nb)
                         CK(cudaStreamWaitEvent(st[0], ev[1][par], 0));
-                    CK(prof_mark(0, true));
+                    CK(prof_mark(0, true, st[0]));
                     rc = tbf_launch_stage_t(p, st[0]);
-                    CK(prof_mark(0, false));
+                    CK(prof_mark(0, false, st[0]));
                     CK(cudaEventRecord(ev[0][par], st[0]));
                 }
                 if (rc == 0) {
                     if (!whirl_input)
                         CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
-                    if (whirl && c >= 2) {
+                    if (whirl && c >= nb) {
                         CK(cudaStreamWaitEvent(st[1], ev[2][par], 0));
                         CK(cudaStreamWaitEvent(st[1], ev[3][par], 0));
                     }
-                    CK(prof_mark(1, true));
+                    CK(prof_mark(1, true, st[1]));
                     rc = tbf_launch_stage_r(p, st[1]);
-                    CK(prof_mark(1, false));
+                    CK(prof_mark(1, false, st[1]));
                     CK(cudaEventRecord(ev[1][par], st[1]));
                 }
                 if (rc == 0 && whirl) {
                     CK(cudaStreamWaitEvent(st[2], ev[1][par], 0));
-                    if (c >= 2)
+                    if (c >= nb)
                         CK(cudaStreamWaitEvent(st[2], ev[3][par], 0));
-                    CK(prof_mark(2, true));
+                    CK(prof_mark(2, true, st[2]));
                     rc = tbf_launch_stage_w(p, ring, st[2]);
-                    CK(prof_mark(2, false));
+                    CK(prof_mark(2, false, st[2]));
                     CK(cudaEventRecord(ev[2][par], st[2]));
                 }
                 if (rc == 0 && whirl) {
                     CK(cudaStreamWaitEvent(st[3], ev[2][par], 0));
-                    CK(prof_mark(3, true));
+                    CK(prof_mark(3, true, st[3]));
                     rc = tbf_launch_stage_d(p, st[3]);
-                    CK(prof_mark(3, false));
+                    CK(prof_mark(3, false, st[3]));
                     CK(cudaEventRecord(ev[3][par], st[3]));
                 }
                 if (rc != 0) {
@@ -1020,7 +1030,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     }
     for (int g = 0; g < n_groups; ++g)
         if (cidx[g])
-            CK(cudaStreamWaitEvent(ctx->stream, ctx->sdone[g][last][(cidx[g] - 1) & 1u], 0));
+            CK(cudaStreamWaitEvent(ctx->stream, ctx->sdone[g][last][(cidx[g] - 1) % (uint32_t)nb], 0));
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
     if (d->checksums)
         CK(cudaMemcpyAsync(d->checksums, ctx->d_csum, sizeof(uint64_t) * n,
@@ -1045,6 +1055,19 @@ int tbf_gpu_synchronize(tbf_ctx *ctx)
     ctx->in_flight = false;
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaStreamSynchronize(ctx->copy_stream));
+    /* debugging aid, TBF_TIMELINE=1: when each stage launch of the overlapped schedule became
+     * ready (its stream reached it: producers done) and when it finished, ms after the batch
+     * started, one line per launch on stderr */
+    if (ctx->timeline) {
+        for (size_t i = 0; i < ctx->prof_stage.size(); ++i) {
+            float t0 = 0.f, t1 = 0.f;
+            CK(cudaEventElapsedTime(&t0, ctx->ev0, ctx->prof_events[2 * i]));
+            CK(cudaEventElapsedTime(&t1, ctx->ev0, ctx->prof_events[2 * i + 1]));
+            fprintf(stderr, "tbf_timeline %c %zu ready %.3f done %.3f\n", "TRWD"[ctx->prof_stage[i]], i,
+                    t0, t1);
+        }
+        ctx->prof_stage.clear();
+    }
     for (size_t i = 0; i < ctx->prof_stage.size(); ++i) {
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, ctx->prof_events[2 * i], ctx->prof_events[2 * i + 1]));

@@ -1191,7 +1191,9 @@ struct RSmem {
                                           filled by cp.async one block ahead of its use   */
     float tout[2][BLK * TILE_PITCH];  /* dx0 | mono, hx0                                 */
     double tang[2][BLK * TILE_PITCH]; /* horn, drum angle                                */
-    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums  */
+    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums.  LAST:
+                                          launched without it unless stage R forms the checksum,
+                                          so that the CTA takes one stage T / W slot, not two */
 };
 
 /* request one 32 x 32 block of u and php: element (row r, sample lane) by cp.async */
@@ -1205,11 +1207,18 @@ __device__ __forceinline__ void r_tile_fetch(const RenderParams &p, float (*tile
     }
 }
 
-__global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
+/* Two warps per 32 organs, lane = organ in both.  The rotor angles do not depend on the audio,
+ * so the warps never meet: role 0 mixes down, runs the horn biquads and writes dx0 / hx0 (or
+ * L, R when the Leslie is bypassed); role 1 applies the rotor events, ramps the speeds and writes
+ * the two angle streams.  Stage R is one serial chain per organ and sits on the critical path of
+ * the stage schedule while it shares its SM with 20 stage T / W warps: halving what one warp has
+ * to issue shortens that chain. */
+__global__ void __launch_bounds__(64) tbf_stage_r(const RenderParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RSmem &sm = *reinterpret_cast<RSmem *>(smem_raw);
-    const int lane = threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool rotors = (threadIdx.x >> 5) != 0; /* warp-uniform role */
     const uint32_t slot0 = blockIdx.x * 32;
     const uint32_t slot = slot0 + lane;
     const bool valid = slot < p.n_instances;
@@ -1219,6 +1228,8 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
     /* Leslie only: plane u holds the caller's mono input (whirlProc's inbuffer) and the
      * tone generator's mixdown state (percussion gain, key compression) stays as it is */
     const bool ext_in = (p.flags & TBF_RENDER_WHIRL_INPUT) != 0;
+    if (rotors && whirl_off)
+        return;
 
     InstState *st = nullptr;
     const DevWhirlTables *wh = p.wh;
@@ -1232,6 +1243,119 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         rp = RampScalars();
     }
     const bool whirl_run = valid && !whirl_off && !wh->bypass;
+    uint32_t new_flags = 0;
+    uint64_t ev_cur = 0, ev_end = 0;
+    if (valid) {
+        ev_cur = p.ev_cursor_r[slot];
+        ev_end = p.ev_start[slot + 1];
+    }
+    const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+
+    if (rotors) {
+        /* ---------------- role 1: rotor events, speed ramps, angle streams ---------------- */
+        double hang = rp.hornAngle, dang = rp.drumAngle;
+        const double SR = wh->sample_rate;
+        for (uint32_t f = 0; f < p.n_fragments; ++f) {
+            while (ev_cur < ev_end) {
+                const tbf_event *evp = p.events + ev_cur;
+                if (evp->fragment > p.frag_base + f)
+                    break;
+                const int type = evp->type, a = evp->a;
+                if (type == TBF_EV_REV_OPTION) {
+                    if (a < 0)
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    else
+                        use_rev_option(rp, wh, a, 2);
+                } else if (type == TBF_EV_REV_SELECT) {
+                    if (a < 0) {
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    } else {
+                        rp.revSelect = a % 3;
+                        use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
+                    }
+                } else if (type == TBF_EV_WHIRL_BRAKE || type == TBF_EV_WHIRL_RAMP) {
+                    const int b = evp->b;
+                    if (a < 0 || a > (type == TBF_EV_WHIRL_BRAKE ? 1 : 3) || b < 0 || b > 127) {
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    } else if (type == TBF_EV_WHIRL_BRAKE) {
+                        /* w->hnBrakePos = (double)uc / 127.0, src/whirl.cpp:883-893 */
+                        rp.brakePos[a] = __ddiv_rn((double)b, 127.0);
+                    } else {
+                        rp.oml[a] = wh->ramp_one_minus_l[a][b];
+                    }
+                }
+                ++ev_cur;
+            }
+            /* -- per-call speed ramps (src/whirl.cpp:1219-1374) -- */
+            int hbrake = 0, dbrake = 0;
+            double hincr = rp.hornIncr, dincr = rp.drumIncr;
+            if (whirl_run) {
+                hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
+                                    rp.oml[0], rp.oml[1]);
+                dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
+                                    rp.oml[2], rp.oml[3]);
+            }
+            /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
+            const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
+            const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
+            for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
+                const size_t col0 = ((size_t)f * (TBF_FRAGMENT / BLK) + (size_t)blk) * BLK;
+                if (whirl_run) {
+#pragma unroll 4
+                    for (int s = 0; s < BLK; ++s) {
+                        sm.tang[0][lane * TILE_PITCH + s] = hang;
+                        sm.tang[1][lane * TILE_PITCH + s] = dang;
+                        if (hfast) {
+                            const double t = __dadd_rn(hang, hincr);
+                            hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                        } else {
+                            hang = angle_step(hang, hincr);
+                        }
+                        if (dfast) {
+                            const double t = __dadd_rn(dang, dincr);
+                            dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                        } else {
+                            dang = angle_step(dang, dincr);
+                        }
+                    }
+                }
+                __syncwarp();
+#pragma unroll 4
+                for (uint32_t r = 0; r < rows; ++r) {
+                    const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+                    p.hang[g] = sm.tang[0][r * TILE_PITCH + lane];
+                    p.dang[g] = sm.tang[1][r * TILE_PITCH + lane];
+                }
+                __syncwarp();
+            }
+            if (whirl_run) {
+                rp.hornIncr = hbrake ? 0.0 : hincr;
+                rp.drumIncr = dbrake ? 0.0 : dincr;
+            }
+        }
+        if (valid) {
+            RampScalars &o = st->rp; /* this role's fields only: role 0 stores the others */
+            o.hornAcDc = rp.hornAcDc;
+            o.drumAcDc = rp.drumAcDc;
+            o.revSelect = rp.revSelect;
+            o.hornAngle = hang;
+            o.drumAngle = dang;
+            o.hornIncr = rp.hornIncr;
+            o.drumIncr = rp.drumIncr;
+            o.hornTarget = rp.hornTarget;
+            o.drumTarget = rp.drumTarget;
+            o.brakePos[0] = rp.brakePos[0];
+            o.brakePos[1] = rp.brakePos[1];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                o.oml[k] = rp.oml[k];
+            if (new_flags)
+                atomicOr(&o.errorFlags, new_flags);
+        }
+        return;
+    }
+
+    /* ---------------- role 0: mixdown, horn biquads, dx0 / hx0 ---------------- */
     float cA[5], cB[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
@@ -1240,53 +1364,23 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
     }
     float zA0 = rp.iirz[0][0], zA1 = rp.iirz[0][1], zB0 = rp.iirz[1][0], zB1 = rp.iirz[1][1];
     float pg = rp.percEnvGain, kc = rp.keyCompLevel;
-    double hang = rp.hornAngle, dang = rp.drumAngle;
-    const double SR = wh->sample_rate;
-    uint64_t ev_cur = 0, ev_end = 0;
-    if (valid) {
-        ev_cur = p.ev_cursor_r[slot];
-        ev_end = p.ev_start[slot + 1];
-    }
-    for (int r = 0; r < BLK; ++r)
-        sm.csum[r][lane] = 0ull;
-    const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+    if (p.checksums && whirl_off) /* csum lies past the launch's shared memory otherwise */
+        for (int r = 0; r < BLK; ++r)
+            sm.csum[r][lane] = 0ull;
     r_tile_fetch(p, sm.tin[0], slot0, rows, 0, lane);
     __pipeline_commit();
     __syncwarp();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
-        /* -- rotor speed events that precede this fragment -- */
+        /* -- horn filter events that precede this fragment (the rotor's belong to role 1) -- */
         while (ev_cur < ev_end) {
             const tbf_event *evp = p.events + ev_cur;
             if (evp->fragment > p.frag_base + f)
                 break;
-            const int type = evp->type, a = evp->a;
-            if (type == TBF_EV_REV_OPTION) {
-                if (a < 0)
-                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
-                else
-                    use_rev_option(rp, wh, a, 2);
-            } else if (type == TBF_EV_REV_SELECT) {
-                if (a < 0) {
-                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
-                } else {
-                    rp.revSelect = a % 3;
-                    use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
-                }
-            } else if (type == TBF_EV_WHIRL_BRAKE || type == TBF_EV_WHIRL_RAMP) {
-                const int b = evp->b;
-                if (a < 0 || a > (type == TBF_EV_WHIRL_BRAKE ? 1 : 3) || b < 0 || b > 127) {
-                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
-                } else if (type == TBF_EV_WHIRL_BRAKE) {
-                    /* w->hnBrakePos = (double)uc / 127.0, src/whirl.cpp:883-893 */
-                    rp.brakePos[a] = __ddiv_rn((double)b, 127.0);
-                } else {
-                    rp.oml[a] = wh->ramp_one_minus_l[a][b];
-                }
-            } else if (type == TBF_EV_HORN_FILTER) {
-                const int k = a & 7;
+            if (evp->type == TBF_EV_HORN_FILTER) {
+                const int a = evp->a, k = a & 7;
                 if (a < 0 || a > 15 || k > 4) {
-                    rp.errorFlags |= TBF_IFLAG_BAD_EVENT;
+                    new_flags |= TBF_IFLAG_BAD_EVENT;
                 } else {
                     const float v = __int_as_float(evp->b);
                     rp.iir[a >> 3][k] = v;
@@ -1309,19 +1403,6 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
         const bool perc_on = (c.flags & FC_PERC_ON) != 0;
         /* (keyComp - level) / 128.f: dividing by 2^7 and multiplying by 2^-7 round identically */
         const float delta = __fmul_rn(__fsub_rn(c.key_comp, kc), 0.0078125f);
-
-        /* -- per-call speed ramps (src/whirl.cpp:1219-1374) -- */
-        int hbrake = 0, dbrake = 0;
-        double hincr = rp.hornIncr, dincr = rp.drumIncr;
-        if (whirl_run) {
-            hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
-                                rp.oml[0], rp.oml[1]);
-            dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
-                                rp.oml[2], rp.oml[3]);
-        }
-        /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
-        const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
-        const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
 
         for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
             const uint32_t gb = f * (TBF_FRAGMENT / BLK) + (uint32_t)blk;
@@ -1357,20 +1438,6 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
                     const float yb = eq_iir(cB, zB0, zB1, ya);
                     sm.tout[0][lane * TILE_PITCH + s] = x;
                     sm.tout[1][lane * TILE_PITCH + s] = yb;
-                    sm.tang[0][lane * TILE_PITCH + s] = hang;
-                    sm.tang[1][lane * TILE_PITCH + s] = dang;
-                    if (hfast) {
-                        const double t = __dadd_rn(hang, hincr);
-                        hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
-                    } else {
-                        hang = angle_step(hang, hincr);
-                    }
-                    if (dfast) {
-                        const double t = __dadd_rn(dang, dincr);
-                        dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
-                    } else {
-                        dang = angle_step(dang, dincr);
-                    }
                 } else {
                     sm.tout[0][lane * TILE_PITCH + s] = mono;
                     sm.tout[1][lane * TILE_PITCH + s] = mono; /* bypassed Leslie: stage D mixes it */
@@ -1392,12 +1459,11 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
                     }
                 }
             } else {
+#pragma unroll 4
                 for (uint32_t r = 0; r < rows; ++r) {
                     const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
                     p.dx0[g] = sm.tout[0][r * TILE_PITCH + lane];
                     p.hx0[g] = sm.tout[1][r * TILE_PITCH + lane];
-                    p.hang[g] = sm.tang[0][r * TILE_PITCH + lane];
-                    p.dang[g] = sm.tang[1][r * TILE_PITCH + lane];
                 }
             }
             __syncwarp();
@@ -1410,23 +1476,26 @@ __global__ void __launch_bounds__(32) tbf_stage_r(const RenderParams p)
             zA1 = isnan(zA1) ? 0.0f : zA1;
             zB0 = isnan(zB0) ? 0.0f : zB0;
             zB1 = isnan(zB1) ? 0.0f : zB1;
-            rp.hornIncr = hbrake ? 0.0 : hincr;
-            rp.drumIncr = dbrake ? 0.0 : dincr;
         }
         if (c.flags & FC_PERC_RESET)
             pg = c.reset;
     }
 
     if (valid) {
-        rp.iirz[0][0] = zA0;
-        rp.iirz[0][1] = zA1;
-        rp.iirz[1][0] = zB0;
-        rp.iirz[1][1] = zB1;
-        rp.percEnvGain = pg;
-        rp.keyCompLevel = kc;
-        rp.hornAngle = hang;
-        rp.drumAngle = dang;
-        st->rp = rp;
+        RampScalars &o = st->rp; /* this role's fields only */
+        o.iirz[0][0] = zA0;
+        o.iirz[0][1] = zA1;
+        o.iirz[1][0] = zB0;
+        o.iirz[1][1] = zB1;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            o.iir[0][k] = rp.iir[0][k];
+            o.iir[1][k] = rp.iir[1][k];
+        }
+        o.percEnvGain = pg;
+        o.keyCompLevel = kc;
+        if (new_flags)
+            atomicOr(&o.errorFlags, new_flags);
         p.ev_cursor_r[slot] = ev_cur;
         if (p.checksums && whirl_off) {
             unsigned long long c = 0ull;
@@ -1788,7 +1857,8 @@ struct DSmem {
     float t[2][5][BLK * TILE_PITCH]; /* [buffer][DL DR HL HR hx0], filled by cp.async one
                                         block ahead of its use                             */
     DRow row[BLK];
-    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums */
+    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums.  LAST:
+                                          launched without it when no checksum is wanted */
 };
 
 /* request one 32 x 32 block of the five streams stage D reads */
@@ -1852,8 +1922,9 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         r.bypass = wh->bypass;
         sm.row[lane] = r;
     }
-    for (int r = 0; r < BLK; ++r)
-        sm.csum[r][lane] = 0ull;
+    if (p.checksums) /* csum lies past the launch's shared memory otherwise */
+        for (int r = 0; r < BLK; ++r)
+            sm.csum[r][lane] = 0ull;
     __syncwarp();
 
     const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
@@ -2002,7 +2073,10 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_r, sizeof(RSmem), &have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    tbf_stage_r<<<grid, 32, sizeof(RSmem), (cudaStream_t)stream>>>(p);
+    const bool r_csum = p.checksums && (p.flags & TBF_RENDER_WHIRL_BYPASS);
+    const size_t smem = sizeof(RSmem) - (r_csum ? 0 : sizeof(RSmem::csum));
+    /* the rotor warp has nothing to do when the Leslie is bypassed */
+    tbf_stage_r<<<grid, (p.flags & TBF_RENDER_WHIRL_BYPASS) ? 32 : 64, smem, (cudaStream_t)stream>>>(p);
     debug_sync(stream, "R");
     return (int)cudaGetLastError();
 }
@@ -2025,7 +2099,8 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), &have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
+    const size_t smem = sizeof(DSmem) - (p.checksums ? 0 : sizeof(DSmem::csum));
+    tbf_stage_d<<<grid, 32, smem, (cudaStream_t)stream>>>(p);
     debug_sync(stream, "D");
     return (int)cudaGetLastError();
 }

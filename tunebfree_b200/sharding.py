@@ -18,12 +18,30 @@ def shard_plan(rank, world, per_gpu, n_table_sets):
     return first, per_set
 
 
+def shard_plan_grouped(rank, world, per_gpu, key_of):
+    """Block partition of the organ list SORTED BY TABLE KEY: organs that share
+    wave tables become neighbours in the batch and land on one GPU, so the warps in flight
+    at any time read a few table sets out of L2 instead of all of them out of HBM.
+    key_of(global_id) -> hashable, sortable.  -> (global ids of this rank's slots,
+    {key: [slots]} in slot order)."""
+    if not (0 <= rank < world) or per_gpu <= 0:
+        raise ValueError("bad shard arguments")
+    order = sorted(range(world * per_gpu), key=lambda g: (key_of(g), g))
+    mine = order[rank * per_gpu:(rank + 1) * per_gpu]
+    groups = {}
+    for slot, g in enumerate(mine):
+        groups.setdefault(key_of(g), []).append(slot)
+    return np.asarray(mine, dtype=np.int64), groups
+
+
 def slot_instance_ids(per_set, create):
-    """create(set_index, count) -> first instance handle of `count` new instances.
+    """create(set index or key, count) -> first instance handle of `count` new instances.
+    per_set: list indexed by set (shard_plan) or {key: slots} (shard_plan_grouped).
     Returns the uint32 handle of every batch slot."""
-    n = sum(len(s) for s in per_set)
+    items = list(per_set.items()) if isinstance(per_set, dict) else list(enumerate(per_set))
+    n = sum(len(slots) for _, slots in items)
     ids = np.zeros(n, dtype=np.uint32)
-    for s, slots in enumerate(per_set):
+    for s, slots in items:
         if slots:
             first = create(s, len(slots))
             ids[slots] = np.arange(first, first + len(slots), dtype=np.uint32)

@@ -5,7 +5,7 @@ renderer, the oracle and the CPU baseline see identical inputs.
 """
 import numpy as np
 
-from . import cabi
+from . import cabi, config5
 
 FRAGMENTS_PER_SECOND = 375  # 48000 / 128
 MASK64 = (1 << 64) - 1
@@ -58,15 +58,34 @@ def instance_events(instance_id, n_fragments, config=3, restrike=187, hold=140):
     return ev
 
 
-def batch_events_numpy(first_instance, n_instances, n_fragments, config=3):
-    """int32 [n, 5] rows (slot, fragment, type, a, b) sorted by (slot, fragment)."""
+def batch_events_numpy(first_instance, n_instances, n_fragments, config=3, global_ids=None):
+    """int32 [n, 5] rows (slot, fragment, type, a, b) sorted by (slot, fragment).  Slot i plays
+    organ global_ids[i] (default: first_instance + i)."""
     rows = []
     for slot in range(n_instances):
-        evs = sorted(instance_events(first_instance + slot, n_fragments, config), key=lambda t: t[0])
+        g = first_instance + slot if global_ids is None else int(global_ids[slot])
+        evs = sorted(instance_events(g, n_fragments, config), key=lambda t: t[0])
         a = np.array(evs, dtype=np.int32).reshape(-1, 4)
         s = np.full((a.shape[0], 1), slot, dtype=np.int32)
         rows.append(np.concatenate([s, a], axis=1))
     return np.concatenate(rows, axis=0)
+
+
+def organ_variant(global_id, config):
+    """(osc variant, whirl variant, engine seed) of organ `global_id`.  Configs 2 and 3 use the
+    compiled-in defaults with 16 engine seeds; config 5 walks the Cartesian mix of the
+    reference's cfg/osc-*.cfg (and the default) x cfg/whirl-*.cfg."""
+    seed = 1 + global_id % 16
+    if config != 5:
+        return ("default", "default", seed)
+    osc = list(config5.OSC_VARIANTS)
+    whirl = list(config5.WHIRL_VARIANTS)
+    return (osc[global_id % len(osc)], whirl[(global_id // len(osc)) % len(whirl)], seed)
+
+
+def variant_cfg(osc, whirl):
+    """cfg text of a variant pair ('default' = no setting)."""
+    return config5.OSC_VARIANTS.get(osc, "") + config5.WHIRL_VARIANTS.get(whirl, "")
 
 
 def render_flags(config):
