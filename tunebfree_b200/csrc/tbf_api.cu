@@ -1014,7 +1014,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                     ctx->err = std::string("stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
                     return TBF_ERR_CUDA;
                 }
-                ctx->launches += n_stages;
+                ctx->launches += n_stages + (whirl ? 1 : 0); /* stage D is two kernels */
             }
             if (host_out)
                 CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->sdone[g][last][par], 0));

@@ -1847,21 +1847,12 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
 /* stage D: drum biquads (lane = instance) + output mix (lane = sample) */
 /* ================================================================== */
 
-struct DRow { /* what the mix needs of an instance's whirl table set */
-    float horn_level, leakage;
-    float hll, hlr, hrl, hrr, dll, dlr, drl, drr;
-    int bypass;
-};
-
 struct DSmem {
-    float t[2][5][BLK * TILE_PITCH]; /* [buffer][DL DR HL HR hx0], filled by cp.async one
-                                        block ahead of its use                             */
-    DRow row[BLK];
-    unsigned long long csum[BLK][BLK]; /* [row = instance][lane]: checksum partial sums.  LAST:
-                                          launched without it when no checksum is wanted */
+    float t[2][2][BLK * TILE_PITCH]; /* [buffer][DL DR] (row = instance, col = sample), filled by
+                                        cp.async one block ahead of its use                  */
 };
 
-/* request one 32 x 32 block of the five streams stage D reads */
+/* request one 32 x 32 block of the two drum delay-line reads */
 __device__ __forceinline__ void d_tile_fetch(const RenderParams &p, float (*tile)[BLK * TILE_PITCH],
                                              uint32_t slot0, uint32_t rows, size_t col0, int lane)
 {
@@ -1870,12 +1861,14 @@ __device__ __forceinline__ void d_tile_fetch(const RenderParams &p, float (*tile
         const int o = r * TILE_PITCH + lane;
         __pipeline_memcpy_async(&tile[0][o], p.line[2] + g, 4);
         __pipeline_memcpy_async(&tile[1][o], p.line[3] + g, 4);
-        __pipeline_memcpy_async(&tile[2][o], p.line[0] + g, 4);
-        __pipeline_memcpy_async(&tile[3][o], p.line[1] + g, 4);
-        __pipeline_memcpy_async(&tile[4][o], p.hx0 + g, 4);
     }
 }
 
+/* Stage D, first kernel: the drum biquads drfL / drfR (src/whirl.cpp:1607-1612), the one serial
+ * recurrence left after stage W; lane = organ, the two line reads are filtered IN PLACE in the
+ * stage streams.  Everything per-sample after them is elementwise and runs in tbf_stage_m with
+ * lane = sample, so this warp -- a latency chain that takes a stage T / W slot of its SM while it
+ * runs -- carries 2 of the 7 streams and a third of the instructions it used to. */
 __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1885,8 +1878,6 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
     const uint32_t slot = slot0 + lane;
     const bool valid = slot < p.n_instances;
     const uint32_t rows = min(32u, p.n_instances - slot0);
-    const bool whirl3 = (p.flags & TBF_RENDER_WHIRLPROC3) != 0;
-    const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
 
     InstState *st = nullptr;
     const DevWhirlTables *wh = p.wh;
@@ -1901,31 +1892,14 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         zr1 = st->dr.iirz[1][1];
     }
     const bool run = valid && !wh->bypass;
+    if (!__any_sync(FULL, run))
+        return; /* every organ of the warp has its Leslie bypassed: nothing to filter */
     float cL[5], cR[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
         cL[k] = wh->iir[2][k];
         cR[k] = wh->iir[3][k];
     }
-    {
-        DRow r;
-        r.horn_level = wh->horn_level;
-        r.leakage = wh->leakage;
-        r.hll = wh->mic_hll;
-        r.hlr = wh->mic_hlr;
-        r.hrl = wh->mic_hrl;
-        r.hrr = wh->mic_hrr;
-        r.dll = wh->mic_dll;
-        r.dlr = wh->mic_dlr;
-        r.drl = wh->mic_drl;
-        r.drr = wh->mic_drr;
-        r.bypass = wh->bypass;
-        sm.row[lane] = r;
-    }
-    if (p.checksums) /* csum lies past the launch's shared memory otherwise */
-        for (int r = 0; r < BLK; ++r)
-            sm.csum[r][lane] = 0ull;
-    __syncwarp();
 
     const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
     d_tile_fetch(p, sm.t[0], slot0, rows, 0, lane);
@@ -1939,7 +1913,6 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         __pipeline_wait_prior(1);
         __syncwarp();
         float *tl = sm.t[cur][0], *tr = sm.t[cur][1];
-        const float *thl = sm.t[cur][2], *thr = sm.t[cur][3], *th0 = sm.t[cur][4];
         if (run) {
 #pragma unroll 4
             for (int s = 0; s < BLK; ++s) {
@@ -1954,46 +1927,11 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
             }
         }
         __syncwarp();
+#pragma unroll 4
         for (uint32_t r = 0; r < rows; ++r) {
-            const DRow w = sm.row[r];
-            const float h0 = th0[r * TILE_PITCH + lane];
-            float o_l, o_r;
-            if (w.bypass) {
-                /* bypassed Leslie: input copied to both horn outputs, drum silent
-                 * (src/whirl.cpp:1197-1215), then whirlProc3's mic mix (:1676-1680) */
-                if (!whirl3) {
-                    o_l = o_r = h0;
-                } else {
-                    o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, w.hll), __fmul_rn(h0, w.hlr)),
-                                              __fmul_rn(0.0f, w.dll)), __fmul_rn(0.0f, w.dlr));
-                    o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, w.hrl), __fmul_rn(h0, w.hrr)),
-                                              __fmul_rn(0.0f, w.drl)), __fmul_rn(0.0f, w.drr));
-                }
-            } else {
-                const float hl = thl[r * TILE_PITCH + lane], hr = thr[r * TILE_PITCH + lane];
-                const float yl = tl[r * TILE_PITCH + lane], yr = tr[r * TILE_PITCH + lane];
-                const float leak = __fmul_rn(h0, w.leakage);
-                const float hpl = __fmul_rn(w.horn_level, hl), hpr = __fmul_rn(w.horn_level, hr);
-                if (!whirl3) {
-                    o_l = __fadd_rn(__fadd_rn(yl, hpl), leak);
-                    o_r = __fadd_rn(__fadd_rn(yr, hpr), leak);
-                } else {
-                    const float ohl = __fadd_rn(hpl, leak), ohr = __fadd_rn(hpr, leak);
-                    o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, w.hll), __fmul_rn(ohr, w.hlr)),
-                                              __fmul_rn(yl, w.dll)), __fmul_rn(yr, w.dlr));
-                    o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, w.hrl), __fmul_rn(ohr, w.hrr)),
-                                              __fmul_rn(yl, w.drl)), __fmul_rn(yr, w.drr));
-                }
-            }
-            if (store) {
-                const size_t o = (size_t)(slot0 + r) * p.out_stride + col0 + lane;
-                p.out_l[o] = o_l;
-                p.out_r[o] = o_r;
-            }
-            if (p.checksums) {
-                const uint32_t pos = (uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + col0 + lane);
-                sm.csum[r][lane] += sample_hash(pos, o_l, o_r);
-            }
+            const size_t g = (size_t)(slot0 + r) * p.pitch + col0 + lane;
+            p.line[2][g] = tl[r * TILE_PITCH + lane];
+            p.line[3][g] = tr[r * TILE_PITCH + lane];
         }
         __syncwarp();
     }
@@ -2004,11 +1942,70 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
         st->dr.iirz[1][0] = zr0;
         st->dr.iirz[1][1] = zr1;
     }
-    if (valid && p.checksums) {
-        unsigned long long c = 0ull;
-        for (int j = 0; j < BLK; ++j)
-            c += sm.csum[lane][(j + lane) & (BLK - 1)];
-        p.checksums[slot] += c; /* zeroed by the host; accumulates over chunks */
+}
+
+#define M_THREADS 256
+
+/* Stage D, second kernel: horn level, leakage and the microphone mix (src/whirl.cpp:1614-1616,
+ * whirlProc3 :1676-1680) -- elementwise over the five streams, lane = sample, one organ per
+ * blockIdx.x, gridDim.y CTAs along the samples; the output checksum is formed here. */
+__global__ void __launch_bounds__(M_THREADS) tbf_stage_m(const RenderParams p)
+{
+    const uint32_t slot = blockIdx.x;
+    const bool whirl3 = (p.flags & TBF_RENDER_WHIRLPROC3) != 0;
+    const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
+    const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
+    const DevWhirlTables *wh = p.wh + p.states[id].tg.whTables;
+    const float horn_level = wh->horn_level, leakage = wh->leakage;
+    const float hll = wh->mic_hll, hlr = wh->mic_hlr, hrl = wh->mic_hrl, hrr = wh->mic_hrr;
+    const float dll = wh->mic_dll, dlr = wh->mic_dlr, drl = wh->mic_drl, drr = wh->mic_drr;
+    const bool bypass = wh->bypass != 0;
+    const uint32_t n = p.n_fragments * TBF_FRAGMENT;
+    const size_t in0 = (size_t)slot * p.pitch, out0 = (size_t)slot * p.out_stride;
+    unsigned long long csum = 0ull;
+    for (uint32_t i = blockIdx.y * M_THREADS + threadIdx.x; i < n; i += gridDim.y * M_THREADS) {
+        const float h0 = p.hx0[in0 + i];
+        float o_l, o_r;
+        if (bypass) {
+            /* bypassed Leslie: input copied to both horn outputs, drum silent
+             * (src/whirl.cpp:1197-1215), then whirlProc3's mic mix (:1676-1680) */
+            if (!whirl3) {
+                o_l = o_r = h0;
+            } else {
+                o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, hll), __fmul_rn(h0, hlr)),
+                                          __fmul_rn(0.0f, dll)), __fmul_rn(0.0f, dlr));
+                o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, hrl), __fmul_rn(h0, hrr)),
+                                          __fmul_rn(0.0f, drl)), __fmul_rn(0.0f, drr));
+            }
+        } else {
+            const float hl = p.line[0][in0 + i], hr = p.line[1][in0 + i];
+            const float yl = p.line[2][in0 + i], yr = p.line[3][in0 + i];
+            const float leak = __fmul_rn(h0, leakage);
+            const float hpl = __fmul_rn(horn_level, hl), hpr = __fmul_rn(horn_level, hr);
+            if (!whirl3) {
+                o_l = __fadd_rn(__fadd_rn(yl, hpl), leak);
+                o_r = __fadd_rn(__fadd_rn(yr, hpr), leak);
+            } else {
+                const float ohl = __fadd_rn(hpl, leak), ohr = __fadd_rn(hpr, leak);
+                o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, hll), __fmul_rn(ohr, hlr)),
+                                          __fmul_rn(yl, dll)), __fmul_rn(yr, dlr));
+                o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, hrl), __fmul_rn(ohr, hrr)),
+                                          __fmul_rn(yl, drl)), __fmul_rn(yr, drr));
+            }
+        }
+        if (store) {
+            p.out_l[out0 + i] = o_l;
+            p.out_r[out0 + i] = o_r;
+        }
+        if (p.checksums)
+            csum += sample_hash((uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + i), o_l, o_r);
+    }
+    if (p.checksums) { /* zeroed by the host; accumulates over chunks and CTAs */
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1)
+            csum += __shfl_xor_sync(FULL, csum, d);
+        if ((threadIdx.x & 31) == 0 && csum)
+            atomicAdd(&p.checksums[slot], csum);
     }
 }
 
@@ -2099,9 +2096,12 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), &have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    const size_t smem = sizeof(DSmem) - (p.checksums ? 0 : sizeof(DSmem::csum));
-    tbf_stage_d<<<grid, 32, smem, (cudaStream_t)stream>>>(p);
+    tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
     debug_sync(stream, "D");
+    const uint32_t n = p.n_fragments * TBF_FRAGMENT;
+    const dim3 mgrid(p.n_instances, std::max(1u, std::min(8u, n / (4 * M_THREADS))));
+    tbf_stage_m<<<mgrid, M_THREADS, 0, (cudaStream_t)stream>>>(p);
+    debug_sync(stream, "M");
     return (int)cudaGetLastError();
 }
 
