@@ -37,12 +37,15 @@ import numpy as np
 METRIC = "realtime-instances: 48 kHz stereo organ-seconds rendered per wall-second"
 UNIT = "organ-seconds/s"
 N_TABLE_SETS = 16  # engine seeds 1 + id mod 16: 16 dither/click realisations
-DEFAULT_INSTANCES = {2: 1024, 3: 4096, 5: 16384}
+DEFAULT_INSTANCES = {2: 1024, 3: 4096, 4: 0, 5: 16384}  # 4: one organ per accepted scale
 WORKLOAD_NAME = {
     2: "config2: tonegen only, drawbars 888888888, 10-note chords re-struck every 0.5 s, "
        "percussion + key click, whirl bypassed",
     3: "config3: tonegen + vibrato C3 + Leslie fast (whirlProc3), drawbars 888888888, 10-note "
        "chords re-struck every 0.5 s, percussion + key click",
+    4: "config4: one organ per Scala scale of the reference's archive (own wave tables each, built "
+       "by tbf_build_tonegen_tables), fixed 5-note chord re-struck every 0.5 s through config 3's "
+       "chain (vibrato C3 + Leslie fast, whirlProc3)",
     5: "config5: config 3's chain and chords over the Cartesian mix of the reference's 10 osc "
        "cfg variants x 3 whirl cfg variants x 16 engine seeds (80 wave-table sets), organs "
        "grouped by table set",
@@ -55,9 +58,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", type=int, default=3, choices=[2, 3, 5])
+    ap.add_argument("--config", type=int, default=3, choices=[2, 3, 4, 5])
     ap.add_argument("--instances", type=int, default=0, help="instances per GPU")
-    ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per instance per step")
+    ap.add_argument("--seconds", type=float, default=0.0,
+                    help="audio seconds per instance per step (default 10; config 4: 2)")
     ap.add_argument("--cpu-sample-seconds", type=float, default=15.0,
                     help="target CPU time of the bounded cpu_baseline sample")
     ap.add_argument("--ref-build", default="strict", choices=["strict", "stock"],
@@ -65,7 +69,10 @@ def parse_args():
                          "the project's stock -O3 -ffast-math flags (timing only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.seconds <= 0:
+        a.seconds = 2.0 if a.config == 4 else 10.0
+    return a
 
 
 # --------------------------------------------------------------------------
@@ -80,6 +87,11 @@ def _cpu_worker(args):
     # organ plays which script, and 3 MB per reference instance adds up on many-core hosts
     engines = []
     for i in ids[:4]:
+        if config == 4:  # one tuning per organ: organ i plays scale i of the sweep
+            from tunebfree_b200 import tables
+            degs = workloads.scala_sweep()[1]
+            engines.append(ref_engine.RefInstance(seed=1, freqs=tables.freqs_from_ratios(degs[i % len(degs)])))
+            continue
         osc, whirl, seed = workloads.organ_variant(i, config)
         engines.append(ref_engine.RefInstance(seed=seed, cfg=workloads.variant_cfg(osc, whirl)))
     insts = []
@@ -279,6 +291,9 @@ def run_gpu_arm(a):
         return float(t.item())
 
     n_inst = a.instances or DEFAULT_INSTANCES[a.config]
+    if a.config == 4:
+        sweep_names, sweep_degs, _ = workloads.scala_sweep()
+        n_inst = n_inst or len(sweep_names)
     n_frag = int(round(a.seconds * 375))
     frames = n_frag * 128
     flags = workloads.render_flags(a.config)
@@ -286,7 +301,11 @@ def run_gpu_arm(a):
     # every rank plays different organs; slot i plays global organ first_global + i with
     # table set (global id) mod 16
     variant = lambda g: workloads.organ_variant(g, a.config)
-    if a.config == 5:
+    if a.config == 4:
+        # rank r plays scales [r * n_inst, (r + 1) * n_inst) of the sweep (wrapping around)
+        global_ids = (rank * n_inst + np.arange(n_inst, dtype=np.int64)) % len(sweep_names)
+        groups = {}
+    elif a.config == 5:
         global_ids, groups = sharding.shard_plan_grouped(rank, world, n_inst, variant)
     else:
         first_global, per_set = sharding.shard_plan(rank, world, n_inst, N_TABLE_SETS)
@@ -306,8 +325,42 @@ def run_gpu_arm(a):
             if whirl not in wh_handles:
                 wh_handles[whirl] = ctx.whirl_tables(wt)
             tables.free_tables(tt, wt)
-    ids = sharding.slot_instance_ids(
-        groups, lambda k, count: ctx.create_instances(tg_handles[(k[0], k[2])], wh_handles[k[1]], count))
+    init = None
+    if a.config == 4:
+        # config 4's init leg: 128 frequencies -> wave tables, key wiring, envelopes (the
+        # product's restatement of initToneGenerator) on the host cores, then the upload
+        import ctypes as C
+        from concurrent.futures import ThreadPoolExecutor
+        threads = os.cpu_count() or 1
+        spec0 = tables.InstanceSpec(seed=1)
+        tt0, wt0 = spec0.build()
+        wh_handles["default"] = ctx.whirl_tables(wt0)
+        tables.free_tables(tt0, wt0)
+
+        def build_one(g):
+            sp = tables.InstanceSpec(freqs=tables.freqs_from_ratios(sweep_degs[g]), seed=1)
+            return sp.build_tonegen()
+
+        ids = np.zeros(n_inst, dtype=np.uint32)
+        t_build = t_upload = 0.0
+        with ThreadPoolExecutor(threads) as pool:
+            for lo in range(0, n_inst, 512):
+                t0 = time.perf_counter()
+                built = list(pool.map(build_one, [int(g) for g in global_ids[lo:lo + 512]]))
+                t1 = time.perf_counter()
+                for k, tt in enumerate(built):
+                    h = ctx.tonegen_tables(tt)
+                    tg_handles[lo + k] = h
+                    ids[lo + k] = ctx.create_instances(h, wh_handles["default"], 1)
+                    tables.free_tables(tt, None)
+                ctx.synchronize()
+                t_build += t1 - t0
+                t_upload += time.perf_counter() - t1
+        init = {"tables_built_per_s": n_inst / t_build, "host_threads": threads,
+                "uploaded_per_s": n_inst / t_upload, "build_s": t_build, "upload_s": t_upload}
+    else:
+        ids = sharding.slot_instance_ids(
+            groups, lambda k, count: ctx.create_instances(tg_handles[(k[0], k[2])], wh_handles[k[1]], count))
     ev_np = workloads.batch_events_numpy(0, n_inst, n_frag, a.config, global_ids=global_ids)
     events = engine.events_from_numpy(ev_np)
     h2d_bytes = int(ev_np.shape[0] * 20 + n_inst * 4 + (n_inst + 1) * 8)
@@ -470,7 +523,8 @@ def run_gpu_arm(a):
             "config": {"workload": WORKLOAD_NAME[a.config], "instances_per_gpu": n_inst,
                        "seconds_per_instance": a.seconds, "sample_rate": 48000,
                        "table_sets": len(tg_handles), "whirl_table_sets": len(wh_handles),
-                       "tuning": "12-TET",
+                       "tuning": "one Scala scale per organ" if a.config == 4 else "12-TET",
+                       "init": init,
                        "l2": "inputs larger than L2 (instance state %.0f MB + %.1f GB of output per step)"
                              % (n_inst * 0.08, 2 * n_inst * frames * 4 / 1e9),
                        "parallelism": "instances sharded over %d GPU(s), no collective" % world},

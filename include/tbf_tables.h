@@ -91,6 +91,11 @@ void tbf_freqs_12tet(double freqs[128]);
 /* Scala .scl text -> 128 note frequencies; degree 0 at MIDI 60 = 261.6255653005986 Hz
  * (what the reference's regression fixtures were generated with, tests/test_regression.py) */
 int tbf_freqs_from_scl(const char *scl_text, double freqs[128]);
+/* the same from the scale's n degrees as frequency ratios over degree 0 (the .scl pitch lines
+ * after cents -> 2^(c/1200) and n/d -> n/d; the last one is the period) */
+int tbf_freqs_from_ratios(const double *degrees, int n, double freqs[128]);
+/* .scl text -> its degrees as ratios; returns n (> 0) or an error */
+int tbf_scl_ratios(const char *scl_text, double *degrees, int capacity);
 
 /* one cfg line "key=value" of the osc.*, scanner.* and whirl.* families
  * (src/tonegen.cpp:2173-2556, src/vibrato.cpp:334-357, src/whirl.cpp:992-1164).

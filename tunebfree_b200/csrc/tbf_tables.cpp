@@ -90,9 +90,9 @@ extern "C" void tbf_freqs_12tet(double freqs[128])
  * degrees, then one pitch per line: with a '.' it is cents, otherwise a ratio
  * n/d or an integer.  Degree 0 (1/1) sits on MIDI note 60 at 261.6255653005986 Hz
  * and the last entry is the period. */
-extern "C" int tbf_freqs_from_scl(const char *text, double freqs[128])
+static int parse_scl(const char *text, std::vector<double> &ratio)
 {
-    if (!text || !freqs)
+    if (!text)
         return TBF_ERR_ARG;
     std::vector<std::string> lines;
     const char *p = text;
@@ -114,8 +114,7 @@ extern "C" int tbf_freqs_from_scl(const char *text, double freqs[128])
     const int n = atoi(lines[1].c_str());
     if (n < 1 || (size_t)n + 2 > lines.size())
         return TBF_ERR_ARG;
-    std::vector<double> ratio(n + 1);
-    ratio[0] = 1.0;
+    ratio.assign(n + 1, 1.0);
     for (int i = 0; i < n; ++i) {
         std::string tok = lines[2 + i];
         size_t sp = tok.find_first_of(" \t");
@@ -141,8 +140,39 @@ extern "C" int tbf_freqs_from_scl(const char *text, double freqs[128])
             return TBF_ERR_ARG;
         ratio[i + 1] = r;
     }
+    return n;
+}
+
+extern "C" int tbf_scl_ratios(const char *text, double *degrees, int capacity)
+{
+    std::vector<double> ratio;
+    const int n = parse_scl(text, ratio);
+    if (n < 0)
+        return n;
+    if (!degrees || n > capacity)
+        return TBF_ERR_ARG;
+    memcpy(degrees, ratio.data() + 1, sizeof(double) * n);
+    return n;
+}
+
+extern "C" int tbf_freqs_from_scl(const char *text, double freqs[128])
+{
+    std::vector<double> ratio;
+    const int n = parse_scl(text, ratio);
+    if (n < 0)
+        return n;
+    return tbf_freqs_from_ratios(ratio.data() + 1, n, freqs);
+}
+
+extern "C" int tbf_freqs_from_ratios(const double *degrees, int n, double freqs[128])
+{
+    if (!degrees || !freqs || n < 1)
+        return TBF_ERR_ARG;
+    for (int i = 0; i < n; ++i)
+        if (!(degrees[i] > 0.0))
+            return TBF_ERR_ARG;
     const double base = 261.6255653005986;
-    const double period = ratio[n];
+    const double period = degrees[n - 1];
     for (int note = 0; note < 128; ++note) {
         const int d = note - 60;
         int oct = d / n, deg = d % n;
@@ -150,7 +180,7 @@ extern "C" int tbf_freqs_from_scl(const char *text, double freqs[128])
             deg += n;
             oct -= 1;
         }
-        freqs[note] = base * ratio[deg] * pow(period, (double)oct);
+        freqs[note] = base * (deg ? degrees[deg - 1] : 1.0) * pow(period, (double)oct);
     }
     return TBF_OK;
 }

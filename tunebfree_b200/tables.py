@@ -26,6 +26,8 @@ def _lib():
         L.tbf_freqs_12tet.argtypes = [C.POINTER(C.c_double)]
         L.tbf_freqs_12tet.restype = None
         L.tbf_freqs_from_scl.argtypes = [C.c_char_p, C.POINTER(C.c_double)]
+        L.tbf_freqs_from_ratios.argtypes = [C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double)]
+        L.tbf_scl_ratios.argtypes = [C.c_char_p, C.POINTER(C.c_double), C.c_int]
         L.tbf_spec_apply_cfg.argtypes = [C.POINTER(cabi.TonegenSpec), C.POINTER(cabi.WhirlSpec),
                                          C.c_char_p, C.c_char_p]
         L.tbf_build_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenSpec),
@@ -58,6 +60,24 @@ def freqs_from_scl(text):
     rc = _lib().tbf_freqs_from_scl(text.encode("latin-1", "replace"), f)
     if rc != cabi.OK:
         raise ValueError("unparsable .scl (%d)" % rc)
+    return np.array(f, dtype=np.float64)
+
+
+def scl_ratios(text):
+    """Scala .scl text -> the scale's degrees as frequency ratios (last = period)."""
+    buf = (C.c_double * 4096)()
+    n = _lib().tbf_scl_ratios(text.encode("latin-1", "replace"), buf, 4096)
+    if n < 1:
+        raise ValueError("unparsable .scl (%d)" % n)
+    return np.array(buf[:n], dtype=np.float64)
+
+
+def freqs_from_ratios(degrees):
+    d = np.ascontiguousarray(degrees, dtype=np.float64)
+    f = (C.c_double * 128)()
+    rc = _lib().tbf_freqs_from_ratios(d.ctypes.data_as(C.POINTER(C.c_double)), len(d), f)
+    if rc != cabi.OK:
+        raise ValueError("bad scale degrees (%d)" % rc)
     return np.array(f, dtype=np.float64)
 
 
@@ -123,6 +143,14 @@ class InstanceSpec:
             elif rc < 0:
                 self.rejected.append((key, val))
 
+    def build_tonegen(self):
+        """-> TonegenTables only (free with free_tables(tt, None))."""
+        tt = cabi.TonegenTables()
+        rc = _lib().tbf_build_tonegen_tables(C.byref(self.tg), C.byref(tt))
+        if rc != cabi.OK:
+            raise ValueError("tbf_build_tonegen_tables failed (%d)" % rc)
+        return tt
+
     def build(self):
         """-> (TonegenTables, WhirlTables); free with free_tables()."""
         L = _lib()
@@ -144,3 +172,25 @@ def free_tables(tt, wt):
         L.tbf_free_tonegen_tables(C.byref(tt))
     if wt is not None:
         L.tbf_free_whirl_tables(C.byref(wt))
+
+
+def table_digest(tt):
+    """blake2b-128 over every table of a tbf_tonegen_tables (value fields and arrays)."""
+    import hashlib
+    h = hashlib.blake2b(digest_size=16)
+    for fname, _ in tt._fields_:
+        v = getattr(tt, fname)
+        if isinstance(v, C._Pointer):
+            continue
+        if isinstance(v, C.Array):
+            h.update(bytes(v))
+        elif isinstance(v, float):
+            h.update(np.float64(v).tobytes())
+        else:
+            h.update(np.int64(v).tobytes())
+    nc = tt.contrib_start[cabi.MAX_KEYS]
+    for ptr, n, dt in ((tt.wave_data, tt.wave_total, np.uint32), (tt.contrib_wheel, nc, np.uint16),
+                       (tt.contrib_bus, nc, np.uint16), (tt.contrib_level, nc, np.uint32)):
+        h.update(np.ctypeslib.as_array(ptr, shape=(int(n),)).view(dt).tobytes())
+    d = h.digest()
+    return int.from_bytes(d[:8], "little"), int.from_bytes(d[8:], "little")

@@ -43,11 +43,15 @@ def setup_events(config):
     return ev
 
 
+SWEEP_CHORD = (36, 48, 55, 64, 70)  # config 4: the same five upper-manual keys in every tuning
+
+
 def instance_events(instance_id, n_fragments, config=3, restrike=187, hold=140):
     """[(fragment, type, a, b)] for one instance: setup at fragment 0, then a 10-note
-    chord struck every `restrike` fragments (~0.5 s) and released after `hold`."""
+    chord struck every `restrike` fragments (~0.5 s) and released after `hold`.  Config 4
+    (one organ per Scala scale) plays a fixed 5-note chord instead, same chain as config 3."""
     ev = setup_events(config)
-    keys = chord_keys(instance_id, config)
+    keys = list(SWEEP_CHORD) if config == 4 else chord_keys(instance_id, config)
     f = 0
     while f < n_fragments:
         ev += [(f, cabi.EV_KEY_ON, k, 0) for k in keys]
@@ -92,3 +96,22 @@ def render_flags(config):
     if config == 2:
         return cabi.RENDER_WHIRL_BYPASS
     return cabi.RENDER_WHIRLPROC3
+
+
+_SWEEP = None
+
+
+def scala_sweep():
+    """Config 4's tunings: (names, [degrees as ratios]) of every scale of the reference's Scala
+    archive that both sides accept (tests/golden/scala_sweep.npz, made by
+    tests/golden/make_scala_sweep.py; 128 note frequencies = tables.freqs_from_ratios(degrees))."""
+    global _SWEEP
+    if _SWEEP is None:
+        import os
+        z = np.load(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                 "tests", "golden", "scala_sweep.npz"))
+        ok = np.flatnonzero(z["status"] == 0)
+        off, deg = z["deg_off"], z["degrees"]
+        _SWEEP = ([str(z["names"][i]) for i in ok], [deg[off[i]:off[i + 1]].copy() for i in ok],
+                  z["digest"][ok])
+    return _SWEEP
