@@ -342,22 +342,32 @@ def run_gpu_arm(a):
             return sp.build_tonegen()
 
         ids = np.zeros(n_inst, dtype=np.uint32)
-        t_build = t_upload = 0.0
+        t_wait = t_upload = 0.0
+        t_init0 = time.perf_counter()
+        chunks = [[int(g) for g in global_ids[lo:lo + 256]] for lo in range(0, n_inst, 256)]
         with ThreadPoolExecutor(threads) as pool:
-            for lo in range(0, n_inst, 512):
+            # the host cores build chunk c + 1 while this thread uploads chunk c
+            futures = [pool.submit(build_one, g) for g in chunks[0]]
+            lo = 0
+            for c in range(len(chunks)):
                 t0 = time.perf_counter()
-                built = list(pool.map(build_one, [int(g) for g in global_ids[lo:lo + 512]]))
+                built = [f.result() for f in futures]
                 t1 = time.perf_counter()
+                futures = [pool.submit(build_one, g) for g in chunks[c + 1]] if c + 1 < len(chunks) else []
                 for k, tt in enumerate(built):
                     h = ctx.tonegen_tables(tt)
                     tg_handles[lo + k] = h
                     ids[lo + k] = ctx.create_instances(h, wh_handles["default"], 1)
                     tables.free_tables(tt, None)
-                ctx.synchronize()
-                t_build += t1 - t0
+                lo += len(built)
+                t_wait += t1 - t0
                 t_upload += time.perf_counter() - t1
-        init = {"tables_built_per_s": n_inst / t_build, "host_threads": threads,
-                "uploaded_per_s": n_inst / t_upload, "build_s": t_build, "upload_s": t_upload}
+        ctx.synchronize()
+        t_init = time.perf_counter() - t_init0
+        init = {"organs_initialised_per_s": n_inst / t_init, "wall_s": t_init, "host_threads": threads,
+                "upload_s": t_upload, "waiting_for_builders_s": t_wait,
+                "what": "128 frequencies -> tone-generator tables on the host cores "
+                        "(tbf_build_tonegen_tables), upload, instance create; builders and uploads overlap"}
     else:
         ids = sharding.slot_instance_ids(
             groups, lambda k, count: ctx.create_instances(tg_handles[(k[0], k[2])], wh_handles[k[1]], count))

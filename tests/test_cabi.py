@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _declared_symbols():
     syms = set()
     for name in os.listdir(os.path.join(ROOT, "include")):
-        if not name.endswith(".h"):
+        if not name.endswith(".h") or name == "tbf_shim.h":  # libtbf_shim.so: tests/test_shim.py
             continue
         txt = open(os.path.join(ROOT, "include", name)).read()
         txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)

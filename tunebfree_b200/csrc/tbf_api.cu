@@ -305,6 +305,7 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
      * aligned in copy (pos & 3) and never wraps, so a lane fetches its four consecutive samples
      * with one 16-byte cp.async (tbf_kernels.cu, wave_request). */
     std::vector<float> wave4;
+    wave4.reserve(4 * ((size_t)t->wave_total + (size_t)TBF_NOF_WHEELS * (TBF_FRAGMENT + 8)));
     uint32_t wave4_offset[TBF_NOF_WHEELS + 1] = {0};
     for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
         const uint32_t len = t->wave_length[w];
@@ -315,9 +316,14 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
             return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave store too large");
         wave4_offset[w] = (uint32_t)wave4.size();
         const float *src = t->wave_data + t->wave_offset[w];
-        for (uint32_t c = 0; c < 4; ++c)
-            for (uint32_t i = 0; i < cl; ++i)
-                wave4.push_back(src[(i + c) % len]);
+        wave4.resize(wave4.size() + (size_t)4 * cl);
+        float *dst = wave4.data() + wave4_offset[w];
+        for (uint32_t c = 0; c < 4; ++c) /* dst[i] = src[(i + c) % len], i < cl */
+            for (uint32_t i = 0, pos = c % len; i < cl; pos = 0) {
+                const uint32_t n = std::min(cl - i, len - pos);
+                memcpy(dst + (size_t)c * cl + i, src + pos, sizeof(float) * n);
+                i += n;
+            }
     }
     CK(cudaMalloc(&s.wave, sizeof(float) * std::max<size_t>(4, wave4.size())));
     CK(cudaMalloc(&s.cw, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
