@@ -874,6 +874,10 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
         const uint32_t per = (uint32_t)(((n + n_groups - 1) / n_groups + 31) / 32 * 32);
         for (int g = 0; g <= n_groups; ++g)
             gfirst[g] = (uint32_t)std::min<size_t>(n, (size_t)per * g);
+        /* experiment: uneven two-way split, group 0 = whole waves of CTAs */
+        if (const char *e = getenv("TBF_GROUP0"))
+            if (n_groups == 2 && (size_t)atoi(e) < n && atoi(e) > 0)
+                gfirst[1] = (uint32_t)(atoi(e) / 32 * 32);
     }
     const int n_stages = whirl ? 4 : 2, last = n_stages - 1;
 
