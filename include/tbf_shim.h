@@ -28,6 +28,17 @@ extern "C" {
 struct b_tonegen; /* opaque here; src/tonegen.h:176-563 there */
 struct b_whirl;   /* src/whirl.h:65-221 */
 
+/* the hosts' handle bag, src/global_inst.h:32-40, same layout; this library reads `synth` */
+typedef struct b_instance {
+    struct b_reverb *reverb;
+    struct b_whirl *whirl;
+    struct b_tonegen *synth;
+    struct b_programme *progs;
+    void *midicfg;
+    void *preamp;
+    void *state;
+} b_instance;
+
 /* src/cfgParser.h:39-44, same layout */
 typedef struct _configContext {
     const char *fname;
@@ -47,8 +58,8 @@ void freeToneGenerator(struct b_tonegen *t);                   /* src/tonegen.cp
 void oscKeyOn(struct b_tonegen *t, short midiNote, short realKey);  /* :3134 */
 void oscKeyOff(struct b_tonegen *t, short midiNote, short realKey); /* :3096 */
 void setDrawBar(struct b_tonegen *t, int bus, unsigned int setting); /* :2738 */
-void setDrawBars(void *inst, unsigned int manual, unsigned int setting[]); /* :2763; inst =
-                                                   the struct b_tonegen* here, not b_instance* */
+/* :2763; inst = the host's struct b_instance*, as in the reference: only ->synth is read */
+void setDrawBars(void *inst, unsigned int manual, unsigned int setting[]);
 void setPercussionEnabled(struct b_tonegen *t, int isEnabled); /* :1678 */
 void setPercussionVolume(struct b_tonegen *t, int isSoft);     /* :1744 */
 void setPercussionFast(struct b_tonegen *t, int isFast);       /* :1733 */

@@ -100,10 +100,25 @@ def test_synthsound_loop_bit_exact(ref, cfg):
     L.initWhirl(w, None, 48000.0)
     assert L.tbf_shim_status() == 0, L.tbf_shim_last_error()
 
+    class BInstance(C.Structure):  # src/global_inst.h:32-40
+        _fields_ = [(n, C.c_void_p) for n in ("reverb", "whirl", "synth", "progs", "midicfg", "preamp", "state")]
+    inst = BInstance(None, w, t, None, None, None, None)
+    upper = [None] * 9
+
+    def set_drawbar(bus, setting):
+        """the nine fragment-0 upper drawbars go through setDrawBars(inst, 0, ...), later
+        single changes through setDrawBar"""
+        if upper is not None and bus < 9 and upper[bus] is None:
+            upper[bus] = setting
+            if all(u is not None for u in upper):
+                L.setDrawBars(C.byref(inst), 0, (C.c_uint * 9)(*upper))
+            return
+        L.setDrawBar(t, bus, setting)
+
     call = {
         cabi.EV_KEY_ON: lambda a, b: L.oscKeyOn(t, a, a),
         cabi.EV_KEY_OFF: lambda a, b: L.oscKeyOff(t, a, a),
-        cabi.EV_DRAWBAR: lambda a, b: L.setDrawBar(t, a, b),
+        cabi.EV_DRAWBAR: set_drawbar,
         cabi.EV_PERC_ENABLE: lambda a, b: L.setPercussionEnabled(t, a),
         cabi.EV_PERC_SOFT: lambda a, b: L.setPercussionVolume(t, a),
         cabi.EV_PERC_FAST: lambda a, b: L.setPercussionFast(t, a),

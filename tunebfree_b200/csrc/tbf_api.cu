@@ -294,12 +294,6 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
 
     TgSet s;
     s.host = *t;
-    CK(cudaMalloc(&s.rw, sizeof(uint16_t) * std::max<size_t>(1, nr)));
-    CK(cudaMalloc(&s.rn, sizeof(uint16_t) * std::max<size_t>(1, nr)));
-    if (nr) {
-        CK(cudaMemcpy(s.rw, run_wheel.data(), sizeof(uint16_t) * nr, cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(s.rn, run_count.data(), sizeof(uint16_t) * nr, cudaMemcpyHostToDevice));
-    }
     /* The device keeps four copies of every wave, copy s rotated left by s samples and extended
      * by one fragment of wrap-around: a 128-sample read from any position then starts 16-byte
      * aligned in copy (pos & 3) and never wraps, so a lane fetches its four consecutive samples
@@ -325,28 +319,44 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
                 i += n;
             }
     }
-    CK(cudaMalloc(&s.wave, sizeof(float) * std::max<size_t>(4, wave4.size())));
-    CK(cudaMalloc(&s.cw, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
-    CK(cudaMalloc(&s.cb, sizeof(uint16_t) * std::max<uint32_t>(1, nc)));
-    CK(cudaMalloc(&s.cl, sizeof(float) * std::max<uint32_t>(1, nc)));
-    if (!wave4.empty())
-        CK(cudaMemcpy(s.wave, wave4.data(), sizeof(float) * wave4.size(), cudaMemcpyHostToDevice));
+    /* one allocation and one copy per table set (config 4 uploads thousands of them): the wave
+     * store first, then the contribution and run arrays, each 16-byte aligned */
+    const size_t n_wave = std::max<size_t>(4, wave4.size());
+    auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
+    const size_t o_cl = up16(sizeof(float) * n_wave);
+    const size_t o_cw = up16(o_cl + sizeof(float) * nc);
+    const size_t o_cb = up16(o_cw + sizeof(uint16_t) * nc);
+    const size_t o_rw = up16(o_cb + sizeof(uint16_t) * nc);
+    const size_t o_rn = up16(o_rw + sizeof(uint16_t) * nr);
+    const size_t blob_bytes = up16(o_rn + sizeof(uint16_t) * nr) + 16;
+    wave4.resize((blob_bytes + sizeof(float) - 1) / sizeof(float), 0.f);
+    unsigned char *blob = reinterpret_cast<unsigned char *>(wave4.data());
     if (nc) {
-        CK(cudaMemcpy(s.cw, t->contrib_wheel, sizeof(uint16_t) * nc, cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(s.cb, t->contrib_bus, sizeof(uint16_t) * nc, cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(s.cl, t->contrib_level, sizeof(float) * nc, cudaMemcpyHostToDevice));
+        memcpy(blob + o_cl, t->contrib_level, sizeof(float) * nc);
+        memcpy(blob + o_cw, t->contrib_wheel, sizeof(uint16_t) * nc);
+        memcpy(blob + o_cb, t->contrib_bus, sizeof(uint16_t) * nc);
     }
+    if (nr) {
+        memcpy(blob + o_rw, run_wheel.data(), sizeof(uint16_t) * nr);
+        memcpy(blob + o_rn, run_count.data(), sizeof(uint16_t) * nr);
+    }
+    unsigned char *dev = nullptr;
+    CK(cudaMalloc(&dev, sizeof(float) * wave4.size()));
+    CK(cudaMemcpy(dev, blob, sizeof(float) * wave4.size(), cudaMemcpyHostToDevice));
+    s.wave = reinterpret_cast<float *>(dev); /* owns the allocation; the rest point into it */
+    s.cl = nullptr;
+    s.cw = s.cb = s.rw = s.rn = nullptr;
     s.host.wave_data = nullptr;
     s.host.contrib_wheel = s.host.contrib_bus = nullptr;
     s.host.contrib_level = nullptr;
 
     DevTonegenTables *d = new DevTonegenTables();
     d->wave4 = s.wave;
-    d->contrib_wheel = s.cw;
-    d->contrib_bus = s.cb;
-    d->contrib_level = s.cl;
-    d->run_wheel = s.rw;
-    d->run_count = s.rn;
+    d->contrib_wheel = reinterpret_cast<const uint16_t *>(dev + o_cw);
+    d->contrib_bus = reinterpret_cast<const uint16_t *>(dev + o_cb);
+    d->contrib_level = reinterpret_cast<const float *>(dev + o_cl);
+    d->run_wheel = reinterpret_cast<const uint16_t *>(dev + o_rw);
+    d->run_count = reinterpret_cast<const uint16_t *>(dev + o_rn);
     memcpy(d->run_start, run_start.data(), sizeof(d->run_start));
     d->coop_events = coop ? 1 : 0;
     memcpy(d->wave4_offset, wave4_offset, sizeof(d->wave4_offset));

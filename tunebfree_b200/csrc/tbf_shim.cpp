@@ -237,7 +237,7 @@ void setDrawBars(void *inst, unsigned int manual, unsigned int setting[])
     if (manual > 2)
         return; /* the reference asserts */
     for (int i = 0; i < 9; ++i)
-        setDrawBar((b_tonegen *)inst, (int)manual * 9 + i, setting[i]);
+        setDrawBar(((b_instance *)inst)->synth, (int)manual * 9 + i, setting[i]);
 }
 
 void setPercussionEnabled(struct b_tonegen *t, int v) { t->organ.push(TBF_EV_PERC_ENABLE, v); }
