@@ -56,6 +56,10 @@ struct tbf_ctx {
     size_t n_inst = 0, cap_inst = 0;
     std::vector<int> inst_tg, inst_wh;
     InstState *d_tmpl = nullptr;
+    /* table upload: page-locked staging and the device copy of the raw waves + their index,
+     * grown on demand (tbf_gpu_tonegen_tables_create) */
+    unsigned char *h_stage = nullptr, *d_stage = nullptr;
+    size_t cap_h_stage = 0, cap_d_stage = 0;
     /* per-render scratch, grown on demand */
     tbf_event *d_events = nullptr;
     size_t cap_events = 0;
@@ -198,6 +202,8 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     cudaFree(ctx->d_wh);
     cudaFree(ctx->d_states);
     cudaFree(ctx->d_tmpl);
+    cudaFreeHost(ctx->h_stage);
+    cudaFree(ctx->d_stage);
     cudaFree(ctx->d_events);
     cudaFree(ctx->d_ev_start);
     cudaFree(ctx->d_ev_cursor);
@@ -297,31 +303,23 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     /* The device keeps four copies of every wave, copy s rotated left by s samples and extended
      * by one fragment of wrap-around: a 128-sample read from any position then starts 16-byte
      * aligned in copy (pos & 3) and never wraps, so a lane fetches its four consecutive samples
-     * with one 16-byte cp.async (tbf_kernels.cu, wave_request). */
-    std::vector<float> wave4;
-    wave4.reserve(4 * ((size_t)t->wave_total + (size_t)TBF_NOF_WHEELS * (TBF_FRAGMENT + 8)));
+     * with one 16-byte cp.async (tbf_kernels.cu, wave_request).  The copies are made on the
+     * device from the raw waves (tbf_wave_store_kernel): a quarter of the bytes over the link. */
     uint32_t wave4_offset[TBF_NOF_WHEELS + 1] = {0};
+    size_t n_wave4 = 0;
     for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
         const uint32_t len = t->wave_length[w];
         if (!len)
             continue;
         const uint32_t cl = tbf_wave_copy_len(len);
-        if (wave4.size() + (size_t)4 * cl > 0xFFFFFFFFull)
+        if (n_wave4 + (size_t)4 * cl > 0xFFFFFFFFull)
             return fail(ctx, TBF_ERR_ARG, "tonegen tables: wave store too large");
-        wave4_offset[w] = (uint32_t)wave4.size();
-        const float *src = t->wave_data + t->wave_offset[w];
-        wave4.resize(wave4.size() + (size_t)4 * cl);
-        float *dst = wave4.data() + wave4_offset[w];
-        for (uint32_t c = 0; c < 4; ++c) /* dst[i] = src[(i + c) % len], i < cl */
-            for (uint32_t i = 0, pos = c % len; i < cl; pos = 0) {
-                const uint32_t n = std::min(cl - i, len - pos);
-                memcpy(dst + (size_t)c * cl + i, src + pos, sizeof(float) * n);
-                i += n;
-            }
+        wave4_offset[w] = (uint32_t)n_wave4;
+        n_wave4 += (size_t)4 * cl;
     }
-    /* one allocation and one copy per table set (config 4 uploads thousands of them): the wave
-     * store first, then the contribution and run arrays, each 16-byte aligned */
-    const size_t n_wave = std::max<size_t>(4, wave4.size());
+    /* one allocation per table set (config 4 uploads thousands of them): the wave store first,
+     * then the contribution and run arrays, each 16-byte aligned */
+    const size_t n_wave = std::max<size_t>(4, n_wave4);
     auto up16 = [](size_t x) { return (x + 15) & ~(size_t)15; };
     const size_t o_cl = up16(sizeof(float) * n_wave);
     const size_t o_cw = up16(o_cl + sizeof(float) * nc);
@@ -329,20 +327,62 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     const size_t o_rw = up16(o_cb + sizeof(uint16_t) * nc);
     const size_t o_rn = up16(o_rw + sizeof(uint16_t) * nr);
     const size_t blob_bytes = up16(o_rn + sizeof(uint16_t) * nr) + 16;
-    wave4.resize((blob_bytes + sizeof(float) - 1) / sizeof(float), 0.f);
-    unsigned char *blob = reinterpret_cast<unsigned char *>(wave4.data());
+    /* staging: [raw waves][wave_offset, wave_length, wave4_offset][the arrays behind the wave store] */
+    const size_t n_meta = 3 * (TBF_NOF_WHEELS + 1);
+    const size_t s_meta = up16(sizeof(float) * (size_t)t->wave_total);
+    const size_t s_tail = up16(s_meta + sizeof(uint32_t) * n_meta);
+    const size_t tail_bytes = blob_bytes - o_cl;
+    const size_t stage_bytes = s_tail + tail_bytes;
+    if (stage_bytes > ctx->cap_h_stage) {
+        cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr;
+        ctx->cap_h_stage = 0;
+        CK(cudaHostAlloc((void **)&ctx->h_stage, stage_bytes + (stage_bytes >> 2), cudaHostAllocDefault));
+        ctx->cap_h_stage = stage_bytes + (stage_bytes >> 2);
+    }
+    if (s_tail > ctx->cap_d_stage) {
+        cudaFree(ctx->d_stage);
+        ctx->d_stage = nullptr;
+        ctx->cap_d_stage = 0;
+        CK(cudaMalloc((void **)&ctx->d_stage, s_tail + (s_tail >> 2)));
+        ctx->cap_d_stage = s_tail + (s_tail >> 2);
+    }
+    unsigned char *hs = ctx->h_stage;
+    memcpy(hs, t->wave_data, sizeof(float) * (size_t)t->wave_total);
+    uint32_t *meta = reinterpret_cast<uint32_t *>(hs + s_meta);
+    memcpy(meta, t->wave_offset, sizeof(t->wave_offset));
+    memcpy(meta + (TBF_NOF_WHEELS + 1), t->wave_length, sizeof(t->wave_length));
+    memcpy(meta + 2 * (TBF_NOF_WHEELS + 1), wave4_offset, sizeof(wave4_offset));
+    unsigned char *tail = hs + s_tail - o_cl; /* tail + o_x = the staged copy of array x */
+    memset(hs + s_tail, 0, tail_bytes);
     if (nc) {
-        memcpy(blob + o_cl, t->contrib_level, sizeof(float) * nc);
-        memcpy(blob + o_cw, t->contrib_wheel, sizeof(uint16_t) * nc);
-        memcpy(blob + o_cb, t->contrib_bus, sizeof(uint16_t) * nc);
+        memcpy(tail + o_cl, t->contrib_level, sizeof(float) * nc);
+        memcpy(tail + o_cw, t->contrib_wheel, sizeof(uint16_t) * nc);
+        memcpy(tail + o_cb, t->contrib_bus, sizeof(uint16_t) * nc);
     }
     if (nr) {
-        memcpy(blob + o_rw, run_wheel.data(), sizeof(uint16_t) * nr);
-        memcpy(blob + o_rn, run_count.data(), sizeof(uint16_t) * nr);
+        memcpy(tail + o_rw, run_wheel.data(), sizeof(uint16_t) * nr);
+        memcpy(tail + o_rn, run_count.data(), sizeof(uint16_t) * nr);
     }
     unsigned char *dev = nullptr;
-    CK(cudaMalloc(&dev, sizeof(float) * wave4.size()));
-    CK(cudaMemcpy(dev, blob, sizeof(float) * wave4.size(), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&dev, blob_bytes));
+    cudaError_t ue = cudaMemcpyAsync(ctx->d_stage, hs, s_tail, cudaMemcpyHostToDevice, ctx->stream);
+    if (ue == cudaSuccess)
+        ue = cudaMemcpyAsync(dev + o_cl, hs + s_tail, tail_bytes, cudaMemcpyHostToDevice, ctx->stream);
+    if (ue == cudaSuccess && n_wave4 < n_wave)
+        ue = cudaMemsetAsync(dev, 0, sizeof(float) * n_wave, ctx->stream);
+    if (ue == cudaSuccess && n_wave4)
+        ue = (cudaError_t)tbf_launch_wave_store(reinterpret_cast<float *>(dev),
+                                                reinterpret_cast<const float *>(ctx->d_stage),
+                                                reinterpret_cast<const uint32_t *>(ctx->d_stage + s_meta),
+                                                ctx->stream);
+    if (ue == cudaSuccess)
+        ue = cudaStreamSynchronize(ctx->stream); /* the staging buffers are reused by the next call */
+    if (ue != cudaSuccess) {
+        cudaFree(dev);
+        ctx->err = std::string("tonegen tables upload: ") + cudaGetErrorString(ue);
+        return TBF_ERR_CUDA;
+    }
     s.wave = reinterpret_cast<float *>(dev); /* owns the allocation; the rest point into it */
     s.cl = nullptr;
     s.cw = s.cb = s.rw = s.rn = nullptr;

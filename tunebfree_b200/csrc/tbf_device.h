@@ -212,6 +212,7 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream);
 int tbf_launch_stage_r(const RenderParams &p, void *stream);
 int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream);
 int tbf_launch_stage_d(const RenderParams &p, void *stream);
+int tbf_launch_wave_store(float *wave4, const float *raw, const uint32_t *meta, void *stream);
 int tbf_launch_replicate(InstState *states, uint32_t first, uint32_t count, const InstState *dev_tmpl,
                          void *stream);
 

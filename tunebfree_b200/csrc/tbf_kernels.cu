@@ -2021,6 +2021,29 @@ __global__ void tbf_replicate_kernel(InstState *states, uint32_t first, uint32_t
     }
 }
 
+/* table upload: the four rotated, wrap-extended copies of every wave (tbf_wave_copy_len) from
+ * the raw waves: copy c of wheel w holds dst[i] = src[(i + c) % len], i < cl.  meta = wave_offset,
+ * wave_length, wave4_offset, 257 entries each.  blockIdx.x = wheel, blockIdx.y = copy */
+__global__ void tbf_wave_store_kernel(float *__restrict__ wave4, const float *__restrict__ raw,
+                                      const uint32_t *__restrict__ meta)
+{
+    const uint32_t w = blockIdx.x + 1, c = blockIdx.y;
+    const uint32_t len = meta[(TBF_NOF_WHEELS + 1) + w];
+    if (!len)
+        return;
+    const float *src = raw + meta[w];
+    const uint32_t cl = tbf_wave_copy_len(len);
+    float *dst = wave4 + meta[2 * (TBF_NOF_WHEELS + 1) + w] + (size_t)c * cl;
+    uint32_t pos = (threadIdx.x + c) % len;
+    const uint32_t step = blockDim.x % len;
+    for (uint32_t i = threadIdx.x; i < cl; i += blockDim.x) {
+        dst[i] = src[pos];
+        pos += step;
+        if (pos >= len)
+            pos -= len;
+    }
+}
+
 template <typename K> int set_smem(K kernel, size_t smem, int *have)
 {
     if (*have < (int)smem) {
@@ -2044,6 +2067,12 @@ static void debug_sync(void *stream, const char *stage)
     const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
     if (e != cudaSuccess)
         fprintf(stderr, "tbf: stage %s: %s\n", stage, cudaGetErrorString(e));
+}
+
+int tbf_launch_wave_store(float *wave4, const float *raw, const uint32_t *meta, void *stream)
+{
+    tbf_wave_store_kernel<<<dim3(TBF_NOF_WHEELS, 4), 256, 0, (cudaStream_t)stream>>>(wave4, raw, meta);
+    return (int)cudaGetLastError();
 }
 
 size_t tbf_stage_t_smem(void) { return sizeof(TWarp) * T_WARPS; }
