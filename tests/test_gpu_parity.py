@@ -16,8 +16,8 @@ from tunebfree_b200 import cabi, workloads
 pytestmark = pytest.mark.gpu
 
 
-def _make(ref, ctx, n=1, seed=1, cfg="", freqs=None):
-    r = ref.RefInstance(freqs=freqs, seed=seed, cfg=cfg)
+def _make(ref, ctx, n=1, seed=1, cfg="", freqs=None, rate=48000.0):
+    r = ref.RefInstance(freqs=freqs, seed=seed, cfg=cfg, rate=rate)
     tg = ctx.tonegen_tables(r.tonegen_tables())
     wh = ctx.whirl_tables(r.whirl_tables())
     first = ctx.create_instances(tg, wh, n)
@@ -59,8 +59,8 @@ def _bits(x):
     return np.ascontiguousarray(x).view(np.uint32)
 
 
-def _check(ref, ctx, events, n_frag, flags, seed=1, cfg="", freqs=None, whirl_state=True):
-    r, first = _make(ref, ctx, 1, seed, cfg, freqs)
+def _check(ref, ctx, events, n_frag, flags, seed=1, cfg="", freqs=None, whirl_state=True, rate=48000.0):
+    r, first = _make(ref, ctx, 1, seed, cfg, freqs, rate)
     rl, rr = r.render(n_frag, flags, events)
     gl, gr, cs = ctx.render(1, n_frag, [events], flags, ids=[first], checksums=True)
     bad = np.nonzero(_bits(gl[0]) != _bits(rl))[0]
@@ -87,6 +87,17 @@ def test_full_chain_config3(ref, gpu_ctx):
     """BASELINE config 3 shape: tonegen + vibrato C3 + Leslie fast through whirlProc3."""
     ev = workloads.instance_events(3, 800, config=3)
     peak = _check(ref, gpu_ctx, ev, 800, cabi.RENDER_WHIRLPROC3)
+    assert peak > 0.05
+
+
+@pytest.mark.parametrize("rate", [44100.0, 22050.0, 96000.0])
+def test_other_sample_rates(ref, gpu_ctx, rate):
+    """The hosts run the engine at the session's rate (SampleRateD): wave lengths, envelopes,
+    scanner increment, Leslie geometry and filters all scale with it."""
+    ev = workloads.instance_events(11, 500, config=3, restrike=120, hold=80)
+    ev += [(260, cabi.EV_REV_OPTION, 4, 0), (380, cabi.EV_REV_OPTION, 8, 0)]
+    ev.sort(key=lambda e: e[0])
+    peak = _check(ref, gpu_ctx, ev, 500, cabi.RENDER_WHIRLPROC3, rate=rate)
     assert peak > 0.05
 
 
