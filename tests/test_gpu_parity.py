@@ -163,6 +163,33 @@ def test_setters_midstream(ref, gpu_ctx):
     _check(ref, gpu_ctx, ev, 260, cabi.RENDER_WHIRLPROC3)
 
 
+def test_ragged_batch_silent_and_playing(ref, gpu_ctx):
+    """Ragged input: organs without any event (silence still runs through the stateful scanner
+    and the Leslie, src/tonegen.cpp:3600-3619), organs with control events only, organs whose
+    only events sit on the last fragment, next to playing ones -- in one batch of 70 slots
+    (three warps of lane = organ stages, the last one partly filled), 1 and 37 fragments."""
+    r, first = _make(ref, gpu_ctx, 70)
+    r.close()
+    scripts = [[], workloads.setup_events(3), [(36, cabi.EV_KEY_ON, 60, 0)],
+               workloads.instance_events(2, 37, config=3, restrike=12, hold=7)]
+    evs = [scripts[i % 4] for i in range(70)]
+    refs = []
+    for sc in scripts:
+        rr_ = _make(ref, gpu_ctx, 1)[0]
+        a = rr_.render(1, cabi.RENDER_WHIRLPROC3, [e for e in sc if e[0] < 1])
+        b = rr_.render(37, cabi.RENDER_WHIRLPROC3, [(e[0], e[1], e[2], e[3]) for e in sc])
+        refs.append((a, b))
+        rr_.close()
+    ids = list(range(first, first + 70))
+    g1 = gpu_ctx.render(70, 1, [[e for e in sc if e[0] < 1] for sc in evs], cabi.RENDER_WHIRLPROC3, ids=ids)
+    g2 = gpu_ctx.render(70, 37, evs, cabi.RENDER_WHIRLPROC3, ids=ids)
+    for i in range(70):
+        a, b = refs[i % 4]
+        for ch in (0, 1):
+            assert np.array_equal(_bits(g1[ch][i]), _bits(a[ch])), (i, ch)
+            assert np.array_equal(_bits(g2[ch][i]), _bits(b[ch])), (i, ch)
+
+
 def test_all_61_keys_and_release(ref, gpu_ctx):
     """Many active wheels (169 wheels / 221 core instructions in the reference: close
     to its 256-instruction corePgm), then full release down to an empty active list."""
