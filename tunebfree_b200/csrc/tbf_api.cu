@@ -463,7 +463,9 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
     s.host = *w;
     const size_t N = TBF_WHIRL_DISPLC;
     /* device layout: 4 displacement tables as pairs (2N floats each), then the two FIR banks
-     * padded to 8 floats per position */
+     * as five planes of N floats (coefficient c of position k at [c][k]): the 32 lanes of a warp
+     * read positions a few steps apart, so a plane read touches ~3 cache lines where an
+     * array-of-positions layout touches one 32-byte sector per lane */
     {
         std::vector<float> t(N * 24, 0.0f);
         const float *src[4] = {w->hn_fwd_displ, w->hn_bwd_displ, w->dr_fwd_displ, w->dr_bwd_displ};
@@ -476,7 +478,7 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
         for (int i = 0; i < 2; ++i)
             for (size_t k = 0; k < N; ++k)
                 for (int c = 0; c < 5; ++c)
-                    t[8 * N + 8 * N * i + 8 * k + c] = fir[i][5 * k + c];
+                    t[8 * N + 8 * N * i + (size_t)c * N + k] = fir[i][5 * k + c];
         CK(cudaMalloc(&s.tables, sizeof(float) * t.size()));
         CK(cudaMemcpy(s.tables, t.data(), sizeof(float) * t.size(), cudaMemcpyHostToDevice));
     }

@@ -141,7 +141,7 @@ struct DevTonegenTables {
 struct DevWhirlTables {
     /* displacement tables as pairs {d[k], d[(k + 1) & mask]} (one 8-byte load per tap) */
     const float2 *hn_fwd_displ, *hn_bwd_displ, *dr_fwd_displ, *dr_bwd_displ;
-    const float *bfw, *bbw; /* FIR banks, 8 floats per position: b0..b4, three of padding */
+    const float *bfw, *bbw; /* FIR banks, five planes of 16384: coefficient c of position k at [c][k] */
     double sample_rate;
     double fw_ang, bw_ang;          /* micAngle*.25, 1 + micAngle*-.25  (whirl.cpp:1379-1380) */
     double one_minus_l[4];          /* 1 - exp(-1/(SR/128*tau)), tau = hornAcc hornDec drumAcc

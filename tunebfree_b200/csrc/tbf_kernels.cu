@@ -1516,7 +1516,7 @@ __global__ void __launch_bounds__(64) tbf_stage_r(const RenderParams p)
  * per-tap registers statically. */
 struct WTap {
     const float2 *dsp; /* displacement table as pairs {d[k], d[k+1]}                    */
-    const float *bw;   /* horn: FIR bank, 8 floats per table position; drum: unused       */
+    const float *bw;   /* horn: FIR bank, five planes of 16384 coefficients; drum: unused    */
     double ang_off;    /* horn: microphone angle offset added to the rotor angle         */
     float spacing;
     int phase;
@@ -1758,13 +1758,13 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
                 uint32_t kr;
                 tap_position(__dadd_rn(hang, t.ang_off), t.phase, t.dsp, t.spacing, outpos, frac, tn[j], kr);
                 const float *hx = &sm.hx[t.stage][8 + i];
-                const float *b = t.bw + 8 * kr;
-                const float4 b03 = __ldg(reinterpret_cast<const float4 *>(b));
-                const float b4 = __ldg(b + 4);
-                float xa = __fmul_rn(b03.x, hx[0]);
-                xa = __fadd_rn(xa, __fmul_rn(b03.y, hx[-1]));
-                xa = __fadd_rn(xa, __fmul_rn(b03.z, hx[-2]));
-                xa = __fadd_rn(xa, __fmul_rn(b03.w, hx[-3]));
+                const float *b = t.bw + kr;
+                const float b0 = __ldg(b), b1 = __ldg(b + DISPLC_MASK + 1), b2 = __ldg(b + 2 * (DISPLC_MASK + 1));
+                const float b3 = __ldg(b + 3 * (DISPLC_MASK + 1)), b4 = __ldg(b + 4 * (DISPLC_MASK + 1));
+                float xa = __fmul_rn(b0, hx[0]);
+                xa = __fadd_rn(xa, __fmul_rn(b1, hx[-1]));
+                xa = __fadd_rn(xa, __fmul_rn(b2, hx[-2]));
+                xa = __fadd_rn(xa, __fmul_rn(b3, hx[-3]));
                 xa = __fadd_rn(xa, __fmul_rn(b4, hx[-4]));
                 const float qq = __fmul_rn(xa, frac);
                 ta[j] = __fsub_rn(xa, qq);
