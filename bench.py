@@ -313,6 +313,8 @@ def run_gpu_arm(a):
         groups = {variant(first_global + slots[0]): slots for slots in per_set if slots}
 
     ctx = engine.Context(local_rank)
+    if os.environ.get("TBF_BENCH_HOST_CHUNK"):  # fragments per device->host staging chunk (sweeps)
+        ctx.set_host_chunk(int(os.environ["TBF_BENCH_HOST_CHUNK"]))
     # table sets built by the product's own host-side builder: wave tables per (osc variant,
     # engine seed), Leslie tables per whirl variant
     tg_handles, wh_handles = {}, {}
