@@ -303,7 +303,7 @@ def run_gpu_arm(a):
     variant = lambda g: workloads.organ_variant(g, a.config)
     if a.config == 4:
         # rank r plays scales [r * n_inst, (r + 1) * n_inst) of the sweep (wrapping around)
-        global_ids = (rank * n_inst + np.arange(n_inst, dtype=np.int64)) % len(sweep_names)
+        global_ids = sharding.shard_plan_sweep(rank, world, n_inst, len(sweep_names))
         groups = {}
     elif a.config == 5:
         global_ids, groups = sharding.shard_plan_grouped(rank, world, n_inst, variant)

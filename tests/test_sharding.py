@@ -102,3 +102,18 @@ def test_grouped_plan_sorts_by_table_key_and_partitions_every_organ():
     assert workloads.organ_variant(7, 3) == ("default", "default", 8)
     with pytest.raises(ValueError):
         sharding.shard_plan_grouped(3, 2, 4, key)
+
+
+def test_sweep_plan_covers_every_scale_once():
+    """Config 4: the ranks' blocks of the Scala sweep are disjoint and cover it; a rank asked for
+    the whole sweep gets every scale once, rotated by its rank."""
+    from tunebfree_b200 import sharding, workloads
+    n = len(workloads.scala_sweep()[0])
+    assert n == 5176
+    per = n // 8
+    seen = np.concatenate([sharding.shard_plan_sweep(r, 8, per, n) for r in range(8)])
+    assert len(np.unique(seen)) == 8 * per == n
+    whole = sharding.shard_plan_sweep(3, 8, n, n)
+    assert sorted(whole.tolist()) == list(range(n)) and whole[0] == (3 * n) % n
+    with pytest.raises(ValueError):
+        sharding.shard_plan_sweep(8, 8, 10, n)

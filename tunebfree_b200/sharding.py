@@ -34,6 +34,16 @@ def shard_plan_grouped(rank, world, per_gpu, key_of):
     return np.asarray(mine, dtype=np.int64), groups
 
 
+def shard_plan_sweep(rank, world, per_gpu, n_items):
+    """Config 4 (one organ per Scala scale): rank r plays items [r * per_gpu, (r + 1) * per_gpu)
+    of the sweep, wrapping around its end, so with per_gpu * world == n_items every scale is
+    rendered exactly once and with per_gpu == n_items every GPU renders the whole sweep (weak
+    scaling).  -> int64 item index of every batch slot."""
+    if not (0 <= rank < world) or per_gpu <= 0 or n_items <= 0:
+        raise ValueError("bad shard arguments")
+    return (rank * per_gpu + np.arange(per_gpu, dtype=np.int64)) % n_items
+
+
 def slot_instance_ids(per_set, create):
     """create(set index or key, count) -> first instance handle of `count` new instances.
     per_set: list indexed by set (shard_plan) or {key: slots} (shard_plan_grouped).
