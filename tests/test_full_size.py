@@ -1,4 +1,4 @@
-"""Full-size runs (BASELINE.json configs 2 and 3 instance counts) checked through properties
+"""Full-size runs (BASELINE.json configs 2, 3, 4 and 5 instance counts) checked through properties
 that do not need the audio on the host: a position-keyed checksum of every organ's L/R bit
 patterns is formed on the device; sampled organs are compared with the oracle's render of the
 same events through the same checksum ("a checksum of checksums"), the run is repeated after a
@@ -87,3 +87,48 @@ def test_config5_cfg_mix_16384_organs(ref, gpu_ctx):
         assert engine.checksum_host(l, rr) == int(cs[slot_of[g]]), (g, osc, whirl, seed)
     for s in (0, n // 3, n - 1):
         assert gpu_ctx.export_state(int(ids[s])).error_flags == 0
+
+
+def test_config4_scala_sweep_all_scales(ref):
+    """BASELINE config 4 at its full size: one organ per scale of the reference's Scala archive
+    (5176 tunings, each with its own wave store built by the product's table builder on the host
+    cores), 0.5 s of the sweep chord through tonegen + vibrato + Leslie.  Every 173rd organ is
+    rendered by the oracle from the same 128 frequencies and compared through the device
+    checksum; different tunings must give different audio."""
+    from concurrent.futures import ThreadPoolExecutor
+    import os
+    from tunebfree_b200 import tables
+    names, degs, _ = workloads.scala_sweep()
+    n, n_frag = len(names), 188
+    ctx = engine.Context(0)  # own context: 31 GB of wave stores are released with it
+    tt0, wt0 = tables.InstanceSpec(seed=1).build()
+    wh = ctx.whirl_tables(wt0)
+    tables.free_tables(tt0, wt0)
+
+    def build(g):
+        return tables.InstanceSpec(freqs=tables.freqs_from_ratios(degs[g]), seed=1).build_tonegen()
+
+    ids = []
+    with ThreadPoolExecutor(os.cpu_count() or 1) as pool:
+        for lo in range(0, n, 256):
+            for tt in pool.map(build, range(lo, min(n, lo + 256))):
+                ids.append(ctx.create_instances(ctx.tonegen_tables(tt), wh, 1))
+                tables.free_tables(tt, None)
+    sc = workloads.instance_events(0, n_frag, config=4)
+    ev_np = np.concatenate([np.concatenate([np.full((len(sc), 1), s, dtype=np.int32),
+                                            np.array(sorted(sc, key=lambda e: e[0]), dtype=np.int32)], axis=1)
+                            for s in range(n)], axis=0)
+    ev = engine.events_from_numpy(ev_np)
+    flags = workloads.render_flags(4)
+    cs = np.zeros(n, dtype=np.uint64)
+    ctx.render_device(n, n_frag, ev, flags, None, None, n_frag * 128, ids=ids, checksums=cs)
+    # duplicates exist in the archive (the same scale under two names); most tunings differ
+    assert len(set(cs.tolist())) > 0.9 * n
+    for i in range(0, n, 173):
+        r = ref.RefInstance(freqs=tables.freqs_from_ratios(degs[i]), seed=1)
+        l, rr = r.render(n_frag, flags, sc)
+        r.close()
+        assert engine.checksum_host(l, rr) == int(cs[i]), names[i]
+    for i in (0, n // 2, n - 1):
+        assert ctx.export_state(ids[i]).error_flags == 0
+    ctx.close()
