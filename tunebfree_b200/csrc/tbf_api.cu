@@ -160,10 +160,12 @@ int tbf_gpu_create(tbf_ctx **out, int device)
      * whenever an SM has room, so they run beside the throughput stages instead of after */
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    const int prio_mask = getenv("TBF_PRIO_MASK") ? atoi(getenv("TBF_PRIO_MASK")) : 10; /* bit s: stage s high; measured 0: 145.5 k, 2: 148.5 k,
+                                                                              4: 139.7 k, 8: 145.1 k, 10: 148.9 k, 14: 149.5 k, 15: 145.5 k */
     for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g)
         for (int st = 0; st < 4 && ok; ++st) {
             ok = cudaStreamCreateWithPriority(&ctx->sstream[g][st], cudaStreamNonBlocking,
-                                              (st & 1) ? prio_hi : prio_lo) == cudaSuccess;
+                                              ((prio_mask >> st) & 1) ? prio_hi : prio_lo) == cudaSuccess;
             for (int b = 0; ok && b < TBF_MAX_STAGE_BUFS; ++b)
                 ok = cudaEventCreateWithFlags(&ctx->sdone[g][st][b], cudaEventDisableTiming) == cudaSuccess;
         }
