@@ -69,6 +69,8 @@ def parse_args():
                          "the project's stock -O3 -ffast-math flags (timing only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true",
+                    help="skip the sampled bit-for-bit comparison of the timed audio with the oracle")
     a = ap.parse_args()
     if a.seconds <= 0:
         a.seconds = 2.0 if a.config == 4 else 10.0
@@ -78,56 +80,67 @@ def parse_args():
 # --------------------------------------------------------------------------
 # CPU arm: the reference's own engine (oracle/_ref), one instance per host core
 # --------------------------------------------------------------------------
-def _cpu_worker(args):
-    """Runs in a forked worker: init its instances, wait for the common start time, render."""
-    ids, n_frag, config, start_at = args
+_CPU_BARRIER = None  # multiprocessing.Barrier shared with the forked workers
+
+
+def _ref_instance(g, config):
+    """A fresh reference organ for global organ id g of a config: every script gets its own
+    engine, so no key of another script is still held when it starts (the GPU arm gives every
+    organ its own instance too)."""
     from oracle import ref_engine
     from tunebfree_b200 import workloads
-    # a few engine instances per worker, cycled: the render cost does not depend on which
-    # organ plays which script, and 3 MB per reference instance adds up on many-core hosts
-    engines = []
-    for i in ids[:4]:
-        if config == 4:  # one tuning per organ: organ i plays scale i of the sweep
-            from tunebfree_b200 import tables
-            degs = workloads.scala_sweep()[1]
-            engines.append(ref_engine.RefInstance(seed=1, freqs=tables.freqs_from_ratios(degs[i % len(degs)])))
-            continue
-        osc, whirl, seed = workloads.organ_variant(i, config)
-        engines.append(ref_engine.RefInstance(seed=seed, cfg=workloads.variant_cfg(osc, whirl)))
-    insts = []
-    for j, i in enumerate(ids):
-        ev = workloads.instance_events(i, n_frag, config)
-        insts.append((engines[j % len(engines)], ref_engine.events_array(ev)))
+    if config == 4:  # one tuning per organ: organ g plays scale g of the sweep
+        from tunebfree_b200 import tables
+        degs = workloads.scala_sweep()[1]
+        return ref_engine.RefInstance(seed=1, freqs=tables.freqs_from_ratios(degs[g % len(degs)]))
+    osc, whirl, seed = workloads.organ_variant(g, config)
+    return ref_engine.RefInstance(seed=seed, cfg=workloads.variant_cfg(osc, whirl))
+
+
+def _cpu_worker(args):
+    """Runs in a forked worker: init its instances, meet the other workers, render."""
+    ids, n_frag, config = args
+    from oracle import ref_engine
+    from tunebfree_b200 import workloads
+    insts = [(_ref_instance(i, config), ref_engine.events_array(workloads.instance_events(i, n_frag, config)))
+             for i in ids]
     flags = workloads.render_flags(config)
     outl = np.zeros(n_frag * 128, dtype=np.float32)
     outr = np.zeros(n_frag * 128, dtype=np.float32)
     L = ref_engine.lib()
     import ctypes as C
-    while time.time() < start_at:
-        time.sleep(0.001)
+    _CPU_BARRIER.wait()  # every worker has finished its inits
     t0 = time.time()
     for r, (arr, n) in insts:
         L.ref_render(r._h, n_frag, flags, arr, n, outl.ctypes.data_as(C.c_void_p),
                      outr.ctypes.data_as(C.c_void_p))
     t1 = time.time()
-    return t0, t1, float(np.abs(outl).max())
+    frags = wheels = 0
+    for r, _ in insts:
+        st = r.export_state()
+        frags += st.stat_fragments
+        wheels += st.stat_active_wheels
+        r.close()
+    return t0, t1, frags, wheels
 
 
 def cpu_reference_pass(config, n_frag, per_core, cores):
-    """One bounded sample: cores x per_core instances of n_frag fragments on `cores` worker
-    processes (the engine is single-threaded and rand() is process-global).  Returns
-    organ-seconds/s over the common render window."""
+    """One bounded sample: cores x per_core organs of n_frag fragments on `cores` worker
+    processes (the engine is single-threaded and rand() is process-global), one fresh engine
+    per organ.  Returns (organ-seconds/s over the common render window, seconds, time-averaged
+    active wheels of the sample)."""
+    global _CPU_BARRIER
     import multiprocessing as mp
     ctx = mp.get_context("fork")
-    start_at = time.time() + 3.0 + 0.01 * per_core  # every worker finishes its inits first
-    jobs = [(list(range(c * per_core, (c + 1) * per_core)), n_frag, config, start_at)
-            for c in range(cores)]
+    _CPU_BARRIER = ctx.Barrier(cores)
+    jobs = [(list(range(c * per_core, (c + 1) * per_core)), n_frag, config) for c in range(cores)]
     with ctx.Pool(cores) as pool:
-        res = pool.map(_cpu_worker, jobs)
+        res = pool.map(_cpu_worker, jobs, chunksize=1)
     t0 = min(r[0] for r in res)
     t1 = max(r[1] for r in res)
     organ_seconds = cores * per_core * n_frag / 375.0
-    return organ_seconds / (t1 - t0), t1 - t0
+    n_act = sum(r[3] for r in res) / max(1, sum(r[2] for r in res))
+    return organ_seconds / (t1 - t0), t1 - t0, n_act
 
 
 def cpu_sample_plan(config, seconds, target_cpu_seconds, cores):
@@ -136,6 +149,45 @@ def cpu_sample_plan(config, seconds, target_cpu_seconds, cores):
     per_core_rate = 45.0 if config >= 3 else 350.0
     per_core = max(1, int(round(target_cpu_seconds * per_core_rate / seconds)))
     return per_core
+
+
+def _parity_worker(args):
+    """Forked worker: the oracle's render of ONE organ of the timed batch, replayed over every
+    pass bench.py makes (the organs keep their state from pass to pass); returns the audio of the
+    passes listed in `keep` for the bit-for-bit comparison with what the GPU arm timed."""
+    g, n_frag, config, n_pass, keep, slices = args
+    from tunebfree_b200 import workloads
+    r = _ref_instance(g, config)
+    ev = sorted(workloads.instance_events(g, n_frag, config), key=lambda e: e[0])
+    flags = workloads.render_flags(config)
+    out = {}
+    for k in range(n_pass):
+        l, rr = r.render(n_frag, flags, ev)
+        if k in keep:
+            out[k] = (l, rr)
+    r.close()
+    return g, out
+
+
+def parity_reference(global_ids_sampled, n_frag, config, n_pass, keep):
+    """{organ: {pass: (L, R)}} from the oracle, computed on forked workers BEFORE the CUDA context
+    exists (checker only: nothing of this is timed or shipped)."""
+    import multiprocessing as mp
+    ctx = mp.get_context("fork")
+    jobs = [(int(g), n_frag, config, n_pass, tuple(keep), 1) for g in global_ids_sampled]
+    with ctx.Pool(min(len(jobs), os.cpu_count() or 1)) as pool:
+        return dict(pool.map(_parity_worker, jobs, chunksize=1))
+
+
+def bench_config(a, n_inst, world, table_sets=None, whirl_sets=None):
+    """The workload description both arms print (the reference arm runs a bounded sample of it)."""
+    frames = int(round(a.seconds * 375)) * 128
+    return {"workload": WORKLOAD_NAME[a.config], "instances_per_gpu": n_inst,
+            "seconds_per_instance": a.seconds, "sample_rate": 48000,
+            "tuning": "one Scala scale per organ" if a.config == 4 else "12-TET",
+            "l2": "inputs larger than L2 (instance state %.0f MB + %.1f GB of output per step)"
+                  % (n_inst * 0.08, 2 * n_inst * frames * 4 / 1e9),
+            "parallelism": "instances sharded over %d GPU(s), no collective" % world}
 
 
 def run_reference_arm(a):
@@ -149,28 +201,30 @@ def run_reference_arm(a):
     cores = os.cpu_count() or 1
     n_frag = int(round(a.seconds * 375))
     per_core = cpu_sample_plan(a.config, a.seconds, a.cpu_sample_seconds, cores)
-    vals = []
+    vals, acts = [], []
     for _ in range(a.warmup and 1):  # one short warm-up pass: page in the library, spin clocks up
         cpu_reference_pass(a.config, max(8, n_frag // 20), 1, cores)
     t_all = 0.0
     for _ in range(a.steps):
-        v, dt = cpu_reference_pass(a.config, n_frag, per_core, cores)
+        v, dt, n_act = cpu_reference_pass(a.config, n_frag, per_core, cores)
         vals.append(v)
+        acts.append(n_act)
         t_all += dt
     value = float(np.mean(vals))
-    sample = "%d instances x %.1f s (%d per core) per step, oracle/_ref = reference engine, %s" % (
+    sample = "%d instances x %.1f s (%d per core, a fresh engine each) per step, oracle/_ref = reference engine, %s" % (
         cores * per_core, a.seconds, per_core,
         "stock flags -O3 -ffast-math (not bit-exact with the oracle)" if a.ref_build == "stock"
         else "strict IEEE -O2")
+    n_inst = a.instances or DEFAULT_INSTANCES[a.config] or 5176
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * t_all / max(1, a.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAME[a.config], "instances_per_step": cores * per_core,
-                   "seconds_per_instance": a.seconds, "sample_rate": 48000, "host_cores": cores},
+        "config": bench_config(a, n_inst, int(os.environ.get("WORLD_SIZE", "1"))),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
-                         "sample": sample},
+                         "sample": sample, "instances_per_step": cores * per_core,
+                         "n_act": float(np.mean(acts))},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -255,41 +309,14 @@ def run_gpu_arm(a):
         n_frag_cpu = int(round(a.seconds * 375))
         per_core = cpu_sample_plan(a.config, a.seconds, a.cpu_sample_seconds, cores)
         cpu_reference_pass(a.config, max(8, n_frag_cpu // 20), 1, cores)
-        v, _ = cpu_reference_pass(a.config, n_frag_cpu, per_core, cores)
+        v, _, cpu_n_act = cpu_reference_pass(a.config, n_frag_cpu, per_core, cores)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference",
-                        "sample": "%d instances x %.1f s (%d per core), oracle/_ref = the reference "
-                                  "engine compiled strict IEEE -O2, one process per core"
-                                  % (cores * per_core, a.seconds, per_core)}
+                        "sample": "%d instances x %.1f s (%d per core, a fresh engine each), oracle/_ref = "
+                                  "the reference engine compiled strict IEEE -O2, one process per core"
+                                  % (cores * per_core, a.seconds, per_core),
+                        "n_act": cpu_n_act}
 
-    import torch
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        # NCCL prints its banner on file descriptor 1 when the communicator comes up
-        sys.stdout.flush()
-        saved = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-            dist.barrier()
-            torch.cuda.synchronize()
-        finally:
-            os.dup2(saved, 1)
-            os.close(saved)
     from tunebfree_b200 import cabi, engine, tables, workloads
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
     n_inst = a.instances or DEFAULT_INSTANCES[a.config]
     if a.config == 4:
         sweep_names, sweep_degs, _ = workloads.scala_sweep()
@@ -311,6 +338,49 @@ def run_gpu_arm(a):
         first_global, per_set = sharding.shard_plan(rank, world, n_inst, N_TABLE_SETS)
         global_ids = first_global + np.arange(n_inst, dtype=np.int64)
         groups = {variant(first_global + slots[0]): slots for slots in per_set if slots}
+
+    # sampled organs of the timed batch, rendered by the oracle over every pass this run makes
+    # (forked workers: before this process owns a CUDA context); compared bit for bit with the
+    # audio of the last timed pass of both legs, outside the timed regions
+    e2e_warm = max(1, min(a.warmup, 2))
+    pass_dev = a.warmup + a.steps - 1
+    pass_e2e = a.warmup + a.steps + 1 + e2e_warm + a.steps - 1
+    parity_ref = None
+    if not a.no_parity_check:
+        n_samp = 8 if world == 1 else 4
+        samp_slots = sorted(set(int(round(k * (n_inst - 1) / max(1, n_samp - 1))) for k in range(n_samp)))
+        keep = [pass_dev] + ([] if a.no_e2e else [pass_e2e])
+        parity_ref = parity_reference([global_ids[s_] for s_ in samp_slots], n_frag, a.config,
+                                      (pass_dev if a.no_e2e else pass_e2e) + 1, keep)
+
+
+    import torch
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        # NCCL prints its banner on file descriptor 1 when the communicator comes up
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     ctx = engine.Context(local_rank)
     if os.environ.get("TBF_BENCH_HOST_CHUNK"):  # fragments per device->host staging chunk (sweeps)
@@ -403,8 +473,22 @@ def run_gpu_arm(a):
     clocks = sampler.stop()
     total_ms = max_over_ranks(total_ms)
     peak_out = float(out[0, 0].abs().max().item())
+    parity = None
+    if parity_ref is not None:
+        bad = 0
+        for s_ in samp_slots:
+            l_ref, r_ref = parity_ref[int(global_ids[s_])][pass_dev]
+            got = out[:, s_].cpu().numpy()
+            if not (np.array_equal(got[0].view(np.uint32), l_ref.view(np.uint32))
+                    and np.array_equal(got[1].view(np.uint32), r_ref.view(np.uint32))):
+                bad += 1
+        parity = {"organs": len(samp_slots), "slots": samp_slots, "pass": pass_dev,
+                  "device_resident_mismatches": bad,
+                  "what": "audio of the last timed pass of the sampled organs, bit patterns, against the "
+                          "oracle replaying every pass; checked outside the timed region"}
     st = ctx.export_state(int(ids[0]))
-    n_act = st.stat_active_wheels / max(1, st.stat_fragments)
+    stat_f, stat_w = ctx.instance_stats(ids)  # every organ of the batch, every pass so far
+    n_act = stat_w / max(1, stat_f)
     # per-stage device times: one extra pass with every stage kernel alone between two CUDA
     # events on its launch stream (outside the timed region: it removes the overlap)
     ctx.set_stage_profiling(True)
@@ -433,16 +517,37 @@ def run_gpu_arm(a):
         except (OSError, IndexError, ValueError):
             pass
         bounds = [int(round(k * n_frag / slices)) for k in range(slices + 1)]
-        slice_frames = max(bounds[k + 1] - bounds[k] for k in range(slices)) * 128
+        slice_frag = max(bounds[k + 1] - bounds[k] for k in range(slices))
+        slice_frames = slice_frag * 128
+        # host layout: chunk-major (TBF_RENDER_OUT_CHUNKED: every staging chunk crosses the link as
+        # one contiguous copy per channel) unless TBF_BENCH_E2E_LAYOUT=rows asks for [organ][sample]
+        chunked = os.environ.get("TBF_BENCH_E2E_LAYOUT", "chunks") != "rows"
+        hchunk = ctx.host_chunk()
+        n_hchunks = -(-slice_frag // hchunk)
+        shape = (n_hchunks, n_inst, hchunk * 128) if chunked else (n_inst, slice_frames)
+        e2e_flags = flags | (cabi.RENDER_OUT_CHUNKED if chunked else 0)
+        wc = bool(os.environ.get("TBF_BENCH_E2E_WC"))
         try:
-            hl, pl = ctx.host_alloc((n_inst, slice_frames))
-            hr, pr = ctx.host_alloc((n_inst, slice_frames))
+            hl, pl = ctx.host_alloc(shape, write_combined=wc)
+            hr, pr = ctx.host_alloc(shape, write_combined=wc)
             pinned = True
         except MemoryError:
-            hl = np.empty((n_inst, slice_frames), dtype=np.float32)
-            hr = np.empty((n_inst, slice_frames), dtype=np.float32)
+            hl = np.empty(shape, dtype=np.float32)
+            hr = np.empty(shape, dtype=np.float32)
             pl = pr = None
             pinned = False
+
+        def host_rows(h, slot, n_frames):
+            """the last call's audio of one slot as a flat array"""
+            if chunked:
+                return h[:, slot, :].reshape(-1)[:n_frames]
+            return h[slot, :n_frames]
+
+        # the link's own ceiling: a plain contiguous 1 GiB device -> page-locked host copy on
+        # every rank at once (outside the timed region)
+        barrier()
+        link_gbs = ctx.measure_d2h(1 << 30, 3)
+        barrier()
         if slices == 1:
             parts = [(n_frag, events)]
         else:
@@ -457,13 +562,13 @@ def run_gpu_arm(a):
 
         def e2e_step():
             for nf_k, ev_k in parts:
-                ctx.prepare(n_inst, nf_k, ev_k, flags, hl.ctypes.data, hr.ctypes.data, slice_frames,
+                ctx.prepare(n_inst, nf_k, ev_k, e2e_flags, hl.ctypes.data, hr.ctypes.data, slice_frames,
                             ids=ids)
                 ctx.launch()
                 ctx.synchronize()
                 e2e_count[0] += ctx.last_launch_ms()[1]
 
-        for _ in range(max(1, min(a.warmup, 2))):
+        for _ in range(e2e_warm):
             e2e_step()
         barrier()
         e2e_count[0] = 0
@@ -476,12 +581,39 @@ def run_gpu_arm(a):
         dt = max_over_ranks(dt)
         e2e = {"value": world * organ_seconds_step * a.steps / dt, "unit": UNIT,
                "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": int(2 * n_inst * frames * 4),
-               "host_buffers": "page-locked" if pinned else "pageable", "time_slices": slices,
-               "peak_abs_sample": float(np.abs(hl[0]).max())}
+               "host_buffers": ("page-locked" if pinned else "pageable") + (", write-combined" if wc else ""),
+               "host_layout": "chunk-major [chunk][organ][%d samples] (TBF_RENDER_OUT_CHUNKED)" % (hchunk * 128)
+                              if chunked else "[organ][sample]",
+               "time_slices": slices,
+               "peak_abs_sample": float(np.abs(host_rows(hl, 0, slice_frames)).max())}
+        # audio bytes over the link per second against the link's own contiguous-copy rate
+        link_min = -max_over_ranks(-link_gbs)
+        e2e["link_peak_gbs"] = link_min
+        e2e["link_peak_what"] = ("slowest rank's plain contiguous 1 GiB device -> page-locked host "
+                                 "cudaMemcpyAsync, all %d rank(s) copying at once" % world)
+        e2e["audio_gbs_per_gpu"] = e2e["d2h_bytes_per_step"] * a.steps / dt / 1e9
+        e2e["frac_of_link"] = e2e["audio_gbs_per_gpu"] / link_min if link_min > 0 else None
+        if parity is not None:
+            bad = 0
+            lo = bounds[-2] * 128  # the host buffers hold the last time slice of the last pass
+            for s_ in samp_slots:
+                l_ref, r_ref = parity_ref[int(global_ids[s_])][pass_e2e]
+                nfr = l_ref.shape[0] - lo
+                if not (np.array_equal(host_rows(hl, s_, nfr).view(np.uint32), l_ref[lo:].view(np.uint32))
+                        and np.array_equal(host_rows(hr, s_, nfr).view(np.uint32), r_ref[lo:].view(np.uint32))):
+                    bad += 1
+            parity["e2e_mismatches"] = bad
+            parity["e2e_pass"] = pass_e2e
         if pl:
             ctx.host_free(pl)
             ctx.host_free(pr)
 
+    if parity is not None and dist is not None:  # mismatches of every rank's sampled organs
+        keys = ["device_resident_mismatches"] + (["e2e_mismatches"] if "e2e_mismatches" in parity else [])
+        t = torch.tensor([parity[k] for k in keys] + [parity["organs"]], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        for k, v in zip(keys + ["organs"], t.tolist()):
+            parity[k] = int(v)
     if rank == 0:
         peaks = measured_peaks()
         hbm_peak = peaks["hbm_gbs"] if peaks else 6650.0
@@ -500,9 +632,18 @@ def run_gpu_arm(a):
         stage_bytes = {"T": 48000 * (4 * n_act + 8), "R": 48000 * (8 + 24), "W": 48000 * (24 + 16),
                        "D": 48000 * (20 + 8)}
         ach_hbm = stage_bytes[dom] * secs_per_dom_launch / dur / 1e9
-        # algorithmic work of the whole path per organ-second
+        # algorithmic work per organ-second: FP32 lane-ops (mul / add / sub = 1 each,
+        # the reference allows no FMA) W32 = 48000 (6 N_act + 17 + 253 [whirl]) and shared-memory
+        # bytes Bsm = 48000 (4 N_act + 70 + 380 [whirl]); per stage:
+        # T = 6 N_act + 11 (wheel sum, scanner, percussion differencer), R = 6 (mixdown) + 18 (two
+        # horn biquads), W = 198 (taps: interpolation, FIRs, fractional scatter), D = 18 (two drum
+        # biquads) + 19 (levels, leak, whirlProc3 mix)
         w32 = 48000 * (6 * n_act + 17 + 253 * whirl)
         bsm = 48000 * (4 * n_act + 70 + 380 * whirl)
+        stage_w32 = {"T": 48000 * (6 * n_act + 11), "R": 48000 * (6 + 18 * whirl), "W": 48000 * 198,
+                     "D": 48000 * 37}
+        issue_peak = 148 * 128 * f_clk  # lane-ops/s = bytes/s of shared memory at 4 B per lane
+        ach_fp32 = stage_w32[dom] * secs_per_dom_launch / dur
         # DRAM bytes of one launch of that kernel: dram__bytes_read.sum + dram__bytes_write.sum of
         # the committed `ncu --set full` capture, scaled by organ-fragments per launch
         traffic = None
@@ -513,36 +654,40 @@ def run_gpu_arm(a):
                 traffic = cap["dram_bytes"] * frag_now / (cap["instances"] * cap["fragments"])
         except (OSError, KeyError, ValueError):
             pass
-        roofline = {"bound": "hbm", "achieved": ach_hbm, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": ach_hbm / hbm_peak, "traffic": traffic,
-                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                    "note": "bytes = the dominant stage kernel's algorithmic reads + writes; the path is "
-                            "bound by instruction issue, not HBM: see fp32_issue / smem_bw (whole path, "
-                            "against the timed region) and profiles/",
+        roofline = {"bound": "fp32_issue", "achieved": ach_fp32 / 1e12, "peak": issue_peak / 1e12,
+                    "unit": "T lane-ops/s", "frac": ach_fp32 / issue_peak, "traffic": traffic,
+                    "peak_source": "148 SMs x 128 FP32 lanes x the SM clock sampled under this load "
+                                   "(SURVEY 8(d): the path is bound by FP32 issue and shared-memory "
+                                   "bandwidth, not by HBM or tensor cores)",
+                    "note": "dominant stage kernel: algorithmic FP32 lane-ops of one launch / its average "
+                            "launch duration (every stage kernel timed alone between CUDA events on its "
+                            "launch stream, one extra pass after the timed region); path_* = the whole "
+                            "path's algorithmic work x the timed rate",
                     "kernel": names[dom], "avg_launch_ms": dur * 1e3, "launches_profiled": dom_n,
                     "n_act": n_act,
                     "stage_ms_per_step": {names[k]: stage[k][0] for k in "TRWD"},
-                    "fp32_issue": {"achieved": w32 * rate / 1e12,
-                                   "peak": 148 * 128 * f_clk / 1e12, "unit": "T lane-ops/s",
-                                   "frac": (w32 * rate) / (148 * 128 * f_clk)},
-                    "smem_bw": {"achieved": bsm * rate / 1e12,
-                                "peak": 148 * 128 * f_clk / 1e12, "unit": "TB/s",
-                                "frac": (bsm * rate) / (148 * 128 * f_clk)}}
+                    "path_fp32_issue": {"achieved": w32 * rate / 1e12, "peak": issue_peak / 1e12,
+                                        "unit": "T lane-ops/s", "frac": (w32 * rate) / issue_peak},
+                    "path_smem_bw": {"achieved": bsm * rate / 1e12, "peak": issue_peak / 1e12,
+                                     "unit": "TB/s", "frac": (bsm * rate) / issue_peak},
+                    "hbm": {"achieved": ach_hbm, "peak": hbm_peak, "unit": "GB/s",
+                            "frac": ach_hbm / hbm_peak,
+                            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
+                            "note": "the dominant kernel's algorithmic reads + writes; not the bound"}}
+        if cpu_baseline is not None and cpu_baseline.get("n_act"):
+            cpu_baseline["n_act_gpu_arm"] = n_act
+            cpu_baseline["same_workload"] = bool(abs(cpu_baseline["n_act"] - n_act) <= 0.01 * n_act)
+        cfg = bench_config(a, n_inst, world)
+        cfg.update({"table_sets": len(tg_handles), "whirl_table_sets": len(wh_handles), "init": init})
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": total_ms / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_NAME[a.config], "instances_per_gpu": n_inst,
-                       "seconds_per_instance": a.seconds, "sample_rate": 48000,
-                       "table_sets": len(tg_handles), "whirl_table_sets": len(wh_handles),
-                       "tuning": "one Scala scale per organ" if a.config == 4 else "12-TET",
-                       "init": init,
-                       "l2": "inputs larger than L2 (instance state %.0f MB + %.1f GB of output per step)"
-                             % (n_inst * 0.08, 2 * n_inst * frames * 4 / 1e9),
-                       "parallelism": "instances sharded over %d GPU(s), no collective" % world},
+            "config": cfg,
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches + (e2e_launches if e2e else 0),
             "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "checks": {"peak_abs_sample": peak_out, "error_flags": int(st.error_flags)},
+            "checks": {"peak_abs_sample": peak_out, "error_flags": int(st.error_flags),
+                       "parity_sampled": parity},
         }
         print(json.dumps(line), flush=True)
     ctx.close()

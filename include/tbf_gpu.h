@@ -174,6 +174,17 @@ typedef struct tbf_event {
                                        -> whirlProc3 (src/clap.cpp:254-258) when the reverb or
                                        the overdrive stays on the CPU.  The tone generator's
                                        state is not touched; only rotor events are applied      */
+#define TBF_RENDER_STEMS 0x20       /* whirlProc2's separate horn / drum outputs
+                                       (src/whirl.h:232-238, src/whirl.cpp:1598-1612): outHL, outHR
+                                       = hornLevel * horn line + leak, outDL, outDR = the filtered
+                                       drum lines, written to stems[0..3] next to out_l / out_r   */
+#define TBF_RENDER_OUT_CHUNKED 0x40 /* host output in chunk-major layout: the batch's fragments are
+                                       cut into chunks of tbf_gpu_get_host_chunk() fragments and
+                                       chunk c of instance i lies at out_x + (c * n_instances + i) *
+                                       chunk_samples -- every chunk then crosses the host link as ONE
+                                       contiguous copy per channel instead of n_instances strided rows
+                                       (out_stride is ignored; the last chunk may be shorter and keeps
+                                       the row length chunk_samples)                                */
 
 typedef struct tbf_batch_desc {
     uint32_t n_instances;
@@ -190,6 +201,8 @@ typedef struct tbf_batch_desc {
     const float *in;      /* TBF_RENDER_WHIRL_INPUT: [n_instances][in_stride] mono input,
                              host memory, or device memory with TBF_RENDER_OUT_DEVICE   */
     uint64_t in_stride;   /* floats between instances, >= n_fragments*128       */
+    float *stems[4];      /* TBF_RENDER_STEMS: outHL outHR outDL outDR, same layout and memory
+                             space as out_l / out_r; NULL entries are skipped      */
 } tbf_batch_desc;
 
 typedef struct tbf_ctx tbf_ctx;
@@ -212,6 +225,25 @@ int tbf_gpu_whirl_tables_info(tbf_ctx *ctx, int handle, int *gather_ok, int *rin
 int tbf_gpu_instance_create(tbf_ctx *ctx, int tonegen_tables, int whirl_tables, uint32_t count,
                             uint32_t *first_id);
 int tbf_gpu_instance_count(const tbf_ctx *ctx);
+/* freeToneGenerator + freeWhirl (src/tonegen.cpp:3079-3090, src/whirl.cpp:140-145) as far as the
+ * run-time state goes: the slots are recycled by later tbf_gpu_instance_create calls, and the
+ * instances stop counting as users of their table sets                                        */
+int tbf_gpu_instance_destroy(tbf_ctx *ctx, uint32_t first_id, uint32_t count);
+/* release a table set.  Table sets are reference-counted by their instances: the device memory
+ * is freed (and the handle recycled) once the set has been destroyed AND its last instance is
+ * gone, whichever comes last -- the order a host calls freeToneGenerator / freeWhirl in does not
+ * matter.  The CLAP host re-creates the tone generator on every tuning change
+ * (src/clap.cpp:129-160): destroy + create keeps HBM flat                                     */
+int tbf_gpu_tonegen_tables_destroy(tbf_ctx *ctx, int handle);
+int tbf_gpu_whirl_tables_destroy(tbf_ctx *ctx, int handle);
+/* live objects and device memory of the context's tables and instance array (lifetime tests) */
+int tbf_gpu_resource_counts(const tbf_ctx *ctx, uint32_t *live_instances, uint32_t *instance_slots,
+                            uint32_t *live_tonegen_sets, uint32_t *live_whirl_sets);
+/* workload statistics of instances (NULL ids = 0..n-1): fragments rendered since create / reset
+ * and the sum over them of the active-list length (oscGenerateFragment's activeOscLEnd after
+ * the message-queue drain, src/tonegen.cpp:3343); summed over the listed instances            */
+int tbf_gpu_instance_stats(tbf_ctx *ctx, const uint32_t *ids, uint32_t n, uint64_t *fragments,
+                           uint64_t *active_wheels);
 /* back to the state right after create (what a host gets by re-creating the
  * engine, b_synth/lv2.cpp:1080-1093)                                         */
 int tbf_gpu_instance_reset(tbf_ctx *ctx, uint32_t first_id, uint32_t count);
@@ -234,6 +266,15 @@ int tbf_gpu_synchronize(tbf_ctx *ctx);
 void *tbf_gpu_host_alloc(tbf_ctx *ctx, size_t bytes);
 void tbf_gpu_host_free(tbf_ctx *ctx, void *p);
 int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments);
+uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx);
+/* page-locked host buffer options (tbf_gpu_host_alloc2): write-combined pages are faster for the
+ * device to fill and slow for the host to read back -- for hosts that hand the audio on (file,
+ * socket) without touching it                                                                  */
+#define TBF_HOST_WRITE_COMBINED 0x1
+void *tbf_gpu_host_alloc2(tbf_ctx *ctx, size_t bytes, unsigned flags);
+/* device -> host link ceiling of this context's GPU: plain 1-D page-locked cudaMemcpyAsync of
+ * `bytes` (repeated `reps` times, the best is reported), GB/s                                   */
+int tbf_gpu_measure_d2h(tbf_ctx *ctx, size_t bytes, int reps, double *gbs);
 /* CUDA-event stopwatch on the library's stream                                 */
 int tbf_gpu_timer_start(tbf_ctx *ctx);
 int tbf_gpu_timer_stop(tbf_ctx *ctx, float *ms);

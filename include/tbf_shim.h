@@ -13,8 +13,8 @@
  * is the drop-in demonstration of the boundary; tbf_gpu_render_batch is the product.
  *
  * Not provided (control plane, SURVEY 8 out of scope): MIDI controller registration (`m` is
- * ignored), whirlProc2's separate horn / drum stems, the fset/iset filter setters (send
- * TBF_EV_HORN_FILTER through the batch API instead).
+ * ignored), the fset/iset filter setters (send TBF_EV_HORN_FILTER through the batch API
+ * instead).  On any failure the audio calls write silence (hosts never poll a status).
  */
 #ifndef TBF_SHIM_H
 #define TBF_SHIM_H
@@ -80,6 +80,9 @@ void setRevSelect(struct b_whirl *w, int n);                   /* src/whirl.cpp:
 /* bufferLengthSamples must be a multiple of 128 (the hosts pass 128) */
 void whirlProc(struct b_whirl *w, const float *inbuffer, float *outbL, float *outbR,
                size_t bufferLengthSamples);                    /* src/whirl.cpp:1640 */
+/* NULL outputs are skipped (src/whirl.cpp:1191, src/whirl.h:232-238) */
+void whirlProc2(struct b_whirl *w, const float *inbuffer, float *outL, float *outR, float *outHL,
+                float *outHR, float *outDL, float *outDR, size_t bufferLengthSamples);
 void whirlProc3(struct b_whirl *w, const float *inbuffer, float *outL, float *outR, float *tmpL,
                 float *tmpR, size_t bufferLengthSamples);      /* src/whirl.cpp:1653 */
 

@@ -52,6 +52,7 @@ def lib():
         L.ref_load_programmes.argtypes = [C.c_void_p, C.c_char_p]
         L.ref_whirl_only.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p, C.POINTER(cabi.Event),
                                      C.c_ulonglong, C.c_void_p, C.c_void_p]
+        L.ref_whirl2.argtypes = [C.c_void_p, C.c_uint] + [C.c_void_p] * 7
         L.ref_dump_tonegen_tables.argtypes = [C.c_void_p, C.POINTER(cabi.TonegenTables)]
         L.ref_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
         L.ref_dump_whirl_tables.argtypes = [C.c_void_p, C.POINTER(cabi.WhirlTables)]
@@ -146,6 +147,14 @@ class RefInstance:
         lib().ref_whirl_only(self._h, n_fragments, flags, mono.ctypes.data_as(C.c_void_p), arr, n,
                              outl.ctypes.data_as(C.c_void_p), outr.ctypes.data_as(C.c_void_p))
         return outl, outr
+
+    def whirl2(self, n_fragments, mono):
+        """whirlProc2 on the caller's mono buffer -> (L, R, [HL, HR, DL, DR])."""
+        mono = np.ascontiguousarray(mono, dtype=np.float32)
+        outs = [np.zeros(n_fragments * 128, dtype=np.float32) for _ in range(6)]
+        lib().ref_whirl2(self._h, n_fragments, mono.ctypes.data_as(C.c_void_p),
+                         *[o.ctypes.data_as(C.c_void_p) for o in outs])
+        return outs[0], outs[1], outs[2:]
 
     def load_programmes(self, text):
         """Programme definitions (.pgm syntax) through the reference's own parser."""

@@ -45,6 +45,10 @@ struct ref_inst {
     b_instance inst;
     double rate;
     float bufA[128], tmpL[128], tmpR[128];
+    /* workload statistics for bench.py: fragments rendered and the sum over them of the
+     * active-list length (the larger of its length before and after the fragment, i.e. with
+     * the wheels a key event adds or removes in that fragment still counted) */
+    unsigned long long stat_fragments, stat_active_wheels;
 };
 
 extern "C" {
@@ -210,7 +214,11 @@ int ref_render(void *h, unsigned n_fragments, unsigned flags, const tbf_event *e
         }
         float *L = outL + (size_t)f * 128;
         float *R = outR + (size_t)f * 128;
+        const int act_before = r->inst.synth->activeOscLEnd;
         oscGenerateFragment(r->inst.synth, r->bufA, 128);
+        const int act_after = r->inst.synth->activeOscLEnd;
+        r->stat_fragments += 1;
+        r->stat_active_wheels += (unsigned long long)(act_before > act_after ? act_before : act_after);
         if (flags & TBF_RENDER_WHIRL_BYPASS) {
             memcpy(L, r->bufA, sizeof(float) * 128);
             memcpy(R, r->bufA, sizeof(float) * 128);
@@ -245,6 +253,20 @@ int ref_whirl_only(void *h, unsigned n_fragments, unsigned flags, const float *i
             whirlProc3(r->inst.whirl, x, L, R, r->tmpL, r->tmpR, 128);
         else
             whirlProc(r->inst.whirl, x, L, R, 128);
+    }
+    return 0;
+}
+
+/* whirlProc2 on the caller's mono input with its separate horn / drum outputs
+ * (src/whirl.cpp:1191, src/whirl.h:232-238).  Oracle for TBF_RENDER_STEMS. */
+int ref_whirl2(void *h, unsigned n_fragments, const float *in, float *outL, float *outR, float *outHL,
+               float *outHR, float *outDL, float *outDR)
+{
+    ref_inst *r = (ref_inst *)h;
+    for (unsigned f = 0; f < n_fragments; ++f) {
+        const size_t o = (size_t)f * 128;
+        whirlProc2(r->inst.whirl, in + o, outL + o, outR + o, outHL + o, outHR + o, outDL + o, outDR + o,
+                   128);
     }
     return 0;
 }
@@ -545,6 +567,8 @@ int ref_export_state(void *h, tbf_state_export *o)
     o->adi[0] = w->adi0;
     o->adi[1] = w->adi1;
     o->adi[2] = w->adi2;
+    o->stat_fragments = r->stat_fragments;
+    o->stat_active_wheels = r->stat_active_wheels;
     return 0;
 }
 

@@ -48,6 +48,9 @@ RENDER_WHIRLPROC3 = 0x2
 RENDER_OUT_DEVICE = 0x4
 RENDER_NO_OUTPUT = 0x8
 RENDER_WHIRL_INPUT = 0x10
+RENDER_STEMS = 0x20
+RENDER_OUT_CHUNKED = 0x40
+HOST_WRITE_COMBINED = 0x1
 
 IFLAG_COREPGM_OVERFLOW = 0x1
 IFLAG_KEYCOMP_OOB = 0x2
@@ -180,6 +183,7 @@ class BatchDesc(C.Structure):
         ("checksums", C.POINTER(C.c_uint64)),
         ("in_", C.c_void_p),
         ("in_stride", C.c_uint64),
+        ("stems", C.c_void_p * 4),
     ]
 
 

@@ -23,11 +23,16 @@ struct TgSet {
     uint16_t *cw = nullptr, *cb = nullptr;
     float *cl = nullptr;
     uint16_t *rw = nullptr, *rn = nullptr; /* per-key wheel runs: wheel, entries */
+    /* lifetime: instances using the set; released by the caller; device memory gone */
+    int refs = 0;
+    bool destroyed = false, freed = false;
 };
 struct WhSet {
     tbf_whirl_tables host;
     float *tables = nullptr; /* 4 x 16384 displacement + 2 x 16384 x 5 FIR */
     int ring_size = TBF_WHIRL_BUF, gather_ok = 0, window = 0;
+    int refs = 0;
+    bool destroyed = false, freed = false;
 };
 
 /* Streams between the stage kernels for one chunk of fragments, [slot][chunk samples]. */
@@ -55,6 +60,10 @@ struct tbf_ctx {
     InstState *d_states = nullptr;
     size_t n_inst = 0, cap_inst = 0;
     std::vector<int> inst_tg, inst_wh;
+    /* lifetime: slots of destroyed instances and handles of freed table sets are recycled */
+    std::vector<uint8_t> inst_alive;
+    size_t n_live = 0;
+    std::vector<int> free_tg, free_wh;
     InstState *d_tmpl = nullptr;
     /* table upload: page-locked staging and the device copy of the raw waves + their index,
      * grown on demand (tbf_gpu_tonegen_tables_create) */
@@ -74,8 +83,10 @@ struct tbf_ctx {
     bool has_prepared = false, prepared_has_ids = false;
     uint32_t prepared_chunk = 0;
     uint32_t host_chunk_fragments = 125; /* 1/3 s of audio per staging chunk */
-    cudaStream_t copy_stream = nullptr;
-    cudaEvent_t render_done[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr};
+    int prepared_ring = 512; /* stage W's shared-memory ring: the largest the batch's whirl sets need */
+    cudaStream_t copy_stream = nullptr, copy_stream2 = nullptr; /* left / right channel */
+    cudaEvent_t render_done[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr},
+                copy_done2[2] = {nullptr, nullptr};
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     uint64_t *d_ev_cursor = nullptr; /* [2][cap_slots]: stage T, stage R */
     StageScratch scratch;
@@ -145,6 +156,9 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     if (cudaSetDevice(device) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copy_stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->copy_done2[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->copy_done2[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
         cudaEventCreate(&ctx->t0) != cudaSuccess || cudaEventCreate(&ctx->t1) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->render_done[0], cudaEventDisableTiming) != cudaSuccess ||
@@ -190,16 +204,12 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
         return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (auto &t : ctx->tg) {
-        cudaFree(t.wave);
-        cudaFree(t.cw);
-        cudaFree(t.cb);
-        cudaFree(t.cl);
-        cudaFree(t.rw);
-        cudaFree(t.rn);
-    }
+    for (auto &t : ctx->tg)
+        if (!t.freed)
+            cudaFree(t.wave); /* one allocation per set: the other arrays point into it */
     for (auto &w : ctx->wh)
-        cudaFree(w.tables);
+        if (!w.freed)
+            cudaFree(w.tables);
     cudaFree(ctx->d_tg);
     cudaFree(ctx->d_wh);
     cudaFree(ctx->d_states);
@@ -220,6 +230,7 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     for (int i = 0; i < 2; ++i) {
         cudaEventDestroy(ctx->render_done[i]);
         cudaEventDestroy(ctx->copy_done[i]);
+        cudaEventDestroy(ctx->copy_done2[i]);
     }
     cudaEventDestroy(ctx->t0);
     cudaEventDestroy(ctx->t1);
@@ -236,6 +247,7 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     for (cudaEvent_t e : ctx->prof_events)
         cudaEventDestroy(e);
     cudaStreamDestroy(ctx->copy_stream);
+    cudaStreamDestroy(ctx->copy_stream2);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -426,7 +438,8 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     memcpy(d->vib_offset_table, t->vib_offset_table, sizeof(d->vib_offset_table));
     d->vib_stator_increment = t->vib_stator_increment;
 
-    const size_t idx = ctx->tg.size();
+    const bool reuse_tg = !ctx->free_tg.empty();
+    const size_t idx = reuse_tg ? (size_t)ctx->free_tg.back() : ctx->tg.size();
     if (idx + 1 > ctx->d_tg_cap) {
         const size_t ncap = std::max<size_t>(8, ctx->d_tg_cap * 2);
         DevTonegenTables *nd = nullptr;
@@ -436,8 +449,8 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
             ctx->err = cudaGetErrorString(e);
             return TBF_ERR_NOMEM;
         }
-        if (idx)
-            cudaMemcpy(nd, ctx->d_tg, sizeof(DevTonegenTables) * idx, cudaMemcpyDeviceToDevice);
+        if (ctx->tg.size())
+            cudaMemcpy(nd, ctx->d_tg, sizeof(DevTonegenTables) * ctx->tg.size(), cudaMemcpyDeviceToDevice);
         cudaFree(ctx->d_tg);
         ctx->d_tg = nd;
         ctx->d_tg_cap = ncap;
@@ -445,10 +458,16 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     cudaError_t e = cudaMemcpy(ctx->d_tg + idx, d, sizeof(DevTonegenTables), cudaMemcpyHostToDevice);
     delete d;
     if (e != cudaSuccess) {
+        cudaFree(dev);
         ctx->err = cudaGetErrorString(e);
         return TBF_ERR_CUDA;
     }
-    ctx->tg.push_back(s);
+    if (reuse_tg) {
+        ctx->free_tg.pop_back();
+        ctx->tg[idx] = s;
+    } else {
+        ctx->tg.push_back(s);
+    }
     *handle = (int)idx;
     return TBF_OK;
 }
@@ -525,8 +544,10 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
     memcpy(d.iir[2], w->drfL, sizeof(float) * 5);
     memcpy(d.iir[3], w->drfR, sizeof(float) * 5);
     for (int i = 0; i < 3; ++i) {
-        if (w->revselects[i] < 0)
+        if (w->revselects[i] < 0) {
+            cudaFree(s.tables);
             return fail(ctx, TBF_ERR_ARG, "whirl tables: negative revselect");
+        }
         d.revselects[i] = w->revselects[i];
     }
     d.horn_level = w->horn_level;
@@ -561,8 +582,10 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
                 mx = std::max(mx, disp[p][i]);
             }
             const float sp = p < 6 ? w->horn_spacing[p] : w->drum_spacing[p - 6];
-            if (!(mn == mn) || !(mx == mx) || !(sp == sp))
+            if (!(mn == mn) || !(mx == mx) || !(sp == sp)) {
+                cudaFree(s.tables);
                 return fail(ctx, TBF_ERR_GEOMETRY, "whirl tables: NaN in displacement tables");
+            }
             /* the float sum spacing + displacement + outpos (< 4096) is within 1e-3 of
              * the exact value; +1 is the secondary slot */
             d.tap_dmin[p] = (int)floor((double)sp + (double)mn - 0.01);
@@ -574,9 +597,11 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
         /* the kernels scatter 32 samples, then read them: after a block's scatter the
          * live slots reach wmax + 32 ahead of the block's first read */
         d.window = wmax + 1 + TBF_SCAT_BLOCK;
-        if (d.window >= TBF_WHIRL_BUF - TBF_SCAT_BLOCK)
+        if (d.window >= TBF_WHIRL_BUF - TBF_SCAT_BLOCK) {
+            cudaFree(s.tables);
             return fail(ctx, TBF_ERR_GEOMETRY,
                         "whirl tables: tap delays do not fit the 2048-sample delay lines");
+        }
         for (int line = 0; line < 4; ++line) {
             int t[3];
             const int base = (line < 2) ? (line & 1) : 6 + (line & 1);
@@ -604,19 +629,25 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
         s.window = d.window;
     }
 
-    const size_t idx = ctx->wh.size();
+    const bool reuse_wh = !ctx->free_wh.empty();
+    const size_t idx = reuse_wh ? (size_t)ctx->free_wh.back() : ctx->wh.size();
     if (idx + 1 > ctx->d_wh_cap) {
         const size_t ncap = std::max<size_t>(8, ctx->d_wh_cap * 2);
         DevWhirlTables *nd = nullptr;
         CK(cudaMalloc(&nd, sizeof(DevWhirlTables) * ncap));
-        if (idx)
-            cudaMemcpy(nd, ctx->d_wh, sizeof(DevWhirlTables) * idx, cudaMemcpyDeviceToDevice);
+        if (ctx->wh.size())
+            cudaMemcpy(nd, ctx->d_wh, sizeof(DevWhirlTables) * ctx->wh.size(), cudaMemcpyDeviceToDevice);
         cudaFree(ctx->d_wh);
         ctx->d_wh = nd;
         ctx->d_wh_cap = ncap;
     }
     CK(cudaMemcpy(ctx->d_wh + idx, &d, sizeof(d), cudaMemcpyHostToDevice));
-    ctx->wh.push_back(s);
+    if (reuse_wh) {
+        ctx->free_wh.pop_back();
+        ctx->wh[idx] = s;
+    } else {
+        ctx->wh.push_back(s);
+    }
     *handle = (int)idx;
     return TBF_OK;
 }
@@ -687,16 +718,59 @@ static int replicate(tbf_ctx *ctx, int tgh, int whh, uint32_t first, uint32_t co
     return TBF_OK;
 }
 
+static bool tg_usable(const tbf_ctx *ctx, int h)
+{
+    return h >= 0 && (size_t)h < ctx->tg.size() && !ctx->tg[h].destroyed && !ctx->tg[h].freed;
+}
+static bool wh_usable(const tbf_ctx *ctx, int h)
+{
+    return h >= 0 && (size_t)h < ctx->wh.size() && !ctx->wh[h].destroyed && !ctx->wh[h].freed;
+}
+
+/* device memory of a table set nobody can reach any more; its handle is recycled */
+static void tg_release_if_unused(tbf_ctx *ctx, int h)
+{
+    TgSet &t = ctx->tg[h];
+    if (t.freed || !t.destroyed || t.refs > 0)
+        return;
+    cudaFree(t.wave);
+    t.wave = nullptr;
+    t.freed = true;
+    ctx->free_tg.push_back(h);
+}
+static void wh_release_if_unused(tbf_ctx *ctx, int h)
+{
+    WhSet &w = ctx->wh[h];
+    if (w.freed || !w.destroyed || w.refs > 0)
+        return;
+    cudaFree(w.tables);
+    w.tables = nullptr;
+    w.freed = true;
+    ctx->free_wh.push_back(h);
+}
+
 int tbf_gpu_instance_create(tbf_ctx *ctx, int tgh, int whh, uint32_t count, uint32_t *first_id)
 {
     if (!ctx || !count)
         return fail(ctx, TBF_ERR_ARG, "instance_create: bad argument");
-    if (tgh < 0 || (size_t)tgh >= ctx->tg.size() || whh < 0 || (size_t)whh >= ctx->wh.size())
+    if (!tg_usable(ctx, tgh) || !wh_usable(ctx, whh))
         return fail(ctx, TBF_ERR_HANDLE, "instance_create: unknown table handle");
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "instance_create: a launch is in flight");
     CK(cudaSetDevice(ctx->device));
-    const size_t need = ctx->n_inst + count;
+    /* first fit among the slots of destroyed instances, else append */
+    size_t first = ctx->n_inst;
+    if (ctx->n_inst - ctx->n_live >= count) {
+        size_t run = 0;
+        for (size_t i = 0; i < ctx->n_inst; ++i) {
+            run = ctx->inst_alive[i] ? 0 : run + 1;
+            if (run == count) {
+                first = i + 1 - count;
+                break;
+            }
+        }
+    }
+    const size_t need = std::max(ctx->n_inst, first + count);
     if (need > ctx->cap_inst) {
         size_t ncap = std::max<size_t>(need, ctx->cap_inst * 2);
         InstState *nd = nullptr;
@@ -712,15 +786,126 @@ int tbf_gpu_instance_create(tbf_ctx *ctx, int tgh, int whh, uint32_t count, uint
         ctx->d_states = nd;
         ctx->cap_inst = ncap;
     }
-    const uint32_t first = (uint32_t)ctx->n_inst;
-    int rc = replicate(ctx, tgh, whh, first, count);
+    int rc = replicate(ctx, tgh, whh, (uint32_t)first, count);
     if (rc != TBF_OK)
         return rc;
-    ctx->n_inst = need;
-    ctx->inst_tg.resize(need, tgh);
-    ctx->inst_wh.resize(need, whh);
+    if (need > ctx->n_inst) {
+        ctx->n_inst = need;
+        ctx->inst_tg.resize(need, -1);
+        ctx->inst_wh.resize(need, -1);
+        ctx->inst_alive.resize(need, 0);
+    }
+    for (size_t i = first; i < first + count; ++i) {
+        ctx->inst_tg[i] = tgh;
+        ctx->inst_wh[i] = whh;
+        ctx->inst_alive[i] = 1;
+    }
+    ctx->n_live += count;
+    ctx->tg[tgh].refs += (int)count;
+    ctx->wh[whh].refs += (int)count;
     if (first_id)
-        *first_id = first;
+        *first_id = (uint32_t)first;
+    return TBF_OK;
+}
+
+int tbf_gpu_instance_destroy(tbf_ctx *ctx, uint32_t first_id, uint32_t count)
+{
+    if (!ctx || (size_t)first_id + count > ctx->n_inst)
+        return fail(ctx, TBF_ERR_HANDLE, "instance_destroy: range out of bounds");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "instance_destroy: a launch is in flight");
+    for (size_t i = first_id; i < (size_t)first_id + count; ++i)
+        if (!ctx->inst_alive[i])
+            return fail(ctx, TBF_ERR_HANDLE, "instance_destroy: instance already destroyed");
+    CK(cudaSetDevice(ctx->device));
+    ctx->has_prepared = false; /* a prepared batch may list the instance */
+    for (size_t i = first_id; i < (size_t)first_id + count; ++i) {
+        const int tgh = ctx->inst_tg[i], whh = ctx->inst_wh[i];
+        ctx->inst_alive[i] = 0;
+        ctx->tg[tgh].refs -= 1;
+        ctx->wh[whh].refs -= 1;
+        tg_release_if_unused(ctx, tgh);
+        wh_release_if_unused(ctx, whh);
+    }
+    ctx->n_live -= count;
+    /* trailing free slots are given back, so ids stay small on a host that re-creates organs */
+    while (ctx->n_inst && !ctx->inst_alive[ctx->n_inst - 1])
+        ctx->n_inst -= 1;
+    ctx->inst_tg.resize(ctx->n_inst);
+    ctx->inst_wh.resize(ctx->n_inst);
+    ctx->inst_alive.resize(ctx->n_inst);
+    return TBF_OK;
+}
+
+int tbf_gpu_tonegen_tables_destroy(tbf_ctx *ctx, int handle)
+{
+    if (!ctx || !tg_usable(ctx, handle))
+        return fail(ctx, TBF_ERR_HANDLE, "tonegen_tables_destroy: unknown handle");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "tonegen_tables_destroy: a launch is in flight");
+    CK(cudaSetDevice(ctx->device));
+    ctx->tg[handle].destroyed = true;
+    tg_release_if_unused(ctx, handle);
+    return TBF_OK;
+}
+
+int tbf_gpu_whirl_tables_destroy(tbf_ctx *ctx, int handle)
+{
+    if (!ctx || !wh_usable(ctx, handle))
+        return fail(ctx, TBF_ERR_HANDLE, "whirl_tables_destroy: unknown handle");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "whirl_tables_destroy: a launch is in flight");
+    CK(cudaSetDevice(ctx->device));
+    ctx->wh[handle].destroyed = true;
+    wh_release_if_unused(ctx, handle);
+    return TBF_OK;
+}
+
+int tbf_gpu_resource_counts(const tbf_ctx *ctx, uint32_t *live_instances, uint32_t *instance_slots,
+                            uint32_t *live_tonegen_sets, uint32_t *live_whirl_sets)
+{
+    if (!ctx)
+        return TBF_ERR_ARG;
+    if (live_instances)
+        *live_instances = (uint32_t)ctx->n_live;
+    if (instance_slots)
+        *instance_slots = (uint32_t)ctx->n_inst;
+    uint32_t nt = 0, nw = 0;
+    for (auto &t : ctx->tg)
+        nt += t.freed ? 0 : 1;
+    for (auto &w : ctx->wh)
+        nw += w.freed ? 0 : 1;
+    if (live_tonegen_sets)
+        *live_tonegen_sets = nt;
+    if (live_whirl_sets)
+        *live_whirl_sets = nw;
+    return TBF_OK;
+}
+
+int tbf_gpu_instance_stats(tbf_ctx *ctx, const uint32_t *ids, uint32_t n, uint64_t *fragments,
+                           uint64_t *active_wheels)
+{
+    if (!ctx || !n || (!ids && n > ctx->n_inst))
+        return fail(ctx, TBF_ERR_ARG, "instance_stats: bad argument");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "instance_stats: synchronize first");
+    CK(cudaSetDevice(ctx->device));
+    /* the two 64-bit counters of every instance in one strided copy */
+    std::vector<unsigned long long> st(2 * ctx->n_inst);
+    CK(cudaMemcpy2D(st.data(), 16, &ctx->d_states[0].tg.statFragments, sizeof(InstState), 16, ctx->n_inst,
+                    cudaMemcpyDeviceToHost));
+    uint64_t f = 0, w = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t id = ids ? ids[i] : i;
+        if (id >= ctx->n_inst || !ctx->inst_alive[id])
+            return fail(ctx, TBF_ERR_HANDLE, "instance_stats: unknown instance id");
+        f += st[2 * (size_t)id];
+        w += st[2 * (size_t)id + 1];
+    }
+    if (fragments)
+        *fragments = f;
+    if (active_wheels)
+        *active_wheels = w;
     return TBF_OK;
 }
 
@@ -732,6 +917,9 @@ int tbf_gpu_instance_reset(tbf_ctx *ctx, uint32_t first_id, uint32_t count)
         return fail(ctx, TBF_ERR_HANDLE, "instance_reset: range out of bounds");
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "instance_reset: a launch is in flight");
+    for (size_t k = first_id; k < (size_t)first_id + count; ++k)
+        if (!ctx->inst_alive[k])
+            return fail(ctx, TBF_ERR_HANDLE, "instance_reset: instance destroyed");
     CK(cudaSetDevice(ctx->device));
     uint32_t i = first_id;
     const uint32_t end = first_id + count;
@@ -791,12 +979,16 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     }
     if (d->n_events && !d->events)
         return fail(ctx, TBF_ERR_ARG, "render: events missing");
+    if ((d->flags & TBF_RENDER_STEMS) && (d->flags & (TBF_RENDER_WHIRL_BYPASS | TBF_RENDER_NO_OUTPUT)))
+        return fail(ctx, TBF_ERR_ARG, "render: STEMS needs the Leslie and output buffers");
+    if ((d->flags & TBF_RENDER_OUT_CHUNKED) && (no_out || dev_out))
+        return fail(ctx, TBF_ERR_ARG, "render: OUT_CHUNKED is a host-output layout");
     if (d->instance_ids) {
         /* an instance may appear once per batch: one CTA owns its state */
         std::vector<uint8_t> seen(ctx->n_inst, 0);
         for (uint32_t i = 0; i < d->n_instances; ++i) {
             const uint32_t id = d->instance_ids[i];
-            if (id >= ctx->n_inst)
+            if (id >= ctx->n_inst || !ctx->inst_alive[id])
                 return fail(ctx, TBF_ERR_HANDLE, "render: unknown instance id");
             if (seen[id])
                 return fail(ctx, TBF_ERR_ARG, "render: instance listed twice");
@@ -804,6 +996,17 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
         }
     } else if (d->n_instances > ctx->n_inst) {
         return fail(ctx, TBF_ERR_HANDLE, "render: more instances than created");
+    } else {
+        for (uint32_t i = 0; i < d->n_instances; ++i)
+            if (!ctx->inst_alive[i])
+                return fail(ctx, TBF_ERR_HANDLE, "render: instance destroyed");
+    }
+    /* stage W's shared-memory delay-line ring: the largest any whirl set OF THIS BATCH needs */
+    {
+        int ring = 512;
+        for (uint32_t i = 0; i < d->n_instances; ++i)
+            ring = std::max(ring, ctx->wh[ctx->inst_wh[d->instance_ids ? d->instance_ids[i] : i]].ring_size);
+        ctx->prepared_ring = ring;
     }
     /* events: sorted by (slot, fragment); build the per-slot CSR */
     std::vector<uint64_t> &evs = ctx->ev_start_host;
@@ -838,8 +1041,11 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
      * of chunk i+1; device outputs (or none) are one launch */
     uint32_t chunk = d->n_fragments;
     if (!no_out && !dev_out) {
-        chunk = std::min<uint32_t>(d->n_fragments, ctx->host_chunk_fragments);
-        const size_t need = (size_t)2 /*buffers*/ * 2 /*L,R*/ * d->n_instances * chunk * TBF_FRAGMENT;
+        chunk = (d->flags & TBF_RENDER_OUT_CHUNKED)
+                    ? ctx->host_chunk_fragments /* the caller's layout is cut by this number */
+                    : std::min<uint32_t>(d->n_fragments, ctx->host_chunk_fragments);
+        const size_t planes = (d->flags & TBF_RENDER_STEMS) ? 6 : 2; /* L R (+ HL HR DL DR) */
+        const size_t need = (size_t)2 /*buffers*/ * planes * d->n_instances * chunk * TBF_FRAGMENT;
         cudaError_t e = grow(&ctx->d_out, &ctx->cap_out, need);
         if (e != cudaSuccess) {
             cudaGetLastError();
@@ -944,15 +1150,16 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     base_p.flags = d->flags | (getenv("TBF_NO_FAST_PASS") ? 0x100u : 0u);
     base_p.pitch = pitch;
     ctx->launches = 0;
-    int ring = 512; /* shared-memory delay-line ring: the largest any table set needs */
-    for (auto &w : ctx->wh)
-        ring = std::max(ring, w.ring_size);
+    const int ring = ctx->prepared_ring;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     CK(cudaEventRecord(ctx->fork, ctx->stream));
     for (int g = 0; g < n_groups; ++g)
         for (int st = 0; st < n_stages; ++st)
             CK(cudaStreamWaitEvent(ctx->sstream[g][st], ctx->fork, 0));
-    const size_t half = (size_t)2 * n * chunk * TBF_FRAGMENT;
+    const bool stems = (d->flags & TBF_RENDER_STEMS) != 0;
+    const bool chunked = (d->flags & TBF_RENDER_OUT_CHUNKED) != 0;
+    const size_t n_planes = stems ? 6 : 2;
+    const size_t half = n_planes * n * chunk * TBF_FRAGMENT;
     uint32_t cidx[TBF_MAX_GROUPS] = {0, 0, 0, 0}; /* stage chunks launched per group */
     ctx->prof_stage.clear();
     ctx->timeline = !ctx->profile_stages && getenv("TBF_TIMELINE") != nullptr;
@@ -976,16 +1183,22 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     for (uint32_t base = 0; base < d->n_fragments; base += chunk, ++k) {
         const uint32_t nf = std::min<uint32_t>(chunk, d->n_fragments - base);
         const int buf = k & 1;
-        float *out_l, *out_r;
+        float *out_l, *out_r, *out_s[4] = {nullptr, nullptr, nullptr, nullptr};
         uint64_t out_stride;
         if (host_out) {
-            out_stride = (uint64_t)nf * TBF_FRAGMENT;
+            /* chunk-major host layout: staging rows keep the full chunk length, so the whole
+             * plane of a chunk is one contiguous block on both sides of the link */
+            out_stride = (uint64_t)(chunked ? chunk : nf) * TBF_FRAGMENT;
             out_l = ctx->d_out + half * buf;
             out_r = out_l + n * out_stride;
+            for (int j = 0; stems && j < 4; ++j)
+                out_s[j] = d->stems[j] ? out_l + (size_t)(2 + j) * n * out_stride : nullptr;
         } else {
             out_stride = d->out_stride;
             out_l = no_out ? nullptr : d->out_l + (size_t)base * TBF_FRAGMENT;
             out_r = no_out ? nullptr : d->out_r + (size_t)base * TBF_FRAGMENT;
+            for (int j = 0; stems && j < 4; ++j)
+                out_s[j] = d->stems[j] ? d->stems[j] + (size_t)base * TBF_FRAGMENT : nullptr;
         }
         for (int g = 0; g < n_groups; ++g) {
             const size_t s0 = gfirst[g];
@@ -995,8 +1208,10 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             cudaStream_t prof_st[4] = {ctx->stream, ctx->stream, ctx->stream, ctx->stream};
             cudaStream_t *st = ctx->profile_stages ? prof_st : ctx->sstream[g];
             /* staging buffer `buf` is free once the copy issued two chunks ago is done */
-            if (host_out && k >= 2)
+            if (host_out && k >= 2) {
                 CK(cudaStreamWaitEvent(st[last], ctx->copy_done[buf], 0));
+                CK(cudaStreamWaitEvent(st[last], ctx->copy_done2[buf], 0));
+            }
             RenderParams p = base_p;
             p.n_instances = ng;
             p.ids = ctx->prepared_has_ids ? ctx->d_ids + s0 : nullptr;
@@ -1027,6 +1242,8 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                 p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
                 p.out_l = out_l ? out_l + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
                 p.out_r = out_r ? out_r + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
+                for (int j = 0; j < 4; ++j)
+                    p.stems[j] = out_s[j] ? out_s[j] + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;
                 cudaEvent_t(*ev)[TBF_MAX_STAGE_BUFS] = ctx->sdone[g];
                 /* a stage waits for its producer of this chunk and, before it overwrites
                  * copy `par` of the streams, for their consumers of chunk c - n_bufs */
@@ -1080,16 +1297,29 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                 }
                 ctx->launches += n_stages + (whirl ? 1 : 0); /* stage D is two kernels */
             }
-            if (host_out)
+            if (host_out) {
                 CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->sdone[g][last][par], 0));
+                CK(cudaStreamWaitEvent(ctx->copy_stream2, ctx->sdone[g][last][par], 0));
+            }
         }
         if (host_out) {
+            /* the planes of this chunk cross the link on two copy streams (left / right) */
+            const float *src[6] = {out_l, out_r, out_s[0], out_s[1], out_s[2], out_s[3]};
+            float *dst[6] = {d->out_l, d->out_r, d->stems[0], d->stems[1], d->stems[2], d->stems[3]};
             const size_t w = sizeof(float) * (size_t)nf * TBF_FRAGMENT;
-            CK(cudaMemcpy2DAsync(d->out_l + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
-                                 out_l, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
-            CK(cudaMemcpy2DAsync(d->out_r + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
-                                 out_r, w, w, d->n_instances, cudaMemcpyDeviceToHost, ctx->copy_stream));
+            for (size_t pl = 0; pl < n_planes; ++pl) {
+                if (!src[pl] || !dst[pl])
+                    continue;
+                cudaStream_t cs = (pl & 1) ? ctx->copy_stream2 : ctx->copy_stream;
+                if (chunked) /* chunk k of every instance: one contiguous block */
+                    CK(cudaMemcpyAsync(dst[pl] + (size_t)k * n * out_stride, src[pl],
+                                       sizeof(float) * n * out_stride, cudaMemcpyDeviceToHost, cs));
+                else
+                    CK(cudaMemcpy2DAsync(dst[pl] + (size_t)base * TBF_FRAGMENT, sizeof(float) * d->out_stride,
+                                         src[pl], w, w, d->n_instances, cudaMemcpyDeviceToHost, cs));
+            }
             CK(cudaEventRecord(ctx->copy_done[buf], ctx->copy_stream));
+            CK(cudaEventRecord(ctx->copy_done2[buf], ctx->copy_stream2));
         }
     }
     for (int g = 0; g < n_groups; ++g)
@@ -1119,6 +1349,7 @@ int tbf_gpu_synchronize(tbf_ctx *ctx)
     ctx->in_flight = false;
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaStreamSynchronize(ctx->copy_stream));
+    CK(cudaStreamSynchronize(ctx->copy_stream2));
     /* debugging aid, TBF_TIMELINE=1: when each stage launch of the overlapped schedule became
      * ready (its stream reached it: producers done) and when it finished, ms after the batch
      * started, one line per launch on stderr */
@@ -1210,6 +1441,59 @@ void *tbf_gpu_host_alloc(tbf_ctx *ctx, size_t bytes)
     return p;
 }
 
+void *tbf_gpu_host_alloc2(tbf_ctx *ctx, size_t bytes, unsigned flags)
+{
+    void *p = nullptr;
+    if (!ctx || cudaSetDevice(ctx->device) != cudaSuccess)
+        return nullptr;
+    const unsigned f = (flags & TBF_HOST_WRITE_COMBINED) ? cudaHostAllocWriteCombined : cudaHostAllocDefault;
+    if (cudaHostAlloc(&p, bytes, f | cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+/* the host link's own ceiling: a plain contiguous device -> page-locked-host copy */
+int tbf_gpu_measure_d2h(tbf_ctx *ctx, size_t bytes, int reps, double *gbs)
+{
+    if (!ctx || !bytes || reps < 1 || !gbs)
+        return fail(ctx, TBF_ERR_ARG, "measure_d2h: bad argument");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "measure_d2h: synchronize first");
+    CK(cudaSetDevice(ctx->device));
+    void *dev = nullptr, *host = nullptr;
+    CK(cudaMalloc(&dev, bytes));
+    cudaError_t e = cudaHostAlloc(&host, bytes, cudaHostAllocDefault);
+    if (e == cudaSuccess)
+        e = cudaMemsetAsync(dev, 0, bytes, ctx->copy_stream);
+    float best = 0.f;
+    for (int r = 0; e == cudaSuccess && r < reps + 1; ++r) { /* first pass untimed */
+        e = cudaEventRecord(ctx->t0, ctx->copy_stream);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->copy_stream);
+        if (e == cudaSuccess)
+            e = cudaEventRecord(ctx->t1, ctx->copy_stream);
+        if (e == cudaSuccess)
+            e = cudaEventSynchronize(ctx->t1);
+        float ms = 0.f;
+        if (e == cudaSuccess)
+            e = cudaEventElapsedTime(&ms, ctx->t0, ctx->t1);
+        if (r > 0 && ms > 0.f && (best == 0.f || ms < best))
+            best = ms;
+    }
+    cudaFree(dev);
+    if (host)
+        cudaFreeHost(host);
+    if (e != cudaSuccess) {
+        ctx->err = std::string("measure_d2h: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        return TBF_ERR_CUDA;
+    }
+    *gbs = best > 0.f ? (double)bytes / (best * 1e-3) / 1e9 : 0.0;
+    return TBF_OK;
+}
+
 void tbf_gpu_host_free(tbf_ctx *ctx, void *p)
 {
     if (ctx && p)
@@ -1252,9 +1536,11 @@ int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments)
     return TBF_OK;
 }
 
+uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx) { return ctx ? ctx->host_chunk_fragments : 0; }
+
 int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
 {
-    if (!ctx || !o || instance >= ctx->n_inst)
+    if (!ctx || !o || instance >= ctx->n_inst || !ctx->inst_alive[instance])
         return fail(ctx, TBF_ERR_HANDLE, "export_state: unknown instance");
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "export_state: synchronize first");

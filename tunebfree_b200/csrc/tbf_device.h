@@ -193,6 +193,7 @@ struct RenderParams {
     uint64_t *ev_cursor_t;     /* [n_instances]: next unapplied event of stage T, over chunks */
     uint64_t *ev_cursor_r;     /* same for stage R (it applies the rotor-speed events)        */
     float *out_l, *out_r;
+    float *stems[4];           /* TBF_RENDER_STEMS: outHL outHR outDL outDR, or NULL */
     unsigned long long *checksums; /* [n_instances] or NULL */
     uint64_t out_stride;
     uint32_t n_instances, n_fragments, flags;

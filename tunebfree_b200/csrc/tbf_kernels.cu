@@ -1946,10 +1946,39 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
 
 #define M_THREADS 256
 
-/* Stage D, second kernel: horn level, leakage and the microphone mix (src/whirl.cpp:1614-1616,
- * whirlProc3 :1676-1680) -- elementwise over the five streams, lane = sample, one organ per
- * blockIdx.x, gridDim.y CTAs along the samples; the output checksum is formed here. */
-__global__ void __launch_bounds__(M_THREADS) tbf_stage_m(const RenderParams p)
+/* V consecutive floats as one access (V = 4: LDG.128 / STG.128) */
+template <int V> struct MVec {
+    float v[V];
+};
+template <int V> __device__ __forceinline__ MVec<V> m_load(const float *p)
+{
+    MVec<V> r;
+    if (V == 4) {
+        const float4 q = *reinterpret_cast<const float4 *>(p);
+        r.v[0] = q.x;
+        r.v[V > 1 ? 1 : 0] = q.y;
+        r.v[V > 2 ? 2 : 0] = q.z;
+        r.v[V > 3 ? 3 : 0] = q.w;
+    } else {
+        r.v[0] = *p;
+    }
+    return r;
+}
+template <int V> __device__ __forceinline__ void m_store(float *p, const MVec<V> &r)
+{
+    if (V == 4)
+        __stcs(reinterpret_cast<float4 *>(p), make_float4(r.v[0], r.v[V > 1 ? 1 : 0], r.v[V > 2 ? 2 : 0],
+                                                          r.v[V > 3 ? 3 : 0])); /* streamed: never re-read */
+    else
+        *p = r.v[0];
+}
+
+/* Stage D, second kernel: horn level, leakage and the microphone mix (src/whirl.cpp:1603-1616,
+ * whirlProc3 :1676-1680) -- elementwise over the five streams, lane = V consecutive samples (V = 4:
+ * float4 loads and stores), one organ per blockIdx.x, gridDim.y CTAs along the samples; the
+ * output checksum is formed here.  With TBF_RENDER_STEMS whirlProc2's separate horn and drum
+ * outputs (outHL outHR outDL outDR, src/whirl.h:232-238) are stored next to L and R. */
+template <int V> __global__ void __launch_bounds__(M_THREADS) tbf_stage_m(const RenderParams p)
 {
     const uint32_t slot = blockIdx.x;
     const bool whirl3 = (p.flags & TBF_RENDER_WHIRLPROC3) != 0;
@@ -1963,42 +1992,68 @@ __global__ void __launch_bounds__(M_THREADS) tbf_stage_m(const RenderParams p)
     const uint32_t n = p.n_fragments * TBF_FRAGMENT;
     const size_t in0 = (size_t)slot * p.pitch, out0 = (size_t)slot * p.out_stride;
     unsigned long long csum = 0ull;
-    for (uint32_t i = blockIdx.y * M_THREADS + threadIdx.x; i < n; i += gridDim.y * M_THREADS) {
-        const float h0 = p.hx0[in0 + i];
-        float o_l, o_r;
+    for (uint32_t i = (blockIdx.y * M_THREADS + threadIdx.x) * V; i < n; i += gridDim.y * M_THREADS * V) {
+        const MVec<V> h0 = m_load<V>(p.hx0 + in0 + i);
+        MVec<V> o_l, o_r, s_hl, s_hr, s_dl, s_dr;
         if (bypass) {
             /* bypassed Leslie: input copied to both horn outputs, drum silent
              * (src/whirl.cpp:1197-1215), then whirlProc3's mic mix (:1676-1680) */
-            if (!whirl3) {
-                o_l = o_r = h0;
-            } else {
-                o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, hll), __fmul_rn(h0, hlr)),
-                                          __fmul_rn(0.0f, dll)), __fmul_rn(0.0f, dlr));
-                o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(h0, hrl), __fmul_rn(h0, hrr)),
-                                          __fmul_rn(0.0f, drl)), __fmul_rn(0.0f, drr));
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                const float x = h0.v[j];
+                s_hl.v[j] = s_hr.v[j] = x;
+                s_dl.v[j] = s_dr.v[j] = 0.0f;
+                if (!whirl3) {
+                    o_l.v[j] = o_r.v[j] = x;
+                } else {
+                    o_l.v[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, hll), __fmul_rn(x, hlr)),
+                                                   __fmul_rn(0.0f, dll)), __fmul_rn(0.0f, dlr));
+                    o_r.v[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(x, hrl), __fmul_rn(x, hrr)),
+                                                   __fmul_rn(0.0f, drl)), __fmul_rn(0.0f, drr));
+                }
             }
         } else {
-            const float hl = p.line[0][in0 + i], hr = p.line[1][in0 + i];
-            const float yl = p.line[2][in0 + i], yr = p.line[3][in0 + i];
-            const float leak = __fmul_rn(h0, leakage);
-            const float hpl = __fmul_rn(horn_level, hl), hpr = __fmul_rn(horn_level, hr);
-            if (!whirl3) {
-                o_l = __fadd_rn(__fadd_rn(yl, hpl), leak);
-                o_r = __fadd_rn(__fadd_rn(yr, hpr), leak);
-            } else {
+            const MVec<V> hl = m_load<V>(p.line[0] + in0 + i), hr = m_load<V>(p.line[1] + in0 + i);
+            const MVec<V> yl = m_load<V>(p.line[2] + in0 + i), yr = m_load<V>(p.line[3] + in0 + i);
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+                const float leak = __fmul_rn(h0.v[j], leakage);
+                const float hpl = __fmul_rn(horn_level, hl.v[j]), hpr = __fmul_rn(horn_level, hr.v[j]);
                 const float ohl = __fadd_rn(hpl, leak), ohr = __fadd_rn(hpr, leak);
-                o_l = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, hll), __fmul_rn(ohr, hlr)),
-                                          __fmul_rn(yl, dll)), __fmul_rn(yr, dlr));
-                o_r = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, hrl), __fmul_rn(ohr, hrr)),
-                                          __fmul_rn(yl, drl)), __fmul_rn(yr, drr));
+                s_hl.v[j] = ohl;
+                s_hr.v[j] = ohr;
+                s_dl.v[j] = yl.v[j];
+                s_dr.v[j] = yr.v[j];
+                if (!whirl3) {
+                    o_l.v[j] = __fadd_rn(__fadd_rn(yl.v[j], hpl), leak);
+                    o_r.v[j] = __fadd_rn(__fadd_rn(yr.v[j], hpr), leak);
+                } else {
+                    o_l.v[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, hll), __fmul_rn(ohr, hlr)),
+                                                   __fmul_rn(yl.v[j], dll)), __fmul_rn(yr.v[j], dlr));
+                    o_r.v[j] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(ohl, hrl), __fmul_rn(ohr, hrr)),
+                                                   __fmul_rn(yl.v[j], drl)), __fmul_rn(yr.v[j], drr));
+                }
             }
         }
         if (store) {
-            p.out_l[out0 + i] = o_l;
-            p.out_r[out0 + i] = o_r;
+            m_store<V>(p.out_l + out0 + i, o_l);
+            m_store<V>(p.out_r + out0 + i, o_r);
+            if (p.flags & TBF_RENDER_STEMS) {
+                if (p.stems[0])
+                    m_store<V>(p.stems[0] + out0 + i, s_hl);
+                if (p.stems[1])
+                    m_store<V>(p.stems[1] + out0 + i, s_hr);
+                if (p.stems[2])
+                    m_store<V>(p.stems[2] + out0 + i, s_dl);
+                if (p.stems[3])
+                    m_store<V>(p.stems[3] + out0 + i, s_dr);
+            }
         }
-        if (p.checksums)
-            csum += sample_hash((uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + i), o_l, o_r);
+        if (p.checksums) {
+#pragma unroll
+            for (int j = 0; j < V; ++j)
+                csum += sample_hash((uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + i + j), o_l.v[j], o_r.v[j]);
+        }
     }
     if (p.checksums) { /* zeroed by the host; accumulates over chunks and CTAs */
 #pragma unroll
@@ -2044,13 +2099,20 @@ __global__ void tbf_wave_store_kernel(float *__restrict__ wave4, const float *__
     }
 }
 
-template <typename K> int set_smem(K kernel, size_t smem, int *have)
+/* cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute and one process may hold
+ * a context per GPU (tbf_multi): the largest size opted into is tracked per device */
+#define TBF_MAX_DEVICES 64
+template <typename K> int set_smem(K kernel, size_t smem, int (&have)[TBF_MAX_DEVICES])
 {
-    if (*have < (int)smem) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= TBF_MAX_DEVICES)
+        dev = TBF_MAX_DEVICES; /* unknown device: set the attribute every time */
+    if (dev == TBF_MAX_DEVICES || have[dev] < (int)smem) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess)
             return (int)e;
-        *have = (int)smem;
+        if (dev < TBF_MAX_DEVICES)
+            have[dev] = (int)smem;
     }
     return 0;
 }
@@ -2083,9 +2145,9 @@ size_t tbf_stage_w_smem(int ring_size)
 
 int tbf_launch_stage_t(const RenderParams &p, void *stream)
 {
-    static int have = 0;
+    static int have[TBF_MAX_DEVICES] = {0};
     const size_t smem = tbf_stage_t_smem();
-    if (int rc = set_smem(tbf_stage_t, smem, &have))
+    if (int rc = set_smem(tbf_stage_t, smem, have))
         return rc;
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
     tbf_stage_t<<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
@@ -2095,8 +2157,8 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
 
 int tbf_launch_stage_r(const RenderParams &p, void *stream)
 {
-    static int have = 0;
-    if (int rc = set_smem(tbf_stage_r, sizeof(RSmem), &have))
+    static int have[TBF_MAX_DEVICES] = {0};
+    if (int rc = set_smem(tbf_stage_r, sizeof(RSmem), have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
     const bool r_csum = p.checksums && (p.flags & TBF_RENDER_WHIRL_BYPASS);
@@ -2109,9 +2171,9 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
 
 int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
 {
-    static int have = 0;
+    static int have[TBF_MAX_DEVICES] = {0};
     const size_t smem = tbf_stage_w_smem(ring_size);
-    if (int rc = set_smem(tbf_stage_w, smem, &have))
+    if (int rc = set_smem(tbf_stage_w, smem, have))
         return rc;
     const uint32_t grid = (p.n_instances + W_WARPS - 1) / W_WARPS;
     tbf_stage_w<<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
@@ -2121,15 +2183,25 @@ int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
 
 int tbf_launch_stage_d(const RenderParams &p, void *stream)
 {
-    static int have = 0;
-    if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), &have))
+    static int have[TBF_MAX_DEVICES] = {0};
+    if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
     tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
     debug_sync(stream, "D");
     const uint32_t n = p.n_fragments * TBF_FRAGMENT;
-    const dim3 mgrid(p.n_instances, std::max(1u, std::min(8u, n / (4 * M_THREADS))));
-    tbf_stage_m<<<mgrid, M_THREADS, 0, (cudaStream_t)stream>>>(p);
+    /* float4 accesses when every output row starts 16-byte aligned (the stage streams always do) */
+    bool vec = (p.out_stride % 4) == 0;
+    const float *outs[6] = {p.out_l, p.out_r, p.stems[0], p.stems[1], p.stems[2], p.stems[3]};
+    for (const float *o : outs)
+        vec = vec && (((uintptr_t)o) & 15u) == 0;
+    if (vec) {
+        const dim3 mgrid(p.n_instances, std::max(1u, std::min(4u, n / (4 * M_THREADS))));
+        tbf_stage_m<4><<<mgrid, M_THREADS, 0, (cudaStream_t)stream>>>(p);
+    } else {
+        const dim3 mgrid(p.n_instances, std::max(1u, std::min(8u, n / (4 * M_THREADS))));
+        tbf_stage_m<1><<<mgrid, M_THREADS, 0, (cudaStream_t)stream>>>(p);
+    }
     debug_sync(stream, "M");
     return (int)cudaGetLastError();
 }

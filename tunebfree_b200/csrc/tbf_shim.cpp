@@ -103,6 +103,7 @@ int default_tonegen_tables(tbf_ctx *ctx)
 struct Organ {
     bool ready = false;
     uint32_t id = 0;
+    int own_tables = -1; // the table set this half uploaded (the other half is a shared default)
     std::vector<tbf_event> pending; // setter calls since the last rendered fragment, in order
     std::vector<float> scratch;
     void push(int type, int a, int b = 0)
@@ -115,12 +116,28 @@ struct Organ {
         e.b = b;
         pending.push_back(e);
     }
-    // one render call: `n_frag` fragments, the pending events before the first
-    void render(uint32_t n_frag, uint32_t flags, const float *in, float *out_l, float *out_r)
+    // one render call: `n_frag` fragments, the pending events before the first.  A host never
+    // polls tbf_shim_status(): on any failure the caller's buffers are silenced, not left as
+    // they were
+    void render(uint32_t n_frag, uint32_t flags, const float *in, float *out_l, float *out_r,
+                float *const *stems = nullptr)
     {
         tbf_ctx *ctx = context();
-        if (!ctx || !ready)
+        auto silence = [&]() {
+            const size_t bytes = sizeof(float) * (size_t)n_frag * TBF_FRAGMENT;
+            if (out_l)
+                memset(out_l, 0, bytes);
+            if (out_r)
+                memset(out_r, 0, bytes);
+            for (int j = 0; stems && j < 4; ++j)
+                if (stems[j])
+                    memset(stems[j], 0, bytes);
+        };
+        if (!ctx || !ready) {
+            silence();
+            pending.clear();
             return;
+        }
         tbf_batch_desc d;
         memset(&d, 0, sizeof(d));
         d.n_instances = 1;
@@ -134,9 +151,16 @@ struct Organ {
         d.flags = flags;
         d.in = in;
         d.in_stride = in ? d.out_stride : 0;
+        if (stems) {
+            d.flags |= TBF_RENDER_STEMS;
+            for (int j = 0; j < 4; ++j)
+                d.stems[j] = stems[j];
+        }
         const int rc = tbf_gpu_render_batch(ctx, &d);
-        if (rc != TBF_OK)
+        if (rc != TBF_OK) {
             fail(rc, "tbf_gpu_render_batch");
+            silence();
+        }
         pending.clear();
     }
 };
@@ -210,16 +234,28 @@ void initToneGenerator(struct b_tonegen *t, void *, double rate, double *targetR
         rc = tbf_gpu_instance_create(ctx, tg, wh, 1, &t->organ.id);
     if (rc != TBF_OK || wh < 0) {
         fail(rc, "tone generator upload");
+        if (tg >= 0)
+            tbf_gpu_tonegen_tables_destroy(ctx, tg); /* uploaded, but no organ came of it */
         return;
     }
     t->organ.ready = true;
+    t->organ.own_tables = tg;
     t->organ.scratch.resize(TBF_FRAGMENT);
 }
 
 void initVibrato(void *, void *) {} /* the scanner's tables are part of the tone generator's */
 
+/* frees the organ's run-time state and its wave tables on the device too: the CLAP host does
+ * freeToneGenerator + allocTonegen + initToneGenerator on every tuning change
+ * (src/clap.cpp:129-160) */
 void freeToneGenerator(struct b_tonegen *t)
 {
+    if (!t)
+        return;
+    if (t->organ.ready && g.ctx) {
+        tbf_gpu_instance_destroy(g.ctx, t->organ.id, 1);
+        tbf_gpu_tonegen_tables_destroy(g.ctx, t->organ.own_tables);
+    }
     delete t;
     --g.live;
 }
@@ -288,13 +324,22 @@ void initWhirl(struct b_whirl *w, void *, double rate)
         rc = tbf_gpu_instance_create(ctx, tg, wh, 1, &w->organ.id);
     if (rc != TBF_OK || tg < 0) {
         fail(rc, "Leslie upload");
+        if (wh >= 0)
+            tbf_gpu_whirl_tables_destroy(ctx, wh);
         return;
     }
     w->organ.ready = true;
+    w->organ.own_tables = wh;
 }
 
 void freeWhirl(struct b_whirl *w)
 {
+    if (!w)
+        return;
+    if (w->organ.ready && g.ctx) {
+        tbf_gpu_instance_destroy(g.ctx, w->organ.id, 1);
+        tbf_gpu_whirl_tables_destroy(g.ctx, w->organ.own_tables);
+    }
     delete w;
     --g.live;
 }
@@ -309,6 +354,24 @@ void whirlProc(struct b_whirl *w, const float *in, float *outL, float *outR, siz
     if (n == 0 || n % TBF_FRAGMENT)
         return fail(TBF_ERR_ARG, "whirlProc: length not a multiple of 128");
     w->organ.render((uint32_t)(n / TBF_FRAGMENT), TBF_RENDER_WHIRL_INPUT, in, outL, outR);
+}
+
+/* the horn and drum stems next to (or instead of) the mix; NULL outputs are skipped, as in the
+ * reference (src/whirl.cpp:1191-1215, :1598-1612) */
+void whirlProc2(struct b_whirl *w, const float *in, float *outL, float *outR, float *outHL, float *outHR,
+                float *outDL, float *outDR, size_t n)
+{
+    if (n == 0 || n % TBF_FRAGMENT)
+        return fail(TBF_ERR_ARG, "whirlProc2: length not a multiple of 128");
+    float *stems[4] = {outHL, outHR, outDL, outDR};
+    if (!outL || !outR) { /* the batch API always forms the mix: give it somewhere to go */
+        w->organ.scratch.resize(2 * n);
+        if (!outL)
+            outL = w->organ.scratch.data();
+        if (!outR)
+            outR = w->organ.scratch.data() + n;
+    }
+    w->organ.render((uint32_t)(n / TBF_FRAGMENT), TBF_RENDER_WHIRL_INPUT, in, outL, outR, stems);
 }
 
 void whirlProc3(struct b_whirl *w, const float *in, float *outL, float *outR, float *, float *, size_t n)

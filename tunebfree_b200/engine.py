@@ -68,6 +68,17 @@ def lib():
         L.tbf_gpu_export_state.argtypes = [vp, C.c_uint32, C.POINTER(cabi.StateExport)]
         L.tbf_gpu_set_stage_profiling.argtypes = [vp, C.c_int]
         L.tbf_gpu_stage_times.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        L.tbf_gpu_instance_destroy.argtypes = [vp, C.c_uint32, C.c_uint32]
+        L.tbf_gpu_tonegen_tables_destroy.argtypes = [vp, C.c_int]
+        L.tbf_gpu_whirl_tables_destroy.argtypes = [vp, C.c_int]
+        L.tbf_gpu_resource_counts.argtypes = [vp] + [C.POINTER(C.c_uint32)] * 4
+        L.tbf_gpu_instance_stats.argtypes = [vp, C.POINTER(C.c_uint32), C.c_uint32,
+                                             C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.tbf_gpu_get_host_chunk.argtypes = [vp]
+        L.tbf_gpu_get_host_chunk.restype = C.c_uint32
+        L.tbf_gpu_host_alloc2.argtypes = [vp, C.c_size_t, C.c_uint]
+        L.tbf_gpu_host_alloc2.restype = C.c_void_p
+        L.tbf_gpu_measure_d2h.argtypes = [vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -167,6 +178,40 @@ class Context:
     def reset(self, first, count):
         self._ck(lib().tbf_gpu_instance_reset(self._h, first, count))
 
+    def destroy_instances(self, first, count=1):
+        self._ck(lib().tbf_gpu_instance_destroy(self._h, first, count))
+
+    def destroy_tonegen_tables(self, handle):
+        self._ck(lib().tbf_gpu_tonegen_tables_destroy(self._h, handle))
+
+    def destroy_whirl_tables(self, handle):
+        self._ck(lib().tbf_gpu_whirl_tables_destroy(self._h, handle))
+
+    def resource_counts(self):
+        """-> (live instances, instance slots, live tonegen sets, live whirl sets)"""
+        v = [C.c_uint32(0) for _ in range(4)]
+        self._ck(lib().tbf_gpu_resource_counts(self._h, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
+
+    def instance_stats(self, ids=None, n=None):
+        """-> (fragments rendered, sum of active-list lengths) over the listed instances."""
+        f, w = C.c_uint64(0), C.c_uint64(0)
+        ida = None
+        if ids is not None:
+            n = len(ids)
+            ida = (C.c_uint32 * n)(*[int(i) for i in ids])
+        self._ck(lib().tbf_gpu_instance_stats(self._h, ida, n, C.byref(f), C.byref(w)))
+        return f.value, w.value
+
+    def measure_d2h(self, nbytes=1 << 30, reps=3):
+        """Plain contiguous device -> page-locked host copy rate of this GPU's link, GB/s."""
+        g = C.c_double(0)
+        self._ck(lib().tbf_gpu_measure_d2h(self._h, nbytes, reps, C.byref(g)))
+        return g.value
+
+    def host_chunk(self):
+        return lib().tbf_gpu_get_host_chunk(self._h)
+
     def instance_count(self):
         return lib().tbf_gpu_instance_count(self._h)
 
@@ -195,7 +240,7 @@ class Context:
         return d, keep
 
     def render(self, n_instances, n_fragments, events=None, flags=0, ids=None, checksums=False,
-               inputs=None):
+               inputs=None, stems=False):
         """Host-buffer render through tbf_gpu_render_batch.
         events: per-slot lists [(fragment, type, a, b)] or a prebuilt (array, n).
         inputs: float32 [n_instances, n_fragments*128] mono buffers -> Leslie only
@@ -213,9 +258,20 @@ class Context:
         if inputs is not None:
             d.in_ = inputs.ctypes.data
             d.in_stride = frames
+        st = None
+        if stems:  # whirlProc2's outHL outHR outDL outDR
+            st = np.empty((4, n_instances, frames), dtype=np.float32)
+            d.flags |= cabi.RENDER_STEMS
+            for j in range(4):
+                d.stems[j] = st[j].ctypes.data
         self._ck(lib().tbf_gpu_render_batch(self._h, C.byref(d)))
         del keep
-        return (out_l, out_r, cs) if checksums else (out_l, out_r)
+        res = (out_l, out_r)
+        if checksums:
+            res += (cs,)
+        if stems:
+            res += (st,)
+        return res
 
     def render_device(self, n_instances, n_fragments, events, flags, out_l_ptr, out_r_ptr, stride,
                       ids=None, checksums=None, launch_only=False):
@@ -249,10 +305,10 @@ class Context:
         self._ck(lib().tbf_gpu_timer_stop(self._h, C.byref(ms)))
         return ms.value
 
-    def host_alloc(self, shape, dtype=np.float32):
+    def host_alloc(self, shape, dtype=np.float32, write_combined=False):
         """Page-locked host array (freed with host_free)."""
         n = int(np.prod(shape)) * np.dtype(dtype).itemsize
-        p = lib().tbf_gpu_host_alloc(self._h, n)
+        p = lib().tbf_gpu_host_alloc2(self._h, n, cabi.HOST_WRITE_COMBINED if write_combined else 0)
         if not p:
             raise MemoryError("tbf_gpu_host_alloc(%d) failed" % n)
         buf = (C.c_char * n).from_address(p)
