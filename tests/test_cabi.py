@@ -71,19 +71,44 @@ def test_product_never_imports_oracle():
                 assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f
 
 
-def test_no_contracted_packed_fma_in_kernels():
-    """The tone generator's sum runs on packed FP32 pairs (FMUL2 / FADD2).  ptxas contracts a
-    mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which would change the
-    reference's rounding; the kernels are written so that it cannot (tbf_kernels.cu, core_tile)
-    and this test pins it: no FFMA2 anywhere in the library's SASS, and the packed multiply /
-    add are there."""
+def _sass():
     import shutil
     import subprocess
     from tunebfree_b200 import engine
     cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
-    if not os.path.exists(cuobjdump) or not os.path.exists(engine.LIB_PATH):
-        pytest.skip("cuobjdump or the built library is not available")
-    sass = subprocess.run([cuobjdump, "-sass", engine.LIB_PATH], capture_output=True, text=True,
+    assert os.path.exists(engine.LIB_PATH), "libtbf_gpu.so is not built (python -c 'import __graft_entry__ as g; g.build()')"
+    assert os.path.exists(cuobjdump), "cuobjdump (CUDA toolkit) not found: the SASS guards cannot run"
+    return subprocess.run([cuobjdump, "-sass", engine.LIB_PATH], capture_output=True, text=True,
                           check=True).stdout
+
+
+def _check_sass():
+    sass = _sass()
+    # no packed fused multiply-add anywhere, the packed multiply is there
     assert "FFMA2" not in sass
-    assert "FMUL2" in sass and "FADD2" in sass
+    assert "FMUL2" in sass
+    # scalar FFMA / DFMA only inside the division sequences ptxas expands (their multiplicand or
+    # addend is RZ or the constant 1): none with three live register operands in a float kernel
+    for line in sass.splitlines():
+        m = re.search(r"\bFFMA\s+(\S+), (\S+), (\S+), (\S+) ;", line)
+        if m:
+            assert "RZ" in (m.group(2), m.group(3)), "a fused float multiply-add: " + line.strip()
+    # the wave tables reach shared memory by TMA bulk copies with mbarrier completion
+    assert "UBLKCP" in sass and "SYNCS" in sass
+
+
+def test_no_contracted_packed_fma_in_kernels():
+    """The tone generator's sum multiplies packed FP32 pairs (FMUL2) and adds with scalar FADDs.
+    ptxas contracts a mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which
+    would change the reference's rounding; the kernels are written so that it cannot
+    (tbf_kernels.cu, acc_plain) and this test pins it: no FFMA2 and no scalar FFMA of three live
+    operands anywhere in the library's SASS, the packed multiply is there, and so are the TMA
+    bulk copies (UBLKCP) with their mbarriers (SYNCS) that stage the wave tables.  Fails -- does
+    not skip -- when the library or cuobjdump is missing."""
+    _check_sass()
+
+
+@pytest.mark.gpu
+def test_sass_guards_on_the_gpu_box():
+    """the same guards in the -m gpu set: what ran on the GPU is what was checked"""
+    _check_sass()

@@ -174,7 +174,8 @@ def test_two_contexts_in_one_process(ref):
     want = {}
     for cfg in ("", wide):
         r = ref.RefInstance(seed=1, cfg=cfg)
-        want[cfg] = (r.render(n_frag, cabi.RENDER_WHIRLPROC3, ev), r.tonegen_tables(), r.whirl_tables(), r)
+        tt, wt = r.tonegen_tables(), r.whirl_tables()  # before rendering: they carry the initial state
+        want[cfg] = (r.render(n_frag, cabi.RENDER_WHIRLPROC3, ev), tt, wt, r)
     r2 = ref.RefInstance(seed=1)
     mono = r2.render(n_frag, cabi.RENDER_WHIRL_BYPASS, ev)[0]
     r2.close()

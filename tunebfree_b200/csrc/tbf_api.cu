@@ -624,6 +624,14 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
                     d.ring_size = r;
                     break;
                 }
+        /* conversion-free index math of stage W (tap_position<true>): phases small and non-
+         * negative, microphone angle offsets within [0, 64), delays non-negative */
+        bool small = ok && d.fw_ang >= 0.0 && d.fw_ang < 64.0 && d.bw_ang >= 0.0 && d.bw_ang < 64.0;
+        for (int i = 0; i < 6; ++i)
+            small = small && d.horn_phase[i] >= 0 && d.horn_phase[i] < (1 << 21) && d.drum_phase[i] >= 0 &&
+                    d.drum_phase[i] < (1 << 21);
+        d.small_index = small ? 1 : 0;
+        d.fast_max_angle = 1.0;
         s.ring_size = d.ring_size;
         s.gather_ok = d.gather_ok;
         s.window = d.window;
@@ -1147,7 +1155,9 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     base_p.tg = ctx->d_tg;
     base_p.wh = ctx->d_wh;
     base_p.events = ctx->d_events;
-    base_p.flags = d->flags | (getenv("TBF_NO_FAST_PASS") ? 0x100u : 0u);
+    /* debugging: 0x100 every fragment takes stage T's full active-list pass, 0x200 quiet
+     * fragments are summed one at a time instead of in pairs */
+    base_p.flags = d->flags | (getenv("TBF_NO_FAST_PASS") ? 0x100u : 0u) | (getenv("TBF_NO_PAIRS") ? 0x200u : 0u);
     base_p.pitch = pitch;
     ctx->launches = 0;
     const int ring = ctx->prepared_ring;

@@ -31,8 +31,10 @@
 #define RT_LOWRVIB 0x01u
 #define RT_VIB 0x03u
 
-#define TBF_VRING 256 /* shared-memory scanner ring: host checks that every offset-table
-                         entry keeps the writes inside it (tbf_api.cu)               */
+#define TBF_VRING 64 /* shared-memory scanner ring: host checks that every offset-table
+                        entry keeps the writes inside it (tbf_api.cu); offsets are
+                        (1 + A + A sin) with A <= 12 (scanner.modulation.*'s range,
+                        src/vibrato.cpp:343-352): 25 slots ahead + a 32-sample block + 2 */
 
 struct OscState {      /* struct _oscillator + the scalar part of AOTElement */
     uint32_t pos;      /* wave read position                                 */
@@ -77,12 +79,13 @@ struct RampScalars {
 
 /* ---- stage W: Leslie reflections, taps, delay lines ---- */
 struct WhirlScalars {
-    uint32_t outpos;
+    uint32_t outpos;      /* the horn half's copy of the delay lines' read position */
     uint32_t errorFlags;
     float z[4];
     float adx[3][8];
     int32_t adi[3];
-    uint32_t pad_;
+    uint32_t outpos_drum; /* the drum half's copy: the two halves of stage W run as independent
+                             warps, each reads and advances its own                            */
 };
 
 /* ---- stage D: drum filters ---- */
@@ -104,10 +107,11 @@ struct InstState {
 };
 
 /* Floats per rotated copy of a wave of `len` samples: copy c holds wave[(i + c) % len] for
- * i < len + 128, padded to whole float4s.  Copies 0..3 of a wheel lie back to back. */
+ * i < len + 256, padded to whole float4s, so the reads of TWO consecutive fragments from any
+ * position are one contiguous, 16-byte aligned kilobyte.  Copies 0..3 of a wheel lie back to back. */
 static inline __host__ __device__ uint32_t tbf_wave_copy_len(uint32_t len)
 {
-    return (len + TBF_FRAGMENT + 3u) & ~3u;
+    return (len + 2u * TBF_FRAGMENT + 3u) & ~3u;
 }
 
 /* tbf_tonegen_tables with device pointers */
@@ -166,6 +170,12 @@ struct DevWhirlTables {
                                so the ordered scatter can be evaluated in parallel passes  */
     int32_t window;         /* slots ahead of the reader that can be non-zero after a
                                32-sample block has been scattered                         */
+    int32_t small_index;    /* 1: every phase is in [0, 2^21) and every tap delay non-negative, so
+                               with the rotor angle in [+0, fast_max_angle) the table index
+                               h1 = angle * 16384 + phase and the delay-line position t lie in
+                               [+0, 2^22): stage W reads floor / round / the integer conversions
+                               off the float's mantissa instead of converting (tbf_kernels.cu)  */
+    double fast_max_angle;  /* 1.0: horn angle + microphone offset stays below 2^7            */
     int32_t tap_order[4][3];/* per line HL HR DL DR: tap ids (0..11), farthest delay first */
     int32_t tap_dmin[12], tap_dmax[12];
 };

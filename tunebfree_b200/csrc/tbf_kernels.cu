@@ -40,6 +40,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "tbf_device.h"
 
@@ -131,30 +132,42 @@ __device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_
  * and one record per wheel suffices. */
 #define REC_TILE 32    /* active-list entries turned into records and summed at a time */
 #define REC_CAP 128   /* longest active list whose records persist across fragments   */
-#define WAVE_STAGES 6  /* wheels whose wave samples are in flight (cp.async) per warp   */
+#define T_SLOTS 2      /* wave staging slots per warp = wheels in flight (bulk copies)  */
 struct TWarp {
     TgScalars sc;
     /* core-program records.  Lists of up to REC_CAP wheels keep their records here from one
      * fragment to the next: a fragment without events only advances the read positions
      * (fast_pass) and never touches the per-wheel state in HBM */
-    int4 recA[REC_CAP];    /* address of the lane-0 float4 of the 128 samples (lo, hi), read
-                              position, env (-1 plain, 0..7 attack, 8..15 release) */
-    float4 recB[REC_CAP];  /* gs gs gv gv: gains duplicated for the packed f32x2 multiply */
-    float2 recC[REC_CAP];  /* gp gp */
-    union {                /* the removal list is built after the last tile has been summed */
-        float4 recD[REC_TILE]; /* ds dv dp - : envelope deltas of the current tile, env >= 0 only */
-        uint16_t removed_wheel[TBF_NOF_WHEELS];
-    };
-    uint2 recP[REC_CAP];   /* wave length | wheel << 16, wave4_offset of the wheel */
-    float4 wstage[WAVE_STAGES][32]; /* [stage][lane]: samples 4*lane .. 4*lane+3 of a wheel */
+    float4 recG[REC_CAP];   /* gs gv gp, env as int bits (-1 plain, 0..7 attack, 8..15 release) */
+    uint32_t recQ[REC_CAP]; /* where the wheel's next 128 (256: pairs) samples start in the wave
+                               store, in float4 units                                            */
+    uint32_t recL[REC_CAP]; /* wave length | read position << 16 (of the record's last fragment) */
+    uint16_t recW[REC_CAP]; /* wheel                                                             */
+    /* wave samples in flight: one 512-byte bulk copy (TMA) per wheel and fragment lands here,
+     * [slot][fragment A / B][lane] = samples 4*lane .. 4*lane+3.  The single-fragment passes use
+     * the A halves only; the B halves then hold the envelope deltas of the current tile
+     * (rec_d) and, once the last tile has been summed, the removal list (removed_wheel) */
+    float4 wstage[T_SLOTS][2][32];
+    unsigned long long mbar[T_SLOTS]; /* "slot filled" barriers of the bulk copies              */
+    const float *wave4;               /* the organ's wave store (read by the lane that requests) */
     float vring[TBF_VRING];
-    uint8_t removed[TBF_NOF_WHEELS + 3];
+    uint8_t removed[TBF_NOF_WHEELS + 4];
     int recompute_routing, draw_bar_change, vib_on, perc_on;
     /* raised by any lane during the active-list pass of a fragment.  Shared-memory flags read
      * after a __syncwarp(), not warp votes: ptxas assumed the warp converged behind the tile
      * loop, dropped the WARPSYNC before VOTE.ANY, and lanes got different answers */
     int any_removed, any_env;
 };
+static_assert(sizeof(TWarp) <= 7040, "stage T: 32 warps per SM need <= 7040 B of shared memory per warp");
+static_assert(REC_TILE * sizeof(float4) <= sizeof(float4) * 32 &&
+              TBF_NOF_WHEELS * sizeof(uint16_t) <= sizeof(float4) * 32, "slow-path arrays fit a B half");
+
+/* envelope deltas ds dv dp of the current tile's records (slow path, env >= 0 only) */
+__device__ __forceinline__ float4 *rec_d(TWarp &sm) { return sm.wstage[0][1]; }
+__device__ __forceinline__ uint16_t *removed_wheel(TWarp &sm)
+{
+    return reinterpret_cast<uint16_t *>(sm.wstage[1][1]);
+}
 
 /* -- key events, one lane (src/tonegen.cpp:3096-3166 + the queue drain :3257-3327): the
  *    fallback when a key's contribution list is not wheel-sorted with unique pairs -- */
@@ -387,11 +400,11 @@ __device__ __forceinline__ uint32_t next_position(uint32_t pos, uint32_t len)
     return (len < pos + TBF_FRAGMENT) ? TBF_FRAGMENT - (len - pos) : pos + TBF_FRAGMENT;
 }
 
-/* where the 128 samples from `pos` start in the wave store: copy (pos & 3), float4-aligned */
-__device__ __forceinline__ unsigned long long wave_addr(const float *wave4, uint32_t off4, uint32_t len,
-                                                        uint32_t pos)
+/* where the 128 samples from `pos` start in the wave store, in float4 units from its base:
+ * copy (pos & 3) of the wheel, 16-byte aligned (tbf_wave_copy_len) */
+__device__ __forceinline__ uint32_t wave_q(uint32_t off4, uint32_t len, uint32_t pos)
 {
-    return (unsigned long long)(wave4 + off4 + (pos & 3u) * tbf_wave_copy_len(len) + (pos & ~3u));
+    return (off4 + (pos & 3u) * tbf_wave_copy_len(len) + (pos & ~3u)) >> 2;
 }
 
 /* active-list pass (src/tonegen.cpp:3333-3594), entries [base, base + cnt) -> records
@@ -494,17 +507,13 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
             my_ins += 1;
         }
         o->rflags = 0;
-        {
-            const uint32_t off4 = tg->wave4_offset[w];
-            const unsigned long long addr = wave_addr(tg->wave4, off4, len, pos);
-            sm.recA[rec0 + i - base] =
-                make_int4((int)(uint32_t)addr, (int)(uint32_t)(addr >> 32), (int)pos, env);
-            sm.recP[rec0 + i - base] = make_uint2(len | ((uint32_t)w << 16), off4);
-        }
-        sm.recB[rec0 + i - base] = make_float4(gs, gs, gv, gv);
-        sm.recC[rec0 + i - base] = make_float2(gp, gp);
+        const int rec = rec0 + i - base;
+        sm.recQ[rec] = wave_q(tg->wave4_offset[w], len, pos);
+        sm.recL[rec] = len | (pos << 16);
+        sm.recW[rec] = (uint16_t)w;
+        sm.recG[rec] = make_float4(gs, gv, gp, __int_as_float(env));
         if (env >= 0) {
-            sm.recD[i - base] = make_float4(ds, dv, dp, 0.0f);
+            rec_d(sm)[i - base] = make_float4(ds, dv, dp, 0.0f);
             sm.any_env = 1;
         }
     }
@@ -512,23 +521,26 @@ __device__ __forceinline__ void active_list_tile(InstState *st, const DevTonegen
 
 /* A fragment without events, routing or drawbar change over a list whose records persist:
  * every wheel plays on with unchanged gains, only its read position advances
- * (src/tonegen.cpp:3521-3555: wrap test `length < pos + 128`, pos may rest at == length). */
+ * (src/tonegen.cpp:3521-3555: wrap test `length < pos + 128`, pos may rest at == length).
+ * NF = 2: the next TWO fragments are quiet, the records are advanced for both at once. */
+template <int NF>
 __device__ __forceinline__ void fast_pass(const DevTonegenTables *tg, TWarp &sm, int lane, int n_act,
-                                          int &my_ins)
+                                          int &ins_a, int &ins_b)
 {
-    const float *wave4 = tg->wave4;
     for (int i = lane; i < n_act; i += 32) {
-        int4 ra = sm.recA[i];
-        const uint2 rp = sm.recP[i];
-        const uint32_t len = rp.x & 0xFFFFu;
-        /* the position this record was rendered from moves on by one fragment */
-        const uint32_t pos = next_position((uint32_t)ra.z, len);
-        my_ins += (len < pos + TBF_FRAGMENT) ? 2 : 1;
-        const unsigned long long addr = wave_addr(wave4, rp.y, len, pos);
-        ra.x = (int)(uint32_t)addr;
-        ra.y = (int)(uint32_t)(addr >> 32);
-        ra.z = (int)pos;
-        sm.recA[i] = ra;
+        const uint32_t l = sm.recL[i];
+        const uint32_t len = l & 0xFFFFu;
+        const uint32_t off4 = __ldg(&tg->wave4_offset[sm.recW[i]]);
+        /* the position this record was last rendered from moves on by one fragment */
+        const uint32_t pos_a = next_position(l >> 16, len);
+        ins_a += (len < pos_a + TBF_FRAGMENT) ? 2 : 1;
+        uint32_t pos_b = pos_a;
+        if (NF == 2) { /* fragment B reads on from where A ends, in the same image of the wave */
+            pos_b = next_position(pos_a, len);
+            ins_b += (len < pos_b + TBF_FRAGMENT) ? 2 : 1;
+        }
+        sm.recQ[i] = wave_q(off4, len, pos_a);
+        sm.recL[i] = len | (pos_b << 16);
     }
 }
 
@@ -536,8 +548,8 @@ __device__ __forceinline__ void fast_pass(const DevTonegenTables *tg, TWarp &sm,
 __device__ __forceinline__ void flush_positions(InstState *st, const TWarp &sm, int lane, int n_act)
 {
     for (int i = lane; i < n_act; i += 32) {
-        const uint32_t x = sm.recP[i].x;
-        st->osc[x >> 16].pos = next_position((uint32_t)sm.recA[i].z, x & 0xFFFFu);
+        const uint32_t l = sm.recL[i];
+        st->osc[sm.recW[i]].pos = next_position(l >> 16, l & 0xFFFFu);
     }
 }
 
@@ -565,11 +577,11 @@ __device__ __forceinline__ void active_list_finish(InstState *st, TWarp &sm, int
             int l_end = n_act;
             for (int i = 0; i < n_act; ++i)
                 if (sm.removed[i])
-                    sm.removed_wheel[i] = (uint16_t)st->activeOscList[i];
+                    removed_wheel(sm)[i] = (uint16_t)st->activeOscList[i];
             for (int i = 0; i < n_act; ++i) {
                 if (!sm.removed[i])
                     continue;
-                const int vic = sm.removed_wheel[i];
+                const int vic = removed_wheel(sm)[i];
                 const int actidx = st->osc[vic].aclPos;
                 st->osc[vic].aclPos = -1;
                 l_end--;
@@ -587,39 +599,80 @@ __device__ __forceinline__ void active_list_finish(InstState *st, TWarp &sm, int
     __syncwarp();
 }
 
+/* ---- TMA bulk copies and their mbarriers (cp.async.bulk -> SASS UBLKCP, SYNCS) ---- */
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "TBF_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra TBF_DONE;\n"
+        "bra TBF_WAIT;\n"
+        "TBF_DONE:\n"
+        "}" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+/* global -> shared, `bytes` a multiple of 16, both addresses 16-byte aligned; completion is
+ * signalled on the mbarrier as `bytes` of its expected transaction count */
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+/* generic-proxy writes to shared memory are ordered before later async-proxy (TMA) accesses */
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 /* core interpreter (src/tonegen.cpp:3607-3687): lane holds samples 4*lane .. 4*lane+3 of the
- * fragment while the wheels are summed.  The device's wave store (tbf_api.cu) has an aligned,
- * never-wrapping image of every 128-sample read, so a lane requests its four samples of record
- * `rec` with ONE 16-byte cp.async into its own float4 of stage `slot` and reads them back with
- * one LDS.128.  Every lane reads back only what it requested itself. */
-__device__ __forceinline__ void wave_request(TWarp &sm, int rec, int slot, int lane)
+ * fragment while the wheels are summed.  The device's wave store (tbf_api.cu) has a 16-byte
+ * aligned, never-wrapping image of every 128-sample read, so ONE lane requests a wheel's 512
+ * bytes with one bulk copy (TMA) into a staging slot; its completion flips the slot's mbarrier
+ * and every lane reads its four samples back with one LDS.128. */
+/* one lane of the (converged) warp, chosen by the hardware: the canonical TMA issue pattern */
+__device__ __forceinline__ bool elect_one()
 {
-    const uint2 a = *reinterpret_cast<const uint2 *>(&sm.recA[rec]);
-    const float4 *q =
-        reinterpret_cast<const float4 *>(((unsigned long long)a.y << 32) | (unsigned long long)a.x) + lane;
-#ifdef TBF_DEBUG_CHECKS
-    if (rec < 0 || rec >= REC_CAP || slot < 0 || slot >= WAVE_STAGES || (a.x & 15u) || a.y == 0) {
-        printf("wave_request bad: rec %d slot %d addr %08x%08x lane %d\n", rec, slot, a.y, a.x, lane);
-        __trap();
-    }
-#endif
-    __pipeline_memcpy_async(&sm.wstage[slot][lane], q, 16);
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}" : "=r"(pred));
+    return pred != 0;
 }
 
-/* the same request with the record's address already in registers */
-__device__ __forceinline__ void wave_request_at(TWarp &sm, const uint2 a, int slot, int lane)
+/* NF = 2: the wave store's images run 256 samples past every start (tbf_wave_copy_len), so the
+ * reads of two consecutive fragments are ONE contiguous kilobyte, wraps included */
+template <int NF>
+__device__ __forceinline__ void wave_request(TWarp &sm, int rec, int slot)
 {
-    const float4 *q =
-        reinterpret_cast<const float4 *>(((unsigned long long)a.y << 32) | (unsigned long long)a.x) + lane;
-    __pipeline_memcpy_async(&sm.wstage[slot][lane], q, 16);
+    const uint32_t q = sm.recQ[rec];
+    const float *wave4 = sm.wave4;
+    const uint32_t bar = smem_u32(&sm.mbar[slot]);
+    mbar_expect_tx(bar, NF * 512u);
+    bulk_g2s(smem_u32(sm.wstage[slot][0]), wave4 + (size_t)q * 4u, NF * 512u, bar);
 }
 
-/* Packed pairs of floats for Blackwell's two-wide FP32 instructions (FMUL2 / FADD2): each
- * half is an IEEE round-to-nearest operation, bit-identical to the scalar one.
+/* Packed pairs of floats for Blackwell's two-wide FP32 multiply (FMUL2): each half is an IEEE
+ * round-to-nearest operation, bit-identical to the scalar one.  The sums are scalar FADDs:
  * ptxas contracts a mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which
- * would break the reference's rounding; core_tile() therefore adds a wheel's products one
- * loop iteration after they were formed (the loop is kept rolled), and tests/test_cabi.py
- * checks that the built kernels contain no fused multiply-add at all. */
+ * would break the reference's rounding (one rounding instead of two); a packed product
+ * feeding scalar adds cannot be contracted, needs no carried products (round 1 carried them
+ * one loop trip: 24 more registers and 8 MOVs per wheel) and tests/test_cabi.py checks that
+ * the built kernels contain no fused multiply-add at all. */
 typedef unsigned long long f32x2;
 __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
 {
@@ -627,175 +680,194 @@ __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
     asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
     return r;
 }
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
-{
-    f32x2 r;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
 __device__ __forceinline__ f32x2 pack2(float lo, float hi)
 {
-    return ((f32x2)__float_as_uint(hi) << 32) | (f32x2)__float_as_uint(lo);
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
 }
-__device__ __forceinline__ float lo2(f32x2 v) { return __uint_as_float((uint32_t)v); }
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
 
-/* accumulators and pending products of the three buffers (swell, scanner, percussion):
- * [0] = samples 4*lane, 4*lane+1; [1] = samples 4*lane+2, 4*lane+3.  Two wheels are pending at
- * a time (A = even record of the last iteration, B = odd). */
-struct WheelProd {
-    f32x2 s[2], v[2], p[2];
-};
+/* running sums of the three buffers (swell, scanner, percussion) over the lane's four samples */
 struct CoreAcc {
-    WheelProd sum;    /* running sums                                            */
-    WheelProd pa, pb; /* products of the previous two wheels, not yet added      */
+    float s[4], v[4], p[4];
 };
 
 /* The first instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680):
  * with the sums started at -0.0f an add IS a copy, bit for bit ((-0) + x = x for every x,
- * (-0) + (-0) = -0); pending products of -0.0f are likewise an exact no-op. */
-__device__ __forceinline__ void prod_none(WheelProd &w)
-{
-    const f32x2 nz = 0x8000000080000000ull;
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-        w.s[h] = w.v[h] = w.p[h] = nz;
-}
+ * (-0) + (-0) = -0). */
 __device__ __forceinline__ void core_begin(CoreAcc &a)
 {
-    prod_none(a.sum);
-    prod_none(a.pa);
-    prod_none(a.pb);
-}
-__device__ __forceinline__ void prod_add(WheelProd &sum, const WheelProd &w)
-{
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        sum.s[h] = add2(sum.s[h], w.s[h]);
-        sum.v[h] = add2(sum.v[h], w.v[h]);
-        sum.p[h] = add2(sum.p[h], w.p[h]);
-    }
+    for (int j = 0; j < 4; ++j)
+        a.s[j] = a.v[j] = a.p[j] = -0.0f;
 }
 
-/* products of record i with the lane's staged samples x.  ENV = false: the caller knows that
- * every record of the tile plays with constant gains (no key click in flight). */
-template <bool ENV>
-__device__ __forceinline__ void wheel_products(const DevTonegenTables *tg, const TWarp &sm, int i,
-                                               int i_tile, int lane, const ulonglong2 x, WheelProd &w)
+/* sum += x * g for the lane's four samples x (two packed pairs) */
+__device__ __forceinline__ void acc_plain(float (&sum)[4], const ulonglong2 x, const f32x2 g2)
 {
-    const ulonglong2 g = *reinterpret_cast<const ulonglong2 *>(&sm.recB[i]);
-    const f32x2 gp = *reinterpret_cast<const f32x2 *>(&sm.recC[i]);
-    const int env = ENV ? sm.recA[i].w : -1;
+    float p0, p1, p2, p3;
+    unpack2(mul2(x.x, g2), p0, p1);
+    unpack2(mul2(x.y, g2), p2, p3);
+    sum[0] = __fadd_rn(sum[0], p0);
+    sum[1] = __fadd_rn(sum[1], p1);
+    sum[2] = __fadd_rn(sum[2], p2);
+    sum[3] = __fadd_rn(sum[3], p3);
+}
+
+/* products of one record with the lane's staged samples x, added in list order.  ENV = false:
+ * the caller knows that every record plays with constant gains (no key click in flight). */
+template <bool ENV>
+__device__ __forceinline__ void wheel_accumulate(const DevTonegenTables *tg, TWarp &sm, const float4 g,
+                                                 int i_tile, int lane, const ulonglong2 x, CoreAcc &a)
+{
+    const int env = ENV ? __float_as_int(g.w) : -1;
     if (!ENV || env < 0) {
-        w.s[0] = mul2(x.x, g.x);
-        w.s[1] = mul2(x.y, g.x);
-        w.v[0] = mul2(x.x, g.y);
-        w.v[1] = mul2(x.y, g.y);
-        w.p[0] = mul2(x.x, gp);
-        w.p[1] = mul2(x.y, gp);
+        acc_plain(a.s, x, pack2(g.x, g.x));
+        acc_plain(a.v, x, pack2(g.y, g.y));
+        acc_plain(a.p, x, pack2(g.z, g.z));
     } else { /* key click: gain = g + env[n] * (next - g), per sample */
-        const float4 d = sm.recD[i_tile]; /* only the pass's tiles (<= REC_TILE records) carry envelopes */
-        const float *ev = tg->env[env] + 4 * lane;
-        const float gs = lo2(g.x), gv = lo2(g.y), gpp = lo2(gp);
-        float e[4];
+        const float4 d = rec_d(sm)[i_tile]; /* only the pass's tiles (<= REC_TILE records) carry envelopes */
+        const float *ep = tg->env[env] + 4 * lane;
+        const float ev[4] = {__ldg(ep), __ldg(ep + 1), __ldg(ep + 2), __ldg(ep + 3)};
+        float xs[4];
+        unpack2(x.x, xs[0], xs[1]);
+        unpack2(x.y, xs[2], xs[3]);
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            e[j] = __ldg(ev + j);
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            const f32x2 xx = h ? x.y : x.x;
-            const float e0 = e[2 * h], e1 = e[2 * h + 1];
-            w.s[h] = mul2(xx, pack2(__fadd_rn(gs, __fmul_rn(e0, d.x)), __fadd_rn(gs, __fmul_rn(e1, d.x))));
-            w.v[h] = mul2(xx, pack2(__fadd_rn(gv, __fmul_rn(e0, d.y)), __fadd_rn(gv, __fmul_rn(e1, d.y))));
-            w.p[h] = mul2(xx, pack2(__fadd_rn(gpp, __fmul_rn(e0, d.z)), __fadd_rn(gpp, __fmul_rn(e1, d.z))));
+        for (int j = 0; j < 4; ++j) {
+            a.s[j] = __fadd_rn(a.s[j], __fmul_rn(xs[j], __fadd_rn(g.x, __fmul_rn(ev[j], d.x))));
+            a.v[j] = __fadd_rn(a.v[j], __fmul_rn(xs[j], __fadd_rn(g.y, __fmul_rn(ev[j], d.y))));
+            a.p[j] = __fadd_rn(a.p[j], __fmul_rn(xs[j], __fadd_rn(g.z, __fmul_rn(ev[j], d.z))));
         }
     }
 }
 
-/* records 0..cnt-1 of the current tile, in order (src/tonegen.cpp:3607-3687), two per trip;
- * WAVE_STAGES wheels stay in flight, committed in pairs.  The loops must stay rolled: the
- * products formed in one trip are added in the next (see the note at mul2/add2).  Without
- * envelopes the bulk of the tile runs in a trip without any conditional. */
-template <bool ENV>
-__device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
-                                          int cnt, CoreAcc &a)
+/* one wheel: wait for its samples in staging slot SLOT, read them and the record's gains,
+ * hand the slot back (the wheel T_SLOTS further is requested into it), accumulate */
+template <int NF, bool ENV, int SLOT>
+__device__ __forceinline__ void core_step(const DevTonegenTables *tg, TWarp &sm, int lane, int rec, int i_tile,
+                                          bool more, CoreAcc (&acc)[NF], uint32_t &parity)
 {
+    mbar_wait(smem_u32(&sm.mbar[SLOT]), parity);
+    parity ^= 1u;
+    ulonglong2 x[NF];
 #pragma unroll
-    for (int j = 0; j < WAVE_STAGES; j += 2) {
-        if (j < cnt)
-            wave_request(sm, rec0 + j, j, lane);
-        if (j + 1 < cnt)
-            wave_request(sm, rec0 + j + 1, j + 1, lane);
-        __pipeline_commit();
+    for (int f = 0; f < NF; ++f)
+        x[f] = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[SLOT][f][lane]);
+    const float4 g = sm.recG[rec];
+    __syncwarp(); /* every lane has read the slot: it may be filled again */
+    if (more && elect_one())
+        wave_request<NF>(sm, rec + T_SLOTS, SLOT);
+#pragma unroll
+    for (int f = 0; f < NF; ++f)
+        wheel_accumulate<ENV>(tg, sm, g, i_tile, lane, x[f], acc[f]);
+}
+
+/* records rec0 .. rec0+cnt-1 in order (src/tonegen.cpp:3607-3687), T_SLOTS = 2 wheels in flight
+ * and two wheels per trip, so that slot numbers are compile-time constants; NF = 2 sums the same
+ * records into two consecutive fragments (acc[0], acc[1]) from the 256-sample read fast_pass<2>
+ * laid out.  par0 / par1: the parity each slot's barrier shows when its next fill has landed. */
+template <int NF, bool ENV>
+__device__ __forceinline__ void core_tile_tma(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
+                                              int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1)
+{
+    static_assert(T_SLOTS == 2, "core_tile is written for two staging slots");
+    if (cnt > 0 && elect_one()) {
+        wave_request<NF>(sm, rec0, 0);
+        if (cnt > 1)
+            wave_request<NF>(sm, rec0 + 1, 1);
     }
-    int i = 0, s = 0; /* s = i % WAVE_STAGES: the stage pair of records i, i+1 */
-    if (!ENV) {
-        /* request addresses are read one trip before they are used (an LDS feeding the
-         * LDGSTS directly was the largest stall of the trip) */
-        uint2 qa = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + WAVE_STAGES, REC_CAP - 1)]);
-        uint2 qb = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + WAVE_STAGES + 1, REC_CAP - 1)]);
+    int i = 0;
 #pragma unroll 1
-        for (; i + WAVE_STAGES + 1 < cnt; i += 2) {
-            __pipeline_wait_prior(WAVE_STAGES / 2 - 1); /* this lane's records i, i+1 landed */
-            const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
-            const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
-            wave_request_at(sm, qa, s, lane);
-            wave_request_at(sm, qb, s + 1, lane);
-            __pipeline_commit();
-            qa = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + i + WAVE_STAGES + 2, REC_CAP - 1)]);
-            qb = *reinterpret_cast<const uint2 *>(&sm.recA[min(rec0 + i + WAVE_STAGES + 3, REC_CAP - 1)]);
-            prod_add(a.sum, a.pa);
-            prod_add(a.sum, a.pb);
-            wheel_products<false>(tg, sm, rec0 + i, i, lane, xa, a.pa);
-            wheel_products<false>(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
-            s = (s == WAVE_STAGES - 2) ? 0 : s + 2;
+    for (; i + 1 < cnt; i += 2) {
+        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, i + 2 < cnt, acc, par0);
+        core_step<NF, ENV, 1>(tg, sm, lane, rec0 + i + 1, i + 1, i + 3 < cnt, acc, par1);
+    }
+    if (i < cnt)
+        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, false, acc, par0);
+}
+
+/* a lane's four samples (two packed pairs) straight from the wave store, past L1 */
+__device__ __forceinline__ ulonglong2 ld_wave(const float4 *p)
+{
+    ulonglong2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p));
+    return r;
+}
+
+/* the same sum with every lane loading its own four samples of a wheel into registers, one
+ * wheel ahead of their use (LDG.128, coalesced: the warp reads the wheel's 512 contiguous
+ * bytes): no staging, no barrier, a third fewer instructions per wheel than the bulk-copy
+ * variant (profiles/r02_*).  Both variants are built; tbf_launch_stage_t picks. */
+template <int NF, bool ENV>
+__device__ __forceinline__ void core_tile_ldg(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
+                                              int cnt, CoreAcc (&acc)[NF])
+{
+    if (cnt <= 0)
+        return;
+    const float4 *base = reinterpret_cast<const float4 *>(sm.wave4) + lane;
+    ulonglong2 xn[NF];
+    {
+        const float4 *q = base + sm.recQ[rec0];
+#pragma unroll
+        for (int f = 0; f < NF; ++f)
+            xn[f] = ld_wave(q + 32 * f);
+    }
+#pragma unroll 1
+    for (int i = 0; i < cnt; ++i) {
+        ulonglong2 x[NF];
+#pragma unroll
+        for (int f = 0; f < NF; ++f)
+            x[f] = xn[f];
+        const float4 g = sm.recG[rec0 + i];
+        {
+            /* the last trip re-reads its own record: a load that is valid and never used */
+            const float4 *q = base + sm.recQ[rec0 + min(i + 1, cnt - 1)];
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                xn[f] = ld_wave(q + 32 * f);
         }
-    }
-#pragma unroll 1
-    for (; i < cnt; i += 2) {
-        __pipeline_wait_prior(WAVE_STAGES / 2 - 1);
-        const ulonglong2 xa = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s][lane]);
-        const ulonglong2 xb = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[s + 1][lane]);
-        if (i + WAVE_STAGES < cnt)
-            wave_request(sm, rec0 + i + WAVE_STAGES, s, lane);
-        if (i + WAVE_STAGES + 1 < cnt)
-            wave_request(sm, rec0 + i + WAVE_STAGES + 1, s + 1, lane);
-        __pipeline_commit();
-        /* add the previous two wheels' products, in list order ... */
-        prod_add(a.sum, a.pa);
-        prod_add(a.sum, a.pb);
-        /* ... and form this pair's */
-        wheel_products<ENV>(tg, sm, rec0 + i, i, lane, xa, a.pa);
-        if (i + 1 < cnt)
-            wheel_products<ENV>(tg, sm, rec0 + i + 1, i + 1, lane, xb, a.pb);
-        else
-            prod_none(a.pb);
-        s = (s == WAVE_STAGES - 2) ? 0 : s + 2;
+#pragma unroll
+        for (int f = 0; f < NF; ++f)
+            wheel_accumulate<ENV>(tg, sm, g, i, lane, x[f], acc[f]);
     }
 }
 
-/* the last wheels' products, then from lane = 4 consecutive samples to lane = sample of a
- * 32-sample block (s[k] = sample 32k + lane) through the idle wave stages; an empty active
- * list leaves the buffers zeroed (src/tonegen.cpp:3607-3612) */
-__device__ __forceinline__ void core_end(CoreAcc &a, TWarp &sm, int n_act, int lane, float (&s)[4],
+template <int NF, bool ENV, bool TMA>
+__device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
+                                          int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1)
+{
+    if (TMA)
+        core_tile_tma<NF, ENV>(tg, sm, lane, rec0, cnt, acc, par0, par1);
+    else
+        core_tile_ldg<NF, ENV>(tg, sm, lane, rec0, cnt, acc);
+}
+
+/* from lane = 4 consecutive samples to lane = sample of a 32-sample block (s[k] = sample
+ * 32k + lane) through the idle wave staging slots; an empty active list leaves the buffers
+ * zeroed (src/tonegen.cpp:3607-3612) */
+__device__ __forceinline__ void core_end(const CoreAcc &a, TWarp &sm, int n_act, int lane, float (&s)[4],
                                          float (&v)[4], float (&p)[4])
 {
-    prod_add(a.sum, a.pa);
-    prod_add(a.sum, a.pb);
-    __pipeline_wait_prior(0);
-    *reinterpret_cast<ulonglong2 *>(&sm.wstage[0][lane]) = make_ulonglong2(a.sum.s[0], a.sum.s[1]);
-    *reinterpret_cast<ulonglong2 *>(&sm.wstage[1][lane]) = make_ulonglong2(a.sum.v[0], a.sum.v[1]);
-    *reinterpret_cast<ulonglong2 *>(&sm.wstage[2][lane]) = make_ulonglong2(a.sum.p[0], a.sum.p[1]);
+    float4 *st = sm.wstage[0][0]; /* 3 x 512 B of the 2 KB */
+    st[lane] = make_float4(a.s[0], a.s[1], a.s[2], a.s[3]);
+    st[32 + lane] = make_float4(a.v[0], a.v[1], a.v[2], a.v[3]);
+    st[64 + lane] = make_float4(a.p[0], a.p[1], a.p[2], a.p[3]);
     __syncwarp();
-    const float *fs = reinterpret_cast<const float *>(sm.wstage[0]);
-    const float *fv = reinterpret_cast<const float *>(sm.wstage[1]);
-    const float *fp = reinterpret_cast<const float *>(sm.wstage[2]);
+    const float *fs = reinterpret_cast<const float *>(st);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         s[k] = fs[BLK * k + lane];
-        v[k] = fv[BLK * k + lane];
-        p[k] = fp[BLK * k + lane];
+        v[k] = fs[128 + BLK * k + lane];
+        p[k] = fs[256 + BLK * k + lane];
     }
-    __syncwarp(); /* the stages are requested into again by the next fragment */
+    /* the slots are requested into again by the next fragment: these generic-proxy accesses
+     * are ordered before its bulk copies */
+    fence_async_smem();
+    __syncwarp();
     if (n_act == 0) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
@@ -893,7 +965,69 @@ __device__ void check_list(InstState *st, TWarp &sm, int lane, int where, int f,
     }
 }
 #endif
-__global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p)
+/* scanner, percussion high-pass and the hand-over to stage R of one fragment whose three
+ * buffers are summed (src/tonegen.cpp:3699-3732) */
+__device__ __forceinline__ void post_fragment(const DevTonegenTables *tg, TWarp &sm, int lane, uint32_t f,
+                                              float *u_row, float *php_row, const float (&swl)[4],
+                                              const float (&vib)[4], const float (&prc)[4])
+{
+    TgScalars &sc = sm.sc;
+    const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
+    const float pz = sc.pz;
+    float *u_out = u_row + (size_t)f * TBF_FRAGMENT;
+    float *php_out = php_row + (size_t)f * TBF_FRAGMENT;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float uu = swl[k];
+        if (vib_on) {
+            const float y = vibrato_block(tg, sm, k, lane, vib[k]);
+            const float vy = sc.vibMixed ? __fmul_rn(__fadd_rn(vib[k], y), (float)0.7071067811865475) : y;
+            uu = __fadd_rn(uu, vy);
+        }
+        u_out[BLK * k + lane] = uu;
+        if (perc_on) { /* in-place differencer, src/tonegen.cpp:3719-3732 */
+            float prev = __shfl_up_sync(FULL, prc[k], 1);
+            float carry = pz; /* sample -1 of the fragment */
+            if (k > 0)
+                carry = __shfl_sync(FULL, prc[k > 0 ? k - 1 : 0], 31);
+            if (lane == 0)
+                prev = carry;
+            php_out[BLK * k + lane] = __fsub_rn(prev, prc[k]);
+        }
+    }
+    const float prc_last = __shfl_sync(FULL, prc[3], 31);
+    if (lane == 0) {
+        if (vib_on) {
+            sc.vibStator = (sc.vibStator + TBF_FRAGMENT * tg->vib_stator_increment) & 0x07FFFFFFu;
+            sc.vibOutPos = (sc.vibOutPos + TBF_FRAGMENT) & VBUF_MASK;
+        }
+        if (perc_on) {
+            sc.outputGain = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
+            sc.pz = prc_last;
+        }
+    }
+    __syncwarp();
+}
+
+/* statistics and the reference-UB flag of a quiet fragment */
+__device__ __forceinline__ void quiet_stats(TgScalars &sc, int lane, int n_act, int my_ins)
+{
+    const int n_ins = __reduce_add_sync(FULL, my_ins);
+    if (lane == 0) {
+        sc.statFragments += 1;
+        sc.statActiveWheels += (unsigned long long)n_act;
+        if (n_ins > 256)
+            sc.errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
+    }
+}
+
+#ifndef T_MIN_CTAS
+#define T_MIN_CTAS 8
+#endif
+/* TMA: the wheels' samples arrive by bulk copies through shared memory (true) or by per-lane
+ * 16-byte loads into registers (false) */
+template <bool TMA>
+__global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const RenderParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -907,8 +1041,17 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
 
     for (int i = lane; i < (int)(sizeof(TgScalars) / 4); i += 32)
         reinterpret_cast<uint32_t *>(&sm.sc)[i] = reinterpret_cast<const uint32_t *>(&st->tg)[i];
+    if (TMA && lane == 0) {
+#pragma unroll
+        for (int j = 0; j < T_SLOTS; ++j)
+            mbar_init(smem_u32(&sm.mbar[j]), 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncwarp();
+    uint32_t par0 = 0u, par1 = 0u; /* parity of each staging slot's next completed fill */
     const DevTonegenTables *tg = p.tg + sc.tgTables;
+    if (lane == 0)
+        sm.wave4 = tg->wave4;
     for (int s = lane; s < TBF_VRING; s += 32) {
         const uint32_t g = (sc.vibOutPos + (uint32_t)s) & VBUF_MASK;
         sm.vring[g & VRING_MASK] = st->vibBuffer[g];
@@ -925,13 +1068,17 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
     int dbg_fast = 0;
 #endif
     int n_act_cached = 0;
-    for (uint32_t f = 0; f < p.n_fragments; ++f) {
+    uint32_t f = 0;
+    while (f < p.n_fragments) {
         /* -- control events that precede this fragment -- */
         bool ev_applied = false;
+        uint32_t next_ev_fragment = 0xFFFFFFFFu; /* batch fragment of the first event still to come */
         while (ev_cur < ev_end) {
             const tbf_event *evp = p.events + ev_cur;
-            if (evp->fragment > p.frag_base + f)
+            if (evp->fragment > p.frag_base + f) {
+                next_ev_fragment = evp->fragment;
                 break;
+            }
             const int type = evp->type, a = evp->a, b = evp->b;
             ev_applied = true;
             if (type == TBF_EV_KEY_ON || type == TBF_EV_KEY_OFF) {
@@ -951,6 +1098,9 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
             ++ev_cur;
         }
         /* -- routing, key compression target, what stage R needs -- */
+        /* a quiet fragment followed by another one: both are summed in one pass over the records */
+        const bool pair_ok = f + 1 < p.n_fragments && next_ev_fragment > p.frag_base + f + 1 &&
+                             !(p.flags & 0x200u);
         if (lane == 0) {
             int kdc = sc.keyDownCount;
             if (kdc > 127 || kdc < 0) { /* reference reads past keyCompTable[128] */
@@ -972,33 +1122,54 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
             c.flags = (sm.perc_on ? FC_PERC_ON : 0u) | (sc.upperKeyCount == 0 ? FC_PERC_RESET : 0u);
             c.pad_[0] = c.pad_[1] = c.pad_[2] = 0u;
             ctl_row[f] = c;
+            /* nothing stage R looks at changes without an event */
+            if (pair_ok && cache_valid && !ev_applied && !sm.recompute_routing && !sm.draw_bar_change)
+                ctl_row[f + 1] = c;
         }
         __syncwarp();
-        const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
 
-        /* -- active-list pass and additive synthesis, REC_TILE wheels at a time -- */
+        /* -- active-list pass and additive synthesis -- */
         float swl[4], vib[4], prc[4];
+        const int n_act = sc.activeOscLEnd;
+        const bool quiet = cache_valid && !ev_applied && !sm.recompute_routing && !sm.draw_bar_change;
+        if (quiet && pair_ok) {
+            /* two quiet fragments: the records of the last fragment, one and two fragments further */
+#ifdef TBF_DEBUG_CHECKS
+            dbg_fast += 2;
+#endif
+            int ins_a = 0, ins_b = 0;
+            CoreAcc acc[2];
+            core_begin(acc[0]);
+            core_begin(acc[1]);
+            fast_pass<2>(tg, sm, lane, n_act, ins_a, ins_b);
+            __syncwarp();
+            core_tile<2, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1);
+            __syncwarp();
+            quiet_stats(sc, lane, n_act, ins_a);
+            quiet_stats(sc, lane, n_act, ins_b);
+            core_end(acc[0], sm, n_act, lane, swl, vib, prc);
+            __syncwarp();
+            post_fragment(tg, sm, lane, f, u_row, php_row, swl, vib, prc);
+            core_end(acc[1], sm, n_act, lane, swl, vib, prc);
+            __syncwarp();
+            post_fragment(tg, sm, lane, f + 1, u_row, php_row, swl, vib, prc);
+            f += 2;
+            continue;
+        }
         {
-            const int n_act = sc.activeOscLEnd;
-            int my_ins = 0;
-            CoreAcc acc;
-            core_begin(acc);
-            if (cache_valid && !ev_applied && !sm.recompute_routing && !sm.draw_bar_change) {
+            int my_ins = 0, unused = 0;
+            CoreAcc acc[1];
+            core_begin(acc[0]);
+            if (quiet) {
                 /* quiet fragment: the records of the last fragment, one fragment further */
 #ifdef TBF_DEBUG_CHECKS
                 ++dbg_fast;
 #endif
-                fast_pass(tg, sm, lane, n_act, my_ins);
+                fast_pass<1>(tg, sm, lane, n_act, my_ins, unused);
                 __syncwarp();
-                core_tile<false>(tg, sm, lane, 0, n_act, acc);
+                core_tile<1, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1);
                 __syncwarp();
-                const int n_ins = __reduce_add_sync(FULL, my_ins);
-                if (lane == 0) {
-                    sc.statFragments += 1;
-                    sc.statActiveWheels += (unsigned long long)n_act;
-                    if (n_ins > 256)
-                        sc.errorFlags |= TBF_IFLAG_COREPGM_OVERFLOW;
-                }
+                quiet_stats(sc, lane, n_act, my_ins);
             } else {
                 if (cache_valid) /* the pass below reads the positions from HBM */
                     flush_positions(st, sm, lane, n_act_cached);
@@ -1008,8 +1179,9 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
                     const int cnt = min(REC_TILE, n_act - base);
                     const int rec0 = persist ? base : 0;
                     active_list_tile(st, tg, sm, lane, base, cnt, rec0, my_ins);
+                    fence_async_smem(); /* rec_d shares the staging slots' B halves */
                     __syncwarp();
-                    core_tile<true>(tg, sm, lane, rec0, cnt, acc);
+                    core_tile<1, true, TMA>(tg, sm, lane, rec0, cnt, acc, par0, par1);
                     __syncwarp();
                 }
                 active_list_finish(st, sm, lane, n_act, my_ins);
@@ -1023,45 +1195,11 @@ __global__ void __launch_bounds__(T_WARPS * 32) tbf_stage_t(const RenderParams p
                 if (p.flags & 0x100u) /* debugging: always take the full pass */
                     cache_valid = false;
             }
-            core_end(acc, sm, n_act, lane, swl, vib, prc);
+            core_end(acc[0], sm, n_act, lane, swl, vib, prc);
         }
         __syncwarp();
-
-        /* -- scanner, percussion high-pass, hand-over to stage R -- */
-        const float pz = sc.pz;
-        float *u_out = u_row + (size_t)f * TBF_FRAGMENT;
-        float *php_out = php_row + (size_t)f * TBF_FRAGMENT;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            float uu = swl[k];
-            if (vib_on) {
-                const float y = vibrato_block(tg, sm, k, lane, vib[k]);
-                const float vy = sc.vibMixed ? __fmul_rn(__fadd_rn(vib[k], y), (float)0.7071067811865475) : y;
-                uu = __fadd_rn(uu, vy);
-            }
-            u_out[BLK * k + lane] = uu;
-            if (perc_on) { /* in-place differencer, src/tonegen.cpp:3719-3732 */
-                float prev = __shfl_up_sync(FULL, prc[k], 1);
-                float carry = pz; /* sample -1 of the fragment */
-                if (k > 0)
-                    carry = __shfl_sync(FULL, prc[k > 0 ? k - 1 : 0], 31);
-                if (lane == 0)
-                    prev = carry;
-                php_out[BLK * k + lane] = __fsub_rn(prev, prc[k]);
-            }
-        }
-        const float prc_last = __shfl_sync(FULL, prc[3], 31);
-        if (lane == 0) {
-            if (vib_on) {
-                sc.vibStator = (sc.vibStator + TBF_FRAGMENT * tg->vib_stator_increment) & 0x07FFFFFFu;
-                sc.vibOutPos = (sc.vibOutPos + TBF_FRAGMENT) & VBUF_MASK;
-            }
-            if (perc_on) {
-                sc.outputGain = __fmul_rn(sc.swellPedalGain, sc.percDrawbarGain);
-                sc.pz = prc_last;
-            }
-        }
-        __syncwarp();
+        post_fragment(tg, sm, lane, f, u_row, php_row, swl, vib, prc);
+        f += 1;
     }
 
     /* ---- write the staged state back ---- */
@@ -1524,13 +1662,19 @@ struct WTap {
     int q;             /* tap id inside its group, 0..5 (serial fallback order)           */
 };
 
+/* Stage W runs as two independent halves per organ, one warp each: the HORN half (reflection
+ * stages with FIR histories, six horn taps, delay lines HL HR) and the DRUM half (two reflection
+ * stages in registers, six drum taps, delay lines DL DR).  Nothing flows between them
+ * (src/whirl.cpp:1525-1588: the drum path restarts from the unfiltered input), so each half keeps
+ * only its own two delay-line rings in shared memory: 6 KB / 4.9 KB per warp instead of 10.9 KB,
+ * i.e. 32 resident warps per SM instead of 20. */
 struct WWarp {
-    float hx[3][8 + TBF_FRAGMENT]; /* horn stage inputs with 8 samples of history */
-    float dx[4 + TBF_FRAGMENT];    /* drum path input, history at index 3 (the two reflection
-                                      stages of a sample are formed in registers)            */
-    float zs[4];                   /* FILTER_C states z[0..3], NaN-scrubbed per fragment */
-    WTap tap[12];                  /* horn taps 0..5, drum taps 6..11 in processing order  */
-    /* followed by float ring[4][ring_size]: the delay lines HL HR DL DR */
+    float x[3][8 + TBF_FRAGMENT]; /* horn: stage inputs with 8 samples of history; drum: x[0] only,
+                                     the path's input with its history at index 7            */
+    float zs[2];                  /* FILTER_C states of the half (z[0..1] / z[2..3]), NaN-scrubbed
+                                     per fragment                                            */
+    WTap tap[6];                  /* the half's taps in processing order                       */
+    /* followed by float ring[2][ring_size]: the half's delay lines (left, right) */
 };
 
 /* FILTER_C(0.4, 0.4): the literals are double, so the 2-tap FIR is evaluated in
@@ -1540,21 +1684,56 @@ __device__ __forceinline__ float filter_c(float x, float z)
     return (float)__dadd_rn(__dmul_rn(0.4, (double)x), __dmul_rn(0.4, (double)z));
 }
 
-/* tap geometry (HN_MOTION / DR_MOTION, src/whirl.cpp:1432-1469) */
-__device__ __forceinline__ void tap_position(double ang_grd, int phase, const float2 *__restrict__ dsp,
-                                             float spacing, uint32_t outpos, float &frac,
-                                             uint32_t &slot, uint32_t &kround)
+/* floorf(x) and (unsigned)floorf(x) of 0 <= x < 2^22 without a conversion instruction: adding
+ * 2^23 with round-down leaves floor(x) in the mantissa (the sum's ulp is 1), both results exact */
+__device__ __forceinline__ float floor_small(float x, uint32_t &as_int)
+{
+    const float y = __fadd_rd(x, 8388608.0f);
+    as_int = __float_as_uint(y) & 0x007FFFFFu;
+    return __fsub_rn(y, 8388608.0f);
+}
+
+/* tap geometry (HN_MOTION / DR_MOTION, src/whirl.cpp:1432-1469).  FAST: the caller has checked
+ * that the rotor angle is in [+0, 1) and the host that phases and delays are small and non-
+ * negative (DevWhirlTables::small_index), so h1 and t lie in [+0, 2^22): truncf = floorf,
+ * roundf(h1) = floorf(h1) + (fractional part >= 0.5), and the float <-> integer conversions of
+ * the reference become mantissa reads -- same values, no XU-pipe instruction. */
+template <bool FAST>
+__device__ __forceinline__ void tap_index(double ang_grd, int phase, float &hd, uint32_t &hl, uint32_t &kround)
 {
     const float h1 = (float)__dadd_rn(__dmul_rn(ang_grd, (double)TBF_WHIRL_DISPLC), (double)phase);
-    const float hd = __fsub_rn(h1, truncf(h1)); /* fmodf(h1, 1.f), exact */
-    const uint32_t hl = f2u_x86(floorf(h1)) & DISPLC_MASK;
-    const float2 d = __ldg(dsp + hl); /* d[hl], d[(hl + 1) & mask] */
+    if (FAST) {
+        const float fl = floor_small(h1, hl);
+        hd = __fsub_rn(h1, fl);
+        kround = hl + (hd >= 0.5f ? 1u : 0u); /* roundf of a non-negative float: halves go up */
+    } else {
+        hd = __fsub_rn(h1, truncf(h1)); /* fmodf(h1, 1.f), exact */
+        hl = f2u_x86(floorf(h1));
+        kround = f2u_x86(roundf(h1));
+    }
+    hl &= DISPLC_MASK;
+    kround &= DISPLC_MASK;
+}
+
+/* d = {displacement[hl], displacement[hl + 1]} -> fractional delay-line position of the tap */
+template <bool FAST>
+__device__ __forceinline__ void tap_slot(const float2 d, float hd, float spacing, uint32_t outpos, float &frac,
+                                         uint32_t &slot)
+{
     const float intp = __fadd_rn(__fmul_rn(d.x, __fsub_rn(1.f, hd)), __fmul_rn(hd, d.y));
-    kround = f2u_x86(roundf(h1)) & DISPLC_MASK;
-    const float t = __fadd_rn(__fadd_rn(spacing, intp), (float)outpos);
-    const float r = floorf(t);
-    frac = __fsub_rn(t, r);
-    slot = f2u_x86(r) & WBUF_MASK;
+    if (FAST) {
+        /* (float)outpos, outpos < 2^11, off the mantissa */
+        const float t_out = __fsub_rn(__uint_as_float(0x4B000000u | outpos), 8388608.0f);
+        const float t = __fadd_rn(__fadd_rn(spacing, intp), t_out);
+        const float r = floor_small(t, slot);
+        frac = __fsub_rn(t, r);
+    } else {
+        const float t = __fadd_rn(__fadd_rn(spacing, intp), (float)outpos);
+        const float r = floorf(t);
+        frac = __fsub_rn(t, r);
+        slot = f2u_x86(r);
+    }
+    slot &= WBUF_MASK;
 }
 
 /* What the parallel delay-line update relies on, checked per block and tap: the
@@ -1649,16 +1828,76 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p, const uint32_t ring_size)
+/* the six taps of one half for one 32-sample block: geometry, table reads, (horn) FIRs, the
+ * fractional split.  Written in groups of three taps -- index math and loads first, consumers
+ * after -- so that the reads of a group are in flight together. */
+template <bool DRUM, bool FAST>
+__device__ __forceinline__ void block_taps(const WWarp &sm, const int i, const double ang, const uint32_t outpos,
+                                           const uint32_t outpos_blk, const uint32_t window, const int lane,
+                                           uint32_t (&tn)[6], uint32_t (&tn1)[6], uint32_t (&tn2)[6],
+                                           float (&ta)[6], float (&tb)[6], int &bad)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t slot = blockIdx.x * W_WARPS + warp;
-    if (slot >= p.n_instances)
-        return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
-    const size_t per_warp = sizeof(WWarp) + (size_t)4 * ring_size * sizeof(float);
-    WWarp &sm = *reinterpret_cast<WWarp *>(smem_raw + per_warp * warp);
-    float *ring = reinterpret_cast<float *>(smem_raw + per_warp * warp + sizeof(WWarp));
+    float d0 = 0.f, d1 = 0.f, d2 = 0.f;
+    if (DRUM) {
+        /* the drum path's reflection stages of this sample; stage 1 of sample i-1 is
+         * recomputed locally instead of exchanged */
+        const float d0m = sm.x[0][7 + i];
+        d0 = sm.x[0][8 + i];
+        d1 = filter_c(d0, d0m);
+        const float d1m = i ? filter_c(d0m, i > 1 ? sm.x[0][6 + i] : sm.zs[0]) : sm.zs[1];
+        d2 = filter_c(d1, d1m);
+    }
+#pragma unroll
+    for (int g = 0; g < 6; g += 3) {
+        float hd[3], b0[3], b1[3], b2[3], b3[3], b4[3];
+        float2 d[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const WTap &t = sm.tap[g + c];
+            uint32_t hl, kr;
+            tap_index<FAST>(DRUM ? ang : __dadd_rn(ang, t.ang_off), t.phase, hd[c], hl, kr);
+            d[c] = __ldg(t.dsp + hl);
+            if (!DRUM) {
+                const float *b = t.bw + kr;
+                b0[c] = __ldg(b);
+                b1[c] = __ldg(b + DISPLC_MASK + 1);
+                b2[c] = __ldg(b + 2 * (DISPLC_MASK + 1));
+                b3[c] = __ldg(b + 3 * (DISPLC_MASK + 1));
+                b4[c] = __ldg(b + 4 * (DISPLC_MASK + 1));
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const int j = g + c;
+            const WTap &t = sm.tap[j];
+            float frac, xa;
+            tap_slot<FAST>(d[c], hd[c], t.spacing, outpos, frac, tn[j]);
+            if (!DRUM) {
+                /* horn taps: 5-tap FIR over the stage's history (src/whirl.cpp:1432-1453) */
+                const float *hx = &sm.x[t.stage][8 + i];
+                xa = __fmul_rn(b0[c], hx[0]);
+                xa = __fadd_rn(xa, __fmul_rn(b1[c], hx[-1]));
+                xa = __fadd_rn(xa, __fmul_rn(b2[c], hx[-2]));
+                xa = __fadd_rn(xa, __fmul_rn(b3[c], hx[-3]));
+                xa = __fadd_rn(xa, __fmul_rn(b4[c], hx[-4]));
+            } else { /* drum taps (src/whirl.cpp:1455-1469, :1566-1588) */
+                xa = t.stage == 0 ? d0 : (t.stage == 1 ? d1 : d2);
+            }
+            const float qq = __fmul_rn(xa, frac);
+            ta[j] = __fsub_rn(xa, qq);
+            tb[j] = qq;
+            tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
+            tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
+            bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
+        }
+    }
+}
+
+/* one half of stage W for one organ: DRUM = false the horn half, true the drum half */
+template <bool DRUM>
+__device__ __forceinline__ void stage_w_half(const RenderParams &p, const uint32_t ring_size, WWarp &sm,
+                                             float *ring, const uint32_t slot, const int lane)
+{
     const uint32_t rmask = ring_size - 1;
     const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
     InstState *st = p.states + id;
@@ -1666,27 +1905,30 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
     if (wh->bypass)
         return; /* whirlProc2 leaves a bypassed Leslie untouched (src/whirl.cpp:1197-1215) */
 
-    WhirlScalars ws = st->wl; /* every lane holds a copy; lane 0 writes it back */
-    uint32_t outpos0 = ws.outpos;
-    for (int line = 0; line < 4; ++line)
+    const WhirlScalars &ws = st->wl;
+    uint32_t outpos0 = DRUM ? ws.outpos_drum : ws.outpos;
+    const int line0 = DRUM ? 2 : 0;
+    for (int line = 0; line < 2; ++line)
         for (uint32_t s = lane; s < ring_size; s += 32) {
             const uint32_t g = (outpos0 + s) & WBUF_MASK;
-            ring[line * ring_size + (g & rmask)] = st->wbuf[line][g];
+            ring[line * ring_size + (g & rmask)] = st->wbuf[line0 + line][g];
         }
-    if (lane < 24) {
+    int adi_l = 0;
+    if (!DRUM && lane < 24) {
         const int s = lane >> 3, k = lane & 7;
-        sm.hx[s][7 - k] = ws.adx[s][(ws.adi[s] + k) & 7];
+        adi_l = ws.adi[s];
+        sm.x[s][7 - k] = ws.adx[s][(adi_l + k) & 7];
     }
-    if (lane < 4)
-        sm.zs[lane] = ws.z[lane];
-    if (lane < 12) {
-        const int g = lane / 6, jj = lane % 6; /* group, processing index */
+    if (lane < 2)
+        sm.zs[lane] = ws.z[(DRUM ? 2 : 0) + lane];
+    if (lane < 6) {
+        const int g = DRUM ? 1 : 0, jj = lane; /* group, processing index */
         const int q = wh->tap_order[2 * g + jj / 3][jj % 3] - 6 * g;
         /* taps 0,3,4 read the forward displacement table with the backward FIR bank,
          * taps 1,2,5 the other way round */
         const bool fwd = (q == 0 || q == 3 || q == 4);
         WTap t;
-        if (g == 0) {
+        if (!DRUM) {
             t.dsp = fwd ? wh->hn_fwd_displ : wh->hn_bwd_displ;
             t.bw = fwd ? wh->bbw : wh->bfw;
             t.ang_off = (q & 1) ? wh->bw_ang : wh->fw_ang;
@@ -1704,10 +1946,15 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
         sm.tap[lane] = t;
     }
     const bool gather_ok = wh->gather_ok != 0;
+    const bool small_index = wh->small_index != 0;
+    const double max_ang = DRUM ? 1.0 : wh->fast_max_angle; /* rotor angles below it keep h1 < 2^22 */
     const uint32_t window = (uint32_t)wh->window;
     int fell_back = 0;
     const size_t row = (size_t)slot * p.pitch;
-    double hang_next = p.hang[row + lane], dang_next = p.dang[row + lane];
+    const double *ang_row = DRUM ? p.dang : p.hang;
+    const float *in_row = DRUM ? p.dx0 : p.hx0;
+    float *out_l_row = p.line[line0], *out_r_row = p.line[line0 + 1];
+    double ang_next = ang_row[row + lane];
     __syncwarp();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
@@ -1715,132 +1962,118 @@ __global__ void __launch_bounds__(W_WARPS * 32) tbf_stage_w(const RenderParams p
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const int i = BLK * k + lane;
-            sm.hx[0][8 + i] = p.hx0[col + i];
-            sm.dx[4 + i] = p.dx0[col + i];
+            sm.x[0][8 + i] = in_row[col + i];
         }
-        if (lane == 0)
-            sm.dx[3] = sm.zs[2];
+        if (DRUM && lane == 0)
+            sm.x[0][7] = sm.zs[0];
         __syncwarp();
-        /* -- the two reflection filters of each path (2-tap FIRs in double); stage 1 of
-         *    sample i-1 is recomputed locally instead of exchanged -- */
+        if (!DRUM) {
+            /* -- the horn path's two reflection filters (2-tap FIRs in double); stage 1 of
+             *    sample i-1 is recomputed locally instead of exchanged -- */
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int i = BLK * k + lane;
-            const float h0 = sm.hx[0][8 + i], h0m = i ? sm.hx[0][7 + i] : sm.zs[0];
-            const float h1 = filter_c(h0, h0m);
-            const float h1m = i ? filter_c(h0m, i > 1 ? sm.hx[0][6 + i] : sm.zs[0]) : sm.zs[1];
-            sm.hx[1][8 + i] = h1;
-            sm.hx[2][8 + i] = filter_c(h1, h1m);
+            for (int k = 0; k < 4; ++k) {
+                const int i = BLK * k + lane;
+                const float h0 = sm.x[0][8 + i], h0m = i ? sm.x[0][7 + i] : sm.zs[0];
+                const float h1 = filter_c(h0, h0m);
+                const float h1m = i ? filter_c(h0m, i > 1 ? sm.x[0][6 + i] : sm.zs[0]) : sm.zs[1];
+                sm.x[1][8 + i] = h1;
+                sm.x[2][8 + i] = filter_c(h1, h1m);
+            }
+            __syncwarp();
         }
-        __syncwarp();
 
 #pragma unroll 1
         for (int k = 0; k < 4; ++k) {
             const int i = BLK * k + lane;
             const uint32_t outpos_blk = (outpos0 + (uint32_t)(BLK * k)) & WBUF_MASK;
             const uint32_t outpos = (outpos_blk + (uint32_t)lane) & WBUF_MASK;
-            const double hang = hang_next, dang = dang_next;
+            const double ang = ang_next;
             { /* the next block's rotor angles, one block ahead of their use */
                 const size_t nx = col + i + BLK;
-                if (k < 3 || f + 1 < p.n_fragments) {
-                    hang_next = p.hang[nx];
-                    dang_next = p.dang[nx];
-                }
+                if (k < 3 || f + 1 < p.n_fragments)
+                    ang_next = ang_row[nx];
             }
-            /* -- horn taps: geometry + 5-tap FIR (src/whirl.cpp:1432-1453, :1540-1563) -- */
+            /* the conversion-free index math needs the angle in [+0, limit): sign bit clear */
+            const bool fast = small_index &&
+                              __all_sync(FULL, __double_as_longlong(ang) >= 0 && ang < max_ang);
             uint32_t tn[6], tn1[6], tn2[6];
             float ta[6], tb[6];
             int bad = gather_ok ? 0 : 1;
-#pragma unroll
-            for (int j = 0; j < 6; ++j) {
-                const WTap &t = sm.tap[j];
-                float frac;
-                uint32_t kr;
-                tap_position(__dadd_rn(hang, t.ang_off), t.phase, t.dsp, t.spacing, outpos, frac, tn[j], kr);
-                const float *hx = &sm.hx[t.stage][8 + i];
-                const float *b = t.bw + kr;
-                const float b0 = __ldg(b), b1 = __ldg(b + DISPLC_MASK + 1), b2 = __ldg(b + 2 * (DISPLC_MASK + 1));
-                const float b3 = __ldg(b + 3 * (DISPLC_MASK + 1)), b4 = __ldg(b + 4 * (DISPLC_MASK + 1));
-                float xa = __fmul_rn(b0, hx[0]);
-                xa = __fadd_rn(xa, __fmul_rn(b1, hx[-1]));
-                xa = __fadd_rn(xa, __fmul_rn(b2, hx[-2]));
-                xa = __fadd_rn(xa, __fmul_rn(b3, hx[-3]));
-                xa = __fadd_rn(xa, __fmul_rn(b4, hx[-4]));
-                const float qq = __fmul_rn(xa, frac);
-                ta[j] = __fsub_rn(xa, qq);
-                tb[j] = qq;
-                tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
-                tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
-                bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
-            }
-            float hl, hr, dl, dr;
+            /* one warp-uniform branch per block, not per tap: inside a variant the six taps are
+             * straight-line code, so their table reads overlap */
+            if (fast)
+                block_taps<DRUM, true>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+            else
+                block_taps<DRUM, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+            float o_l, o_r;
             group_scatter_read(&sm.tap[0], ring, ring + ring_size, rmask, lane, outpos_blk, bad,
-                               gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, hl, hr);
-            /* -- drum taps (src/whirl.cpp:1455-1469, :1566-1588) -- */
-            bad = gather_ok ? 0 : 1;
-            /* the drum path's reflection stages of this sample; stage 1 of sample i-1 is
-             * recomputed locally instead of exchanged */
-            const float d0 = sm.dx[4 + i], d0m = sm.dx[3 + i];
-            const float d1 = filter_c(d0, d0m);
-            const float d1m = i ? filter_c(d0m, i > 1 ? sm.dx[2 + i] : sm.zs[2]) : sm.zs[3];
-            const float d2 = filter_c(d1, d1m);
-#pragma unroll
-            for (int j = 0; j < 6; ++j) {
-                const WTap &t = sm.tap[6 + j];
-                float frac;
-                uint32_t kr;
-                tap_position(dang, t.phase, t.dsp, t.spacing, outpos, frac, tn[j], kr);
-                const float x = t.stage == 0 ? d0 : (t.stage == 1 ? d1 : d2);
-                const float qq = __fmul_rn(x, frac);
-                ta[j] = __fsub_rn(x, qq);
-                tb[j] = qq;
-                tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
-                tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
-                bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
-            }
-            group_scatter_read(&sm.tap[6], ring + 2 * ring_size, ring + 3 * ring_size, rmask, lane,
-                               outpos_blk, bad, gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, dl, dr);
-            p.line[0][col + i] = hl;
-            p.line[1][col + i] = hr;
-            p.line[2][col + i] = dl;
-            p.line[3][col + i] = dr;
+                               gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, o_l, o_r);
+            out_l_row[col + i] = o_l;
+            out_r_row[col + i] = o_r;
         }
 
         /* carry FIR histories / filter states into the next fragment */
         float keep = 0.f;
-        if (lane < 24)
-            keep = sm.hx[lane >> 3][TBF_FRAGMENT + (lane & 7)];
+        if (!DRUM && lane < 24)
+            keep = sm.x[lane >> 3][TBF_FRAGMENT + (lane & 7)];
         float zc = 0.f;
-        if (lane < 4)
-            zc = (lane == 0) ? sm.hx[0][8 + 127] : (lane == 1) ? sm.hx[1][8 + 127]
-                 : (lane == 2) ? sm.dx[4 + 127] : filter_c(sm.dx[4 + 127], sm.dx[4 + 126]);
+        if (lane < 2) {
+            const float last = sm.x[0][8 + 127];
+            if (!DRUM)
+                zc = (lane == 0) ? last : sm.x[1][8 + 127];
+            else
+                zc = (lane == 0) ? last : filter_c(last, sm.x[0][8 + 126]);
+        }
         __syncwarp();
-        if (lane < 24)
-            sm.hx[lane >> 3][lane & 7] = keep;
-        if (lane < 4)
+        if (!DRUM && lane < 24)
+            sm.x[lane >> 3][lane & 7] = keep;
+        if (lane < 2)
             sm.zs[lane] = isnan(zc) ? 0.0f : zc; /* src/whirl.cpp:1627-1630 */
         outpos0 = (outpos0 + TBF_FRAGMENT) & WBUF_MASK;
         __syncwarp();
     }
 
     /* ---- write the staged state back ---- */
-    if (lane < 24) {
+    if (!DRUM && lane < 24) {
         const int s = lane >> 3, k = lane & 7;
-        st->wl.adx[s][(ws.adi[s] + k) & 7] = sm.hx[s][7 - k];
+        st->wl.adx[s][(adi_l + k) & 7] = sm.x[s][7 - k];
     }
-    if (lane < 4)
-        st->wl.z[lane] = sm.zs[lane];
+    if (lane < 2)
+        st->wl.z[(DRUM ? 2 : 0) + lane] = sm.zs[lane];
     if (lane == 0) {
-        st->wl.outpos = outpos0;
+        if (DRUM) /* both halves advance their read position alike */
+            st->wl.outpos_drum = outpos0;
+        else
+            st->wl.outpos = outpos0;
         if (fell_back)
-            st->wl.errorFlags = ws.errorFlags | TBF_IFLAG_GATHER_FALLBACK;
+            atomicOr(&st->wl.errorFlags, TBF_IFLAG_GATHER_FALLBACK);
     }
     /* outside the live windows every ring slot is zero (cleared when read) */
-    for (int line = 0; line < 4; ++line)
+    for (int line = 0; line < 2; ++line)
         for (uint32_t s = lane; s < TBF_WHIRL_BUF; s += 32) {
             const uint32_t g = (outpos0 + s) & WBUF_MASK;
-            st->wbuf[line][g] = (s < ring_size) ? ring[line * ring_size + (g & rmask)] : 0.0f;
+            st->wbuf[line0 + line][g] = (s < ring_size) ? ring[line * ring_size + (g & rmask)] : 0.0f;
         }
+}
+
+/* blockIdx.y = 0: horn halves, 1: drum halves; W_WARPS organs per CTA */
+#ifndef W_MIN_CTAS
+#define W_MIN_CTAS 8
+#endif
+__global__ void __launch_bounds__(W_WARPS * 32, W_MIN_CTAS) tbf_stage_w(const RenderParams p, const uint32_t ring_size)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t slot = blockIdx.x * W_WARPS + warp;
+    if (slot >= p.n_instances)
+        return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
+    const size_t per_warp = sizeof(WWarp) + (size_t)2 * ring_size * sizeof(float);
+    WWarp &sm = *reinterpret_cast<WWarp *>(smem_raw + per_warp * warp);
+    float *ring = reinterpret_cast<float *>(smem_raw + per_warp * warp + sizeof(WWarp));
+    if (blockIdx.y == 0)
+        stage_w_half<false>(p, ring_size, sm, ring, slot, lane);
+    else
+        stage_w_half<true>(p, ring_size, sm, ring, slot, lane);
 }
 
 /* ================================================================== */
@@ -2140,17 +2373,25 @@ int tbf_launch_wave_store(float *wave4, const float *raw, const uint32_t *meta, 
 size_t tbf_stage_t_smem(void) { return sizeof(TWarp) * T_WARPS; }
 size_t tbf_stage_w_smem(int ring_size)
 {
-    return (sizeof(WWarp) + (size_t)4 * ring_size * sizeof(float)) * W_WARPS;
+    return (sizeof(WWarp) + (size_t)2 * ring_size * sizeof(float)) * W_WARPS;
 }
 
 int tbf_launch_stage_t(const RenderParams &p, void *stream)
 {
-    static int have[TBF_MAX_DEVICES] = {0};
+    static int have[2][TBF_MAX_DEVICES] = {{0}, {0}};
     const size_t smem = tbf_stage_t_smem();
-    if (int rc = set_smem(tbf_stage_t, smem, have))
-        return rc;
+    /* wave loads: "ldg" (default, the faster one: profiles/r02_*) or "tma" (bulk copies) */
+    static const bool tma = getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "tma");
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
-    tbf_stage_t<<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
+    if (tma) {
+        if (int rc = set_smem(tbf_stage_t<true>, smem, have[1]))
+            return rc;
+        tbf_stage_t<true><<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
+    } else {
+        if (int rc = set_smem(tbf_stage_t<false>, smem, have[0]))
+            return rc;
+        tbf_stage_t<false><<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
+    }
     debug_sync(stream, "T");
     return (int)cudaGetLastError();
 }
@@ -2175,7 +2416,7 @@ int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
     const size_t smem = tbf_stage_w_smem(ring_size);
     if (int rc = set_smem(tbf_stage_w, smem, have))
         return rc;
-    const uint32_t grid = (p.n_instances + W_WARPS - 1) / W_WARPS;
+    const dim3 grid((p.n_instances + W_WARPS - 1) / W_WARPS, 2); /* y: horn halves, drum halves */
     tbf_stage_w<<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
     debug_sync(stream, "W");
     return (int)cudaGetLastError();
