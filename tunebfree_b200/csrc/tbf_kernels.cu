@@ -1021,8 +1021,10 @@ __device__ __forceinline__ void quiet_stats(TgScalars &sc, int lane, int n_act, 
     }
 }
 
+/* 7 CTAs = 28 warps per SM at 72 registers: measured ahead of 8 CTAs at 64 registers, where the
+ * pair loop spills two of its 24 running sums (profiles/r02_knob_sweep.md) */
 #ifndef T_MIN_CTAS
-#define T_MIN_CTAS 8
+#define T_MIN_CTAS 7
 #endif
 /* TMA: the wheels' samples arrive by bulk copies through shared memory (true) or by per-lane
  * 16-byte loads into registers (false) */

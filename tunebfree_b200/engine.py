@@ -18,7 +18,8 @@ import numpy as np
 from . import cabi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtbf_gpu.so")
+# TBF_LIB: another build of the same library (kernel experiments); the product is libtbf_gpu.so
+LIB_PATH = os.environ.get("TBF_LIB") or os.path.join(_HERE, "libtbf_gpu.so")
 _lib = None
 
 
