@@ -409,9 +409,11 @@ def run_gpu_arm(a):
         wh_handles["default"] = ctx.whirl_tables(wt0)
         tables.free_tables(tt0, wt0)
 
+        host_waves = bool(os.environ.get("TBF_BENCH_HOST_WAVES"))  # round 1's path, for comparison
+
         def build_one(g):
             sp = tables.InstanceSpec(freqs=tables.freqs_from_ratios(sweep_degs[g]), seed=1)
-            return sp.build_tonegen()
+            return (sp.build_tonegen(), None) if host_waves else sp.build_tonegen_synth()
 
         ids = np.zeros(n_inst, dtype=np.uint32)
         t_wait = t_upload = 0.0
@@ -426,8 +428,8 @@ def run_gpu_arm(a):
                 built = [f.result() for f in futures]
                 t1 = time.perf_counter()
                 futures = [pool.submit(build_one, g) for g in chunks[c + 1]] if c + 1 < len(chunks) else []
-                for k, tt in enumerate(built):
-                    h = ctx.tonegen_tables(tt)
+                for k, (tt, ws) in enumerate(built):
+                    h = ctx.tonegen_tables(tt) if ws is None else ctx.tonegen_tables_synth(tt, ws)
                     tg_handles[lo + k] = h
                     ids[lo + k] = ctx.create_instances(h, wh_handles["default"], 1)
                     tables.free_tables(tt, None)
@@ -438,8 +440,12 @@ def run_gpu_arm(a):
         t_init = time.perf_counter() - t_init0
         init = {"organs_initialised_per_s": n_inst / t_init, "wall_s": t_init, "host_threads": threads,
                 "upload_s": t_upload, "waiting_for_builders_s": t_wait,
-                "what": "128 frequencies -> tone-generator tables on the host cores "
-                        "(tbf_build_tonegen_tables), upload, instance create; builders and uploads overlap"}
+                "wave_synthesis": "host" if host_waves else "device",
+                "synth_samples_flagged_differed": None if host_waves else list(ctx.synth_stats()),
+                "what": "128 frequencies -> wheel choice, play matrix, loop lengths, envelopes on the host "
+                        "cores (tbf_build_tonegen_tables_synth), the 256 wavetables of every organ "
+                        "synthesised on the device (tbf_gpu_tonegen_tables_create_synth), instance "
+                        "create; builders and uploads overlap"}
     else:
         ids = sharding.slot_instance_ids(
             groups, lambda k, count: ctx.create_instances(tg_handles[(k[0], k[2])], wh_handles[k[1]], count))

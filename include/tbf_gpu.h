@@ -215,6 +215,19 @@ const char *tbf_gpu_last_error(const tbf_ctx *ctx);
 /* upload table sets; the library copies everything                          */
 int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int *handle);
 int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *handle);
+/* GPU-side init: the same as tbf_gpu_tonegen_tables_create, but the 256
+ * wavetables -- writeSamples(), src/tonegen.cpp:1402-1457, nine tenths of initToneGenerator's
+ * time -- are synthesised on the device from `synth` (include/tbf_tables.h:
+ * tbf_build_tonegen_tables_synth leaves t->wave_data NULL and fills it).  Bit-identical to the
+ * host-built tables: every double operation is the reference's; samples whose float could
+ * hinge on the last bit of a libm sine (about one in ten table sets) are recomputed by the
+ * host's libm and patched.  tbf_gpu_synth_stats: how many samples were flagged / differed. */
+struct tbf_wave_synth;
+int tbf_gpu_tonegen_tables_create_synth(tbf_ctx *ctx, const tbf_tonegen_tables *t,
+                                        const struct tbf_wave_synth *synth, int *handle);
+int tbf_gpu_synth_stats(const tbf_ctx *ctx, uint64_t *flagged, uint64_t *differed);
+/* the raw waves of a set as the device holds them (wave_offset layout): parity tests */
+int tbf_gpu_tonegen_tables_read_waves(tbf_ctx *ctx, int handle, float *out, uint64_t n_floats);
 /* how the kernels treat a whirl table set: 1 = parallel ordered gather of the delay lines
  * (the three taps of each line have disjoint delay ranges), 0 = serial path; ring = shared-
  * memory slots per delay line (512 or 2048); window = live slots ahead of the reader */

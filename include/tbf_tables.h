@@ -108,6 +108,28 @@ int tbf_spec_apply_cfg(tbf_tonegen_spec *tg, tbf_whirl_spec *wh, const char *key
  * (e.g. transformer crosstalk > 0 with 256 wheels, src/tonegen.cpp:925-937). */
 int tbf_build_tonegen_tables(const tbf_tonegen_spec *spec, tbf_tonegen_tables *out);
 void tbf_free_tonegen_tables(tbf_tonegen_tables *t);
+
+/* What writeSamples() (src/tonegen.cpp:1402-1457) needs to synthesise the 256 wavetables: the
+ * GPU-side init path builds everything else on the host and leaves the waves
+ * -- nine tenths of initToneGenerator's time -- to tbf_gpu_tonegen_tables_create_synth(). */
+typedef struct tbf_wave_synth {
+    double sample_rate;
+    uint32_t seed;                           /* srand() value: one rand() per sample (dither) */
+    uint32_t pad_;
+    double harmonics[TBF_MAX_PARTIALS];      /* wheelHarmonics after osc.harmonic.*           */
+    double f1[TBF_NOF_WHEELS + 1];           /* wheel frequency, Hz                           */
+    double attenuation[TBF_NOF_WHEELS + 1];  /* wheel equalisation                            */
+} tbf_wave_synth;
+/* tbf_build_tonegen_tables without the wave samples: out->wave_data stays NULL (offsets,
+ * lengths and wave_total are filled) and *synth says how to make them; every other table,
+ * the click envelopes' position in the rand() stream included, is identical. */
+int tbf_build_tonegen_tables_synth(const tbf_tonegen_spec *spec, tbf_tonegen_tables *out,
+                                   tbf_wave_synth *synth);
+/* sample i of wheel `wheel` exactly as writeSamples computes it with the host's libm;
+ * dither_bit = 1 when the sample's rand() draw was below RAND_MAX / 2 */
+float tbf_wave_sample(const tbf_wave_synth *synth, int wheel, uint32_t i, int dither_bit);
+/* the dither decisions of the first n draws after srand(seed), bit k of bits[k / 32] */
+void tbf_dither_bits(uint32_t seed, uint64_t n, uint32_t *bits);
 int tbf_build_whirl_tables(const tbf_whirl_spec *spec, tbf_whirl_tables *out);
 
 /* setIIRFilter() (src/whirl.cpp:147-172) over eqCompute() (src/eqcomp.cpp:109-203): the

@@ -39,23 +39,24 @@ def _run(ref, ctx, n, n_frag, config, sampled):
 
 
 def test_config3_4096_organs(ref, gpu_ctx):
-    """4096 organs x 1 s through tonegen + vibrato + Leslie (whirlProc3)."""
-    _run(ref, gpu_ctx, 4096, 375, 3, sampled=(0, 1, 31, 32, 1000, 2047, 2048, 4095))
+    """BASELINE config 3 at its full size: 4096 organs x 10 s through tonegen + vibrato + Leslie
+    (whirlProc3); 8 sampled organs against the oracle."""
+    _run(ref, gpu_ctx, 4096, 3750, 3, sampled=(0, 1, 31, 32, 1000, 2047, 2048, 4095))
 
 
 def test_config2_1024_organs(ref, gpu_ctx):
-    """1024 organs x 2 s, tone generator only."""
-    _run(ref, gpu_ctx, 1024, 750, 2, sampled=(0, 5, 511, 1023))
+    """BASELINE config 2 at its full size: 1024 organs x 10 s, tone generator only."""
+    _run(ref, gpu_ctx, 1024, 3750, 2, sampled=(0, 5, 511, 1023))
 
 
 def test_config5_cfg_mix_16384_organs(ref, gpu_ctx):
-    """BASELINE config 5 at its full instance count, 0.25 s: every pair of the reference's 10 osc x
+    """BASELINE config 5 at its full size (16 384 organs x 10 s): every pair of the reference's 10 osc x
     3 whirl cfg variants with 16 engine seeds (80 wave-table sets, 3 Leslie table sets, tables from
     the product's own builder), organs grouped by table set.  One organ of each of the 30 pairs
     and a few others are rendered by the oracle -- its own cfg parser fed the same text -- and
     compared through the device checksum."""
     from tunebfree_b200 import sharding, tables
-    n, n_frag = 16384, 94
+    n, n_frag = 16384, 3750
     variant = lambda g: workloads.organ_variant(g, 5)
     gids, groups = sharding.shard_plan_grouped(0, 1, n, variant)
     assert len(groups) == 240 and sorted(gids.tolist()) == list(range(n))
@@ -92,14 +93,14 @@ def test_config5_cfg_mix_16384_organs(ref, gpu_ctx):
 def test_config4_scala_sweep_all_scales(ref):
     """BASELINE config 4 at its full size: one organ per scale of the reference's Scala archive
     (5176 tunings, each with its own wave store built by the product's table builder on the host
-    cores), 0.5 s of the sweep chord through tonegen + vibrato + Leslie.  Every 173rd organ is
+    cores), 2 s of the sweep chord through tonegen + vibrato + Leslie.  Every 173rd organ (30) is
     rendered by the oracle from the same 128 frequencies and compared through the device
     checksum; different tunings must give different audio."""
     from concurrent.futures import ThreadPoolExecutor
     import os
     from tunebfree_b200 import tables
     names, degs, _ = workloads.scala_sweep()
-    n, n_frag = len(names), 188
+    n, n_frag = len(names), 750
     ctx = engine.Context(0)  # own context: 31 GB of wave stores are released with it
     tt0, wt0 = tables.InstanceSpec(seed=1).build()
     wh = ctx.whirl_tables(wt0)

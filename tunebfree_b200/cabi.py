@@ -169,6 +169,18 @@ class Event(C.Structure):
     ]
 
 
+class WaveSynth(C.Structure):
+    """tbf_wave_synth (include/tbf_tables.h)"""
+    _fields_ = [
+        ("sample_rate", C.c_double),
+        ("seed", C.c_uint32),
+        ("pad_", C.c_uint32),
+        ("harmonics", C.c_double * 12),
+        ("f1", C.c_double * (NOF_WHEELS + 1)),
+        ("attenuation", C.c_double * (NOF_WHEELS + 1)),
+    ]
+
+
 class BatchDesc(C.Structure):
     _fields_ = [
         ("n_instances", C.c_uint32),

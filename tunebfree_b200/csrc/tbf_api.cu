@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "tbf_device.h"
+#include "tbf_tables.h"
 
 struct TgSet {
     tbf_tonegen_tables host; /* scalars only; pointers nulled */
@@ -67,8 +68,27 @@ struct tbf_ctx {
     InstState *d_tmpl = nullptr;
     /* table upload: page-locked staging and the device copy of the raw waves + their index,
      * grown on demand (tbf_gpu_tonegen_tables_create) */
-    unsigned char *h_stage = nullptr, *d_stage = nullptr;
-    size_t cap_h_stage = 0, cap_d_stage = 0;
+    /* two staging slots in rotation: the copies and kernels of one table set run while the host
+     * fills the other slot; a slot is reused once its event has fired (no per-call sync) */
+    struct StageSlot {
+        unsigned char *h = nullptr, *d = nullptr;
+        size_t cap_h = 0, cap_d = 0;
+        cudaEvent_t done = nullptr;
+        bool used = false;
+    } stage[2];
+    int stage_next = 0;
+    /* device-side wave synthesis (tbf_gpu_tonegen_tables_create_synth): the dither decisions
+     * of each rand() seed, host and device copies, and the list of flagged samples */
+    struct DitherStream {
+        uint32_t seed = 0;
+        uint64_t n = 0; /* draws covered */
+        std::vector<uint32_t> host;
+        uint32_t *dev = nullptr;
+    };
+    std::vector<DitherStream> dither;
+    uint32_t *d_flags = nullptr, *h_flags = nullptr; /* [0] = count, then uint4 records */
+    float *h_patch = nullptr;                         /* page-locked repaired samples        */
+    uint64_t synth_flagged = 0, synth_differed = 0;
     /* per-render scratch, grown on demand */
     tbf_event *d_events = nullptr;
     size_t cap_events = 0;
@@ -170,6 +190,17 @@ int tbf_gpu_create(tbf_ctx **out, int device)
         return TBF_ERR_CUDA;
     }
     bool ok = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming) == cudaSuccess;
+    {
+        /* table sets come from the stream-ordered pool (a host that re-tunes frees and allocates
+         * one per change): freed blocks stay cached instead of going back to the driver */
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        for (auto &sl : ctx->stage)
+            ok = ok && cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) == cudaSuccess;
+    }
     /* the lane = instance stages (R, D) are latency-bound and small: their CTAs go first
      * whenever an SM has room, so they run beside the throughput stages instead of after */
     int prio_lo = 0, prio_hi = 0;
@@ -214,8 +245,17 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     cudaFree(ctx->d_wh);
     cudaFree(ctx->d_states);
     cudaFree(ctx->d_tmpl);
-    cudaFreeHost(ctx->h_stage);
-    cudaFree(ctx->d_stage);
+    for (auto &sl : ctx->stage) {
+        cudaFreeHost(sl.h);
+        cudaFree(sl.d);
+        if (sl.done)
+            cudaEventDestroy(sl.done);
+    }
+    for (auto &ds : ctx->dither)
+        cudaFree(ds.dev);
+    cudaFree(ctx->d_flags);
+    cudaFreeHost(ctx->h_flags);
+    cudaFreeHost(ctx->h_patch);
     cudaFree(ctx->d_events);
     cudaFree(ctx->d_ev_start);
     cudaFree(ctx->d_ev_cursor);
@@ -254,9 +294,51 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
 
 const char *tbf_gpu_last_error(const tbf_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
-int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int *handle)
+} /* extern "C" */
+
+extern "C" {
+static bool tg_usable(const tbf_ctx *ctx, int h);
+}
+
+/* the dither decisions of the first `n` rand() draws after srand(seed), on both sides */
+static int dither_stream(tbf_ctx *ctx, uint32_t seed, uint64_t n, const uint32_t **host, const uint32_t **dev)
 {
-    if (!ctx || !t || !handle || !t->wave_data)
+    tbf_ctx::DitherStream *ds = nullptr;
+    for (auto &d : ctx->dither)
+        if (d.seed == seed)
+            ds = &d;
+    if (!ds) {
+        ctx->dither.emplace_back();
+        ds = &ctx->dither.back();
+        ds->seed = seed;
+    }
+    if (ds->n < n) {
+        const uint64_t want = std::max<uint64_t>(n, (uint64_t)1 << 20); /* 1 Mi draws cover 48 kHz sets */
+        std::vector<uint32_t> bits((want + 31) / 32);
+        tbf_dither_bits(seed, want, bits.data());
+        uint32_t *dev_new = nullptr;
+        CK(cudaMalloc(&dev_new, sizeof(uint32_t) * bits.size()));
+        CK(cudaMemcpy(dev_new, bits.data(), sizeof(uint32_t) * bits.size(), cudaMemcpyHostToDevice));
+        if (ds->dev) {
+            CK(cudaStreamSynchronize(ctx->stream)); /* a synthesis in flight may still read the old copy */
+            cudaFree(ds->dev);
+        }
+        ds->dev = dev_new;
+        ds->host.swap(bits);
+        ds->n = want;
+    }
+    *host = ds->host.data();
+    *dev = ds->dev;
+    return TBF_OK;
+}
+
+#define TBF_SYNTH_FLAG_CAP 4096u
+
+/* upload one tone-generator table set; with `synth` the wave samples are made on the device */
+static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, const tbf_wave_synth *synth,
+                                 int *handle)
+{
+    if (!ctx || !t || !handle || (!synth && !t->wave_data))
         return fail(ctx, TBF_ERR_ARG, "tonegen tables: null argument");
     const uint32_t nc = t->contrib_start[TBF_MAX_KEYS];
     for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
@@ -274,38 +356,41 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
         if (t->contrib_wheel[e] < 1 || t->contrib_wheel[e] > TBF_NOF_WHEELS ||
             t->contrib_bus[e] >= TBF_NOF_BUSES || t->wave_length[t->contrib_wheel[e]] == 0)
             return fail(ctx, TBF_ERR_ARG, "tonegen tables: contribution out of range");
-    /* the kernels keep a 256-slot window of the scanner's delay line in shared memory:
-     * every write must land inside it (offsets are (1 + A + A sin) * 65536 with A <= 9
-     * for the reference's tables, src/vibrato.cpp:249-255) */
+    /* the kernels keep a TBF_VRING-slot window of the scanner's delay line in shared memory:
+     * every write must land inside it (offsets are (1 + A + A sin) * 65536 with A <= 12
+     * for everything scanner.modulation.* accepts, src/vibrato.cpp:249-255, :343-352) */
     for (int k = 0; k < 3; ++k)
         for (int i = 0; i < TBF_VIB_TBL; ++i)
             if ((t->vib_offset_table[k][i] >> 16) + TBF_SCAT_BLOCK + 2 >= TBF_VRING)
-                return fail(ctx, TBF_ERR_GEOMETRY, "tonegen tables: scanner offset beyond the 256-slot window");
+                return fail(ctx, TBF_ERR_GEOMETRY, "tonegen tables: scanner offset beyond the shared-memory window");
     /* wheel runs of every key's contribution list; a warp applies a key event with
      * lane = contribution when the list is wheel-sorted with unique (wheel, bus) pairs
      * (compilePlayMatrix builds it that way, src/tonegen.cpp:1183-1201) */
     std::vector<uint16_t> run_wheel, run_count;
     std::vector<uint32_t> run_start(TBF_MAX_KEYS + 1, 0);
     bool coop = true;
-    for (int k = 0; k < TBF_MAX_KEYS; ++k) {
-        run_start[k] = (uint32_t)run_wheel.size();
-        std::vector<uint8_t> wheel_seen(TBF_NOF_WHEELS + 1, 0);
-        for (uint32_t e = t->contrib_start[k]; e < t->contrib_start[k + 1];) {
-            const uint16_t w = t->contrib_wheel[e];
-            if (wheel_seen[w])
-                coop = false; /* the wheel comes back after another one */
-            wheel_seen[w] = 1;
-            uint32_t e2 = e;
-            uint32_t bus_seen = 0;
-            while (e2 < t->contrib_start[k + 1] && t->contrib_wheel[e2] == w) {
-                if (bus_seen & (1u << t->contrib_bus[e2]))
-                    coop = false;
-                bus_seen |= 1u << t->contrib_bus[e2];
-                ++e2;
+    {
+        std::vector<uint8_t> wheel_seen(TBF_NOF_WHEELS + 1);
+        for (int k = 0; k < TBF_MAX_KEYS; ++k) {
+            run_start[k] = (uint32_t)run_wheel.size();
+            std::fill(wheel_seen.begin(), wheel_seen.end(), 0);
+            for (uint32_t e = t->contrib_start[k]; e < t->contrib_start[k + 1];) {
+                const uint16_t w = t->contrib_wheel[e];
+                if (wheel_seen[w])
+                    coop = false; /* the wheel comes back after another one */
+                wheel_seen[w] = 1;
+                uint32_t e2 = e;
+                uint32_t bus_seen = 0;
+                while (e2 < t->contrib_start[k + 1] && t->contrib_wheel[e2] == w) {
+                    if (bus_seen & (1u << t->contrib_bus[e2]))
+                        coop = false;
+                    bus_seen |= 1u << t->contrib_bus[e2];
+                    ++e2;
+                }
+                run_wheel.push_back(w);
+                run_count.push_back((uint16_t)(e2 - e));
+                e = e2;
             }
-            run_wheel.push_back(w);
-            run_count.push_back((uint16_t)(e2 - e));
-            e = e2;
         }
     }
     run_start[TBF_MAX_KEYS] = (uint32_t)run_wheel.size();
@@ -314,11 +399,12 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
 
     TgSet s;
     s.host = *t;
-    /* The device keeps four copies of every wave, copy s rotated left by s samples and extended
-     * by one fragment of wrap-around: a 128-sample read from any position then starts 16-byte
-     * aligned in copy (pos & 3) and never wraps, so a lane fetches its four consecutive samples
-     * with one 16-byte cp.async (tbf_kernels.cu, wave_request).  The copies are made on the
-     * device from the raw waves (tbf_wave_store_kernel): a quarter of the bytes over the link. */
+    /* The device keeps four copies of every wave, copy c rotated left by c samples and extended
+     * by two fragments of wrap-around: the reads of two consecutive fragments from any position
+     * are then one contiguous, 16-byte aligned kilobyte in copy (pos & 3) that never wraps, which
+     * one TMA bulk copy fetches (tbf_kernels.cu, wave_request).  The copies are made on the
+     * device from the raw waves (tbf_wave_store_kernel): a quarter of the bytes over the link,
+     * none at all when the raw waves are synthesised there. */
     uint32_t wave4_offset[TBF_NOF_WHEELS + 1] = {0};
     size_t n_wave4 = 0;
     for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
@@ -341,32 +427,47 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     const size_t o_rw = up16(o_cb + sizeof(uint16_t) * nc);
     const size_t o_rn = up16(o_rw + sizeof(uint16_t) * nr);
     const size_t blob_bytes = up16(o_rn + sizeof(uint16_t) * nr) + 16;
-    /* staging: [raw waves][wave_offset, wave_length, wave4_offset][the arrays behind the wave store] */
+    const size_t tail_bytes = blob_bytes - o_cl;
+    /* staging, host and device sides alike:
+     *   [raw waves][wave_offset, wave_length, wave4_offset][f1, attenuation (synthesis)]
+     * host side only, behind it: [DevTonegenTables][the arrays behind the wave store] */
     const size_t n_meta = 3 * (TBF_NOF_WHEELS + 1);
     const size_t s_meta = up16(sizeof(float) * (size_t)t->wave_total);
-    const size_t s_tail = up16(s_meta + sizeof(uint32_t) * n_meta);
-    const size_t tail_bytes = blob_bytes - o_cl;
+    const size_t s_synth = up16(s_meta + sizeof(uint32_t) * n_meta);
+    const size_t s_desc = up16(s_synth + sizeof(double) * 2 * (TBF_NOF_WHEELS + 1));
+    const size_t s_tail = up16(s_desc + sizeof(DevTonegenTables));
     const size_t stage_bytes = s_tail + tail_bytes;
-    if (stage_bytes > ctx->cap_h_stage) {
-        cudaFreeHost(ctx->h_stage);
-        ctx->h_stage = nullptr;
-        ctx->cap_h_stage = 0;
-        CK(cudaHostAlloc((void **)&ctx->h_stage, stage_bytes + (stage_bytes >> 2), cudaHostAllocDefault));
-        ctx->cap_h_stage = stage_bytes + (stage_bytes >> 2);
+
+    tbf_ctx::StageSlot &sl = ctx->stage[ctx->stage_next];
+    ctx->stage_next ^= 1;
+    if (sl.used)
+        CK(cudaEventSynchronize(sl.done)); /* the slot's last table set has left it */
+    if (stage_bytes > sl.cap_h) {
+        cudaFreeHost(sl.h);
+        sl.h = nullptr;
+        sl.cap_h = 0;
+        CK(cudaHostAlloc((void **)&sl.h, stage_bytes + (stage_bytes >> 2), cudaHostAllocDefault));
+        sl.cap_h = stage_bytes + (stage_bytes >> 2);
     }
-    if (s_tail > ctx->cap_d_stage) {
-        cudaFree(ctx->d_stage);
-        ctx->d_stage = nullptr;
-        ctx->cap_d_stage = 0;
-        CK(cudaMalloc((void **)&ctx->d_stage, s_tail + (s_tail >> 2)));
-        ctx->cap_d_stage = s_tail + (s_tail >> 2);
+    if (s_desc > sl.cap_d) {
+        cudaFree(sl.d);
+        sl.d = nullptr;
+        sl.cap_d = 0;
+        CK(cudaMalloc((void **)&sl.d, s_desc + (s_desc >> 2)));
+        sl.cap_d = s_desc + (s_desc >> 2);
     }
-    unsigned char *hs = ctx->h_stage;
-    memcpy(hs, t->wave_data, sizeof(float) * (size_t)t->wave_total);
+    unsigned char *hs = sl.h;
+    if (!synth)
+        memcpy(hs, t->wave_data, sizeof(float) * (size_t)t->wave_total);
     uint32_t *meta = reinterpret_cast<uint32_t *>(hs + s_meta);
     memcpy(meta, t->wave_offset, sizeof(t->wave_offset));
     memcpy(meta + (TBF_NOF_WHEELS + 1), t->wave_length, sizeof(t->wave_length));
     memcpy(meta + 2 * (TBF_NOF_WHEELS + 1), wave4_offset, sizeof(wave4_offset));
+    if (synth) {
+        memcpy(hs + s_synth, synth->f1, sizeof(double) * (TBF_NOF_WHEELS + 1));
+        memcpy(hs + s_synth + sizeof(double) * (TBF_NOF_WHEELS + 1), synth->attenuation,
+               sizeof(double) * (TBF_NOF_WHEELS + 1));
+    }
     unsigned char *tail = hs + s_tail - o_cl; /* tail + o_x = the staged copy of array x */
     memset(hs + s_tail, 0, tail_bytes);
     if (nc) {
@@ -378,34 +479,99 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
         memcpy(tail + o_rw, run_wheel.data(), sizeof(uint16_t) * nr);
         memcpy(tail + o_rn, run_count.data(), sizeof(uint16_t) * nr);
     }
+
+    /* the set's slot in the device array of descriptors */
+    const bool reuse_tg = !ctx->free_tg.empty();
+    const size_t idx = reuse_tg ? (size_t)ctx->free_tg.back() : ctx->tg.size();
+    if (idx + 1 > ctx->d_tg_cap) {
+        const size_t ncap = std::max<size_t>(64, ctx->d_tg_cap * 2);
+        DevTonegenTables *nd = nullptr;
+        cudaError_t e = cudaMalloc(&nd, sizeof(DevTonegenTables) * ncap);
+        if (e != cudaSuccess) {
+            ctx->err = cudaGetErrorString(e);
+            return TBF_ERR_NOMEM;
+        }
+        if (ctx->tg.size()) {
+            CK(cudaStreamSynchronize(ctx->stream)); /* descriptors still on their way into the old array */
+            cudaMemcpy(nd, ctx->d_tg, sizeof(DevTonegenTables) * ctx->tg.size(), cudaMemcpyDeviceToDevice);
+        }
+        cudaFree(ctx->d_tg);
+        ctx->d_tg = nd;
+        ctx->d_tg_cap = ncap;
+    }
+
     unsigned char *dev = nullptr;
-    CK(cudaMalloc(&dev, blob_bytes));
-    cudaError_t ue = cudaMemcpyAsync(ctx->d_stage, hs, s_tail, cudaMemcpyHostToDevice, ctx->stream);
+    CK(cudaMallocAsync((void **)&dev, blob_bytes, ctx->stream));
+    float *d_raw = reinterpret_cast<float *>(sl.d);
+    const uint32_t *d_meta = reinterpret_cast<const uint32_t *>(sl.d + s_meta);
+    cudaError_t ue = cudaSuccess;
+    if (!synth) {
+        ue = cudaMemcpyAsync(sl.d, hs, s_synth, cudaMemcpyHostToDevice, ctx->stream);
+    } else {
+        /* ---- the waves are made here (tbf_wave_synth_kernel) ---- */
+        const uint32_t *bits_h = nullptr, *bits_d = nullptr;
+        int rc = dither_stream(ctx, synth->seed, t->wave_total, &bits_h, &bits_d);
+        if (rc != TBF_OK) {
+            cudaFreeAsync(dev, ctx->stream);
+            return rc;
+        }
+        const size_t flag_bytes = sizeof(uint32_t) * 4 * (1 + TBF_SYNTH_FLAG_CAP);
+        if (!ctx->d_flags) {
+            CK(cudaMalloc((void **)&ctx->d_flags, flag_bytes));
+            CK(cudaHostAlloc((void **)&ctx->h_flags, flag_bytes, cudaHostAllocDefault));
+            CK(cudaHostAlloc((void **)&ctx->h_patch, sizeof(float) * TBF_SYNTH_FLAG_CAP, cudaHostAllocDefault));
+        }
+        WaveSynthParams sp;
+        sp.rate = synth->sample_rate;
+        memcpy(sp.harmonics, synth->harmonics, sizeof(sp.harmonics));
+        ue = cudaMemcpyAsync(sl.d + s_meta, hs + s_meta, s_desc - s_meta, cudaMemcpyHostToDevice, ctx->stream);
+        if (ue == cudaSuccess)
+            ue = cudaMemsetAsync(ctx->d_flags, 0, 16, ctx->stream);
+        if (ue == cudaSuccess)
+            ue = (cudaError_t)tbf_launch_wave_synth(
+                d_raw, d_meta, reinterpret_cast<const double *>(sl.d + s_synth),
+                reinterpret_cast<const double *>(sl.d + s_synth) + (TBF_NOF_WHEELS + 1), sp, bits_d,
+                ctx->d_flags, ctx->d_flags + 4, TBF_SYNTH_FLAG_CAP, ctx->stream);
+        if (ue == cudaSuccess)
+            ue = cudaMemcpyAsync(ctx->h_flags, ctx->d_flags, 16, cudaMemcpyDeviceToHost, ctx->stream);
+        if (ue == cudaSuccess)
+            ue = cudaStreamSynchronize(ctx->stream);
+        /* samples whose float could hinge on the last bit of a sine: the host's libm decides */
+        const uint32_t n_flag = ue == cudaSuccess ? ctx->h_flags[0] : 0;
+        if (ue == cudaSuccess && n_flag > TBF_SYNTH_FLAG_CAP) {
+            cudaFreeAsync(dev, ctx->stream);
+            return fail(ctx, TBF_ERR_ARG, "wave synthesis: too many ambiguous samples (degenerate spec)");
+        }
+        if (ue == cudaSuccess && n_flag) {
+            ue = cudaMemcpy(ctx->h_flags + 4, ctx->d_flags + 4, sizeof(uint32_t) * 4 * n_flag,
+                            cudaMemcpyDeviceToHost);
+            for (uint32_t k = 0; ue == cudaSuccess && k < n_flag; ++k) {
+                const uint32_t *f = ctx->h_flags + 4 + 4 * k;
+                const uint32_t w = f[0], i = f[1];
+                const uint32_t pos = t->wave_offset[w] + i;
+                const float v = tbf_wave_sample(synth, (int)w, i, (bits_h[pos >> 5] >> (pos & 31u)) & 1u);
+                uint32_t vb;
+                memcpy(&vb, &v, 4);
+                ctx->synth_flagged += 1;
+                if (vb != f[2]) {
+                    ctx->synth_differed += 1;
+                    ctx->h_patch[k] = v;
+                    ue = cudaMemcpyAsync(d_raw + pos, &ctx->h_patch[k], sizeof(float), cudaMemcpyHostToDevice,
+                                         ctx->stream);
+                }
+            }
+        }
+    }
     if (ue == cudaSuccess)
         ue = cudaMemcpyAsync(dev + o_cl, hs + s_tail, tail_bytes, cudaMemcpyHostToDevice, ctx->stream);
     if (ue == cudaSuccess && n_wave4 < n_wave)
         ue = cudaMemsetAsync(dev, 0, sizeof(float) * n_wave, ctx->stream);
     if (ue == cudaSuccess && n_wave4)
-        ue = (cudaError_t)tbf_launch_wave_store(reinterpret_cast<float *>(dev),
-                                                reinterpret_cast<const float *>(ctx->d_stage),
-                                                reinterpret_cast<const uint32_t *>(ctx->d_stage + s_meta),
-                                                ctx->stream);
-    if (ue == cudaSuccess)
-        ue = cudaStreamSynchronize(ctx->stream); /* the staging buffers are reused by the next call */
-    if (ue != cudaSuccess) {
-        cudaFree(dev);
-        ctx->err = std::string("tonegen tables upload: ") + cudaGetErrorString(ue);
-        return TBF_ERR_CUDA;
-    }
-    s.wave = reinterpret_cast<float *>(dev); /* owns the allocation; the rest point into it */
-    s.cl = nullptr;
-    s.cw = s.cb = s.rw = s.rn = nullptr;
-    s.host.wave_data = nullptr;
-    s.host.contrib_wheel = s.host.contrib_bus = nullptr;
-    s.host.contrib_level = nullptr;
+        ue = (cudaError_t)tbf_launch_wave_store(reinterpret_cast<float *>(dev), d_raw, d_meta, ctx->stream);
 
-    DevTonegenTables *d = new DevTonegenTables();
-    d->wave4 = s.wave;
+    DevTonegenTables *d = reinterpret_cast<DevTonegenTables *>(hs + s_desc);
+    memset(d, 0, sizeof(*d));
+    d->wave4 = reinterpret_cast<float *>(dev);
     d->contrib_wheel = reinterpret_cast<const uint16_t *>(dev + o_cw);
     d->contrib_bus = reinterpret_cast<const uint16_t *>(dev + o_cb);
     d->contrib_level = reinterpret_cast<const float *>(dev + o_cl);
@@ -437,31 +603,24 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
     d->output_level_trim = t->output_level_trim;
     memcpy(d->vib_offset_table, t->vib_offset_table, sizeof(d->vib_offset_table));
     d->vib_stator_increment = t->vib_stator_increment;
-
-    const bool reuse_tg = !ctx->free_tg.empty();
-    const size_t idx = reuse_tg ? (size_t)ctx->free_tg.back() : ctx->tg.size();
-    if (idx + 1 > ctx->d_tg_cap) {
-        const size_t ncap = std::max<size_t>(8, ctx->d_tg_cap * 2);
-        DevTonegenTables *nd = nullptr;
-        cudaError_t e = cudaMalloc(&nd, sizeof(DevTonegenTables) * ncap);
-        if (e != cudaSuccess) {
-            delete d;
-            ctx->err = cudaGetErrorString(e);
-            return TBF_ERR_NOMEM;
-        }
-        if (ctx->tg.size())
-            cudaMemcpy(nd, ctx->d_tg, sizeof(DevTonegenTables) * ctx->tg.size(), cudaMemcpyDeviceToDevice);
-        cudaFree(ctx->d_tg);
-        ctx->d_tg = nd;
-        ctx->d_tg_cap = ncap;
-    }
-    cudaError_t e = cudaMemcpy(ctx->d_tg + idx, d, sizeof(DevTonegenTables), cudaMemcpyHostToDevice);
-    delete d;
-    if (e != cudaSuccess) {
-        cudaFree(dev);
-        ctx->err = cudaGetErrorString(e);
+    if (ue == cudaSuccess)
+        ue = cudaMemcpyAsync(ctx->d_tg + idx, d, sizeof(DevTonegenTables), cudaMemcpyHostToDevice, ctx->stream);
+    if (ue == cudaSuccess)
+        ue = cudaEventRecord(sl.done, ctx->stream);
+    sl.used = true;
+    if (ue != cudaSuccess) {
+        cudaStreamSynchronize(ctx->stream);
+        cudaFreeAsync(dev, ctx->stream);
+        ctx->err = std::string("tonegen tables upload: ") + cudaGetErrorString(ue);
+        cudaGetLastError();
         return TBF_ERR_CUDA;
     }
+    s.wave = reinterpret_cast<float *>(dev); /* owns the allocation; the rest point into it */
+    s.cl = nullptr;
+    s.cw = s.cb = s.rw = s.rn = nullptr;
+    s.host.wave_data = nullptr;
+    s.host.contrib_wheel = s.host.contrib_bus = nullptr;
+    s.host.contrib_level = nullptr;
     if (reuse_tg) {
         ctx->free_tg.pop_back();
         ctx->tg[idx] = s;
@@ -469,6 +628,54 @@ int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int
         ctx->tg.push_back(s);
     }
     *handle = (int)idx;
+    return TBF_OK;
+}
+
+extern "C" {
+
+int tbf_gpu_tonegen_tables_create(tbf_ctx *ctx, const tbf_tonegen_tables *t, int *handle)
+{
+    return create_tonegen_tables(ctx, t, nullptr, handle);
+}
+
+int tbf_gpu_tonegen_tables_create_synth(tbf_ctx *ctx, const tbf_tonegen_tables *t, const tbf_wave_synth *synth,
+                                        int *handle)
+{
+    if (!synth)
+        return fail(ctx, TBF_ERR_ARG, "tonegen tables: null synthesis description");
+    return create_tonegen_tables(ctx, t, synth, handle);
+}
+
+int tbf_gpu_synth_stats(const tbf_ctx *ctx, uint64_t *flagged, uint64_t *differed)
+{
+    if (!ctx)
+        return TBF_ERR_ARG;
+    if (flagged)
+        *flagged = ctx->synth_flagged;
+    if (differed)
+        *differed = ctx->synth_differed;
+    return TBF_OK;
+}
+
+/* the raw waves of a set (copy 0 of every wheel, wave_offset layout): parity tests of the
+ * device-side synthesis */
+int tbf_gpu_tonegen_tables_read_waves(tbf_ctx *ctx, int handle, float *out, uint64_t n_floats)
+{
+    if (!ctx || !out || !tg_usable(ctx, handle))
+        return fail(ctx, TBF_ERR_HANDLE, "read_waves: unknown handle");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const TgSet &s = ctx->tg[handle];
+    size_t off4 = 0;
+    for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
+        const uint32_t len = s.host.wave_length[w];
+        if (!len)
+            continue;
+        if ((uint64_t)s.host.wave_offset[w] + len > n_floats)
+            return fail(ctx, TBF_ERR_ARG, "read_waves: buffer too small");
+        CK(cudaMemcpy(out + s.host.wave_offset[w], s.wave + off4, sizeof(float) * len, cudaMemcpyDeviceToHost));
+        off4 += (size_t)4 * tbf_wave_copy_len(len);
+    }
     return TBF_OK;
 }
 
@@ -662,9 +869,8 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
 
 /* the state allocTonegen+initToneGenerator+init_vibrato and allocWhirl+initWhirl
  * leave behind (src/tonegen.cpp:196-300, :2905-3022; src/vibrato.cpp:288-317;
- * src/whirl.cpp:40-131, :626-662) */
-static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
-                          const tbf_whirl_tables &w, int whh)
+ * src/whirl.cpp:40-131, :626-662): everything not set here starts as zero */
+static void fill_init(InstInit *s, const tbf_tonegen_tables &t, int tgh, const tbf_whirl_tables &w, int whh)
 {
     memset(s, 0, sizeof(*s));
     s->tg.newRouting = s->tg.oldRouting = t.init_routing;
@@ -683,8 +889,6 @@ static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
     s->tg.pz = 0.0f;
     s->rp.keyCompLevel = 1.0f; /* KEYCOMP_ZERO_LEVEL */
     memcpy(s->tg.drawBarGain, t.init_draw_bar_gain, sizeof(s->tg.drawBarGain));
-    for (int i = 0; i <= TBF_NOF_WHEELS; ++i)
-        s->osc[i].aclPos = -1;
     s->tg.vibStator = 0;
     s->tg.vibOutPos = 0x3FF / 2; /* BUF_MASK_SAMPLES / 2, src/vibrato.cpp:294 */
     s->tg.vibTable = t.init_vib_table;
@@ -709,16 +913,13 @@ static void fill_template(InstState *s, const tbf_tonegen_tables &t, int tgh,
     s->tg.whTables = whh;
 }
 
+/* stream-ordered: the initialising kernel takes its few hundred bytes as a kernel argument,
+ * so creating or resetting instances costs a launch, no upload and no synchronisation */
 static int replicate(tbf_ctx *ctx, int tgh, int whh, uint32_t first, uint32_t count)
 {
-    InstState *tmpl = new InstState();
-    fill_template(tmpl, ctx->tg[tgh].host, tgh, ctx->wh[whh].host, whh);
-    cudaError_t e = cudaMemcpyAsync(ctx->d_tmpl, tmpl, sizeof(InstState), cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess)
-        e = (cudaError_t)tbf_launch_replicate(ctx->d_states, first, count, ctx->d_tmpl, ctx->stream);
-    if (e == cudaSuccess)
-        e = cudaStreamSynchronize(ctx->stream);
-    delete tmpl;
+    InstInit init;
+    fill_init(&init, ctx->tg[tgh].host, tgh, ctx->wh[whh].host, whh);
+    const cudaError_t e = (cudaError_t)tbf_launch_init_instances(ctx->d_states, first, count, init, ctx->stream);
     if (e != cudaSuccess) {
         ctx->err = std::string("instance init: ") + cudaGetErrorString(e);
         return TBF_ERR_CUDA;
@@ -741,7 +942,7 @@ static void tg_release_if_unused(tbf_ctx *ctx, int h)
     TgSet &t = ctx->tg[h];
     if (t.freed || !t.destroyed || t.refs > 0)
         return;
-    cudaFree(t.wave);
+    cudaFreeAsync(t.wave, ctx->stream); /* back to the stream-ordered pool */
     t.wave = nullptr;
     t.freed = true;
     ctx->free_tg.push_back(h);

@@ -217,6 +217,17 @@ struct RenderParams {
     uint64_t pitch;            /* elements per slot row of every stream                 */
 };
 
+/* what a fresh instance starts from (tbf_init_instances_kernel); everything else is zero */
+struct InstInit {
+    TgScalars tg;
+    RampScalars rp;
+};
+/* kernel-side view of tbf_wave_synth (include/tbf_tables.h) */
+struct WaveSynthParams {
+    double rate;
+    double harmonics[TBF_MAX_PARTIALS];
+};
+
 size_t tbf_stage_t_smem(void);
 size_t tbf_stage_w_smem(int ring_size);
 int tbf_launch_stage_t(const RenderParams &p, void *stream);
@@ -226,5 +237,10 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream);
 int tbf_launch_wave_store(float *wave4, const float *raw, const uint32_t *meta, void *stream);
 int tbf_launch_replicate(InstState *states, uint32_t first, uint32_t count, const InstState *dev_tmpl,
                          void *stream);
+int tbf_launch_init_instances(InstState *states, uint32_t first, uint32_t count, const InstInit &init,
+                              void *stream);
+int tbf_launch_wave_synth(float *raw, const uint32_t *meta, const double *wheel_f1, const double *wheel_att,
+                          const WaveSynthParams &sp, const uint32_t *dither_bits, uint32_t *flag_count,
+                          void *flags, uint32_t flag_cap, void *stream);
 
 #endif

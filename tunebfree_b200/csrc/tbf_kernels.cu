@@ -2299,6 +2299,88 @@ template <int V> __global__ void __launch_bounds__(M_THREADS) tbf_stage_m(const 
     }
 }
 
+/* instance (re)initialisation without a host-side template: every block clears one InstState and
+ * installs the scalars allocTonegen + initToneGenerator + allocWhirl + initWhirl leave behind
+ * (the caller fills InstInit from the table sets, tbf_api.cu) -- no upload, no synchronisation */
+__global__ void tbf_init_instances_kernel(InstState *states, uint32_t first, uint32_t count, const InstInit init)
+{
+    for (uint32_t inst = blockIdx.x; inst < count; inst += gridDim.x) {
+        InstState *st = states + first + inst;
+        uint4 *dst = reinterpret_cast<uint4 *>(st);
+        const uint32_t n16 = sizeof(InstState) / 16;
+        for (uint32_t i = threadIdx.x; i < n16; i += blockDim.x)
+            dst[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (uint32_t i = n16 * 16 / 4 + threadIdx.x; i < sizeof(InstState) / 4; i += blockDim.x)
+            reinterpret_cast<uint32_t *>(st)[i] = 0u;
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < sizeof(TgScalars) / 4; i += blockDim.x)
+            reinterpret_cast<uint32_t *>(&st->tg)[i] = reinterpret_cast<const uint32_t *>(&init.tg)[i];
+        for (uint32_t i = threadIdx.x; i < sizeof(RampScalars) / 4; i += blockDim.x)
+            reinterpret_cast<uint32_t *>(&st->rp)[i] = reinterpret_cast<const uint32_t *>(&init.rp)[i];
+        for (uint32_t i = threadIdx.x; i <= TBF_NOF_WHEELS; i += blockDim.x)
+            st->osc[i].aclPos = -1;
+        __syncthreads();
+    }
+}
+
+/* writeSamples (src/tonegen.cpp:1402-1457) on the device: blockIdx.x = wheel - 1, one thread per
+ * sample.  Every double operation is the reference's, in its order, individually rounded; the
+ * one thing that can differ from the host is libm: CUDA's sin() and glibc's may disagree in the
+ * last bit of the double.  A sample whose double value lies so close to the midpoint of two
+ * floats that such a disagreement could change the float it rounds to is FLAGGED (bound:
+ * attenuation * 2^-46, thirty times what twelve partials of 2-ulp sines can add up to); the
+ * host recomputes flagged samples with its own libm and patches them (tbf_api.cu) -- about one
+ * sample in ten table sets. */
+__global__ void tbf_wave_synth_kernel(float *__restrict__ raw, const uint32_t *__restrict__ meta,
+                                      const double *__restrict__ wheel_f1, const double *__restrict__ wheel_att,
+                                      const WaveSynthParams sp, const uint32_t *__restrict__ dither_bits,
+                                      uint32_t *flag_count, uint4 *flags, uint32_t flag_cap)
+{
+    const uint32_t w = blockIdx.x + 1;
+    const uint32_t len = meta[(TBF_NOF_WHEELS + 1) + w];
+    if (!len)
+        return;
+    const uint32_t off = meta[w];
+    const double full_circle = 6.283185307179586; /* 2.0 * M_PI */
+    const double f1 = wheel_f1[w], att = wheel_att[w];
+    double apl[TBF_MAX_PARTIALS], pl_hz[TBF_MAX_PARTIALS];
+    double sum = 0.0;
+#pragma unroll
+    for (int j = 0; j < TBF_MAX_PARTIALS; ++j) {
+        apl[j] = sp.harmonics[j];
+        sum = __dadd_rn(sum, fabs(apl[j]));
+        pl_hz[j] = __dmul_rn(f1, (double)(j + 1));
+        if (__dmul_rn(sp.rate, 0.5) <= pl_hz[j])
+            apl[j] = 0.0;
+    }
+    const double U = __ddiv_rn(att, sum);
+    const double bound = __dmul_rn(fabs(att), 1.4210854715202004e-14); /* 2^-46 */
+    const float lsb = (float)(1.0 / 32767.0);
+    for (uint32_t i = threadIdx.x; i < len; i += blockDim.x) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int j = 0; j < TBF_MAX_PARTIALS; ++j) {
+            if (apl[j] == 0.0)
+                continue;
+            const double arg = __ddiv_rn(__dmul_rn(__dmul_rn(pl_hz[j], full_circle), (double)i), sp.rate);
+            sacc = __dadd_rn(sacc, __dmul_rn(apl[j], sin(remainder(arg, full_circle))));
+        }
+        const uint32_t k = off + i; /* the sample's position in the rand() stream */
+        const float d = ((dither_bits[k >> 5] >> (k & 31u)) & 1u) ? lsb : 0.0f;
+        const double v = __dadd_rn((double)d, __dmul_rn(U, sacc));
+        const float f = (float)v;
+        raw[k] = f;
+        /* distance of v from the two rounding boundaries around f */
+        const double up = 0.5 * ((double)f + (double)nextafterf(f, INFINITY));
+        const double dn = 0.5 * ((double)f + (double)nextafterf(f, -INFINITY));
+        if (fmin(fabs(up - v), fabs(v - dn)) <= bound || !(v == v)) {
+            const uint32_t slot = atomicAdd(flag_count, 1u);
+            if (slot < flag_cap)
+                flags[slot] = make_uint4(w, i, __float_as_uint(f), 0u);
+        }
+    }
+}
+
 __global__ void tbf_replicate_kernel(InstState *states, uint32_t first, uint32_t count,
                                      const InstState *tmpl)
 {
@@ -2446,6 +2528,25 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream)
         tbf_stage_m<1><<<mgrid, M_THREADS, 0, (cudaStream_t)stream>>>(p);
     }
     debug_sync(stream, "M");
+    return (int)cudaGetLastError();
+}
+
+int tbf_launch_init_instances(InstState *states, uint32_t first, uint32_t count, const InstInit &init,
+                              void *stream)
+{
+    if (!count)
+        return 0;
+    const uint32_t grid = count < 1184 ? count : 1184; /* 148 SMs x 8 */
+    tbf_init_instances_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(states, first, count, init);
+    return (int)cudaGetLastError();
+}
+
+int tbf_launch_wave_synth(float *raw, const uint32_t *meta, const double *wheel_f1, const double *wheel_att,
+                          const WaveSynthParams &sp, const uint32_t *dither_bits, uint32_t *flag_count,
+                          void *flags, uint32_t flag_cap, void *stream)
+{
+    tbf_wave_synth_kernel<<<TBF_NOF_WHEELS, 256, 0, (cudaStream_t)stream>>>(
+        raw, meta, wheel_f1, wheel_att, sp, dither_bits, flag_count, reinterpret_cast<uint4 *>(flags), flag_cap);
     return (int)cudaGetLastError();
 }
 

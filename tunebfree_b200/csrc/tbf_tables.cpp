@@ -689,32 +689,44 @@ void wheel_attenuation(const tbf_tonegen_spec *s, double *att)
  * normalised by the sum of magnitudes, partials at or above Nyquist muted,
  * one rand() per sample for a one-LSB (1/32767) dither.  Partials whose
  * amplitude is zero add +-0 to a sum that is never -0, so they are skipped. */
+struct WheelSynth {
+    double apl[TBF_MAX_PARTIALS], pl_hz[TBF_MAX_PARTIALS], U;
+};
+
+void wheel_synth(WheelSynth &ws, const double *ap, double attenuation, double f1, double rate)
+{
+    double sum = 0.0;
+    for (int i = 0; i < TBF_MAX_PARTIALS; ++i) {
+        ws.apl[i] = ap[i];
+        sum += fabs(ws.apl[i]);
+        ws.pl_hz[i] = f1 * ((double)(i + 1));
+        if ((rate * 0.5) <= ws.pl_hz[i])
+            ws.apl[i] = 0.0;
+    }
+    ws.U = attenuation / sum;
+}
+
+inline float synth_sample(const WheelSynth &ws, double rate, unsigned int i, bool dither)
+{
+    const double full_circle = 2.0 * M_PI;
+    const float lsb = (float)(1.0 / 32767.0);
+    double sacc = 0.0;
+    for (int j = 0; j < TBF_MAX_PARTIALS; ++j) {
+        if (ws.apl[j] == 0.0)
+            continue;
+        sacc += ws.apl[j] * sin(remainder((ws.pl_hz[j] * full_circle * (double)i) / rate, full_circle));
+    }
+    const float d = dither ? lsb : 0.0f;
+    return (float)((double)d + (ws.U * sacc));
+}
+
 void write_samples(float *buf, size_t n, const double *ap, double attenuation, double f1, double rate,
                    Rng &rng)
 {
-    const double full_circle = 2.0 * M_PI;
-    double apl[TBF_MAX_PARTIALS], pl_hz[TBF_MAX_PARTIALS];
-    double sum = 0.0;
-    for (int i = 0; i < TBF_MAX_PARTIALS; ++i) {
-        apl[i] = ap[i];
-        sum += fabs(apl[i]);
-        pl_hz[i] = f1 * ((double)(i + 1));
-        if ((rate * 0.5) <= pl_hz[i])
-            apl[i] = 0.0;
-    }
-    const double U = attenuation / sum;
-    const float lsb = (float)(1.0 / 32767.0);
-    for (size_t i = 0; i < n; ++i) {
-        double sacc = 0.0;
-        for (int j = 0; j < TBF_MAX_PARTIALS; ++j) {
-            if (apl[j] == 0.0)
-                continue;
-            sacc += apl[j] * sin(remainder((pl_hz[j] * full_circle * (double)(unsigned int)i) / rate,
-                                           full_circle));
-        }
-        const float d = (rng.next() < (kRandMax >> 1)) ? lsb : 0.0f;
-        buf[i] = (float)((double)d + (U * sacc));
-    }
+    WheelSynth ws;
+    wheel_synth(ws, ap, attenuation, f1, rate);
+    for (size_t i = 0; i < n; ++i)
+        buf[i] = synth_sample(ws, rate, (unsigned int)i, rng.next() < (kRandMax >> 1));
 }
 
 } // namespace
@@ -822,7 +834,43 @@ void init_key_comp(float *tab)
 
 } // namespace
 
+static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_wave_synth *synth);
+
 extern "C" int tbf_build_tonegen_tables(const tbf_tonegen_spec *s, tbf_tonegen_tables *o)
+{
+    return build_tonegen(s, o, nullptr);
+}
+
+extern "C" int tbf_build_tonegen_tables_synth(const tbf_tonegen_spec *s, tbf_tonegen_tables *o,
+                                              tbf_wave_synth *synth)
+{
+    if (!synth)
+        return TBF_ERR_ARG;
+    return build_tonegen(s, o, synth);
+}
+
+extern "C" float tbf_wave_sample(const tbf_wave_synth *y, int wheel, uint32_t i, int dither_bit)
+{
+    if (!y || wheel < 1 || wheel > TBF_NOF_WHEELS)
+        return 0.0f;
+    WheelSynth ws;
+    wheel_synth(ws, y->harmonics, y->attenuation[wheel], y->f1[wheel], y->sample_rate);
+    return synth_sample(ws, y->sample_rate, i, dither_bit != 0);
+}
+
+extern "C" void tbf_dither_bits(uint32_t seed, uint64_t n, uint32_t *bits)
+{
+    Rng rng(seed);
+    for (uint64_t k = 0; k < n; k += 32) {
+        uint32_t w = 0;
+        for (uint64_t j = k; j < n && j < k + 32; ++j)
+            if (rng.next() < (kRandMax >> 1))
+                w |= 1u << (j - k);
+        bits[k >> 5] = w;
+    }
+}
+
+static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_wave_synth *synth)
 {
     if (!s || !o || !(s->sample_rate > 0))
         return TBF_ERR_ARG;
@@ -878,13 +926,28 @@ extern "C" int tbf_build_tonegen_tables(const tbf_tonegen_spec *s, tbf_tonegen_t
         o->wave_length[i] = (uint32_t)len[i];
         total += len[i];
     }
-    float *wave = (float *)malloc(sizeof(float) * (size_t)total);
-    if (!wave)
-        return TBF_ERR_NOMEM;
+    float *wave = nullptr;
     Rng rng(s->seed);
-    for (int i = 1; i <= TBF_NOF_WHEELS; ++i)
-        write_samples(wave + o->wave_offset[i], len[i], harmonics, att[i], osc_frequency(freq300, i),
-                      rate, rng);
+    if (synth) {
+        /* the device makes the samples; the rand() stream moves on as if they had been made */
+        memset(synth, 0, sizeof(*synth));
+        synth->sample_rate = rate;
+        synth->seed = s->seed;
+        memcpy(synth->harmonics, harmonics, sizeof(harmonics));
+        for (int i = 1; i <= TBF_NOF_WHEELS; ++i) {
+            synth->f1[i] = osc_frequency(freq300, i);
+            synth->attenuation[i] = att[i];
+        }
+        for (uint64_t k = 0; k < total; ++k)
+            (void)rng.next();
+    } else {
+        wave = (float *)malloc(sizeof(float) * (size_t)total);
+        if (!wave)
+            return TBF_ERR_NOMEM;
+        for (int i = 1; i <= TBF_NOF_WHEELS; ++i)
+            write_samples(wave + o->wave_offset[i], len[i], harmonics, att[i], osc_frequency(freq300, i),
+                          rate, rng);
+    }
     o->wave_data = wave;
     o->wave_total = total;
 

@@ -69,6 +69,10 @@ def lib():
         L.tbf_gpu_export_state.argtypes = [vp, C.c_uint32, C.POINTER(cabi.StateExport)]
         L.tbf_gpu_set_stage_profiling.argtypes = [vp, C.c_int]
         L.tbf_gpu_stage_times.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        L.tbf_gpu_tonegen_tables_create_synth.argtypes = [vp, C.POINTER(cabi.TonegenTables),
+                                                          C.POINTER(cabi.WaveSynth), C.POINTER(C.c_int)]
+        L.tbf_gpu_synth_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.tbf_gpu_tonegen_tables_read_waves.argtypes = [vp, C.c_int, C.c_void_p, C.c_uint64]
         L.tbf_gpu_instance_destroy.argtypes = [vp, C.c_uint32, C.c_uint32]
         L.tbf_gpu_tonegen_tables_destroy.argtypes = [vp, C.c_int]
         L.tbf_gpu_whirl_tables_destroy.argtypes = [vp, C.c_int]
@@ -158,6 +162,24 @@ class Context:
         h = C.c_int(-1)
         self._ck(lib().tbf_gpu_tonegen_tables_create(self._h, C.byref(tables), C.byref(h)))
         return h.value
+
+    def tonegen_tables_synth(self, tables, synth):
+        """Upload a table set whose wavetables the device synthesises (tables.wave_data NULL)."""
+        h = C.c_int(-1)
+        self._ck(lib().tbf_gpu_tonegen_tables_create_synth(self._h, C.byref(tables), C.byref(synth),
+                                                           C.byref(h)))
+        return h.value
+
+    def synth_stats(self):
+        """-> (samples flagged as rounding-ambiguous, of those: differed from the host's libm)"""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        self._ck(lib().tbf_gpu_synth_stats(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def read_waves(self, handle, n_floats):
+        out = np.zeros(int(n_floats), dtype=np.float32)
+        self._ck(lib().tbf_gpu_tonegen_tables_read_waves(self._h, handle, out.ctypes.data, int(n_floats)))
+        return out
 
     def whirl_tables(self, tables):
         h = C.c_int(-1)

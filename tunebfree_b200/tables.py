@@ -32,6 +32,12 @@ def _lib():
                                          C.c_char_p, C.c_char_p]
         L.tbf_build_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenSpec),
                                                C.POINTER(cabi.TonegenTables)]
+        L.tbf_build_tonegen_tables_synth.argtypes = [C.POINTER(cabi.TonegenSpec), C.POINTER(cabi.TonegenTables),
+                                                     C.POINTER(cabi.WaveSynth)]
+        L.tbf_wave_sample.argtypes = [C.POINTER(cabi.WaveSynth), C.c_int, C.c_uint32, C.c_int]
+        L.tbf_wave_sample.restype = C.c_float
+        L.tbf_dither_bits.argtypes = [C.c_uint32, C.c_uint64, C.c_void_p]
+        L.tbf_dither_bits.restype = None
         L.tbf_free_tonegen_tables.argtypes = [C.POINTER(cabi.TonegenTables)]
         L.tbf_free_tonegen_tables.restype = None
         L.tbf_build_whirl_tables.argtypes = [C.POINTER(cabi.WhirlSpec), C.POINTER(cabi.WhirlTables)]
@@ -150,6 +156,16 @@ class InstanceSpec:
         if rc != cabi.OK:
             raise ValueError("tbf_build_tonegen_tables failed (%d)" % rc)
         return tt
+
+    def build_tonegen_synth(self):
+        """-> (TonegenTables without wave samples, WaveSynth): everything initToneGenerator builds
+        except the wavetables, which tbf_gpu_tonegen_tables_create_synth makes on the device."""
+        tt = cabi.TonegenTables()
+        ws = cabi.WaveSynth()
+        rc = _lib().tbf_build_tonegen_tables_synth(C.byref(self.tg), C.byref(tt), C.byref(ws))
+        if rc != cabi.OK:
+            raise ValueError("tbf_build_tonegen_tables_synth failed (%d)" % rc)
+        return tt, ws
 
     def build(self):
         """-> (TonegenTables, WhirlTables); free with free_tables()."""
