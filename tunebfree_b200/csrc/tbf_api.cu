@@ -540,7 +540,8 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
         const uint32_t n_flag = ue == cudaSuccess ? ctx->h_flags[0] : 0;
         if (ue == cudaSuccess && n_flag > TBF_SYNTH_FLAG_CAP) {
             cudaFreeAsync(dev, ctx->stream);
-            return fail(ctx, TBF_ERR_ARG, "wave synthesis: too many ambiguous samples (degenerate spec)");
+            ctx->err = "wave synthesis: too many ambiguous samples (" + std::to_string(n_flag) + ", degenerate spec)";
+            return TBF_ERR_ARG;
         }
         if (ue == cudaSuccess && n_flag) {
             ue = cudaMemcpy(ctx->h_flags + 4, ctx->d_flags + 4, sizeof(uint32_t) * 4 * n_flag,
@@ -989,8 +990,12 @@ int tbf_gpu_instance_create(tbf_ctx *ctx, int tgh, int whh, uint32_t count, uint
             cudaGetLastError();
             return TBF_ERR_NOMEM;
         }
-        if (ctx->n_inst)
+        if (ctx->n_inst) {
+            /* instance init kernels are stream-ordered on the library's (non-blocking) stream:
+             * they must have written the old array before it is copied */
+            CK(cudaStreamSynchronize(ctx->stream));
             CK(cudaMemcpy(nd, ctx->d_states, sizeof(InstState) * ctx->n_inst, cudaMemcpyDeviceToDevice));
+        }
         cudaFree(ctx->d_states);
         ctx->d_states = nd;
         ctx->cap_inst = ncap;
@@ -1099,6 +1104,7 @@ int tbf_gpu_instance_stats(tbf_ctx *ctx, const uint32_t *ids, uint32_t n, uint64
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "instance_stats: synchronize first");
     CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
     /* the two 64-bit counters of every instance in one strided copy */
     std::vector<unsigned long long> st(2 * ctx->n_inst);
     CK(cudaMemcpy2D(st.data(), 16, &ctx->d_states[0].tg.statFragments, sizeof(InstState), 16, ctx->n_inst,
@@ -1756,6 +1762,7 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "export_state: synchronize first");
     CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream)); /* a create / reset may still be initialising it */
     InstState *s = new InstState();
     cudaError_t e = cudaMemcpy(s, ctx->d_states + instance, sizeof(InstState), cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) {

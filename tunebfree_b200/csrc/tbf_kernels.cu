@@ -2353,6 +2353,10 @@ __global__ void tbf_wave_synth_kernel(float *__restrict__ raw, const uint32_t *_
         if (__dmul_rn(sp.rate, 0.5) <= pl_hz[j])
             apl[j] = 0.0;
     }
+    bool any_partial = false;
+#pragma unroll
+    for (int j = 0; j < TBF_MAX_PARTIALS; ++j)
+        any_partial = any_partial || apl[j] != 0.0;
     const double U = __ddiv_rn(att, sum);
     const double bound = __dmul_rn(fabs(att), 1.4210854715202004e-14); /* 2^-46 */
     const float lsb = (float)(1.0 / 32767.0);
@@ -2373,7 +2377,9 @@ __global__ void tbf_wave_synth_kernel(float *__restrict__ raw, const uint32_t *_
         /* distance of v from the two rounding boundaries around f */
         const double up = 0.5 * ((double)f + (double)nextafterf(f, INFINITY));
         const double dn = 0.5 * ((double)f + (double)nextafterf(f, -INFINITY));
-        if (fmin(fabs(up - v), fabs(v - dn)) <= bound || !(v == v)) {
+        /* nothing to decide where no sine enters: a wheel with every partial muted (at or above
+         * Nyquist) is the dither alone, and sample 0 is sin(0) = 0 on either side */
+        if (any_partial && i > 0 && (fmin(fabs(up - v), fabs(v - dn)) <= bound || !(v == v))) {
             const uint32_t slot = atomicAdd(flag_count, 1u);
             if (slot < flag_cap)
                 flags[slot] = make_uint4(w, i, __float_as_uint(f), 0u);
