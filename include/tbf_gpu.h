@@ -266,6 +266,28 @@ int tbf_gpu_instance_reset(tbf_ctx *ctx, uint32_t first_id, uint32_t count);
  * (src/clap.cpp:254-258)                                                     */
 int tbf_gpu_render_batch(tbf_ctx *ctx, const tbf_batch_desc *desc);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that
+ * may not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  tbf_gpu_render_batch's chain for one SMALL batch with every intermediate buffer
+ * (stage streams, per-fragment records, the uploaded events, ids, checksums) in one file-scope
+ * static device array of tbf_gpu_noalloc_scratch_bytes() bytes (6.4 MB; every GPU that loads
+ * the library holds it until exit): the call makes no cudaMalloc / cudaFree and calls no
+ * allocating routine.  Limits: n_instances <= TBF_NOALLOC_MAX_INSTANCES, n_fragments <=
+ * TBF_NOALLOC_MAX_FRAGMENTS, n_events <= TBF_NOALLOC_MAX_EVENTS per call -- larger batches are
+ * rejected with TBF_ERR_ARG and a message naming the limits.  flags: TBF_RENDER_OUT_DEVICE is
+ * required (out_l / out_r are the caller's device buffers), plus WHIRL_BYPASS / WHIRLPROC3;
+ * checksums (host) are supported; `in` and `stems` are not.  The instances keep their state
+ * from call to call exactly as with tbf_gpu_render_batch (results are bit-identical to it).
+ * The array is shared by every call and every context on the device and keeps the last call's
+ * contents; what must start at zero is cleared per call.  Calls that overlap on the GPU race:
+ * the function runs on the context's stream and returns after that stream has drained; do not
+ * call it from two threads for the same device at once.                                      */
+#define TBF_NOALLOC_MAX_INSTANCES 32
+#define TBF_NOALLOC_MAX_FRAGMENTS 32
+#define TBF_NOALLOC_MAX_EVENTS 4096
+int tbf_gpu_render_small_noalloc(tbf_ctx *ctx, const tbf_batch_desc *desc);
+unsigned long long tbf_gpu_noalloc_scratch_bytes(void);
+
 /* asynchronous pieces: prepare validates the batch and uploads events / ids once;
  * launch renders the prepared batch on the library's stream and may be repeated
  * (the instances keep playing the same event script); render_batch_launch =

@@ -1812,6 +1812,196 @@ int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
     return TBF_OK;
 }
 
+} /* extern "C" */
+
+/* ------------------------------------------------------------------------------------------
+ * tbf_gpu_render_small_noalloc: the render chain for callers that may not allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Everything
+ * the stage kernels need between them -- the [slot][sample] stage streams, the per-fragment
+ * FragCtl records, the uploaded events with their CSR and cursors, the instance ids and the
+ * checksums -- lives in ONE file-scope device array of fixed size instead of the context's
+ * grow-on-demand buffers.  Every GPU that loads the library holds these 6.4 MB until exit.
+ * All calls (of all contexts on a device) share the array and it keeps the last call's
+ * contents: what must start at zero is cleared per call, and calls that overlap on the GPU race
+ * -- the entry point therefore runs on the context's stream and returns when it has finished.
+ * ---------------------------------------------------------------------------------------- */
+#define NA_MAX_INSTANCES TBF_NOALLOC_MAX_INSTANCES
+#define NA_MAX_FRAGMENTS TBF_NOALLOC_MAX_FRAGMENTS
+#define NA_MAX_EVENTS TBF_NOALLOC_MAX_EVENTS
+#define NA_PITCH ((size_t)NA_MAX_FRAGMENTS * TBF_FRAGMENT)
+#define NA_UP256(x) (((x) + 255) & ~(size_t)255)
+#define NA_OFF_F32 ((size_t)0) /* 8 planes [slot][pitch] of float */
+#define NA_OFF_F64 NA_UP256(NA_OFF_F32 + sizeof(float) * 8 * NA_MAX_INSTANCES * NA_PITCH)
+#define NA_OFF_CTL NA_UP256(NA_OFF_F64 + sizeof(double) * 2 * NA_MAX_INSTANCES * NA_PITCH)
+#define NA_OFF_EVENTS NA_UP256(NA_OFF_CTL + sizeof(FragCtl) * NA_MAX_INSTANCES * NA_MAX_FRAGMENTS)
+#define NA_OFF_EVSTART NA_UP256(NA_OFF_EVENTS + sizeof(tbf_event) * NA_MAX_EVENTS)
+#define NA_OFF_CURSOR NA_UP256(NA_OFF_EVSTART + sizeof(uint64_t) * (NA_MAX_INSTANCES + 1))
+#define NA_OFF_IDS NA_UP256(NA_OFF_CURSOR + sizeof(uint64_t) * 2 * NA_MAX_INSTANCES)
+#define NA_OFF_CSUM NA_UP256(NA_OFF_IDS + sizeof(uint32_t) * NA_MAX_INSTANCES)
+#define NA_BYTES NA_UP256(NA_OFF_CSUM + sizeof(uint64_t) * NA_MAX_INSTANCES)
+
+static __device__ __align__(256) unsigned char tbf_noalloc_scratch[NA_BYTES];
+
+/* In host code `tbf_noalloc_scratch` is a host-side stand-in, not a device address: the address
+ * the kernels get comes from cudaGetSymbolAddress, once per device, with that device current. */
+static int noalloc_scratch_address(tbf_ctx *ctx, unsigned char **out)
+{
+    static unsigned char *addr[64] = {nullptr};
+    const int dev = ctx->device;
+    unsigned char *p = (dev >= 0 && dev < 64) ? addr[dev] : nullptr;
+    if (!p) {
+        CK(cudaSetDevice(dev));
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, tbf_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            ctx->err = std::string("render_small_noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e);
+            cudaGetLastError();
+            return TBF_ERR_CUDA;
+        }
+        if (dev >= 0 && dev < 64)
+            addr[dev] = p;
+    }
+    *out = p;
+    return TBF_OK;
+}
+
+extern "C" {
+
+unsigned long long tbf_gpu_noalloc_scratch_bytes(void) { return (unsigned long long)NA_BYTES; }
+
+int tbf_gpu_render_small_noalloc(tbf_ctx *ctx, const tbf_batch_desc *d)
+{
+    if (!ctx || !d)
+        return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: null argument");
+    if (ctx->in_flight)
+        return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: previous launch not synchronized");
+    if (!d->n_instances || !d->n_fragments)
+        return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: empty batch");
+    if (d->n_instances > NA_MAX_INSTANCES || d->n_fragments > NA_MAX_FRAGMENTS || d->n_events > NA_MAX_EVENTS) {
+        ctx->err = "render_small_noalloc: batch beyond the static scratch (max " +
+                   std::to_string(NA_MAX_INSTANCES) + " instances x " + std::to_string(NA_MAX_FRAGMENTS) +
+                   " fragments, " + std::to_string(NA_MAX_EVENTS) + " events per call): got " +
+                   std::to_string(d->n_instances) + " x " + std::to_string(d->n_fragments) + ", " +
+                   std::to_string(d->n_events) + " events; use tbf_gpu_render_batch";
+        return TBF_ERR_ARG;
+    }
+    const uint32_t allowed = TBF_RENDER_WHIRL_BYPASS | TBF_RENDER_WHIRLPROC3 | TBF_RENDER_OUT_DEVICE;
+    if ((d->flags & ~allowed) || !(d->flags & TBF_RENDER_OUT_DEVICE))
+        return fail(ctx, TBF_ERR_ARG,
+                    "render_small_noalloc: flags must be OUT_DEVICE plus WHIRL_BYPASS / WHIRLPROC3 only");
+    const uint64_t frames = (uint64_t)d->n_fragments * TBF_FRAGMENT;
+    if (!d->out_l || !d->out_r || d->out_stride < frames)
+        return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: output buffers missing or stride too small");
+    if (d->n_events && !d->events)
+        return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: events missing");
+    const uint32_t n = d->n_instances;
+    uint32_t ids[NA_MAX_INSTANCES];
+    int ring = 512;
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t id = d->instance_ids ? d->instance_ids[i] : i;
+        if (id >= ctx->n_inst || !ctx->inst_alive[id])
+            return fail(ctx, TBF_ERR_HANDLE, "render_small_noalloc: unknown instance id");
+        for (uint32_t j = 0; j < i; ++j)
+            if (ids[j] == id)
+                return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: instance listed twice");
+        ids[i] = id;
+        ring = std::max(ring, ctx->wh[ctx->inst_wh[id]].ring_size);
+    }
+    uint64_t ev_start[NA_MAX_INSTANCES + 1] = {0};
+    {
+        uint32_t prev_slot = 0, prev_frag = 0;
+        for (uint64_t e = 0; e < d->n_events; ++e) {
+            const tbf_event &ev = d->events[e];
+            if (ev.instance >= n || ev.fragment >= d->n_fragments)
+                return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: event slot or fragment out of range");
+            if (ev.instance < prev_slot || (ev.instance == prev_slot && ev.fragment < prev_frag))
+                return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: events not sorted by (slot, fragment)");
+            prev_slot = ev.instance;
+            prev_frag = ev.fragment;
+            ev_start[ev.instance + 1]++;
+        }
+        for (uint32_t i = 0; i < n; ++i)
+            ev_start[i + 1] += ev_start[i];
+    }
+    unsigned char *base = nullptr;
+    if (int rc = noalloc_scratch_address(ctx, &base))
+        return rc;
+    CK(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    float *f32 = reinterpret_cast<float *>(base + NA_OFF_F32);
+    double *f64 = reinterpret_cast<double *>(base + NA_OFF_F64);
+    tbf_event *d_events = reinterpret_cast<tbf_event *>(base + NA_OFF_EVENTS);
+    uint64_t *d_ev_start = reinterpret_cast<uint64_t *>(base + NA_OFF_EVSTART);
+    uint64_t *d_cursor = reinterpret_cast<uint64_t *>(base + NA_OFF_CURSOR);
+    uint32_t *d_ids = reinterpret_cast<uint32_t *>(base + NA_OFF_IDS);
+    unsigned long long *d_csum = reinterpret_cast<unsigned long long *>(base + NA_OFF_CSUM);
+
+    /* the array keeps the last call's contents: everything read before it is written by this
+     * call's own kernels is set here (events, CSR, cursors, ids, checksums).  The stage streams
+     * and FragCtl records are fully written by their producer stage before a consumer reads them */
+    if (d->n_events)
+        CK(cudaMemcpyAsync(d_events, d->events, sizeof(tbf_event) * d->n_events, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_ev_start, ev_start, sizeof(uint64_t) * (n + 1), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_cursor, ev_start, sizeof(uint64_t) * n, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_cursor + NA_MAX_INSTANCES, ev_start, sizeof(uint64_t) * n, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_ids, ids, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, st));
+    if (d->checksums)
+        CK(cudaMemsetAsync(d_csum, 0, sizeof(uint64_t) * n, st));
+    /* the host arrays above are on this function's stack: pageable copies are staged by the
+     * runtime before cudaMemcpyAsync returns, and the call synchronizes before it returns */
+
+    const bool whirl = (d->flags & TBF_RENDER_WHIRL_BYPASS) == 0;
+    const size_t pitch = (size_t)d->n_fragments * TBF_FRAGMENT;
+    RenderParams p;
+    memset(&p, 0, sizeof(p));
+    p.states = ctx->d_states;
+    p.ids = d_ids;
+    p.tg = ctx->d_tg;
+    p.wh = ctx->d_wh;
+    p.events = d_events;
+    p.ev_start = d_ev_start;
+    p.ev_cursor_t = d_cursor;
+    p.ev_cursor_r = d_cursor + NA_MAX_INSTANCES;
+    p.out_l = d->out_l;
+    p.out_r = d->out_r;
+    p.checksums = d->checksums ? d_csum : nullptr;
+    p.out_stride = d->out_stride;
+    p.n_instances = n;
+    p.n_fragments = d->n_fragments;
+    p.flags = d->flags;
+    p.frag_base = 0;
+    p.ctl = reinterpret_cast<FragCtl *>(base + NA_OFF_CTL);
+    p.pitch = pitch;
+    p.u = f32;
+    p.php = f32 + (size_t)n * pitch;
+    if (whirl) {
+        p.dx0 = f32 + (size_t)2 * n * pitch;
+        p.hx0 = f32 + (size_t)3 * n * pitch;
+        for (int l = 0; l < 4; ++l)
+            p.line[l] = f32 + (size_t)(4 + l) * n * pitch;
+        p.hang = f64;
+        p.dang = f64 + (size_t)n * pitch;
+    }
+    CK(cudaEventRecord(ctx->ev0, st));
+    int rc = tbf_launch_stage_t(p, st);
+    if (rc == 0)
+        rc = tbf_launch_stage_r(p, st);
+    if (rc == 0 && whirl)
+        rc = tbf_launch_stage_w(p, ring, st);
+    if (rc == 0 && whirl)
+        rc = tbf_launch_stage_d(p, st);
+    if (rc != 0) {
+        ctx->err = std::string("render_small_noalloc: stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
+        cudaStreamSynchronize(st);
+        return TBF_ERR_CUDA;
+    }
+    ctx->launches = whirl ? 5 : 2;
+    CK(cudaEventRecord(ctx->ev1, st));
+    if (d->checksums)
+        CK(cudaMemcpyAsync(d->checksums, d_csum, sizeof(uint64_t) * n, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return TBF_OK;
+}
+
 unsigned tbf_sizeof_tonegen_tables(void) { return (unsigned)sizeof(tbf_tonegen_tables); }
 unsigned tbf_sizeof_whirl_tables(void) { return (unsigned)sizeof(tbf_whirl_tables); }
 unsigned tbf_sizeof_state_export(void) { return (unsigned)sizeof(tbf_state_export); }

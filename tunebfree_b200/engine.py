@@ -73,6 +73,8 @@ def lib():
                                                           C.POINTER(cabi.WaveSynth), C.POINTER(C.c_int)]
         L.tbf_gpu_synth_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.tbf_gpu_tonegen_tables_read_waves.argtypes = [vp, C.c_int, C.c_void_p, C.c_uint64]
+        L.tbf_gpu_render_small_noalloc.argtypes = [vp, C.POINTER(cabi.BatchDesc)]
+        L.tbf_gpu_noalloc_scratch_bytes.restype = C.c_ulonglong
         L.tbf_gpu_instance_destroy.argtypes = [vp, C.c_uint32, C.c_uint32]
         L.tbf_gpu_tonegen_tables_destroy.argtypes = [vp, C.c_int]
         L.tbf_gpu_whirl_tables_destroy.argtypes = [vp, C.c_int]
@@ -305,6 +307,15 @@ class Context:
         fn = lib().tbf_gpu_render_batch_launch if launch_only else lib().tbf_gpu_render_batch
         self._ck(fn(self._h, C.byref(d)))
         self._keep = keep
+
+    def render_small_noalloc(self, n_instances, n_fragments, events, flags, out_l_ptr, out_r_ptr, stride,
+                             ids=None, checksums=None):
+        """tbf_gpu_render_small_noalloc: a small batch with all scratch in the library's static
+        device array (no allocation); outputs are raw device addresses."""
+        d, keep = self._desc(n_instances, n_fragments, events, flags | cabi.RENDER_OUT_DEVICE, ids,
+                             out_l_ptr, out_r_ptr, stride, checksums)
+        self._ck(lib().tbf_gpu_render_small_noalloc(self._h, C.byref(d)))
+        del keep
 
     def prepare(self, n_instances, n_fragments, events, flags, out_l_ptr=None, out_r_ptr=None,
                 stride=0, ids=None, checksums=None):
