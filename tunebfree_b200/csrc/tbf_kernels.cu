@@ -800,8 +800,10 @@ __device__ __forceinline__ ulonglong2 ld_wave(const float4 *p)
 
 /* the same sum with every lane loading its own four samples of a wheel into registers, one
  * wheel ahead of their use (LDG.128, coalesced: the warp reads the wheel's 512 contiguous
- * bytes): no staging, no barrier, a third fewer instructions per wheel than the bulk-copy
- * variant (profiles/r02_*).  Both variants are built; tbf_launch_stage_t picks. */
+ * bytes): no staging, no barrier and a quarter fewer instructions per wheel than the bulk-copy
+ * variant -- and 1.6 times SLOWER: one wheel of load latency per trip is exposed where the bulk
+ * copies run two wheels ahead without holding registers (profiles/r02_kernels.md).  Kept as the
+ * comparison variant (TBF_T_LOADS=ldg); tbf_launch_stage_t picks. */
 template <int NF, bool ENV>
 __device__ __forceinline__ void core_tile_ldg(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
                                               int cnt, CoreAcc (&acc)[NF])
@@ -2470,8 +2472,9 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
 {
     static int have[2][TBF_MAX_DEVICES] = {{0}, {0}};
     const size_t smem = tbf_stage_t_smem();
-    /* wave loads: "ldg" (default, the faster one: profiles/r02_*) or "tma" (bulk copies) */
-    static const bool tma = getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "tma");
+    /* wave loads: TMA bulk copies (default; stage T alone 1.11 ms per 4096 organs x 32 fragments)
+     * or, with TBF_T_LOADS=ldg, per-lane 16-byte loads (1.82 ms: profiles/r02_kernels.md) */
+    static const bool tma = !(getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "ldg"));
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
     if (tma) {
         if (int rc = set_smem(tbf_stage_t<true>, smem, have[1]))
