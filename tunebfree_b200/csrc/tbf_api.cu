@@ -12,13 +12,68 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
+#include <map>
 #include <string>
 #include <vector>
 
 #include "tbf_device.h"
 #include "tbf_tables.h"
 
+/* Device memory of the tone-generator table sets: slabs from cudaMalloc, blocks bumped off them
+ * and recycled by size class.  A sweep uploads thousands of sets and a re-tuning host frees and
+ * creates one per change (src/clap.cpp:129-160): neither should pay a driver allocation (or a
+ * pool growth) per set -- that was the largest part of round 1's 1.4 ms per set. */
+struct DevArena {
+    struct Slab {
+        unsigned char *p;
+        size_t cap, used;
+    };
+    std::vector<Slab> slabs;
+    std::multimap<size_t, unsigned char *> free_blocks; /* size class -> block */
+    size_t next_slab = (size_t)32 << 20;
+
+    static size_t size_class(size_t bytes)
+    {
+        const size_t g = bytes >= ((size_t)4 << 20) ? ((size_t)1 << 20) : ((size_t)64 << 10);
+        return (bytes + g - 1) / g * g;
+    }
+    unsigned char *alloc(size_t bytes)
+    {
+        const size_t sz = size_class(bytes);
+        auto it = free_blocks.find(sz);
+        if (it != free_blocks.end()) {
+            unsigned char *p = it->second;
+            free_blocks.erase(it);
+            return p;
+        }
+        if (slabs.empty() || slabs.back().cap - slabs.back().used < sz) {
+            const size_t cap = std::max(next_slab, sz);
+            unsigned char *p = nullptr;
+            if (cudaMalloc((void **)&p, cap) != cudaSuccess) {
+                cudaGetLastError();
+                return nullptr;
+            }
+            slabs.push_back(Slab{p, cap, 0});
+            next_slab = std::min(next_slab * 2, (size_t)1 << 30);
+        }
+        Slab &sl = slabs.back();
+        unsigned char *p = sl.p + sl.used;
+        sl.used += sz;
+        return p;
+    }
+    void release(unsigned char *p, size_t bytes) { free_blocks.insert({size_class(bytes), p}); }
+    void destroy()
+    {
+        for (auto &sl : slabs)
+            cudaFree(sl.p);
+        slabs.clear();
+        free_blocks.clear();
+    }
+};
+
 struct TgSet {
+    size_t blob_bytes = 0;   /* of the arena block `wave` points to */
     tbf_tonegen_tables host; /* scalars only; pointers nulled */
     float *wave = nullptr;
     uint16_t *cw = nullptr, *cb = nullptr;
@@ -65,6 +120,9 @@ struct tbf_ctx {
     std::vector<uint8_t> inst_alive;
     size_t n_live = 0;
     std::vector<int> free_tg, free_wh;
+    DevArena arena;
+    double upload_us[4] = {0, 0, 0, 0};
+    uint64_t upload_n = 0;
     InstState *d_tmpl = nullptr;
     /* table upload: page-locked staging and the device copy of the raw waves + their index,
      * grown on demand (tbf_gpu_tonegen_tables_create) */
@@ -75,6 +133,14 @@ struct tbf_ctx {
         size_t cap_h = 0, cap_d = 0;
         cudaEvent_t done = nullptr;
         bool used = false;
+        /* device-side wave synthesis: the samples the kernel flagged as rounding-ambiguous are
+         * checked against the host's libm AFTER the call that made them has returned (the next
+         * use of the slot, or the next entry point that reads tables): no synchronisation per
+         * table set.  [0] = count, [4..] = uint4 records (wheel, sample, float bits, -) */
+        uint32_t *d_flags = nullptr, *h_flags = nullptr;
+        bool pending = false;
+        int pending_handle = -1;
+        tbf_wave_synth pending_synth;
     } stage[2];
     int stage_next = 0;
     /* device-side wave synthesis (tbf_gpu_tonegen_tables_create_synth): the dither decisions
@@ -86,8 +152,6 @@ struct tbf_ctx {
         uint32_t *dev = nullptr;
     };
     std::vector<DitherStream> dither;
-    uint32_t *d_flags = nullptr, *h_flags = nullptr; /* [0] = count, then uint4 records */
-    float *h_patch = nullptr;                         /* page-locked repaired samples        */
     uint64_t synth_flagged = 0, synth_differed = 0;
     /* per-render scratch, grown on demand */
     tbf_event *d_events = nullptr;
@@ -191,13 +255,6 @@ int tbf_gpu_create(tbf_ctx **out, int device)
     }
     bool ok = cudaEventCreateWithFlags(&ctx->fork, cudaEventDisableTiming) == cudaSuccess;
     {
-        /* table sets come from the stream-ordered pool (a host that re-tunes frees and allocates
-         * one per change): freed blocks stay cached instead of going back to the driver */
-        cudaMemPool_t pool;
-        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-            unsigned long long keep = ~0ull;
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-        }
         for (auto &sl : ctx->stage)
             ok = ok && cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming) == cudaSuccess;
     }
@@ -235,9 +292,12 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
         return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (auto &t : ctx->tg)
-        if (!t.freed)
-            cudaFree(t.wave); /* one allocation per set: the other arrays point into it */
+    ctx->arena.destroy(); /* every table set's block */
+    if (ctx->upload_n && getenv("TBF_UPLOAD_PROFILE"))
+        fprintf(stderr, "tbf upload profile: %llu sets; per set: validate+runs %.0f us, slot wait %.0f us, "
+                        "staging fill %.0f us, descriptor+CUDA calls %.0f us\n",
+                (unsigned long long)ctx->upload_n, ctx->upload_us[0] / ctx->upload_n, ctx->upload_us[1] / ctx->upload_n,
+                ctx->upload_us[2] / ctx->upload_n, ctx->upload_us[3] / ctx->upload_n);
     for (auto &w : ctx->wh)
         if (!w.freed)
             cudaFree(w.tables);
@@ -248,14 +308,13 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
     for (auto &sl : ctx->stage) {
         cudaFreeHost(sl.h);
         cudaFree(sl.d);
+        cudaFree(sl.d_flags);
+        cudaFreeHost(sl.h_flags);
         if (sl.done)
             cudaEventDestroy(sl.done);
     }
     for (auto &ds : ctx->dither)
         cudaFree(ds.dev);
-    cudaFree(ctx->d_flags);
-    cudaFreeHost(ctx->h_flags);
-    cudaFreeHost(ctx->h_patch);
     cudaFree(ctx->d_events);
     cudaFree(ctx->d_ev_start);
     cudaFree(ctx->d_ev_cursor);
@@ -333,6 +392,68 @@ static int dither_stream(tbf_ctx *ctx, uint32_t seed, uint64_t n, const uint32_t
 }
 
 #define TBF_SYNTH_FLAG_CAP 4096u
+#define TBF_SYNTH_FLAG_EAGER 255u /* records that travel with the count (4 KB) */
+
+/* The flagged samples of the table set a staging slot synthesised last: recompute each with the
+ * host's libm (tbf_wave_sample) and, where the device's float differs, patch the set's wave
+ * store -- every image of the sample in the four rotated, wrap-extended copies. */
+static int finish_pending_synth(tbf_ctx *ctx, tbf_ctx::StageSlot &sl)
+{
+    if (!sl.pending)
+        return TBF_OK;
+    sl.pending = false;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventSynchronize(sl.done));
+    const uint32_t n_flag = sl.h_flags[0];
+    const int h = sl.pending_handle;
+    if (!n_flag || h < 0 || (size_t)h >= ctx->tg.size() || ctx->tg[h].freed)
+        return TBF_OK;
+    if (n_flag > TBF_SYNTH_FLAG_CAP) {
+        ctx->err = "wave synthesis: too many ambiguous samples in table set " + std::to_string(h) + " (" +
+                   std::to_string(n_flag) + ", degenerate spec)";
+        return TBF_ERR_ARG;
+    }
+    if (n_flag > TBF_SYNTH_FLAG_EAGER)
+        CK(cudaMemcpy(sl.h_flags + 4, sl.d_flags + 4, sizeof(uint32_t) * 4 * n_flag, cudaMemcpyDeviceToHost));
+    const tbf_tonegen_tables &t = ctx->tg[h].host;
+    const uint32_t *bits_h = nullptr, *bits_d = nullptr;
+    if (int rc = dither_stream(ctx, sl.pending_synth.seed, t.wave_total, &bits_h, &bits_d))
+        return rc;
+    size_t off4[TBF_NOF_WHEELS + 1] = {0}, acc = 0;
+    for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
+        off4[w] = acc;
+        if (t.wave_length[w])
+            acc += (size_t)4 * tbf_wave_copy_len(t.wave_length[w]);
+    }
+    for (uint32_t k = 0; k < n_flag; ++k) {
+        const uint32_t *f = sl.h_flags + 4 + 4 * k;
+        const uint32_t w = f[0], i = f[1];
+        if (w < 1 || w > TBF_NOF_WHEELS || i >= t.wave_length[w])
+            continue;
+        const uint32_t pos = t.wave_offset[w] + i;
+        const float v = tbf_wave_sample(&sl.pending_synth, (int)w, i, (bits_h[pos >> 5] >> (pos & 31u)) & 1u);
+        uint32_t vb;
+        memcpy(&vb, &v, 4);
+        ctx->synth_flagged += 1;
+        if (vb == f[2])
+            continue;
+        ctx->synth_differed += 1;
+        const uint32_t len = t.wave_length[w], cl = tbf_wave_copy_len(len);
+        for (uint32_t c = 0; c < 4; ++c) /* copy c holds wave[(j + c) % len] at j < cl */
+            for (uint32_t j = (i + len - (c % len)) % len; j < cl; j += len)
+                CK(cudaMemcpy(ctx->tg[h].wave + off4[w] + (size_t)c * cl + j, &v, sizeof(float),
+                              cudaMemcpyHostToDevice));
+    }
+    return TBF_OK;
+}
+
+static int finish_all_pending_synth(tbf_ctx *ctx)
+{
+    for (auto &sl : ctx->stage)
+        if (int rc = finish_pending_synth(ctx, sl))
+            return rc;
+    return TBF_OK;
+}
 
 /* upload one tone-generator table set; with `synth` the wave samples are made on the device */
 static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, const tbf_wave_synth *synth,
@@ -340,6 +461,17 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
 {
     if (!ctx || !t || !handle || (!synth && !t->wave_data))
         return fail(ctx, TBF_ERR_ARG, "tonegen tables: null argument");
+    /* TBF_UPLOAD_PROFILE=1: where the host time of a table-set upload goes (printed at destroy) */
+    static const bool prof = getenv("TBF_UPLOAD_PROFILE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto lap = [&](int k, std::chrono::steady_clock::time_point &t0) {
+        if (prof) {
+            const auto t1 = now();
+            ctx->upload_us[k] += std::chrono::duration<double, std::micro>(t1 - t0).count();
+            t0 = t1;
+        }
+    };
+    auto tp = now();
     const uint32_t nc = t->contrib_start[TBF_MAX_KEYS];
     for (int w = 1; w <= TBF_NOF_WHEELS; ++w) {
         if ((uint64_t)t->wave_offset[w] + t->wave_length[w] > t->wave_total)
@@ -396,6 +528,7 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
     run_start[TBF_MAX_KEYS] = (uint32_t)run_wheel.size();
     const size_t nr = run_wheel.size();
     CK(cudaSetDevice(ctx->device));
+    lap(0, tp); /* validation + wheel runs */
 
     TgSet s;
     s.host = *t;
@@ -440,8 +573,13 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
 
     tbf_ctx::StageSlot &sl = ctx->stage[ctx->stage_next];
     ctx->stage_next ^= 1;
-    if (sl.used)
+    if (sl.pending) {
+        if (int rc = finish_pending_synth(ctx, sl)) /* waits for the slot's last table set, too */
+            return rc;
+    } else if (sl.used) {
         CK(cudaEventSynchronize(sl.done)); /* the slot's last table set has left it */
+    }
+    lap(1, tp); /* waiting for the staging slot (device-bound when this dominates) */
     if (stage_bytes > sl.cap_h) {
         cudaFreeHost(sl.h);
         sl.h = nullptr;
@@ -480,6 +618,7 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
         memcpy(tail + o_rn, run_count.data(), sizeof(uint16_t) * nr);
     }
 
+    lap(2, tp); /* filling the staging slot */
     /* the set's slot in the device array of descriptors */
     const bool reuse_tg = !ctx->free_tg.empty();
     const size_t idx = reuse_tg ? (size_t)ctx->free_tg.back() : ctx->tg.size();
@@ -500,8 +639,9 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
         ctx->d_tg_cap = ncap;
     }
 
-    unsigned char *dev = nullptr;
-    CK(cudaMallocAsync((void **)&dev, blob_bytes, ctx->stream));
+    unsigned char *dev = ctx->arena.alloc(blob_bytes);
+    if (!dev)
+        return fail(ctx, TBF_ERR_NOMEM, "tonegen tables: out of device memory");
     float *d_raw = reinterpret_cast<float *>(sl.d);
     const uint32_t *d_meta = reinterpret_cast<const uint32_t *>(sl.d + s_meta);
     cudaError_t ue = cudaSuccess;
@@ -512,56 +652,31 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
         const uint32_t *bits_h = nullptr, *bits_d = nullptr;
         int rc = dither_stream(ctx, synth->seed, t->wave_total, &bits_h, &bits_d);
         if (rc != TBF_OK) {
-            cudaFreeAsync(dev, ctx->stream);
+            ctx->arena.release(dev, blob_bytes);
             return rc;
         }
         const size_t flag_bytes = sizeof(uint32_t) * 4 * (1 + TBF_SYNTH_FLAG_CAP);
-        if (!ctx->d_flags) {
-            CK(cudaMalloc((void **)&ctx->d_flags, flag_bytes));
-            CK(cudaHostAlloc((void **)&ctx->h_flags, flag_bytes, cudaHostAllocDefault));
-            CK(cudaHostAlloc((void **)&ctx->h_patch, sizeof(float) * TBF_SYNTH_FLAG_CAP, cudaHostAllocDefault));
+        if (!sl.d_flags) {
+            CK(cudaMalloc((void **)&sl.d_flags, flag_bytes));
+            CK(cudaHostAlloc((void **)&sl.h_flags, flag_bytes, cudaHostAllocDefault));
         }
         WaveSynthParams sp;
         sp.rate = synth->sample_rate;
         memcpy(sp.harmonics, synth->harmonics, sizeof(sp.harmonics));
         ue = cudaMemcpyAsync(sl.d + s_meta, hs + s_meta, s_desc - s_meta, cudaMemcpyHostToDevice, ctx->stream);
         if (ue == cudaSuccess)
-            ue = cudaMemsetAsync(ctx->d_flags, 0, 16, ctx->stream);
+            ue = cudaMemsetAsync(sl.d_flags, 0, 16, ctx->stream);
         if (ue == cudaSuccess)
             ue = (cudaError_t)tbf_launch_wave_synth(
                 d_raw, d_meta, reinterpret_cast<const double *>(sl.d + s_synth),
                 reinterpret_cast<const double *>(sl.d + s_synth) + (TBF_NOF_WHEELS + 1), sp, bits_d,
-                ctx->d_flags, ctx->d_flags + 4, TBF_SYNTH_FLAG_CAP, ctx->stream);
+                sl.d_flags, sl.d_flags + 4, TBF_SYNTH_FLAG_CAP, ctx->stream);
+        /* the count and the first records come back with the rest of the set's work; they are
+         * looked at in finish_pending_synth(), not here: no wait per table set */
         if (ue == cudaSuccess)
-            ue = cudaMemcpyAsync(ctx->h_flags, ctx->d_flags, 16, cudaMemcpyDeviceToHost, ctx->stream);
-        if (ue == cudaSuccess)
-            ue = cudaStreamSynchronize(ctx->stream);
-        /* samples whose float could hinge on the last bit of a sine: the host's libm decides */
-        const uint32_t n_flag = ue == cudaSuccess ? ctx->h_flags[0] : 0;
-        if (ue == cudaSuccess && n_flag > TBF_SYNTH_FLAG_CAP) {
-            cudaFreeAsync(dev, ctx->stream);
-            ctx->err = "wave synthesis: too many ambiguous samples (" + std::to_string(n_flag) + ", degenerate spec)";
-            return TBF_ERR_ARG;
-        }
-        if (ue == cudaSuccess && n_flag) {
-            ue = cudaMemcpy(ctx->h_flags + 4, ctx->d_flags + 4, sizeof(uint32_t) * 4 * n_flag,
-                            cudaMemcpyDeviceToHost);
-            for (uint32_t k = 0; ue == cudaSuccess && k < n_flag; ++k) {
-                const uint32_t *f = ctx->h_flags + 4 + 4 * k;
-                const uint32_t w = f[0], i = f[1];
-                const uint32_t pos = t->wave_offset[w] + i;
-                const float v = tbf_wave_sample(synth, (int)w, i, (bits_h[pos >> 5] >> (pos & 31u)) & 1u);
-                uint32_t vb;
-                memcpy(&vb, &v, 4);
-                ctx->synth_flagged += 1;
-                if (vb != f[2]) {
-                    ctx->synth_differed += 1;
-                    ctx->h_patch[k] = v;
-                    ue = cudaMemcpyAsync(d_raw + pos, &ctx->h_patch[k], sizeof(float), cudaMemcpyHostToDevice,
-                                         ctx->stream);
-                }
-            }
-        }
+            ue = cudaMemcpyAsync(sl.h_flags, sl.d_flags, 16 * (1 + TBF_SYNTH_FLAG_EAGER), cudaMemcpyDeviceToHost,
+                                 ctx->stream);
+        sl.pending_synth = *synth;
     }
     if (ue == cudaSuccess)
         ue = cudaMemcpyAsync(dev + o_cl, hs + s_tail, tail_bytes, cudaMemcpyHostToDevice, ctx->stream);
@@ -609,14 +724,17 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
     if (ue == cudaSuccess)
         ue = cudaEventRecord(sl.done, ctx->stream);
     sl.used = true;
+    lap(3, tp); /* descriptor + CUDA calls */
+    ctx->upload_n += 1;
     if (ue != cudaSuccess) {
         cudaStreamSynchronize(ctx->stream);
-        cudaFreeAsync(dev, ctx->stream);
+        ctx->arena.release(dev, blob_bytes);
         ctx->err = std::string("tonegen tables upload: ") + cudaGetErrorString(ue);
         cudaGetLastError();
         return TBF_ERR_CUDA;
     }
-    s.wave = reinterpret_cast<float *>(dev); /* owns the allocation; the rest point into it */
+    s.wave = reinterpret_cast<float *>(dev); /* owns the block; the rest point into it */
+    s.blob_bytes = blob_bytes;
     s.cl = nullptr;
     s.cw = s.cb = s.rw = s.rn = nullptr;
     s.host.wave_data = nullptr;
@@ -627,6 +745,10 @@ static int create_tonegen_tables(tbf_ctx *ctx, const tbf_tonegen_tables *t, cons
         ctx->tg[idx] = s;
     } else {
         ctx->tg.push_back(s);
+    }
+    if (synth) {
+        sl.pending = true;
+        sl.pending_handle = (int)idx;
     }
     *handle = (int)idx;
     return TBF_OK;
@@ -651,6 +773,8 @@ int tbf_gpu_synth_stats(const tbf_ctx *ctx, uint64_t *flagged, uint64_t *differe
 {
     if (!ctx)
         return TBF_ERR_ARG;
+    if (finish_all_pending_synth(const_cast<tbf_ctx *>(ctx)) != TBF_OK)
+        return TBF_ERR_CUDA;
     if (flagged)
         *flagged = ctx->synth_flagged;
     if (differed)
@@ -665,6 +789,8 @@ int tbf_gpu_tonegen_tables_read_waves(tbf_ctx *ctx, int handle, float *out, uint
     if (!ctx || !out || !tg_usable(ctx, handle))
         return fail(ctx, TBF_ERR_HANDLE, "read_waves: unknown handle");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = finish_all_pending_synth(ctx))
+        return rc;
     CK(cudaStreamSynchronize(ctx->stream));
     const TgSet &s = ctx->tg[handle];
     size_t off4 = 0;
@@ -943,7 +1069,9 @@ static void tg_release_if_unused(tbf_ctx *ctx, int h)
     TgSet &t = ctx->tg[h];
     if (t.freed || !t.destroyed || t.refs > 0)
         return;
-    cudaFreeAsync(t.wave, ctx->stream); /* back to the stream-ordered pool */
+    /* back to the arena: its next user writes it with work ordered on the library's stream,
+     * which every render has joined by then */
+    ctx->arena.release(reinterpret_cast<unsigned char *>(t.wave), t.blob_bytes);
     t.wave = nullptr;
     t.freed = true;
     ctx->free_tg.push_back(h);
@@ -1032,6 +1160,8 @@ int tbf_gpu_instance_destroy(tbf_ctx *ctx, uint32_t first_id, uint32_t count)
         if (!ctx->inst_alive[i])
             return fail(ctx, TBF_ERR_HANDLE, "instance_destroy: instance already destroyed");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = finish_all_pending_synth(ctx))
+        return rc;
     ctx->has_prepared = false; /* a prepared batch may list the instance */
     for (size_t i = first_id; i < (size_t)first_id + count; ++i) {
         const int tgh = ctx->inst_tg[i], whh = ctx->inst_wh[i];
@@ -1058,6 +1188,8 @@ int tbf_gpu_tonegen_tables_destroy(tbf_ctx *ctx, int handle)
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "tonegen_tables_destroy: a launch is in flight");
     CK(cudaSetDevice(ctx->device));
+    if (int rc = finish_all_pending_synth(ctx))
+        return rc;
     ctx->tg[handle].destroyed = true;
     tg_release_if_unused(ctx, handle);
     return TBF_OK;
@@ -1177,6 +1309,8 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "render: previous launch not synchronized");
     ctx->has_prepared = false;
+    if (int rc = finish_all_pending_synth(ctx)) /* table sets still awaiting their libm check */
+        return rc;
     if (!d->n_instances || !d->n_fragments)
         return fail(ctx, TBF_ERR_ARG, "render: empty batch");
     const bool no_out = (d->flags & TBF_RENDER_NO_OUTPUT) != 0;
@@ -1874,6 +2008,8 @@ int tbf_gpu_render_small_noalloc(tbf_ctx *ctx, const tbf_batch_desc *d)
         return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: null argument");
     if (ctx->in_flight)
         return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: previous launch not synchronized");
+    if (int rc = finish_all_pending_synth(ctx))
+        return rc;
     if (!d->n_instances || !d->n_fragments)
         return fail(ctx, TBF_ERR_ARG, "render_small_noalloc: empty batch");
     if (d->n_instances > NA_MAX_INSTANCES || d->n_fragments > NA_MAX_FRAGMENTS || d->n_events > NA_MAX_EVENTS) {

@@ -6,7 +6,10 @@
  * every table entry has to come out bit-identical.
  * Compiled with -ffp-contract=off, no fast-math.
  */
+#include <algorithm>
+#include <chrono>
 #include <math.h>
+#include <cmath>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -70,6 +73,24 @@ struct Rng {
     int32_t next() { return tbf_rand(&st); }
     /* drnd(), src/tonegen.cpp:342 */
     double drnd() { return ((double)next()) / (double)kRandMax; }
+    /* n draws thrown away: x[i] = x[i - 31] + x[i - 3] on a linear buffer (no ring arithmetic) */
+    void skip(uint64_t n)
+    {
+        enum { CHUNK = 4096 };
+        uint32_t lin[31 + CHUNK];
+        for (int j = 0; j < 31; ++j)
+            lin[j] = (uint32_t)st.r[(st.idx + j) % 31];
+        while (n) {
+            const uint32_t m = (uint32_t)(n < CHUNK ? n : CHUNK);
+            for (uint32_t i = 31; i < 31 + m; ++i)
+                lin[i] = lin[i - 31] + lin[i - 3];
+            memmove(lin, lin + m, sizeof(uint32_t) * 31);
+            n -= m;
+        }
+        for (int j = 0; j < 31; ++j)
+            st.r[j] = (int32_t)lin[j];
+        st.idx = 0;
+    }
 };
 
 /* dBToGain, src/tonegen.cpp:337 */
@@ -434,19 +455,50 @@ double osc_frequency(const double *freq300, int wheel)
 void manual_defaults(const tbf_tonegen_spec *s, const double *freq300, Wiring &w, int key_offset,
                      int bus_offset)
 {
-    double of[TBF_NOF_WHEELS + 1];
-    for (int i = 1; i <= TBF_NOF_WHEELS; ++i)
+    double of[TBF_NOF_WHEELS + 1], log_of[TBF_NOF_WHEELS + 1], log_tr[9];
+    for (int i = 1; i <= TBF_NOF_WHEELS; ++i) {
         of[i] = osc_frequency(freq300, i);
+        log_of[i] = log2(of[i]);
+    }
+    for (int b = 0; b < 9; ++b)
+        log_tr[b] = log2(s->target_ratio[b]);
+    bool logs_finite = true;
+    for (int i = 1; i <= TBF_NOF_WHEELS; ++i)
+        logs_finite = logs_finite && std::isfinite(log_of[i]);
+    /* the reference's distance of wheel t, evaluated exactly as it does */
+    auto exact_cent = [&](int t, int k, int b) {
+        const float ratio = (float)(of[t] / freq300[k]);
+        return (float)(1200 * fabs(log2(s->target_ratio[b] / (double)ratio)));
+    };
     for (int k = 0; k < 128; ++k) {
         const int key = k + key_offset;
         if (!w.key_taper[key].empty())
             continue;
+        w.key_taper[key].reserve(9);
+        const double log_fk = log2(freq300[k]);
         for (int b = 0; b < 9; ++b) {
+            /* The reference scans all 256 wheels with one log2 each (300 000 calls per manual).
+             * Here: the distance from precomputed logarithms first -- it is within
+             * 1e-3 + 1e-6 * cent of the reference's float value (float rounding of the ratio
+             * and of the result) -- then the reference's own expression, in the reference's
+             * order and with its strict comparison, for the wheels within twice that of the
+             * approximate minimum: the wheel the full scan picks is always among them. */
+            double approx[TBF_NOF_WHEELS + 1]; /* in octaves: cents / 1200 */
+            double a_min = std::numeric_limits<double>::infinity();
+            const double centre = log_tr[b] + log_fk;
+            const bool finite = logs_finite && std::isfinite(centre);
+            for (int t = 1; t <= TBF_NOF_WHEELS; ++t) {
+                approx[t] = fabs(centre - log_of[t]);
+                a_min = approx[t] < a_min ? approx[t] : a_min;
+            }
+            const double limit = finite ? a_min + 2.0 * (1e-3 / 1200 + 1e-6 * a_min)
+                                        : std::numeric_limits<double>::infinity();
             float smallest = std::numeric_limits<float>::infinity();
             int best = 0;
             for (int t = 1; t <= TBF_NOF_WHEELS; ++t) {
-                const float ratio = (float)(of[t] / freq300[k]);
-                const float cent = (float)(1200 * fabs(log2(s->target_ratio[b] / (double)ratio)));
+                if (finite && approx[t] > limit)
+                    continue;
+                const float cent = exact_cent(t, k, b);
                 if (cent < smallest) {
                     smallest = cent;
                     best = t;
@@ -493,6 +545,7 @@ void default_crosstalk(const tbf_tonegen_spec *s, Wiring &w, int key_offset, int
         const int key = k + key_offset;
         if (!w.key_crosstalk[key].empty())
             continue;
+        w.key_crosstalk[key].reserve(9 * w.key_taper[key].size());
         for (int b = 0; b < 9; ++b) {
             const int bus = bus_offset + b;
             for (const Conn &c : w.key_taper[key]) {
@@ -577,11 +630,17 @@ void compile_play_matrix(const tbf_tonegen_spec *s, const Wiring &w, std::vector
                          std::vector<float> &cl)
 {
     start.assign(TBF_MAX_KEYS + 1, 0);
+    cw.reserve(49152);
+    cb.reserve(49152);
+    cl.reserve(49152);
     static thread_local float gain[TBF_NOF_WHEELS + 1][TBF_NOF_BUSES];
-    static thread_local unsigned char used[TBF_NOF_WHEELS + 1][TBF_NOF_BUSES];
+    /* the cells a key touches (a few hundred of the 257 x 27) as bit masks: which buses of a
+     * wheel, which wheels -- so that neither the clearing nor the (wheel, bus)-ordered read-out
+     * walks the whole matrix 384 times, and nothing has to be sorted */
+    uint32_t bus_mask[TBF_NOF_WHEELS + 1] = {0};
+    uint64_t wheel_mask[(TBF_NOF_WHEELS + 64) / 64] = {0};
     for (int k = 0; k < TBF_MAX_KEYS; ++k) {
         start[k] = (uint32_t)cw.size();
-        memset(used, 0, sizeof(used));
         const std::vector<Conn> *lists[2] = {&w.key_taper[k], &w.key_crosstalk[k]};
         for (int l = 0; l < 2; ++l)
             for (const Conn &c : *lists[l]) {
@@ -591,27 +650,39 @@ void compile_play_matrix(const tbf_tonegen_spec *s, const Wiring &w, std::vector
                     const float g = t.level * c.level;
                     if (g == 0.0)
                         continue;
-                    if (!used[t.a][c.bus]) {
-                        used[t.a][c.bus] = 1;
+                    const uint32_t bit = 1u << c.bus;
+                    if (!(bus_mask[t.a] & bit)) {
+                        bus_mask[t.a] |= bit;
+                        wheel_mask[t.a >> 6] |= 1ull << (t.a & 63);
                         gain[t.a][c.bus] = g;
                     } else {
                         gain[t.a][c.bus] += g;
                     }
                 }
             }
-        for (int wh = 0; wh <= TBF_NOF_WHEELS; ++wh)
-            for (int b = 0; b < TBF_NOF_BUSES; ++b) {
-                if (!used[wh][b])
-                    continue;
-                float g = gain[wh][b];
-                if ((double)g < s->contribution_floor)
-                    continue;
-                if ((double)g < s->contribution_min)
-                    g = (float)s->contribution_min;
-                cw.push_back((uint16_t)wh);
-                cb.push_back((uint16_t)b);
-                cl.push_back(g);
+        /* wheel-major, bus-minor: the reference's order (src/tonegen.cpp:1183-1201) */
+        for (size_t word = 0; word < sizeof(wheel_mask) / sizeof(wheel_mask[0]); ++word) {
+            uint64_t wm = wheel_mask[word];
+            wheel_mask[word] = 0;
+            while (wm) {
+                const int wh = (int)(word * 64) + __builtin_ctzll(wm);
+                wm &= wm - 1;
+                uint32_t bm = bus_mask[wh];
+                bus_mask[wh] = 0;
+                while (bm) {
+                    const int b = __builtin_ctz(bm);
+                    bm &= bm - 1;
+                    float g = gain[wh][b];
+                    if ((double)g < s->contribution_floor)
+                        continue;
+                    if ((double)g < s->contribution_min)
+                        g = (float)s->contribution_min;
+                    cw.push_back((uint16_t)wh);
+                    cb.push_back((uint16_t)b);
+                    cl.push_back(g);
+                }
             }
+        }
     }
     start[TBF_MAX_KEYS] = (uint32_t)cw.size();
 }
@@ -629,7 +700,17 @@ int fit_wave(double hz, double precision, int min_samples, int max_samples, doub
     const int max_waves = (int)floor((hz * (double)max_samples) / rate);
     if (!(min_samples < max_samples) || !(min_waves <= max_waves) || !(min_waves > 0))
         return TBF_ERR_REFERENCE_UB; /* reference asserts */
+    /* The reference divides once per candidate (up to ~2000 candidates for the top wheels).
+     * Here a product with the reciprocal comes first: it is within 1e-8 of the quotient (the
+     * quotient is below 2^13, the reciprocal's relative error 2^-52), and only a candidate that
+     * could lower the running minimum or pass the precision test by that margin is evaluated
+     * with the reference's own division -- same minimum, same first hit, same result. */
+    const double inv_hz = 1.0 / hz, margin = 1e-8;
     for (int i = min_waves; i <= max_waves; ++i) {
+        const double approx = (rate * i) * inv_hz;
+        const double approx_err = fabs(approx - rint(approx));
+        if (approx_err >= min_err + margin && approx_err >= precision + margin && approx_err < 0.5 - margin)
+            continue;
         const double nws = (rate * i) / hz;
         const double spn = rint(nws);
         const double err = fabs(nws - spn);
@@ -888,8 +969,20 @@ static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_w
     if (max_len > TBF_FRAGMENT)
         max_len = TBF_FRAGMENT;
 
+    /* TBF_BUILD_PROFILE=1: phase times of one build on stderr */
+    static const bool prof = getenv("TBF_BUILD_PROFILE") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (prof) {
+            const auto t1 = std::chrono::steady_clock::now();
+            fprintf(stderr, "tbf build %-22s %7.0f us\n", what,
+                    std::chrono::duration<double, std::micro>(t1 - t_prev).count());
+            t_prev = t1;
+        }
+    };
     double freq300[TBF_NOF_FREQS];
     tbf_extend_frequencies(s->freqs, freq300, NULL, NULL);
+    lap("extend_frequencies");
 
     Wiring *w = new Wiring();
     int rc = default_configuration(s, freq300, *w);
@@ -900,8 +993,10 @@ static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_w
     std::vector<uint32_t> start;
     std::vector<uint16_t> cw, cb;
     std::vector<float> cl;
+    lap("default_configuration");
     compile_play_matrix(s, *w, start, cw, cb, cl);
     delete w;
+    lap("compile_play_matrix");
 
     /* initOscillators, src/tonegen.cpp:1470-1630 */
     double att[TBF_NOF_WHEELS + 1];
@@ -926,6 +1021,7 @@ static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_w
         o->wave_length[i] = (uint32_t)len[i];
         total += len[i];
     }
+    lap("fit_wave x 256");
     float *wave = nullptr;
     Rng rng(s->seed);
     if (synth) {
@@ -938,8 +1034,7 @@ static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_w
             synth->f1[i] = osc_frequency(freq300, i);
             synth->attenuation[i] = att[i];
         }
-        for (uint64_t k = 0; k < total; ++k)
-            (void)rng.next();
+        rng.skip(total);
     } else {
         wave = (float *)malloc(sizeof(float) * (size_t)total);
         if (!wave)
@@ -950,6 +1045,7 @@ static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_w
     }
     o->wave_data = wave;
     o->wave_total = total;
+    lap("waves / rand() skip");
 
     const size_t nc = cw.size();
     uint16_t *pw = (uint16_t *)malloc(sizeof(uint16_t) * (nc ? nc : 1));
@@ -975,6 +1071,7 @@ static int build_tonegen(const tbf_tonegen_spec *s, tbf_tonegen_tables *o, tbf_w
 
     init_key_comp(o->key_comp_table);
     init_envelopes(s, min_len, max_len, o, rng);
+    lap("copies, envelopes");
 
     for (int i = 0; i < TBF_NOF_BUSES; ++i)
         for (int st = 0; st < 9; ++st)
