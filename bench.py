@@ -410,42 +410,27 @@ def run_gpu_arm(a):
         tables.free_tables(tt0, wt0)
 
         host_waves = bool(os.environ.get("TBF_BENCH_HOST_WAVES"))  # round 1's path, for comparison
-
-        def build_one(g):
-            sp = tables.InstanceSpec(freqs=tables.freqs_from_ratios(sweep_degs[g]), seed=1)
-            return (sp.build_tonegen(), None) if host_waves else sp.build_tonegen_synth()
-
-        ids = np.zeros(n_inst, dtype=np.uint32)
-        t_wait = t_upload = 0.0
+        specs = (cabi.TonegenSpec * n_inst)()
+        for k, g in enumerate(global_ids):
+            sp = tables.InstanceSpec(freqs=tables.freqs_from_ratios(sweep_degs[int(g)]), seed=1)
+            C.memmove(C.byref(specs[k]), C.byref(sp.tg), C.sizeof(cabi.TonegenSpec))
+        # tbf_gpu_organs_create (tbf_pipeline.cpp): builder threads on the host cores, the calling
+        # thread uploads in order; nothing of the loop runs in Python
         t_init0 = time.perf_counter()
-        chunks = [[int(g) for g in global_ids[lo:lo + 256]] for lo in range(0, n_inst, 256)]
-        with ThreadPoolExecutor(threads) as pool:
-            # the host cores build chunk c + 1 while this thread uploads chunk c
-            futures = [pool.submit(build_one, g) for g in chunks[0]]
-            lo = 0
-            for c in range(len(chunks)):
-                t0 = time.perf_counter()
-                built = [f.result() for f in futures]
-                t1 = time.perf_counter()
-                futures = [pool.submit(build_one, g) for g in chunks[c + 1]] if c + 1 < len(chunks) else []
-                for k, (tt, ws) in enumerate(built):
-                    h = ctx.tonegen_tables(tt) if ws is None else ctx.tonegen_tables_synth(tt, ws)
-                    tg_handles[lo + k] = h
-                    ids[lo + k] = ctx.create_instances(h, wh_handles["default"], 1)
-                    tables.free_tables(tt, None)
-                lo += len(built)
-                t_wait += t1 - t0
-                t_upload += time.perf_counter() - t1
+        ids, handles, (t_wall, t_wait, t_upload) = ctx.create_organs(specs, wh_handles["default"], threads,
+                                                                     device_waves=not host_waves)
         ctx.synchronize()
         t_init = time.perf_counter() - t_init0
+        for k, h in enumerate(handles):
+            tg_handles[k] = h
         init = {"organs_initialised_per_s": n_inst / t_init, "wall_s": t_init, "host_threads": threads,
                 "upload_s": t_upload, "waiting_for_builders_s": t_wait,
                 "wave_synthesis": "host" if host_waves else "device",
                 "synth_samples_flagged_differed": None if host_waves else list(ctx.synth_stats()),
                 "what": "128 frequencies -> wheel choice, play matrix, loop lengths, envelopes on the host "
-                        "cores (tbf_build_tonegen_tables_synth), the 256 wavetables of every organ "
-                        "synthesised on the device (tbf_gpu_tonegen_tables_create_synth), instance "
-                        "create; builders and uploads overlap"}
+                        "cores (tbf_build_tonegen_tables_synth on builder threads), the 256 wavetables of "
+                        "every organ synthesised on the device (tbf_gpu_tonegen_tables_create_synth), "
+                        "instance create: tbf_gpu_organs_create, builders and uploads overlap"}
     else:
         ids = sharding.slot_instance_ids(
             groups, lambda k, count: ctx.create_instances(tg_handles[(k[0], k[2])], wh_handles[k[1]], count))

@@ -226,6 +226,18 @@ struct tbf_wave_synth;
 int tbf_gpu_tonegen_tables_create_synth(tbf_ctx *ctx, const tbf_tonegen_tables *t,
                                         const struct tbf_wave_synth *synth, int *handle);
 int tbf_gpu_synth_stats(const tbf_ctx *ctx, uint64_t *flagged, uint64_t *differed);
+/* initToneGenerator for MANY organs at once (BASELINE config 4: one tuning per organ, the
+ * reference re-runs initToneGenerator per tuning: src/clap.cpp:129-160, src/tonegen.cpp:2905):
+ * n_threads host threads (<= 0: one per core) build the table sets of specs[0..n) while the
+ * calling thread uploads them in order and creates one instance each with Leslie set
+ * `whirl_tables`; device_waves != 0 synthesises the wavetables on the GPU.  tonegen_handles
+ * (may be NULL) and instance_ids receive n entries; stats (may be NULL) = {wall seconds, seconds
+ * the uploader waited for builders, seconds it spent uploading}.  On an error the organs created
+ * so far stay; the code is the first failing call's.  (tbf_pipeline.cpp) */
+struct tbf_tonegen_spec;
+int tbf_gpu_organs_create(tbf_ctx *ctx, const struct tbf_tonegen_spec *specs, uint32_t n, int whirl_tables,
+                          int n_threads, int device_waves, int *tonegen_handles, uint32_t *instance_ids,
+                          double *stats);
 /* the raw waves of a set as the device holds them (wave_offset layout): parity tests */
 int tbf_gpu_tonegen_tables_read_waves(tbf_ctx *ctx, int handle, float *out, uint64_t n_floats);
 /* how the kernels treat a whirl table set: 1 = parallel ordered gather of the delay lines

@@ -3,7 +3,7 @@
 (tests/scala_scale_archive/scl, 5176 files) through (1) this repo's parser + table builder
 and (2) the reference engine (oracle/_ref) given the same 128 frequencies.
 
-Writes tests/golden/scala_sweep.npz:
+Writes tunebfree_b200/data/scala_sweep.npz (package data: the product's config-4 workload reads it):
   names    [S]        file names
   status   [S] int8   0 ok: tables bit-identical on both sides
                       1 unparsable by tbf_scl_ratios (not a scale this repo accepts)
@@ -34,7 +34,7 @@ sys.path.insert(0, ROOT)
 import numpy as np
 
 ARCHIVE = "/root/reference/tests/scala_scale_archive/scl"
-OUT = os.path.join(ROOT, "tests", "golden", "scala_sweep.npz")
+OUT = os.path.join(ROOT, "tunebfree_b200", "data", "scala_sweep.npz")
 
 
 def files():

@@ -106,15 +106,16 @@ def test_config4_scala_sweep_all_scales(ref):
     wh = ctx.whirl_tables(wt0)
     tables.free_tables(tt0, wt0)
 
-    def build(g):
-        return tables.InstanceSpec(freqs=tables.freqs_from_ratios(degs[g]), seed=1).build_tonegen()
-
-    ids = []
-    with ThreadPoolExecutor(os.cpu_count() or 1) as pool:
-        for lo in range(0, n, 256):
-            for tt in pool.map(build, range(lo, min(n, lo + 256))):
-                ids.append(ctx.create_instances(ctx.tonegen_tables(tt), wh, 1))
-                tables.free_tables(tt, None)
+    import ctypes as C
+    specs = (cabi.TonegenSpec * n)()
+    for g in range(n):
+        sp = tables.InstanceSpec(freqs=tables.freqs_from_ratios(degs[g]), seed=1)
+        C.memmove(C.byref(specs[g]), C.byref(sp.tg), C.sizeof(cabi.TonegenSpec))
+    # builder threads on the host cores, wavetables synthesised on the device (tbf_gpu_organs_create)
+    ids, _, _ = ctx.create_organs(specs, wh, threads=os.cpu_count() or 1)
+    ids = [int(i) for i in ids]
+    flagged, differed = ctx.synth_stats()
+    print("config 4: %d organs, %d wave samples flagged, %d repaired with the host's libm" % (n, flagged, differed))
     sc = workloads.instance_events(0, n_frag, config=4)
     ev_np = np.concatenate([np.concatenate([np.full((len(sc), 1), s, dtype=np.int32),
                                             np.array(sorted(sc, key=lambda e: e[0]), dtype=np.int32)], axis=1)

@@ -1,7 +1,7 @@
 """BASELINE config 4: one organ per Scala scale of the reference's archive
 (/root/reference/tests/scala_scale_archive/scl, 5176 files).
 
-tests/golden/scala_sweep.npz (tests/golden/make_scala_sweep.py, run in the build container
+tunebfree_b200/data/scala_sweep.npz (tests/golden/make_scala_sweep.py, run in the build container
 against the reference engine) holds, for every file, the scale's degrees, what each side did
 with it and a digest of the REFERENCE's tone-generator tables.  The CPU tests rebuild a sample
 of the tunings with the product's table builder and compare digests; the GPU test renders a
@@ -14,7 +14,8 @@ import pytest
 
 from tunebfree_b200 import cabi, tables, workloads
 
-FIXTURE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "scala_sweep.npz")
+FIXTURE = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tunebfree_b200", "data",
+                       "scala_sweep.npz")
 ARCHIVE = "/root/reference/tests/scala_scale_archive/scl"
 
 

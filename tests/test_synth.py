@@ -104,3 +104,46 @@ def test_device_waves_bit_identical_to_host_waves(ref):
     tables.free_tables(part, None)
     tables.free_tables(tt0, wt0)
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_organs_create_pipeline_matches_one_by_one(ref):
+    """tbf_gpu_organs_create (builder threads + in-order uploads, wavetables on the device) gives
+    the organs that building and uploading one by one on the host gives: same waves, and the
+    render of a few of them is the oracle's."""
+    from tunebfree_b200 import engine
+    names, degs, _ = workloads.scala_sweep()
+    pick = list(range(5, len(names), len(names) // 60))[:60]
+    ctx = engine.Context(0)
+    tt0, wt0 = tables.InstanceSpec(seed=1).build()
+    wh = ctx.whirl_tables(wt0)
+    tables.free_tables(tt0, wt0)
+    specs = (cabi.TonegenSpec * len(pick))()
+    for k, g in enumerate(pick):
+        sp = tables.InstanceSpec(freqs=tables.freqs_from_ratios(degs[g]), seed=1)
+        C.memmove(C.byref(specs[k]), C.byref(sp.tg), C.sizeof(cabi.TonegenSpec))
+    ids, handles, (wall, wait, up) = ctx.create_organs(specs, wh, threads=4)
+    assert len(set(ids.tolist())) == len(pick) and len(set(handles)) == len(pick) and wall > 0
+    for k in (0, 17, 59):
+        full = tables.InstanceSpec(freqs=tables.freqs_from_ratios(degs[pick[k]]), seed=1).build_tonegen()
+        got = ctx.read_waves(handles[k], full.wave_total)
+        assert np.array_equal(got.view(np.uint32), _waves(full).view(np.uint32)), names[pick[k]]
+        tables.free_tables(full, None)
+    n_frag = 120
+    ev = workloads.instance_events(0, n_frag, config=4)
+    sel = [3, 31, 58]
+    gl, gr = ctx.render(len(sel), n_frag, [ev] * len(sel), cabi.RENDER_WHIRLPROC3, ids=[int(ids[k]) for k in sel])
+    for j, k in enumerate(sel):
+        r = ref.RefInstance(freqs=tables.freqs_from_ratios(degs[pick[k]]), seed=1)
+        rl, rr = r.render(n_frag, cabi.RENDER_WHIRLPROC3, ev)
+        r.close()
+        assert np.array_equal(gl[j].view(np.uint32), rl.view(np.uint32)), names[pick[k]]
+        assert np.array_equal(gr[j].view(np.uint32), rr.view(np.uint32)), names[pick[k]]
+    # a spec the builder refuses stops the pipeline with its error code
+    bad = (cabi.TonegenSpec * 3)()
+    for k in range(3):
+        C.memmove(C.byref(bad[k]), C.byref(specs[k]), C.sizeof(cabi.TonegenSpec))
+    bad[1].sample_rate = -1.0
+    with pytest.raises(engine.TbfError):
+        ctx.create_organs(bad, wh, threads=2)
+    ctx.close()

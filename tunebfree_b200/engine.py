@@ -73,6 +73,8 @@ def lib():
                                                           C.POINTER(cabi.WaveSynth), C.POINTER(C.c_int)]
         L.tbf_gpu_synth_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.tbf_gpu_tonegen_tables_read_waves.argtypes = [vp, C.c_int, C.c_void_p, C.c_uint64]
+        L.tbf_gpu_organs_create.argtypes = [vp, C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_int,
+                                            C.POINTER(C.c_int), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
         L.tbf_gpu_render_small_noalloc.argtypes = [vp, C.POINTER(cabi.BatchDesc)]
         L.tbf_gpu_noalloc_scratch_bytes.restype = C.c_ulonglong
         L.tbf_gpu_instance_destroy.argtypes = [vp, C.c_uint32, C.c_uint32]
@@ -182,6 +184,18 @@ class Context:
         out = np.zeros(int(n_floats), dtype=np.float32)
         self._ck(lib().tbf_gpu_tonegen_tables_read_waves(self._h, handle, out.ctypes.data, int(n_floats)))
         return out
+
+    def create_organs(self, specs, whirl_handle, threads=0, device_waves=True):
+        """tbf_gpu_organs_create: one organ per cabi.TonegenSpec of `specs` (a ctypes array), built
+        on `threads` host threads, uploaded and created in order.
+        -> (instance ids, tonegen handles, (wall s, waiting-for-builders s, upload s))"""
+        n = len(specs)
+        ids = (C.c_uint32 * n)()
+        tgh = (C.c_int * n)()
+        st = (C.c_double * 3)()
+        self._ck(lib().tbf_gpu_organs_create(self._h, C.cast(specs, C.c_void_p), n, whirl_handle, threads,
+                                             1 if device_waves else 0, tgh, ids, st))
+        return np.array(ids, dtype=np.uint32), list(tgh), tuple(st)
 
     def whirl_tables(self, tables):
         h = C.c_int(-1)

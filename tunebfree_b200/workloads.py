@@ -103,13 +103,12 @@ _SWEEP = None
 
 def scala_sweep():
     """Config 4's tunings: (names, [degrees as ratios]) of every scale of the reference's Scala
-    archive that both sides accept (tests/golden/scala_sweep.npz, made by
+    archive that both sides accept (tunebfree_b200/data/scala_sweep.npz, made by
     tests/golden/make_scala_sweep.py; 128 note frequencies = tables.freqs_from_ratios(degrees))."""
     global _SWEEP
     if _SWEEP is None:
         import os
-        z = np.load(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
-                                 "tests", "golden", "scala_sweep.npz"))
+        z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "scala_sweep.npz"))
         ok = np.flatnonzero(z["status"] == 0)
         off, deg = z["deg_off"], z["degrees"]
         _SWEEP = ([str(z["names"][i]) for i in ok], [deg[off[i]:off[i + 1]].copy() for i in ok],
