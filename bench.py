@@ -304,7 +304,15 @@ def run_gpu_arm(a):
 
     # CPU baseline first (forks worker processes: must happen before any CUDA context)
     cpu_baseline = None
-    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+    # multi-rank runs: rank 0 measures the CPU baseline alone on the host cores; the other ranks
+    # wait at a file gate (no process group yet: the workers are forked before any CUDA / NCCL
+    # state exists) and only then start their own oracle workers for the sampled parity check
+    gate = os.path.join("/tmp", "tbf_bench_gate_%d_%s" % (os.getppid(), os.environ.get("MASTER_PORT", "0")))
+    if world > 1 and rank != 0 and not a.no_cpu_baseline:
+        t_gate = time.time()
+        while not os.path.exists(gate) and time.time() - t_gate < 900:
+            time.sleep(0.2)
+    if rank == 0 and not a.no_cpu_baseline:
         cores = os.cpu_count() or 1
         n_frag_cpu = int(round(a.seconds * 375))
         per_core = cpu_sample_plan(a.config, a.seconds, a.cpu_sample_seconds, cores)
@@ -315,6 +323,8 @@ def run_gpu_arm(a):
                                   "the reference engine compiled strict IEEE -O2, one process per core"
                                   % (cores * per_core, a.seconds, per_core),
                         "n_act": cpu_n_act}
+        if world > 1:
+            open(gate, "w").close()
 
     from tunebfree_b200 import cabi, engine, tables, workloads
     n_inst = a.instances or DEFAULT_INSTANCES[a.config]
@@ -537,7 +547,7 @@ def run_gpu_arm(a):
         # the link's own ceiling: a plain contiguous 1 GiB device -> page-locked host copy on
         # every rank at once (outside the timed region)
         barrier()
-        link_gbs = ctx.measure_d2h(1 << 30, 3)
+        link_gbs = ctx.measure_d2h(1 << 30, 8)  # ~8 GiB per rank: long enough to overlap on every rank
         barrier()
         if slices == 1:
             parts = [(n_frag, events)]
@@ -581,7 +591,7 @@ def run_gpu_arm(a):
         link_min = -max_over_ranks(-link_gbs)
         e2e["link_peak_gbs"] = link_min
         e2e["link_peak_what"] = ("slowest rank's plain contiguous 1 GiB device -> page-locked host "
-                                 "cudaMemcpyAsync, all %d rank(s) copying at once" % world)
+                                 "cudaMemcpyAsync, mean of 8 passes, all %d rank(s) copying at once" % world)
         e2e["audio_gbs_per_gpu"] = e2e["d2h_bytes_per_step"] * a.steps / dt / 1e9
         e2e["frac_of_link"] = e2e["audio_gbs_per_gpu"] / link_min if link_min > 0 else None
         if parity is not None:
@@ -683,6 +693,9 @@ def run_gpu_arm(a):
         print(json.dumps(line), flush=True)
     ctx.close()
     if dist is not None:
+        dist.barrier()
+        if rank == 0 and os.path.exists(gate):
+            os.remove(gate)
         dist.destroy_process_group()
 
 

@@ -320,7 +320,7 @@ uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx);
 #define TBF_HOST_WRITE_COMBINED 0x1
 void *tbf_gpu_host_alloc2(tbf_ctx *ctx, size_t bytes, unsigned flags);
 /* device -> host link ceiling of this context's GPU: plain 1-D page-locked cudaMemcpyAsync of
- * `bytes` (repeated `reps` times, the best is reported), GB/s                                   */
+ * `bytes`, `reps` timed passes after one untimed, the mean rate in GB/s                        */
 int tbf_gpu_measure_d2h(tbf_ctx *ctx, size_t bytes, int reps, double *gbs);
 /* CUDA-event stopwatch on the library's stream                                 */
 int tbf_gpu_timer_start(tbf_ctx *ctx);
