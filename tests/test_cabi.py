@@ -84,9 +84,15 @@ def _sass():
 
 def _check_sass():
     sass = _sass()
-    # no packed fused multiply-add anywhere, the packed multiply is there
-    assert "FFMA2" not in sass
-    assert "FMUL2" in sass
+    # The packed sums are FFMA2 used as an ADDER (product * 1.0 + sum, the 1.0 a run-time value:
+    # tbf_kernels.cu add2_via_fma), each fed by its own packed multiply.  Had ptxas contracted a
+    # multiply into the add (one rounding instead of two) the FMUL2 would be gone: there must be
+    # one FMUL2 per FFMA2, and no packed add at all (a packed add fed by a packed multiply is what
+    # ptxas contracts even under --fmad=false)
+    n_mul = len(re.findall(r"\bFMUL2\b", sass))
+    n_fma = len(re.findall(r"\bFFMA2\b", sass))
+    assert n_mul > 0 and n_fma > 0 and n_mul >= n_fma, (n_mul, n_fma)
+    assert not re.search(r"\bFADD2\b", sass)
     # scalar FFMA / DFMA only inside the division sequences ptxas expands (their multiplicand or
     # addend is RZ or the constant 1): none with three live register operands in a float kernel
     for line in sass.splitlines():
@@ -98,11 +104,12 @@ def _check_sass():
 
 
 def test_no_contracted_packed_fma_in_kernels():
-    """The tone generator's sum multiplies packed FP32 pairs (FMUL2) and adds with scalar FADDs.
-    ptxas contracts a mul.f32x2 feeding an add.f32x2 into FFMA2 even with --fmad=false, which
-    would change the reference's rounding; the kernels are written so that it cannot
-    (tbf_kernels.cu, acc_plain) and this test pins it: no FFMA2 and no scalar FFMA of three live
-    operands anywhere in the library's SASS, the packed multiply is there, and so are the TMA
+    """The tone generator's sum multiplies packed FP32 pairs (FMUL2) and adds them with FFMA2 used
+    as an adder (x * 1.0 + sum: exact product, one rounding = add.rn).  ptxas contracts a
+    mul.f32x2 feeding an add.f32x2 into one FFMA2 even with --fmad=false, which would change the
+    reference's rounding; the kernels are written so that it cannot (tbf_kernels.cu,
+    add2_via_fma) and this test pins it: one FMUL2 per FFMA2, no FADD2, no scalar FFMA of three
+    live operands anywhere in the library's SASS, and the TMA
     bulk copies (UBLKCP) with their mbarriers (SYNCS) that stage the wave tables.  Fails -- does
     not skip -- when the library or cuobjdump is missing."""
     _check_sass()

@@ -1500,6 +1500,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
      * fragments are summed one at a time instead of in pairs */
     base_p.flags = d->flags | (getenv("TBF_NO_FAST_PASS") ? 0x100u : 0u) | (getenv("TBF_NO_PAIRS") ? 0x200u : 0u);
     base_p.pitch = pitch;
+    base_p.one = 1.0f;
     ctx->launches = 0;
     const int ring = ctx->prepared_ring;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -2112,6 +2113,7 @@ int tbf_gpu_render_small_noalloc(tbf_ctx *ctx, const tbf_batch_desc *d)
     p.frag_base = 0;
     p.ctl = reinterpret_cast<FragCtl *>(base + NA_OFF_CTL);
     p.pitch = pitch;
+    p.one = 1.0f;
     p.u = f32;
     p.php = f32 + (size_t)n * pitch;
     if (whirl) {

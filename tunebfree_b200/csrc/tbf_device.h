@@ -215,6 +215,7 @@ struct RenderParams {
     double *hang, *dang;       /* R -> W: rotor angles                                  */
     float *line[4];            /* W -> D: delay-line reads HL HR DL DR                  */
     uint64_t pitch;            /* elements per slot row of every stream                 */
+    float one;                 /* 1.0f, as a run-time value (tbf_kernels.cu: add2_via_fma) */
 };
 
 /* what a fresh instance starts from (tbf_init_instances_kernel); everything else is zero */

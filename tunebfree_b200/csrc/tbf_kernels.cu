@@ -691,9 +691,22 @@ __device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
     asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
 }
 
-/* running sums of the three buffers (swell, scanner, percussion) over the lane's four samples */
+/* a + b as a packed instruction that ptxas cannot fuse with the multiply that made `a`:
+ * fma(a, one, b) with `one` = 1.0f in both halves, a value the compiler cannot see (it arrives in
+ * RenderParams).  a * 1.0 is exact, so the result is the correctly rounded sum -- bit for bit
+ * add.rn(a, b), signed zeros included.  (A plain add.rn.f32x2 fed by mul.rn.f32x2 is contracted
+ * into FFMA2 -- one rounding instead of the reference's two -- even under --fmad=false.) */
+__device__ __forceinline__ f32x2 add2_via_fma(f32x2 a, f32x2 one2, f32x2 b)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(one2), "l"(b));
+    return r;
+}
+
+/* running sums of the three buffers (swell, scanner, percussion) over the lane's four samples,
+ * as packed pairs: [0] = samples 4*lane, 4*lane+1; [1] = 4*lane+2, 4*lane+3 */
 struct CoreAcc {
-    float s[4], v[4], p[4];
+    f32x2 s[2], v[2], p[2];
 };
 
 /* The first instruction of a fragment copies, the rest add (src/tonegen.cpp:3640-3680):
@@ -701,34 +714,44 @@ struct CoreAcc {
  * (-0) + (-0) = -0). */
 __device__ __forceinline__ void core_begin(CoreAcc &a)
 {
+    const f32x2 nz = 0x8000000080000000ull;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
-        a.s[j] = a.v[j] = a.p[j] = -0.0f;
+    for (int h = 0; h < 2; ++h)
+        a.s[h] = a.v[h] = a.p[h] = nz;
 }
 
-/* sum += x * g for the lane's four samples x (two packed pairs) */
-__device__ __forceinline__ void acc_plain(float (&sum)[4], const ulonglong2 x, const f32x2 g2)
+/* sum += x * g for the lane's four samples x (two packed pairs): 2 FMUL2 + 2 FFMA2 */
+__device__ __forceinline__ void acc_plain(f32x2 (&sum)[2], const ulonglong2 x, const f32x2 g2, const f32x2 one2)
 {
-    float p0, p1, p2, p3;
-    unpack2(mul2(x.x, g2), p0, p1);
-    unpack2(mul2(x.y, g2), p2, p3);
-    sum[0] = __fadd_rn(sum[0], p0);
-    sum[1] = __fadd_rn(sum[1], p1);
-    sum[2] = __fadd_rn(sum[2], p2);
-    sum[3] = __fadd_rn(sum[3], p3);
+    sum[0] = add2_via_fma(mul2(x.x, g2), one2, sum[0]);
+    sum[1] = add2_via_fma(mul2(x.y, g2), one2, sum[1]);
+}
+
+/* the same with a gain per sample (key click), scalar: the rare path */
+__device__ __forceinline__ void acc_env(f32x2 (&sum)[2], const float (&xs)[4], const float (&ev)[4], float g, float d)
+{
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float lo, hi;
+        unpack2(sum[h], lo, hi);
+        lo = __fadd_rn(lo, __fmul_rn(xs[2 * h], __fadd_rn(g, __fmul_rn(ev[2 * h], d))));
+        hi = __fadd_rn(hi, __fmul_rn(xs[2 * h + 1], __fadd_rn(g, __fmul_rn(ev[2 * h + 1], d))));
+        sum[h] = pack2(lo, hi);
+    }
 }
 
 /* products of one record with the lane's staged samples x, added in list order.  ENV = false:
  * the caller knows that every record plays with constant gains (no key click in flight). */
 template <bool ENV>
 __device__ __forceinline__ void wheel_accumulate(const DevTonegenTables *tg, TWarp &sm, const float4 g,
-                                                 int i_tile, int lane, const ulonglong2 x, CoreAcc &a)
+                                                 int i_tile, int lane, const ulonglong2 x, CoreAcc &a,
+                                                 const f32x2 one2)
 {
     const int env = ENV ? __float_as_int(g.w) : -1;
     if (!ENV || env < 0) {
-        acc_plain(a.s, x, pack2(g.x, g.x));
-        acc_plain(a.v, x, pack2(g.y, g.y));
-        acc_plain(a.p, x, pack2(g.z, g.z));
+        acc_plain(a.s, x, pack2(g.x, g.x), one2);
+        acc_plain(a.v, x, pack2(g.y, g.y), one2);
+        acc_plain(a.p, x, pack2(g.z, g.z), one2);
     } else { /* key click: gain = g + env[n] * (next - g), per sample */
         const float4 d = rec_d(sm)[i_tile]; /* only the pass's tiles (<= REC_TILE records) carry envelopes */
         const float *ep = tg->env[env] + 4 * lane;
@@ -736,12 +759,9 @@ __device__ __forceinline__ void wheel_accumulate(const DevTonegenTables *tg, TWa
         float xs[4];
         unpack2(x.x, xs[0], xs[1]);
         unpack2(x.y, xs[2], xs[3]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            a.s[j] = __fadd_rn(a.s[j], __fmul_rn(xs[j], __fadd_rn(g.x, __fmul_rn(ev[j], d.x))));
-            a.v[j] = __fadd_rn(a.v[j], __fmul_rn(xs[j], __fadd_rn(g.y, __fmul_rn(ev[j], d.y))));
-            a.p[j] = __fadd_rn(a.p[j], __fmul_rn(xs[j], __fadd_rn(g.z, __fmul_rn(ev[j], d.z))));
-        }
+        acc_env(a.s, xs, ev, g.x, d.x);
+        acc_env(a.v, xs, ev, g.y, d.y);
+        acc_env(a.p, xs, ev, g.z, d.z);
     }
 }
 
@@ -749,7 +769,7 @@ __device__ __forceinline__ void wheel_accumulate(const DevTonegenTables *tg, TWa
  * hand the slot back (the wheel T_SLOTS further is requested into it), accumulate */
 template <int NF, bool ENV, int SLOT>
 __device__ __forceinline__ void core_step(const DevTonegenTables *tg, TWarp &sm, int lane, int rec, int i_tile,
-                                          bool more, CoreAcc (&acc)[NF], uint32_t &parity)
+                                          bool more, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
 {
     mbar_wait(smem_u32(&sm.mbar[SLOT]), parity);
     parity ^= 1u;
@@ -763,7 +783,7 @@ __device__ __forceinline__ void core_step(const DevTonegenTables *tg, TWarp &sm,
         wave_request<NF>(sm, rec + T_SLOTS, SLOT);
 #pragma unroll
     for (int f = 0; f < NF; ++f)
-        wheel_accumulate<ENV>(tg, sm, g, i_tile, lane, x[f], acc[f]);
+        wheel_accumulate<ENV>(tg, sm, g, i_tile, lane, x[f], acc[f], one2);
 }
 
 /* records rec0 .. rec0+cnt-1 in order (src/tonegen.cpp:3607-3687), T_SLOTS = 2 wheels in flight
@@ -772,7 +792,8 @@ __device__ __forceinline__ void core_step(const DevTonegenTables *tg, TWarp &sm,
  * laid out.  par0 / par1: the parity each slot's barrier shows when its next fill has landed. */
 template <int NF, bool ENV>
 __device__ __forceinline__ void core_tile_tma(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
-                                              int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1)
+                                              int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1,
+                                              const f32x2 one2)
 {
     static_assert(T_SLOTS == 2, "core_tile is written for two staging slots");
     if (cnt > 0 && elect_one()) {
@@ -783,11 +804,11 @@ __device__ __forceinline__ void core_tile_tma(const DevTonegenTables *tg, TWarp 
     int i = 0;
 #pragma unroll 1
     for (; i + 1 < cnt; i += 2) {
-        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, i + 2 < cnt, acc, par0);
-        core_step<NF, ENV, 1>(tg, sm, lane, rec0 + i + 1, i + 1, i + 3 < cnt, acc, par1);
+        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, i + 2 < cnt, acc, par0, one2);
+        core_step<NF, ENV, 1>(tg, sm, lane, rec0 + i + 1, i + 1, i + 3 < cnt, acc, par1, one2);
     }
     if (i < cnt)
-        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, false, acc, par0);
+        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, false, acc, par0, one2);
 }
 
 /* a lane's four samples (two packed pairs) straight from the wave store, past L1 */
@@ -806,7 +827,7 @@ __device__ __forceinline__ ulonglong2 ld_wave(const float4 *p)
  * comparison variant (TBF_T_LOADS=ldg); tbf_launch_stage_t picks. */
 template <int NF, bool ENV>
 __device__ __forceinline__ void core_tile_ldg(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
-                                              int cnt, CoreAcc (&acc)[NF])
+                                              int cnt, CoreAcc (&acc)[NF], const f32x2 one2)
 {
     if (cnt <= 0)
         return;
@@ -834,18 +855,19 @@ __device__ __forceinline__ void core_tile_ldg(const DevTonegenTables *tg, TWarp 
         }
 #pragma unroll
         for (int f = 0; f < NF; ++f)
-            wheel_accumulate<ENV>(tg, sm, g, i, lane, x[f], acc[f]);
+            wheel_accumulate<ENV>(tg, sm, g, i, lane, x[f], acc[f], one2);
     }
 }
 
 template <int NF, bool ENV, bool TMA>
 __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
-                                          int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1)
+                                          int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1,
+                                          const f32x2 one2)
 {
     if (TMA)
-        core_tile_tma<NF, ENV>(tg, sm, lane, rec0, cnt, acc, par0, par1);
+        core_tile_tma<NF, ENV>(tg, sm, lane, rec0, cnt, acc, par0, par1, one2);
     else
-        core_tile_ldg<NF, ENV>(tg, sm, lane, rec0, cnt, acc);
+        core_tile_ldg<NF, ENV>(tg, sm, lane, rec0, cnt, acc, one2);
 }
 
 /* from lane = 4 consecutive samples to lane = sample of a 32-sample block (s[k] = sample
@@ -855,9 +877,9 @@ __device__ __forceinline__ void core_end(const CoreAcc &a, TWarp &sm, int n_act,
                                          float (&v)[4], float (&p)[4])
 {
     float4 *st = sm.wstage[0][0]; /* 3 x 512 B of the 2 KB */
-    st[lane] = make_float4(a.s[0], a.s[1], a.s[2], a.s[3]);
-    st[32 + lane] = make_float4(a.v[0], a.v[1], a.v[2], a.v[3]);
-    st[64 + lane] = make_float4(a.p[0], a.p[1], a.p[2], a.p[3]);
+    *reinterpret_cast<ulonglong2 *>(&st[lane]) = make_ulonglong2(a.s[0], a.s[1]);
+    *reinterpret_cast<ulonglong2 *>(&st[32 + lane]) = make_ulonglong2(a.v[0], a.v[1]);
+    *reinterpret_cast<ulonglong2 *>(&st[64 + lane]) = make_ulonglong2(a.p[0], a.p[1]);
     __syncwarp();
     const float *fs = reinterpret_cast<const float *>(st);
 #pragma unroll
@@ -1053,6 +1075,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
     }
     __syncwarp();
     uint32_t par0 = 0u, par1 = 0u; /* parity of each staging slot's next completed fill */
+    const f32x2 one2 = pack2(p.one, p.one); /* 1.0f the compiler cannot see: add2_via_fma() */
     const DevTonegenTables *tg = p.tg + sc.tgTables;
     if (lane == 0)
         sm.wave4 = tg->wave4;
@@ -1147,7 +1170,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
             core_begin(acc[1]);
             fast_pass<2>(tg, sm, lane, n_act, ins_a, ins_b);
             __syncwarp();
-            core_tile<2, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1);
+            core_tile<2, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1, one2);
             __syncwarp();
             quiet_stats(sc, lane, n_act, ins_a);
             quiet_stats(sc, lane, n_act, ins_b);
@@ -1171,7 +1194,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
 #endif
                 fast_pass<1>(tg, sm, lane, n_act, my_ins, unused);
                 __syncwarp();
-                core_tile<1, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1);
+                core_tile<1, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1, one2);
                 __syncwarp();
                 quiet_stats(sc, lane, n_act, my_ins);
             } else {
@@ -1185,7 +1208,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
                     active_list_tile(st, tg, sm, lane, base, cnt, rec0, my_ins);
                     fence_async_smem(); /* rec_d shares the staging slots' B halves */
                     __syncwarp();
-                    core_tile<1, true, TMA>(tg, sm, lane, rec0, cnt, acc, par0, par1);
+                    core_tile<1, true, TMA>(tg, sm, lane, rec0, cnt, acc, par0, par1, one2);
                     __syncwarp();
                 }
                 active_list_finish(st, sm, lane, n_act, my_ins);
