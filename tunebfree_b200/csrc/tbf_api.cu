@@ -966,6 +966,32 @@ int tbf_gpu_whirl_tables_create(tbf_ctx *ctx, const tbf_whirl_tables *w, int *ha
                     d.drum_phase[i] < (1 << 21);
         d.small_index = small ? 1 : 0;
         d.fast_max_angle = 1.0;
+        /* Can a tap's destination slot ever fail the parallel scatter's per-block checks (slots
+         * monotone in the sample index, at most two samples per slot, inside the window)?  Not if
+         * its delay changes by less than half a sample per sample.  The delay is piecewise linear
+         * in the rotor angle (16384 steps per turn), the angle moves |incr| * 16384 steps per
+         * sample, and |incr| never exceeds the largest speed the set knows: the ramp
+         * incr += (1 - l)(target - incr), 0 < 1 - l < 1, approaches its target from one side
+         * (src/whirl.cpp:1255-1257), the brake moves at most 60 / 100 rpm (:1333-1374).  The float
+         * rounding of the table index (1/128 of a step at most) rides on the step count. */
+        {
+            double vmax[2] = {fabs(w->init_horn_incr), fabs(w->init_drum_incr)};
+            for (int i = 0; i < 9; ++i) {
+                vmax[0] = std::max(vmax[0], fabs(w->rev_horn_target[i]));
+                vmax[1] = std::max(vmax[1], fabs(w->rev_drum_target[i]));
+            }
+            vmax[0] = std::max(vmax[0], 60.0 / (60.0 * w->sample_rate));
+            vmax[1] = std::max(vmax[1], 100.0 / (60.0 * w->sample_rate));
+            bool cert = ok;
+            for (int p = 0; p < 12 && cert; ++p) {
+                double slope = 0.0;
+                for (size_t i = 0; i < N; ++i)
+                    slope = std::max(slope, fabs((double)disp[p][(i + 1) & (N - 1)] - (double)disp[p][i]));
+                const double steps = vmax[p < 6 ? 0 : 1] * (double)N + 0.02;
+                cert = slope * steps <= 0.49 && vmax[p < 6 ? 0 : 1] < 0.25;
+            }
+            d.taps_certified = cert ? 1 : 0;
+        }
         s.ring_size = d.ring_size;
         s.gather_ok = d.gather_ok;
         s.window = d.window;

@@ -176,6 +176,11 @@ struct DevWhirlTables {
                                [+0, 2^22): stage W reads floor / round / the integer conversions
                                off the float's mantissa instead of converting (tbf_kernels.cu)  */
     double fast_max_angle;  /* 1.0: horn angle + microphone offset stays below 2^7            */
+    int32_t taps_certified; /* 1: the host has bounded every tap's delay change per sample by
+                               0.49 for every rotor speed this set can reach (tbf_api.cu), so
+                               the per-block slot checks of the ordered scatter cannot fire and
+                               stage W skips them                                               */
+    int32_t pad_cert_;
     int32_t tap_order[4][3];/* per line HL HR DL DR: tap ids (0..11), farthest delay first */
     int32_t tap_dmin[12], tap_dmax[12];
 };

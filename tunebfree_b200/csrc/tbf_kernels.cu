@@ -1858,7 +1858,7 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_
 /* the six taps of one half for one 32-sample block: geometry, table reads, (horn) FIRs, the
  * fractional split.  Written in groups of three taps -- index math and loads first, consumers
  * after -- so that the reads of a group are in flight together. */
-template <bool DRUM, bool FAST>
+template <bool DRUM, bool FAST, bool CERT>
 __device__ __forceinline__ void block_taps(const WWarp &sm, const int i, const double ang, const uint32_t outpos,
                                            const uint32_t outpos_blk, const uint32_t window, const int lane,
                                            uint32_t (&tn)[6], uint32_t (&tn1)[6], uint32_t (&tn2)[6],
@@ -1915,7 +1915,8 @@ __device__ __forceinline__ void block_taps(const WWarp &sm, const int i, const d
             tb[j] = qq;
             tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
             tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
-            bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
+            if (!CERT) /* CERT: the host bounded the slot motion (DevWhirlTables::taps_certified) */
+                bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
         }
     }
 }
@@ -1974,6 +1975,7 @@ __device__ __forceinline__ void stage_w_half(const RenderParams &p, const uint32
     }
     const bool gather_ok = wh->gather_ok != 0;
     const bool small_index = wh->small_index != 0;
+    const bool certified = wh->taps_certified != 0 && wh->gather_ok != 0;
     const double max_ang = DRUM ? 1.0 : wh->fast_max_angle; /* rotor angles below it keep h1 < 2^22 */
     const uint32_t window = (uint32_t)wh->window;
     int fell_back = 0;
@@ -2028,10 +2030,12 @@ __device__ __forceinline__ void stage_w_half(const RenderParams &p, const uint32
             int bad = gather_ok ? 0 : 1;
             /* one warp-uniform branch per block, not per tap: inside a variant the six taps are
              * straight-line code, so their table reads overlap */
-            if (fast)
-                block_taps<DRUM, true>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+            if (fast && certified)
+                block_taps<DRUM, true, true>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+            else if (fast)
+                block_taps<DRUM, true, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
             else
-                block_taps<DRUM, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+                block_taps<DRUM, false, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
             float o_l, o_r;
             group_scatter_read(&sm.tap[0], ring, ring + ring_size, rmask, lane, outpos_blk, bad,
                                gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, o_l, o_r);
