@@ -132,7 +132,9 @@ __device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_
  * and one record per wheel suffices. */
 #define REC_TILE 32    /* active-list entries turned into records and summed at a time */
 #define REC_CAP 128   /* longest active list whose records persist across fragments   */
-#define T_SLOTS 2      /* wave staging slots per warp = wheels in flight (bulk copies)  */
+#define T_MAX_SLOTS 8  /* wave staging slots per warp = wheels in flight (bulk copies): 2 when the
+                          SMs are full (6 KB per warp, 28 warps per SM), 6 for small batches, where a
+                          warp's own copies are all that hides the copy latency                    */
 struct TWarp {
     TgScalars sc;
     /* core-program records.  Lists of up to REC_CAP wheels keep their records here from one
@@ -146,9 +148,10 @@ struct TWarp {
     /* wave samples in flight: one 512-byte bulk copy (TMA) per wheel and fragment lands here,
      * [slot][fragment A / B][lane] = samples 4*lane .. 4*lane+3.  The single-fragment passes use
      * the A halves only; the B halves then hold the envelope deltas of the current tile
-     * (rec_d) and, once the last tile has been summed, the removal list (removed_wheel) */
-    float4 wstage[T_SLOTS][2][32];
-    unsigned long long mbar[T_SLOTS]; /* "slot filled" barriers of the bulk copies              */
+     * (rec_d) and, once the last tile has been summed, the removal list (removed_wheel).
+     * The slots lie BEHIND this struct in the warp's shared memory (wslot()): their number is a
+     * launch-time choice */
+    unsigned long long mbar[T_MAX_SLOTS]; /* "slot filled" barriers of the bulk copies          */
     const float *wave4;               /* the organ's wave store (read by the lane that requests) */
     float vring[TBF_VRING];
     uint8_t removed[TBF_NOF_WHEELS + 4];
@@ -158,15 +161,21 @@ struct TWarp {
      * loop, dropped the WARPSYNC before VOTE.ANY, and lanes got different answers */
     int any_removed, any_env;
 };
-static_assert(sizeof(TWarp) <= 7040, "stage T: 32 warps per SM need <= 7040 B of shared memory per warp");
+static_assert(sizeof(TWarp) % 16 == 0, "the staging slots behind the struct are float4-aligned");
+static_assert(sizeof(TWarp) + 2 * 1024 <= 7040, "stage T: 32 warps per SM need <= 7040 B of shared memory per warp");
 static_assert(REC_TILE * sizeof(float4) <= sizeof(float4) * 32 &&
               TBF_NOF_WHEELS * sizeof(uint16_t) <= sizeof(float4) * 32, "slow-path arrays fit a B half");
 
 /* envelope deltas ds dv dp of the current tile's records (slow path, env >= 0 only) */
-__device__ __forceinline__ float4 *rec_d(TWarp &sm) { return sm.wstage[0][1]; }
+/* staging slot `slot`, fragment half `f`: 32 float4 */
+__device__ __forceinline__ float4 *wslot(TWarp &sm, int slot, int f)
+{
+    return reinterpret_cast<float4 *>(&sm + 1) + (slot * 2 + f) * 32;
+}
+__device__ __forceinline__ float4 *rec_d(TWarp &sm) { return wslot(sm, 0, 1); }
 __device__ __forceinline__ uint16_t *removed_wheel(TWarp &sm)
 {
-    return reinterpret_cast<uint16_t *>(sm.wstage[1][1]);
+    return reinterpret_cast<uint16_t *>(wslot(sm, 1, 1));
 }
 
 /* -- key events, one lane (src/tonegen.cpp:3096-3166 + the queue drain :3257-3327): the
@@ -663,7 +672,7 @@ __device__ __forceinline__ void wave_request(TWarp &sm, int rec, int slot)
     const float *wave4 = sm.wave4;
     const uint32_t bar = smem_u32(&sm.mbar[slot]);
     mbar_expect_tx(bar, NF * 512u);
-    bulk_g2s(smem_u32(sm.wstage[slot][0]), wave4 + (size_t)q * 4u, NF * 512u, bar);
+    bulk_g2s(smem_u32(wslot(sm, slot, 0)), wave4 + (size_t)q * 4u, NF * 512u, bar);
 }
 
 /* Packed pairs of floats for Blackwell's two-wide FP32 multiply (FMUL2): each half is an IEEE
@@ -766,108 +775,136 @@ __device__ __forceinline__ void wheel_accumulate(const DevTonegenTables *tg, TWa
 }
 
 /* one wheel: wait for its samples in staging slot SLOT, read them and the record's gains,
- * hand the slot back (the wheel T_SLOTS further is requested into it), accumulate */
-template <int NF, bool ENV, int SLOT>
+ * hand the slot back (the wheel SLOTS further is requested into it), accumulate */
+template <int NF, bool ENV, int SLOTS, int SLOT>
 __device__ __forceinline__ void core_step(const DevTonegenTables *tg, TWarp &sm, int lane, int rec, int i_tile,
                                           bool more, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
 {
-    mbar_wait(smem_u32(&sm.mbar[SLOT]), parity);
-    parity ^= 1u;
+    mbar_wait(smem_u32(&sm.mbar[SLOT]), (parity >> SLOT) & 1u);
+    parity ^= 1u << SLOT;
     ulonglong2 x[NF];
 #pragma unroll
     for (int f = 0; f < NF; ++f)
-        x[f] = *reinterpret_cast<const ulonglong2 *>(&sm.wstage[SLOT][f][lane]);
+        x[f] = *reinterpret_cast<const ulonglong2 *>(wslot(sm, SLOT, f) + lane);
     const float4 g = sm.recG[rec];
     __syncwarp(); /* every lane has read the slot: it may be filled again */
     if (more && elect_one())
-        wave_request<NF>(sm, rec + T_SLOTS, SLOT);
+        wave_request<NF>(sm, rec + SLOTS, SLOT);
 #pragma unroll
     for (int f = 0; f < NF; ++f)
         wheel_accumulate<ENV>(tg, sm, g, i_tile, lane, x[f], acc[f], one2);
 }
 
-/* records rec0 .. rec0+cnt-1 in order (src/tonegen.cpp:3607-3687), T_SLOTS = 2 wheels in flight
- * and two wheels per trip, so that slot numbers are compile-time constants; NF = 2 sums the same
+/* compile-time loop over the staging slots */
+template <int NF, bool ENV, int SLOTS, int J>
+struct CoreSteps {
+    /* a full trip: wheels i .. i + SLOTS - 1, one per slot */
+    static __device__ __forceinline__ void trip(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0, int i,
+                                                int cnt, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
+    {
+        core_step<NF, ENV, SLOTS, J>(tg, sm, lane, rec0 + i + J, i + J, i + J + SLOTS < cnt, acc, parity, one2);
+        CoreSteps<NF, ENV, SLOTS, J + 1>::trip(tg, sm, lane, rec0, i, cnt, acc, parity, one2);
+    }
+    /* the last, partial trip: nothing is requested any more */
+    static __device__ __forceinline__ void tail(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0, int i,
+                                                int cnt, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
+    {
+        if (i + J < cnt) {
+            core_step<NF, ENV, SLOTS, J>(tg, sm, lane, rec0 + i + J, i + J, false, acc, parity, one2);
+            CoreSteps<NF, ENV, SLOTS, J + 1>::tail(tg, sm, lane, rec0, i, cnt, acc, parity, one2);
+        }
+    }
+};
+template <int NF, bool ENV, int SLOTS>
+struct CoreSteps<NF, ENV, SLOTS, SLOTS> {
+    static __device__ __forceinline__ void trip(const DevTonegenTables *, TWarp &, int, int, int, int,
+                                                CoreAcc (&)[NF], uint32_t &, const f32x2)
+    {
+    }
+    static __device__ __forceinline__ void tail(const DevTonegenTables *, TWarp &, int, int, int, int,
+                                                CoreAcc (&)[NF], uint32_t &, const f32x2)
+    {
+    }
+};
+
+/* records rec0 .. rec0+cnt-1 in order (src/tonegen.cpp:3607-3687), SLOTS wheels in flight and
+ * SLOTS wheels per trip, so that slot numbers are compile-time constants; NF = 2 sums the same
  * records into two consecutive fragments (acc[0], acc[1]) from the 256-sample read fast_pass<2>
- * laid out.  par0 / par1: the parity each slot's barrier shows when its next fill has landed. */
-template <int NF, bool ENV>
+ * laid out.  parity: bit s = the parity slot s's barrier shows when its next fill has landed. */
+template <int NF, bool ENV, int SLOTS>
 __device__ __forceinline__ void core_tile_tma(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
-                                              int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1,
-                                              const f32x2 one2)
+                                              int cnt, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
 {
-    static_assert(T_SLOTS == 2, "core_tile is written for two staging slots");
     if (cnt > 0 && elect_one()) {
-        wave_request<NF>(sm, rec0, 0);
-        if (cnt > 1)
-            wave_request<NF>(sm, rec0 + 1, 1);
+#pragma unroll
+        for (int j = 0; j < SLOTS; ++j)
+            if (j < cnt)
+                wave_request<NF>(sm, rec0 + j, j);
     }
     int i = 0;
 #pragma unroll 1
-    for (; i + 1 < cnt; i += 2) {
-        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, i + 2 < cnt, acc, par0, one2);
-        core_step<NF, ENV, 1>(tg, sm, lane, rec0 + i + 1, i + 1, i + 3 < cnt, acc, par1, one2);
-    }
-    if (i < cnt)
-        core_step<NF, ENV, 0>(tg, sm, lane, rec0 + i, i, false, acc, par0, one2);
+    for (; i + SLOTS <= cnt; i += SLOTS)
+        CoreSteps<NF, ENV, SLOTS, 0>::trip(tg, sm, lane, rec0, i, cnt, acc, parity, one2);
+    CoreSteps<NF, ENV, SLOTS, 0>::tail(tg, sm, lane, rec0, i, cnt, acc, parity, one2);
 }
 
-/* a lane's four samples (two packed pairs) straight from the wave store, past L1 */
-__device__ __forceinline__ ulonglong2 ld_wave(const float4 *p)
-{
-    ulonglong2 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0, %1}, [%2];" : "=l"(r.x), "=l"(r.y) : "l"(p));
-    return r;
-}
-
-/* the same sum with every lane loading its own four samples of a wheel into registers, one
- * wheel ahead of their use (LDG.128, coalesced: the warp reads the wheel's 512 contiguous
- * bytes): no staging, no barrier and a quarter fewer instructions per wheel than the bulk-copy
- * variant -- and 1.6 times SLOWER: one wheel of load latency per trip is exposed where the bulk
- * copies run two wheels ahead without holding registers (profiles/r02_kernels.md).  Kept as the
- * comparison variant (TBF_T_LOADS=ldg); tbf_launch_stage_t picks. */
-template <int NF, bool ENV>
-__device__ __forceinline__ void core_tile_ldg(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
+/* The same sum with the Ampere-style pipeline: every lane copies its own 16 bytes of a wheel (per
+ * fragment) into the staging slot with cp.async (LDGSTS), STAGES wheels ahead, and reads back
+ * only what it requested itself -- no barrier object, no elected lane, a third fewer instructions
+ * per wheel than the bulk-copy variant and a shorter dependent chain per step, at the price of 32
+ * requests through the LSU per wheel instead of one through the TMA unit.  It is the variant for
+ * SMALL batches, where each scheduler holds one or two warps and the step latency of a warp is
+ * what bounds the kernel (profiles/r02_kernels.md); tbf_launch_stage_t picks. */
+template <int NF, bool ENV, int STAGES>
+__device__ __forceinline__ void core_tile_cpa(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
                                               int cnt, CoreAcc (&acc)[NF], const f32x2 one2)
 {
-    if (cnt <= 0)
-        return;
     const float4 *base = reinterpret_cast<const float4 *>(sm.wave4) + lane;
-    ulonglong2 xn[NF];
-    {
-        const float4 *q = base + sm.recQ[rec0];
+    float4 *stage = wslot(sm, 0, 0) + lane; /* slot s, half f: + (2 s + f) * 32 */
 #pragma unroll
-        for (int f = 0; f < NF; ++f)
-            xn[f] = ld_wave(q + 32 * f);
+    for (int j = 0; j < STAGES; ++j) {
+        if (j < cnt) {
+            const float4 *q = base + sm.recQ[rec0 + j];
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                __pipeline_memcpy_async(stage + (2 * j + f) * 32, q + 32 * f, 16);
+        }
+        __pipeline_commit();
     }
+    int s = 0;
 #pragma unroll 1
     for (int i = 0; i < cnt; ++i) {
+        __pipeline_wait_prior(STAGES - 1); /* this lane's copies of wheel i have landed */
         ulonglong2 x[NF];
 #pragma unroll
         for (int f = 0; f < NF; ++f)
-            x[f] = xn[f];
+            x[f] = *reinterpret_cast<const ulonglong2 *>(stage + (2 * s + f) * 32);
         const float4 g = sm.recG[rec0 + i];
-        {
-            /* the last trip re-reads its own record: a load that is valid and never used */
-            const float4 *q = base + sm.recQ[rec0 + min(i + 1, cnt - 1)];
+        if (i + STAGES < cnt) {
+            const float4 *q = base + sm.recQ[rec0 + i + STAGES];
 #pragma unroll
             for (int f = 0; f < NF; ++f)
-                xn[f] = ld_wave(q + 32 * f);
+                __pipeline_memcpy_async(stage + (2 * s + f) * 32, q + 32 * f, 16);
         }
+        __pipeline_commit();
 #pragma unroll
         for (int f = 0; f < NF; ++f)
             wheel_accumulate<ENV>(tg, sm, g, i, lane, x[f], acc[f], one2);
+        s = (s == STAGES - 1) ? 0 : s + 1;
     }
+    __pipeline_wait_prior(0);
 }
 
-template <int NF, bool ENV, bool TMA>
+/* SLOTS > 0: TMA bulk copies through that many staging slots; SLOTS < 0: per-lane cp.async
+ * through -SLOTS slots */
+template <int NF, bool ENV, int SLOTS>
 __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
-                                          int cnt, CoreAcc (&acc)[NF], uint32_t &par0, uint32_t &par1,
-                                          const f32x2 one2)
+                                          int cnt, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
 {
-    if (TMA)
-        core_tile_tma<NF, ENV>(tg, sm, lane, rec0, cnt, acc, par0, par1, one2);
+    if (SLOTS > 0)
+        core_tile_tma<NF, ENV, (SLOTS > 0 ? SLOTS : 2)>(tg, sm, lane, rec0, cnt, acc, parity, one2);
     else
-        core_tile_ldg<NF, ENV>(tg, sm, lane, rec0, cnt, acc, one2);
+        core_tile_cpa<NF, ENV, (SLOTS < 0 ? -SLOTS : 2)>(tg, sm, lane, rec0, cnt, acc, one2);
 }
 
 /* from lane = 4 consecutive samples to lane = sample of a 32-sample block (s[k] = sample
@@ -876,7 +913,7 @@ __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm,
 __device__ __forceinline__ void core_end(const CoreAcc &a, TWarp &sm, int n_act, int lane, float (&s)[4],
                                          float (&v)[4], float (&p)[4])
 {
-    float4 *st = sm.wstage[0][0]; /* 3 x 512 B of the 2 KB */
+    float4 *st = wslot(sm, 0, 0); /* 3 x 512 B of the (at least) 2 KB */
     *reinterpret_cast<ulonglong2 *>(&st[lane]) = make_ulonglong2(a.s[0], a.s[1]);
     *reinterpret_cast<ulonglong2 *>(&st[32 + lane]) = make_ulonglong2(a.v[0], a.v[1]);
     *reinterpret_cast<ulonglong2 *>(&st[64 + lane]) = make_ulonglong2(a.p[0], a.p[1]);
@@ -1050,17 +1087,20 @@ __device__ __forceinline__ void quiet_stats(TgScalars &sc, int lane, int n_act, 
 #ifndef T_MIN_CTAS
 #define T_MIN_CTAS 7
 #endif
-/* TMA: the wheels' samples arrive by bulk copies through shared memory (true) or by per-lane
- * 16-byte loads into registers (false) */
-template <bool TMA>
-__global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const RenderParams p)
+/* SLOTS > 0: the wheels' samples arrive by TMA bulk copies through that many shared-memory staging
+ * slots; SLOTS < 0: by per-lane cp.async through -SLOTS slots */
+template <int SLOTS>
+__global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_MIN_CTAS : 4) tbf_stage_t(const RenderParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t slot = blockIdx.x * T_WARPS + warp;
     if (slot >= p.n_instances)
         return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
-    TWarp &sm = reinterpret_cast<TWarp *>(smem_raw)[warp];
+    constexpr bool TMA = SLOTS > 0;
+    constexpr int N_SLOTS = SLOTS < 0 ? -SLOTS : SLOTS;
+    constexpr size_t per_warp = sizeof(TWarp) + (size_t)N_SLOTS * 1024;
+    TWarp &sm = *reinterpret_cast<TWarp *>(smem_raw + per_warp * warp);
     const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
     InstState *st = p.states + id;
     TgScalars &sc = sm.sc;
@@ -1069,12 +1109,12 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
         reinterpret_cast<uint32_t *>(&sm.sc)[i] = reinterpret_cast<const uint32_t *>(&st->tg)[i];
     if (TMA && lane == 0) {
 #pragma unroll
-        for (int j = 0; j < T_SLOTS; ++j)
+        for (int j = 0; j < SLOTS; ++j)
             mbar_init(smem_u32(&sm.mbar[j]), 1u);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    uint32_t par0 = 0u, par1 = 0u; /* parity of each staging slot's next completed fill */
+    uint32_t parity = 0u; /* bit s: parity of staging slot s's next completed fill */
     const f32x2 one2 = pack2(p.one, p.one); /* 1.0f the compiler cannot see: add2_via_fma() */
     const DevTonegenTables *tg = p.tg + sc.tgTables;
     if (lane == 0)
@@ -1170,7 +1210,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
             core_begin(acc[1]);
             fast_pass<2>(tg, sm, lane, n_act, ins_a, ins_b);
             __syncwarp();
-            core_tile<2, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1, one2);
+            core_tile<2, false, SLOTS>(tg, sm, lane, 0, n_act, acc, parity, one2);
             __syncwarp();
             quiet_stats(sc, lane, n_act, ins_a);
             quiet_stats(sc, lane, n_act, ins_b);
@@ -1194,7 +1234,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
 #endif
                 fast_pass<1>(tg, sm, lane, n_act, my_ins, unused);
                 __syncwarp();
-                core_tile<1, false, TMA>(tg, sm, lane, 0, n_act, acc, par0, par1, one2);
+                core_tile<1, false, SLOTS>(tg, sm, lane, 0, n_act, acc, parity, one2);
                 __syncwarp();
                 quiet_stats(sc, lane, n_act, my_ins);
             } else {
@@ -1208,7 +1248,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, T_MIN_CTAS) tbf_stage_t(const Re
                     active_list_tile(st, tg, sm, lane, base, cnt, rec0, my_ins);
                     fence_async_smem(); /* rec_d shares the staging slots' B halves */
                     __syncwarp();
-                    core_tile<1, true, TMA>(tg, sm, lane, rec0, cnt, acc, par0, par1, one2);
+                    core_tile<1, true, SLOTS>(tg, sm, lane, rec0, cnt, acc, parity, one2);
                     __syncwarp();
                 }
                 active_list_finish(st, sm, lane, n_act, my_ins);
@@ -2489,29 +2529,48 @@ int tbf_launch_wave_store(float *wave4, const float *raw, const uint32_t *meta, 
     return (int)cudaGetLastError();
 }
 
-size_t tbf_stage_t_smem(void) { return sizeof(TWarp) * T_WARPS; }
+size_t tbf_stage_t_smem(void) { return (sizeof(TWarp) + 2 * 1024) * T_WARPS; }
 size_t tbf_stage_w_smem(int ring_size)
 {
     return (sizeof(WWarp) + (size_t)2 * ring_size * sizeof(float)) * W_WARPS;
 }
 
+template <int SLOTS> static int launch_stage_t(const RenderParams &p, cudaStream_t stream)
+{
+    static int have[TBF_MAX_DEVICES] = {0};
+    const size_t smem = (sizeof(TWarp) + (size_t)(SLOTS < 0 ? -SLOTS : SLOTS) * 1024) * T_WARPS;
+    if (int rc = set_smem(tbf_stage_t<SLOTS>, smem, have))
+        return rc;
+    const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
+    tbf_stage_t<SLOTS><<<grid, T_WARPS * 32, smem, stream>>>(p);
+    return 0;
+}
+
 int tbf_launch_stage_t(const RenderParams &p, void *stream)
 {
-    static int have[2][TBF_MAX_DEVICES] = {{0}, {0}};
-    const size_t smem = tbf_stage_t_smem();
-    /* wave loads: TMA bulk copies (default; stage T alone 1.11 ms per 4096 organs x 32 fragments)
-     * or, with TBF_T_LOADS=ldg, per-lane 16-byte loads (1.82 ms: profiles/r02_kernels.md) */
-    static const bool tma = !(getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "ldg"));
+    /* wave loads: TMA bulk copies through 2 staging slots per warp when the batch fills the SMs (28
+     * warps per SM hide the copy latency for one another); per-lane cp.async six wheels deep for
+     * small batches (fewer than three CTAs per SM), where a warp's own step latency is the bound.
+     * TBF_T_LOADS = tma | cpasync forces the mover, TBF_T_SLOTS = 2 | 3 | 6 the depth
+     * (profiles/r02_kernels.md has the sweep) */
+    static const bool cpa = getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "cpasync");
+    static const bool tma_only = getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "tma");
+    static const int forced = getenv("TBF_T_SLOTS") ? atoi(getenv("TBF_T_SLOTS")) : 0;
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
-    if (tma) {
-        if (int rc = set_smem(tbf_stage_t<true>, smem, have[1]))
-            return rc;
-        tbf_stage_t<true><<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
-    } else {
-        if (int rc = set_smem(tbf_stage_t<false>, smem, have[0]))
-            return rc;
-        tbf_stage_t<false><<<grid, T_WARPS * 32, smem, (cudaStream_t)stream>>>(p);
-    }
+    const bool small = grid <= 148u * 3u; /* fewer than three CTAs per SM */
+    const bool use_cpa = cpa || (small && !tma_only);
+    const int slots = forced ? forced : (small ? 6 : 2);
+    int rc;
+    if (use_cpa)
+        rc = slots >= 6   ? launch_stage_t<-6>(p, (cudaStream_t)stream)
+             : slots >= 3 ? launch_stage_t<-3>(p, (cudaStream_t)stream)
+                          : launch_stage_t<-2>(p, (cudaStream_t)stream);
+    else
+        rc = slots >= 6   ? launch_stage_t<6>(p, (cudaStream_t)stream)
+             : slots >= 3 ? launch_stage_t<3>(p, (cudaStream_t)stream)
+                          : launch_stage_t<2>(p, (cudaStream_t)stream);
+    if (rc)
+        return rc;
     debug_sync(stream, "T");
     return (int)cudaGetLastError();
 }
