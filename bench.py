@@ -674,7 +674,9 @@ def run_gpu_arm(a):
                     "hbm": {"achieved": ach_hbm, "peak": hbm_peak, "unit": "GB/s",
                             "frac": ach_hbm / hbm_peak,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                            "note": "the dominant kernel's algorithmic reads + writes; not the bound"}}
+                            "note": "the dominant kernel's algorithmic reads + writes over its launch time; "
+                                    "not the bound: stage T's reads are the wavetables (4 B per wheel and "
+                                    "sample), which stay in L2 -- what reaches DRAM is roofline.traffic"}}
         if cpu_baseline is not None and cpu_baseline.get("n_act"):
             cpu_baseline["n_act_gpu_arm"] = n_act
             cpu_baseline["same_workload"] = bool(abs(cpu_baseline["n_act"] - n_act) <= 0.01 * n_act)
