@@ -186,6 +186,21 @@ typedef struct tbf_event {
                                        (out_stride is ignored; the last chunk may be shorter and keeps
                                        the row length chunk_samples)                                */
 
+/* Testing and measurement only: variants of stage T that all produce the same bits.  0x100: every
+ * fragment takes the full active-list pass; 0x200: quiet fragments one at a time, not in pairs;
+ * 0x400: every bus sum of a quiet fragment is taken again over all records; 0x800: quiet fragments
+ * by the one merged loop, never bus by bus; 0x4000: quiet fragments sum all three buses, read or not;
+ * bits 12-13: how the wheels' samples are loaded (0 = the library's choice, 1 = TMA bulk copies,
+ * 2 = per-lane cp.async, 3 = direct loads). */
+#define TBF_RENDER_DEBUG_FULL_PASS 0x100
+#define TBF_RENDER_DEBUG_NO_PAIRS 0x200
+#define TBF_RENDER_DEBUG_BUS_ALL 0x400
+#define TBF_RENDER_DEBUG_NO_BUS 0x800
+#define TBF_RENDER_DEBUG_T_TMA 0x1000
+#define TBF_RENDER_DEBUG_T_CPASYNC 0x2000
+#define TBF_RENDER_DEBUG_T_DIRECT 0x3000
+#define TBF_RENDER_DEBUG_ALL_BUSES 0x4000
+
 typedef struct tbf_batch_desc {
     uint32_t n_instances;
     const uint32_t *instance_ids; /* NULL = instances 0..n_instances-1         */

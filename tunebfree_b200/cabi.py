@@ -50,6 +50,15 @@ RENDER_NO_OUTPUT = 0x8
 RENDER_WHIRL_INPUT = 0x10
 RENDER_STEMS = 0x20
 RENDER_OUT_CHUNKED = 0x40
+# testing / measurement: stage T variants (include/tbf_gpu.h TBF_RENDER_DEBUG_*)
+RENDER_DEBUG_FULL_PASS = 0x100
+RENDER_DEBUG_NO_PAIRS = 0x200
+RENDER_DEBUG_BUS_ALL = 0x400
+RENDER_DEBUG_NO_BUS = 0x800
+RENDER_DEBUG_T_TMA = 0x1000
+RENDER_DEBUG_T_CPASYNC = 0x2000
+RENDER_DEBUG_T_DIRECT = 0x3000
+RENDER_DEBUG_ALL_BUSES = 0x4000
 HOST_WRITE_COMBINED = 0x1
 
 IFLAG_COREPGM_OVERFLOW = 0x1

@@ -17,6 +17,7 @@
 #define TBF_DEVICE_H
 
 #include <stdint.h>
+#include <cstddef>
 #include "tbf_gpu.h"
 
 /* rendering flag bits, src/tonegen.cpp:124-130 */
@@ -31,6 +32,7 @@
 #define RT_LOWRVIB 0x01u
 #define RT_VIB 0x03u
 
+#define TBF_REC_CAP 160 /* longest active list whose records persist across fragments and launches */
 #define TBF_VRING 64 /* shared-memory scanner ring: host checks that every offset-table
                         entry keeps the writes inside it (tbf_api.cu); offsets are
                         (1 + A + A sin) with A <= 12 (scanner.modulation.*'s range,
@@ -104,7 +106,17 @@ struct InstState {
     float busLevel[(TBF_NOF_WHEELS + 1) * TBF_NOF_BUSES]; /* aot[w].busLevel[b] */
     float vibBuffer[TBF_VIB_BUF];
     float wbuf[4][TBF_WHIRL_BUF]; /* HL HR DL DR */
+    /* Stage T's records of the active list (gains, wave length | position of the fragment last
+     * rendered, wheel), kept from one launch to the next: they are derived state, valid only while
+     * rec_valid is set (stage T clears it whenever its last fragment left no reusable records; a
+     * fresh or re-initialised instance has it clear).  With them the first fragment of a chunk is as
+     * cheap as any other quiet one instead of a full active-list pass over state in HBM. */
+    alignas(16) float recG[TBF_REC_CAP][4];
+    uint32_t recL[TBF_REC_CAP];
+    uint16_t recW[TBF_REC_CAP];
+    int32_t rec_valid, rec_count;
 };
+static_assert(offsetof(InstState, recG) % 16 == 0 && sizeof(InstState) % 16 == 0, "recG is read as float4");
 
 /* Floats per rotated copy of a wave of `len` samples: copy c holds wave[(i + c) % len] for
  * i < len + 256, padded to whole float4s, so the reads of TWO consecutive fragments from any

@@ -131,7 +131,7 @@ __device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_
  * active wheel (src/tonegen.h:114-129); with a modular index the wrap split collapses
  * and one record per wheel suffices. */
 #define REC_TILE 32    /* active-list entries turned into records and summed at a time */
-#define REC_CAP 128   /* longest active list whose records persist across fragments   */
+#define REC_CAP TBF_REC_CAP /* longest active list whose records persist across fragments */
 #define T_MAX_SLOTS 8  /* wave staging slots per warp = wheels in flight (bulk copies): 2 when the
                           SMs are full (6 KB per warp, 28 warps per SM), 6 for small batches, where a
                           warp's own copies are all that hides the copy latency                    */
@@ -145,6 +145,10 @@ struct TWarp {
                                store, in float4 units                                            */
     uint32_t recL[REC_CAP]; /* wave length | read position << 16 (of the record's last fragment) */
     uint16_t recW[REC_CAP]; /* wheel                                                             */
+    /* per bus (swell, scanner, percussion): the records whose gain on that bus is not zero, in list
+     * order (bus_lists_build) */
+    uint8_t bus_list[3][REC_CAP];
+    int bus_n[3];
     /* wave samples in flight: one 512-byte bulk copy (TMA) per wheel and fragment lands here,
      * [slot][fragment A / B][lane] = samples 4*lane .. 4*lane+3.  The single-fragment passes use
      * the A halves only; the B halves then hold the envelope deltas of the current tile
@@ -162,7 +166,7 @@ struct TWarp {
     int any_removed, any_env;
 };
 static_assert(sizeof(TWarp) % 16 == 0, "the staging slots behind the struct are float4-aligned");
-static_assert(sizeof(TWarp) + 2 * 1024 <= 7040, "stage T: 32 warps per SM need <= 7040 B of shared memory per warp");
+static_assert(sizeof(TWarp) + 2 * 1024 <= 7936, "stage T: 7 CTAs of 4 warps per SM need <= 7936 B of shared memory per warp");
 static_assert(REC_TILE * sizeof(float4) <= sizeof(float4) * 32 &&
               TBF_NOF_WHEELS * sizeof(uint16_t) <= sizeof(float4) * 32, "slow-path arrays fit a B half");
 
@@ -751,16 +755,20 @@ __device__ __forceinline__ void acc_env(f32x2 (&sum)[2], const float (&xs)[4], c
 
 /* products of one record with the lane's staged samples x, added in list order.  ENV = false:
  * the caller knows that every record plays with constant gains (no key click in flight). */
-template <bool ENV>
+template <bool ENV, int MASK = 7>
 __device__ __forceinline__ void wheel_accumulate(const DevTonegenTables *tg, TWarp &sm, const float4 g,
                                                  int i_tile, int lane, const ulonglong2 x, CoreAcc &a,
                                                  const f32x2 one2)
 {
     const int env = ENV ? __float_as_int(g.w) : -1;
     if (!ENV || env < 0) {
-        acc_plain(a.s, x, pack2(g.x, g.x), one2);
-        acc_plain(a.v, x, pack2(g.y, g.y), one2);
-        acc_plain(a.p, x, pack2(g.z, g.z), one2);
+        /* MASK: the buses this fragment needs (quiet fragments only: quiet_mask) */
+        if (MASK & 1)
+            acc_plain(a.s, x, pack2(g.x, g.x), one2);
+        if (MASK & 2)
+            acc_plain(a.v, x, pack2(g.y, g.y), one2);
+        if (MASK & 4)
+            acc_plain(a.p, x, pack2(g.z, g.z), one2);
     } else { /* key click: gain = g + env[n] * (next - g), per sample */
         const float4 d = rec_d(sm)[i_tile]; /* only the pass's tiles (<= REC_TILE records) carry envelopes */
         const float *ep = tg->env[env] + 4 * lane;
@@ -895,16 +903,281 @@ __device__ __forceinline__ void core_tile_cpa(const DevTonegenTables *tg, TWarp 
     __pipeline_wait_prior(0);
 }
 
-/* SLOTS > 0: TMA bulk copies through that many staging slots; SLOTS < 0: per-lane cp.async
- * through -SLOTS slots */
+/* The same sum without staging: every lane loads its own 16 bytes of a wheel (per fragment) straight
+ * into registers with LDG.128, DEPTH wheels ahead, the register sets rotating at compile time.  Two
+ * instructions per wheel and fragment pair fetch the samples (no request, no barrier, no read-back
+ * from shared memory), and the L1 data pipe sees the same four wavefronts per 512 bytes a bulk copy's
+ * read-back costs; the price is 8 registers per wheel in flight. */
+template <int NF>
+__device__ __forceinline__ void wave_load_direct(const char *lane_base, uint32_t q, ulonglong2 (&x)[NF])
+{
+    const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(lane_base + (size_t)q * 16u);
+#pragma unroll
+    for (int f = 0; f < NF; ++f)
+        x[f] = __ldg(src + 32 * f);
+}
+/* One trip = DEPTH records, register set J holding record i + J.  Three stages are in flight: record
+ * i + J is summed, the samples of record i + J + DEPTH are requested into the set it leaves (their
+ * address has been waiting in qn[J] since the trip before, so the request goes out the moment the
+ * set is free -- with the address looked up in the same trip ptxas places the loads at the trip's
+ * end, right before their first use, and every trip waits out a full L2 round trip), and the address
+ * of record i + J + 2 DEPTH is looked up.  Records past the tile's end are clamped to its last one: a
+ * load nobody uses instead of a branch (a predicated load makes ptxas shuffle the register sets). */
+template <int NF, bool ENV, int MASK, int DEPTH, int J, bool LOAD>
+struct DirectSteps {
+    static __device__ __forceinline__ void run(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0, int i,
+                                               int cnt, const char *lane_base, ulonglong2 (&x)[DEPTH][NF],
+                                               uint32_t (&qn)[DEPTH], CoreAcc (&acc)[NF], const f32x2 one2)
+    {
+        if (LOAD || i + J < cnt) {
+            const float4 g = sm.recG[rec0 + i + J];
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                wheel_accumulate<ENV, MASK>(tg, sm, g, i + J, lane, x[J][f], acc[f], one2);
+            if (LOAD) {
+                wave_load_direct<NF>(lane_base, qn[J], x[J]);
+                qn[J] = sm.recQ[rec0 + min(i + J + 2 * DEPTH, cnt - 1)];
+            }
+            DirectSteps<NF, ENV, MASK, DEPTH, J + 1, LOAD>::run(tg, sm, lane, rec0, i, cnt, lane_base, x, qn, acc, one2);
+        }
+    }
+};
+template <int NF, bool ENV, int MASK, int DEPTH, bool LOAD>
+struct DirectSteps<NF, ENV, MASK, DEPTH, DEPTH, LOAD> {
+    static __device__ __forceinline__ void run(const DevTonegenTables *, TWarp &, int, int, int, int, const char *,
+                                               ulonglong2 (&)[DEPTH][NF], uint32_t (&)[DEPTH], CoreAcc (&)[NF],
+                                               const f32x2)
+    {
+    }
+};
+template <int NF, bool ENV, int DEPTH, int MASK = 7>
+__device__ __forceinline__ void core_tile_direct(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
+                                                 int cnt, CoreAcc (&acc)[NF], const f32x2 one2)
+{
+    if (cnt <= 0)
+        return;
+    /* the lane's window into the wave store, as a value ptxas keeps in a register pair instead of
+     * re-deriving it from the thread index inside the loop */
+    const char *lane_base = reinterpret_cast<const char *>(sm.wave4) + lane * 16;
+    asm volatile("" : "+l"(lane_base));
+    ulonglong2 x[DEPTH][NF];
+    uint32_t qn[DEPTH];
+#pragma unroll
+    for (int j = 0; j < DEPTH; ++j)
+        wave_load_direct<NF>(lane_base, sm.recQ[rec0 + min(j, cnt - 1)], x[j]);
+#pragma unroll
+    for (int j = 0; j < DEPTH; ++j)
+        qn[j] = sm.recQ[rec0 + min(DEPTH + j, cnt - 1)];
+    int i = 0;
+#pragma unroll 1
+    for (; i + DEPTH <= cnt; i += DEPTH)
+        DirectSteps<NF, ENV, MASK, DEPTH, 0, true>::run(tg, sm, lane, rec0, i, cnt, lane_base, x, qn, acc, one2);
+    DirectSteps<NF, ENV, MASK, DEPTH, 0, false>::run(tg, sm, lane, rec0, i, cnt, lane_base, x, qn, acc, one2);
+}
+
+/* ---- quiet fragments, one bus at a time over the records that feed it ----
+ *
+ * Most gains are zero: a wheel played from a manual that is routed to the scanner has no swell
+ * gain, only the wheels of the percussion harmonic have a percussion gain.  The reference
+ * multiplies by those zeros and adds the products (src/tonegen.cpp:3640-3680); the sums do not
+ * need them.  A product x * (+-0) is +-0, and adding +-0 changes a running sum only while that sum
+ * is itself +-0, and then only its sign.  So the sum over the records with a NON-ZERO gain, in list
+ * order, equals the reference's sum bit for bit wherever the final value is not zero; where it is
+ * zero only the sign can differ, and that case is recomputed over all records (bus_sum<.., true>).
+ * The buses are independent sums, so each runs as its own loop over its own list, samples loaded
+ * straight into registers DEPTH records ahead. */
+__device__ __forceinline__ void bus_lists_build(TWarp &sm, int lane, int n_act)
+{
+    int cnt[3] = {0, 0, 0};
+    for (int base = 0; base < n_act; base += 32) {
+        const int i = base + lane;
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (i < n_act)
+            g = sm.recG[i];
+        const float gb[3] = {g.x, g.y, g.z};
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+            const bool mine = gb[b] != 0.0f; /* -0 is a zero too; NaN counts as a gain */
+            const uint32_t m = __ballot_sync(FULL, mine);
+            if (mine)
+                sm.bus_list[b][cnt[b] + __popc(m & ((1u << lane) - 1u))] = (uint8_t)i;
+            cnt[b] += __popc(m);
+        }
+    }
+    if (lane < 3)
+        sm.bus_n[lane] = lane == 0 ? cnt[0] : (lane == 1 ? cnt[1] : cnt[2]);
+    __syncwarp();
+}
+
+/* entry e of a bus loop: the record it names, where its samples start, its gain on the bus */
+template <bool ALL>
+__device__ __forceinline__ void bus_entry(const TWarp &sm, const uint8_t *list, int bus, int e, uint32_t &q, float &g)
+{
+    const int r = ALL ? e : (int)list[e];
+    q = sm.recQ[r];
+    g = reinterpret_cast<const float *>(&sm.recG[r])[bus];
+}
+/* One trip = DEPTH entries, register set J holding entry e + J.  Three stages are in flight: entry
+ * e + J is summed, the samples of entry e + J + DEPTH are requested into the set it leaves (their
+ * address has been waiting in qn[J] since the trip before, so the request can go out the moment the
+ * set is free -- with the address looked up in the same trip the loads end up at the trip's end, right
+ * before their first use), and the address and gain of entry e + J + 2 DEPTH are looked up.  Entries
+ * past the list's end are clamped to its last one: a load nobody uses instead of a branch. */
+template <int NF, int DEPTH, bool ALL, int J, bool LOAD>
+struct BusSteps {
+    static __device__ __forceinline__ void run(const TWarp &sm, const uint8_t *list, int bus, int e, int cnt,
+                                               const char *lane_base, ulonglong2 (&x)[DEPTH][NF], float (&g)[DEPTH],
+                                               uint32_t (&qn)[DEPTH], float (&gn)[DEPTH], f32x2 (&sum)[NF][2],
+                                               const f32x2 one2)
+    {
+        if (LOAD || e + J < cnt) {
+            const f32x2 g2 = pack2(g[J], g[J]);
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                acc_plain(sum[f], x[J][f], g2, one2);
+            if (LOAD) {
+                wave_load_direct<NF>(lane_base, qn[J], x[J]);
+                g[J] = gn[J];
+                bus_entry<ALL>(sm, list, bus, min(e + J + 2 * DEPTH, cnt - 1), qn[J], gn[J]);
+            }
+            BusSteps<NF, DEPTH, ALL, J + 1, LOAD>::run(sm, list, bus, e, cnt, lane_base, x, g, qn, gn, sum, one2);
+        }
+    }
+};
+template <int NF, int DEPTH, bool ALL, bool LOAD>
+struct BusSteps<NF, DEPTH, ALL, DEPTH, LOAD> {
+    static __device__ __forceinline__ void run(const TWarp &, const uint8_t *, int, int, int, const char *,
+                                               ulonglong2 (&)[DEPTH][NF], float (&)[DEPTH], uint32_t (&)[DEPTH],
+                                               float (&)[DEPTH], f32x2 (&)[NF][2], const f32x2)
+    {
+    }
+};
+/* sum[f] = the bus's samples of fragment f (the lane's four, as two packed pairs) over the `cnt`
+ * records of `list` (ALL: over records 0 .. cnt-1), starting from -0 */
+template <int NF, int DEPTH, bool ALL>
+__device__ __forceinline__ void bus_sum(const TWarp &sm, int lane, const uint8_t *list, int bus, int cnt,
+                                        f32x2 (&sum)[NF][2], const f32x2 one2)
+{
+    const f32x2 nz = 0x8000000080000000ull;
+#pragma unroll
+    for (int f = 0; f < NF; ++f)
+        sum[f][0] = sum[f][1] = nz;
+    if (cnt <= 0)
+        return;
+    const char *lane_base = reinterpret_cast<const char *>(sm.wave4) + lane * 16;
+    asm volatile("" : "+l"(lane_base));
+    ulonglong2 x[DEPTH][NF];
+    float g[DEPTH], gn[DEPTH];
+    uint32_t qn[DEPTH];
+#pragma unroll
+    for (int j = 0; j < DEPTH; ++j) {
+        uint32_t q;
+        bus_entry<ALL>(sm, list, bus, min(j, cnt - 1), q, g[j]);
+        wave_load_direct<NF>(lane_base, q, x[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < DEPTH; ++j)
+        bus_entry<ALL>(sm, list, bus, min(DEPTH + j, cnt - 1), qn[j], gn[j]);
+    int e = 0;
+#pragma unroll 1
+    for (; e + DEPTH <= cnt; e += DEPTH)
+        BusSteps<NF, DEPTH, ALL, 0, true>::run(sm, list, bus, e, cnt, lane_base, x, g, qn, gn, sum, one2);
+    BusSteps<NF, DEPTH, ALL, 0, false>::run(sm, list, bus, e, cnt, lane_base, x, g, qn, gn, sum, one2);
+}
+/* any of the lane's samples exactly +-0 */
+template <int NF>
+__device__ __forceinline__ bool bus_has_zero(const f32x2 (&sum)[NF][2])
+{
+    bool z = false;
+#pragma unroll
+    for (int f = 0; f < NF; ++f)
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+            z |= ((uint32_t)sum[f][h] << 1) == 0u || ((uint32_t)(sum[f][h] >> 32) << 1) == 0u;
+    return z;
+}
+/* one bus of NF quiet fragments: over its own list, again over all records where a sample came out
+ * as zero (its sign is the reference's only with the zero products added), over all records straight
+ * away when no record feeds the bus */
+template <int NF, int DEPTH>
+__device__ __forceinline__ void bus_render(const TWarp &sm, int lane, int bus, int n_act, f32x2 (&sum)[NF][2],
+                                           const f32x2 one2, bool force_all)
+{
+    const int nz = sm.bus_n[bus];
+    if (nz > 0 && nz < n_act) {
+        bus_sum<NF, DEPTH, false>(sm, lane, sm.bus_list[bus], bus, nz, sum, one2);
+        if (!force_all && !__any_sync(FULL, bus_has_zero<NF>(sum)))
+            return;
+    }
+    bus_sum<NF, DEPTH, true>(sm, lane, nullptr, bus, n_act, sum, one2);
+}
+
+/* NF quiet fragments with direct loads.  Only the buses somebody reads are summed: the scanner bus
+ * without vibrato routing and the percussion bus without percussion are never looked at
+ * (post_fragment), and a swell bus that no record feeds is left at -0 when the scanner runs and
+ * its delay line held no -0 when the launch began (no_neg_zero): then it never will, the scanner's
+ * output vy is never -0, and swell + vy = vy for a swell bus that is +-0 whatever its sign.  The
+ * remaining buses are summed by one merged loop over all records, or bus by bus over their own
+ * lists when those are short (about 19 instructions per list entry against 9 + 8 per bus and
+ * record). */
+template <int NF, int DEPTH, int BUS_DEPTH>
+__device__ __forceinline__ void quiet_sum(const DevTonegenTables *tg, TWarp &sm, int lane, int n_act,
+                                          CoreAcc (&acc)[NF], const f32x2 one2, bool no_neg_zero, uint32_t flags)
+{
+    const bool vib_on = sm.vib_on != 0, perc_on = sm.perc_on != 0;
+    const int ns = sm.bus_n[0], nv = sm.bus_n[1], np = sm.bus_n[2];
+    const bool skip_s = ns == 0 && vib_on && no_neg_zero;
+    int mask = (skip_s ? 0 : 1) | (vib_on ? 2 : 0) | (perc_on ? 4 : 0);
+    if (flags & 0x4000u) /* debugging: every bus, always */
+        mask = 7;
+    const int entries = ((mask & 1) ? (ns ? ns : n_act) : 0) + ((mask & 2) ? (nv ? nv : n_act) : 0) +
+                        ((mask & 4) ? (np ? np : n_act) : 0);
+    if (!(flags & 0x800u) && entries * 19 < n_act * (9 + 8 * __popc(mask))) {
+        const bool force_all = (flags & 0x400u) != 0;
+        f32x2 sum[NF][2];
+        if (mask & 1) {
+            bus_render<NF, BUS_DEPTH>(sm, lane, 0, n_act, sum, one2, force_all);
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                acc[f].s[0] = sum[f][0], acc[f].s[1] = sum[f][1];
+        }
+        if (mask & 2) {
+            bus_render<NF, BUS_DEPTH>(sm, lane, 1, n_act, sum, one2, force_all);
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                acc[f].v[0] = sum[f][0], acc[f].v[1] = sum[f][1];
+        }
+        if (mask & 4) {
+            bus_render<NF, BUS_DEPTH>(sm, lane, 2, n_act, sum, one2, force_all);
+#pragma unroll
+            for (int f = 0; f < NF; ++f)
+                acc[f].p[0] = sum[f][0], acc[f].p[1] = sum[f][1];
+        }
+        return;
+    }
+    switch (mask) {
+    case 1: core_tile_direct<NF, false, DEPTH, 1>(tg, sm, lane, 0, n_act, acc, one2); break;
+    case 2: core_tile_direct<NF, false, DEPTH, 2>(tg, sm, lane, 0, n_act, acc, one2); break;
+    case 3: core_tile_direct<NF, false, DEPTH, 3>(tg, sm, lane, 0, n_act, acc, one2); break;
+    case 4: core_tile_direct<NF, false, DEPTH, 4>(tg, sm, lane, 0, n_act, acc, one2); break;
+    case 5: core_tile_direct<NF, false, DEPTH, 5>(tg, sm, lane, 0, n_act, acc, one2); break;
+    case 6: core_tile_direct<NF, false, DEPTH, 6>(tg, sm, lane, 0, n_act, acc, one2); break;
+    default: core_tile_direct<NF, false, DEPTH, 7>(tg, sm, lane, 0, n_act, acc, one2); break;
+    }
+}
+
+/* SLOTS > 0: TMA bulk copies through that many staging slots; -8 <= SLOTS < 0: per-lane cp.async
+ * through -SLOTS slots; SLOTS <= -10: direct register loads -SLOTS - 10 wheels ahead */
 template <int NF, bool ENV, int SLOTS>
 __device__ __forceinline__ void core_tile(const DevTonegenTables *tg, TWarp &sm, int lane, int rec0,
                                           int cnt, CoreAcc (&acc)[NF], uint32_t &parity, const f32x2 one2)
 {
     if (SLOTS > 0)
         core_tile_tma<NF, ENV, (SLOTS > 0 ? SLOTS : 2)>(tg, sm, lane, rec0, cnt, acc, parity, one2);
+    else if (SLOTS > -10)
+        core_tile_cpa<NF, ENV, ((SLOTS < 0 && SLOTS > -10) ? -SLOTS : 2)>(tg, sm, lane, rec0, cnt, acc, one2);
     else
-        core_tile_cpa<NF, ENV, (SLOTS < 0 ? -SLOTS : 2)>(tg, sm, lane, rec0, cnt, acc, one2);
+        core_tile_direct<NF, ENV, (SLOTS <= -10 ? -SLOTS - 10 : 2)>(tg, sm, lane, rec0, cnt, acc, one2);
 }
 
 /* from lane = 4 consecutive samples to lane = sample of a 32-sample block (s[k] = sample
@@ -1089,8 +1362,12 @@ __device__ __forceinline__ void quiet_stats(TgScalars &sc, int lane, int n_act, 
 #endif
 /* SLOTS > 0: the wheels' samples arrive by TMA bulk copies through that many shared-memory staging
  * slots; SLOTS < 0: by per-lane cp.async through -SLOTS slots */
+/* direct loads: 8 registers per wheel in flight */
+#ifndef T_DIRECT_CTAS
+#define T_DIRECT_CTAS(depth) ((depth) <= 3 ? 7 : 5)
+#endif
 template <int SLOTS>
-__global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_MIN_CTAS : 4) tbf_stage_t(const RenderParams p)
+__global__ void __launch_bounds__(T_WARPS * 32, SLOTS <= -10 ? T_DIRECT_CTAS(-SLOTS - 10) : (SLOTS >= -3 && SLOTS <= 3) ? T_MIN_CTAS : 4) tbf_stage_t(const RenderParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1098,7 +1375,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_
     if (slot >= p.n_instances)
         return; /* warps are independent: no CTA-wide barrier anywhere in this kernel */
     constexpr bool TMA = SLOTS > 0;
-    constexpr int N_SLOTS = SLOTS < 0 ? -SLOTS : SLOTS;
+    constexpr int N_SLOTS = SLOTS <= -10 ? 2 : SLOTS < 0 ? -SLOTS : SLOTS; /* direct loads: the two slots the transposes use */
     constexpr size_t per_warp = sizeof(TWarp) + (size_t)N_SLOTS * 1024;
     TWarp &sm = *reinterpret_cast<TWarp *>(smem_raw + per_warp * warp);
     const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
@@ -1119,10 +1396,21 @@ __global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_
     const DevTonegenTables *tg = p.tg + sc.tgTables;
     if (lane == 0)
         sm.wave4 = tg->wave4;
+    bool no_neg_zero = true; /* no -0 in the scanner's delay line (quiet_buses) */
     for (int s = lane; s < TBF_VRING; s += 32) {
         const uint32_t g = (sc.vibOutPos + (uint32_t)s) & VBUF_MASK;
-        sm.vring[g & VRING_MASK] = st->vibBuffer[g];
+        const float y = st->vibBuffer[g];
+        no_neg_zero &= __float_as_uint(y) != 0x80000000u;
+        sm.vring[g & VRING_MASK] = y;
     }
+    no_neg_zero = __all_sync(FULL, no_neg_zero);
+    constexpr bool DIRECT = SLOTS <= -10;
+#ifndef TBF_BUS_DEPTH
+#define TBF_BUS_DEPTH 3
+#endif
+    constexpr int BUS_DEPTH = TBF_BUS_DEPTH;
+    constexpr int DIRECT_DEPTH = DIRECT ? -SLOTS - 10 : 2;
+    bool lists_valid = false;
     uint64_t ev_cur = p.ev_cursor_t[slot];
     const uint64_t ev_end = p.ev_start[slot + 1];
     float *u_row = p.u + (size_t)slot * p.pitch;
@@ -1135,6 +1423,17 @@ __global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_
     int dbg_fast = 0;
 #endif
     int n_act_cached = 0;
+    /* the records the last launch left behind (InstState::recG ...) */
+    if (st->rec_valid && !(p.flags & 0x100u)) {
+        n_act_cached = st->rec_count;
+        for (int i = lane; i < n_act_cached; i += 32) {
+            sm.recG[i] = *reinterpret_cast<const float4 *>(st->recG[i]);
+            sm.recL[i] = st->recL[i];
+            sm.recW[i] = st->recW[i];
+        }
+        cache_valid = true;
+        __syncwarp();
+    }
     uint32_t f = 0;
     while (f < p.n_fragments) {
         /* -- control events that precede this fragment -- */
@@ -1209,8 +1508,16 @@ __global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_
             core_begin(acc[0]);
             core_begin(acc[1]);
             fast_pass<2>(tg, sm, lane, n_act, ins_a, ins_b);
+            if (DIRECT && !lists_valid) {
+                __syncwarp();
+                bus_lists_build(sm, lane, n_act);
+                lists_valid = true;
+            }
             __syncwarp();
-            core_tile<2, false, SLOTS>(tg, sm, lane, 0, n_act, acc, parity, one2);
+            if (DIRECT)
+                quiet_sum<2, DIRECT_DEPTH, BUS_DEPTH>(tg, sm, lane, n_act, acc, one2, no_neg_zero, p.flags);
+            else
+                core_tile<2, false, SLOTS>(tg, sm, lane, 0, n_act, acc, parity, one2);
             __syncwarp();
             quiet_stats(sc, lane, n_act, ins_a);
             quiet_stats(sc, lane, n_act, ins_b);
@@ -1233,11 +1540,20 @@ __global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_
                 ++dbg_fast;
 #endif
                 fast_pass<1>(tg, sm, lane, n_act, my_ins, unused);
+                if (DIRECT && !lists_valid) {
+                    __syncwarp();
+                    bus_lists_build(sm, lane, n_act);
+                    lists_valid = true;
+                }
                 __syncwarp();
-                core_tile<1, false, SLOTS>(tg, sm, lane, 0, n_act, acc, parity, one2);
+                if (DIRECT)
+                    quiet_sum<1, DIRECT_DEPTH, BUS_DEPTH>(tg, sm, lane, n_act, acc, one2, no_neg_zero, p.flags);
+                else
+                    core_tile<1, false, SLOTS>(tg, sm, lane, 0, n_act, acc, parity, one2);
                 __syncwarp();
                 quiet_stats(sc, lane, n_act, my_ins);
             } else {
+                lists_valid = false; /* new records */
                 if (cache_valid) /* the pass below reads the positions from HBM */
                     flush_positions(st, sm, lane, n_act_cached);
                 __syncwarp();
@@ -1274,10 +1590,19 @@ __global__ void __launch_bounds__(T_WARPS * 32, (SLOTS >= -3 && SLOTS <= 3) ? T_
     if (slot == 5 && lane == 0)
         printf("slot 5: %d of %u fragments on the fast path, lend %d\n", dbg_fast, p.n_fragments, sc.activeOscLEnd);
 #endif
-    if (cache_valid)
+    if (cache_valid) {
         flush_positions(st, sm, lane, n_act_cached);
-    if (lane == 0)
+        for (int i = lane; i < n_act_cached; i += 32) {
+            *reinterpret_cast<float4 *>(st->recG[i]) = sm.recG[i];
+            st->recL[i] = sm.recL[i];
+            st->recW[i] = sm.recW[i];
+        }
+    }
+    if (lane == 0) {
+        st->rec_valid = cache_valid ? 1 : 0;
+        st->rec_count = n_act_cached;
         p.ev_cursor_t[slot] = ev_cur;
+    }
     for (int i = lane; i < (int)(sizeof(TgScalars) / 4); i += 32)
         reinterpret_cast<uint32_t *>(&st->tg)[i] = reinterpret_cast<const uint32_t *>(&sm.sc)[i];
     /* outside the live window every ring slot is zero (cleared when read) */
@@ -2538,7 +2863,7 @@ size_t tbf_stage_w_smem(int ring_size)
 template <int SLOTS> static int launch_stage_t(const RenderParams &p, cudaStream_t stream)
 {
     static int have[TBF_MAX_DEVICES] = {0};
-    const size_t smem = (sizeof(TWarp) + (size_t)(SLOTS < 0 ? -SLOTS : SLOTS) * 1024) * T_WARPS;
+    const size_t smem = (sizeof(TWarp) + (size_t)(SLOTS <= -10 ? 2 : SLOTS < 0 ? -SLOTS : SLOTS) * 1024) * T_WARPS;
     if (int rc = set_smem(tbf_stage_t<SLOTS>, smem, have))
         return rc;
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
@@ -2548,27 +2873,40 @@ template <int SLOTS> static int launch_stage_t(const RenderParams &p, cudaStream
 
 int tbf_launch_stage_t(const RenderParams &p, void *stream)
 {
-    /* wave loads: TMA bulk copies through 2 staging slots per warp when the batch fills the SMs (28
-     * warps per SM hide the copy latency for one another); per-lane cp.async six wheels deep for
-     * small batches (fewer than three CTAs per SM), where a warp's own step latency is the bound.
-     * TBF_T_LOADS = tma | cpasync forces the mover, TBF_T_SLOTS = 2 | 3 | 6 the depth
-     * (profiles/r02_kernels.md has the sweep) */
-    static const bool cpa = getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "cpasync");
-    static const bool tma_only = getenv("TBF_T_LOADS") && !strcmp(getenv("TBF_T_LOADS"), "tma");
+    /* How the wheels' samples reach the sums (profiles/r02_kernels.md has the sweeps):
+     *   direct  -- LDG.128 straight into registers, a few records ahead; quiet fragments bus by bus
+     *              over the records with a non-zero gain (quiet_buses).  The default.
+     *   tma     -- bulk copies (cp.async.bulk + mbarrier) through 2 / 3 / 6 staging slots per warp
+     *   cpasync -- per-lane cp.async through 2 / 3 / 6 slots
+     * TBF_T_LOADS = direct | tma | cpasync or the TBF_RENDER_DEBUG_T_* flag bits pick one,
+     * TBF_T_SLOTS the depth. */
+    static const char *env = getenv("TBF_T_LOADS");
+    static const int env_mover = !env ? 0 : !strcmp(env, "tma") ? 1 : !strcmp(env, "cpasync") ? 2 : !strcmp(env, "direct") ? 3 : 0;
     static const int forced = getenv("TBF_T_SLOTS") ? atoi(getenv("TBF_T_SLOTS")) : 0;
+    const int flag_mover = (int)((p.flags >> 12) & 3u);
+    int mover = flag_mover ? flag_mover : env_mover;
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
-    const bool small = grid <= 148u * 3u; /* fewer than three CTAs per SM */
-    const bool use_cpa = cpa || (small && !tma_only);
-    const int slots = forced ? forced : (small ? 6 : 2);
+    const bool small = grid <= 148u * 3u; /* fewer than three CTAs per SM: a warp's own loads are all
+                                             that hides their latency */
+    if (!mover)
+        mover = 3;
     int rc;
-    if (use_cpa)
-        rc = slots >= 6   ? launch_stage_t<-6>(p, (cudaStream_t)stream)
-             : slots >= 3 ? launch_stage_t<-3>(p, (cudaStream_t)stream)
-                          : launch_stage_t<-2>(p, (cudaStream_t)stream);
-    else
-        rc = slots >= 6   ? launch_stage_t<6>(p, (cudaStream_t)stream)
-             : slots >= 3 ? launch_stage_t<3>(p, (cudaStream_t)stream)
-                          : launch_stage_t<2>(p, (cudaStream_t)stream);
+    if (mover == 3) {
+        const int depth = forced ? forced : (small ? 4 : 2);
+        rc = depth >= 4   ? launch_stage_t<-14>(p, (cudaStream_t)stream)
+             : depth == 3 ? launch_stage_t<-13>(p, (cudaStream_t)stream)
+                          : launch_stage_t<-12>(p, (cudaStream_t)stream);
+    } else {
+        const int slots = forced ? forced : (small ? 6 : 2);
+        if (mover == 2)
+            rc = slots >= 6   ? launch_stage_t<-6>(p, (cudaStream_t)stream)
+                 : slots >= 3 ? launch_stage_t<-3>(p, (cudaStream_t)stream)
+                              : launch_stage_t<-2>(p, (cudaStream_t)stream);
+        else
+            rc = slots >= 6   ? launch_stage_t<6>(p, (cudaStream_t)stream)
+                 : slots >= 3 ? launch_stage_t<3>(p, (cudaStream_t)stream)
+                              : launch_stage_t<2>(p, (cudaStream_t)stream);
+    }
     if (rc)
         return rc;
     debug_sync(stream, "T");
