@@ -191,7 +191,8 @@ typedef struct tbf_event {
  * 0x400: every bus sum of a quiet fragment is taken again over all records; 0x800: quiet fragments
  * by the one merged loop, never bus by bus; 0x4000: quiet fragments sum all three buses, read or not;
  * bits 12-13: how the wheels' samples are loaded (0 = the library's choice, 1 = TMA bulk copies,
- * 2 = per-lane cp.async, 3 = direct loads). */
+ * 2 = per-lane cp.async, 3 = direct loads); 0x8000: stages R and D move their 32 x 32 tiles with
+ * cp.async and store loops instead of 2-D TMA boxes. */
 #define TBF_RENDER_DEBUG_FULL_PASS 0x100
 #define TBF_RENDER_DEBUG_NO_PAIRS 0x200
 #define TBF_RENDER_DEBUG_BUS_ALL 0x400
@@ -200,6 +201,7 @@ typedef struct tbf_event {
 #define TBF_RENDER_DEBUG_T_CPASYNC 0x2000
 #define TBF_RENDER_DEBUG_T_DIRECT 0x3000
 #define TBF_RENDER_DEBUG_ALL_BUSES 0x4000
+#define TBF_RENDER_DEBUG_NO_TMA_TILES 0x8000
 
 typedef struct tbf_batch_desc {
     uint32_t n_instances;

@@ -7,6 +7,8 @@ by the zeros too).  Every combination is compared bit for bit with the oracle on
 exercise each case of the bus-by-bus path: a swell bus nobody feeds (all keys on a manual routed to
 the scanner), one fed by some records (lower manual without vibrato next to the upper one with),
 no scanner routing at all, percussion on and off, silence between chords, drawbar changes mid-note.
+Stages R and D move their organ x sample tiles by 2-D TMA boxes or (TBF_RENDER_DEBUG_NO_TMA_TILES)
+by cp.async and store loops: both are in the combinations.
 """
 import numpy as np
 import pytest
@@ -16,7 +18,7 @@ from tunebfree_b200 import cabi, workloads
 pytestmark = pytest.mark.gpu
 
 MOVERS = {"tma": 0x1000, "cpasync": 0x2000, "direct": 0x3000}
-BUS_ALL, NO_BUS, NO_PAIRS, ALL_BUSES = 0x400, 0x800, 0x200, 0x4000
+BUS_ALL, NO_BUS, NO_PAIRS, ALL_BUSES, NO_TILES = 0x400, 0x800, 0x200, 0x4000, 0x8000
 
 
 def _bits(x):
@@ -74,7 +76,7 @@ def test_every_mover_and_bus_mode_is_bit_exact(ref, gpu_ctx, kind):
     assert np.abs(rl).max() > 0.01
     combos = [(m, 0) for m in MOVERS] + [("direct", BUS_ALL), ("direct", NO_BUS), ("direct", NO_PAIRS),
                                          ("direct", NO_PAIRS | BUS_ALL), ("direct", ALL_BUSES), ("direct", ALL_BUSES | NO_BUS),
-                                         ("tma", NO_PAIRS)]
+                                         ("tma", NO_PAIRS), ("direct", NO_TILES), ("tma", NO_TILES)]
     for mover, extra in combos:
         i = gpu_ctx.create_instances(tg, wh, 1)
         gl, gr = gpu_ctx.render(1, n_frag, [ev], flags | MOVERS[mover] | extra, ids=[i])
@@ -99,7 +101,7 @@ def test_many_organs_direct_against_tma(gpu_ctx):
     n, n_frag = 4200, 96
     evs = [workloads.instance_events(g, n_frag, config=3, restrike=40, hold=30) for g in range(n)]
     sums = []
-    for mover in (0, MOVERS["tma"], MOVERS["direct"] | BUS_ALL):
+    for mover in (0, MOVERS["tma"] | NO_TILES, MOVERS["direct"] | BUS_ALL):
         first = gpu_ctx.create_instances(tg, wh, n)
         _, _, cs = gpu_ctx.render(n, n_frag, evs, cabi.RENDER_WHIRLPROC3 | cabi.RENDER_NO_OUTPUT | mover,
                                   ids=list(range(first, first + n)), checksums=True)

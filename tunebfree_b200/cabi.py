@@ -59,6 +59,7 @@ RENDER_DEBUG_T_TMA = 0x1000
 RENDER_DEBUG_T_CPASYNC = 0x2000
 RENDER_DEBUG_T_DIRECT = 0x3000
 RENDER_DEBUG_ALL_BUSES = 0x4000
+RENDER_DEBUG_NO_TMA_TILES = 0x8000
 HOST_WRITE_COMBINED = 0x1
 
 IFLAG_COREPGM_OVERFLOW = 0x1

@@ -97,7 +97,45 @@ struct StageScratch {
     float *f32 = nullptr;   /* u, php, dx0, hx0, line[4]: 8 planes */
     double *f64 = nullptr;  /* hang, dang: 2 planes */
     size_t cap_ctl = 0, cap_f32 = 0, cap_f64 = 0;
+    /* tensor maps over f32 / f64 for the 2-D TMA tiles of stages R and D, and what they describe */
+    TileMaps maps;
+    bool maps_ok = false;
+    const void *map_f32 = nullptr, *map_f64 = nullptr;
+    size_t map_pitch = 0, map_rows32 = 0, map_rows64 = 0;
 };
+
+/* cuTensorMapEncodeTiled through the runtime (no link against libcuda) */
+typedef CUresult (*tbf_encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                        const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                        CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                        CUtensorMapFloatOOBfill);
+static tbf_encode_tiled_fn tbf_encode_tiled()
+{
+    static tbf_encode_tiled_fn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        cudaGetLastError();
+        return (tbf_encode_tiled_fn)f;
+    }();
+    return fn;
+}
+/* rows x row_floats floats at `base` (row pitch = row_floats * 4 bytes) as boxes of 32 rows x 32
+ * floats (128 bytes, the 128-byte swizzle's span) */
+static bool tile_map_make(CUtensorMap *m, void *base, size_t row_floats, size_t rows)
+{
+    tbf_encode_tiled_fn enc = tbf_encode_tiled();
+    if (!enc || ((uintptr_t)base & 127u) || (row_floats % 32) || !rows || rows >> 31 || row_floats >> 31)
+        return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)row_floats, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)row_floats * 4};
+    const cuuint32_t box[2] = {32, 32}, estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 
 #define TBF_MAX_GROUPS 4
 #define TBF_MAX_STAGE_BUFS 4
@@ -1488,19 +1526,36 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     sc_frag = std::min(sc_frag, chunk);
     const size_t pitch = (size_t)sc_frag * TBF_FRAGMENT;
     const size_t planes32 = whirl ? 8 : 2;
+    /* rows per plane, padded to whole 32-organ tiles: a TMA box never reaches into the next plane */
+    const size_t np = (n + 31) / 32 * 32;
     StageScratch &ss = ctx->scratch;
     {
         cudaError_t e = grow(&ss.ctl, &ss.cap_ctl, nb * n * sc_frag);
         if (e == cudaSuccess)
-            e = grow(&ss.f32, &ss.cap_f32, nb * n * pitch * planes32);
+            e = grow(&ss.f32, &ss.cap_f32, nb * np * pitch * planes32);
         if (e == cudaSuccess && whirl)
-            e = grow(&ss.f64, &ss.cap_f64, nb * n * pitch * 2);
+            e = grow(&ss.f64, &ss.cap_f64, nb * np * pitch * 2);
         if (e != cudaSuccess) {
             cudaGetLastError();
             ctx->err = "render: stage stream buffers do not fit";
             return TBF_ERR_NOMEM;
         }
     }
+    /* tensor maps of the scratch as it is laid out for this batch (TBF_NO_TMA_TILES=1: none, the
+     * lane = organ kernels then move their tiles with cp.async) */
+    static const bool no_tiles = getenv("TBF_NO_TMA_TILES") != nullptr;
+    bool tiles = whirl && !no_tiles && !(d->flags & 0x8000u);
+    if (tiles && !(ss.maps_ok && ss.map_f32 == ss.f32 && ss.map_f64 == ss.f64 && ss.map_pitch == pitch &&
+                   ss.map_rows32 == nb * np * planes32 && ss.map_rows64 == nb * np * 2)) {
+        ss.maps_ok = tile_map_make(&ss.maps.m32, ss.f32, pitch, nb * np * planes32) &&
+                     tile_map_make(&ss.maps.m64, ss.f64, 2 * pitch, nb * np * 2);
+        ss.map_f32 = ss.f32;
+        ss.map_f64 = ss.f64;
+        ss.map_pitch = pitch;
+        ss.map_rows32 = nb * np * planes32;
+        ss.map_rows64 = nb * np * 2;
+    }
+    tiles = tiles && ss.maps_ok;
 
     /* instance groups (multiples of 32 slots, so the lane = instance warps stay full) */
     int n_groups = std::min<int>(ctx->n_groups_max, n >= 2048 ? 4 : (n >= 512 ? 2 : 1));
@@ -1603,19 +1658,24 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             for (uint32_t ib = 0; ib < nf; ib += sc_frag) {
                 const uint32_t c = cidx[g]++;
                 par = (int)(c % (uint32_t)nb);
-                float *f32 = ss.f32 + (size_t)par * n * pitch * planes32;
+                float *f32 = ss.f32 + (size_t)par * np * pitch * planes32;
                 p.ctl = ss.ctl + ((size_t)par * n + s0) * sc_frag;
                 p.u = f32 + s0 * pitch;
-                p.php = f32 + (n + s0) * pitch;
+                p.php = f32 + (np + s0) * pitch;
                 if (whirl) {
-                    p.dx0 = f32 + (2 * n + s0) * pitch;
-                    p.hx0 = f32 + (3 * n + s0) * pitch;
+                    p.dx0 = f32 + (2 * np + s0) * pitch;
+                    p.hx0 = f32 + (3 * np + s0) * pitch;
                     for (int l = 0; l < 4; ++l)
-                        p.line[l] = f32 + ((4 + l) * n + s0) * pitch;
-                    double *f64 = ss.f64 + (size_t)par * n * pitch * 2;
+                        p.line[l] = f32 + ((4 + l) * np + s0) * pitch;
+                    double *f64 = ss.f64 + (size_t)par * np * pitch * 2;
                     p.hang = f64 + s0 * pitch;
-                    p.dang = f64 + (n + s0) * pitch;
+                    p.dang = f64 + (np + s0) * pitch;
                 }
+                p.tile_maps = tiles ? &ss.maps : nullptr;
+                for (int k = 0; k < 8; ++k) /* u php dx0 hx0 line[0..3] */
+                    p.tile_row[k] = (uint32_t)(((size_t)par * planes32 + (size_t)k) * np + s0);
+                p.tile_row[8] = (uint32_t)(((size_t)par * 2) * np + s0);
+                p.tile_row[9] = (uint32_t)(((size_t)par * 2 + 1) * np + s0);
                 p.frag_base = base + ib;
                 p.n_fragments = std::min<uint32_t>(sc_frag, nf - ib);
                 p.out_l = out_l ? out_l + s0 * out_stride + (size_t)ib * TBF_FRAGMENT : nullptr;

@@ -18,6 +18,7 @@
 
 #include <stdint.h>
 #include <cstddef>
+#include <cuda.h>
 #include "tbf_gpu.h"
 
 /* rendering flag bits, src/tonegen.cpp:124-130 */
@@ -233,6 +234,16 @@ struct RenderParams {
     float *line[4];            /* W -> D: delay-line reads HL HR DL DR                  */
     uint64_t pitch;            /* elements per slot row of every stream                 */
     float one;                 /* 1.0f, as a run-time value (tbf_kernels.cu: add2_via_fma) */
+    /* 2-D TMA tiles (stages R and D): the launch's first slot as a row of the tensor maps, per plane
+     * u php dx0 hx0 line[0..3] (float map) and hang dang (double map); tile_maps = host pointer to the
+     * maps, NULL when the scratch layout has none (then the kernels move tiles with cp.async) */
+    uint32_t tile_row[10];
+    const struct TileMaps *tile_maps;
+};
+/* tensor maps over the stage-stream scratch, rows = every plane's slots back to back */
+struct TileMaps {
+    CUtensorMap m32; /* float planes: dim0 = pitch, dim1 = rows */
+    CUtensorMap m64; /* double planes as pairs of floats: dim0 = 2 * pitch */
 };
 
 /* what a fresh instance starts from (tbf_init_instances_kernel); everything else is zero */

@@ -35,6 +35,7 @@
  *                               src/whirl.cpp:174-236
  */
 #include <cuda_pipeline.h>
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -1716,6 +1717,35 @@ __device__ __forceinline__ float eq_iir(const float (&c)[5], float &z0, float &z
     return y;
 }
 
+/* ---- 2-D TMA tiles for the lane = organ kernels (stages R and D) ----
+ *
+ * The stage streams are [slot][sample] planes; a lane = organ kernel wants the transpose.  A tensor
+ * map over the whole scratch (rows = every plane's slots, back to back; tbf_api.cu) lets ONE lane
+ * move a 32 organs x 32 samples box with one instruction (cp.async.bulk.tensor, SASS UTMALDG /
+ * UTMASTG) instead of 32 lanes x 32 four-byte cp.async and a 32-trip transposed store loop.  The box
+ * lands row-major, 128 bytes per organ, with the 128-byte swizzle: 16-byte chunk c of row r sits at
+ * chunk c ^ (r & 7), so the eight lanes of a quarter-warp reading "their" row's chunk c with one
+ * LDS.128 touch all 32 banks once. */
+__device__ __forceinline__ void tma_tile_load(uint32_t dst, const CUtensorMap *map, uint32_t col, uint32_t row, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+                 "l"(map), "r"(col), "r"(row), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_tile_store(const CUtensorMap *map, uint32_t col, uint32_t row, uint32_t src)
+{
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%1, %2}], [%3];" ::"l"(map), "r"(col),
+                 "r"(row), "r"(src)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+/* the committed stores have READ their shared-memory source (it may be overwritten) */
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+/* byte offset of 16-byte chunk c (4 floats / 2 doubles) of row r inside a 32-row, 128-byte-row tile */
+__device__ __forceinline__ uint32_t tile_chunk(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+
+#define TILE_BYTES 4096 /* 32 rows x 128 B */
 struct RSmem {
     float tin[2][2][BLK * TILE_PITCH]; /* [buffer][u, php] (row = instance, col = sample);
                                           filled by cp.async one block ahead of its use   */
@@ -2034,6 +2064,322 @@ __global__ void __launch_bounds__(64) tbf_stage_r(const RenderParams p)
             p.checksums[slot] += c; /* zeroed by the host; accumulates over chunks */
         }
     }
+}
+
+/* Stage R with TMA tiles (Leslie running: the bypass-only batch keeps tbf_stage_r): the same two
+ * roles and the same arithmetic, the 32 x 32 tiles moved by one lane with cp.async.bulk.tensor and
+ * read / written by every lane as 16-byte chunks of its own row (tile_chunk). */
+struct RTmaSmem {
+    float tin[2][2][TILE_BYTES / 4]; /* [buffer][u, php], filled by TMA one block ahead */
+    float tout[2][TILE_BYTES / 4];   /* dx0, hx0 */
+    double tang[2][2 * TILE_BYTES / 8]; /* horn, drum angle: two boxes of 16 samples each */
+    unsigned long long bar[2];
+};
+__global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    RTmaSmem &sm = *reinterpret_cast<RTmaSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
+    const int lane = threadIdx.x & 31;
+    const bool rotors = (threadIdx.x >> 5) != 0; /* warp-uniform role */
+    const uint32_t slot0 = blockIdx.x * 32;
+    const uint32_t slot = slot0 + lane;
+    const bool valid = slot < p.n_instances;
+    const bool whirl_off = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
+    /* Leslie only: plane u holds the caller's mono input (whirlProc's inbuffer) and the
+     * tone generator's mixdown state (percussion gain, key compression) stays as it is */
+    const bool ext_in = (p.flags & TBF_RENDER_WHIRL_INPUT) != 0;
+    if (rotors && whirl_off)
+        return;
+
+    InstState *st = nullptr;
+    const DevWhirlTables *wh = p.wh;
+    RampScalars rp;
+    if (valid) {
+        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
+        st = p.states + id;
+        rp = st->rp;
+        wh = p.wh + st->tg.whTables;
+    } else {
+        rp = RampScalars();
+    }
+    const bool whirl_run = valid && !whirl_off && !wh->bypass;
+    uint32_t new_flags = 0;
+    uint64_t ev_cur = 0, ev_end = 0;
+    if (valid) {
+        ev_cur = p.ev_cursor_r[slot];
+        ev_end = p.ev_start[slot + 1];
+    }
+    const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+
+    if (rotors) {
+        /* ---------------- role 1: rotor events, speed ramps, angle streams ---------------- */
+        double hang = rp.hornAngle, dang = rp.drumAngle;
+        const double SR = wh->sample_rate;
+        for (uint32_t f = 0; f < p.n_fragments; ++f) {
+            while (ev_cur < ev_end) {
+                const tbf_event *evp = p.events + ev_cur;
+                if (evp->fragment > p.frag_base + f)
+                    break;
+                const int type = evp->type, a = evp->a;
+                if (type == TBF_EV_REV_OPTION) {
+                    if (a < 0)
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    else
+                        use_rev_option(rp, wh, a, 2);
+                } else if (type == TBF_EV_REV_SELECT) {
+                    if (a < 0) {
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    } else {
+                        rp.revSelect = a % 3;
+                        use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
+                    }
+                } else if (type == TBF_EV_WHIRL_BRAKE || type == TBF_EV_WHIRL_RAMP) {
+                    const int b = evp->b;
+                    if (a < 0 || a > (type == TBF_EV_WHIRL_BRAKE ? 1 : 3) || b < 0 || b > 127) {
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    } else if (type == TBF_EV_WHIRL_BRAKE) {
+                        /* w->hnBrakePos = (double)uc / 127.0, src/whirl.cpp:883-893 */
+                        rp.brakePos[a] = __ddiv_rn((double)b, 127.0);
+                    } else {
+                        rp.oml[a] = wh->ramp_one_minus_l[a][b];
+                    }
+                }
+                ++ev_cur;
+            }
+            /* -- per-call speed ramps (src/whirl.cpp:1219-1374) -- */
+            int hbrake = 0, dbrake = 0;
+            double hincr = rp.hornIncr, dincr = rp.drumIncr;
+            if (whirl_run) {
+                hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
+                                    rp.oml[0], rp.oml[1]);
+                dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
+                                    rp.oml[2], rp.oml[3]);
+            }
+            /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
+            const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
+            const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
+            for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
+                const size_t col0 = ((size_t)f * (TBF_FRAGMENT / BLK) + (size_t)blk) * BLK;
+                if (lane == 0)
+                    tma_store_wait_read(); /* the last block's angle tiles have left shared memory */
+                __syncwarp();
+                if (whirl_run) {
+#pragma unroll 4
+                    for (int s2 = 0; s2 < BLK / 2; ++s2) { /* two samples = one 16-byte chunk */
+                        double h[2], dd[2];
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            h[e] = hang;
+                            dd[e] = dang;
+                            if (hfast) {
+                                const double t = __dadd_rn(hang, hincr);
+                                hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                            } else {
+                                hang = angle_step(hang, hincr);
+                            }
+                            if (dfast) {
+                                const double t = __dadd_rn(dang, dincr);
+                                dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                            } else {
+                                dang = angle_step(dang, dincr);
+                            }
+                        }
+                        const uint32_t o = (uint32_t)(s2 >> 3) * TILE_BYTES + tile_chunk(lane, s2 & 7);
+                        *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(sm.tang[0]) + o) = make_double2(h[0], h[1]);
+                        *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(sm.tang[1]) + o) = make_double2(dd[0], dd[1]);
+                    }
+                }
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    const uint32_t c2 = 2u * (uint32_t)col0; /* the double planes as pairs of floats */
+                    tma_tile_store(&maps.m64, c2, p.tile_row[8] + slot0, smem_u32(sm.tang[0]));
+                    tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[8] + slot0, smem_u32(sm.tang[0]) + TILE_BYTES);
+                    tma_tile_store(&maps.m64, c2, p.tile_row[9] + slot0, smem_u32(sm.tang[1]));
+                    tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[9] + slot0, smem_u32(sm.tang[1]) + TILE_BYTES);
+                    tma_store_commit();
+                }
+            }
+            if (whirl_run) {
+                rp.hornIncr = hbrake ? 0.0 : hincr;
+                rp.drumIncr = dbrake ? 0.0 : dincr;
+            }
+        }
+        if (valid) {
+            RampScalars &o = st->rp; /* this role's fields only: role 0 stores the others */
+            o.hornAcDc = rp.hornAcDc;
+            o.drumAcDc = rp.drumAcDc;
+            o.revSelect = rp.revSelect;
+            o.hornAngle = hang;
+            o.drumAngle = dang;
+            o.hornIncr = rp.hornIncr;
+            o.drumIncr = rp.drumIncr;
+            o.hornTarget = rp.hornTarget;
+            o.drumTarget = rp.drumTarget;
+            o.brakePos[0] = rp.brakePos[0];
+            o.brakePos[1] = rp.brakePos[1];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                o.oml[k] = rp.oml[k];
+            if (new_flags)
+                atomicOr(&o.errorFlags, new_flags);
+        }
+        if (lane == 0)
+            tma_store_wait_all();
+        return;
+    }
+
+    /* ---------------- role 0: mixdown, horn biquads, dx0 / hx0 ---------------- */
+    float cA[5], cB[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        cA[k] = rp.iir[0][k];
+        cB[k] = rp.iir[1][k];
+    }
+    float zA0 = rp.iirz[0][0], zA1 = rp.iirz[0][1], zB0 = rp.iirz[1][0], zB1 = rp.iirz[1][1];
+    float pg = rp.percEnvGain, kc = rp.keyCompLevel;
+    const uint32_t bar0 = smem_u32(&sm.bar[0]);
+    if (lane == 0) {
+        mbar_init(bar0, 1u);
+        mbar_init(bar0 + 8u, 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(bar0, 2u * TILE_BYTES);
+        tma_tile_load(smem_u32(sm.tin[0][0]), &maps.m32, 0u, p.tile_row[0] + slot0, bar0);
+        tma_tile_load(smem_u32(sm.tin[0][1]), &maps.m32, 0u, p.tile_row[1] + slot0, bar0);
+    }
+    uint32_t parity = 0u;
+    __syncwarp();
+
+    for (uint32_t f = 0; f < p.n_fragments; ++f) {
+        /* -- horn filter events that precede this fragment (the rotor's belong to role 1) -- */
+        while (ev_cur < ev_end) {
+            const tbf_event *evp = p.events + ev_cur;
+            if (evp->fragment > p.frag_base + f)
+                break;
+            if (evp->type == TBF_EV_HORN_FILTER) {
+                const int a = evp->a, k = a & 7;
+                if (a < 0 || a > 15 || k > 4) {
+                    new_flags |= TBF_IFLAG_BAD_EVENT;
+                } else {
+                    const float v = __int_as_float(evp->b);
+                    rp.iir[a >> 3][k] = v;
+#pragma unroll
+                    for (int j = 0; j < 5; ++j) {
+                        if (a == j)
+                            cA[j] = v;
+                        if (a == 8 + j)
+                            cB[j] = v;
+                    }
+                }
+            }
+            ++ev_cur;
+        }
+        FragCtl c_;
+        c_.key_comp = c_.gain = c_.decay = c_.reset = 0.0f;
+        c_.flags = 0;
+        if (valid && !ext_in)
+            c_ = p.ctl[(size_t)slot * p.n_fragments + f];
+        const bool perc_on = (c_.flags & FC_PERC_ON) != 0;
+        /* (keyComp - level) / 128.f: dividing by 2^7 and multiplying by 2^-7 round identically */
+        const float delta = __fmul_rn(__fsub_rn(c_.key_comp, kc), 0.0078125f);
+
+        for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
+            const uint32_t gb = f * (TBF_FRAGMENT / BLK) + (uint32_t)blk;
+            const size_t col0 = (size_t)gb * BLK;
+            const int cur = (int)(gb & 1u);
+            /* the next block's tiles are requested before this block's serial loop */
+            if (lane == 0 && gb + 1 < n_blocks) {
+                const uint32_t bar = bar0 + 8u * (uint32_t)(cur ^ 1);
+                mbar_expect_tx(bar, 2u * TILE_BYTES);
+                tma_tile_load(smem_u32(sm.tin[cur ^ 1][0]), &maps.m32, (gb + 1) * BLK, p.tile_row[0] + slot0, bar);
+                tma_tile_load(smem_u32(sm.tin[cur ^ 1][1]), &maps.m32, (gb + 1) * BLK, p.tile_row[1] + slot0, bar);
+            }
+            mbar_wait(bar0 + 8u * (uint32_t)cur, (parity >> cur) & 1u);
+            parity ^= 1u << cur;
+            if (lane == 0)
+                tma_store_wait_read(); /* the last block's output tiles have left shared memory */
+            __syncwarp();
+            const unsigned char *t_u = reinterpret_cast<const unsigned char *>(sm.tin[cur][0]);
+            const unsigned char *t_p = reinterpret_cast<const unsigned char *>(sm.tin[cur][1]);
+            unsigned char *o_x = reinterpret_cast<unsigned char *>(sm.tout[0]);
+            unsigned char *o_y = reinterpret_cast<unsigned char *>(sm.tout[1]);
+#pragma unroll 2
+            for (int c = 0; c < 8; ++c) { /* four samples = one 16-byte chunk of the lane's row */
+                const uint32_t o = tile_chunk(lane, c);
+                const float4 u4 = *reinterpret_cast<const float4 *>(t_u + o);
+                const float4 p4 = *reinterpret_cast<const float4 *>(t_p + o);
+                const float us[4] = {u4.x, u4.y, u4.z, u4.w}, ps[4] = {p4.x, p4.y, p4.z, p4.w};
+                float xs[4], ys[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float uu = us[e];
+                    float mono;
+                    if (ext_in) {
+                        mono = uu;
+                    } else {
+                        if (perc_on) {
+                            const float pterm = __fmul_rn(ps[e], pg);
+                            mono = __fmul_rn(__fmul_rn(c_.gain, kc), __fadd_rn(uu, pterm));
+                            pg = __fmul_rn(pg, c_.decay);
+                        } else {
+                            mono = __fmul_rn(__fmul_rn(c_.gain, kc), uu);
+                        }
+                        kc = __fadd_rn(kc, delta);
+                    }
+                    if (whirl_run) {
+                        const float x = (float)__dadd_rn((double)mono, 1e-14); /* DENORMAL_HACK */
+                        const float ya = eq_iir(cA, zA0, zA1, x);
+                        xs[e] = x;
+                        ys[e] = eq_iir(cB, zB0, zB1, ya);
+                    } else {
+                        xs[e] = mono;
+                        ys[e] = mono; /* bypassed Leslie: stage D mixes it */
+                    }
+                }
+                *reinterpret_cast<float4 *>(o_x + o) = make_float4(xs[0], xs[1], xs[2], xs[3]);
+                *reinterpret_cast<float4 *>(o_y + o) = make_float4(ys[0], ys[1], ys[2], ys[3]);
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_tile_store(&maps.m32, (uint32_t)col0, p.tile_row[2] + slot0, smem_u32(o_x));
+                tma_tile_store(&maps.m32, (uint32_t)col0, p.tile_row[3] + slot0, smem_u32(o_y));
+                tma_store_commit();
+            }
+        }
+
+        /* -- end of the fragment -- */
+        if (whirl_run) {
+            /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
+            zA0 = isnan(zA0) ? 0.0f : zA0;
+            zA1 = isnan(zA1) ? 0.0f : zA1;
+            zB0 = isnan(zB0) ? 0.0f : zB0;
+            zB1 = isnan(zB1) ? 0.0f : zB1;
+        }
+        if (c_.flags & FC_PERC_RESET)
+            pg = c_.reset;
+    }
+
+    if (valid) {
+        RampScalars &o = st->rp; /* this role's fields only */
+        o.iirz[0][0] = zA0;
+        o.iirz[0][1] = zA1;
+        o.iirz[1][0] = zB0;
+        o.iirz[1][1] = zB1;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            o.iir[0][k] = rp.iir[0][k];
+            o.iir[1][k] = rp.iir[1][k];
+        }
+        o.percEnvGain = pg;
+        o.keyCompLevel = kc;
+        if (new_flags)
+            atomicOr(&o.errorFlags, new_flags);
+        p.ev_cursor_r[slot] = ev_cur;
+    }
+    if (lane == 0)
+        tma_store_wait_all();
 }
 
 /* ================================================================== */
@@ -2573,6 +2919,110 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
     }
 }
 
+struct DTmaSmem {
+    float t[2][2][TILE_BYTES / 4]; /* [buffer][DL DR], swizzled boxes; 1024-byte aligned */
+    unsigned long long bar[2];
+};
+
+/* Stage D with TMA tiles: same arithmetic as tbf_stage_d, the two drum line reads filtered in place. */
+__global__ void __launch_bounds__(32) tbf_stage_d_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    DTmaSmem &sm = *reinterpret_cast<DTmaSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
+    const int lane = threadIdx.x;
+    const uint32_t slot0 = blockIdx.x * 32;
+    const uint32_t slot = slot0 + lane;
+    const bool valid = slot < p.n_instances;
+
+    InstState *st = nullptr;
+    const DevWhirlTables *wh = p.wh;
+    float zl0 = 0.f, zl1 = 0.f, zr0 = 0.f, zr1 = 0.f;
+    if (valid) {
+        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
+        st = p.states + id;
+        wh = p.wh + st->tg.whTables;
+        zl0 = st->dr.iirz[0][0];
+        zl1 = st->dr.iirz[0][1];
+        zr0 = st->dr.iirz[1][0];
+        zr1 = st->dr.iirz[1][1];
+    }
+    const bool run = valid && !wh->bypass;
+    if (!__any_sync(FULL, run))
+        return; /* every organ of the warp has its Leslie bypassed: nothing to filter */
+    float cL[5], cR[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        cL[k] = wh->iir[2][k];
+        cR[k] = wh->iir[3][k];
+    }
+    const uint32_t row_l = p.tile_row[6] + slot0, row_r = p.tile_row[7] + slot0; /* line[2], line[3] */
+    const uint32_t bar0 = smem_u32(&sm.bar[0]);
+    if (lane == 0) {
+        mbar_init(bar0, 1u);
+        mbar_init(bar0 + 8u, 1u);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(bar0, 2u * TILE_BYTES);
+        tma_tile_load(smem_u32(sm.t[0][0]), &maps.m32, 0u, row_l, bar0);
+        tma_tile_load(smem_u32(sm.t[0][1]), &maps.m32, 0u, row_r, bar0);
+    }
+    __syncwarp();
+    const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
+    uint32_t parity = 0u;
+    for (uint32_t blk = 0; blk < n_blocks; ++blk) {
+        const int cur = (int)(blk & 1u);
+        if (lane == 0 && blk + 1 < n_blocks) {
+            tma_store_wait_read(); /* the other buffer's store (block blk - 1) has left shared memory */
+            const uint32_t bar = bar0 + 8u * (uint32_t)(cur ^ 1);
+            mbar_expect_tx(bar, 2u * TILE_BYTES);
+            tma_tile_load(smem_u32(sm.t[cur ^ 1][0]), &maps.m32, (blk + 1) * BLK, row_l, bar);
+            tma_tile_load(smem_u32(sm.t[cur ^ 1][1]), &maps.m32, (blk + 1) * BLK, row_r, bar);
+        }
+        mbar_wait(bar0 + 8u * (uint32_t)cur, (parity >> cur) & 1u);
+        parity ^= 1u << cur;
+        unsigned char *tl = reinterpret_cast<unsigned char *>(sm.t[cur][0]);
+        unsigned char *tr = reinterpret_cast<unsigned char *>(sm.t[cur][1]);
+        if (run) {
+#pragma unroll 2
+            for (int c = 0; c < 8; ++c) {
+                const uint32_t o = tile_chunk(lane, c);
+                float4 a = *reinterpret_cast<float4 *>(tl + o), b = *reinterpret_cast<float4 *>(tr + o);
+                a.x = eq_iir(cL, zl0, zl1, a.x);
+                b.x = eq_iir(cR, zr0, zr1, b.x);
+                a.y = eq_iir(cL, zl0, zl1, a.y);
+                b.y = eq_iir(cR, zr0, zr1, b.y);
+                a.z = eq_iir(cL, zl0, zl1, a.z);
+                b.z = eq_iir(cR, zr0, zr1, b.z);
+                a.w = eq_iir(cL, zl0, zl1, a.w);
+                b.w = eq_iir(cR, zr0, zr1, b.w);
+                *reinterpret_cast<float4 *>(tl + o) = a;
+                *reinterpret_cast<float4 *>(tr + o) = b;
+            }
+            if ((blk & 3u) == 3u) { /* end of a fragment: NaN scrub (src/whirl.cpp:1624-1625) */
+                zl0 = isnan(zl0) ? 0.0f : zl0;
+                zl1 = isnan(zl1) ? 0.0f : zl1;
+                zr0 = isnan(zr0) ? 0.0f : zr0;
+                zr1 = isnan(zr1) ? 0.0f : zr1;
+            }
+        }
+        fence_async_smem(); /* this lane's writes, before the TMA store reads them */
+        __syncwarp();
+        if (lane == 0) {
+            tma_tile_store(&maps.m32, blk * BLK, row_l, smem_u32(tl));
+            tma_tile_store(&maps.m32, blk * BLK, row_r, smem_u32(tr));
+            tma_store_commit();
+        }
+    }
+    if (lane == 0)
+        tma_store_wait_all();
+    if (run) {
+        st->dr.iirz[0][0] = zl0;
+        st->dr.iirz[0][1] = zl1;
+        st->dr.iirz[1][0] = zr0;
+        st->dr.iirz[1][1] = zr1;
+    }
+}
+
 #define M_THREADS 256
 
 /* V consecutive floats as one access (V = 4: LDG.128 / STG.128) */
@@ -2919,6 +3369,14 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_r, sizeof(RSmem), have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
+    if (p.tile_maps && !(p.flags & TBF_RENDER_WHIRL_BYPASS)) {
+        static int have_tma[TBF_MAX_DEVICES] = {0};
+        if (int rc = set_smem(tbf_stage_r_tma, sizeof(RTmaSmem) + 1024, have_tma))
+            return rc;
+        tbf_stage_r_tma<<<grid, 64, sizeof(RTmaSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+        debug_sync(stream, "R");
+        return (int)cudaGetLastError();
+    }
     const bool r_csum = p.checksums && (p.flags & TBF_RENDER_WHIRL_BYPASS);
     const size_t smem = sizeof(RSmem) - (r_csum ? 0 : sizeof(RSmem::csum));
     /* the rotor warp has nothing to do when the Leslie is bypassed */
@@ -2945,7 +3403,10 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
+    if (p.tile_maps)
+        tbf_stage_d_tma<<<grid, 32, sizeof(DTmaSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+    else
+        tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
     debug_sync(stream, "D");
     const uint32_t n = p.n_fragments * TBF_FRAGMENT;
     /* float4 accesses when every output row starts 16-byte aligned (the stage streams always do) */
