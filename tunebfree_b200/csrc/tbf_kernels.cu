@@ -90,39 +90,60 @@ __device__ __forceinline__ unsigned f2u_x86(float f) { return (unsigned)(long lo
 /* run skips it, or the block ends) is completed by the last sample of  */
 /* the run before.  Distinct lanes own distinct slots: no atomics.      */
 /* ------------------------------------------------------------------ */
-__device__ __forceinline__ void ordered_pass_reg(const uint32_t n, const uint32_t n1, const uint32_t n2,
-                                                 const float a, const float b, float *ring,
-                                                 const uint32_t rmask, const uint32_t smask,
-                                                 const int lane)
+/* The pass, from two ballots instead of per-lane neighbour compares.  With n[] never decreasing,
+ * everything the pass has to know about its neighbours is in e (bit i: n[i] == n[i-1]) and d (bit i:
+ * n[i] == n[i-1] + 1): "n[i-2] hits n[i]-1" is d[i] & e[i-1], "n[i+1] hits n[i]" is e[i+1], "n[i+1]
+ * hits n[i]+1" is d[i+1].  Written without branches: a term that does not apply is replaced by -0.0f,
+ * whose addition changes no value (x + -0 = x for every x, -0 included), so all lanes run the same
+ * dozen instructions instead of the union of the branches.  When every sample lands exactly one slot
+ * after the one before (d all ones: a rotor that moved the tap by less than a slot in 32 samples --
+ * most blocks), slot n[i] takes b[i-1] then a[i] and nothing else has to be looked at. */
+struct RunBits {
+    uint32_t e, d;
+};
+__device__ __forceinline__ RunBits run_bits(const uint32_t n, const uint32_t smask, const int lane, uint32_t &dn)
 {
-    const uint32_t nx = __shfl_down_sync(FULL, n, 1);
-    const float b1 = __shfl_up_sync(FULL, b, 1), b2 = __shfl_up_sync(FULL, b, 2);
-    const float ax = __shfl_down_sync(FULL, a, 1);
-    const bool has1 = lane >= 1, has2 = lane >= 2, hasx = lane < BLK - 1;
-    if (!has1 || n1 != n) { /* first sample of the run hitting slot n */
-        float v = ring[n & rmask];
-        const uint32_t sm1 = (n - 1) & smask;
-        if (has2 && n2 == sm1)
-            v = __fadd_rn(v, b2);
-        if (has1 && n1 == sm1)
-            v = __fadd_rn(v, b1);
-        v = __fadd_rn(v, a);
-        if (hasx && nx == n)
-            v = __fadd_rn(v, ax);
-        ring[n & rmask] = v;
-    }
-    if (!hasx || nx != n) { /* last sample of its run */
-        const uint32_t sp1 = (n + 1) & smask;
-        if (!hasx || nx != sp1) { /* nobody hits n+1 as a main slot in this block */
-            float v = ring[sp1 & rmask];
-            if (has1 && n1 == n)
-                v = __fadd_rn(v, b1);
-            v = __fadd_rn(v, b);
-            ring[sp1 & rmask] = v;
-        }
-    }
+    const uint32_t n1 = __shfl_up_sync(FULL, n, 1);
+    dn = (n - n1) & smask;
+    RunBits r;
+    r.e = __ballot_sync(FULL, lane >= 1 && dn == 0u);
+    r.d = __ballot_sync(FULL, lane >= 1 && dn == 1u);
+    return r;
 }
-
+__device__ __forceinline__ void ordered_pass_bits(const uint32_t n, const RunBits rb, const float a, const float b,
+                                                  float *ring, const uint32_t rmask, const uint32_t smask,
+                                                  const int lane)
+{
+    const float nz = -0.0f;
+    const float b1 = __shfl_up_sync(FULL, b, 1);
+    const uint32_t sp1 = (n + 1) & smask;
+    if (rb.d == 0xFFFFFFFEu) { /* warp-uniform */
+        float v = ring[n & rmask];
+        v = __fadd_rn(v, lane ? b1 : nz);
+        v = __fadd_rn(v, a);
+        ring[n & rmask] = v;
+        if (lane == BLK - 1)
+            ring[sp1 & rmask] = __fadd_rn(ring[sp1 & rmask], b);
+        return;
+    }
+    const float b2 = __shfl_up_sync(FULL, b, 2);
+    const float ax = __shfl_down_sync(FULL, a, 1);
+    const uint32_t ee = rb.e >> lane, ep = (rb.e << 1) >> lane, dd = rb.d >> lane;
+    const bool e_i = (ee & 1u) != 0, e_x = (ee & 2u) != 0, e_p = (ep & 1u) != 0;
+    const bool d_i = (dd & 1u) != 0, d_x = (dd & 2u) != 0;
+    float v = ring[n & rmask];
+    float w = ring[sp1 & rmask]; /* a slot no lane has as its main slot whenever it is stored below */
+    v = __fadd_rn(v, (d_i && e_p) ? b2 : nz);
+    v = __fadd_rn(v, d_i ? b1 : nz);
+    v = __fadd_rn(v, a);
+    v = __fadd_rn(v, e_x ? ax : nz);
+    w = __fadd_rn(w, e_i ? b1 : nz);
+    w = __fadd_rn(w, b);
+    if (!e_i) /* first sample of the run hitting slot n */
+        ring[n & rmask] = v;
+    if (!e_x && !d_x) /* last sample of its run, and nobody hits n+1 as a main slot in this block */
+        ring[sp1 & rmask] = w;
+}
 
 /* ================================================================== */
 /* stage T: tone generator + scanner                                   */
@@ -1233,15 +1254,15 @@ __device__ __forceinline__ float vibrato_block(const DevTonegenTables *tg, TWarp
      * own sample's read position */
     const uint32_t rel = (h - op + (uint32_t)lane) & VBUF_MASK;
     int bad = (rel < (uint32_t)lane) || (rel + 1 >= (uint32_t)TBF_VRING);
-    const uint32_t h1 = __shfl_up_sync(FULL, h, 1), h2 = __shfl_up_sync(FULL, h, 2);
+    uint32_t dh;
+    const RunBits rb = run_bits(h, VBUF_MASK, lane, dh);
     if (lane >= 1)
-        bad |= ((h - h1) & VBUF_MASK) >= (TBF_VIB_BUF / 2);
-    if (lane >= 2)
-        bad |= (h2 == h);
+        bad |= dh >= (TBF_VIB_BUF / 2);
+    bad |= ((rb.e >> lane) & ((rb.e << 1) >> lane) & 1u) != 0u; /* three samples on one slot */
     bad = __any_sync(FULL, bad);
     float y;
     if (!bad) {
-        ordered_pass_reg(h, h1, h2, va, vb, sm.vring, VRING_MASK, VBUF_MASK, lane);
+        ordered_pass_bits(h, rb, va, vb, sm.vring, VRING_MASK, VBUF_MASK, lane);
         __syncwarp();
         y = sm.vring[op & VRING_MASK];
         sm.vring[op & VRING_MASK] = 0.0f;
@@ -2477,15 +2498,14 @@ __device__ __forceinline__ void tap_slot(const float2 d, float hd, float spacing
 /* What the parallel delay-line update relies on, checked per block and tap: the
  * destination slots advance monotonically with the sample index, at most two samples
  * share a slot, and all stay inside [reader, reader + window). */
-__device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t n1, const uint32_t n2,
+__device__ __forceinline__ int tap_bad(const uint32_t n, const uint32_t dn, const RunBits rb,
                                        const uint32_t window, const int lane, const uint32_t outpos_blk)
 {
     const uint32_t rel = (n - outpos_blk) & WBUF_MASK;
     int bad = (rel < (uint32_t)lane) | (rel + 1 >= window);
     if (lane >= 1)
-        bad |= ((n - n1) & WBUF_MASK) >= (TBF_WHIRL_BUF / 2);
-    if (lane >= 2)
-        bad |= (n2 == n);
+        bad |= dn >= (TBF_WHIRL_BUF / 2);
+    bad |= ((rb.e >> lane) & ((rb.e << 1) >> lane) & 1u) != 0u; /* three samples on one slot */
     return bad;
 }
 
@@ -2496,7 +2516,7 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_
                                                    float *ring_r, uint32_t rmask, int lane,
                                                    uint32_t outpos_blk, int bad, int gather_ok,
                                                    int &fell_back, const uint32_t (&tn)[6],
-                                                   const uint32_t (&tn1)[6], const uint32_t (&tn2)[6],
+                                                   const RunBits (&trb)[6],
                                                    const float (&ta)[6], const float (&tb)[6],
                                                    float &out_l, float &out_r)
 {
@@ -2505,9 +2525,8 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_
     if (!bad) {
 #pragma unroll
         for (int j = 0; j < 3; ++j) {
-            ordered_pass_reg(tn[j], tn1[j], tn2[j], ta[j], tb[j], ring_l, rmask, WBUF_MASK, lane);
-            ordered_pass_reg(tn[3 + j], tn1[3 + j], tn2[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, WBUF_MASK,
-                             lane);
+            ordered_pass_bits(tn[j], trb[j], ta[j], tb[j], ring_l, rmask, WBUF_MASK, lane);
+            ordered_pass_bits(tn[3 + j], trb[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, WBUF_MASK, lane);
             __syncwarp();
         }
         out_l = ring_l[op & rmask];
@@ -2572,7 +2591,7 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_
 template <bool DRUM, bool FAST, bool CERT>
 __device__ __forceinline__ void block_taps(const WWarp &sm, const int i, const double ang, const uint32_t outpos,
                                            const uint32_t outpos_blk, const uint32_t window, const int lane,
-                                           uint32_t (&tn)[6], uint32_t (&tn1)[6], uint32_t (&tn2)[6],
+                                           uint32_t (&tn)[6], RunBits (&trb)[6],
                                            float (&ta)[6], float (&tb)[6], int &bad)
 {
     float d0 = 0.f, d1 = 0.f, d2 = 0.f;
@@ -2624,10 +2643,10 @@ __device__ __forceinline__ void block_taps(const WWarp &sm, const int i, const d
             const float qq = __fmul_rn(xa, frac);
             ta[j] = __fsub_rn(xa, qq);
             tb[j] = qq;
-            tn1[j] = __shfl_up_sync(FULL, tn[j], 1);
-            tn2[j] = __shfl_up_sync(FULL, tn[j], 2);
+            uint32_t dn;
+            trb[j] = run_bits(tn[j], WBUF_MASK, lane, dn);
             if (!CERT) /* CERT: the host bounded the slot motion (DevWhirlTables::taps_certified) */
-                bad |= tap_bad(tn[j], tn1[j], tn2[j], window, lane, outpos_blk);
+                bad |= tap_bad(tn[j], dn, trb[j], window, lane, outpos_blk);
         }
     }
 }
@@ -2736,20 +2755,21 @@ __device__ __forceinline__ void stage_w_half(const RenderParams &p, const uint32
             /* the conversion-free index math needs the angle in [+0, limit): sign bit clear */
             const bool fast = small_index &&
                               __all_sync(FULL, __double_as_longlong(ang) >= 0 && ang < max_ang);
-            uint32_t tn[6], tn1[6], tn2[6];
+            uint32_t tn[6];
+            RunBits trb[6];
             float ta[6], tb[6];
             int bad = gather_ok ? 0 : 1;
             /* one warp-uniform branch per block, not per tap: inside a variant the six taps are
              * straight-line code, so their table reads overlap */
             if (fast && certified)
-                block_taps<DRUM, true, true>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+                block_taps<DRUM, true, true>(sm, i, ang, outpos, outpos_blk, window, lane, tn, trb, ta, tb, bad);
             else if (fast)
-                block_taps<DRUM, true, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+                block_taps<DRUM, true, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, trb, ta, tb, bad);
             else
-                block_taps<DRUM, false, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, tn1, tn2, ta, tb, bad);
+                block_taps<DRUM, false, false>(sm, i, ang, outpos, outpos_blk, window, lane, tn, trb, ta, tb, bad);
             float o_l, o_r;
             group_scatter_read(&sm.tap[0], ring, ring + ring_size, rmask, lane, outpos_blk, bad,
-                               gather_ok ? 1 : 0, fell_back, tn, tn1, tn2, ta, tb, o_l, o_r);
+                               gather_ok ? 1 : 0, fell_back, tn, trb, ta, tb, o_l, o_r);
             out_l_row[col + i] = o_l;
             out_r_row[col + i] = o_r;
         }
