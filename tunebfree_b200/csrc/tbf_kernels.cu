@@ -95,9 +95,10 @@ __device__ __forceinline__ unsigned f2u_x86(float f) { return (unsigned)(long lo
  * n[i] == n[i-1] + 1): "n[i-2] hits n[i]-1" is d[i] & e[i-1], "n[i+1] hits n[i]" is e[i+1], "n[i+1]
  * hits n[i]+1" is d[i+1].  Written without branches: a term that does not apply is replaced by -0.0f,
  * whose addition changes no value (x + -0 = x for every x, -0 included), so all lanes run the same
- * dozen instructions instead of the union of the branches.  When every sample lands exactly one slot
- * after the one before (d all ones: a rotor that moved the tap by less than a slot in 32 samples --
- * most blocks), slot n[i] takes b[i-1] then a[i] and nothing else has to be looked at. */
+ * dozen instructions instead of the union of the branches.  When no two samples share a slot (e
+ * empty: most blocks, a tap moves by less than a slot in 32 samples most of the time) every lane owns
+ * slot n[i], which takes b[i-1] if the sample before sits right below, then a[i]; slot n[i]+1 is
+ * completed with b[i] where the next sample skips it. */
 struct RunBits {
     uint32_t e, d;
 };
@@ -117,13 +118,16 @@ __device__ __forceinline__ void ordered_pass_bits(const uint32_t n, const RunBit
     const float nz = -0.0f;
     const float b1 = __shfl_up_sync(FULL, b, 1);
     const uint32_t sp1 = (n + 1) & smask;
-    if (rb.d == 0xFFFFFFFEu) { /* warp-uniform */
+    if (rb.e == 0u) { /* warp-uniform: no slot is hit twice, every lane owns its slot n */
+        const uint32_t dd = rb.d >> lane;
         float v = ring[n & rmask];
-        v = __fadd_rn(v, lane ? b1 : nz);
+        float w = ring[sp1 & rmask]; /* stored only where no lane has n+1 as its own slot */
+        v = __fadd_rn(v, (dd & 1u) ? b1 : nz);
         v = __fadd_rn(v, a);
+        w = __fadd_rn(w, b);
         ring[n & rmask] = v;
-        if (lane == BLK - 1)
-            ring[sp1 & rmask] = __fadd_rn(ring[sp1 & rmask], b);
+        if (!(dd & 2u))
+            ring[sp1 & rmask] = w;
         return;
     }
     const float b2 = __shfl_up_sync(FULL, b, 2);
