@@ -206,6 +206,7 @@ struct tbf_ctx {
     uint32_t prepared_chunk = 0;
     uint32_t host_chunk_fragments = 125; /* 1/3 s of audio per staging chunk */
     int prepared_ring = 512; /* stage W's shared-memory ring: the largest the batch's whirl sets need */
+    uint32_t prepared_tg_sets = 0; /* distinct tone-generator table sets among the batch's organs */
     cudaStream_t copy_stream = nullptr, copy_stream2 = nullptr; /* left / right channel */
     cudaEvent_t render_done[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr},
                 copy_done2[2] = {nullptr, nullptr};
@@ -1421,6 +1422,20 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
             ring = std::max(ring, ctx->wh[ctx->inst_wh[d->instance_ids ? d->instance_ids[i] : i]].ring_size);
         ctx->prepared_ring = ring;
     }
+    /* how many tone-generator table sets the batch's organs share: stage T picks its sample mover by
+     * it (many organs per set: the waves stay in L2; one set per organ: they come from HBM) */
+    {
+        std::vector<uint8_t> used(ctx->tg.size(), 0);
+        uint32_t sets = 0;
+        for (uint32_t i = 0; i < d->n_instances; ++i) {
+            const int h = ctx->inst_tg[d->instance_ids ? d->instance_ids[i] : i];
+            if (h >= 0 && (size_t)h < used.size() && !used[h]) {
+                used[h] = 1;
+                ++sets;
+            }
+        }
+        ctx->prepared_tg_sets = sets;
+    }
     /* events: sorted by (slot, fragment); build the per-slot CSR */
     std::vector<uint64_t> &evs = ctx->ev_start_host;
     evs.assign((size_t)d->n_instances + 1, 0);
@@ -1582,6 +1597,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     base_p.flags = d->flags | (getenv("TBF_NO_FAST_PASS") ? 0x100u : 0u) | (getenv("TBF_NO_PAIRS") ? 0x200u : 0u);
     base_p.pitch = pitch;
     base_p.one = 1.0f;
+    base_p.tg_sets = ctx->prepared_tg_sets;
     ctx->launches = 0;
     const int ring = ctx->prepared_ring;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));

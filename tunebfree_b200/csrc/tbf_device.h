@@ -234,6 +234,7 @@ struct RenderParams {
     float *line[4];            /* W -> D: delay-line reads HL HR DL DR                  */
     uint64_t pitch;            /* elements per slot row of every stream                 */
     float one;                 /* 1.0f, as a run-time value (tbf_kernels.cu: add2_via_fma) */
+    uint32_t tg_sets;          /* tone-generator table sets the batch's organs share (0: unknown) */
     /* 2-D TMA tiles (stages R and D): the launch's first slot as a row of the tensor maps, per plane
      * u php dx0 hx0 line[0..3] (float map) and hang dang (double map); tile_maps = host pointer to the
      * maps, NULL when the scratch layout has none (then the kernels move tiles with cp.async) */

@@ -3337,7 +3337,9 @@ size_t tbf_stage_w_smem(int ring_size)
 template <int SLOTS> static int launch_stage_t(const RenderParams &p, cudaStream_t stream)
 {
     static int have[TBF_MAX_DEVICES] = {0};
-    const size_t smem = (sizeof(TWarp) + (size_t)(SLOTS <= -10 ? 2 : SLOTS < 0 ? -SLOTS : SLOTS) * 1024) * T_WARPS;
+    /* experiment: TBF_T_PAD_KB pads the CTA's shared memory, i.e. caps stage T's CTAs per SM */
+    static const size_t pad = getenv("TBF_T_PAD_KB") ? (size_t)atoi(getenv("TBF_T_PAD_KB")) * 1024 : 0;
+    const size_t smem = (sizeof(TWarp) + (size_t)(SLOTS <= -10 ? 2 : SLOTS < 0 ? -SLOTS : SLOTS) * 1024) * T_WARPS + pad;
     if (int rc = set_smem(tbf_stage_t<SLOTS>, smem, have))
         return rc;
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
@@ -3362,8 +3364,13 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
     const uint32_t grid = (p.n_instances + T_WARPS - 1) / T_WARPS;
     const bool small = grid <= 148u * 3u; /* fewer than three CTAs per SM: a warp's own loads are all
                                              that hides their latency */
+    /* Organs that share table sets read their waves out of L2 and direct loads win (config 3: 185 k
+     * organ-s/s against 172 k with bulk copies).  With a table set per organ (config 4) every wave
+     * comes from HBM, and what hides that latency is depth, without registers: six wheels in flight
+     * through shared memory (per-lane cp.async 181 k, bulk copies 168 k, direct loads 154 - 164 k). */
+    const bool from_hbm = p.tg_sets && (uint64_t)p.tg_sets * 8u > p.n_instances;
     if (!mover)
-        mover = 3;
+        mover = from_hbm ? 2 : 3;
     int rc;
     if (mover == 3) {
         const int depth = forced ? forced : (small ? 4 : 2);
@@ -3371,7 +3378,7 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
              : depth == 3 ? launch_stage_t<-13>(p, (cudaStream_t)stream)
                           : launch_stage_t<-12>(p, (cudaStream_t)stream);
     } else {
-        const int slots = forced ? forced : (small ? 6 : 2);
+        const int slots = forced ? forced : ((small || from_hbm) ? 6 : 2);
         if (mover == 2)
             rc = slots >= 6   ? launch_stage_t<-6>(p, (cudaStream_t)stream)
                  : slots >= 3 ? launch_stage_t<-3>(p, (cudaStream_t)stream)
@@ -3412,7 +3419,9 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
 int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
 {
     static int have[TBF_MAX_DEVICES] = {0};
-    const size_t smem = tbf_stage_w_smem(ring_size);
+    /* experiment: TBF_W_PAD_KB pads the CTA's shared memory, i.e. caps stage W's CTAs per SM */
+    static const size_t pad = getenv("TBF_W_PAD_KB") ? (size_t)atoi(getenv("TBF_W_PAD_KB")) * 1024 : 0;
+    const size_t smem = tbf_stage_w_smem(ring_size) + pad;
     if (int rc = set_smem(tbf_stage_w, smem, have))
         return rc;
     const dim3 grid((p.n_instances + W_WARPS - 1) / W_WARPS, 2); /* y: horn halves, drum halves */
