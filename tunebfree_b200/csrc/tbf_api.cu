@@ -1559,16 +1559,17 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     /* tensor maps of the scratch as it is laid out for this batch (TBF_NO_TMA_TILES=1: none, the
      * lane = organ kernels then move their tiles with cp.async) */
     static const bool no_tiles = getenv("TBF_NO_TMA_TILES") != nullptr;
-    bool tiles = whirl && !no_tiles && !(d->flags & 0x8000u);
-    if (tiles && !(ss.maps_ok && ss.map_f32 == ss.f32 && ss.map_f64 == ss.f64 && ss.map_pitch == pitch &&
-                   ss.map_rows32 == nb * np * planes32 && ss.map_rows64 == nb * np * 2)) {
+    bool tiles = !no_tiles && !(d->flags & 0x8000u);
+    const size_t rows64 = whirl ? nb * np * 2 : 0; /* a bypass-only batch has no angle planes */
+    if (tiles && !(ss.maps_ok && ss.map_f32 == ss.f32 && ss.map_f64 == (whirl ? ss.f64 : nullptr) &&
+                   ss.map_pitch == pitch && ss.map_rows32 == nb * np * planes32 && ss.map_rows64 == rows64)) {
         ss.maps_ok = tile_map_make(&ss.maps.m32, ss.f32, pitch, nb * np * planes32) &&
-                     tile_map_make(&ss.maps.m64, ss.f64, 2 * pitch, nb * np * 2);
+                     (!whirl || tile_map_make(&ss.maps.m64, ss.f64, 2 * pitch, rows64));
         ss.map_f32 = ss.f32;
-        ss.map_f64 = ss.f64;
+        ss.map_f64 = whirl ? ss.f64 : nullptr;
         ss.map_pitch = pitch;
         ss.map_rows32 = nb * np * planes32;
-        ss.map_rows64 = nb * np * 2;
+        ss.map_rows64 = rows64;
     }
     tiles = tiles && ss.maps_ok;
 

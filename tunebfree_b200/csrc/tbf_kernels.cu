@@ -2099,6 +2099,8 @@ struct RTmaSmem {
     float tout[2][TILE_BYTES / 4];   /* dx0, hx0 */
     double tang[2][2 * TILE_BYTES / 8]; /* horn, drum angle: two boxes of 16 samples each */
     unsigned long long bar[2];
+    unsigned long long csum[BLK][BLK]; /* LAST: only in the launch's shared memory when stage R forms
+                                          the checksum (bypass-only batch with checksums) */
 };
 __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
 {
@@ -2264,6 +2266,12 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
     }
     float zA0 = rp.iirz[0][0], zA1 = rp.iirz[0][1], zB0 = rp.iirz[1][0], zB1 = rp.iirz[1][1];
     float pg = rp.percEnvGain, kc = rp.keyCompLevel;
+    const uint32_t rows = min(32u, p.n_instances - slot0);
+    const bool store = !(p.flags & TBF_RENDER_NO_OUTPUT);
+    const bool out_vec = (p.out_stride % 4) == 0 && (((uintptr_t)p.out_l | (uintptr_t)p.out_r) & 15u) == 0;
+    if (p.checksums && whirl_off) /* csum lies past the launch's shared memory otherwise */
+        for (int r = 0; r < BLK; ++r)
+            sm.csum[r][lane] = 0ull;
     const uint32_t bar0 = smem_u32(&sm.bar[0]);
     if (lane == 0) {
         mbar_init(bar0, 1u);
@@ -2365,6 +2373,39 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
                 *reinterpret_cast<float4 *>(o_x + o) = make_float4(xs[0], xs[1], xs[2], xs[3]);
                 *reinterpret_cast<float4 *>(o_y + o) = make_float4(ys[0], ys[1], ys[2], ys[3]);
             }
+            if (whirl_off) {
+                /* the whole batch bypasses the Leslie: L = R = mono, straight to the output rows;
+                 * lane = four samples of a row, eight lanes per row, four rows per trip */
+                __syncwarp();
+                if (store) {
+                    const int c = lane & 7;
+                    if (out_vec) {
+#pragma unroll 2
+                        for (uint32_t r = (uint32_t)lane >> 3; r < rows; r += 4) {
+                            const float4 m = *reinterpret_cast<const float4 *>(o_x + tile_chunk((int)r, c));
+                            const size_t g = (size_t)(slot0 + r) * p.out_stride + col0 + 4 * c;
+                            *reinterpret_cast<float4 *>(p.out_l + g) = m;
+                            *reinterpret_cast<float4 *>(p.out_r + g) = m;
+                        }
+                    } else {
+                        for (uint32_t r = 0; r < rows; ++r) {
+                            const float m = *reinterpret_cast<const float *>(o_x + tile_chunk((int)r, lane >> 2) + 4 * (lane & 3));
+                            const size_t g = (size_t)(slot0 + r) * p.out_stride + col0 + lane;
+                            p.out_l[g] = m;
+                            p.out_r[g] = m;
+                        }
+                    }
+                }
+                if (p.checksums) {
+                    for (uint32_t r = 0; r < rows; ++r) {
+                        const float m = *reinterpret_cast<const float *>(o_x + tile_chunk((int)r, lane >> 2) + 4 * (lane & 3));
+                        const uint32_t pos = (uint32_t)((size_t)p.frag_base * TBF_FRAGMENT + col0 + lane);
+                        sm.csum[r][lane] += sample_hash(pos, m, m);
+                    }
+                }
+                __syncwarp();
+                continue;
+            }
             fence_async_smem();
             __syncwarp();
             if (lane == 0) {
@@ -2402,6 +2443,12 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
         if (new_flags)
             atomicOr(&o.errorFlags, new_flags);
         p.ev_cursor_r[slot] = ev_cur;
+        if (p.checksums && whirl_off) {
+            unsigned long long c = 0ull;
+            for (int j = 0; j < BLK; ++j)
+                c += sm.csum[lane][(j + lane) & (BLK - 1)];
+            p.checksums[slot] += c; /* zeroed by the host; accumulates over chunks */
+        }
     }
     if (lane == 0)
         tma_store_wait_all();
@@ -3400,11 +3447,14 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_r, sizeof(RSmem), have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    if (p.tile_maps && !(p.flags & TBF_RENDER_WHIRL_BYPASS)) {
+    if (p.tile_maps) {
         static int have_tma[TBF_MAX_DEVICES] = {0};
+        const bool bypass = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
+        const size_t smem = sizeof(RTmaSmem) + 1024 - ((p.checksums && bypass) ? 0 : sizeof(RTmaSmem::csum));
         if (int rc = set_smem(tbf_stage_r_tma, sizeof(RTmaSmem) + 1024, have_tma))
             return rc;
-        tbf_stage_r_tma<<<grid, 64, sizeof(RTmaSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+        /* the rotor warp has nothing to do when the Leslie is bypassed */
+        tbf_stage_r_tma<<<grid, bypass ? 32 : 64, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
         debug_sync(stream, "R");
         return (int)cudaGetLastError();
     }
