@@ -99,8 +99,12 @@ def _check_sass():
         m = re.search(r"\bFFMA\s+(\S+), (\S+), (\S+), (\S+) ;", line)
         if m:
             assert "RZ" in (m.group(2), m.group(3)), "a fused float multiply-add: " + line.strip()
-    # the wave tables reach shared memory by TMA bulk copies with mbarrier completion
+    # stage T's bulk-copy variants stage the waves in shared memory by TMA (UBLKCP) with mbarrier
+    # completion (SYNCS); stages R and D move their organ x sample tiles by 2-D tensor-map TMA
+    # (UTMALDG loads, UTMASTG stores); stage T's default loads are 128-bit
     assert "UBLKCP" in sass and "SYNCS" in sass
+    assert "UTMALDG" in sass and "UTMASTG" in sass
+    assert re.search(r"\bLDG\.E\.128", sass)
 
 
 def test_no_contracted_packed_fma_in_kernels():
