@@ -1422,7 +1422,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, SLOTS <= -10 ? T_DIRECT_CTAS(-SL
     const DevTonegenTables *tg = p.tg + sc.tgTables;
     if (lane == 0)
         sm.wave4 = tg->wave4;
-    bool no_neg_zero = true; /* no -0 in the scanner's delay line (quiet_buses) */
+    bool no_neg_zero = true; /* no -0 in the scanner's delay line (quiet_sum) */
     for (int s = lane; s < TBF_VRING; s += 32) {
         const uint32_t g = (sc.vibOutPos + (uint32_t)s) & VBUF_MASK;
         const float y = st->vibBuffer[g];
@@ -1431,10 +1431,7 @@ __global__ void __launch_bounds__(T_WARPS * 32, SLOTS <= -10 ? T_DIRECT_CTAS(-SL
     }
     no_neg_zero = __all_sync(FULL, no_neg_zero);
     constexpr bool DIRECT = SLOTS <= -10;
-#ifndef TBF_BUS_DEPTH
-#define TBF_BUS_DEPTH 3
-#endif
-    constexpr int BUS_DEPTH = TBF_BUS_DEPTH;
+    constexpr int BUS_DEPTH = 3; /* list entries in flight in the bus-by-bus loops */
     constexpr int DIRECT_DEPTH = DIRECT ? -SLOTS - 10 : 2;
     bool lists_valid = false;
     uint64_t ev_cur = p.ev_cursor_t[slot];
@@ -3398,7 +3395,7 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
 {
     /* How the wheels' samples reach the sums (profiles/r02_kernels.md has the sweeps):
      *   direct  -- LDG.128 straight into registers, a few records ahead; quiet fragments bus by bus
-     *              over the records with a non-zero gain (quiet_buses).  The default.
+     *              over the records with a non-zero gain or masked to the buses in use (quiet_sum).
      *   tma     -- bulk copies (cp.async.bulk + mbarrier) through 2 / 3 / 6 staging slots per warp
      *   cpasync -- per-lane cp.async through 2 / 3 / 6 slots
      * TBF_T_LOADS = direct | tma | cpasync or the TBF_RENDER_DEBUG_T_* flag bits pick one,
