@@ -1764,6 +1764,12 @@ __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk
 /* the committed stores have READ their shared-memory source (it may be overwritten) */
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+/* all but the most recently committed store have read their shared-memory source */
+__device__ __forceinline__ void tma_store_wait_read_but_one() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 /* byte offset of 16-byte chunk c (4 floats / 2 doubles) of row r inside a 32-row, 128-byte-row tile */
 __device__ __forceinline__ uint32_t tile_chunk(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
 
@@ -2093,19 +2099,23 @@ __global__ void __launch_bounds__(64) tbf_stage_r(const RenderParams p)
  * read / written by every lane as 16-byte chunks of its own row (tile_chunk). */
 struct RTmaSmem {
     float tin[2][2][TILE_BYTES / 4]; /* [buffer][u, php], filled by TMA one block ahead */
-    float tout[2][TILE_BYTES / 4];   /* dx0, hx0 */
+    float tout[3][TILE_BYTES / 4];   /* dx0, hx0; three-warp form: dx0 tile 0, dx0 tile 1, hx0 */
     double tang[2][2 * TILE_BYTES / 8]; /* horn, drum angle: two boxes of 16 samples each */
-    unsigned long long bar[2];
+    unsigned long long bar[6];       /* input tiles landed [2]; x tile written [2], read [2] */
     unsigned long long csum[BLK][BLK]; /* LAST: only in the launch's shared memory when stage R forms
                                           the checksum (bypass-only batch with checksums) */
 };
-__global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+template <bool SPLIT>
+__global__ void __launch_bounds__(SPLIT ? 96 : 64) tbf_stage_r_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     RTmaSmem &sm = *reinterpret_cast<RTmaSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
     const int lane = threadIdx.x & 31;
-    const bool rotors = (threadIdx.x >> 5) != 0; /* warp-uniform role */
+    /* warp-uniform roles: warp 0 mixes down (and, unless SPLIT, runs the horn biquads), warp 1 the
+     * rotors, warp 2 (SPLIT) the horn biquads one block behind warp 0 */
+    const bool rotors = (threadIdx.x >> 5) == 1;
+    const bool filters = SPLIT && (threadIdx.x >> 5) == 2;
     const uint32_t slot0 = blockIdx.x * 32;
     const uint32_t slot = slot0 + lane;
     const bool valid = slot < p.n_instances;
@@ -2115,6 +2125,16 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
     const bool ext_in = (p.flags & TBF_RENDER_WHIRL_INPUT) != 0;
     if (rotors && whirl_off)
         return;
+    const uint32_t bar0 = smem_u32(&sm.bar[0]);
+    if (SPLIT) { /* bar[0..1]: input tiles landed; [2..3]: x tile b written; [4..5]: x tile b read */
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int j = 0; j < 6; ++j)
+                mbar_init(bar0 + 8u * j, 1u);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+    }
 
     InstState *st = nullptr;
     const DevWhirlTables *wh = p.wh;
@@ -2254,6 +2274,102 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
         return;
     }
 
+    if (filters) {
+        /* ---------------- role 2 (SPLIT): horn biquads A and B, x tile -> hx0 ---------------- */
+        float cA[5], cB[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            cA[k] = rp.iir[0][k];
+            cB[k] = rp.iir[1][k];
+        }
+        float zA0 = rp.iirz[0][0], zA1 = rp.iirz[0][1], zB0 = rp.iirz[1][0], zB1 = rp.iirz[1][1];
+        uint32_t par_full = 0u;
+        unsigned char *o_y = reinterpret_cast<unsigned char *>(sm.tout[2]);
+        for (uint32_t f = 0; f < p.n_fragments; ++f) {
+            /* horn filter events that precede this fragment (the rotor's belong to role 1) */
+            while (ev_cur < ev_end) {
+                const tbf_event *evp = p.events + ev_cur;
+                if (evp->fragment > p.frag_base + f)
+                    break;
+                if (evp->type == TBF_EV_HORN_FILTER) {
+                    const int a = evp->a, k = a & 7;
+                    if (a < 0 || a > 15 || k > 4) {
+                        new_flags |= TBF_IFLAG_BAD_EVENT;
+                    } else {
+                        const float v = __int_as_float(evp->b);
+                        rp.iir[a >> 3][k] = v;
+#pragma unroll
+                        for (int j = 0; j < 5; ++j) {
+                            if (a == j)
+                                cA[j] = v;
+                            if (a == 8 + j)
+                                cB[j] = v;
+                        }
+                    }
+                }
+                ++ev_cur;
+            }
+            for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
+                const uint32_t gb = f * (TBF_FRAGMENT / BLK) + (uint32_t)blk;
+                const int cur = (int)(gb & 1u);
+                mbar_wait(bar0 + 8u * (uint32_t)(2 + cur), (par_full >> cur) & 1u); /* x tile written */
+                par_full ^= 1u << cur;
+                if (lane == 0)
+                    tma_store_wait_read(); /* the last block's hx0 tile has left shared memory */
+                __syncwarp();
+                const unsigned char *t_x = reinterpret_cast<const unsigned char *>(sm.tout[cur]);
+#pragma unroll 2
+                for (int c = 0; c < 8; ++c) {
+                    const uint32_t o = tile_chunk(lane, c);
+                    const float4 x4 = *reinterpret_cast<const float4 *>(t_x + o);
+                    const float xs[4] = {x4.x, x4.y, x4.z, x4.w};
+                    float ys[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        if (whirl_run) {
+                            const float ya = eq_iir(cA, zA0, zA1, xs[e]);
+                            ys[e] = eq_iir(cB, zB0, zB1, ya);
+                        } else {
+                            ys[e] = xs[e]; /* bypassed Leslie: stage D mixes it */
+                        }
+                    }
+                    *reinterpret_cast<float4 *>(o_y + o) = make_float4(ys[0], ys[1], ys[2], ys[3]);
+                }
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(bar0 + 8u * (uint32_t)(4 + cur)); /* x tile read: warp 0 may refill it */
+                    tma_tile_store(&maps.m32, gb * BLK, p.tile_row[3] + slot0, smem_u32(o_y));
+                    tma_store_commit();
+                }
+            }
+            if (whirl_run) { /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
+                zA0 = isnan(zA0) ? 0.0f : zA0;
+                zA1 = isnan(zA1) ? 0.0f : zA1;
+                zB0 = isnan(zB0) ? 0.0f : zB0;
+                zB1 = isnan(zB1) ? 0.0f : zB1;
+            }
+        }
+        if (valid) {
+            RampScalars &o = st->rp; /* this role's fields only */
+            o.iirz[0][0] = zA0;
+            o.iirz[0][1] = zA1;
+            o.iirz[1][0] = zB0;
+            o.iirz[1][1] = zB1;
+#pragma unroll
+            for (int k = 0; k < 5; ++k) {
+                o.iir[0][k] = rp.iir[0][k];
+                o.iir[1][k] = rp.iir[1][k];
+            }
+            if (new_flags)
+                atomicOr(&o.errorFlags, new_flags);
+            p.ev_cursor_r[slot] = ev_cur;
+        }
+        if (lane == 0)
+            tma_store_wait_all();
+        return;
+    }
+
     /* ---------------- role 0: mixdown, horn biquads, dx0 / hx0 ---------------- */
     float cA[5], cB[5];
 #pragma unroll
@@ -2269,21 +2385,23 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
     if (p.checksums && whirl_off) /* csum lies past the launch's shared memory otherwise */
         for (int r = 0; r < BLK; ++r)
             sm.csum[r][lane] = 0ull;
-    const uint32_t bar0 = smem_u32(&sm.bar[0]);
     if (lane == 0) {
-        mbar_init(bar0, 1u);
-        mbar_init(bar0 + 8u, 1u);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (!SPLIT) {
+            mbar_init(bar0, 1u);
+            mbar_init(bar0 + 8u, 1u);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
         mbar_expect_tx(bar0, 2u * TILE_BYTES);
         tma_tile_load(smem_u32(sm.tin[0][0]), &maps.m32, 0u, p.tile_row[0] + slot0, bar0);
         tma_tile_load(smem_u32(sm.tin[0][1]), &maps.m32, 0u, p.tile_row[1] + slot0, bar0);
     }
-    uint32_t parity = 0u;
+    uint32_t parity = 0u, par_empty = 0u;
     __syncwarp();
 
     for (uint32_t f = 0; f < p.n_fragments; ++f) {
-        /* -- horn filter events that precede this fragment (the rotor's belong to role 1) -- */
-        while (ev_cur < ev_end) {
+        /* -- horn filter events that precede this fragment (the rotor's belong to role 1; with SPLIT
+         *    warp 2 applies them and this warp has nothing to look for) -- */
+        while (!SPLIT && ev_cur < ev_end) {
             const tbf_event *evp = p.events + ev_cur;
             if (evp->fragment > p.frag_base + f)
                 break;
@@ -2327,13 +2445,23 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
             }
             mbar_wait(bar0 + 8u * (uint32_t)cur, (parity >> cur) & 1u);
             parity ^= 1u << cur;
-            if (lane == 0)
+            if (SPLIT) {
+                /* x tile `cur` is free: warp 2 has read block gb - 2 out of it (and this warp's own
+                 * store of that block, the one but last committed, has left shared memory) */
+                if (gb >= 2) {
+                    mbar_wait(bar0 + 8u * (uint32_t)(4 + cur), (par_empty >> cur) & 1u);
+                    par_empty ^= 1u << cur;
+                }
+                if (lane == 0)
+                    tma_store_wait_read_but_one();
+            } else if (lane == 0) {
                 tma_store_wait_read(); /* the last block's output tiles have left shared memory */
+            }
             __syncwarp();
             const unsigned char *t_u = reinterpret_cast<const unsigned char *>(sm.tin[cur][0]);
             const unsigned char *t_p = reinterpret_cast<const unsigned char *>(sm.tin[cur][1]);
-            unsigned char *o_x = reinterpret_cast<unsigned char *>(sm.tout[0]);
-            unsigned char *o_y = reinterpret_cast<unsigned char *>(sm.tout[1]);
+            unsigned char *o_x = reinterpret_cast<unsigned char *>(sm.tout[SPLIT ? cur : 0]);
+            unsigned char *o_y = reinterpret_cast<unsigned char *>(sm.tout[SPLIT ? 2 : 1]);
 #pragma unroll 2
             for (int c = 0; c < 8; ++c) { /* four samples = one 16-byte chunk of the lane's row */
                 const uint32_t o = tile_chunk(lane, c);
@@ -2359,16 +2487,19 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
                     }
                     if (whirl_run) {
                         const float x = (float)__dadd_rn((double)mono, 1e-14); /* DENORMAL_HACK */
-                        const float ya = eq_iir(cA, zA0, zA1, x);
                         xs[e] = x;
-                        ys[e] = eq_iir(cB, zB0, zB1, ya);
+                        if (!SPLIT) {
+                            const float ya = eq_iir(cA, zA0, zA1, x);
+                            ys[e] = eq_iir(cB, zB0, zB1, ya);
+                        }
                     } else {
                         xs[e] = mono;
                         ys[e] = mono; /* bypassed Leslie: stage D mixes it */
                     }
                 }
                 *reinterpret_cast<float4 *>(o_x + o) = make_float4(xs[0], xs[1], xs[2], xs[3]);
-                *reinterpret_cast<float4 *>(o_y + o) = make_float4(ys[0], ys[1], ys[2], ys[3]);
+                if (!SPLIT)
+                    *reinterpret_cast<float4 *>(o_y + o) = make_float4(ys[0], ys[1], ys[2], ys[3]);
             }
             if (whirl_off) {
                 /* the whole batch bypasses the Leslie: L = R = mono, straight to the output rows;
@@ -2407,13 +2538,16 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
             __syncwarp();
             if (lane == 0) {
                 tma_tile_store(&maps.m32, (uint32_t)col0, p.tile_row[2] + slot0, smem_u32(o_x));
-                tma_tile_store(&maps.m32, (uint32_t)col0, p.tile_row[3] + slot0, smem_u32(o_y));
+                if (!SPLIT)
+                    tma_tile_store(&maps.m32, (uint32_t)col0, p.tile_row[3] + slot0, smem_u32(o_y));
                 tma_store_commit();
+                if (SPLIT)
+                    mbar_arrive(bar0 + 8u * (uint32_t)(2 + cur)); /* x tile written: warp 2 may filter it */
             }
         }
 
         /* -- end of the fragment -- */
-        if (whirl_run) {
+        if (!SPLIT && whirl_run) {
             /* NaN scrub after the loop (EQ_IIR_NAN, src/whirl.cpp:1622-1625) */
             zA0 = isnan(zA0) ? 0.0f : zA0;
             zA1 = isnan(zA1) ? 0.0f : zA1;
@@ -2426,20 +2560,22 @@ __global__ void __launch_bounds__(64) tbf_stage_r_tma(const RenderParams p, cons
 
     if (valid) {
         RampScalars &o = st->rp; /* this role's fields only */
-        o.iirz[0][0] = zA0;
-        o.iirz[0][1] = zA1;
-        o.iirz[1][0] = zB0;
-        o.iirz[1][1] = zB1;
+        if (!SPLIT) {
+            o.iirz[0][0] = zA0;
+            o.iirz[0][1] = zA1;
+            o.iirz[1][0] = zB0;
+            o.iirz[1][1] = zB1;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            o.iir[0][k] = rp.iir[0][k];
-            o.iir[1][k] = rp.iir[1][k];
+            for (int k = 0; k < 5; ++k) {
+                o.iir[0][k] = rp.iir[0][k];
+                o.iir[1][k] = rp.iir[1][k];
+            }
+            if (new_flags)
+                atomicOr(&o.errorFlags, new_flags);
+            p.ev_cursor_r[slot] = ev_cur;
         }
         o.percEnvGain = pg;
         o.keyCompLevel = kc;
-        if (new_flags)
-            atomicOr(&o.errorFlags, new_flags);
-        p.ev_cursor_r[slot] = ev_cur;
         if (p.checksums && whirl_off) {
             unsigned long long c = 0ull;
             for (int j = 0; j < BLK; ++j)
@@ -3448,10 +3584,22 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
         static int have_tma[TBF_MAX_DEVICES] = {0};
         const bool bypass = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
         const size_t smem = sizeof(RTmaSmem) + 1024 - ((p.checksums && bypass) ? 0 : sizeof(RTmaSmem::csum));
-        if (int rc = set_smem(tbf_stage_r_tma, sizeof(RTmaSmem) + 1024, have_tma))
+        /* three warps per 32 organs (mixdown | rotors | horn biquads one block behind): stage R sits on
+         * the critical path of the stage schedule, and in the mix its single-warp chains run three to
+         * four times slower than alone -- half the chain per warp, half the time (TBF_R_SPLIT=0: two) */
+        static const bool split = !(getenv("TBF_R_SPLIT") && atoi(getenv("TBF_R_SPLIT")) == 0);
+        if (split && !bypass) {
+            static int have_split[TBF_MAX_DEVICES] = {0};
+            if (int rc = set_smem(tbf_stage_r_tma<true>, sizeof(RTmaSmem) + 1024, have_split))
+                return rc;
+            tbf_stage_r_tma<true><<<grid, 96, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
+            debug_sync(stream, "R");
+            return (int)cudaGetLastError();
+        }
+        if (int rc = set_smem(tbf_stage_r_tma<false>, sizeof(RTmaSmem) + 1024, have_tma))
             return rc;
         /* the rotor warp has nothing to do when the Leslie is bypassed */
-        tbf_stage_r_tma<<<grid, bypass ? 32 : 64, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
+        tbf_stage_r_tma<false><<<grid, bypass ? 32 : 64, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
         debug_sync(stream, "R");
         return (int)cudaGetLastError();
     }
