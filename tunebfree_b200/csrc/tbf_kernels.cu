@@ -3227,7 +3227,9 @@ __global__ void __launch_bounds__(32) tbf_stage_d_tma(const RenderParams p, cons
     }
 }
 
+#ifndef M_THREADS
 #define M_THREADS 256
+#endif
 
 /* V consecutive floats as one access (V = 4: LDG.128 / STG.128) */
 template <int V> struct MVec {
