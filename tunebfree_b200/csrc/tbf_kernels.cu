@@ -111,23 +111,24 @@ __device__ __forceinline__ RunBits run_bits(const uint32_t n, const uint32_t sma
     r.d = __ballot_sync(FULL, lane >= 1 && dn == 1u);
     return r;
 }
+/* rmask: the ring actually held (a power of two that divides the delay line's length, so the slot
+ * index may be reduced by it alone) */
 __device__ __forceinline__ void ordered_pass_bits(const uint32_t n, const RunBits rb, const float a, const float b,
-                                                  float *ring, const uint32_t rmask, const uint32_t smask,
-                                                  const int lane)
+                                                  float *ring, const uint32_t rmask, const int lane)
 {
     const float nz = -0.0f;
     const float b1 = __shfl_up_sync(FULL, b, 1);
-    const uint32_t sp1 = (n + 1) & smask;
+    float *const p0 = ring + (n & rmask), *const p1 = ring + ((n + 1) & rmask);
     if (rb.e == 0u) { /* warp-uniform: no slot is hit twice, every lane owns its slot n */
         const uint32_t dd = rb.d >> lane;
-        float v = ring[n & rmask];
-        float w = ring[sp1 & rmask]; /* stored only where no lane has n+1 as its own slot */
+        float v = *p0;
+        float w = *p1; /* stored only where no lane has n+1 as its own slot */
         v = __fadd_rn(v, (dd & 1u) ? b1 : nz);
         v = __fadd_rn(v, a);
         w = __fadd_rn(w, b);
-        ring[n & rmask] = v;
+        *p0 = v;
         if (!(dd & 2u))
-            ring[sp1 & rmask] = w;
+            *p1 = w;
         return;
     }
     const float b2 = __shfl_up_sync(FULL, b, 2);
@@ -135,8 +136,8 @@ __device__ __forceinline__ void ordered_pass_bits(const uint32_t n, const RunBit
     const uint32_t ee = rb.e >> lane, ep = (rb.e << 1) >> lane, dd = rb.d >> lane;
     const bool e_i = (ee & 1u) != 0, e_x = (ee & 2u) != 0, e_p = (ep & 1u) != 0;
     const bool d_i = (dd & 1u) != 0, d_x = (dd & 2u) != 0;
-    float v = ring[n & rmask];
-    float w = ring[sp1 & rmask]; /* a slot no lane has as its main slot whenever it is stored below */
+    float v = *p0;
+    float w = *p1; /* a slot no lane has as its main slot whenever it is stored below */
     v = __fadd_rn(v, (d_i && e_p) ? b2 : nz);
     v = __fadd_rn(v, d_i ? b1 : nz);
     v = __fadd_rn(v, a);
@@ -144,9 +145,9 @@ __device__ __forceinline__ void ordered_pass_bits(const uint32_t n, const RunBit
     w = __fadd_rn(w, e_i ? b1 : nz);
     w = __fadd_rn(w, b);
     if (!e_i) /* first sample of the run hitting slot n */
-        ring[n & rmask] = v;
+        *p0 = v;
     if (!e_x && !d_x) /* last sample of its run, and nobody hits n+1 as a main slot in this block */
-        ring[sp1 & rmask] = w;
+        *p1 = w;
 }
 
 /* ================================================================== */
@@ -1266,7 +1267,7 @@ __device__ __forceinline__ float vibrato_block(const DevTonegenTables *tg, TWarp
     bad = __any_sync(FULL, bad);
     float y;
     if (!bad) {
-        ordered_pass_bits(h, rb, va, vb, sm.vring, VRING_MASK, VBUF_MASK, lane);
+        ordered_pass_bits(h, rb, va, vb, sm.vring, VRING_MASK, lane);
         __syncwarp();
         y = sm.vring[op & VRING_MASK];
         sm.vring[op & VRING_MASK] = 0.0f;
@@ -2709,8 +2710,8 @@ __device__ __forceinline__ void group_scatter_read(const WTap *tap, float *ring_
     if (!bad) {
 #pragma unroll
         for (int j = 0; j < 3; ++j) {
-            ordered_pass_bits(tn[j], trb[j], ta[j], tb[j], ring_l, rmask, WBUF_MASK, lane);
-            ordered_pass_bits(tn[3 + j], trb[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, WBUF_MASK, lane);
+            ordered_pass_bits(tn[j], trb[j], ta[j], tb[j], ring_l, rmask, lane);
+            ordered_pass_bits(tn[3 + j], trb[3 + j], ta[3 + j], tb[3 + j], ring_r, rmask, lane);
             __syncwarp();
         }
         out_l = ring_l[op & rmask];
@@ -3006,8 +3007,12 @@ __device__ __forceinline__ void stage_w_half(const RenderParams &p, const uint32
 #ifndef W_MIN_CTAS
 #define W_MIN_CTAS 8
 #endif
-__global__ void __launch_bounds__(W_WARPS * 32, W_MIN_CTAS) tbf_stage_w(const RenderParams p, const uint32_t ring_size)
+/* RING: the delay-line ring held in shared memory as a compile-time constant (512: every default
+ * geometry; the masks become immediates), 0: taken from the launch (wide geometries) */
+template <int RING>
+__global__ void __launch_bounds__(W_WARPS * 32, W_MIN_CTAS) tbf_stage_w(const RenderParams p, const uint32_t ring_size_arg)
 {
+    const uint32_t ring_size = RING ? (uint32_t)RING : ring_size_arg;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t slot = blockIdx.x * W_WARPS + warp;
@@ -3619,10 +3624,17 @@ int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream)
     /* experiment: TBF_W_PAD_KB pads the CTA's shared memory, i.e. caps stage W's CTAs per SM */
     static const size_t pad = getenv("TBF_W_PAD_KB") ? (size_t)atoi(getenv("TBF_W_PAD_KB")) * 1024 : 0;
     const size_t smem = tbf_stage_w_smem(ring_size) + pad;
-    if (int rc = set_smem(tbf_stage_w, smem, have))
-        return rc;
     const dim3 grid((p.n_instances + W_WARPS - 1) / W_WARPS, 2); /* y: horn halves, drum halves */
-    tbf_stage_w<<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
+    if (ring_size == 512) {
+        if (int rc = set_smem(tbf_stage_w<512>, smem, have))
+            return rc;
+        tbf_stage_w<512><<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, 512u);
+    } else {
+        static int have_dyn[TBF_MAX_DEVICES] = {0};
+        if (int rc = set_smem(tbf_stage_w<0>, smem, have_dyn))
+            return rc;
+        tbf_stage_w<0><<<grid, W_WARPS * 32, smem, (cudaStream_t)stream>>>(p, (uint32_t)ring_size);
+    }
     debug_sync(stream, "W");
     return (int)cudaGetLastError();
 }
