@@ -211,13 +211,15 @@ struct tbf_ctx {
     cudaEvent_t render_done[2] = {nullptr, nullptr}, copy_done[2] = {nullptr, nullptr},
                 copy_done2[2] = {nullptr, nullptr};
     cudaEvent_t t0 = nullptr, t1 = nullptr;
-    uint64_t *d_ev_cursor = nullptr; /* [2][cap_slots]: stage T, stage R */
+    uint64_t *d_ev_cursor = nullptr; /* [3][cap_slots]: stage T, stage R, the rotor kernel */
     StageScratch scratch;
     /* instance groups: each renders its share of a batch on its own stream, so the
      * latency-bound lane = instance stages of one group overlap the others' stages */
     /* ... and every stage of a group has its own stream: stage s of chunk c overlaps stage
      * s-1 of chunk c+1 (the stage streams between them are double-buffered by chunk parity) */
     cudaStream_t sstream[TBF_MAX_GROUPS][4] = {};
+    cudaStream_t rot_stream[TBF_MAX_GROUPS] = {}; /* the rotor kernel, ahead of stage R's audio chain */
+    cudaEvent_t rot_done[TBF_MAX_GROUPS][TBF_MAX_STAGE_BUFS] = {};
     cudaEvent_t sdone[TBF_MAX_GROUPS][4][TBF_MAX_STAGE_BUFS] = {}; /* [group][stage][chunk % n_bufs] */
     int n_bufs = 3; /* copies of the stage streams in flight, 2..TBF_MAX_STAGE_BUFS (TBF_STAGE_BUFS) */
     cudaEvent_t fork = nullptr;
@@ -310,6 +312,11 @@ int tbf_gpu_create(tbf_ctx **out, int device)
             for (int b = 0; ok && b < TBF_MAX_STAGE_BUFS; ++b)
                 ok = cudaEventCreateWithFlags(&ctx->sdone[g][st][b], cudaEventDisableTiming) == cudaSuccess;
         }
+    for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g) {
+        ok = cudaStreamCreateWithPriority(&ctx->rot_stream[g], cudaStreamNonBlocking, prio_hi) == cudaSuccess;
+        for (int b = 0; ok && b < TBF_MAX_STAGE_BUFS; ++b)
+            ok = cudaEventCreateWithFlags(&ctx->rot_done[g][b], cudaEventDisableTiming) == cudaSuccess;
+    }
     if (!ok) {
         delete ctx;
         return TBF_ERR_CUDA;
@@ -376,6 +383,11 @@ void tbf_gpu_destroy(tbf_ctx *ctx)
         for (int st = 0; st < 4; ++st) {
             if (ctx->sstream[g][st])
                 cudaStreamDestroy(ctx->sstream[g][st]);
+            if (st == 0 && ctx->rot_stream[g])
+                cudaStreamDestroy(ctx->rot_stream[g]);
+            for (int par = 0; st == 0 && par < TBF_MAX_STAGE_BUFS; ++par)
+                if (ctx->rot_done[g][par])
+                    cudaEventDestroy(ctx->rot_done[g][par]);
             for (int par = 0; par < TBF_MAX_STAGE_BUFS; ++par)
                 if (ctx->sdone[g][st][par])
                     cudaEventDestroy(ctx->sdone[g][st][par]);
@@ -1459,7 +1471,7 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     if ((size_t)d->n_instances + 1 > ctx->cap_slots) {
         size_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
         CK(grow(&ctx->d_ev_start, &c0, (size_t)d->n_instances + 1));
-        CK(grow(&ctx->d_ev_cursor, &c3, 2 * ((size_t)d->n_instances + 1)));
+        CK(grow(&ctx->d_ev_cursor, &c3, 3 * ((size_t)d->n_instances + 1)));
         CK(grow(&ctx->d_ids, &c1, (size_t)d->n_instances + 1));
         CK(grow(&ctx->d_csum, &c2, (size_t)d->n_instances + 1));
         ctx->cap_slots = (size_t)d->n_instances + 1;
@@ -1524,9 +1536,11 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     const uint32_t chunk = ctx->prepared_chunk;
     const size_t n = d->n_instances;
     CK(cudaSetDevice(ctx->device));
-    uint64_t *cur_t = ctx->d_ev_cursor, *cur_r = ctx->d_ev_cursor + ctx->cap_slots;
+    uint64_t *cur_t = ctx->d_ev_cursor, *cur_r = ctx->d_ev_cursor + ctx->cap_slots,
+             *cur_rot = ctx->d_ev_cursor + 2 * ctx->cap_slots;
     CK(cudaMemcpyAsync(cur_t, ctx->d_ev_start, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, ctx->stream));
     CK(cudaMemcpyAsync(cur_r, ctx->d_ev_start, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(cur_rot, ctx->d_ev_start, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, ctx->stream));
     if (d->checksums)
         CK(cudaMemsetAsync(ctx->d_csum, 0, sizeof(uint64_t) * n, ctx->stream));
 
@@ -1603,9 +1617,11 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
     const int ring = ctx->prepared_ring;
     CK(cudaEventRecord(ctx->ev0, ctx->stream));
     CK(cudaEventRecord(ctx->fork, ctx->stream));
-    for (int g = 0; g < n_groups; ++g)
+    for (int g = 0; g < n_groups; ++g) {
         for (int st = 0; st < n_stages; ++st)
             CK(cudaStreamWaitEvent(ctx->sstream[g][st], ctx->fork, 0));
+        CK(cudaStreamWaitEvent(ctx->rot_stream[g], ctx->fork, 0));
+    }
     const bool stems = (d->flags & TBF_RENDER_STEMS) != 0;
     const bool chunked = (d->flags & TBF_RENDER_OUT_CHUNKED) != 0;
     const size_t n_planes = stems ? 6 : 2;
@@ -1669,6 +1685,7 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
             p.ev_start = ctx->d_ev_start + s0;
             p.ev_cursor_t = cur_t + s0;
             p.ev_cursor_r = cur_r + s0;
+            p.ev_cursor_rot = cur_rot + s0;
             p.checksums = d->checksums ? ctx->d_csum + s0 : nullptr;
             p.out_stride = out_stride;
             int par = 0;
@@ -1719,16 +1736,29 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                     CK(cudaEventRecord(ev[0][par], st[0]));
                 }
                 if (rc == 0) {
-                    if (!whirl_input)
-                        CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
                     if (whirl && c >= nb) {
                         CK(cudaStreamWaitEvent(st[1], ev[2][par], 0));
                         CK(cudaStreamWaitEvent(st[1], ev[3][par], 0));
                     }
                     CK(prof_mark(1, true, st[1]));
-                    rc = tbf_launch_stage_r(p, st[1]);
+                    /* the rotors need nothing from stage T: their kernel runs on a stream of its own,
+                     * as far ahead of the audio chain as the stage-stream copies allow */
+                    const bool rot_apart = whirl && tbf_stage_r_rotors_apart(p);
+                    if (rot_apart) {
+                        cudaStream_t rs = ctx->profile_stages ? st[1] : ctx->rot_stream[g];
+                        if (c >= nb) /* stage W of chunk c - n_bufs has read this copy's angle planes */
+                            CK(cudaStreamWaitEvent(rs, ev[2][par], 0));
+                        rc = tbf_launch_stage_rot(p, rs);
+                        CK(cudaEventRecord(ctx->rot_done[g][par], rs));
+                    }
+                    if (!whirl_input)
+                        CK(cudaStreamWaitEvent(st[1], ev[0][par], 0));
+                    if (rc == 0)
+                        rc = tbf_launch_stage_r(p, st[1]);
                     CK(prof_mark(1, false, st[1]));
                     CK(cudaEventRecord(ev[1][par], st[1]));
+                    if (rot_apart)
+                        CK(cudaStreamWaitEvent(st[2], ctx->rot_done[g][par], 0));
                 }
                 if (rc == 0 && whirl) {
                     CK(cudaStreamWaitEvent(st[2], ev[1][par], 0));

@@ -220,6 +220,7 @@ struct RenderParams {
     const uint64_t *ev_start;  /* [n_instances + 1] */
     uint64_t *ev_cursor_t;     /* [n_instances]: next unapplied event of stage T, over chunks */
     uint64_t *ev_cursor_r;     /* same for stage R (it applies the rotor-speed events)        */
+    uint64_t *ev_cursor_rot;   /* the rotor kernel's own cursor when it runs ahead of stage R's audio chain (else NULL) */
     float *out_l, *out_r;
     float *stems[4];           /* TBF_RENDER_STEMS: outHL outHR outDL outDR, or NULL */
     unsigned long long *checksums; /* [n_instances] or NULL */
@@ -262,6 +263,8 @@ size_t tbf_stage_t_smem(void);
 size_t tbf_stage_w_smem(int ring_size);
 int tbf_launch_stage_t(const RenderParams &p, void *stream);
 int tbf_launch_stage_r(const RenderParams &p, void *stream);
+bool tbf_stage_r_rotors_apart(const RenderParams &p);
+int tbf_launch_stage_rot(const RenderParams &p, void *stream); /* before stage R waits for stage T */
 int tbf_launch_stage_w(const RenderParams &p, int ring_size, void *stream);
 int tbf_launch_stage_d(const RenderParams &p, void *stream);
 int tbf_launch_wave_store(float *wave4, const float *raw, const uint32_t *meta, void *stream);

@@ -2100,23 +2100,161 @@ __global__ void __launch_bounds__(64) tbf_stage_r(const RenderParams p)
  * read / written by every lane as 16-byte chunks of its own row (tile_chunk). */
 struct RTmaSmem {
     float tin[2][2][TILE_BYTES / 4]; /* [buffer][u, php], filled by TMA one block ahead */
-    float tout[3][TILE_BYTES / 4];   /* dx0, hx0; three-warp form: dx0 tile 0, dx0 tile 1, hx0 */
-    double tang[2][2 * TILE_BYTES / 8]; /* horn, drum angle: two boxes of 16 samples each */
+    float tout[3][TILE_BYTES / 4];   /* dx0, hx0; with the biquads in their own warp: dx0 tile 0, dx0 tile 1, hx0 */
     unsigned long long bar[6];       /* input tiles landed [2]; x tile written [2], read [2] */
-    unsigned long long csum[BLK][BLK]; /* LAST: only in the launch's shared memory when stage R forms
-                                          the checksum (bypass-only batch with checksums) */
+    unsigned long long pad_[122];    /* keeps tang 1024-byte aligned */
+    /* LAST, and only in the launch's shared memory when needed: the angle tiles when the rotors run
+     * as a warp of this kernel, the checksum sums of a bypass-only batch (never both) */
+    union {
+        double tang[2][2 * TILE_BYTES / 8]; /* horn, drum angle: two boxes of 16 samples each */
+        unsigned long long csum[BLK][BLK];
+    };
 };
-template <bool SPLIT>
-__global__ void __launch_bounds__(SPLIT ? 96 : 64) tbf_stage_r_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+static_assert(offsetof(RTmaSmem, tang) % 1024 == 0, "TMA tiles are 1024-byte aligned");
+struct RotSmem {
+    double tang[2][2 * TILE_BYTES / 8];
+};
+/* The rotor role of stage R: rotor events, per-fragment speed ramps (src/whirl.cpp:1219-1374), the
+ * angle recurrences (:1618-1619) and the two angle streams, written as 2-D TMA boxes out of `tang`.
+ * It needs nothing from stage T, so it runs either as a warp of tbf_stage_r_tma or, ahead of the audio
+ * chain, as its own small kernel (tbf_stage_rot_tma). */
+__device__ __forceinline__ void r_rotor_role(const RenderParams &p, const TileMaps &maps,
+                                             double (*tang)[2 * TILE_BYTES / 8], const int lane,
+                                             const uint32_t slot0, const bool valid, InstState *st,
+                                             const DevWhirlTables *wh, RampScalars &rp, const bool whirl_run,
+                                             uint64_t ev_cur, const uint64_t ev_end, uint64_t *cursor_out)
+{
+    uint32_t new_flags = 0;
+    /* ---------------- role 1: rotor events, speed ramps, angle streams ---------------- */
+    double hang = rp.hornAngle, dang = rp.drumAngle;
+    const double SR = wh->sample_rate;
+    for (uint32_t f = 0; f < p.n_fragments; ++f) {
+        while (ev_cur < ev_end) {
+            const tbf_event *evp = p.events + ev_cur;
+            if (evp->fragment > p.frag_base + f)
+                break;
+            const int type = evp->type, a = evp->a;
+            if (type == TBF_EV_REV_OPTION) {
+                if (a < 0)
+                    new_flags |= TBF_IFLAG_BAD_EVENT;
+                else
+                    use_rev_option(rp, wh, a, 2);
+            } else if (type == TBF_EV_REV_SELECT) {
+                if (a < 0) {
+                    new_flags |= TBF_IFLAG_BAD_EVENT;
+                } else {
+                    rp.revSelect = a % 3;
+                    use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
+                }
+            } else if (type == TBF_EV_WHIRL_BRAKE || type == TBF_EV_WHIRL_RAMP) {
+                const int b = evp->b;
+                if (a < 0 || a > (type == TBF_EV_WHIRL_BRAKE ? 1 : 3) || b < 0 || b > 127) {
+                    new_flags |= TBF_IFLAG_BAD_EVENT;
+                } else if (type == TBF_EV_WHIRL_BRAKE) {
+                    /* w->hnBrakePos = (double)uc / 127.0, src/whirl.cpp:883-893 */
+                    rp.brakePos[a] = __ddiv_rn((double)b, 127.0);
+                } else {
+                    rp.oml[a] = wh->ramp_one_minus_l[a][b];
+                }
+            }
+            ++ev_cur;
+        }
+        /* -- per-call speed ramps (src/whirl.cpp:1219-1374) -- */
+        int hbrake = 0, dbrake = 0;
+        double hincr = rp.hornIncr, dincr = rp.drumIncr;
+        if (whirl_run) {
+            hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
+                                rp.oml[0], rp.oml[1]);
+            dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
+                                rp.oml[2], rp.oml[3]);
+        }
+        /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
+        const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
+        const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
+        for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
+            const size_t col0 = ((size_t)f * (TBF_FRAGMENT / BLK) + (size_t)blk) * BLK;
+            if (lane == 0)
+                tma_store_wait_read(); /* the last block's angle tiles have left shared memory */
+            __syncwarp();
+            if (whirl_run) {
+#pragma unroll 4
+                for (int s2 = 0; s2 < BLK / 2; ++s2) { /* two samples = one 16-byte chunk */
+                    double h[2], dd[2];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        h[e] = hang;
+                        dd[e] = dang;
+                        if (hfast) {
+                            const double t = __dadd_rn(hang, hincr);
+                            hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                        } else {
+                            hang = angle_step(hang, hincr);
+                        }
+                        if (dfast) {
+                            const double t = __dadd_rn(dang, dincr);
+                            dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
+                        } else {
+                            dang = angle_step(dang, dincr);
+                        }
+                    }
+                    const uint32_t o = (uint32_t)(s2 >> 3) * TILE_BYTES + tile_chunk(lane, s2 & 7);
+                    *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(tang[0]) + o) = make_double2(h[0], h[1]);
+                    *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(tang[1]) + o) = make_double2(dd[0], dd[1]);
+                }
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t c2 = 2u * (uint32_t)col0; /* the double planes as pairs of floats */
+                tma_tile_store(&maps.m64, c2, p.tile_row[8] + slot0, smem_u32(tang[0]));
+                tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[8] + slot0, smem_u32(tang[0]) + TILE_BYTES);
+                tma_tile_store(&maps.m64, c2, p.tile_row[9] + slot0, smem_u32(tang[1]));
+                tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[9] + slot0, smem_u32(tang[1]) + TILE_BYTES);
+                tma_store_commit();
+            }
+        }
+        if (whirl_run) {
+            rp.hornIncr = hbrake ? 0.0 : hincr;
+            rp.drumIncr = dbrake ? 0.0 : dincr;
+        }
+    }
+    if (valid) {
+        RampScalars &o = st->rp; /* this role's fields only: role 0 stores the others */
+        o.hornAcDc = rp.hornAcDc;
+        o.drumAcDc = rp.drumAcDc;
+        o.revSelect = rp.revSelect;
+        o.hornAngle = hang;
+        o.drumAngle = dang;
+        o.hornIncr = rp.hornIncr;
+        o.drumIncr = rp.drumIncr;
+        o.hornTarget = rp.hornTarget;
+        o.drumTarget = rp.drumTarget;
+        o.brakePos[0] = rp.brakePos[0];
+        o.brakePos[1] = rp.brakePos[1];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            o.oml[k] = rp.oml[k];
+        if (new_flags)
+            atomicOr(&o.errorFlags, new_flags);
+    }
+    if (cursor_out)
+        *cursor_out = ev_cur;
+    if (lane == 0)
+        tma_store_wait_all();
+}
+
+template <bool SPLIT, bool ROT>
+__global__ void __launch_bounds__((SPLIT && ROT) ? 96 : 64) tbf_stage_r_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     RTmaSmem &sm = *reinterpret_cast<RTmaSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
     const int lane = threadIdx.x & 31;
-    /* warp-uniform roles: warp 0 mixes down (and, unless SPLIT, runs the horn biquads), warp 1 the
-     * rotors, warp 2 (SPLIT) the horn biquads one block behind warp 0 */
-    const bool rotors = (threadIdx.x >> 5) == 1;
-    const bool filters = SPLIT && (threadIdx.x >> 5) == 2;
+    /* warp-uniform roles: warp 0 mixes down (and, unless SPLIT, runs the horn biquads), then the rotor
+     * warp (ROT; otherwise tbf_stage_rot_tma has run them already), then (SPLIT) the warp of the horn
+     * biquads, one block behind warp 0 */
+    const bool rotors = ROT && (threadIdx.x >> 5) == 1;
+    const bool filters = SPLIT && (threadIdx.x >> 5) == (ROT ? 2 : 1);
     const uint32_t slot0 = blockIdx.x * 32;
     const uint32_t slot = slot0 + lane;
     const bool valid = slot < p.n_instances;
@@ -2159,119 +2297,7 @@ __global__ void __launch_bounds__(SPLIT ? 96 : 64) tbf_stage_r_tma(const RenderP
 
     if (rotors) {
         /* ---------------- role 1: rotor events, speed ramps, angle streams ---------------- */
-        double hang = rp.hornAngle, dang = rp.drumAngle;
-        const double SR = wh->sample_rate;
-        for (uint32_t f = 0; f < p.n_fragments; ++f) {
-            while (ev_cur < ev_end) {
-                const tbf_event *evp = p.events + ev_cur;
-                if (evp->fragment > p.frag_base + f)
-                    break;
-                const int type = evp->type, a = evp->a;
-                if (type == TBF_EV_REV_OPTION) {
-                    if (a < 0)
-                        new_flags |= TBF_IFLAG_BAD_EVENT;
-                    else
-                        use_rev_option(rp, wh, a, 2);
-                } else if (type == TBF_EV_REV_SELECT) {
-                    if (a < 0) {
-                        new_flags |= TBF_IFLAG_BAD_EVENT;
-                    } else {
-                        rp.revSelect = a % 3;
-                        use_rev_option(rp, wh, wh->revselects[rp.revSelect], 1);
-                    }
-                } else if (type == TBF_EV_WHIRL_BRAKE || type == TBF_EV_WHIRL_RAMP) {
-                    const int b = evp->b;
-                    if (a < 0 || a > (type == TBF_EV_WHIRL_BRAKE ? 1 : 3) || b < 0 || b > 127) {
-                        new_flags |= TBF_IFLAG_BAD_EVENT;
-                    } else if (type == TBF_EV_WHIRL_BRAKE) {
-                        /* w->hnBrakePos = (double)uc / 127.0, src/whirl.cpp:883-893 */
-                        rp.brakePos[a] = __ddiv_rn((double)b, 127.0);
-                    } else {
-                        rp.oml[a] = wh->ramp_one_minus_l[a][b];
-                    }
-                }
-                ++ev_cur;
-            }
-            /* -- per-call speed ramps (src/whirl.cpp:1219-1374) -- */
-            int hbrake = 0, dbrake = 0;
-            double hincr = rp.hornIncr, dincr = rp.drumIncr;
-            if (whirl_run) {
-                hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
-                                    rp.oml[0], rp.oml[1]);
-                dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
-                                    rp.oml[2], rp.oml[3]);
-            }
-            /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
-            const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
-            const bool dfast = dang >= 0.0 && dang < 1.0 && dincr >= 0.0 && dincr < 1.0;
-            for (int blk = 0; blk < TBF_FRAGMENT / BLK; ++blk) {
-                const size_t col0 = ((size_t)f * (TBF_FRAGMENT / BLK) + (size_t)blk) * BLK;
-                if (lane == 0)
-                    tma_store_wait_read(); /* the last block's angle tiles have left shared memory */
-                __syncwarp();
-                if (whirl_run) {
-#pragma unroll 4
-                    for (int s2 = 0; s2 < BLK / 2; ++s2) { /* two samples = one 16-byte chunk */
-                        double h[2], dd[2];
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            h[e] = hang;
-                            dd[e] = dang;
-                            if (hfast) {
-                                const double t = __dadd_rn(hang, hincr);
-                                hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
-                            } else {
-                                hang = angle_step(hang, hincr);
-                            }
-                            if (dfast) {
-                                const double t = __dadd_rn(dang, dincr);
-                                dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
-                            } else {
-                                dang = angle_step(dang, dincr);
-                            }
-                        }
-                        const uint32_t o = (uint32_t)(s2 >> 3) * TILE_BYTES + tile_chunk(lane, s2 & 7);
-                        *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(sm.tang[0]) + o) = make_double2(h[0], h[1]);
-                        *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(sm.tang[1]) + o) = make_double2(dd[0], dd[1]);
-                    }
-                }
-                fence_async_smem();
-                __syncwarp();
-                if (lane == 0) {
-                    const uint32_t c2 = 2u * (uint32_t)col0; /* the double planes as pairs of floats */
-                    tma_tile_store(&maps.m64, c2, p.tile_row[8] + slot0, smem_u32(sm.tang[0]));
-                    tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[8] + slot0, smem_u32(sm.tang[0]) + TILE_BYTES);
-                    tma_tile_store(&maps.m64, c2, p.tile_row[9] + slot0, smem_u32(sm.tang[1]));
-                    tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[9] + slot0, smem_u32(sm.tang[1]) + TILE_BYTES);
-                    tma_store_commit();
-                }
-            }
-            if (whirl_run) {
-                rp.hornIncr = hbrake ? 0.0 : hincr;
-                rp.drumIncr = dbrake ? 0.0 : dincr;
-            }
-        }
-        if (valid) {
-            RampScalars &o = st->rp; /* this role's fields only: role 0 stores the others */
-            o.hornAcDc = rp.hornAcDc;
-            o.drumAcDc = rp.drumAcDc;
-            o.revSelect = rp.revSelect;
-            o.hornAngle = hang;
-            o.drumAngle = dang;
-            o.hornIncr = rp.hornIncr;
-            o.drumIncr = rp.drumIncr;
-            o.hornTarget = rp.hornTarget;
-            o.drumTarget = rp.drumTarget;
-            o.brakePos[0] = rp.brakePos[0];
-            o.brakePos[1] = rp.brakePos[1];
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                o.oml[k] = rp.oml[k];
-            if (new_flags)
-                atomicOr(&o.errorFlags, new_flags);
-        }
-        if (lane == 0)
-            tma_store_wait_all();
+        r_rotor_role(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end, nullptr);
         return;
     }
 
@@ -2586,6 +2612,37 @@ __global__ void __launch_bounds__(SPLIT ? 96 : 64) tbf_stage_r_tma(const RenderP
     }
     if (lane == 0)
         tma_store_wait_all();
+}
+
+/* The rotors of 32 organs as a kernel of their own: launched on stage R's stream BEFORE it waits for
+ * stage T, so the angle streams are written while stage T still runs and the audio chain's CTAs need
+ * neither the angle tiles (16 KB) nor a third warp. */
+__global__ void __launch_bounds__(32) tbf_stage_rot_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    RotSmem &sm = *reinterpret_cast<RotSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
+    const int lane = threadIdx.x;
+    const uint32_t slot0 = blockIdx.x * 32;
+    const uint32_t slot = slot0 + lane;
+    const bool valid = slot < p.n_instances;
+    InstState *st = nullptr;
+    const DevWhirlTables *wh = p.wh;
+    RampScalars rp;
+    uint64_t ev_cur = 0, ev_end = 0;
+    if (valid) {
+        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
+        st = p.states + id;
+        rp = st->rp;
+        wh = p.wh + st->tg.whTables;
+        ev_cur = p.ev_cursor_rot[slot]; /* its own: this kernel runs ahead of the audio chain's */
+        ev_end = p.ev_start[slot + 1];
+    } else {
+        rp = RampScalars();
+    }
+    const bool whirl_run = valid && !wh->bypass;
+    r_rotor_role(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end,
+                 valid ? p.ev_cursor_rot + slot : nullptr);
 }
 
 /* ================================================================== */
@@ -3581,6 +3638,21 @@ int tbf_launch_stage_t(const RenderParams &p, void *stream)
     return (int)cudaGetLastError();
 }
 
+/* the rotors run as their own kernel, ahead of the audio chain (Leslie running, TMA tiles available) */
+bool tbf_stage_r_rotors_apart(const RenderParams &p)
+{
+    static const bool split = !(getenv("TBF_R_SPLIT") && atoi(getenv("TBF_R_SPLIT")) == 0);
+    return split && p.tile_maps && p.ev_cursor_rot && !(p.flags & TBF_RENDER_WHIRL_BYPASS);
+}
+
+int tbf_launch_stage_rot(const RenderParams &p, void *stream)
+{
+    const uint32_t grid = (p.n_instances + 31) / 32;
+    tbf_stage_rot_tma<<<grid, 32, sizeof(RotSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+    debug_sync(stream, "R (rotors)");
+    return (int)cudaGetLastError();
+}
+
 int tbf_launch_stage_r(const RenderParams &p, void *stream)
 {
     static int have[TBF_MAX_DEVICES] = {0};
@@ -3590,23 +3662,25 @@ int tbf_launch_stage_r(const RenderParams &p, void *stream)
     if (p.tile_maps) {
         static int have_tma[TBF_MAX_DEVICES] = {0};
         const bool bypass = (p.flags & TBF_RENDER_WHIRL_BYPASS) != 0;
-        const size_t smem = sizeof(RTmaSmem) + 1024 - ((p.checksums && bypass) ? 0 : sizeof(RTmaSmem::csum));
-        /* three warps per 32 organs (mixdown | rotors | horn biquads one block behind): stage R sits on
-         * the critical path of the stage schedule, and in the mix its single-warp chains run three to
-         * four times slower than alone -- half the chain per warp, half the time (TBF_R_SPLIT=0: two) */
-        static const bool split = !(getenv("TBF_R_SPLIT") && atoi(getenv("TBF_R_SPLIT")) == 0);
-        if (split && !bypass) {
+        const size_t smem = (bypass && !p.checksums) ? offsetof(RTmaSmem, tang) + 1024 : sizeof(RTmaSmem) + 1024;
+        /* The audio chain as two warps per 32 organs (mixdown | horn biquads one block behind), the
+         * rotors in a kernel of their own that tbf_api.cu launches ahead (tbf_launch_stage_rot).  Stage
+         * R sits on the critical path of the stage schedule and what it costs there is its CTAs'
+         * residency times the stage T / W CTAs they displace: half the chain per warp and 30 KB
+         * instead of 46 KB per CTA.  TBF_R_SPLIT=0: everything in one kernel of two warps. */
+        if (tbf_stage_r_rotors_apart(p)) {
             static int have_split[TBF_MAX_DEVICES] = {0};
-            if (int rc = set_smem(tbf_stage_r_tma<true>, sizeof(RTmaSmem) + 1024, have_split))
+            const size_t smem_a = offsetof(RTmaSmem, tang) + 1024;
+            if (int rc = set_smem(tbf_stage_r_tma<true, false>, smem_a, have_split))
                 return rc;
-            tbf_stage_r_tma<true><<<grid, 96, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
+            tbf_stage_r_tma<true, false><<<grid, 64, smem_a, (cudaStream_t)stream>>>(p, *p.tile_maps);
             debug_sync(stream, "R");
             return (int)cudaGetLastError();
         }
-        if (int rc = set_smem(tbf_stage_r_tma<false>, sizeof(RTmaSmem) + 1024, have_tma))
+        if (int rc = set_smem(tbf_stage_r_tma<false, true>, sizeof(RTmaSmem) + 1024, have_tma))
             return rc;
         /* the rotor warp has nothing to do when the Leslie is bypassed */
-        tbf_stage_r_tma<false><<<grid, bypass ? 32 : 64, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
+        tbf_stage_r_tma<false, true><<<grid, bypass ? 32 : 64, smem, (cudaStream_t)stream>>>(p, *p.tile_maps);
         debug_sync(stream, "R");
         return (int)cudaGetLastError();
     }
