@@ -303,8 +303,10 @@ int tbf_gpu_create(tbf_ctx **out, int device)
      * whenever an SM has room, so they run beside the throughput stages instead of after */
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-    const int prio_mask = getenv("TBF_PRIO_MASK") ? atoi(getenv("TBF_PRIO_MASK")) : 10; /* bit s: stage s high; measured 0: 145.5 k, 2: 148.5 k,
-                                                                              4: 139.7 k, 8: 145.1 k, 10: 148.9 k, 14: 149.5 k, 15: 145.5 k */
+    /* bit s: stage s on a high-priority stream.  Measured on the v5 kernels (config 3, 4096 | 16 384
+     * organs, k organ-s/s): 0: 205.7 | 217.1, 2 (stage R): 203.4 | 217.8, 8: 201.3 | 215.3, 10: 199.6 |
+     * 215.8, 12: 197.5 | 212.5, 14: 197.6 | 208.4, 6: 196.9 | 209.6 */
+    const int prio_mask = getenv("TBF_PRIO_MASK") ? atoi(getenv("TBF_PRIO_MASK")) : 2;
     for (int g = 0; g < TBF_MAX_GROUPS && ok; ++g)
         for (int st = 0; st < 4 && ok; ++st) {
             ok = cudaStreamCreateWithPriority(&ctx->sstream[g][st], cudaStreamNonBlocking,
