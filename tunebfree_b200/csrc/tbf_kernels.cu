@@ -2117,7 +2117,10 @@ struct RotSmem {
 /* The rotor role of stage R: rotor events, per-fragment speed ramps (src/whirl.cpp:1219-1374), the
  * angle recurrences (:1618-1619) and the two angle streams, written as 2-D TMA boxes out of `tang`.
  * It needs nothing from stage T, so it runs either as a warp of tbf_stage_r_tma or, ahead of the audio
- * chain, as its own small kernel (tbf_stage_rot_tma). */
+ * chain, as its own small kernel (tbf_stage_rot_tma).  WHICH: 0 both rotors in this warp, 1 the horn
+ * only, 2 the drum only -- the two recurrences share nothing but the events, so two warps halve the
+ * time the kernel's CTAs stay resident; each warp stores the state fields of its own rotor. */
+template <int WHICH>
 __device__ __forceinline__ void r_rotor_role(const RenderParams &p, const TileMaps &maps,
                                              double (*tang)[2 * TILE_BYTES / 8], const int lane,
                                              const uint32_t slot0, const bool valid, InstState *st,
@@ -2163,10 +2166,12 @@ __device__ __forceinline__ void r_rotor_role(const RenderParams &p, const TileMa
         int hbrake = 0, dbrake = 0;
         double hincr = rp.hornIncr, dincr = rp.drumIncr;
         if (whirl_run) {
-            hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
-                                rp.oml[0], rp.oml[1]);
-            dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
-                                rp.oml[2], rp.oml[3]);
+            if (WHICH != 2)
+                hbrake = rotor_ramp(SR, true, &rp.hornAcDc, &hincr, &hang, rp.hornTarget, rp.brakePos[0],
+                                    rp.oml[0], rp.oml[1]);
+            if (WHICH != 1)
+                dbrake = rotor_ramp(SR, false, &rp.drumAcDc, &dincr, &dang, rp.drumTarget, rp.brakePos[1],
+                                    rp.oml[2], rp.oml[3]);
         }
         /* fmod(t, 1.0) of a sum in [0, 2) is t or t - 1, both exact */
         const bool hfast = hang >= 0.0 && hang < 1.0 && hincr >= 0.0 && hincr < 1.0;
@@ -2184,13 +2189,15 @@ __device__ __forceinline__ void r_rotor_role(const RenderParams &p, const TileMa
                     for (int e = 0; e < 2; ++e) {
                         h[e] = hang;
                         dd[e] = dang;
-                        if (hfast) {
+                        if (WHICH == 2) {
+                        } else if (hfast) {
                             const double t = __dadd_rn(hang, hincr);
                             hang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
                         } else {
                             hang = angle_step(hang, hincr);
                         }
-                        if (dfast) {
+                        if (WHICH == 1) {
+                        } else if (dfast) {
                             const double t = __dadd_rn(dang, dincr);
                             dang = (t >= 1.0) ? __dsub_rn(t, 1.0) : t;
                         } else {
@@ -2198,44 +2205,57 @@ __device__ __forceinline__ void r_rotor_role(const RenderParams &p, const TileMa
                         }
                     }
                     const uint32_t o = (uint32_t)(s2 >> 3) * TILE_BYTES + tile_chunk(lane, s2 & 7);
-                    *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(tang[0]) + o) = make_double2(h[0], h[1]);
-                    *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(tang[1]) + o) = make_double2(dd[0], dd[1]);
+                    if (WHICH != 2)
+                        *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(tang[0]) + o) = make_double2(h[0], h[1]);
+                    if (WHICH != 1)
+                        *reinterpret_cast<double2 *>(reinterpret_cast<unsigned char *>(tang[1]) + o) = make_double2(dd[0], dd[1]);
                 }
             }
             fence_async_smem();
             __syncwarp();
             if (lane == 0) {
                 const uint32_t c2 = 2u * (uint32_t)col0; /* the double planes as pairs of floats */
-                tma_tile_store(&maps.m64, c2, p.tile_row[8] + slot0, smem_u32(tang[0]));
-                tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[8] + slot0, smem_u32(tang[0]) + TILE_BYTES);
-                tma_tile_store(&maps.m64, c2, p.tile_row[9] + slot0, smem_u32(tang[1]));
-                tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[9] + slot0, smem_u32(tang[1]) + TILE_BYTES);
+                if (WHICH != 2) {
+                    tma_tile_store(&maps.m64, c2, p.tile_row[8] + slot0, smem_u32(tang[0]));
+                    tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[8] + slot0, smem_u32(tang[0]) + TILE_BYTES);
+                }
+                if (WHICH != 1) {
+                    tma_tile_store(&maps.m64, c2, p.tile_row[9] + slot0, smem_u32(tang[1]));
+                    tma_tile_store(&maps.m64, c2 + 32u, p.tile_row[9] + slot0, smem_u32(tang[1]) + TILE_BYTES);
+                }
                 tma_store_commit();
             }
         }
         if (whirl_run) {
-            rp.hornIncr = hbrake ? 0.0 : hincr;
-            rp.drumIncr = dbrake ? 0.0 : dincr;
+            if (WHICH != 2)
+                rp.hornIncr = hbrake ? 0.0 : hincr;
+            if (WHICH != 1)
+                rp.drumIncr = dbrake ? 0.0 : dincr;
         }
     }
     if (valid) {
         RampScalars &o = st->rp; /* this role's fields only: role 0 stores the others */
-        o.hornAcDc = rp.hornAcDc;
-        o.drumAcDc = rp.drumAcDc;
-        o.revSelect = rp.revSelect;
-        o.hornAngle = hang;
-        o.drumAngle = dang;
-        o.hornIncr = rp.hornIncr;
-        o.drumIncr = rp.drumIncr;
-        o.hornTarget = rp.hornTarget;
-        o.drumTarget = rp.drumTarget;
-        o.brakePos[0] = rp.brakePos[0];
-        o.brakePos[1] = rp.brakePos[1];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            o.oml[k] = rp.oml[k];
-        if (new_flags)
-            atomicOr(&o.errorFlags, new_flags);
+        if (WHICH != 2) {
+            o.hornAcDc = rp.hornAcDc;
+            o.revSelect = rp.revSelect;
+            o.hornAngle = hang;
+            o.hornIncr = rp.hornIncr;
+            o.hornTarget = rp.hornTarget;
+            o.brakePos[0] = rp.brakePos[0];
+            o.oml[0] = rp.oml[0];
+            o.oml[1] = rp.oml[1];
+            if (new_flags)
+                atomicOr(&o.errorFlags, new_flags);
+        }
+        if (WHICH != 1) {
+            o.drumAcDc = rp.drumAcDc;
+            o.drumAngle = dang;
+            o.drumIncr = rp.drumIncr;
+            o.drumTarget = rp.drumTarget;
+            o.brakePos[1] = rp.brakePos[1];
+            o.oml[2] = rp.oml[2];
+            o.oml[3] = rp.oml[3];
+        }
     }
     if (cursor_out)
         *cursor_out = ev_cur;
@@ -2297,7 +2317,7 @@ __global__ void __launch_bounds__((SPLIT && ROT) ? 96 : 64) tbf_stage_r_tma(cons
 
     if (rotors) {
         /* ---------------- role 1: rotor events, speed ramps, angle streams ---------------- */
-        r_rotor_role(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end, nullptr);
+        r_rotor_role<0>(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end, nullptr);
         return;
     }
 
@@ -2617,12 +2637,13 @@ __global__ void __launch_bounds__((SPLIT && ROT) ? 96 : 64) tbf_stage_r_tma(cons
 /* The rotors of 32 organs as a kernel of their own: launched on stage R's stream BEFORE it waits for
  * stage T, so the angle streams are written while stage T still runs and the audio chain's CTAs need
  * neither the angle tiles (16 KB) nor a third warp. */
-__global__ void __launch_bounds__(32) tbf_stage_rot_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+template <bool TWO>
+__global__ void __launch_bounds__(TWO ? 64 : 32) tbf_stage_rot_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     RotSmem &sm = *reinterpret_cast<RotSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
-    const int lane = threadIdx.x;
+    const int lane = threadIdx.x & 31;
     const uint32_t slot0 = blockIdx.x * 32;
     const uint32_t slot = slot0 + lane;
     const bool valid = slot < p.n_instances;
@@ -2641,8 +2662,15 @@ __global__ void __launch_bounds__(32) tbf_stage_rot_tma(const RenderParams p, co
         rp = RampScalars();
     }
     const bool whirl_run = valid && !wh->bypass;
-    r_rotor_role(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end,
-                 valid ? p.ev_cursor_rot + slot : nullptr);
+    /* warp 0 the horn (and the event cursor), warp 1 the drum: both read the same events */
+    if (!TWO)
+        r_rotor_role<0>(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end,
+                        valid ? p.ev_cursor_rot + slot : nullptr);
+    else if ((threadIdx.x >> 5) == 0)
+        r_rotor_role<1>(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end,
+                        valid ? p.ev_cursor_rot + slot : nullptr);
+    else
+        r_rotor_role<2>(p, maps, sm.tang, lane, slot0, valid, st, wh, rp, whirl_run, ev_cur, ev_end, nullptr);
 }
 
 /* ================================================================== */
@@ -3187,50 +3215,38 @@ __global__ void __launch_bounds__(32) tbf_stage_d(const RenderParams p)
 
 struct DTmaSmem {
     float t[2][2][TILE_BYTES / 4]; /* [buffer][DL DR], swizzled boxes; 1024-byte aligned */
-    unsigned long long bar[2];
+    unsigned long long bar[2][2];  /* [warp][buffer] */
 };
 
-/* Stage D with TMA tiles: same arithmetic as tbf_stage_d, the two drum line reads filtered in place. */
-__global__ void __launch_bounds__(32) tbf_stage_d_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+/* One warp's share of stage D: NCH of the two drum line reads (from channel ch0), filtered in place
+ * in their TMA tiles.  The two channels' filters share nothing (src/whirl.cpp:1609-1612), so one warp
+ * per channel halves the time a CTA of stage D stays on its SM. */
+template <int NCH>
+__device__ __forceinline__ void d_channel_role(const RenderParams &p, const TileMaps &maps, DTmaSmem &sm,
+                                               const int lane, const uint32_t slot0, const bool run,
+                                               InstState *st, const DevWhirlTables *wh, const int ch0,
+                                               const int warp)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const uint32_t raw = smem_u32(smem_raw);
-    DTmaSmem &sm = *reinterpret_cast<DTmaSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
-    const int lane = threadIdx.x;
-    const uint32_t slot0 = blockIdx.x * 32;
-    const uint32_t slot = slot0 + lane;
-    const bool valid = slot < p.n_instances;
-
-    InstState *st = nullptr;
-    const DevWhirlTables *wh = p.wh;
-    float zl0 = 0.f, zl1 = 0.f, zr0 = 0.f, zr1 = 0.f;
-    if (valid) {
-        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
-        st = p.states + id;
-        wh = p.wh + st->tg.whTables;
-        zl0 = st->dr.iirz[0][0];
-        zl1 = st->dr.iirz[0][1];
-        zr0 = st->dr.iirz[1][0];
-        zr1 = st->dr.iirz[1][1];
-    }
-    const bool run = valid && !wh->bypass;
-    if (!__any_sync(FULL, run))
-        return; /* every organ of the warp has its Leslie bypassed: nothing to filter */
-    float cL[5], cR[5];
+    float z[NCH][2], c[NCH][5];
+    uint32_t row[NCH];
 #pragma unroll
-    for (int k = 0; k < 5; ++k) {
-        cL[k] = wh->iir[2][k];
-        cR[k] = wh->iir[3][k];
+    for (int k = 0; k < NCH; ++k) {
+        z[k][0] = run ? st->dr.iirz[ch0 + k][0] : 0.f;
+        z[k][1] = run ? st->dr.iirz[ch0 + k][1] : 0.f;
+#pragma unroll
+        for (int j = 0; j < 5; ++j)
+            c[k][j] = wh->iir[2 + ch0 + k][j];
+        row[k] = p.tile_row[6 + ch0 + k] + slot0; /* line[2], line[3] */
     }
-    const uint32_t row_l = p.tile_row[6] + slot0, row_r = p.tile_row[7] + slot0; /* line[2], line[3] */
-    const uint32_t bar0 = smem_u32(&sm.bar[0]);
+    const uint32_t bar0 = smem_u32(&sm.bar[warp][0]);
     if (lane == 0) {
         mbar_init(bar0, 1u);
         mbar_init(bar0 + 8u, 1u);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        mbar_expect_tx(bar0, 2u * TILE_BYTES);
-        tma_tile_load(smem_u32(sm.t[0][0]), &maps.m32, 0u, row_l, bar0);
-        tma_tile_load(smem_u32(sm.t[0][1]), &maps.m32, 0u, row_r, bar0);
+        mbar_expect_tx(bar0, (uint32_t)NCH * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < NCH; ++k)
+            tma_tile_load(smem_u32(sm.t[0][ch0 + k]), &maps.m32, 0u, row[k], bar0);
     }
     __syncwarp();
     const uint32_t n_blocks = p.n_fragments * (TBF_FRAGMENT / BLK);
@@ -3240,53 +3256,91 @@ __global__ void __launch_bounds__(32) tbf_stage_d_tma(const RenderParams p, cons
         if (lane == 0 && blk + 1 < n_blocks) {
             tma_store_wait_read(); /* the other buffer's store (block blk - 1) has left shared memory */
             const uint32_t bar = bar0 + 8u * (uint32_t)(cur ^ 1);
-            mbar_expect_tx(bar, 2u * TILE_BYTES);
-            tma_tile_load(smem_u32(sm.t[cur ^ 1][0]), &maps.m32, (blk + 1) * BLK, row_l, bar);
-            tma_tile_load(smem_u32(sm.t[cur ^ 1][1]), &maps.m32, (blk + 1) * BLK, row_r, bar);
+            mbar_expect_tx(bar, (uint32_t)NCH * TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < NCH; ++k)
+                tma_tile_load(smem_u32(sm.t[cur ^ 1][ch0 + k]), &maps.m32, (blk + 1) * BLK, row[k], bar);
         }
         mbar_wait(bar0 + 8u * (uint32_t)cur, (parity >> cur) & 1u);
         parity ^= 1u << cur;
-        unsigned char *tl = reinterpret_cast<unsigned char *>(sm.t[cur][0]);
-        unsigned char *tr = reinterpret_cast<unsigned char *>(sm.t[cur][1]);
         if (run) {
 #pragma unroll 2
-            for (int c = 0; c < 8; ++c) {
-                const uint32_t o = tile_chunk(lane, c);
-                float4 a = *reinterpret_cast<float4 *>(tl + o), b = *reinterpret_cast<float4 *>(tr + o);
-                a.x = eq_iir(cL, zl0, zl1, a.x);
-                b.x = eq_iir(cR, zr0, zr1, b.x);
-                a.y = eq_iir(cL, zl0, zl1, a.y);
-                b.y = eq_iir(cR, zr0, zr1, b.y);
-                a.z = eq_iir(cL, zl0, zl1, a.z);
-                b.z = eq_iir(cR, zr0, zr1, b.z);
-                a.w = eq_iir(cL, zl0, zl1, a.w);
-                b.w = eq_iir(cR, zr0, zr1, b.w);
-                *reinterpret_cast<float4 *>(tl + o) = a;
-                *reinterpret_cast<float4 *>(tr + o) = b;
+            for (int ck = 0; ck < 8; ++ck) {
+                const uint32_t o = tile_chunk(lane, ck);
+                float4 a[NCH];
+#pragma unroll
+                for (int k = 0; k < NCH; ++k)
+                    a[k] = *reinterpret_cast<float4 *>(reinterpret_cast<unsigned char *>(sm.t[cur][ch0 + k]) + o);
+#pragma unroll
+                for (int k = 0; k < NCH; ++k)
+                    a[k].x = eq_iir(c[k], z[k][0], z[k][1], a[k].x);
+#pragma unroll
+                for (int k = 0; k < NCH; ++k)
+                    a[k].y = eq_iir(c[k], z[k][0], z[k][1], a[k].y);
+#pragma unroll
+                for (int k = 0; k < NCH; ++k)
+                    a[k].z = eq_iir(c[k], z[k][0], z[k][1], a[k].z);
+#pragma unroll
+                for (int k = 0; k < NCH; ++k)
+                    a[k].w = eq_iir(c[k], z[k][0], z[k][1], a[k].w);
+#pragma unroll
+                for (int k = 0; k < NCH; ++k)
+                    *reinterpret_cast<float4 *>(reinterpret_cast<unsigned char *>(sm.t[cur][ch0 + k]) + o) = a[k];
             }
             if ((blk & 3u) == 3u) { /* end of a fragment: NaN scrub (src/whirl.cpp:1624-1625) */
-                zl0 = isnan(zl0) ? 0.0f : zl0;
-                zl1 = isnan(zl1) ? 0.0f : zl1;
-                zr0 = isnan(zr0) ? 0.0f : zr0;
-                zr1 = isnan(zr1) ? 0.0f : zr1;
+#pragma unroll
+                for (int k = 0; k < NCH; ++k) {
+                    z[k][0] = isnan(z[k][0]) ? 0.0f : z[k][0];
+                    z[k][1] = isnan(z[k][1]) ? 0.0f : z[k][1];
+                }
             }
         }
         fence_async_smem(); /* this lane's writes, before the TMA store reads them */
         __syncwarp();
         if (lane == 0) {
-            tma_tile_store(&maps.m32, blk * BLK, row_l, smem_u32(tl));
-            tma_tile_store(&maps.m32, blk * BLK, row_r, smem_u32(tr));
+#pragma unroll
+            for (int k = 0; k < NCH; ++k)
+                tma_tile_store(&maps.m32, blk * BLK, row[k], smem_u32(sm.t[cur][ch0 + k]));
             tma_store_commit();
         }
     }
     if (lane == 0)
         tma_store_wait_all();
     if (run) {
-        st->dr.iirz[0][0] = zl0;
-        st->dr.iirz[0][1] = zl1;
-        st->dr.iirz[1][0] = zr0;
-        st->dr.iirz[1][1] = zr1;
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+            st->dr.iirz[ch0 + k][0] = z[k][0];
+            st->dr.iirz[ch0 + k][1] = z[k][1];
+        }
     }
+}
+
+/* Stage D with TMA tiles: same arithmetic as tbf_stage_d.  TWO: one warp per channel. */
+template <bool TWO>
+__global__ void __launch_bounds__(TWO ? 64 : 32) tbf_stage_d_tma(const RenderParams p, const __grid_constant__ TileMaps maps)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    DTmaSmem &sm = *reinterpret_cast<DTmaSmem *>(smem_raw + (((raw + 1023u) & ~1023u) - raw));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t slot0 = blockIdx.x * 32;
+    const uint32_t slot = slot0 + lane;
+    const bool valid = slot < p.n_instances;
+
+    InstState *st = nullptr;
+    const DevWhirlTables *wh = p.wh;
+    if (valid) {
+        const uint32_t id = p.ids ? p.ids[slot] : p.id_base + slot;
+        st = p.states + id;
+        wh = p.wh + st->tg.whTables;
+    }
+    const bool run = valid && !wh->bypass;
+    if (!__any_sync(FULL, run))
+        return; /* every organ of the warp has its Leslie bypassed: nothing to filter */
+    if (TWO)
+        d_channel_role<1>(p, maps, sm, lane, slot0, run, st, wh, warp, warp);
+    else
+        d_channel_role<2>(p, maps, sm, lane, slot0, run, st, wh, 0, 0);
 }
 
 #ifndef M_THREADS
@@ -3648,7 +3702,11 @@ bool tbf_stage_r_rotors_apart(const RenderParams &p)
 int tbf_launch_stage_rot(const RenderParams &p, void *stream)
 {
     const uint32_t grid = (p.n_instances + 31) / 32;
-    tbf_stage_rot_tma<<<grid, 32, sizeof(RotSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+    static const bool one_warp = getenv("TBF_ROT_WARPS") && atoi(getenv("TBF_ROT_WARPS")) == 1;
+    if (one_warp)
+        tbf_stage_rot_tma<false><<<grid, 32, sizeof(RotSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+    else
+        tbf_stage_rot_tma<true><<<grid, 64, sizeof(RotSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
     debug_sync(stream, "R (rotors)");
     return (int)cudaGetLastError();
 }
@@ -3719,8 +3777,11 @@ int tbf_launch_stage_d(const RenderParams &p, void *stream)
     if (int rc = set_smem(tbf_stage_d, sizeof(DSmem), have))
         return rc;
     const uint32_t grid = (p.n_instances + 31) / 32;
-    if (p.tile_maps)
-        tbf_stage_d_tma<<<grid, 32, sizeof(DTmaSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+    static const bool one_warp = getenv("TBF_D_WARPS") && atoi(getenv("TBF_D_WARPS")) == 1;
+    if (p.tile_maps && one_warp)
+        tbf_stage_d_tma<false><<<grid, 32, sizeof(DTmaSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
+    else if (p.tile_maps)
+        tbf_stage_d_tma<true><<<grid, 64, sizeof(DTmaSmem) + 1024, (cudaStream_t)stream>>>(p, *p.tile_maps);
     else
         tbf_stage_d<<<grid, 32, sizeof(DSmem), (cudaStream_t)stream>>>(p);
     debug_sync(stream, "D");
