@@ -549,30 +549,51 @@ def run_gpu_arm(a):
         barrier()
         link_gbs = ctx.measure_d2h(1 << 30, 8)  # ~8 GiB per rank: long enough to overlap on every rank
         barrier()
+        # the step's inputs (the events) wait in page-locked memory, like the outputs
+        ev_pinned = []
+
+        def pinned_events(ev_arr):
+            try:
+                evs, addr = engine.events_from_numpy_pinned(ctx, ev_arr)
+                ev_pinned.append(addr)
+                return evs
+            except MemoryError:
+                return engine.events_from_numpy(ev_arr)
+
         if slices == 1:
-            parts = [(n_frag, events)]
+            parts = [(n_frag, pinned_events(ev_np))]
         else:
             parts = []
             for k in range(slices):
                 lo, hi = bounds[k], bounds[k + 1]
                 sub = ev_np[(ev_np[:, 1] >= lo) & (ev_np[:, 1] < hi)].copy()
                 sub[:, 1] -= lo
-                parts.append((hi - lo, engine.events_from_numpy(sub)))
+                parts.append((hi - lo, pinned_events(sub)))
 
         e2e_count = [0]
 
+        e2e_split = [0.0, 0.0, 0.0]  # host seconds in prepare (event upload) | launch | synchronize
+
         def e2e_step():
             for nf_k, ev_k in parts:
+                ta = time.perf_counter()
                 ctx.prepare(n_inst, nf_k, ev_k, e2e_flags, hl.ctypes.data, hr.ctypes.data, slice_frames,
                             ids=ids)
+                tb = time.perf_counter()
                 ctx.launch()
+                tc = time.perf_counter()
                 ctx.synchronize()
+                td = time.perf_counter()
+                e2e_split[0] += tb - ta
+                e2e_split[1] += tc - tb
+                e2e_split[2] += td - tc
                 e2e_count[0] += ctx.last_launch_ms()[1]
 
         for _ in range(e2e_warm):
             e2e_step()
         barrier()
         e2e_count[0] = 0
+        e2e_split[:] = [0.0, 0.0, 0.0]
         t0 = time.perf_counter()
         for _ in range(a.steps):
             e2e_step()
@@ -586,6 +607,9 @@ def run_gpu_arm(a):
                "host_layout": "chunk-major [chunk][organ][%d samples] (TBF_RENDER_OUT_CHUNKED)" % (hchunk * 128)
                               if chunked else "[organ][sample]",
                "time_slices": slices,
+               "host_ms_per_step": {"prepare": 1e3 * e2e_split[0] / a.steps, "launch": 1e3 * e2e_split[1] / a.steps,
+                                    "synchronize": 1e3 * e2e_split[2] / a.steps,
+                                    "link_alone": 1e3 * 2 * n_inst * frames * 4 / 1e9 / link_gbs if link_gbs > 0 else None},
                "peak_abs_sample": float(np.abs(host_rows(hl, 0, slice_frames)).max())}
         # audio bytes over the link per second against the link's own contiguous-copy rate
         link_min = -max_over_ranks(-link_gbs)
@@ -608,6 +632,9 @@ def run_gpu_arm(a):
         if pl:
             ctx.host_free(pl)
             ctx.host_free(pr)
+        parts = None
+        for addr in ev_pinned:
+            ctx.host_free(addr)
 
     if parity is not None and dist is not None:  # mismatches of every rank's sampled organs
         keys = ["device_resident_mismatches"] + (["e2e_mismatches"] if "e2e_mismatches" in parity else [])

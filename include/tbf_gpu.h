@@ -329,6 +329,9 @@ int tbf_gpu_render_batch_launch(tbf_ctx *ctx, const tbf_batch_desc *desc);
 int tbf_gpu_synchronize(tbf_ctx *ctx);
 void *tbf_gpu_host_alloc(tbf_ctx *ctx, size_t bytes);
 void tbf_gpu_host_free(tbf_ctx *ctx, void *p);
+/* fragments per device -> host staging chunk: get returns what TBF_RENDER_OUT_CHUNKED cuts the
+ * caller's buffers by (32 unless set); set applies to both host layouts (the row layout's default is
+ * 125) */
 int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments);
 uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx);
 /* page-locked host buffer options (tbf_gpu_host_alloc2): write-combined pages are faster for the

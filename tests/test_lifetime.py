@@ -195,3 +195,60 @@ def test_two_contexts_in_one_process(ref):
         ctx.close()
     for cfg in want:
         want[cfg][3].close()
+
+
+def test_event_list_checks_and_the_threaded_event_index(gpu_ctx):
+    """tbf_gpu_batch_prepare rejects event lists that are not sorted by (slot, fragment) or name a slot /
+    fragment outside the batch, and its per-slot index is the same whether one thread builds it or
+    several do (lists of 2^18 events and more are cut into ranges): one batch of 330 000 events against
+    the same organs rendered as two batches of half the organs."""
+    tt, wt = tables.InstanceSpec(seed=2).build()
+    tg, wh = gpu_ctx.tonegen_tables(tt), gpu_ctx.whirl_tables(wt)
+    tables.free_tables(tt, wt)
+    n, n_frag = 44, 300
+    a = gpu_ctx.create_instances(tg, wh, n)
+    on, off = cabi.EV_KEY_ON, cabi.EV_KEY_OFF
+    for bad in ([[0, 5, on, 30, 0], [0, 4, off, 30, 0]],            # fragments go back inside a slot
+                [[0, 0, on, 30, 0], [0, n_frag, off, 30, 0]],       # fragment past the end
+                [[1, 0, on, 30, 0], [0, 1, off, 30, 0]],            # slots go back
+                [[0, 0, on, 30, 0], [2, 1, off, 30, 0]]):           # slot past the batch
+        with pytest.raises(engine.TbfError):
+            gpu_ctx.render(2, n_frag, engine.events_from_numpy(np.array(bad, dtype=np.int32)),
+                           cabi.RENDER_WHIRLPROC3, ids=[a, a + 1])
+    good = np.array([[0, 0, on, 30, 0], [0, 5, off, 30, 0], [1, 5, on, 31, 0]], dtype=np.int32)
+    gpu_ctx.render(2, n_frag, engine.events_from_numpy(good), cabi.RENDER_WHIRLPROC3, ids=[a, a + 1])
+    gpu_ctx.destroy_instances(a, n)
+
+    rng = np.random.RandomState(5)
+    per = 7500                                   # events per organ: 44 x 7500 = 330 000 > 2^18
+    rows = []
+    for g in range(n):
+        if g in (0, 17):                         # organs without any event, first and in the middle
+            continue
+        fr = np.sort(rng.randint(0, n_frag, per))
+        ev = np.empty((per, 5), dtype=np.int32)
+        ev[:, 0], ev[:, 1] = g, fr
+        ev[:, 2] = cabi.EV_DRAWBAR
+        ev[:, 3] = rng.randint(0, 27, per)
+        ev[:, 4] = rng.randint(0, 9, per)
+        ev[:40, 1], ev[:40, 2] = 0, cabi.EV_KEY_ON
+        ev[:40, 3] = np.concatenate([rng.choice(61, 20, replace=False), 64 + rng.choice(61, 20, replace=False)])
+        ev[:40, 4] = 0
+        rows.append(ev)
+    ev_all = np.concatenate(rows)
+    assert ev_all.shape[0] >= (1 << 18)
+    a = gpu_ctx.create_instances(tg, wh, n)
+    l0, r0 = gpu_ctx.render(n, n_frag, engine.events_from_numpy(ev_all), cabi.RENDER_WHIRLPROC3,
+                            ids=list(range(a, a + n)))
+    gpu_ctx.destroy_instances(a, n)
+    assert np.abs(l0[1]).max() > 0.01 and np.abs(l0[0]).max() < 1e-9   # organ 0 never plays a key
+    b = gpu_ctx.create_instances(tg, wh, n)
+    h = n // 2
+    for lo, hi in ((0, h), (h, n)):
+        sub = ev_all[(ev_all[:, 0] >= lo) & (ev_all[:, 0] < hi)].copy()
+        sub[:, 0] -= lo
+        assert sub.shape[0] < (1 << 18)
+        l1, r1 = gpu_ctx.render(hi - lo, n_frag, engine.events_from_numpy(sub), cabi.RENDER_WHIRLPROC3,
+                                ids=list(range(b + lo, b + hi)))
+        assert np.array_equal(_bits(l1), _bits(l0[lo:hi])) and np.array_equal(_bits(r1), _bits(r0[lo:hi]))
+    gpu_ctx.destroy_instances(b, n)

@@ -15,6 +15,7 @@
 #include <chrono>
 #include <map>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "tbf_device.h"
@@ -204,7 +205,13 @@ struct tbf_ctx {
     tbf_batch_desc prepared{};
     bool has_prepared = false, prepared_has_ids = false;
     uint32_t prepared_chunk = 0;
-    uint32_t host_chunk_fragments = 125; /* 1/3 s of audio per staging chunk */
+    /* fragments per device -> host staging chunk.  0 = not set by the caller: 32 (one stage launch)
+     * for the chunk-major layout, whose chunks are single contiguous copies -- the first one leaves
+     * after one stage launch instead of four -- and 125 (1/3 s) for the row layout, whose strided
+     * copies want long rows (config 3 through host buffers, same run: chunk-major 136.8 k organ-s/s
+     * with 32, 132.3 k with 125; rows 117.5 k with 32, 128.3 k with 125) */
+    uint32_t host_chunk_fragments = 0;
+    uint32_t host_chunk(bool chunked) const { return host_chunk_fragments ? host_chunk_fragments : chunked ? 32u : 125u; }
     int prepared_ring = 512; /* stage W's shared-memory ring: the largest the batch's whirl sets need */
     uint32_t prepared_tg_sets = 0; /* distinct tone-generator table sets among the batch's organs */
     cudaStream_t copy_stream = nullptr, copy_stream2 = nullptr; /* left / right channel */
@@ -1381,6 +1388,70 @@ extern "C" {
 /* Validate a batch, upload its events / ids and reset the per-slot event cursors.
  * The prepared batch can then be launched (and re-launched: the instances simply
  * keep playing) without touching the host data again. */
+/* Events must come sorted by (slot, fragment); start[s] = index of the first event of a slot >= s
+ * (start[n_instances] = n_events).  One compare of a 64-bit key per event; the list is cut into
+ * ranges for a few threads, because at millions of events per batch the pass is bound by one core's
+ * memory bandwidth and it is host time inside every end-to-end step.  Returns what is wrong, or null. */
+static const char *event_csr(const tbf_event *ev, uint64_t n_events, uint32_t n_instances, uint32_t n_fragments,
+                             uint64_t *start)
+{
+    static const char *const unsorted = "render: events not sorted by (slot, fragment)";
+    static const char *const range = "render: event slot or fragment out of range";
+    struct Part {
+        bool sorted = true, bad_slot = false;
+        uint32_t frag_max = 0;
+    };
+    auto scan = [&](uint64_t lo, uint64_t hi, Part *r) {
+        uint32_t prev_slot = lo ? ev[lo - 1].instance : 0;
+        uint64_t prev_key = lo ? (((uint64_t)ev[lo - 1].instance << 32) | ev[lo - 1].fragment) : 0;
+        bool sorted = true;
+        uint32_t frag_max = 0;
+        for (uint64_t e = lo; e < hi; ++e) {
+            const uint32_t slot = ev[e].instance, frag = ev[e].fragment;
+            const uint64_t key = ((uint64_t)slot << 32) | frag;
+            sorted = sorted && key >= prev_key;
+            prev_key = key;
+            frag_max = frag > frag_max ? frag : frag_max;
+            if (slot != prev_slot) {
+                if (slot < prev_slot || slot >= n_instances) { /* nothing is written past the array */
+                    r->bad_slot = true;
+                    r->sorted = sorted && slot > prev_slot;
+                    return;
+                }
+                for (uint32_t s = prev_slot + 1; s <= slot; ++s)
+                    start[s] = e;
+                prev_slot = slot;
+            }
+        }
+        r->sorted = sorted;
+        r->frag_max = frag_max;
+    };
+    start[0] = 0;
+    const unsigned hw = std::thread::hardware_concurrency();
+    const unsigned n_thr = n_events < (1u << 18) ? 1u : std::min(8u, std::max(1u, hw));
+    std::vector<Part> parts(n_thr);
+    if (n_thr == 1) {
+        scan(0, n_events, &parts[0]);
+    } else {
+        std::vector<std::thread> thr;
+        for (unsigned t = 0; t < n_thr; ++t)
+            thr.emplace_back(scan, n_events * t / n_thr, n_events * (t + 1) / n_thr, &parts[t]);
+        for (auto &t : thr)
+            t.join();
+    }
+    for (const Part &r : parts) { /* the same verdicts, in the same order, as one pass in sequence */
+        if (!r.sorted)
+            return unsorted;
+        if (r.bad_slot || r.frag_max >= n_fragments)
+            return range;
+    }
+    if (n_events && ev[0].instance >= n_instances)
+        return range;
+    for (uint32_t s = (n_events ? ev[n_events - 1].instance : 0) + 1; s <= n_instances; ++s)
+        start[s] = n_events;
+    return nullptr;
+}
+
 int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
 {
     if (!ctx || !d)
@@ -1450,26 +1521,18 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
         }
         ctx->prepared_tg_sets = sets;
     }
-    /* events: sorted by (slot, fragment); build the per-slot CSR */
-    std::vector<uint64_t> &evs = ctx->ev_start_host;
-    evs.assign((size_t)d->n_instances + 1, 0);
-    {
-        uint32_t prev_slot = 0, prev_frag = 0;
-        for (uint64_t e = 0; e < d->n_events; ++e) {
-            const tbf_event &ev = d->events[e];
-            if (ev.instance >= d->n_instances || ev.fragment >= d->n_fragments)
-                return fail(ctx, TBF_ERR_ARG, "render: event slot or fragment out of range");
-            if (ev.instance < prev_slot || (ev.instance == prev_slot && ev.fragment < prev_frag))
-                return fail(ctx, TBF_ERR_ARG, "render: events not sorted by (slot, fragment)");
-            prev_slot = ev.instance;
-            prev_frag = ev.fragment;
-            evs[ev.instance + 1]++;
-        }
-        for (uint32_t i = 0; i < d->n_instances; ++i)
-            evs[i + 1] += evs[i];
-    }
+    /* the events start crossing the link while the host checks them and builds the per-slot CSR */
     CK(cudaSetDevice(ctx->device));
     CK(grow(&ctx->d_events, &ctx->cap_events, std::max<uint64_t>(1, d->n_events)));
+    if (d->n_events)
+        CK(cudaMemcpyAsync(ctx->d_events, d->events, sizeof(tbf_event) * d->n_events,
+                           cudaMemcpyHostToDevice, ctx->stream));
+    std::vector<uint64_t> &evs = ctx->ev_start_host;
+    evs.resize((size_t)d->n_instances + 1);
+    if (const char *why = event_csr(d->events, d->n_events, d->n_instances, d->n_fragments, evs.data())) {
+        cudaStreamSynchronize(ctx->stream); /* the caller may free the events once we return */
+        return fail(ctx, TBF_ERR_ARG, why);
+    }
     if ((size_t)d->n_instances + 1 > ctx->cap_slots) {
         size_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
         CK(grow(&ctx->d_ev_start, &c0, (size_t)d->n_instances + 1));
@@ -1484,8 +1547,8 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     uint32_t chunk = d->n_fragments;
     if (!no_out && !dev_out) {
         chunk = (d->flags & TBF_RENDER_OUT_CHUNKED)
-                    ? ctx->host_chunk_fragments /* the caller's layout is cut by this number */
-                    : std::min<uint32_t>(d->n_fragments, ctx->host_chunk_fragments);
+                    ? ctx->host_chunk(true) /* the caller's layout is cut by this number */
+                    : std::min<uint32_t>(d->n_fragments, ctx->host_chunk(false));
         const size_t planes = (d->flags & TBF_RENDER_STEMS) ? 6 : 2; /* L R (+ HL HR DL DR) */
         const size_t need = (size_t)2 /*buffers*/ * planes * d->n_instances * chunk * TBF_FRAGMENT;
         cudaError_t e = grow(&ctx->d_out, &ctx->cap_out, need);
@@ -1495,9 +1558,6 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
             return TBF_ERR_NOMEM;
         }
     }
-    if (d->n_events)
-        CK(cudaMemcpyAsync(ctx->d_events, d->events, sizeof(tbf_event) * d->n_events,
-                           cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->d_ev_start, evs.data(), sizeof(uint64_t) * evs.size(),
                        cudaMemcpyHostToDevice, ctx->stream));
     if (d->instance_ids)
@@ -2028,7 +2088,7 @@ int tbf_gpu_set_host_chunk(tbf_ctx *ctx, uint32_t fragments)
     return TBF_OK;
 }
 
-uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx) { return ctx ? ctx->host_chunk_fragments : 0; }
+uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx) { return ctx ? ctx->host_chunk(true) : 0; }
 
 int tbf_gpu_export_state(tbf_ctx *ctx, uint32_t instance, tbf_state_export *o)
 {

@@ -121,6 +121,18 @@ def events_from_numpy(ev):
     return arr, n
 
 
+def events_from_numpy_pinned(ctx, ev):
+    """As events_from_numpy, the array in page-locked memory of `ctx` (a plain DMA instead of a staged
+    copy when the batch is prepared) -> ((array, n), address for ctx.host_free)."""
+    ev = np.ascontiguousarray(ev, dtype=np.int32)
+    n = ev.shape[0]
+    host, addr = ctx.host_alloc((max(1, n) * C.sizeof(cabi.Event),), dtype=np.uint8)
+    if n:
+        C.memmove(addr, ev.ctypes.data, n * C.sizeof(cabi.Event))
+    arr = (cabi.Event * max(1, n)).from_address(addr)
+    return (arr, n), addr
+
+
 def checksum_host(out_l, out_r):
     """The kernel's position-keyed additive hash of one instance's L/R bit patterns."""
     def mix(x):
@@ -260,7 +272,8 @@ class Context:
         d.n_fragments = n_fragments
         keep = []
         if ids is not None:
-            ida = (C.c_uint32 * n_instances)(*[int(i) for i in ids])
+            ida = (C.c_uint32 * n_instances).from_buffer_copy(
+                np.ascontiguousarray(np.asarray(ids, dtype=np.uint32)[:n_instances]))
             keep.append(ida)
             d.instance_ids = ida
         if isinstance(events, tuple):
