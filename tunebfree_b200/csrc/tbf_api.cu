@@ -1842,7 +1842,8 @@ int tbf_gpu_batch_launch(tbf_ctx *ctx)
                     ctx->err = std::string("stage kernel launch: ") + cudaGetErrorString((cudaError_t)rc);
                     return TBF_ERR_CUDA;
                 }
-                ctx->launches += n_stages + (whirl ? 1 : 0); /* stage D is two kernels */
+                /* stage D is two kernels (D, M); the rotors are one more when they run apart */
+                ctx->launches += n_stages + (whirl ? 1 : 0) + (whirl && tbf_stage_r_rotors_apart(p) ? 1 : 0);
             }
             if (host_out) {
                 CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->sdone[g][last][par], 0));
