@@ -339,6 +339,13 @@ uint32_t tbf_gpu_get_host_chunk(const tbf_ctx *ctx);
  * socket) without touching it                                                                  */
 #define TBF_HOST_WRITE_COMBINED 0x1
 void *tbf_gpu_host_alloc2(tbf_ctx *ctx, size_t bytes, unsigned flags);
+/* What tbf_gpu_batch_prepare does with a batch's event list before anything reaches the device, for
+ * callers that want to check a list ahead of time (needs no context and no GPU): the events must be
+ * sorted by (slot, fragment) with slot < n_instances and fragment < n_fragments; start[s] receives
+ * the index of the first event of a slot >= s, start[n_instances] = n_events (n_instances + 1
+ * entries).  TBF_OK, or TBF_ERR_ARG with *why (may be null) naming the rule that was broken.      */
+int tbf_gpu_event_index(const tbf_event *events, uint64_t n_events, uint32_t n_instances,
+                        uint32_t n_fragments, uint64_t *start, const char **why);
 /* device -> host link ceiling of this context's GPU: plain 1-D page-locked cudaMemcpyAsync of
  * `bytes`, `reps` timed passes after one untimed, the mean rate in GB/s                        */
 int tbf_gpu_measure_d2h(tbf_ctx *ctx, size_t bytes, int reps, double *gbs);

@@ -1,10 +1,12 @@
 """CPU-side checks of the C-ABI boundary: the library loads, exports every symbol
 include/tbf_gpu.h declares, and the ctypes mirror matches the C struct sizes.
-No compute calls (no GPU here)."""
+No device calls (no GPU here); the host-side event check of tbf_gpu_batch_prepare runs through
+tbf_gpu_event_index."""
 import ctypes as C
 import os
 import re
 
+import numpy as np
 import pytest
 
 from tunebfree_b200 import cabi, engine
@@ -123,3 +125,55 @@ def test_no_contracted_packed_fma_in_kernels():
 def test_sass_guards_on_the_gpu_box():
     """the same guards in the -m gpu set: what ran on the GPU is what was checked"""
     _check_sass()
+
+
+def _random_event_list(rng, n_events, n_inst, n_frag):
+    slot = np.sort(rng.randint(0, n_inst, n_events))
+    frag = rng.randint(0, n_frag, n_events)
+    order = np.lexsort((frag, slot))
+    ev = np.zeros((n_events, 5), dtype=np.int32)
+    ev[:, 0], ev[:, 1] = slot[order], frag[order]
+    ev[:, 2] = cabi.EV_DRAWBAR
+    return ev
+
+
+@pytest.mark.parametrize("n_events", [0, 1, 1000, (1 << 18) - 1, (1 << 18) + 12345, 1500000])
+def test_event_index_matches_numpy(n_events):
+    """tbf_gpu_event_index (what tbf_gpu_batch_prepare runs on the host; from 2^18 events on in ranges
+    on several threads): start[s] = first event of a slot >= s, for lists with empty slots at both ends."""
+    rng = np.random.RandomState(n_events % 1000 + 1)
+    n_inst, n_frag = 4099, 3750
+    ev = _random_event_list(rng, n_events, n_inst, n_frag)
+    if n_events > 10:
+        ev = ev[(ev[:, 0] > 2) & (ev[:, 0] < n_inst - 3) & (ev[:, 0] != 2000)]   # slots nobody names
+    start = engine.event_index(ev, n_inst, n_frag)
+    want = np.searchsorted(ev[:, 0], np.arange(n_inst + 1), side="left").astype(np.uint64)
+    assert np.array_equal(start, want)
+
+
+def test_event_index_names_the_broken_rule():
+    rng = np.random.RandomState(3)
+    n_inst, n_frag = 64, 500
+    for n_events in (200, 400000):          # one thread | several
+        ev = _random_event_list(rng, n_events, n_inst, n_frag)
+        engine.event_index(ev, n_inst, n_frag)
+        for where in (0, n_events // 3, n_events - 1):
+            bad = ev.copy()
+            bad[where, 1] = n_frag                       # a fragment past the batch
+            bad = bad[np.lexsort((bad[:, 1], bad[:, 0]))]
+            with pytest.raises(engine.TbfError, match="out of range"):
+                engine.event_index(bad, n_inst, n_frag)
+        bad = ev.copy()
+        bad[-1, 0] = n_inst                              # a slot past the batch
+        with pytest.raises(engine.TbfError, match="out of range"):
+            engine.event_index(bad, n_inst, n_frag)
+        for where in (1, n_events // 2, n_events - 1):
+            bad = ev.copy()
+            k = where
+            while k > 0 and (bad[k, 0], bad[k, 1]) == (bad[k - 1, 0], bad[k - 1, 1]):
+                k -= 1
+            if k == 0:
+                continue
+            bad[[k - 1, k]] = bad[[k, k - 1]]            # two neighbours swapped
+            with pytest.raises(engine.TbfError, match="not sorted"):
+                engine.event_index(bad, n_inst, n_frag)

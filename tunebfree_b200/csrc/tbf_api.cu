@@ -1452,6 +1452,19 @@ static const char *event_csr(const tbf_event *ev, uint64_t n_events, uint32_t n_
     return nullptr;
 }
 
+int tbf_gpu_event_index(const tbf_event *events, uint64_t n_events, uint32_t n_instances,
+                        uint32_t n_fragments, uint64_t *start, const char **why)
+{
+    const char *w = nullptr;
+    if (!start || !n_instances || !n_fragments || (n_events && !events))
+        w = "event_index: null argument or empty batch";
+    else
+        w = event_csr(events, n_events, n_instances, n_fragments, start);
+    if (why)
+        *why = w;
+    return w ? TBF_ERR_ARG : TBF_OK;
+}
+
 int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
 {
     if (!ctx || !d)

@@ -88,6 +88,8 @@ def lib():
         L.tbf_gpu_host_alloc2.argtypes = [vp, C.c_size_t, C.c_uint]
         L.tbf_gpu_host_alloc2.restype = C.c_void_p
         L.tbf_gpu_measure_d2h.argtypes = [vp, C.c_size_t, C.c_int, C.POINTER(C.c_double)]
+        L.tbf_gpu_event_index.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
+                                          C.POINTER(C.c_uint64), C.POINTER(C.c_char_p)]
         _lib = L
     return _lib
 
@@ -119,6 +121,19 @@ def events_from_numpy(ev):
     if n:
         C.memmove(arr, ev.ctypes.data, n * C.sizeof(cabi.Event))
     return arr, n
+
+
+def event_index(ev, n_instances, n_fragments):
+    """tbf_gpu_event_index on an [n, 5] int32 array: the per-slot start indices (n_instances + 1), or
+    TbfError naming the rule the list breaks.  Needs no GPU."""
+    ev = np.ascontiguousarray(ev, dtype=np.int32).reshape(-1, 5)
+    start = np.zeros(n_instances + 1, dtype=np.uint64)
+    why = C.c_char_p()
+    rc = lib().tbf_gpu_event_index(ev.ctypes.data, ev.shape[0], n_instances, n_fragments,
+                                   start.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(why))
+    if rc != 0:
+        raise TbfError(rc, (why.value or b"").decode())
+    return start
 
 
 def events_from_numpy_pinned(ctx, ev):
