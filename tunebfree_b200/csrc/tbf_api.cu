@@ -1537,15 +1537,17 @@ int tbf_gpu_batch_prepare(tbf_ctx *ctx, const tbf_batch_desc *d)
     /* the events start crossing the link while the host checks them and builds the per-slot CSR */
     CK(cudaSetDevice(ctx->device));
     CK(grow(&ctx->d_events, &ctx->cap_events, std::max<uint64_t>(1, d->n_events)));
+    struct DrainOnReturn { /* the caller may free its arrays once we return, on every path */
+        cudaStream_t s;
+        ~DrainOnReturn() { cudaStreamSynchronize(s); }
+    } drain{ctx->stream};
     if (d->n_events)
         CK(cudaMemcpyAsync(ctx->d_events, d->events, sizeof(tbf_event) * d->n_events,
                            cudaMemcpyHostToDevice, ctx->stream));
     std::vector<uint64_t> &evs = ctx->ev_start_host;
     evs.resize((size_t)d->n_instances + 1);
-    if (const char *why = event_csr(d->events, d->n_events, d->n_instances, d->n_fragments, evs.data())) {
-        cudaStreamSynchronize(ctx->stream); /* the caller may free the events once we return */
+    if (const char *why = event_csr(d->events, d->n_events, d->n_instances, d->n_fragments, evs.data()))
         return fail(ctx, TBF_ERR_ARG, why);
-    }
     if ((size_t)d->n_instances + 1 > ctx->cap_slots) {
         size_t c0 = 0, c1 = 0, c2 = 0, c3 = 0;
         CK(grow(&ctx->d_ev_start, &c0, (size_t)d->n_instances + 1));
